@@ -1,0 +1,194 @@
+"""ctypes binding of the CPU oracle (oracle/liboracle.so).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and the
+cpu_baseline / --impl reference legs of bench.py.  The product package never imports it.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_DIR, "liboracle.so")
+P = 0xFFFFFFFF00000001
+u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+
+
+def build(force=False):
+    srcs = [os.path.join(_DIR, f) for f in ("plonky2_oracle.c", "plonky2_fri_oracle.c", "plonky2_oracle.h",
+                                              "poseidon_rc.h", "Makefile")]
+    if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
+        subprocess.check_call(["make", "-C", _DIR, "-s"])
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_SO)
+        L = _lib
+        for name in ("orc_add", "orc_sub", "orc_mul", "orc_pow"):
+            getattr(L, name).restype = C.c_uint64
+            getattr(L, name).argtypes = [C.c_uint64, C.c_uint64]
+        L.orc_inv.restype = C.c_uint64
+        L.orc_inv.argtypes = [C.c_uint64]
+        L.orc_root_of_unity.restype = C.c_uint64
+        L.orc_root_of_unity.argtypes = [C.c_int]
+        L.orc_reverse_bits.restype = C.c_uint64
+        L.orc_reverse_bits.argtypes = [C.c_uint64, C.c_int]
+        L.orc_round_constants.restype = C.POINTER(C.c_uint64)
+        L.orc_num_threads.restype = C.c_int
+    return _lib
+
+
+def _a(x):
+    return np.ascontiguousarray(x, dtype=np.uint64)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def fft(a):
+    a = _a(a).copy()
+    lib().orc_fft(_ptr(a), C.c_int(int(np.log2(a.size))))
+    return a
+
+
+def ifft(a):
+    a = _a(a).copy()
+    lib().orc_ifft(_ptr(a), C.c_int(int(np.log2(a.size))))
+    return a
+
+
+def coset_fft(a, shift=7):
+    a = _a(a).copy()
+    lib().orc_coset_fft(_ptr(a), C.c_int(int(np.log2(a.size))), C.c_uint64(shift))
+    return a
+
+
+def lde(coeffs, rate_bits, shift=7):
+    coeffs = _a(coeffs)
+    out = np.empty(coeffs.size << rate_bits, dtype=np.uint64)
+    lib().orc_lde(_ptr(coeffs), C.c_int(int(np.log2(coeffs.size))), C.c_int(rate_bits), C.c_uint64(shift), _ptr(out))
+    return out
+
+
+def poseidon(states):
+    """Permute one (12,) state or a batch (n, 12)."""
+    s = _a(states).copy()
+    flat = s.reshape(-1, 12)
+    for i in range(flat.shape[0]):
+        lib().orc_poseidon(C.c_void_p(flat[i].ctypes.data))
+    return s
+
+
+def hash_no_pad(x):
+    x = _a(x)
+    out = np.empty(4, dtype=np.uint64)
+    lib().orc_hash_no_pad(_ptr(x), C.c_size_t(x.size), _ptr(out))
+    return out
+
+
+def hash_or_noop(x):
+    x = _a(x)
+    out = np.empty(4, dtype=np.uint64)
+    lib().orc_hash_or_noop(_ptr(x), C.c_size_t(x.size), _ptr(out))
+    return out
+
+
+def two_to_one(l, r):
+    l, r = _a(l), _a(r)
+    out = np.empty(4, dtype=np.uint64)
+    lib().orc_two_to_one(_ptr(l), _ptr(r), _ptr(out))
+    return out
+
+
+def n_digest_words(log_leaves, cap_height):
+    return 4 * 2 * ((1 << log_leaves) - (1 << cap_height))
+
+
+def merkle_build(leaves, cap_height):
+    """leaves: (n_leaves, leaf_len) row-major.  Returns (digests level-order (k,4), cap (2^cap,4))."""
+    leaves = _a(leaves)
+    n, w = leaves.shape
+    log_leaves = int(np.log2(n))
+    assert 1 << log_leaves == n, "leaf count must be a power of two"
+    digests = np.zeros(n_digest_words(log_leaves, cap_height) if cap_height <= log_leaves else 0, dtype=np.uint64)
+    cap = np.zeros(4 << min(cap_height, 62), dtype=np.uint64) if cap_height <= log_leaves else np.zeros(4, np.uint64)
+    rc = lib().orc_merkle_build(_ptr(leaves), C.c_int(log_leaves), C.c_size_t(w), C.c_int(cap_height),
+                                _ptr(digests) if digests.size else None, _ptr(cap))
+    if rc != 0:
+        raise ValueError("cap_height %d > log2(leaves) %d" % (cap_height, log_leaves))
+    return digests.reshape(-1, 4), cap.reshape(-1, 4)
+
+
+def merkle_prove(digests, log_leaves, cap_height, leaf_index):
+    digests = _a(digests)
+    sib = np.zeros(4 * (log_leaves - cap_height), dtype=np.uint64)
+    rc = lib().orc_merkle_prove(_ptr(digests), C.c_int(log_leaves), C.c_int(cap_height), C.c_size_t(leaf_index),
+                                _ptr(sib))
+    if rc != 0:
+        raise ValueError("bad leaf index")
+    return sib.reshape(-1, 4)
+
+
+def merkle_verify(leaf, leaf_index, siblings, cap):
+    leaf, siblings, cap = _a(leaf), _a(siblings), _a(cap)
+    cap_height = int(np.log2(cap.size // 4))
+    return bool(lib().orc_merkle_verify(_ptr(leaf), C.c_size_t(leaf.size), C.c_size_t(leaf_index), _ptr(siblings),
+                                        C.c_int(siblings.size // 4), _ptr(cap), C.c_int(cap_height)))
+
+
+def merkle_digests_to_plonky2(digests, log_leaves, cap_height):
+    digests = _a(digests)
+    out = np.zeros_like(digests)
+    if digests.size:
+        lib().orc_merkle_digests_to_plonky2(_ptr(digests), C.c_int(log_leaves), C.c_int(cap_height), _ptr(out))
+    return out
+
+
+def batch_from_values(values, rate_bits, cap_height, salt=None, want=("coeffs", "leaves", "digests"), from_coeffs=False):
+    """values: (n_cols, n) column-major witness.  Returns dict(coeffs, leaves, digests, cap)."""
+    values = _a(values)
+    n_cols, n = values.shape
+    log_n = int(np.log2(n))
+    assert 1 << log_n == n
+    nb = n << rate_bits
+    n_salt = 0 if salt is None else salt.shape[0]
+    salt = None if salt is None else _a(salt)
+    out = {}
+    coeffs = np.empty_like(values) if ("coeffs" in want and not from_coeffs) else None
+    leaves = np.empty((nb, n_cols + n_salt), dtype=np.uint64) if "leaves" in want else None
+    nd = n_digest_words(log_n + rate_bits, cap_height)
+    digests = np.zeros(nd, dtype=np.uint64) if ("digests" in want and nd > 0) else None
+    cap = np.zeros(4 << cap_height, dtype=np.uint64)
+    L = lib()
+    if from_coeffs:
+        rc = L.orc_batch_from_coeffs(_ptr(values), C.c_int(log_n), C.c_int(n_cols), C.c_int(rate_bits),
+                                     C.c_int(cap_height), _ptr(salt), C.c_int(n_salt), _ptr(leaves), _ptr(digests),
+                                     _ptr(cap))
+    else:
+        rc = L.orc_batch_from_values(_ptr(values), C.c_int(log_n), C.c_int(n_cols), C.c_int(rate_bits),
+                                     C.c_int(cap_height), _ptr(salt), C.c_int(n_salt), _ptr(coeffs), _ptr(leaves),
+                                     _ptr(digests), _ptr(cap))
+    if rc != 0:
+        raise ValueError("orc_batch_from_values failed rc=%d" % rc)
+    out["coeffs"] = values if from_coeffs else coeffs
+    out["leaves"] = leaves
+    out["digests"] = None if digests is None else digests.reshape(-1, 4)
+    out["cap"] = cap.reshape(-1, 4)
+    return out
+
+
+def num_threads():
+    return lib().orc_num_threads()
+
+
+def set_num_threads(n):
+    lib().orc_set_num_threads(C.c_int(n))

@@ -1,0 +1,92 @@
+/* plonky2_oracle.h -- CPU restatement of the plonky2 commitment phase.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing in the shipped product path may include,
+ * link or call this file: only tests/, __graft_entry__.smoke() and the
+ * cpu_baseline / --impl reference legs of bench.py use it, and only as the checker
+ * or as the timed CPU arm.
+ *
+ * PARITY STATUS: "parity unpinned" against the reference's own prover.  The
+ * reference mount (/root/reference) holds no source and no
+ * Rust toolchain exists here, so this file restates the PUBLIC plonky2 algorithm
+ *  from the upstream files named beside each function.
+ * What IS pinned: the Poseidon permutation against plonky2's published
+ * known-answer vectors (hash/poseidon_goldilocks.rs `check_test_vectors`),
+ * field constants, and NTT/Merkle/FRI self-consistency (naive evaluation,
+ * proof verification, a FRI verifier restatement).
+ *
+ * All field elements are canonical little-endian u64 (< p = 2^64 - 2^32 + 1).
+ * Extension elements F_p[x]/(x^2-7) are two consecutive u64 [c0, c1].
+ */
+#ifndef PLONKY2_ORACLE_H
+#define PLONKY2_ORACLE_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORC_P 0xFFFFFFFF00000001ULL
+
+/* ---- field (plonky2 field/src/goldilocks_field.rs, extension/quadratic.rs) ---- */
+uint64_t orc_add(uint64_t a, uint64_t b);
+uint64_t orc_sub(uint64_t a, uint64_t b);
+uint64_t orc_mul(uint64_t a, uint64_t b);
+uint64_t orc_pow(uint64_t a, uint64_t e);
+uint64_t orc_inv(uint64_t a);
+uint64_t orc_root_of_unity(int log_n);          /* primitive 2^log_n-th root */
+void orc_ext_mul(const uint64_t a[2], const uint64_t b[2], uint64_t out[2]);
+void orc_ext_inv(const uint64_t a[2], uint64_t out[2]);
+
+/* ---- FFT family (field/src/fft.rs, field/src/polynomial/mod.rs) ---- */
+void orc_fft(uint64_t *a, int log_n);                       /* natural in, natural out */
+void orc_ifft(uint64_t *a, int log_n);
+void orc_coset_fft(uint64_t *a, int log_n, uint64_t shift); /* a_j *= shift^j ; fft */
+/* PolynomialCoeffs::lde(rate_bits).coset_fft(shift): out has 2^(log_n+rate_bits) entries */
+void orc_lde(const uint64_t *coeffs, int log_n, int rate_bits, uint64_t shift, uint64_t *out);
+/* strided variants for extension polynomials stored interleaved [c0,c1,...] */
+void orc_fft_strided(uint64_t *a, int log_n, size_t stride);
+uint64_t orc_reverse_bits(uint64_t x, int bits);
+
+/* ---- Poseidon (hash/poseidon.rs, poseidon_goldilocks.rs, hashing.rs) ---- */
+void orc_poseidon(uint64_t state[12]);
+void orc_hash_no_pad(const uint64_t *in, size_t len, uint64_t out[4]);
+void orc_hash_or_noop(const uint64_t *in, size_t len, uint64_t out[4]);
+void orc_two_to_one(const uint64_t l[4], const uint64_t r[4], uint64_t out[4]);
+const uint64_t *orc_round_constants(void);
+
+/* ---- Merkle tree (hash/merkle_tree.rs, merkle_proofs.rs) ----
+ * leaves: row-major n_leaves x leaf_len.  digests (level order, leaf level first):
+ * level k has (n_leaves >> k) digests of 4 words, for k = 0 .. log_leaves-cap_height-1.
+ * Total words = 4 * 2 * (n_leaves - 2^cap_height).  cap: 2^cap_height x 4 words.
+ * Returns 0, or -1 on invalid arguments (upstream panics). */
+int orc_merkle_build(const uint64_t *leaves, int log_leaves, size_t leaf_len, int cap_height,
+                     uint64_t *digests, uint64_t *cap);
+/* siblings bottom-up, (log_leaves - cap_height) x 4 words */
+int orc_merkle_prove(const uint64_t *digests, int log_leaves, int cap_height, size_t leaf_index,
+                     uint64_t *siblings);
+/* 1 if the proof verifies against cap, else 0 */
+int orc_merkle_verify(const uint64_t *leaf, size_t leaf_len, size_t leaf_index,
+                      const uint64_t *siblings, int n_siblings, const uint64_t *cap, int cap_height);
+/* level-order digests -> plonky2's recursive `digests` Vec layout (merkle_tree.rs fill_subtree) */
+void orc_merkle_digests_to_plonky2(const uint64_t *level_digests, int log_leaves, int cap_height,
+                                   uint64_t *out);
+
+/* ---- PolynomialBatch::from_values / from_coeffs (fri/oracle.rs) ----
+ * values/coeffs: column-major n_cols x 2^log_n.  salt (optional, blinding): 4 x 2^(log_n+rate_bits)
+ * column-major LDE-domain salt columns appended after the real columns (upstream draws them at random).
+ * leaves: row-major 2^(log_n+rate_bits) x (n_cols + n_salt), rows in bit-reversed order.
+ * Any output pointer except cap may be NULL.  */
+int orc_batch_from_values(const uint64_t *values, int log_n, int n_cols, int rate_bits,
+                          int cap_height, const uint64_t *salt, int n_salt, uint64_t *coeffs,
+                          uint64_t *leaves, uint64_t *digests, uint64_t *cap);
+int orc_batch_from_coeffs(const uint64_t *coeffs, int log_n, int n_cols, int rate_bits,
+                          int cap_height, const uint64_t *salt, int n_salt, uint64_t *leaves,
+                          uint64_t *digests, uint64_t *cap);
+
+int orc_num_threads(void);
+void orc_set_num_threads(int n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
