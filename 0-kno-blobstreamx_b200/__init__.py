@@ -1,0 +1,30 @@
+"""blobstreamx_b200 -- B200-native plonky2 commitment core (host-side mirror over the C ABI).
+
+The product is `csrc/libbsx_b200.so` (hand-written sm_100a CUDA behind `include/bsx_b200.h`).
+This package is the thin host mirror of the plonky2 interface the BlobstreamX prover calls on
+its hot path -- `PolynomialBatch::from_values / from_coeffs / get_lde_values`, `MerkleTree::new /
+get / prove` and `fri_proof` -- with the same names, argument meaning and error behaviour
+(plonky2 panics -> Python exceptions), bound with ctypes.  The reference's host language is Rust,
+which this image does not have; INTEGRATION.md carries the Rust shim.
+
+There is NO CPU fallback: importing works anywhere (so the ABI can be checked on a CPU box),
+but creating a `Context` without a CUDA device, or without the built library, raises.
+
+The directory name (`0-kno-blobstreamx_b200`) is not a Python identifier; load it with
+`__graft_entry__.load_package()` which registers it as `blobstreamx_b200`.
+"""
+from .binding import (  # noqa: F401
+    BSX_DEVICE,
+    BSX_HOST,
+    BsxError,
+    Context,
+    MerkleTree,
+    PolynomialBatch,
+    Timing,
+    lib,
+    library_path,
+    EXPORTED_SYMBOLS,
+)
+from .fri import FriConfig, FriParams, fri_reduction_arity_bits  # noqa: F401
+
+P = 0xFFFFFFFF00000001

@@ -1,0 +1,334 @@
+"""ctypes binding of include/bsx_b200.h and the plonky2-shaped host classes on top of it."""
+import ctypes as C
+import os
+
+import numpy as np
+
+BSX_HOST, BSX_DEVICE = 0, 1
+_DIR = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_DIR, "csrc", "libbsx_b200.so")
+
+# every symbol include/bsx_b200.h declares (checked by tests/test_abi.py against the header text)
+EXPORTED_SYMBOLS = [
+    "bsx_version", "bsx_device_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
+    "bsx_ctx_sync", "bsx_batch_from_values", "bsx_batch_from_coeffs", "bsx_batch_free", "bsx_batch_cap",
+    "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
+    "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
+    "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
+    "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_ntt",
+]
+
+
+class BsxError(RuntimeError):
+    """A non-zero status from the C ABI (upstream plonky2 would panic)."""
+
+
+class Timing(C.Structure):
+    _fields_ = [("h2d_ms", C.c_float), ("ifft_ms", C.c_float), ("lde_ms", C.c_float), ("leaf_hash_ms", C.c_float),
+                ("tree_ms", C.c_float), ("total_ms", C.c_float)]
+
+    def as_dict(self):
+        return {k: float(getattr(self, k)) for k, _ in self._fields_}
+
+
+def library_path():
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    """Load libbsx_b200.so.  Raises if it has not been built: there is no fallback path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_SO):
+        raise BsxError("libbsx_b200.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "or `make -C 0-kno-blobstreamx_b200/csrc`); there is no CPU fallback")
+    L = C.CDLL(_SO)
+    vp, i32, u64, sz = C.c_void_p, C.c_int32, C.c_uint64, C.c_size_t
+    pp = C.POINTER(C.c_void_p)
+    sig = {
+        "bsx_version": (C.c_char_p, []),
+        "bsx_device_count": (i32, []),
+        "bsx_ctx_create": (i32, [i32, pp]),
+        "bsx_ctx_destroy": (None, [vp]),
+        "bsx_last_error": (C.c_char_p, [vp]),
+        "bsx_ctx_stream": (vp, [vp]),
+        "bsx_ctx_sync": (i32, [vp]),
+        "bsx_batch_from_values": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
+        "bsx_batch_from_coeffs": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
+        "bsx_batch_free": (None, [vp]),
+        "bsx_batch_cap": (i32, [vp, vp]),
+        "bsx_batch_tree": (vp, [vp]),
+        "bsx_batch_get_lde_values": (i32, [vp, u64, u64, vp]),
+        "bsx_batch_coeffs": (i32, [vp, vp, i32]),
+        "bsx_batch_export": (i32, [vp, vp, vp, vp]),
+        "bsx_batch_shape": (i32, [vp] + [C.POINTER(i32)] * 5),
+        "bsx_batch_lde_device": (vp, [vp]),
+        "bsx_batch_digests_device": (vp, [vp]),
+        "bsx_merkle_new": (i32, [vp, vp, i32, i32, i32, i32, pp]),
+        "bsx_merkle_new_colmajor_device": (i32, [vp, vp, sz, i32, i32, i32, pp]),
+        "bsx_merkle_free": (None, [vp]),
+        "bsx_merkle_cap": (i32, [vp, vp]),
+        "bsx_merkle_get": (i32, [vp, vp, i32, vp]),
+        "bsx_merkle_prove": (i32, [vp, u64, vp]),
+        "bsx_merkle_digests": (i32, [vp, vp]),
+        "bsx_merkle_shape": (i32, [vp] + [C.POINTER(i32)] * 3),
+        "bsx_poseidon_permute": (i32, [vp, vp, i32, sz]),
+        "bsx_ntt": (i32, [vp, vp, i32, i32, i32, i32, u64]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def _np(a):
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+def _ptr(a):
+    """Host numpy array or raw integer address -> c_void_p."""
+    if a is None:
+        return None
+    if isinstance(a, (int, np.integer)):
+        return C.c_void_p(int(a))
+    return C.c_void_p(a.ctypes.data)
+
+
+def _log2_strict(n):
+    """plonky2_util::log2_strict: panics unless n is a power of two."""
+    if n <= 0 or n & (n - 1):
+        raise BsxError("Not a power of two: %d" % n)
+    return n.bit_length() - 1
+
+
+class Context:
+    """One per (host thread, device): owns a CUDA stream, twiddle tables and the memory pool."""
+
+    def __init__(self, device=0):
+        self._h = None
+        L = lib()
+        h = C.c_void_p()
+        rc = L.bsx_ctx_create(int(device), C.byref(h))
+        if rc != 0:
+            raise BsxError("bsx_ctx_create(device=%d) failed with %d: no usable CUDA device "
+                           "(this library has no CPU fallback)" % (device, rc))
+        self._h = h
+        self.device = int(device)
+
+    def check(self, rc):
+        if rc != 0:
+            raise BsxError("%s (code %d)" % (lib().bsx_last_error(self._h).decode(), rc))
+
+    @property
+    def stream(self):
+        return lib().bsx_ctx_stream(self._h)
+
+    def sync(self):
+        self.check(lib().bsx_ctx_sync(self._h))
+
+    def close(self):
+        if self._h is not None:
+            lib().bsx_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- test hooks
+    def poseidon_permute(self, states):
+        s = _np(states).copy()
+        flat = s.reshape(-1, 12)
+        self.check(lib().bsx_poseidon_permute(self._h, _ptr(flat), BSX_HOST, flat.shape[0]))
+        return s
+
+    def ntt(self, cols, kind="fft", shift=7):
+        """cols: (n_cols, n) column vectors; natural order in and out."""
+        a = _np(cols).copy()
+        two_d = a.reshape(-1, a.shape[-1])
+        k = {"fft": 0, "ifft": 1, "coset_fft": 2}[kind]
+        self.check(lib().bsx_ntt(self._h, _ptr(two_d), BSX_HOST, _log2_strict(two_d.shape[1]), two_d.shape[0], k,
+                                 C.c_uint64(shift)))
+        return a
+
+
+class MerkleTree:
+    """plonky2 hash/merkle_tree.rs `MerkleTree<GoldilocksField, PoseidonHash>`, device resident."""
+
+    def __init__(self, ctx, leaves=None, cap_height=0, _handle=None, _owner=None):
+        """`MerkleTree::new(leaves, cap_height)`; leaves: (n_leaves, leaf_len) row-major."""
+        self.ctx = ctx
+        self._owner = _owner  # a PolynomialBatch keeping the handle alive
+        if _handle is not None:
+            self._h = _handle
+            return
+        self._h = None
+        leaves = _np(leaves)
+        if leaves.ndim != 2:
+            raise BsxError("leaves must be (n_leaves, leaf_len)")
+        log_leaves = _log2_strict(leaves.shape[0])
+        h = C.c_void_p()
+        ctx.check(lib().bsx_merkle_new(ctx._h, _ptr(leaves), BSX_HOST, log_leaves, leaves.shape[1], int(cap_height),
+                                       C.byref(h)))
+        self._h = h
+
+    @classmethod
+    def from_device_colmajor(cls, ctx, dev_ptr, col_stride, log_leaves, leaf_len, cap_height):
+        h = C.c_void_p()
+        ctx.check(lib().bsx_merkle_new_colmajor_device(ctx._h, C.c_void_p(int(dev_ptr)), int(col_stride),
+                                                       int(log_leaves), int(leaf_len), int(cap_height), C.byref(h)))
+        return cls(ctx, _handle=h)
+
+    def shape(self):
+        a, b, c = C.c_int32(), C.c_int32(), C.c_int32()
+        self.ctx.check(lib().bsx_merkle_shape(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    @property
+    def cap(self):
+        _, _, ch = self.shape()
+        out = np.zeros((1 << ch, 4), dtype=np.uint64)
+        self.ctx.check(lib().bsx_merkle_cap(self._h, _ptr(out)))
+        return out
+
+    def get(self, leaf_index):
+        """`MerkleTree::get(i)` for one index or a list of indices."""
+        _, leaf_len, _ = self.shape()
+        idx = _np(np.atleast_1d(leaf_index))
+        out = np.zeros((idx.size, leaf_len), dtype=np.uint64)
+        self.ctx.check(lib().bsx_merkle_get(self._h, _ptr(idx), idx.size, _ptr(out)))
+        return out[0] if np.isscalar(leaf_index) else out
+
+    def prove(self, leaf_index):
+        """`MerkleTree::prove(leaf_index).siblings`, bottom-up."""
+        log_leaves, _, ch = self.shape()
+        out = np.zeros((log_leaves - ch, 4), dtype=np.uint64)
+        self.ctx.check(lib().bsx_merkle_prove(self._h, C.c_uint64(int(leaf_index)), _ptr(out)))
+        return out
+
+    @property
+    def digests(self):
+        """`MerkleTree.digests` in plonky2's Vec layout."""
+        log_leaves, _, ch = self.shape()
+        out = np.zeros((2 * ((1 << log_leaves) - (1 << ch)), 4), dtype=np.uint64)
+        self.ctx.check(lib().bsx_merkle_digests(self._h, _ptr(out)))
+        return out
+
+    def close(self):
+        if self._h is not None and self._owner is None:
+            lib().bsx_merkle_free(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class PolynomialBatch:
+    """plonky2 fri/oracle.rs `PolynomialBatch<GoldilocksField, PoseidonGoldilocksConfig, 2>`."""
+
+    def __init__(self, ctx, handle, timing=None):
+        self.ctx = ctx
+        self._h = handle
+        self.timing = timing
+
+    @staticmethod
+    def _build(fn, ctx, cols, rate_bits, blinding, cap_height, salt, device_ptr, shape, timing):
+        if device_ptr is not None:
+            n_cols, n = shape
+            src, mem = C.c_void_p(int(device_ptr)), BSX_DEVICE
+        else:
+            cols = _np(cols)
+            if cols.ndim != 2:
+                raise BsxError("expected (n_cols, n) column vectors")
+            n_cols, n = cols.shape
+            src, mem = _ptr(cols), BSX_HOST
+        log_n = _log2_strict(n)
+        if salt is not None and mem == BSX_HOST:
+            salt = _np(salt)
+        h = C.c_void_p()
+        t = Timing() if timing else None
+        ctx.check(fn(ctx._h, src, mem, log_n, n_cols, int(rate_bits), int(cap_height), 1 if blinding else 0,
+                     _ptr(salt), C.byref(h), C.byref(t) if t is not None else None))
+        return PolynomialBatch(ctx, h, t)
+
+    @classmethod
+    def from_values(cls, ctx, values, rate_bits, blinding, cap_height, salt=None, device_ptr=None, shape=None,
+                    timing=False):
+        """`PolynomialBatch::from_values(values, rate_bits, blinding, cap_height, timing, fft_root_table)`.
+        values: (n_cols, n) -- one row per PolynomialValues.  `device_ptr`/`shape` pass a device buffer."""
+        return cls._build(lib().bsx_batch_from_values, ctx, values, rate_bits, blinding, cap_height, salt,
+                          device_ptr, shape, timing)
+
+    @classmethod
+    def from_coeffs(cls, ctx, coeffs, rate_bits, blinding, cap_height, salt=None, device_ptr=None, shape=None,
+                    timing=False):
+        """`PolynomialBatch::from_coeffs(polynomials, rate_bits, blinding, cap_height, timing, fft_root_table)`."""
+        return cls._build(lib().bsx_batch_from_coeffs, ctx, coeffs, rate_bits, blinding, cap_height, salt,
+                          device_ptr, shape, timing)
+
+    def shape(self):
+        v = [C.c_int32() for _ in range(5)]
+        self.ctx.check(lib().bsx_batch_shape(self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("degree_log", "n_cols", "rate_bits", "cap_height", "n_salt"), [x.value for x in v]))
+
+    @property
+    def merkle_tree(self):
+        return MerkleTree(self.ctx, _handle=C.c_void_p(lib().bsx_batch_tree(self._h)), _owner=self)
+
+    @property
+    def cap(self):
+        sh = self.shape()
+        out = np.zeros((1 << sh["cap_height"], 4), dtype=np.uint64)
+        self.ctx.check(lib().bsx_batch_cap(self._h, _ptr(out)))
+        return out
+
+    @property
+    def polynomials(self):
+        """Coefficient vectors in natural order, (n_cols, n)."""
+        sh = self.shape()
+        out = np.zeros((sh["n_cols"], 1 << sh["degree_log"]), dtype=np.uint64)
+        self.ctx.check(lib().bsx_batch_coeffs(self._h, _ptr(out), BSX_HOST))
+        return out
+
+    def get_lde_values(self, index, step=1):
+        """`PolynomialBatch::get_lde_values(index, step)`: leaf reverse_bits(index*step), salt stripped."""
+        out = np.zeros(self.shape()["n_cols"], dtype=np.uint64)
+        self.ctx.check(lib().bsx_batch_get_lde_values(self._h, C.c_uint64(int(index)), C.c_uint64(int(step)),
+                                                      _ptr(out)))
+        return out
+
+    def export(self, coeffs=True, leaves=True, digests=True):
+        sh = self.shape()
+        n, nb = 1 << sh["degree_log"], 1 << (sh["degree_log"] + sh["rate_bits"])
+        w = sh["n_cols"] + sh["n_salt"]
+        c = np.zeros((sh["n_cols"], n), dtype=np.uint64) if coeffs else None
+        lv = np.zeros((nb, w), dtype=np.uint64) if leaves else None
+        d = np.zeros((2 * (nb - (1 << sh["cap_height"])), 4), dtype=np.uint64) if digests else None
+        self.ctx.check(lib().bsx_batch_export(self._h, _ptr(c), _ptr(lv), _ptr(d)))
+        return {"coeffs": c, "leaves": lv, "digests": d, "cap": self.cap}
+
+    @property
+    def lde_device_ptr(self):
+        return lib().bsx_batch_lde_device(self._h)
+
+    def close(self):
+        if self._h is not None:
+            lib().bsx_batch_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

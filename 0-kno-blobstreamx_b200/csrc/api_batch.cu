@@ -1,0 +1,509 @@
+// api_batch.cu -- PolynomialBatch and MerkleTree entry points of the C ABI.
+// Upstream: plonky2 fri/oracle.rs (from_values, from_coeffs, lde_values, get_lde_values),
+// hash/merkle_tree.rs (MerkleTree::new, get, prove).
+#include "api_internal.h"
+
+#include <cstring>
+
+static inline size_t n_digest_words(int log_leaves, int cap_height) {
+    return 4 * 2 * (((size_t)1 << log_leaves) - ((size_t)1 << cap_height));
+}
+
+// ------------------------------------------------------------------------------------ MerkleTree
+int bsx_tree_build(bsx_tree *t, cudaEvent_t ev_after_leaf_hash) {
+    bsx_ctx *ctx = t->ctx;
+    const size_t n = (size_t)1 << t->log_leaves;
+    const size_t cap_words = (size_t)4 << t->cap_height;
+    t->digests = nullptr;
+    t->cap_dev = nullptr;
+    TRY(bsx_alloc(ctx, &t->cap_dev, cap_words));
+    TRY(bsx_alloc(ctx, &t->digests, n_digest_words(t->log_leaves, t->cap_height)));
+    // cap_height == log2(leaves): the leaf digests are the cap (merkle_tree.rs fill_digests_buf)
+    u64 *leaf_digests = t->cap_height == t->log_leaves ? t->cap_dev : t->digests;
+    launch_leaf_hash(t->leaves, t->col_stride, t->leaf_len, n, leaf_digests, ctx->stream);
+    if (ev_after_leaf_hash) cudaEventRecord(ev_after_leaf_hash, ctx->stream);
+    launch_merkle_tree(t->digests, t->cap_dev, t->log_leaves, t->cap_height, ctx->stream);
+    CU(ctx, cudaGetLastError());
+    t->cap_host.resize(cap_words);
+    CU(ctx, cudaMemcpyAsync(t->cap_host.data(), t->cap_dev, cap_words * sizeof(u64), cudaMemcpyDeviceToHost,
+                            ctx->stream));
+    return BSX_OK;
+}
+
+void bsx_tree_release(bsx_tree *t) {
+    if (t->owns_leaves) bsx_free(t->ctx, (u64 *)t->leaves);
+    bsx_free(t->ctx, t->digests);
+    bsx_free(t->ctx, t->cap_dev);
+    t->leaves = nullptr;
+    t->digests = t->cap_dev = nullptr;
+}
+
+static int tree_check_shape(bsx_ctx *ctx, int log_leaves, int leaf_len, int cap_height) {
+    if (log_leaves < 0 || log_leaves > 40 || leaf_len < 0)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad tree shape: log_leaves=%d leaf_len=%d", log_leaves, leaf_len);
+    if (cap_height < 0 || cap_height > log_leaves)  // upstream: assert in MerkleTree::new
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG,
+                        "cap_height=%d should be at most log2(leaves.len())=%d", cap_height, log_leaves);
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_merkle_new(bsx_ctx *ctx, const uint64_t *leaves, int32_t mem, int32_t log_leaves,
+                                  int32_t leaf_len, int32_t cap_height, bsx_tree **out) {
+    if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    *out = nullptr;
+    TRY(tree_check_shape(ctx, log_leaves, leaf_len, cap_height));
+    if (!leaves && leaf_len > 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "leaves is NULL");
+    CU(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)1 << log_leaves, words = n * (size_t)leaf_len;
+    u64 *rowmajor = nullptr, *colmajor = nullptr;
+    const u64 *src = (const u64 *)leaves;
+    if (mem != BSX_DEVICE) {
+        TRY(bsx_alloc(ctx, &rowmajor, words));
+        TRY(bsx_copy_in(ctx, rowmajor, (const u64 *)leaves, words, mem));
+        src = rowmajor;
+    }
+    TRY(bsx_alloc(ctx, &colmajor, words));
+    launch_transpose(src, colmajor, n, (size_t)leaf_len, ctx->stream);
+    bsx_free(ctx, rowmajor);
+    bsx_tree *t = new bsx_tree();
+    t->ctx = ctx;
+    t->log_leaves = log_leaves;
+    t->leaf_len = leaf_len;
+    t->cap_height = cap_height;
+    t->leaves = colmajor;
+    t->col_stride = n;
+    t->owns_leaves = true;
+    t->embedded = false;
+    int rc = bsx_tree_build(t, nullptr);
+    if (rc == BSX_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+        rc = bsx_fail(ctx, BSX_ERR_CUDA, "merkle build failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc != BSX_OK) {
+        bsx_tree_release(t);
+        delete t;
+        return rc;
+    }
+    *out = t;
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_merkle_new_colmajor_device(bsx_ctx *ctx, const uint64_t *leaves_dev, size_t col_stride,
+                                                  int32_t log_leaves, int32_t leaf_len, int32_t cap_height,
+                                                  bsx_tree **out) {
+    if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    *out = nullptr;
+    TRY(tree_check_shape(ctx, log_leaves, leaf_len, cap_height));
+    if (col_stride < ((size_t)1 << log_leaves)) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "col_stride too small");
+    CU(ctx, cudaSetDevice(ctx->device));
+    bsx_tree *t = new bsx_tree();
+    t->ctx = ctx;
+    t->log_leaves = log_leaves;
+    t->leaf_len = leaf_len;
+    t->cap_height = cap_height;
+    t->leaves = (const u64 *)leaves_dev;
+    t->col_stride = col_stride;
+    t->owns_leaves = false;
+    t->embedded = false;
+    int rc = bsx_tree_build(t, nullptr);
+    if (rc == BSX_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+        rc = bsx_fail(ctx, BSX_ERR_CUDA, "merkle build failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc != BSX_OK) {
+        bsx_tree_release(t);
+        delete t;
+        return rc;
+    }
+    *out = t;
+    return BSX_OK;
+}
+
+extern "C" void bsx_merkle_free(bsx_tree *t) {
+    if (!t || t->embedded) return;
+    cudaSetDevice(t->ctx->device);
+    bsx_tree_release(t);
+    delete t;
+}
+
+extern "C" int32_t bsx_merkle_cap(const bsx_tree *t, uint64_t *out_host) {
+    if (!t || !out_host) return BSX_ERR_INVALID_ARG;
+    memcpy(out_host, t->cap_host.data(), t->cap_host.size() * sizeof(u64));
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_merkle_shape(const bsx_tree *t, int32_t *log_leaves, int32_t *leaf_len, int32_t *cap_height) {
+    if (!t) return BSX_ERR_INVALID_ARG;
+    if (log_leaves) *log_leaves = t->log_leaves;
+    if (leaf_len) *leaf_len = t->leaf_len;
+    if (cap_height) *cap_height = t->cap_height;
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_merkle_get(bsx_tree *t, const uint64_t *idx_host, int32_t k, uint64_t *out_host) {
+    if (!t || k < 0 || (k > 0 && (!idx_host || !out_host))) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = t->ctx;
+    if (k == 0 || t->leaf_len == 0) return BSX_OK;
+    for (int i = 0; i < k; i++)
+        if (idx_host[i] >> t->log_leaves)
+            return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "leaf index %llu out of range", (unsigned long long)idx_host[i]);
+    CU(ctx, cudaSetDevice(ctx->device));
+    u64 *idx_dev, *rows_dev;
+    TRY(bsx_alloc(ctx, &idx_dev, (size_t)k));
+    TRY(bsx_alloc(ctx, &rows_dev, (size_t)k * t->leaf_len));
+    CU(ctx, cudaMemcpyAsync(idx_dev, idx_host, (size_t)k * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+    launch_gather_rows(t->leaves, t->col_stride, t->leaf_len, idx_dev, k, rows_dev, ctx->stream);
+    CU(ctx, cudaMemcpyAsync(out_host, rows_dev, (size_t)k * t->leaf_len * sizeof(u64), cudaMemcpyDeviceToHost,
+                            ctx->stream));
+    bsx_free(ctx, idx_dev);
+    bsx_free(ctx, rows_dev);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_merkle_prove(bsx_tree *t, uint64_t leaf_index, uint64_t *siblings_host) {
+    if (!t) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = t->ctx;
+    if (leaf_index >> t->log_leaves)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "leaf index %llu out of range", (unsigned long long)leaf_index);
+    int levels = t->log_leaves - t->cap_height;
+    if (levels == 0) return BSX_OK;
+    if (!siblings_host) return BSX_ERR_INVALID_ARG;
+    CU(ctx, cudaSetDevice(ctx->device));
+    u64 *sib;
+    TRY(bsx_alloc(ctx, &sib, (size_t)4 * levels));
+    launch_gather_siblings(t->digests, t->log_leaves, levels, leaf_index, sib, ctx->stream);
+    CU(ctx, cudaMemcpyAsync(siblings_host, sib, (size_t)4 * levels * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    bsx_free(ctx, sib);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
+// level-order -> plonky2's recursive `digests` layout (merkle_tree.rs fill_subtree):
+// left recursive buffer || left child digest || right child digest || right recursive buffer.
+static void to_plonky2_layout(const u64 *lv, size_t n, int height, size_t node, u64 *buf, size_t buf_len) {
+    if (buf_len == 0) return;
+    size_t half = buf_len / 2, off = 0;
+    for (int k = 0; k < height - 1; k++) off += n >> k;
+    memcpy(buf + 4 * (half - 1), lv + 4 * (off + 2 * node), 4 * sizeof(u64));
+    memcpy(buf + 4 * half, lv + 4 * (off + 2 * node + 1), 4 * sizeof(u64));
+    to_plonky2_layout(lv, n, height - 1, 2 * node, buf, half - 1);
+    to_plonky2_layout(lv, n, height - 1, 2 * node + 1, buf + 4 * (half + 1), half - 1);
+}
+
+extern "C" int32_t bsx_merkle_digests(bsx_tree *t, uint64_t *out_host) {
+    if (!t) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = t->ctx;
+    size_t words = n_digest_words(t->log_leaves, t->cap_height);
+    if (words == 0) return BSX_OK;
+    if (!out_host) return BSX_ERR_INVALID_ARG;
+    CU(ctx, cudaSetDevice(ctx->device));
+    std::vector<u64> lv(words);
+    CU(ctx, cudaMemcpyAsync(lv.data(), t->digests, words * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    int height = t->log_leaves - t->cap_height;
+    size_t sub = ((size_t)2 << height) - 2, n = (size_t)1 << t->log_leaves;
+    for (size_t c = 0; c < ((size_t)1 << t->cap_height); c++)
+        to_plonky2_layout(lv.data(), n, height, c, (u64 *)out_host + 4 * c * sub, sub);
+    return BSX_OK;
+}
+
+// ------------------------------------------------------------------------------------ PolynomialBatch
+struct PhaseTimer {
+    cudaEvent_t ev[6];
+    bool on;
+    PhaseTimer(bool enable) : on(enable) {
+        if (on)
+            for (auto &e : ev) cudaEventCreate(&e);
+    }
+    ~PhaseTimer() {
+        if (on)
+            for (auto &e : ev) cudaEventDestroy(e);
+    }
+    void mark(int i, cudaStream_t st) {
+        if (on) cudaEventRecord(ev[i], st);
+    }
+    float ms(int i, int j) {
+        float t = 0;
+        cudaEventElapsedTime(&t, ev[i], ev[j]);
+        return t;
+    }
+};
+
+static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n_cols, int rate_bits, int cap_height,
+                       int blinding, const u64 *salt, bool input_is_coeffs, bsx_batch **out, bsx_timing *timing) {
+    if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    *out = nullptr;
+    if (log_n < 0 || log_n > 24)
+        return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "degree_log=%d outside the supported range [0, 24]", log_n);
+    if (rate_bits < 0 || rate_bits > 8 || log_n + rate_bits > 32)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad rate_bits=%d", rate_bits);
+    if (n_cols < 0 || n_cols > 65535) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad n_cols=%d", n_cols);
+    const int log_nb = log_n + rate_bits;
+    if (cap_height < 0 || cap_height > log_nb)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "cap_height=%d should be at most log2(leaves.len())=%d",
+                        cap_height, log_nb);
+    if (!input && n_cols > 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "input is NULL");
+    CU(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)1 << log_n, nb = (size_t)1 << log_nb;
+    const int n_salt = blinding ? BSX_SALT_SIZE : 0;
+    PhaseTimer pt(timing != nullptr);
+
+    bsx_batch *bt = new bsx_batch();
+    bt->ctx = ctx;
+    bt->log_n = log_n;
+    bt->n_cols = n_cols;
+    bt->n_salt = n_salt;
+    bt->rate_bits = rate_bits;
+    bt->coeffs = bt->lde = nullptr;
+    bt->tree.ctx = ctx;
+    bt->tree.leaves = nullptr;
+    bt->tree.digests = bt->tree.cap_dev = nullptr;
+    bt->tree.owns_leaves = false;
+    bt->tree.embedded = true;
+    int rc = BSX_OK;
+    do {
+        pt.mark(0, ctx->stream);
+        if ((rc = bsx_alloc(ctx, &bt->coeffs, n * n_cols))) break;
+        if ((rc = bsx_copy_in(ctx, bt->coeffs, input, n * n_cols, mem))) break;
+        pt.mark(1, ctx->stream);
+        int a, b;
+        bsx_split(log_n, &a, &b);
+        NttPlan plan;
+        plan.log_n = log_n;
+        plan.a = a;
+        plan.b = b;
+        if (!input_is_coeffs) {
+            // PolynomialValues::ifft per column, in place; result is stored bit-reversed
+            plan.inverse = 1;
+            plan.src_bitrev = 0;
+            plan.n_cosets = 1;
+            plan.pre_hi = plan.pre_lo = nullptr;
+            if ((rc = bsx_pow_table(ctx, log_n, 1, &plan.tw))) break;
+            plan.scale = gl_host_inv((u64)n % GL_P);
+            launch_ntt(ctx->tables, plan, bt->coeffs, n, bt->coeffs, n, n_cols, ctx->stream);
+            bt->coeffs_bitrev = true;
+        } else {
+            bt->coeffs_bitrev = false;
+        }
+        pt.mark(2, ctx->stream);
+        // lde_values: zero-pad + coset FFT(shift = 7) == 2^rate_bits coset transforms of size n
+        if ((rc = bsx_alloc(ctx, &bt->lde, nb * (size_t)(n_cols + n_salt)))) break;
+        plan.inverse = 0;
+        plan.src_bitrev = bt->coeffs_bitrev ? 1 : 0;
+        plan.n_cosets = 1 << rate_bits;
+        if ((rc = bsx_coset_tables(ctx, log_n, rate_bits, 7, &plan.pre_hi, &plan.pre_lo))) break;
+        if ((rc = bsx_pow_table(ctx, log_n, 0, &plan.tw))) break;
+        plan.scale = 1;
+        launch_ntt(ctx->tables, plan, bt->coeffs, n, bt->lde, nb, n_cols, ctx->stream);
+        if (n_salt) {
+            u64 *dst = bt->lde + nb * (size_t)n_cols;
+            if (salt) {
+                u64 *tmp = nullptr;
+                const u64 *src = salt;
+                if (mem != BSX_DEVICE) {
+                    if ((rc = bsx_alloc(ctx, &tmp, nb * n_salt))) break;
+                    if ((rc = bsx_copy_in(ctx, tmp, salt, nb * n_salt, mem))) break;
+                    src = tmp;
+                }
+                launch_bitrev_copy(src, nb, dst, nb, log_nb, n_salt, ctx->stream);
+                bsx_free(ctx, tmp);
+            } else {
+                launch_fill_random(dst, nb * n_salt, 0x5A17C0DEULL ^ (u64)(uintptr_t)bt, ctx->stream);
+            }
+        }
+        if (cudaGetLastError() != cudaSuccess) {
+            rc = bsx_fail(ctx, BSX_ERR_CUDA, "NTT launch failed");
+            break;
+        }
+        pt.mark(3, ctx->stream);
+        bt->tree.log_leaves = log_nb;
+        bt->tree.leaf_len = n_cols + n_salt;
+        bt->tree.cap_height = cap_height;
+        bt->tree.leaves = bt->lde;
+        bt->tree.col_stride = nb;
+        if ((rc = bsx_tree_build(&bt->tree, pt.on ? pt.ev[4] : nullptr))) break;
+        pt.mark(5, ctx->stream);
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) {
+            rc = bsx_fail(ctx, BSX_ERR_CUDA, "commit failed: %s", cudaGetErrorString(e));
+            break;
+        }
+    } while (0);
+    if (rc != BSX_OK) {
+        bsx_tree_release(&bt->tree);
+        bsx_free(ctx, bt->coeffs);
+        bsx_free(ctx, bt->lde);
+        delete bt;
+        return rc;
+    }
+    if (timing) {
+        timing->h2d_ms = pt.ms(0, 1);
+        timing->ifft_ms = pt.ms(1, 2);
+        timing->lde_ms = pt.ms(2, 3);
+        timing->leaf_hash_ms = pt.ms(3, 4);
+        timing->tree_ms = pt.ms(4, 5);
+        timing->total_ms = pt.ms(0, 5);
+    }
+    *out = bt;
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_batch_from_values(bsx_ctx *ctx, const uint64_t *values, int32_t mem, int32_t log_n,
+                                         int32_t n_cols, int32_t rate_bits, int32_t cap_height, int32_t blinding,
+                                         const uint64_t *salt, bsx_batch **out, bsx_timing *timing) {
+    return batch_build(ctx, (const u64 *)values, mem, log_n, n_cols, rate_bits, cap_height, blinding,
+                       (const u64 *)salt, false, out, timing);
+}
+extern "C" int32_t bsx_batch_from_coeffs(bsx_ctx *ctx, const uint64_t *coeffs, int32_t mem, int32_t log_n,
+                                         int32_t n_cols, int32_t rate_bits, int32_t cap_height, int32_t blinding,
+                                         const uint64_t *salt, bsx_batch **out, bsx_timing *timing) {
+    return batch_build(ctx, (const u64 *)coeffs, mem, log_n, n_cols, rate_bits, cap_height, blinding,
+                       (const u64 *)salt, true, out, timing);
+}
+
+extern "C" void bsx_batch_free(bsx_batch *b) {
+    if (!b) return;
+    cudaSetDevice(b->ctx->device);
+    bsx_tree_release(&b->tree);
+    bsx_free(b->ctx, b->coeffs);
+    bsx_free(b->ctx, b->lde);
+    delete b;
+}
+
+extern "C" int32_t bsx_batch_cap(const bsx_batch *b, uint64_t *out_host) {
+    return b ? bsx_merkle_cap(&b->tree, out_host) : BSX_ERR_INVALID_ARG;
+}
+extern "C" bsx_tree *bsx_batch_tree(bsx_batch *b) { return b ? &b->tree : nullptr; }
+extern "C" const uint64_t *bsx_batch_lde_device(const bsx_batch *b) { return b ? (const uint64_t *)b->lde : nullptr; }
+extern "C" const uint64_t *bsx_batch_digests_device(const bsx_batch *b) {
+    return b ? (const uint64_t *)b->tree.digests : nullptr;
+}
+extern "C" int32_t bsx_batch_shape(const bsx_batch *b, int32_t *log_n, int32_t *n_cols, int32_t *rate_bits,
+                                   int32_t *cap_height, int32_t *n_salt) {
+    if (!b) return BSX_ERR_INVALID_ARG;
+    if (log_n) *log_n = b->log_n;
+    if (n_cols) *n_cols = b->n_cols;
+    if (rate_bits) *rate_bits = b->rate_bits;
+    if (cap_height) *cap_height = b->tree.cap_height;
+    if (n_salt) *n_salt = b->n_salt;
+    return BSX_OK;
+}
+
+static inline u64 host_bitrev(u64 x, int bits) {
+    u64 r = 0;
+    for (int i = 0; i < bits; i++) r |= ((x >> i) & 1ULL) << (bits - 1 - i);
+    return r;
+}
+
+// fri/oracle.rs get_lde_values: &merkle_tree.leaves[reverse_bits(index * step, degree_log + rate_bits)]
+// [..len - salt_size]
+extern "C" int32_t bsx_batch_get_lde_values(bsx_batch *b, uint64_t index, uint64_t step, uint64_t *out_host) {
+    if (!b) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = b->ctx;
+    int log_nb = b->log_n + b->rate_bits;
+    u64 i = index * step;
+    if (i >> log_nb) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "index * step out of range");
+    if (b->n_cols == 0) return BSX_OK;
+    u64 leaf = host_bitrev(i, log_nb);
+    CU(ctx, cudaSetDevice(ctx->device));
+    u64 *idx_dev, *row_dev;
+    TRY(bsx_alloc(ctx, &idx_dev, 1));
+    TRY(bsx_alloc(ctx, &row_dev, (size_t)b->n_cols));
+    CU(ctx, cudaMemcpyAsync(idx_dev, &leaf, sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+    launch_gather_rows(b->lde, (size_t)1 << log_nb, b->n_cols, idx_dev, 1, row_dev, ctx->stream);
+    CU(ctx, cudaMemcpyAsync(out_host, row_dev, (size_t)b->n_cols * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream));
+    bsx_free(ctx, idx_dev);
+    bsx_free(ctx, row_dev);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_batch_coeffs(bsx_batch *b, uint64_t *out, int32_t mem) {
+    if (!b || (!out && b->n_cols > 0)) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = b->ctx;
+    size_t n = (size_t)1 << b->log_n, words = n * (size_t)b->n_cols;
+    if (words == 0) return BSX_OK;
+    CU(ctx, cudaSetDevice(ctx->device));
+    if (b->coeffs_bitrev) {
+        u64 *tmp;
+        TRY(bsx_alloc(ctx, &tmp, words));
+        launch_bitrev_copy(b->coeffs, n, tmp, n, b->log_n, b->n_cols, ctx->stream);
+        TRY(bsx_copy_out(ctx, (u64 *)out, tmp, words, mem));
+        bsx_free(ctx, tmp);
+    } else {
+        TRY(bsx_copy_out(ctx, (u64 *)out, b->coeffs, words, mem));
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_batch_export(bsx_batch *b, uint64_t *coeffs_host, uint64_t *leaves_host,
+                                    uint64_t *digests_host) {
+    if (!b) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = b->ctx;
+    if (coeffs_host) TRY(bsx_batch_coeffs(b, coeffs_host, BSX_HOST));
+    if (leaves_host) {
+        size_t nb = (size_t)1 << (b->log_n + b->rate_bits), w = (size_t)(b->n_cols + b->n_salt);
+        if (nb * w) {
+            CU(ctx, cudaSetDevice(ctx->device));
+            u64 *tmp;
+            TRY(bsx_alloc(ctx, &tmp, nb * w));
+            // LDE viewed as a (w x nb) row-major matrix -> (nb x w) row-major leaves
+            launch_transpose(b->lde, tmp, w, nb, ctx->stream);
+            TRY(bsx_copy_out(ctx, (u64 *)leaves_host, tmp, nb * w, BSX_HOST));
+            bsx_free(ctx, tmp);
+            CU(ctx, cudaStreamSynchronize(ctx->stream));
+        }
+    }
+    if (digests_host) TRY(bsx_merkle_digests(&b->tree, digests_host));
+    return BSX_OK;
+}
+
+// ------------------------------------------------------------------------------------ test hooks
+extern "C" int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n) {
+    if (!ctx || (!states && n)) return BSX_ERR_INVALID_ARG;
+    if (n == 0) return BSX_OK;
+    CU(ctx, cudaSetDevice(ctx->device));
+    u64 *d = (u64 *)states;
+    if (mem != BSX_DEVICE) {
+        TRY(bsx_alloc(ctx, &d, n * 12));
+        TRY(bsx_copy_in(ctx, d, (const u64 *)states, n * 12, mem));
+    }
+    launch_poseidon_permute(d, n, ctx->stream);
+    CU(ctx, cudaGetLastError());
+    if (mem != BSX_DEVICE) {
+        TRY(bsx_copy_out(ctx, (u64 *)states, d, n * 12, mem));
+        bsx_free(ctx, d);
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t log_n, int32_t n_cols, int32_t kind,
+                           uint64_t shift) {
+    if (!ctx || (!data && n_cols > 0)) return BSX_ERR_INVALID_ARG;
+    if (log_n < 0 || log_n > 24) return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "log_n=%d outside [0, 24]", log_n);
+    if (kind < 0 || kind > 2 || n_cols < 0 || n_cols > 65535) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad kind/n_cols");
+    if (n_cols == 0) return BSX_OK;
+    CU(ctx, cudaSetDevice(ctx->device));
+    size_t n = (size_t)1 << log_n, words = n * (size_t)n_cols;
+    u64 *buf, *tmp;
+    TRY(bsx_alloc(ctx, &buf, words));
+    TRY(bsx_alloc(ctx, &tmp, words));
+    TRY(bsx_copy_in(ctx, buf, (const u64 *)data, words, mem));
+    NttPlan plan;
+    plan.log_n = log_n;
+    bsx_split(log_n, &plan.a, &plan.b);
+    plan.inverse = kind == 1;
+    plan.src_bitrev = 0;
+    plan.n_cosets = 1;
+    plan.pre_hi = plan.pre_lo = nullptr;
+    if (kind == 2) TRY(bsx_coset_tables(ctx, log_n, 0, shift % GL_P, &plan.pre_hi, &plan.pre_lo));
+    TRY(bsx_pow_table(ctx, log_n, plan.inverse, &plan.tw));
+    plan.scale = plan.inverse ? gl_host_inv((u64)n % GL_P) : 1;
+    launch_ntt(ctx->tables, plan, buf, n, buf, n, n_cols, ctx->stream);
+    launch_bitrev_copy(buf, n, tmp, n, log_n, n_cols, ctx->stream);
+    CU(ctx, cudaGetLastError());
+    TRY(bsx_copy_out(ctx, (u64 *)data, tmp, words, mem));
+    bsx_free(ctx, buf);
+    bsx_free(ctx, tmp);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}

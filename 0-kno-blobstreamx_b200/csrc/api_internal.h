@@ -1,0 +1,80 @@
+// api_internal.h -- host-side structs behind the opaque handles of include/bsx_b200.h.
+#pragma once
+#include <map>
+#include <utility>
+#include <vector>
+
+#include "../../include/bsx_b200.h"
+#include "gl.cuh"
+#include "internal.h"
+
+struct CosetKey {
+    int log_n, r_log;
+    u64 shift;
+    bool operator<(const CosetKey &o) const {
+        if (log_n != o.log_n) return log_n < o.log_n;
+        if (r_log != o.r_log) return r_log < o.r_log;
+        return shift < o.shift;
+    }
+};
+
+struct bsx_ctx {
+    int device;
+    cudaStream_t stream;
+    char err[512];
+    NttTables tables;
+    std::map<int, PowTable> pow_tables;
+    std::map<CosetKey, std::pair<const u64 *, const u64 *>> coset_tables;
+};
+
+// plonky2 hash/merkle_tree.rs MerkleTree { leaves, digests, cap }, device resident.
+struct bsx_tree {
+    bsx_ctx *ctx;
+    int log_leaves, leaf_len, cap_height;
+    const u64 *leaves;  // column-major: (row, col) at leaves[col * col_stride + row]
+    size_t col_stride;
+    bool owns_leaves;
+    u64 *digests;  // level order, leaf digests first; 2 * (n_leaves - 2^cap_height) digests
+    u64 *cap_dev;  // 2^cap_height digests
+    std::vector<u64> cap_host;
+    bool embedded;  // lives inside a bsx_batch
+};
+
+// plonky2 fri/oracle.rs PolynomialBatch { polynomials, merkle_tree, degree_log, rate_bits, blinding }
+struct bsx_batch {
+    bsx_ctx *ctx;
+    int log_n, n_cols, n_salt, rate_bits;
+    u64 *coeffs;        // n_cols x 2^log_n, column-major
+    bool coeffs_bitrev;  // coefficient i stored at position bitrev(i)
+    u64 *lde;           // (n_cols + n_salt) x 2^(log_n + rate_bits), column-major, leaf order
+    bsx_tree tree;
+};
+
+int bsx_fail(bsx_ctx *ctx, int code, const char *fmt, ...);
+int bsx_alloc(bsx_ctx *ctx, u64 **p, size_t words);
+void bsx_free(bsx_ctx *ctx, u64 *p);
+int bsx_copy_in(bsx_ctx *ctx, u64 *dst_dev, const u64 *src, size_t words, int mem);
+int bsx_copy_out(bsx_ctx *ctx, u64 *dst, const u64 *src_dev, size_t words, int mem);
+int bsx_pow_table(bsx_ctx *ctx, int log_n, int inverse, PowTable *out);
+int bsx_coset_tables(bsx_ctx *ctx, int log_n, int r_log, u64 shift, const u64 **pre_hi, const u64 **pre_lo);
+void bsx_split(int log_n, int *a, int *b);
+void ntt_init_device();
+
+// builds digests + cap for a tree whose leaves/shape fields are set; allocates digests/cap_dev
+int bsx_tree_build(bsx_tree *t, cudaEvent_t ev_after_leaf_hash);
+void bsx_tree_release(bsx_tree *t);
+
+#define CU(ctx, expr)                                                                             \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess) {                                                                  \
+            cudaGetLastError();                                                                   \
+            return bsx_fail((ctx), BSX_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                            __FILE__, __LINE__);                                                  \
+        }                                                                                         \
+    } while (0)
+#define TRY(expr)                  \
+    do {                           \
+        int _rc = (expr);          \
+        if (_rc != BSX_OK) return _rc; \
+    } while (0)

@@ -1,0 +1,65 @@
+// internal.h -- launcher prototypes shared by the translation units of libbsx_b200.so.
+// Everything here is device-pointer based; the C ABI in include/bsx_b200.h sits on top (api.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstddef>
+#include <cstdint>
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+// ---------------------------------------------------------------- hashing / Merkle
+// Leaves are COLUMN-major on device: element (row, col) at data[col * col_stride + row].
+// digests_out: n_rows x 4 words.  Leaves of <= 4 elements are zero-extended (hash_or_noop).
+void launch_leaf_hash(const u64 *data, size_t col_stride, int n_cols, size_t n_rows, u64 *digests_out,
+                      cudaStream_t st);
+// parents[i] = two_to_one(children[2i], children[2i+1]), n_parents digests
+void launch_merkle_level(const u64 *children, u64 *parents, size_t n_parents, cudaStream_t st);
+// Whole tree below the cap from leaf digests: level-order buffer (leaf level first), cap separately.
+// digests holds 2*(n_leaves - 2^cap_height) digests with level 0 already filled when levels > 0;
+// when log_leaves == cap_height the leaf digests ARE the cap and are expected in `cap`.
+void launch_merkle_tree(u64 *digests, u64 *cap, int log_leaves, int cap_height, cudaStream_t st);
+// states: n x 12 row-major, permuted in place (test hook)
+void launch_poseidon_permute(u64 *states, size_t n, cudaStream_t st);
+// row-major (n_rows x n_cols) <-> column-major (n_cols x n_rows, stride n_rows)
+void launch_transpose(const u64 *src, u64 *dst, size_t n_rows, size_t n_cols, cudaStream_t st);
+// out[r * n_cols + c] = data[c * col_stride + idx[r]]
+void launch_gather_rows(const u64 *data, size_t col_stride, int n_cols, const u64 *idx, int n_idx, u64 *out,
+                        cudaStream_t st);
+// siblings of leaf_index, bottom-up, from the level-order digest buffer: n_levels x 4 words
+void launch_gather_siblings(const u64 *digests, int log_leaves, int n_levels, u64 leaf_index, u64 *out,
+                            cudaStream_t st);
+
+// ---------------------------------------------------------------- NTT
+struct NttTables {
+    // omega_{4096}^j, j < 2048 (forward / inverse): sub-transform twiddles
+    const u64 *w_fwd, *w_inv;
+};
+// base^e = hi[e >> 12] * lo[e & 4095], e < 2^24
+struct PowTable {
+    const u64 *lo, *hi;
+};
+struct NttPlan {
+    int log_n;     // transform size
+    int a, b;      // log_n = a + b: a high bits (strided pass), b low bits (contiguous pass)
+    int inverse;   // use omega^-1 and scale by n^-1
+    int src_bitrev;  // source holds coefficient i at position bitrev(i)
+    int n_cosets;  // 1, or 2^rate_bits output cosets (LDE)
+    // coset k pre-factor g_k^i, i = i1 * 2^b + i0: pre_hi[k << a | i1] * pre_lo[k << b | i0]; null = none
+    const u64 *pre_hi, *pre_lo;
+    PowTable tw;   // powers of omega_N (or its inverse) for the inter-pass twiddle
+    u64 scale;     // multiplied into every output (n^-1 for the inverse); 1 = none
+};
+// Transforms n_cols columns.  src column c at src + c*src_stride (2^log_n words);
+// dst column c at dst + c*dst_stride; coset k is written to the block [bitrev_r(k) << log_n, +2^log_n)
+// of the column, every block in bit-reversed (DIF) order.  In place allowed when n_cosets == 1.
+void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t src_stride, u64 *dst,
+                size_t dst_stride, int n_cols, cudaStream_t st);
+// out[i] = first * base^(i * step_mul) for i < n
+void launch_fill_powers(u64 *out, u64 base, u64 first, size_t n, cudaStream_t st);
+// dst[c][i] = src[c][bitrev_log_n(i)]
+void launch_bitrev_copy(const u64 *src, size_t src_stride, u64 *dst, size_t dst_stride, int log_n, int n_cols,
+                        cudaStream_t st);
+int ntt_max_single_pass_log();
+void ntt_init_device();
+void launch_fill_random(u64 *out, size_t n, u64 seed, cudaStream_t st);

@@ -1,0 +1,133 @@
+/* bsx_b200.h -- C ABI of libbsx_b200.so: the B200-native plonky2 commitment core.
+ *
+ * This is the drop-in boundary for the hot path of the BlobstreamX prover.
+ * The reference has NO FFI for this path: plonky2 exposes plain Rust functions that its prover
+ * calls directly.  Each entry point below names the upstream plonky2 function it replaces; the
+ * reference mount (/root/reference) is empty, so upstream paths are cited instead of file:line
+ * (SURVEY.md section 0).  INTEGRATION.md shows the Rust `extern "C"` block and the patched
+ * `PolynomialBatch` / `MerkleTree` / `fri_proof` shims a maintainer would add.
+ *
+ * Conventions
+ *  - every field element is a canonical little-endian u64 (< p = 2^64 - 2^32 + 1); extension
+ *    elements are two consecutive u64 [c0, c1]; digests are 4 x u64.
+ *  - every function returns 0 on success or a negative BSX_ERR_* code; bsx_last_error(ctx) gives
+ *    the message.  Upstream panics on the same misuse (non power-of-two lengths,
+ *    cap_height > log2(leaves)); the Rust shim turns a non-zero code into panic!().
+ *  - one bsx_ctx per (host thread, device); calls on a ctx are serialised by the caller; distinct
+ *    contexts are independent.  Functions are synchronous at return.
+ *  - `mem` says where a caller buffer lives: BSX_HOST (pageable or pinned) or BSX_DEVICE.
+ *  - there is no CPU fallback: without a CUDA device bsx_ctx_create fails.
+ */
+#ifndef BSX_B200_H
+#define BSX_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BSX_OK 0
+#define BSX_ERR_INVALID_ARG (-1)
+#define BSX_ERR_CUDA (-2)
+#define BSX_ERR_OOM (-3)
+#define BSX_ERR_UNSUPPORTED (-4)
+
+#define BSX_HOST 0
+#define BSX_DEVICE 1
+
+#define BSX_SALT_SIZE 4 /* plonky2 plonk/plonk_common.rs SALT_SIZE */
+
+typedef struct bsx_ctx bsx_ctx;
+typedef struct bsx_tree bsx_tree;   /* plonky2 hash/merkle_tree.rs MerkleTree<F, PoseidonHash> */
+typedef struct bsx_batch bsx_batch; /* plonky2 fri/oracle.rs PolynomialBatch<F, C, 2> */
+
+/* per-phase device milliseconds (CUDA events), the analogue of plonky2 util/timing.rs TimingTree
+ * scopes "IFFT", "FFT + blinding", "build Merkle tree" inside from_values. */
+typedef struct bsx_timing {
+    float h2d_ms;
+    float ifft_ms;
+    float lde_ms;
+    float leaf_hash_ms;
+    float tree_ms;
+    float total_ms;
+} bsx_timing;
+
+const char *bsx_version(void);
+int32_t bsx_device_count(void);
+
+int32_t bsx_ctx_create(int32_t device, bsx_ctx **out);
+void bsx_ctx_destroy(bsx_ctx *ctx);
+const char *bsx_last_error(const bsx_ctx *ctx);
+/* the CUDA stream all work of this ctx runs on (cudaStream_t as void*), for event timing */
+void *bsx_ctx_stream(const bsx_ctx *ctx);
+int32_t bsx_ctx_sync(bsx_ctx *ctx);
+
+/* ---- PolynomialBatch (fri/oracle.rs) ------------------------------------------------------
+ * from_values: values = n_cols column vectors of 2^log_n evaluations on the subgroup, column-major
+ * (column c at values + c * 2^log_n), i.e. Vec<PolynomialValues<F>>.  Does ifft per column,
+ * zero-pad by 2^rate_bits, coset FFT with shift g = 7, appends BSX_SALT_SIZE salt columns iff
+ * blinding, and builds the Poseidon Merkle tree over the bit-reversed LDE rows down to the cap.
+ * salt: optional caller-supplied salt columns (BSX_SALT_SIZE x 2^(log_n+rate_bits), column-major,
+ * LDE-domain natural order, same `mem`); NULL with blinding != 0 draws them on the device
+ * (upstream uses F::rand_vec, so salted caps are not reproducible against any reference).
+ * Replaces PolynomialBatch::from_values. */
+int32_t bsx_batch_from_values(bsx_ctx *ctx, const uint64_t *values, int32_t mem, int32_t log_n, int32_t n_cols,
+                              int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt,
+                              bsx_batch **out, bsx_timing *timing);
+/* Replaces PolynomialBatch::from_coeffs: coeffs = n_cols coefficient vectors of length 2^log_n. */
+int32_t bsx_batch_from_coeffs(bsx_ctx *ctx, const uint64_t *coeffs, int32_t mem, int32_t log_n, int32_t n_cols,
+                              int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt,
+                              bsx_batch **out, bsx_timing *timing);
+void bsx_batch_free(bsx_batch *b);
+/* merkle_tree.cap: 2^cap_height digests -> out_host[2^cap_height * 4] */
+int32_t bsx_batch_cap(const bsx_batch *b, uint64_t *out_host);
+/* the batch's MerkleTree (borrowed; freed with the batch) */
+bsx_tree *bsx_batch_tree(bsx_batch *b);
+/* Replaces PolynomialBatch::get_lde_values(index, step): row bitrev(index * step) of the leaves with
+ * the salt stripped -> out[n_cols].  `index` counts in the degree * 2^log2(step)... domain exactly as
+ * upstream: leaf = reverse_bits(index * step, log_n + rate_bits). */
+int32_t bsx_batch_get_lde_values(bsx_batch *b, uint64_t index, uint64_t step, uint64_t *out_host);
+/* polynomials[c].coeffs in natural order -> out[n_cols * 2^log_n] (column-major), `mem` side */
+int32_t bsx_batch_coeffs(bsx_batch *b, uint64_t *out, int32_t mem);
+/* Full export for serialisation (circuit artefacts): any pointer may be NULL.
+ * leaves: row-major 2^(log_n+rate_bits) x (n_cols+salt), rows in leaf (bit-reversed) order;
+ * digests: plonky2's `digests` Vec layout (fill_subtree order), 2*(leaves - 2^cap_height) x 4 words. */
+int32_t bsx_batch_export(bsx_batch *b, uint64_t *coeffs_host, uint64_t *leaves_host, uint64_t *digests_host);
+int32_t bsx_batch_shape(const bsx_batch *b, int32_t *log_n, int32_t *n_cols, int32_t *rate_bits,
+                        int32_t *cap_height, int32_t *n_salt);
+/* device pointers for callers that keep working on the GPU (quotient evaluation, multi-GPU exchange):
+ * LDE is column-major, column c at lde + c * 2^(log_n+rate_bits), position l = leaf index. */
+const uint64_t *bsx_batch_lde_device(const bsx_batch *b);
+const uint64_t *bsx_batch_digests_device(const bsx_batch *b);
+
+/* ---- MerkleTree (hash/merkle_tree.rs) ------------------------------------------------------
+ * Replaces MerkleTree::new(leaves, cap_height): leaves row-major 2^log_leaves x leaf_len. */
+int32_t bsx_merkle_new(bsx_ctx *ctx, const uint64_t *leaves, int32_t mem, int32_t log_leaves, int32_t leaf_len,
+                       int32_t cap_height, bsx_tree **out);
+/* Same tree from column-major device leaves (element (row, col) at leaves[col * col_stride + row]);
+ * the tree BORROWS the leaves (no copy).  Used by the multi-GPU path after the all-to-all. */
+int32_t bsx_merkle_new_colmajor_device(bsx_ctx *ctx, const uint64_t *leaves_dev, size_t col_stride,
+                                       int32_t log_leaves, int32_t leaf_len, int32_t cap_height, bsx_tree **out);
+void bsx_merkle_free(bsx_tree *t);
+int32_t bsx_merkle_cap(const bsx_tree *t, uint64_t *out_host);
+/* MerkleTree::get(i) for k indices: out_host[k * leaf_len] */
+int32_t bsx_merkle_get(bsx_tree *t, const uint64_t *idx_host, int32_t k, uint64_t *out_host);
+/* MerkleTree::prove(leaf_index).siblings bottom-up: out_host[(log_leaves - cap_height) * 4] */
+int32_t bsx_merkle_prove(bsx_tree *t, uint64_t leaf_index, uint64_t *siblings_host);
+/* digests in plonky2's Vec layout (host) */
+int32_t bsx_merkle_digests(bsx_tree *t, uint64_t *out_host);
+int32_t bsx_merkle_shape(const bsx_tree *t, int32_t *log_leaves, int32_t *leaf_len, int32_t *cap_height);
+
+/* ---- test hooks -----------------------------------------------------------------------------
+ * Poseidon::poseidon on n states (n x 12 words, in place). */
+int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n);
+/* Batched transforms on n_cols columns of 2^log_n words, column-major, in place, natural order in and
+ * out.  kind: 0 = fft (PolynomialCoeffs::fft), 1 = ifft (PolynomialValues::ifft),
+ * 2 = coset_fft(shift) (PolynomialCoeffs::coset_fft). */
+int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t log_n, int32_t n_cols, int32_t kind,
+                uint64_t shift);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
