@@ -10,7 +10,7 @@ _SO = os.path.join(_DIR, "csrc", "libbsx_b200.so")
 
 # every symbol include/bsx_b200.h declares (checked by tests/test_abi.py against the header text)
 EXPORTED_SYMBOLS = [
-    "bsx_version", "bsx_device_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
+    "bsx_version", "bsx_device_count", "bsx_launch_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
     "bsx_ctx_sync", "bsx_batch_from_values", "bsx_batch_from_coeffs", "bsx_batch_free", "bsx_batch_cap",
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
@@ -52,6 +52,7 @@ def lib():
     sig = {
         "bsx_version": (C.c_char_p, []),
         "bsx_device_count": (i32, []),
+        "bsx_launch_count": (u64, []),
         "bsx_ctx_create": (i32, [i32, pp]),
         "bsx_ctx_destroy": (None, [vp]),
         "bsx_last_error": (C.c_char_p, [vp]),

@@ -110,6 +110,9 @@ int bsx_coset_tables(bsx_ctx *ctx, int log_n, int r_log, u64 shift, const u64 **
 }
 
 // ------------------------------------------------------------------------------------ context
+unsigned long long g_bsx_launches = 0;
+extern "C" uint64_t bsx_launch_count(void) { return g_bsx_launches; }
+
 extern "C" const char *bsx_version(void) { return "bsx_b200 0.1 (sm_100a)"; }
 
 extern "C" int32_t bsx_device_count(void) {

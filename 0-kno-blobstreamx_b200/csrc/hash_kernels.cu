@@ -41,7 +41,7 @@ void launch_leaf_hash(const u64 *data, size_t col_stride, int n_cols, size_t n_r
                       cudaStream_t st) {
     if (n_rows == 0) return;
     unsigned blocks = (unsigned)((n_rows + 255) / 256);
-    leaf_hash_kernel<<<blocks, 256, 0, st>>>(data, col_stride, n_cols, n_rows, digests_out);
+    BSX_COUNT_LAUNCH(); leaf_hash_kernel<<<blocks, 256, 0, st>>>(data, col_stride, n_cols, n_rows, digests_out);
 }
 
 // ------------------------------------------------------------------ inner levels
@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(256) merkle_level_kernel(const u64 *__restrict
 void launch_merkle_level(const u64 *children, u64 *parents, size_t n_parents, cudaStream_t st) {
     if (n_parents == 0) return;
     unsigned blocks = (unsigned)((n_parents + 255) / 256);
-    merkle_level_kernel<<<blocks, 256, 0, st>>>(children, parents, n_parents);
+    BSX_COUNT_LAUNCH(); merkle_level_kernel<<<blocks, 256, 0, st>>>(children, parents, n_parents);
 }
 
 // One block per subtree of 2^SUB_LOG nodes at the input level: digest layers stay in shared
@@ -127,7 +127,7 @@ void launch_merkle_tree(u64 *digests, u64 *cap, int log_leaves, int cap_height, 
         if (log_in >= SUB_LOG && rem >= 1) {
             int climb = rem < SUB_LOG ? rem : SUB_LOG;
             unsigned blocks = (unsigned)(n_in >> SUB_LOG);
-            merkle_subtree_kernel<<<blocks, 256, 0, st>>>(in, out, n_in, climb, 0, cap, rem <= SUB_LOG ? rem : -1);
+            BSX_COUNT_LAUNCH(); merkle_subtree_kernel<<<blocks, 256, 0, st>>>(in, out, n_in, climb, 0, cap, rem <= SUB_LOG ? rem : -1);
             // advance: the last produced level becomes the next input
             size_t words = 0, ln = n_in >> 1;
             for (int j = 1; j < climb; j++) {
@@ -165,7 +165,7 @@ __global__ void poseidon_permute_kernel(u64 *states, size_t n) {
 }
 void launch_poseidon_permute(u64 *states, size_t n, cudaStream_t st) {
     if (n == 0) return;
-    poseidon_permute_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(states, n);
+    BSX_COUNT_LAUNCH(); poseidon_permute_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(states, n);
 }
 
 // 32x32 tiled transpose through shared memory, both sides coalesced.
@@ -185,7 +185,7 @@ __global__ void transpose_kernel(const u64 *__restrict__ src, u64 *__restrict__ 
 void launch_transpose(const u64 *src, u64 *dst, size_t n_rows, size_t n_cols, cudaStream_t st) {
     if (n_rows == 0 || n_cols == 0) return;
     dim3 grid((unsigned)((n_cols + 31) / 32), (unsigned)((n_rows + 31) / 32));
-    transpose_kernel<<<grid, dim3(32, 8), 0, st>>>(src, dst, n_rows, n_cols);
+    BSX_COUNT_LAUNCH(); transpose_kernel<<<grid, dim3(32, 8), 0, st>>>(src, dst, n_rows, n_cols);
 }
 
 __global__ void gather_rows_kernel(const u64 *__restrict__ data, size_t col_stride, int n_cols,
@@ -198,7 +198,7 @@ __global__ void gather_rows_kernel(const u64 *__restrict__ data, size_t col_stri
 void launch_gather_rows(const u64 *data, size_t col_stride, int n_cols, const u64 *idx, int n_idx, u64 *out,
                         cudaStream_t st) {
     if (n_idx == 0 || n_cols == 0) return;
-    gather_rows_kernel<<<n_idx, 128, 0, st>>>(data, col_stride, n_cols, idx, n_idx, out);
+    BSX_COUNT_LAUNCH(); gather_rows_kernel<<<n_idx, 128, 0, st>>>(data, col_stride, n_cols, idx, n_idx, out);
 }
 
 __global__ void gather_siblings_kernel(const u64 *__restrict__ digests, int log_leaves, int n_levels, u64 leaf_index,
@@ -213,5 +213,5 @@ __global__ void gather_siblings_kernel(const u64 *__restrict__ digests, int log_
 void launch_gather_siblings(const u64 *digests, int log_leaves, int n_levels, u64 leaf_index, u64 *out,
                             cudaStream_t st) {
     if (n_levels <= 0) return;
-    gather_siblings_kernel<<<n_levels, 4, 0, st>>>(digests, log_leaves, n_levels, leaf_index, out);
+    BSX_COUNT_LAUNCH(); gather_siblings_kernel<<<n_levels, 4, 0, st>>>(digests, log_leaves, n_levels, leaf_index, out);
 }

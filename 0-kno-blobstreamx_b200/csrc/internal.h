@@ -8,6 +8,10 @@
 typedef unsigned long long u64;
 typedef unsigned int u32;
 
+// process-wide count of kernel launches issued by this library (bench.py reports it)
+extern unsigned long long g_bsx_launches;
+#define BSX_COUNT_LAUNCH() (++g_bsx_launches)
+
 // ---------------------------------------------------------------- hashing / Merkle
 // Leaves are COLUMN-major on device: element (row, col) at data[col * col_stride + row].
 // digests_out: n_rows x 4 words.  Leaves of <= 4 elements are zero-extended (hash_or_noop).

@@ -179,7 +179,7 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         size_t smem = sizeof(u64) << (plan.a + w_log);
         int threads = NTT_THREADS;
         while (threads > 32 && threads > (1 << (plan.a + w_log))) threads >>= 1;
-        ntt_pass_hi<<<grid, threads, smem, st>>>(P);
+        BSX_COUNT_LAUNCH(); ntt_pass_hi<<<grid, threads, smem, st>>>(P);
     }
     if (plan.b > 0) {
         size_t rows = ((size_t)plan.n_cosets << plan.log_n) >> plan.b;  // per column
@@ -191,7 +191,7 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         size_t smem = sizeof(u64) << (plan.b + w_log);
         int threads = NTT_THREADS;
         while (threads > 32 && threads > (1 << (plan.b + w_log))) threads >>= 1;
-        ntt_pass_lo<<<grid, threads, smem, st>>>(P);
+        BSX_COUNT_LAUNCH(); ntt_pass_lo<<<grid, threads, smem, st>>>(P);
     }
 }
 
@@ -201,7 +201,7 @@ __global__ void fill_powers_kernel(u64 *out, u64 base, u64 first, size_t n) {
 }
 void launch_fill_powers(u64 *out, u64 base, u64 first, size_t n, cudaStream_t st) {
     if (n == 0) return;
-    fill_powers_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, base, first, n);
+    BSX_COUNT_LAUNCH(); fill_powers_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, base, first, n);
 }
 
 __global__ void bitrev_copy_kernel(const u64 *__restrict__ src, size_t src_stride, u64 *__restrict__ dst,
@@ -216,7 +216,7 @@ void launch_bitrev_copy(const u64 *src, size_t src_stride, u64 *dst, size_t dst_
     if (n_cols <= 0) return;
     size_t n = (size_t)1 << log_n;
     dim3 grid((unsigned)((n + 255) / 256), (unsigned)n_cols);
-    bitrev_copy_kernel<<<grid, 256, 0, st>>>(src, src_stride, dst, dst_stride, log_n);
+    BSX_COUNT_LAUNCH(); bitrev_copy_kernel<<<grid, 256, 0, st>>>(src, src_stride, dst, dst_stride, log_n);
 }
 
 // counter-based SplitMix64 stream reduced mod p: salt columns when the caller supplies none
@@ -231,5 +231,5 @@ __global__ void fill_random_kernel(u64 *out, size_t n, u64 seed) {
 }
 void launch_fill_random(u64 *out, size_t n, u64 seed, cudaStream_t st) {
     if (n == 0) return;
-    fill_random_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, n, seed);
+    BSX_COUNT_LAUNCH(); fill_random_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, n, seed);
 }

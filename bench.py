@@ -1,0 +1,293 @@
+#!/usr/bin/env python3
+"""bench.py -- LDE + Poseidon-Merkle commit throughput (BASELINE.json `metric`) on N B200s.
+
+A step is one `PolynomialBatch::from_values` over one synthetic witness: iNTT, coset LDE, leaf
+hashing, Merkle tree down to the cap.  Workload at every N: the headline configuration
+2^20 rows x 135 columns, rate_bits 3, cap_height 4 per GPU (one independent commit per rank: the
+header_range map jobs of the north star share no state, so ranks exchange nothing on the data path
+-- weak scaling).  `value` = committed input elements (N * C per rank, all ranks) per second with
+the witness already in HBM; `e2e` = the same through the C ABI with the witness in pinned HOST
+memory (H2D inside the timed call, cap back on the host).
+
+`--impl reference` times the CPU arm instead: the in-repo oracle port of the plonky2 algorithm
+(the reference mount holds no source and there is no Rust toolchain) with all
+host threads on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+P = 0xFFFFFFFF00000001
+
+LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT = 20, 135, 3, 4
+CPU_SAMPLE_LOG_N = 15  # bounded CPU sample: same columns / rate / cap, 2^15 rows
+
+
+def splitmix_field(seed, shape):
+    n = int(np.prod(shape))
+    out = np.empty(n, dtype=np.uint64)
+    chunk = 1 << 24
+    with np.errstate(over="ignore"):
+        for lo in range(0, n, chunk):
+            idx = np.arange(lo + 1, min(lo + chunk, n) + 1, dtype=np.uint64)
+            z = np.uint64(seed) + idx * np.uint64(0x9E3779B97F4A7C15)
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            z = z ^ (z >> np.uint64(31))
+            out[lo:lo + idx.size] = z % np.uint64(P)
+    return out.reshape(shape)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peak_gbs():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_reference_arm(args, rank, world):
+    """--impl reference: the oracle port on all host threads, bounded sample per step."""
+    if rank != 0:
+        return
+    from oracle import oracle as O
+    n = 1 << CPU_SAMPLE_LOG_N
+    vals = splitmix_field(0x5EED0001, (N_COLS, n))
+    cores = O.num_threads()
+    for _ in range(args.warmup):
+        O.batch_from_values(vals, RATE_BITS, CAP_HEIGHT, want=())
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        O.batch_from_values(vals, RATE_BITS, CAP_HEIGHT, want=())
+    dt = (time.perf_counter() - t0) / args.steps
+    v = n * N_COLS / dt / 1e6
+    sample = "2^%d rows x %d cols per step (1/%d of the 2^%d-row workload), rate_bits %d, cap_height %d" % (
+        CPU_SAMPLE_LOG_N, N_COLS, 1 << (LOG_N - CPU_SAMPLE_LOG_N), LOG_N, RATE_BITS, CAP_HEIGHT)
+    print(json.dumps({
+        "impl": "reference", "metric": "lde_poseidon_merkle_commit", "value": v, "unit": "Melem/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": v, "unit": "Melem/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "CPU restatement of the plonky2 algorithm (oracle/), not the plonky2 crate: the reference "
+                "mount holds no source and no Rust toolchain exists on this image",
+    }))
+
+
+def workload_config(n_gpus):
+    return {"workload": "PolynomialBatch::from_values commit, 2^%d rows x %d cols per GPU, rate_bits %d, "
+                        "cap_height %d (BASELINE.json configs[4] headline point; standard_recursion_config)"
+                        % (LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT),
+            "log_n": LOG_N, "n_cols": N_COLS, "rate_bits": RATE_BITS, "cap_height": CAP_HEIGHT,
+            "sharding": "one independent commit per GPU, no data-path collective" if n_gpus > 1 else "single GPU",
+            "l2": "inputs (1.13 GB) and LDE (9.06 GB) exceed the 126 MB L2; no flush needed"}
+
+
+def gpu_arm(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as G
+    pkg = G.load_package()
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    ctx = pkg.Context(local_rank)  # raises without the built CUDA library or a GPU: no fallback
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+    n = 1 << LOG_N
+    host = torch.empty((N_COLS, n), dtype=torch.int64).pin_memory()
+    host_np = host.numpy().view(np.uint64)
+    host_np[:] = splitmix_field(0x5EED0001 + rank, (N_COLS, n))
+    dev = host.to("cuda:%d" % local_rank)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device(timing):
+        b = pkg.PolynomialBatch.from_values(ctx, None, RATE_BITS, False, CAP_HEIGHT, device_ptr=dev.data_ptr(),
+                                            shape=(N_COLS, n), timing=timing)
+        t = b.timing.as_dict() if timing else None
+        cap = b.cap
+        b.close()
+        return cap, t
+
+    def step_host():
+        b = pkg.PolynomialBatch.from_values(ctx, host_np, RATE_BITS, False, CAP_HEIGHT)
+        cap = b.cap
+        b.close()
+        return cap
+
+    cap0 = None
+    for _ in range(args.warmup):
+        cap0, _ = step_device(True)
+    # ---- device-resident arm
+    launches0 = pkg.lib().bsx_launch_count()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    phases = []
+    for _ in range(args.steps):
+        cap, t = step_device(True)
+        phases.append(t)
+    e1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = (pkg.lib().bsx_launch_count() - launches0) // args.steps
+    assert (cap == cap0).all(), "cap changed between identical steps"
+    # ---- end-to-end arm: pinned host witness -> cap on host, through the C ABI
+    for _ in range(max(1, min(args.warmup, 2))):
+        cap_h = step_host()
+    assert (cap_h == cap0).all(), "host-buffer path and device-buffer path disagree"
+    barrier()
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h0.record(stream)
+    for _ in range(args.steps):
+        step_host()
+    h1.record(stream)
+    barrier()
+    ms_e2e = h0.elapsed_time(h1) / args.steps
+    if world > 1:
+        t = torch.tensor([ms, ms_e2e], device="cuda:%d" % local_rank, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    elems = n * N_COLS
+    nb = n << RATE_BITS
+    value = world * elems / (ms * 1e-3) / 1e6
+    e2e = world * elems / (ms_e2e * 1e-3) / 1e6
+    avg = {k: float(np.mean([p[k] for p in phases])) for k in phases[0]}
+    peak, peak_src = measured_peak_gbs()
+
+    def roof(bytes_, ms_, traffic=None):
+        a = bytes_ / (ms_ * 1e-3) / 1e9
+        return {"bound": "hbm", "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak, "traffic": traffic}
+
+    leaf_bytes = 8 * nb * N_COLS + 32 * nb
+    roofline = roof(leaf_bytes, avg["leaf_hash_ms"])
+    roofline.update({"kernel": "leaf_hash_kernel", "ms_per_launch": avg["leaf_hash_ms"], "peak_source": peak_src,
+                     "algorithmic_bytes": leaf_bytes,
+                     "note": "dominant kernel by time; Poseidon is integer-pipe bound, so its HBM fraction is low "
+                             "by construction (see DESIGN.md and profiles/ for pipe utilisation)"})
+    perms = nb * ((N_COLS + 7) // 8) + nb - (1 << CAP_HEIGHT)
+    out = {
+        "metric": "lde_poseidon_merkle_commit", "value": value, "unit": "Melem/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": workload_config(world),
+        "lde_melem_per_s": value * (1 << RATE_BITS),
+        "e2e": {"value": e2e, "unit": "Melem/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * elems,
+                "d2h_bytes_per_step": 32 << CAP_HEIGHT},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+        "phases_ms": avg,
+        "roofline_ntt": {
+            "ifft": dict(roof(16 * elems, avg["ifft_ms"]), algorithmic_bytes=16 * elems),
+            "lde": dict(roof(8 * elems + 8 * nb * N_COLS, avg["lde_ms"]), algorithmic_bytes=8 * elems + 8 * nb * N_COLS),
+        },
+        "whole_commit": dict(roof(8 * elems * (2 + (1 << RATE_BITS)) + 64 * nb, ms),
+                             algorithmic_bytes=8 * elems * (2 + (1 << RATE_BITS)) + 64 * nb),
+        "poseidon": {"permutations_per_step": perms,
+                     "gperm_per_s": perms / ((avg["leaf_hash_ms"] + avg["tree_ms"]) * 1e-3) / 1e9},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import oracle as O
+        ns = 1 << CPU_SAMPLE_LOG_N
+        sample = host_np[:, :ns].copy()
+        O.batch_from_values(sample, RATE_BITS, CAP_HEIGHT, want=())
+        t0 = time.perf_counter()
+        reps = 2
+        for _ in range(reps):
+            O.batch_from_values(sample, RATE_BITS, CAP_HEIGHT, want=())
+        dt = (time.perf_counter() - t0) / reps
+        out["cpu_baseline"] = {
+            "value": ns * N_COLS / dt / 1e6, "unit": "Melem/s", "cores": O.num_threads(), "kind": "port",
+            "sample": "2^%d rows x %d cols, rate_bits %d, cap_height %d (1/%d of the GPU workload), OpenMP C oracle; "
+                      "a CPU restatement, not the plonky2 crate" % (CPU_SAMPLE_LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT,
+                                                                   1 << (LOG_N - CPU_SAMPLE_LOG_N))}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        cpu_reference_arm(args, rank, world)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+    gpu_arm(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

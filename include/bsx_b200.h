@@ -54,6 +54,8 @@ typedef struct bsx_timing {
 
 const char *bsx_version(void);
 int32_t bsx_device_count(void);
+/* kernels launched by this library in this process so far (bench.py `gpu_launches`) */
+uint64_t bsx_launch_count(void);
 
 int32_t bsx_ctx_create(int32_t device, bsx_ctx **out);
 void bsx_ctx_destroy(bsx_ctx *ctx);

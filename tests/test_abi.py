@@ -1,0 +1,59 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads and exports every symbol
+include/bsx_b200.h declares, and the product fails loudly without a GPU (no fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from conftest import ROOT
+import __graft_entry__ as G
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    return G.load_package()
+
+
+def _header_symbols():
+    text = open(os.path.join(ROOT, "include", "bsx_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(bsx_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    if not os.path.exists(pkg.library_path()):
+        G.build()
+    L = ctypes.CDLL(pkg.library_path())
+    declared = _header_symbols()
+    assert len(declared) >= 25
+    for name in declared:
+        assert hasattr(L, name), "libbsx_b200.so does not export %s" % name
+    assert sorted(pkg.EXPORTED_SYMBOLS) == declared, "binding.py and the header disagree"
+
+
+def test_no_cpu_fallback(pkg):
+    L = pkg.lib()
+    if L.bsx_device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(pkg.BsxError):
+        pkg.Context(0)
+
+
+def test_product_never_imports_oracle():
+    pkg_dir = os.path.join(ROOT, "0-kno-blobstreamx_b200")
+    for dirpath, _, files in os.walk(pkg_dir):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp")) or f == "Makefile":
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.replace("fri/oracle.rs", "").replace("oracle.rs", ""), \
+                    "%s references the oracle" % f
+
+
+def test_fri_reduction_strategy(pkg):
+    # ConstantArityBits(4, 5) at standard_recursion_config
+    assert pkg.fri_reduction_arity_bits(20, 3, 4) == [4, 4, 4, 4]
+    assert pkg.fri_reduction_arity_bits(14, 3, 4) == [4, 4, 4]
+    assert pkg.fri_reduction_arity_bits(5, 3, 4) == []
+    p = pkg.FriConfig().fri_params(20)
+    assert p.lde_bits() == 23 and p.final_poly_len() == 16

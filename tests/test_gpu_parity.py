@@ -1,0 +1,182 @@
+"""Tier 2: every CUDA kernel bit-exact against the CPU oracle, through the C ABI.  Integer field
+arithmetic: comparisons are exact equality, no tolerances."""
+import numpy as np
+import pytest
+
+from conftest import P, splitmix_field
+import __graft_entry__ as G
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    return G.load_package()
+
+
+@pytest.fixture(scope="module")
+def ctx(pkg):
+    c = pkg.Context(0)
+    yield c
+    c.close()
+
+
+EDGE = [0, 1, 2, P - 1, P - 2, 2**32 - 1, 2**32, 2**32 + 1, 2**63, P - 2**32, 0xFFFFFFFF00000000, 0xFFFFFFFF]
+
+
+def test_poseidon_kat_on_device(ctx):
+    z = ctx.poseidon_permute(np.zeros(12, dtype=np.uint64))
+    assert "%016x" % int(z[0]) == "3c18a9786cb0b359" and "%016x" % int(z[11]) == "1792b1c4342109d7"
+    i = ctx.poseidon_permute(np.arange(12, dtype=np.uint64))
+    assert "%016x" % int(i[0]) == "d64e1e3efc5b8e9e"
+    m = ctx.poseidon_permute(np.full(12, P - 1, dtype=np.uint64))
+    assert "%016x" % int(m[0]) == "be0085cfc57a8357"
+
+
+def test_poseidon_random_and_adversarial(ctx, oracle):
+    st = splitmix_field(42, (4096, 12))
+    # rows built from reduction edge values: products hit the borrow/carry paths of reduce128
+    adv = np.array([[EDGE[(i + j) % len(EDGE)] for j in range(12)] for i in range(64)], dtype=np.uint64)
+    st[:64] = adv
+    got = ctx.poseidon_permute(st)
+    want = oracle.poseidon(st)
+    assert (got == want).all()
+
+
+@pytest.mark.parametrize("log_n", [0, 1, 2, 5, 10, 12, 13, 14, 16])
+def test_ntt_kinds(ctx, oracle, log_n):
+    n_cols = 3
+    v = splitmix_field(100 + log_n, (n_cols, 1 << log_n))
+    if log_n >= 2:
+        v[0, :4] = np.array([0, P - 1, 2**32 - 1, 2**32], dtype=np.uint64)
+    got = ctx.ntt(v, "fft")
+    assert all((got[c] == oracle.fft(v[c])).all() for c in range(n_cols))
+    got = ctx.ntt(v, "ifft")
+    assert all((got[c] == oracle.ifft(v[c])).all() for c in range(n_cols))
+    got = ctx.ntt(v, "coset_fft", shift=7)
+    assert all((got[c] == oracle.coset_fft(v[c], 7)).all() for c in range(n_cols))
+    got = ctx.ntt(v, "coset_fft", shift=pow(7, 16, P))
+    assert (got[1] == oracle.coset_fft(v[1], pow(7, 16, P))).all()
+
+
+def test_ntt_roundtrip_large(ctx):
+    v = splitmix_field(7, (2, 1 << 20))
+    assert (ctx.ntt(ctx.ntt(v, "fft"), "ifft") == v).all()
+
+
+@pytest.mark.parametrize("n_leaves,leaf_len,cap_height", [
+    (1, 7, 0), (2, 3, 0), (2, 3, 1), (16, 4, 2), (64, 5, 0), (64, 135, 4), (1024, 8, 4), (1024, 9, 10),
+    (2048, 32, 4), (4096, 20, 0), (1 << 14, 17, 4),
+])
+def test_merkle_tree_vs_oracle(pkg, ctx, oracle, n_leaves, leaf_len, cap_height):
+    leaves = splitmix_field(n_leaves + leaf_len, (n_leaves, leaf_len))
+    t = pkg.MerkleTree(ctx, leaves, cap_height)
+    digests, cap = oracle.merkle_build(leaves, cap_height)
+    assert (t.cap == cap).all()
+    log_leaves = n_leaves.bit_length() - 1
+    for i in sorted({0, n_leaves - 1, n_leaves // 3}):
+        assert (t.get(i) == leaves[i]).all()
+        sib = t.prove(i)
+        assert (sib == oracle.merkle_prove(digests, log_leaves, cap_height, i)).all()
+        assert oracle.merkle_verify(leaves[i], i, sib, cap)
+    want_p2 = oracle.merkle_digests_to_plonky2(digests, log_leaves, cap_height)
+    assert (t.digests.reshape(-1) == want_p2.reshape(-1)).all()
+    t.close()
+
+
+def test_merkle_errors_match_upstream_panics(pkg, ctx):
+    leaves = splitmix_field(1, (8, 5))
+    with pytest.raises(pkg.BsxError, match="cap_height=4 should be at most"):
+        pkg.MerkleTree(ctx, leaves, 4)
+    with pytest.raises(pkg.BsxError, match="power of two"):
+        pkg.MerkleTree(ctx, leaves[:6], 0)
+    t = pkg.MerkleTree(ctx, leaves, 1)
+    with pytest.raises(pkg.BsxError, match="out of range"):
+        t.prove(8)
+
+
+@pytest.mark.parametrize("log_n,n_cols,rate_bits,cap_height", [
+    (0, 1, 1, 0), (3, 2, 1, 0), (5, 7, 2, 1), (8, 135, 3, 4), (10, 9, 3, 4), (12, 20, 3, 4), (13, 16, 1, 4),
+    (14, 5, 4, 0), (11, 3, 0, 2),
+])
+def test_batch_from_values_vs_oracle(pkg, ctx, oracle, log_n, n_cols, rate_bits, cap_height):
+    vals = splitmix_field(0x5EED0000 + log_n, (n_cols, 1 << log_n))
+    b = pkg.PolynomialBatch.from_values(ctx, vals, rate_bits, False, cap_height)
+    want = oracle.batch_from_values(vals, rate_bits, cap_height)
+    assert (b.cap == want["cap"]).all()
+    ex = b.export()
+    assert (ex["coeffs"] == want["coeffs"]).all()
+    assert (ex["leaves"] == want["leaves"]).all()
+    log_nb = log_n + rate_bits
+    if want["digests"] is not None:
+        assert (ex["digests"].reshape(-1) ==
+                oracle.merkle_digests_to_plonky2(want["digests"], log_nb, cap_height).reshape(-1)).all()
+    # get_lde_values(index, step) = leaves[reverse_bits(index * step)]
+    for idx, step in ((0, 1), ((1 << log_n) - 1, 1 << rate_bits), (1, 1)):
+        if idx * step >> log_nb:
+            continue
+        leaf = int(oracle.lib().orc_reverse_bits(idx * step, log_nb))
+        assert (b.get_lde_values(idx, step) == want["leaves"][leaf]).all()
+    b.close()
+
+
+def test_config1_standard_recursion_commit(pkg, ctx, oracle):
+    """BASELINE.json configs[0]: 2^14 x 135, rate_bits 3, cap_height 4."""
+    vals = splitmix_field(0x5EED0001, (135, 1 << 14))
+    b = pkg.PolynomialBatch.from_values(ctx, vals, 3, False, 4, timing=True)
+    want = oracle.batch_from_values(vals, 3, 4, want=("digests",))
+    assert (b.cap == want["cap"]).all()
+    tree = b.merkle_tree
+    for i in (0, 12345, (1 << 17) - 1):
+        assert (tree.prove(i) == oracle.merkle_prove(want["digests"], 17, 4, i)).all()
+    assert b.timing.total_ms > 0
+    b.close()
+
+
+def test_edge_inputs_zero_and_minus_one(pkg, ctx, oracle):
+    for fill in (0, P - 1):
+        vals = np.full((6, 1 << 9), fill, dtype=np.uint64)
+        b = pkg.PolynomialBatch.from_values(ctx, vals, 3, False, 4)
+        assert (b.cap == oracle.batch_from_values(vals, 3, 4, want=())["cap"]).all()
+        b.close()
+
+
+def test_from_coeffs_and_salt(pkg, ctx, oracle):
+    log_n, n_cols, rate_bits = 9, 6, 3
+    coeffs = splitmix_field(77, (n_cols, 1 << log_n))
+    b = pkg.PolynomialBatch.from_coeffs(ctx, coeffs, rate_bits, False, 4)
+    want = oracle.batch_from_values(coeffs, rate_bits, 4, from_coeffs=True)
+    assert (b.cap == want["cap"]).all()
+    assert (b.polynomials == coeffs).all()
+    b.close()
+    salt = splitmix_field(78, (4, 1 << (log_n + rate_bits)))
+    b = pkg.PolynomialBatch.from_values(ctx, coeffs, rate_bits, True, 4, salt=salt)
+    want = oracle.batch_from_values(coeffs, rate_bits, 4, salt=salt)
+    assert (b.cap == want["cap"]).all()
+    assert b.shape()["n_salt"] == 4
+    assert (b.export()["leaves"] == want["leaves"]).all()
+    # salt is stripped by get_lde_values
+    assert b.get_lde_values(3, 1).shape == (n_cols,)
+    b.close()
+    # device-drawn salt: caps differ from the unsalted commit, tree is still self-consistent
+    b = pkg.PolynomialBatch.from_values(ctx, coeffs, rate_bits, True, 4)
+    ex = b.export()
+    _, cap = oracle.merkle_build(ex["leaves"], 4)
+    assert (cap == b.cap).all() and ex["leaves"].shape[1] == n_cols + 4
+    assert (ex["leaves"] < np.uint64(P)).all()
+    b.close()
+
+
+def test_linearity_full_size(pkg, ctx):
+    """Size-independent property at a size the oracle would take minutes for: LDE is linear, so
+    lde(a + b) == lde(a) + lde(b) row by row (checked on sampled rows)."""
+    log_n, n_cols = 18, 16
+    a = splitmix_field(1, (n_cols, 1 << log_n))
+    b = splitmix_field(2, (n_cols, 1 << log_n))
+    s = ((a.astype(object) + b.astype(object)) % P).astype(np.uint64)
+    ba, bb, bs = (pkg.PolynomialBatch.from_values(ctx, x, 3, False, 4) for x in (a, b, s))
+    for idx in (0, 1, 99999, (1 << 21) - 1):
+        ra, rb, rs = (t.get_lde_values(idx) for t in (ba, bb, bs))
+        assert (((ra.astype(object) + rb.astype(object)) % P).astype(np.uint64) == rs).all()
+    for t in (ba, bb, bs):
+        t.close()
