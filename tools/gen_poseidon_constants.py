@@ -112,16 +112,120 @@ FIRST12 = [0xb585f766f2144405, 0x7746a55f43921ad7, 0xb2fb0d31cee799b4, 0x0f6760a
            0xcdc4a239b0c44426, 0x277fa208bf337bff, 0xe17653a29da578a1, 0xc54302f225db2c76]
 
 
-def emit(path, rc, guard):
+# ---------------------------------------------------------------------------------------------
+# Fast partial rounds (same permutation, fewer multiplications).  The 22 partial rounds
+#     x += c_p ; x_0 <- x_0^7 ; x <- M x
+# are rewritten, as in the Poseidon paper's optimised form (plonky2 hash/poseidon.rs
+# `partial_first_constant_layer`, `mds_partial_layer_init`, `mds_partial_layer_fast`), into
+#     x += FIRST ; x[1:] <- INIT x[1:] ; for p: x_0 <- x_0^7 + K[p] ;
+#                                              (x_0, x[1:]) <- (25 x_0 + V[p].x[1:], x[1:] + x_0 W[p])
+# The factorisation is derived here from RC and the MDS matrix and checked against the naive
+# permutation; it need not (and is not claimed to) reproduce plonky2's constant tables word for
+# word -- only the permutation, which the KATs pin.
+def mds_matrix():
+    m = [[0] * 12 for _ in range(12)]
+    for r in range(12):
+        for i in range(12):
+            m[r][(i + r) % 12] = (m[r][(i + r) % 12] + MDS_CIRC[i]) % P
+        m[r][r] = (m[r][r] + MDS_DIAG[r]) % P
+    return m
+
+
+def mat_mul(a, b):
+    n, k, m = len(a), len(b), len(b[0])
+    return [[sum(a[i][t] * b[t][j] for t in range(k)) % P for j in range(m)] for i in range(n)]
+
+
+def mat_vec(a, v):
+    return [sum(a[i][j] * v[j] for j in range(len(v))) % P for i in range(len(a))]
+
+
+def mat_inv(a):
+    n = len(a)
+    a = [list(row) + [1 if i == j else 0 for j in range(n)] for i, row in enumerate(a)]
+    for c in range(n):
+        piv = next(r for r in range(c, n) if a[r][c])
+        a[c], a[piv] = a[piv], a[c]
+        inv = pow(a[c][c], P - 2, P)
+        a[c] = [x * inv % P for x in a[c]]
+        for r in range(n):
+            if r != c and a[r][c]:
+                f = a[r][c]
+                a[r] = [(x - f * y) % P for x, y in zip(a[r], a[c])]
+    return [row[n:] for row in a]
+
+
+def fast_partial_constants(rc):
+    M = mds_matrix()
+    Minv = mat_inv(M)
+    # constants: push every partial-round constant vector back through the linear layers
+    K = [0] * 22
+    acc = list(rc[12 * 25:12 * 26])  # constants of the last partial round (global round 25)
+    for p in range(21, 0, -1):
+        d = mat_vec(Minv, acc)
+        K[p - 1] = d[0]
+        prev = rc[12 * (4 + p - 1):12 * (4 + p)]
+        acc = [prev[0]] + [(prev[i] + d[i]) % P for i in range(1, 12)]
+    first = acc
+    # matrices: M_eff = SPARSE_p * DENSE'_p, DENSE' = diag(1, Mhat) moves back one round
+    V, W = [None] * 22, [None] * 22
+    Meff = M
+    for p in range(21, -1, -1):
+        Mhat = [row[1:] for row in Meff[1:]]
+        w = [Meff[i][0] for i in range(1, 12)]
+        v = Meff[0][1:]
+        MhatInv = mat_inv(Mhat)
+        vhat = [sum(v[t] * MhatInv[t][j] for t in range(11)) % P for j in range(11)]  # v^T Mhat^-1
+        assert Meff[0][0] == 25
+        V[p], W[p] = vhat, w
+        Mprime = [[1] + [0] * 11] + [[0] + row for row in Mhat]
+        Meff = mat_mul(Mprime, M)
+    init = [row[1:] for row in Mprime[1:]]  # 11 x 11, applied to x[1:] before the first partial round
+    return first, init, K, V, W
+
+
+def poseidon_fast(state, rc, fc):
+    first, init, K, V, W = fc
+    s = list(state)
+    for r in range(4):
+        s = [pow((s[i] + rc[12 * r + i]) % P, 7, P) for i in range(12)]
+        s = mds(s)
+    s = [(s[i] + first[i]) % P for i in range(12)]
+    s = [s[0]] + mat_vec(init, s[1:])
+    for p in range(22):
+        s0 = (pow(s[0], 7, P) + K[p]) % P
+        d = (25 * s0 + sum(V[p][i] * s[1 + i] for i in range(11))) % P
+        s = [d] + [(s[1 + i] + s0 * W[p][i]) % P for i in range(11)]
+    for r in range(26, 30):
+        s = [pow((s[i] + rc[12 * r + i]) % P, 7, P) for i in range(12)]
+        s = mds(s)
+    return s
+
+
+def c_list(name, vals, per_line=4):
+    out = "#define %s \\\n" % name
+    for i in range(0, len(vals), per_line):
+        out += "  " + ", ".join("0x%016xULL" % c for c in vals[i:i + per_line])
+        out += ", \\\n" if i + per_line < len(vals) else "\n"
+    return out
+
+
+def emit(path, rc, guard, fc=None):
     with open(path, "w") as f:
         f.write("/* Generated by tools/gen_poseidon_constants.py -- do not edit.\n"
                 " * Poseidon-Goldilocks width-12 round constants (plonky2 hash/poseidon_goldilocks.rs\n"
                 " * ALL_ROUND_CONSTANTS), regenerated offline and pinned by the all-zeros KAT. */\n")
         f.write("#ifndef %s\n#define %s\n" % (guard, guard))
         f.write("#define POSEIDON_N_RC 360\n")
-        f.write("#define POSEIDON_RC_LIST \\\n")
-        for i in range(0, 360, 4):
-            f.write("  " + ", ".join("0x%016xULL" % c for c in rc[i:i + 4]) + (", \\\n" if i + 4 < 360 else "\n"))
+        f.write(c_list("POSEIDON_RC_LIST", rc))
+        if fc is not None:
+            first, init, K, V, W = fc
+            f.write("/* fast partial rounds: derived from RC and the MDS matrix, checked against the naive form */\n")
+            f.write(c_list("POSEIDON_FAST_FIRST_LIST", first))
+            f.write(c_list("POSEIDON_FAST_INIT_LIST", [x for row in init for x in row]))  # [11][11] row-major
+            f.write(c_list("POSEIDON_FAST_K_LIST", K))
+            f.write(c_list("POSEIDON_FAST_V_LIST", [x for row in V for x in row]))  # [22][11]
+            f.write(c_list("POSEIDON_FAST_W_LIST", [x for row in W for x in row]))  # [22][11]
         f.write("#endif\n")
 
 
@@ -130,12 +234,19 @@ def main():
     assert rc[:12] == FIRST12, "first 12 constants differ from the recalled upstream values"
     assert max(rc) < 0xfffeeac900011537
     assert poseidon_naive([0] * 12, rc) == KAT_ZERO, "all-zeros KAT mismatch"
+    fc = fast_partial_constants(rc)
+    import random
+    rnd = random.Random(1)
+    for t in range(6):
+        st = [0] * 12 if t == 0 else [P - 1] * 12 if t == 1 else [rnd.randrange(P) for _ in range(12)]
+        assert poseidon_fast(st, rc, fc) == poseidon_naive(st, rc), "fast partial rounds differ from naive"
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     emit(os.path.join(root, "oracle", "poseidon_rc.h"), rc, "ORACLE_POSEIDON_RC_H")
-    emit(os.path.join(root, "0-kno-blobstreamx_b200", "csrc", "poseidon_rc.h"), rc, "BSX_POSEIDON_RC_H")
-    print("ok: 360 constants, KAT(zeros) matches")
+    emit(os.path.join(root, "0-kno-blobstreamx_b200", "csrc", "poseidon_rc.h"), rc, "BSX_POSEIDON_RC_H", fc)
+    print("ok: 360 constants, KAT(zeros) matches, fast partial rounds == naive")
     for name, inp in (("0..11", list(range(12))), ("p-1", [P - 1] * 12)):
         print(name, " ".join("%016x" % x for x in poseidon_naive(inp, rc)))
+    print("max |init|", max(max(r) for r in fc[1]), "K[21]", fc[2][21])
 
 
 if __name__ == "__main__":
