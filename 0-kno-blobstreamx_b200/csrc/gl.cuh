@@ -53,6 +53,152 @@ __device__ __forceinline__ u64 gl_mul(u64 a, u64 b) {
 }
 __device__ __forceinline__ u64 gl_sqr(u64 a) { return gl_mul(a, a); }
 
+// ---------------------------------------------------------------------------------------------
+// Lazy arithmetic for the hot kernels.  "Lazy" values are any u64 (a representative of the
+// residue, not necessarily < p).  Everything below is branch-free inline PTX on 32-bit limbs so
+// that ptxas emits IMAD.WIDE.U32 (+carry-out / .X carry-in) for the products and IADD3/IMAD.X
+// carry chains for the reduction -- no IMAD.HI (quarter rate on B200, tools/microbench/pipes.cu)
+// and no compare+select sequences.  ~20 SASS instructions per multiply instead of ~36.
+
+// 128-bit product + 64-bit addend, reduced:  a * b + c  (mod p), all lazy.
+//   x = x0 + x1 2^32 + x2 2^64 + x3 2^96 == (x1:x0) - x3 + x2 * EPS   (2^64 == EPS, 2^96 == -1)
+__device__ __forceinline__ u64 gl_mul_add_lazy(u64 a, u64 b, u64 c) {
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32);
+    u32 c0 = (u32)c, c1 = (u32)(c >> 32), r0, r1;
+    asm("{\n\t.reg .u32 x0,x1,x2,x3,t0,t1,t2,m,e0,e1;\n\t.reg .u64 w0,w3,t,e;\n\t"
+        "mul.wide.u32 w0, %2, %4;\n\t"
+        "mul.wide.u32 w3, %3, %5;\n\t"
+        "mul.wide.u32 t, %2, %5;\n\t"
+        "mov.b64 {t0,t1}, t;\n\t"
+        "mad.lo.cc.u32 t0, %3, %4, t0;\n\t"
+        "madc.hi.cc.u32 t1, %3, %4, t1;\n\t"
+        "addc.u32 t2, 0, 0;\n\t"
+        "mov.b64 {x0,x1}, w0;\n\t"
+        "mov.b64 {x2,x3}, w3;\n\t"
+        "add.cc.u32 x1, x1, t0;\n\t"
+        "addc.cc.u32 x2, x2, t1;\n\t"
+        "addc.u32 x3, x3, t2;\n\t"
+        "add.cc.u32 x0, x0, %6;\n\t"  // + c (cannot overflow 128 bits)
+        "addc.cc.u32 x1, x1, %7;\n\t"
+        "addc.cc.u32 x2, x2, 0;\n\t"
+        "addc.u32 x3, x3, 0;\n\t"
+        "sub.cc.u32 x0, x0, x3;\n\t"  // (x1:x0) - x3, borrowed 2^64 == EPS
+        "subc.cc.u32 x1, x1, 0;\n\t"
+        "subc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 x0, x0, m;\n\t"
+        "subc.u32 x1, x1, 0;\n\t"
+        "mul.wide.u32 e, x2, 0xFFFFFFFF;\n\t"  // + x2 * EPS, wrapped 2^64 == EPS
+        "mov.b64 {e0,e1}, e;\n\t"
+        "add.cc.u32 x0, x0, e0;\n\t"
+        "addc.cc.u32 x1, x1, e1;\n\t"
+        "addc.u32 t2, 0, 0;\n\t"
+        "sub.u32 m, 0, t2;\n\t"
+        "add.cc.u32 %0, x0, m;\n\t"
+        "addc.u32 %1, x1, 0;\n\t}"
+        : "=r"(r0), "=r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(c0), "r"(c1));
+    return ((u64)r1 << 32) | r0;
+}
+
+// a * b (mod p), lazy in, lazy out
+__device__ __forceinline__ u64 gl_mul_lazy(u64 a, u64 b) {
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32), r0, r1;
+    asm("{\n\t.reg .u32 x0,x1,x2,x3,t0,t1,t2,m,e0,e1;\n\t.reg .u64 w0,w3,t,e;\n\t"
+        "mul.wide.u32 w0, %2, %4;\n\t"
+        "mul.wide.u32 w3, %3, %5;\n\t"
+        "mul.wide.u32 t, %2, %5;\n\t"
+        "mov.b64 {t0,t1}, t;\n\t"
+        "mad.lo.cc.u32 t0, %3, %4, t0;\n\t"
+        "madc.hi.cc.u32 t1, %3, %4, t1;\n\t"
+        "addc.u32 t2, 0, 0;\n\t"
+        "mov.b64 {x0,x1}, w0;\n\t"
+        "mov.b64 {x2,x3}, w3;\n\t"
+        "add.cc.u32 x1, x1, t0;\n\t"
+        "addc.cc.u32 x2, x2, t1;\n\t"
+        "addc.u32 x3, x3, t2;\n\t"
+        "sub.cc.u32 x0, x0, x3;\n\t"
+        "subc.cc.u32 x1, x1, 0;\n\t"
+        "subc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 x0, x0, m;\n\t"
+        "subc.u32 x1, x1, 0;\n\t"
+        "mul.wide.u32 e, x2, 0xFFFFFFFF;\n\t"
+        "mov.b64 {e0,e1}, e;\n\t"
+        "add.cc.u32 x0, x0, e0;\n\t"
+        "addc.cc.u32 x1, x1, e1;\n\t"
+        "addc.u32 t2, 0, 0;\n\t"
+        "sub.u32 m, 0, t2;\n\t"
+        "add.cc.u32 %0, x0, m;\n\t"
+        "addc.u32 %1, x1, 0;\n\t}"
+        : "=r"(r0), "=r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+    return ((u64)r1 << 32) | r0;
+}
+
+// a + b (mod p): a lazy, b CANONICAL (< p) -> lazy.  One wrap fix suffices:
+// a + b - 2^64 + EPS <= (2^64-1) + (p-1) - 2^64 + EPS < 2^64.
+__device__ __forceinline__ u64 gl_add_lazy_canon(u64 a, u64 b) {
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32), r0, r1;
+    asm("{\n\t.reg .u32 c,m;\n\t"
+        "add.cc.u32 %0, %2, %4;\n\t"
+        "addc.cc.u32 %1, %3, %5;\n\t"
+        "addc.u32 c, 0, 0;\n\t"
+        "sub.u32 m, 0, c;\n\t"
+        "add.cc.u32 %0, %0, m;\n\t"
+        "addc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+    return ((u64)r1 << 32) | r0;
+}
+
+// Five-limb accumulator for sums of up to 16 products: acc += a * b.
+struct gl_acc160 {
+    u32 x0, x1, x2, x3, x4;
+};
+__device__ __forceinline__ void gl_acc_mac(gl_acc160 &A, u64 a, u64 b) {
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32);
+    asm("{\n\t.reg .u32 y0,y1,y2,y3,t0,t1,t2;\n\t.reg .u64 w0,w3,t;\n\t"
+        "mul.wide.u32 w0, %5, %7;\n\t"
+        "mul.wide.u32 w3, %6, %8;\n\t"
+        "mul.wide.u32 t, %5, %8;\n\t"
+        "mov.b64 {t0,t1}, t;\n\t"
+        "mad.lo.cc.u32 t0, %6, %7, t0;\n\t"
+        "madc.hi.cc.u32 t1, %6, %7, t1;\n\t"
+        "addc.u32 t2, 0, 0;\n\t"
+        "mov.b64 {y0,y1}, w0;\n\t"
+        "mov.b64 {y2,y3}, w3;\n\t"
+        "add.cc.u32 y1, y1, t0;\n\t"
+        "addc.cc.u32 y2, y2, t1;\n\t"
+        "addc.u32 y3, y3, t2;\n\t"
+        "add.cc.u32 %0, %0, y0;\n\t"
+        "addc.cc.u32 %1, %1, y1;\n\t"
+        "addc.cc.u32 %2, %2, y2;\n\t"
+        "addc.cc.u32 %3, %3, y3;\n\t"
+        "addc.u32 %4, %4, 0;\n\t}"
+        : "+r"(A.x0), "+r"(A.x1), "+r"(A.x2), "+r"(A.x3), "+r"(A.x4)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+}
+// x0 + x1 2^32 + x2 2^64 + x3 2^96 + x4 2^128 == (x1:x0) - (x4:x3) + x2 * EPS   (2^128 == -2^32)
+__device__ __forceinline__ u64 gl_acc_reduce(const gl_acc160 &A) {
+    u32 r0, r1;
+    asm("{\n\t.reg .u32 x0,x1,m,t2,e0,e1;\n\t.reg .u64 e;\n\t"
+        "sub.cc.u32 x0, %2, %5;\n\t"
+        "subc.cc.u32 x1, %3, %6;\n\t"
+        "subc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 x0, x0, m;\n\t"
+        "subc.u32 x1, x1, 0;\n\t"
+        "mul.wide.u32 e, %4, 0xFFFFFFFF;\n\t"
+        "mov.b64 {e0,e1}, e;\n\t"
+        "add.cc.u32 x0, x0, e0;\n\t"
+        "addc.cc.u32 x1, x1, e1;\n\t"
+        "addc.u32 t2, 0, 0;\n\t"
+        "sub.u32 m, 0, t2;\n\t"
+        "add.cc.u32 %0, x0, m;\n\t"
+        "addc.u32 %1, x1, 0;\n\t}"
+        : "=r"(r0), "=r"(r1)
+        : "r"(A.x0), "r"(A.x1), "r"(A.x2), "r"(A.x3), "r"(A.x4));
+    return ((u64)r1 << 32) | r0;
+}
+
 // small-constant multiply: c < 2^32, a canonical
 __device__ __forceinline__ u64 gl_mul_small(u64 a, u32 c) {
     u64 l = (u64)(u32)a * c;

@@ -19,18 +19,23 @@ __global__ void __launch_bounds__(256) leaf_hash_kernel(const u64 *__restrict__ 
     if (n_cols <= 4) {  // hash_or_noop: zero-extend, no permutation
         for (int c = 0; c < n_cols; c++) s[c] = p[(size_t)c * col_stride];
     } else {
-        int c = 0;
-        for (; c + 8 <= n_cols; c += 8) {
+        // One permutation call site (code size), next chunk prefetched while the current one is
+        // permuted.  A short last chunk overwrites only its own lanes (no padding, hashing.rs).
+        u64 nxt[8];
 #pragma unroll
-            for (int i = 0; i < 8; i++) s[i] = __ldg(p + (size_t)(c + i) * col_stride);
-            poseidon_permute(s);
-        }
-        if (c < n_cols) {  // short last chunk: the remaining rate lanes keep their values
+        for (int i = 0; i < 8; i++) nxt[i] = i < n_cols ? __ldg(p + (size_t)i * col_stride) : 0;
+#pragma unroll 1
+        for (int c = 0; c < n_cols; c += 8) {
 #pragma unroll
             for (int i = 0; i < 8; i++)
-                if (c + i < n_cols) s[i] = __ldg(p + (size_t)(c + i) * col_stride);
-            poseidon_permute(s);
+                if (c + i < n_cols) s[i] = nxt[i];
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                if (c + 8 + i < n_cols) nxt[i] = __ldg(p + (size_t)(c + 8 + i) * col_stride);
+            poseidon_permute_lazy(s);
         }
+#pragma unroll
+        for (int i = 0; i < 4; i++) s[i] = gl_canon(s[i]);
     }
     ulonglong2 *o = reinterpret_cast<ulonglong2 *>(digests + 4 * row);
     o[0] = make_ulonglong2(s[0], s[1]);
@@ -52,7 +57,9 @@ __global__ void __launch_bounds__(256) merkle_level_kernel(const u64 *__restrict
     const ulonglong2 *c = reinterpret_cast<const ulonglong2 *>(children + 8 * i);
     ulonglong2 a = c[0], b = c[1], d = c[2], e = c[3];
     u64 s[12] = {a.x, a.y, b.x, b.y, d.x, d.y, e.x, e.y, 0, 0, 0, 0};
-    poseidon_permute(s);
+    poseidon_permute_lazy(s);
+#pragma unroll
+    for (int t = 0; t < 4; t++) s[t] = gl_canon(s[t]);
     ulonglong2 *o = reinterpret_cast<ulonglong2 *>(parents + 4 * i);
     o[0] = make_ulonglong2(s[0], s[1]);
     o[1] = make_ulonglong2(s[2], s[3]);
@@ -98,7 +105,9 @@ __global__ void __launch_bounds__(256) merkle_subtree_kernel(const u64 *__restri
                 for (int t = 0; t < 8; t++) s[t] = c[t];
             }
             s[8] = s[9] = s[10] = s[11] = 0;
-            poseidon_permute(s);
+            poseidon_permute_lazy(s);
+#pragma unroll
+            for (int t = 0; t < 4; t++) s[t] = gl_canon(s[t]);
             u64 *d_s = sm[buf] + 4 * i;
             d_s[0] = s[0]; d_s[1] = s[1]; d_s[2] = s[2]; d_s[3] = s[3];
             ulonglong2 *o = reinterpret_cast<ulonglong2 *>(dst_g + 4 * (base_out + i));

@@ -1,21 +1,55 @@
 // poseidon.cuh -- Poseidon-Goldilocks width-12 x^7 permutation and the sponge modes built on it.
-// Replaces plonky2 hash/poseidon.rs (`Poseidon::poseidon`), hash/poseidon_goldilocks.rs (constants,
-// MDS) and hash/hashing.rs (`hash_n_to_hash_no_pad`, `compress`).  Round structure 4 full +
-// 22 partial + 4 full; MDS = circulant(17,15,41,16,2,28,13,13,39,18,34,20) + diag(8,0,...).
+// Replaces plonky2 hash/poseidon.rs (`Poseidon::poseidon`, `full_rounds`, `partial_rounds`,
+// `mds_partial_layer_init/fast`), hash/poseidon_goldilocks.rs (constants, MDS) and hash/hashing.rs
+// (`hash_n_to_hash_no_pad`, `compress`).  Round structure 4 full + 22 partial + 4 full; MDS =
+// circulant(17,15,41,16,2,28,13,13,39,18,34,20) + diag(8,0,...).
+//
+// B200 shape of the computation (measured choices):
+//  * state lives in registers as LAZY u64 (any representative), canonicalised only on output;
+//  * full rounds: x^7 by four lazy multiplies; the MDS layer runs on 32-bit halves with
+//    IMAD.WIDE accumulation, and the NEXT round's constants are the accumulators' initial values,
+//    so constant addition costs no instruction;
+//  * partial rounds use the sparse factorisation (23 multiplies instead of a dense 12x12 layer);
+//    its constants are derived by tools/gen_poseidon_constants.py and checked against the naive form;
+//  * one shared full-round body and one partial-round body (no unrolling over rounds): the whole
+//    permutation is ~30 KB of SASS and stays inside the instruction cache (v1 was 112 KB and stalled
+//    on instruction fetch for 12.6 warp-cycles per issue).
 #pragma once
 #include "gl.cuh"
 #include "poseidon_rc.h"
 
 __constant__ u64 POSEIDON_RC[POSEIDON_N_RC] = {POSEIDON_RC_LIST};
+__constant__ u64 POSEIDON_POST_LO[96] = {POSEIDON_POST_LO_LIST};
+__constant__ u64 POSEIDON_POST_HI[96] = {POSEIDON_POST_HI_LIST};
+__constant__ u64 POSEIDON_FAST_INIT[121] = {POSEIDON_FAST_INIT_LIST};
+__constant__ u64 POSEIDON_FAST_K[22] = {POSEIDON_FAST_K_LIST};
+__constant__ u64 POSEIDON_FAST_V[242] = {POSEIDON_FAST_V_LIST};
+__constant__ u64 POSEIDON_FAST_W[242] = {POSEIDON_FAST_W_LIST};
 
 __device__ __forceinline__ u64 poseidon_sbox(u64 x) {
-    u64 x2 = gl_sqr(x), x4 = gl_sqr(x2), x3 = gl_mul(x, x2);
-    return gl_mul(x3, x4);
+    u64 x2 = gl_mul_lazy(x, x), x4 = gl_mul_lazy(x2, x2), x3 = gl_mul_lazy(x, x2);
+    return gl_mul_lazy(x3, x4);
 }
 
-// MDS layer on 32-bit halves: each 12-term dot product with constants <= 41 stays below 2^42, so
-// the low and high halves accumulate in plain u64 (IMAD.WIDE) and are recombined and reduced once.
-__device__ __forceinline__ void poseidon_mds(u64 s[12]) {
+// al + ah * 2^32 (al, ah < 2^43) -> lazy u64.   ah = hh 2^32 + hl:  == al + hh * EPS + hl 2^32
+__device__ __forceinline__ u64 poseidon_fold96(u64 al, u64 ah) {
+    u32 hl = (u32)ah, hh = (u32)(ah >> 32), r0, r1;
+    u64 t = (u64)hh * 0xFFFFFFFFu + al;  // < 2^44, no overflow
+    u32 t0 = (u32)t, t1 = (u32)(t >> 32);
+    asm("{\n\t.reg .u32 c,m;\n\t"
+        "add.cc.u32 %1, %3, %4;\n\t"   // high word += hl; a wrap is worth EPS, and the high word is
+        "addc.u32 c, 0, 0;\n\t"         // then < 2^12 so adding EPS cannot wrap again
+        "sub.u32 m, 0, c;\n\t"
+        "add.cc.u32 %0, %2, m;\n\t"
+        "addc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(t0), "r"(t1), "r"(hl));
+    return ((u64)r1 << 32) | r0;
+}
+
+// MDS layer with the following constant vector fused: s <- M s + post, post given as 32-bit halves.
+__device__ __forceinline__ void poseidon_mds_post(u64 s[12], const u64 *__restrict__ post_lo,
+                                                  const u64 *__restrict__ post_hi) {
     const u32 C[12] = {17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20};
     u32 lo[12], hi[12];
 #pragma unroll
@@ -25,7 +59,7 @@ __device__ __forceinline__ void poseidon_mds(u64 s[12]) {
     }
 #pragma unroll
     for (int r = 0; r < 12; r++) {
-        u64 al = 0, ah = 0;
+        u64 al = post_lo[r], ah = post_hi[r];
 #pragma unroll
         for (int i = 0; i < 12; i++) {
             al += (u64)C[i] * lo[(i + r) % 12];
@@ -35,49 +69,67 @@ __device__ __forceinline__ void poseidon_mds(u64 s[12]) {
             al += (u64)8 * lo[0];
             ah += (u64)8 * hi[0];
         }
-        // value = al + ah * 2^32 < 2^75: fold the part above 2^64 with 2^64 == EPS
-        u64 low = al + (ah << 32);
-        u64 top = (ah >> 32) + (low < al ? 1 : 0);  // < 2^11
-        u64 t1 = (top << 32) - top;                  // top * EPS
-        u64 v = low + t1;
-        if (v < t1) v += GL_EPS;
-        s[r] = gl_canon(v);
+        s[r] = poseidon_fold96(al, ah);
     }
 }
 
-// state canonical in, canonical out
+// lazy in, lazy out
+__device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
+#pragma unroll
+    for (int i = 0; i < 12; i++) s[i] = gl_add_lazy_canon(s[i], POSEIDON_RC[i]);
+#pragma unroll 1
+    for (int half = 0; half < 2; half++) {
+#pragma unroll 1
+        for (int r = 0; r < 4; r++) {
+#pragma unroll
+            for (int i = 0; i < 12; i++) s[i] = poseidon_sbox(s[i]);
+            const int j = half * 4 + r;
+            poseidon_mds_post(s, POSEIDON_POST_LO + 12 * j, POSEIDON_POST_HI + 12 * j);
+        }
+        if (half == 0) {
+            // mds_partial_layer_init: x[1:] <- INIT x[1:] (dense 11x11, once per permutation).  Rows are
+            // produced by a rolled loop into a small local array to keep the code short.
+            u64 t[11];
+#pragma unroll 1
+            for (int r = 0; r < 11; r++) {
+                gl_acc160 A = {0, 0, 0, 0, 0};
+#pragma unroll
+                for (int c = 0; c < 11; c++) gl_acc_mac(A, s[1 + c], POSEIDON_FAST_INIT[11 * r + c]);
+                t[r] = gl_acc_reduce(A);
+            }
+#pragma unroll
+            for (int r = 0; r < 11; r++) s[1 + r] = t[r];
+#pragma unroll 1
+            for (int p = 0; p < 22; p++) {
+                u64 s0 = gl_add_lazy_canon(poseidon_sbox(s[0]), POSEIDON_FAST_K[p]);
+                // d = 25 s0 + V[p] . x[1:]
+                gl_acc160 A = {0, 0, 0, 0, 0};
+                gl_acc_mac(A, s0, 25);
+#pragma unroll
+                for (int i = 0; i < 11; i++) gl_acc_mac(A, s[1 + i], POSEIDON_FAST_V[11 * p + i]);
+#pragma unroll
+                for (int i = 0; i < 11; i++) s[1 + i] = gl_mul_add_lazy(s0, POSEIDON_FAST_W[11 * p + i], s[1 + i]);
+                s[0] = gl_acc_reduce(A);
+            }
+#pragma unroll
+            for (int i = 0; i < 12; i++) s[i] = gl_add_lazy_canon(s[i], POSEIDON_RC[12 * 26 + i]);
+        }
+    }
+}
+
+// state canonical (or lazy) in, canonical out
 __device__ __forceinline__ void poseidon_permute(u64 s[12]) {
-    int rc = 0;
-#pragma unroll 1
-    for (int r = 0; r < 4; r++) {
+    poseidon_permute_lazy(s);
 #pragma unroll
-        for (int i = 0; i < 12; i++) s[i] = poseidon_sbox(gl_add(s[i], POSEIDON_RC[rc + i]));
-        poseidon_mds(s);
-        rc += 12;
-    }
-#pragma unroll 1
-    for (int r = 0; r < 22; r++) {
-#pragma unroll
-        for (int i = 0; i < 12; i++) s[i] = gl_add(s[i], POSEIDON_RC[rc + i]);
-        s[0] = poseidon_sbox(s[0]);
-        poseidon_mds(s);
-        rc += 12;
-    }
-#pragma unroll 1
-    for (int r = 0; r < 4; r++) {
-#pragma unroll
-        for (int i = 0; i < 12; i++) s[i] = poseidon_sbox(gl_add(s[i], POSEIDON_RC[rc + i]));
-        poseidon_mds(s);
-        rc += 12;
-    }
+    for (int i = 0; i < 12; i++) s[i] = gl_canon(s[i]);
 }
 
 // PoseidonHash::two_to_one: state = [l, r, 0, 0, 0, 0]; permute; first four words
 __device__ __forceinline__ void poseidon_two_to_one(const u64 l[4], const u64 r[4], u64 out[4]) {
     u64 s[12] = {l[0], l[1], l[2], l[3], r[0], r[1], r[2], r[3], 0, 0, 0, 0};
-    poseidon_permute(s);
-    out[0] = s[0];
-    out[1] = s[1];
-    out[2] = s[2];
-    out[3] = s[3];
+    poseidon_permute_lazy(s);
+    out[0] = gl_canon(s[0]);
+    out[1] = gl_canon(s[1]);
+    out[2] = gl_canon(s[2]);
+    out[3] = gl_canon(s[3]);
 }

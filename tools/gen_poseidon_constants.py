@@ -226,6 +226,13 @@ def emit(path, rc, guard, fc=None):
             f.write(c_list("POSEIDON_FAST_K_LIST", K))
             f.write(c_list("POSEIDON_FAST_V_LIST", [x for row in V for x in row]))  # [22][11]
             f.write(c_list("POSEIDON_FAST_W_LIST", [x for row in W for x in row]))  # [22][11]
+            # constants added right after the MDS of full round j (j = 0..7): the next round's RC, the
+            # fast-partial FIRST vector after round 3, nothing after the last round; 32-bit halves as u64
+            post = [rc[12:24], rc[24:36], rc[36:48], first, rc[12 * 27:12 * 28], rc[12 * 28:12 * 29],
+                    rc[12 * 29:12 * 30], [0] * 12]
+            flat = [x for row in post for x in row]
+            f.write(c_list("POSEIDON_POST_LO_LIST", [x & M32 for x in flat]))  # [8][12]
+            f.write(c_list("POSEIDON_POST_HI_LIST", [x >> 32 for x in flat]))  # [8][12]
         f.write("#endif\n")
 
 
