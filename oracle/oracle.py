@@ -192,3 +192,128 @@ def num_threads():
 
 def set_num_threads(n):
     lib().orc_set_num_threads(C.c_int(n))
+
+
+# ------------------------------------------------------------------ challenger / FRI
+class Challenger(C.Structure):
+    """plonky2 iop/challenger.rs `Challenger<GoldilocksField, PoseidonHash>` (oracle side)."""
+    _fields_ = [("state", C.c_uint64 * 12), ("inbuf", C.c_uint64 * 8), ("outbuf", C.c_uint64 * 8),
+                ("n_in", C.c_int32), ("n_out", C.c_int32)]
+
+    def __init__(self):
+        super().__init__()
+        lib().orc_challenger_init(C.byref(self))
+
+    def observe(self, xs):
+        xs = _a(np.atleast_1d(xs)).reshape(-1)
+        lib().orc_challenger_observe_many(C.byref(self), _ptr(xs), C.c_size_t(xs.size))
+
+    def get_challenge(self):
+        f = lib().orc_challenger_get
+        f.restype = C.c_uint64
+        return int(f(C.byref(self)))
+
+    def get_extension_challenge(self):
+        out = np.zeros(2, dtype=np.uint64)
+        lib().orc_challenger_get_ext(C.byref(self), _ptr(out))
+        return out
+
+    def copy(self):
+        c = Challenger()
+        C.memmove(C.byref(c), C.byref(self), C.sizeof(Challenger))
+        return c
+
+    def snapshot(self):
+        return (list(self.state), list(self.inbuf)[:self.n_in], list(self.outbuf)[:self.n_out])
+
+
+class _BatchView(C.Structure):
+    _fields_ = [("log_n", C.c_int32), ("n_cols", C.c_int32), ("n_salt", C.c_int32), ("rate_bits", C.c_int32),
+                ("cap_height", C.c_int32), ("coeffs", C.c_void_p), ("leaves", C.c_void_p), ("digests", C.c_void_p),
+                ("cap", C.c_void_p)]
+
+
+class _FriInstance(C.Structure):
+    _fields_ = [("n_batches", C.c_int32), ("points", C.c_void_p), ("n_polys", C.c_void_p),
+                ("poly_oracle", C.c_void_p), ("poly_index", C.c_void_p)]
+
+
+class _FriParams(C.Structure):
+    _fields_ = [("degree_bits", C.c_int32), ("rate_bits", C.c_int32), ("cap_height", C.c_int32),
+                ("proof_of_work_bits", C.c_int32), ("num_query_rounds", C.c_int32), ("n_arity", C.c_int32),
+                ("arity_bits", C.c_int32 * 16)]
+
+
+def _views(batches, rate_bits, cap_height):
+    """batches: list of dicts from batch_from_values (coeffs, leaves, digests, cap)."""
+    arr = (_BatchView * len(batches))()
+    keep = []
+    for i, b in enumerate(batches):
+        n_cols, n = b["coeffs"].shape
+        co, lv, cp = _a(b["coeffs"]), _a(b["leaves"]), _a(b["cap"])
+        dg = _a(b["digests"]) if b["digests"] is not None else np.zeros(4, np.uint64)
+        keep += [co, lv, cp, dg]
+        arr[i] = _BatchView(int(np.log2(n)), n_cols, lv.shape[1] - n_cols, rate_bits, cap_height,
+                            co.ctypes.data, lv.ctypes.data, dg.ctypes.data, cp.ctypes.data)
+    return arr, keep
+
+
+def _instance(points, polys):
+    """points: (n_batches, 2); polys: per batch list of (oracle_index, poly_index)."""
+    pts = _a(points).reshape(-1, 2)
+    n_polys = np.array([len(p) for p in polys], dtype=np.int32)
+    po = np.array([o for p in polys for o, _ in p], dtype=np.int32)
+    pi = np.array([i for p in polys for _, i in p], dtype=np.int32)
+    inst = _FriInstance(len(polys), pts.ctypes.data, n_polys.ctypes.data, po.ctypes.data, pi.ctypes.data)
+    return inst, [pts, n_polys, po, pi]
+
+
+def _params(degree_bits, rate_bits, cap_height, pow_bits, num_queries, arity_bits):
+    p = _FriParams(degree_bits, rate_bits, cap_height, pow_bits, num_queries, len(arity_bits))
+    for i, a in enumerate(arity_bits):
+        p.arity_bits[i] = a
+    return p
+
+
+def fri_final_poly(batches, rate_bits, cap_height, points, polys, alpha):
+    v, k1 = _views(batches, rate_bits, cap_height)
+    inst, k2 = _instance(points, polys)
+    n = batches[0]["coeffs"].shape[1]
+    out = np.zeros((n, 2), dtype=np.uint64)
+    al = _a(alpha)
+    rc = lib().orc_fri_final_poly(v, len(batches), C.byref(inst), _ptr(al), _ptr(out))
+    assert rc == 0
+    return out
+
+
+def fri_prove_openings(batches, points, polys, challenger, degree_bits, rate_bits, cap_height, pow_bits,
+                       num_queries, arity_bits):
+    """PolynomialBatch::prove_openings restated; returns the flat proof (layout in plonky2_fri_oracle.c)."""
+    v, k1 = _views(batches, rate_bits, cap_height)
+    inst, k2 = _instance(points, polys)
+    fp = _params(degree_bits, rate_bits, cap_height, pow_bits, num_queries, arity_bits)
+    f = lib().orc_fri_proof_words
+    f.restype = C.c_size_t
+    proof = np.zeros(f(v, len(batches), C.byref(fp)), dtype=np.uint64)
+    rc = lib().orc_fri_prove_openings(v, len(batches), C.byref(inst), C.byref(challenger), C.byref(fp), _ptr(proof))
+    if rc != 0:
+        raise ValueError("orc_fri_prove_openings failed")
+    return proof
+
+
+def eval_poly_ext(batch, poly_index, z, rate_bits=0, cap_height=0):
+    v, k = _views([batch], rate_bits, cap_height)
+    out = np.zeros(2, dtype=np.uint64)
+    zz = _a(z)
+    lib().orc_eval_poly_ext(v, C.c_int(poly_index), _ptr(zz), _ptr(out))
+    return out
+
+
+def fri_verify(batches, points, polys, openings, challenger, degree_bits, rate_bits, cap_height, pow_bits,
+               num_queries, arity_bits, proof):
+    v, k1 = _views(batches, rate_bits, cap_height)
+    inst, k2 = _instance(points, polys)
+    fp = _params(degree_bits, rate_bits, cap_height, pow_bits, num_queries, arity_bits)
+    op, pr = _a(openings), _a(proof)
+    return bool(lib().orc_fri_verify(v, len(batches), C.byref(inst), _ptr(op), C.byref(challenger), C.byref(fp),
+                                     _ptr(pr)))

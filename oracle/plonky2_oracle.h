@@ -83,6 +83,57 @@ int orc_batch_from_coeffs(const uint64_t *coeffs, int log_n, int n_cols, int rat
                           int cap_height, const uint64_t *salt, int n_salt, uint64_t *leaves,
                           uint64_t *digests, uint64_t *cap);
 
+
+/* ---- Challenger (iop/challenger.rs), Poseidon duplex sponge in overwrite mode ---- */
+typedef struct orc_challenger {
+    uint64_t state[12];
+    uint64_t in[8];
+    uint64_t out[8];
+    int32_t n_in, n_out;
+} orc_challenger;
+void orc_challenger_init(orc_challenger *c);
+void orc_challenger_observe(orc_challenger *c, uint64_t x);
+void orc_challenger_observe_many(orc_challenger *c, const uint64_t *x, size_t n);
+uint64_t orc_challenger_get(orc_challenger *c);
+void orc_challenger_get_ext(orc_challenger *c, uint64_t out[2]);
+
+/* ---- FRI (fri/oracle.rs prove_openings, fri/prover.rs, fri/verifier.rs) ---- */
+typedef struct orc_batch_view { /* one committed PolynomialBatch as produced by orc_batch_from_* */
+    int32_t log_n, n_cols, n_salt, rate_bits, cap_height;
+    const uint64_t *coeffs;  /* n_cols x 2^log_n, natural order */
+    const uint64_t *leaves;  /* 2^(log_n+rate_bits) x (n_cols+n_salt) row-major */
+    const uint64_t *digests; /* level order */
+    const uint64_t *cap;
+} orc_batch_view;
+typedef struct orc_fri_instance { /* FriInstanceInfo.batches: opening point + (oracle, polynomial) list each */
+    int32_t n_batches;
+    const uint64_t *points;     /* n_batches x 2 (extension) */
+    const int32_t *n_polys;     /* per batch */
+    const int32_t *poly_oracle; /* concatenated over batches */
+    const int32_t *poly_index;
+} orc_fri_instance;
+typedef struct orc_fri_params { /* FriParams + FriConfig */
+    int32_t degree_bits, rate_bits, cap_height, proof_of_work_bits, num_query_rounds;
+    int32_t n_arity;
+    int32_t arity_bits[16];
+} orc_fri_params;
+int orc_fri_final_poly(const orc_batch_view *oracles, int n_oracles, const orc_fri_instance *inst,
+                       const uint64_t alpha[2], uint64_t *out /* 2^log_n x 2 */);
+size_t orc_fri_proof_words(const orc_batch_view *oracles, int n_oracles, const orc_fri_params *fp);
+/* PolynomialBatch::prove_openings: draws alpha from the challenger, builds the final polynomial,
+ * LDE, then fri_proof (commit phase, PoW with the SMALLEST valid witness, query rounds).
+ * proof: flat u64 stream, layout in plonky2_fri_oracle.c.  The challenger is advanced exactly as upstream. */
+int orc_fri_prove_openings(const orc_batch_view *oracles, int n_oracles, const orc_fri_instance *inst,
+                           orc_challenger *ch, const orc_fri_params *fp, uint64_t *proof);
+/* fri/verifier.rs verify_fri_proof restated.  openings: per opening batch, the claimed evaluations of
+ * its polynomials (extension, concatenated in instance order).  `ch` must be in the state the prover's
+ * challenger had when prove_openings was called.  Returns 1 when the proof verifies, 0 otherwise. */
+int orc_fri_verify(const orc_batch_view *oracles /* only shapes + cap used */, int n_oracles,
+                   const orc_fri_instance *inst, const uint64_t *openings, orc_challenger *ch,
+                   const orc_fri_params *fp, const uint64_t *proof);
+/* evaluate polynomial `poly_index` of an oracle (coefficient form) at an extension point */
+void orc_eval_poly_ext(const orc_batch_view *o, int poly_index, const uint64_t z[2], uint64_t out[2]);
+
 int orc_num_threads(void);
 void orc_set_num_threads(int n);
 
