@@ -25,6 +25,16 @@ from .binding import (  # noqa: F401
     library_path,
     EXPORTED_SYMBOLS,
 )
-from .fri import FriConfig, FriParams, fri_reduction_arity_bits  # noqa: F401
+from .fri import (  # noqa: F401
+    Challenger,
+    FriConfig,
+    FriInstanceInfo,
+    FriParams,
+    final_poly,
+    fri_proof,
+    fri_proof_words,
+    fri_reduction_arity_bits,
+    prove_openings,
+)
 
 P = 0xFFFFFFFF00000001

@@ -15,7 +15,8 @@ EXPORTED_SYMBOLS = [
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
-    "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_ntt",
+    "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
+    "bsx_challenger_get", "bsx_fri_proof_words", "bsx_fri_prove_openings", "bsx_fri_proof", "bsx_fri_final_poly",
 ]
 
 
@@ -79,6 +80,13 @@ def lib():
         "bsx_merkle_shape": (i32, [vp] + [C.POINTER(i32)] * 3),
         "bsx_poseidon_permute": (i32, [vp, vp, i32, sz]),
         "bsx_ntt": (i32, [vp, vp, i32, i32, i32, i32, u64]),
+        "bsx_challenger_init": (None, [vp]),
+        "bsx_challenger_observe": (i32, [vp, vp, vp, sz]),
+        "bsx_challenger_get": (i32, [vp, vp, vp, i32]),
+        "bsx_fri_proof_words": (i32, [vp, i32, vp, C.POINTER(sz)]),
+        "bsx_fri_prove_openings": (i32, [vp, vp, i32, vp, vp, vp, vp]),
+        "bsx_fri_proof": (i32, [vp, vp, i32, vp, vp, vp, vp]),
+        "bsx_fri_final_poly": (i32, [vp, vp, i32, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

@@ -67,3 +67,24 @@ void launch_bitrev_copy(const u64 *src, size_t src_stride, u64 *dst, size_t dst_
 int ntt_max_single_pass_log();
 void ntt_init_device();
 void launch_fill_random(u64 *out, size_t n, u64 seed, cudaStream_t st);
+
+// ---------------------------------------------------------------- FRI / challenger (fri_kernels.cu)
+void launch_chal_observe(void *chal_dev, const u64 *data, size_t n, int mode, size_t plane_stride, cudaStream_t st);
+void launch_chal_get(void *chal_dev, u64 *out, int n, u64 modulus, cudaStream_t st);
+void launch_pow(const void *chal_dev, u64 base, u64 n, int pow_bits, u64 *best, cudaStream_t st);
+void launch_chal_pow_finish(void *chal_dev, const u64 *witness, u64 *response, cudaStream_t st);
+void launch_ext_powers(const u64 *alpha, u64 *pw, int n, cudaStream_t st);
+void launch_combine(const u64 *const *ptrs, const int *pw_index, int n_polys, const u64 *pw, size_t n, u64 *comp0,
+                    u64 *comp1, int accumulate, cudaStream_t st);
+size_t divide_by_linear_workspace_words(size_t n);
+void launch_divide_by_linear_accumulate(const u64 *comp0, const u64 *comp1, size_t n, const u64 *z, const u64 *sh,
+                                        u64 *fin0, u64 *fin1, u64 *work, cudaStream_t st);
+void launch_fri_fold(const u64 *in0, const u64 *in1, size_t n_out, int arity_bits, const u64 *beta, u64 *out0,
+                     u64 *out1, cudaStream_t st);
+void launch_fri_leaves(const u64 *v0, const u64 *v1, size_t len, int arity_bits, u64 *leaves, cudaStream_t st);
+void launch_fri_query_gather(const u64 *idx, int n_queries, int shift, const u64 *leaves, size_t col_stride, int width,
+                             const u64 *digests, int log_leaves, int n_sib, u64 *out, size_t q_stride, size_t off,
+                             cudaStream_t st);
+void launch_ext_interleave(const u64 *planar, size_t plane_stride, size_t n, u64 *out, cudaStream_t st);
+void launch_ext_deinterleave(const u64 *in, size_t n, u64 *planar, size_t plane_stride, cudaStream_t st);
+void launch_ext_pow(const u64 *a, u64 k, u64 *out, cudaStream_t st);

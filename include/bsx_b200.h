@@ -120,6 +120,60 @@ int32_t bsx_merkle_prove(bsx_tree *t, uint64_t leaf_index, uint64_t *siblings_ho
 int32_t bsx_merkle_digests(bsx_tree *t, uint64_t *out_host);
 int32_t bsx_merkle_shape(const bsx_tree *t, int32_t *log_leaves, int32_t *leaf_len, int32_t *cap_height);
 
+/* ---- Challenger (iop/challenger.rs) and FRI (fri/oracle.rs prove_openings, fri/prover.rs) -------------
+ * bsx_challenger mirrors plonky2's `Challenger<F, PoseidonHash>`: sponge state, input buffer, output
+ * buffer (outputs are popped from the BACK, as Vec::pop does).  The struct lives on the host between calls;
+ * the duplexing permutations run on the device. */
+typedef struct bsx_challenger {
+    uint64_t sponge_state[12];
+    uint64_t input_buffer[8];
+    uint64_t output_buffer[8];
+    int32_t n_input, n_output;
+} bsx_challenger;
+/* Challenger::new() */
+void bsx_challenger_init(bsx_challenger *ch);
+/* Challenger::observe_elements / observe_cap / observe_hash (n words) */
+int32_t bsx_challenger_observe(bsx_ctx *ctx, bsx_challenger *ch, const uint64_t *elems_host, size_t n);
+/* Challenger::get_n_challenges (get_extension_challenge = 2 challenges as [c0, c1]) */
+int32_t bsx_challenger_get(bsx_ctx *ctx, bsx_challenger *ch, uint64_t *out_host, int32_t n);
+
+/* FriInstanceInfo.batches: per opening batch a point (extension) and its (oracle index, polynomial index) list */
+typedef struct bsx_fri_instance {
+    int32_t n_batches;
+    const uint64_t *points;     /* n_batches x 2 */
+    const int32_t *n_polys;     /* per batch */
+    const int32_t *poly_oracle; /* concatenated over batches */
+    const int32_t *poly_index;
+} bsx_fri_instance;
+/* FriParams + FriConfig (fri/mod.rs); reduction_arity_bits as produced by FriReductionStrategy */
+typedef struct bsx_fri_params {
+    int32_t degree_bits, rate_bits, cap_height, proof_of_work_bits, num_query_rounds;
+    int32_t n_arity;
+    int32_t arity_bits[16];
+} bsx_fri_params;
+/* Words of the flat FriProof stream for these oracles/params.  Layout, in plonky2 `FriProof` field order:
+ *   commit_phase_merkle_caps[n_arity][2^cap_height][4]
+ *   query_round_proofs[num_query_rounds]: initial_trees_proof per oracle { leaf[width], siblings[..][4] },
+ *                                         steps per round { evals[2^arity][2], siblings[..][4] }
+ *   final_poly[2^(degree_bits - sum arity)][2]
+ *   pow_witness */
+int32_t bsx_fri_proof_words(bsx_batch *const *oracles, int32_t n_oracles, const bsx_fri_params *params, size_t *out);
+/* Replaces PolynomialBatch::prove_openings(instance, oracles, challenger, fri_params): draws alpha, builds
+ * the final polynomial (alpha-combination, division by (X - z), times X), LDE, then fri_proof.
+ * The proof-of-work witness is the SMALLEST valid one (upstream takes any).
+ * challenger is advanced exactly as upstream's is.  proof_host receives bsx_fri_proof_words() words. */
+int32_t bsx_fri_prove_openings(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
+                               const bsx_fri_instance *instance, bsx_challenger *challenger,
+                               const bsx_fri_params *params, uint64_t *proof_host);
+/* Replaces fri::prover::fri_proof(initial_merkle_trees, lde_polynomial_coeffs, lde_polynomial_values, ..):
+ * lde_coeffs_host = 2^(degree_bits + rate_bits) extension coefficients [c0, c1] (only the first 1/rate are
+ * non-zero); the values are recomputed on the device. */
+int32_t bsx_fri_proof(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles, const uint64_t *lde_coeffs_host,
+                      bsx_challenger *challenger, const bsx_fri_params *params, uint64_t *proof_host);
+/* test hook: the final polynomial of prove_openings for a given alpha -> out_host[2^degree_bits][2] */
+int32_t bsx_fri_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
+                           const bsx_fri_instance *instance, const uint64_t alpha[2], uint64_t *out_host);
+
 /* ---- test hooks -----------------------------------------------------------------------------
  * Poseidon::poseidon on n states (n x 12 words, in place). */
 int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n);
