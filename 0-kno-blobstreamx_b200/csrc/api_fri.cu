@@ -5,6 +5,8 @@
 // the host only sequences launches and makes one small read for the proof-of-work result.
 #include "api_internal.h"
 
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 static_assert(sizeof(bsx_challenger) == 28 * 8 + 8, "bsx_challenger layout must match DevChallenger");
@@ -218,6 +220,16 @@ extern "C" int32_t bsx_fri_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, i
 // ------------------------------------------------------------------------------------ fri_proof
 // values <- coset_fft(coeffs, shift) for a planar extension polynomial of length 2^lg whose
 // coefficients beyond 2^(lg - rb) are zero: run as 2^rb coset transforms of size 2^(lg - rb).
+static void dbg_chal(bsx_ctx *ctx, const u64 *chal, const char *tag) {
+    if (!getenv("BSX_DEBUG_FRI")) return;
+    bsx_challenger h;
+    cudaMemcpyAsync(&h, chal, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
+    fprintf(stderr, "[fri] %-14s st0=%016llx st1=%016llx n_in=%d n_out=%d in0=%016llx\n", tag,
+            (unsigned long long)h.sponge_state[0], (unsigned long long)h.sponge_state[1], h.n_input, h.n_output,
+            (unsigned long long)h.input_buffer[0]);
+}
+
 static int ext_coset_ntt(bsx_ctx *ctx, const u64 *coeffs, u64 *values, int lg, int rb, u64 shift) {
     NttPlan plan;
     plan.log_n = lg - rb;
@@ -285,7 +297,9 @@ static int fri_proof_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracl
     if (rc == BSX_OK) do {
         // coeffs.truncate(len >> rate_bits); challenger.observe_extension_elements(coeffs)
         const size_t final_len = len >> rb;
+        dbg_chal(ctx, chal, "before final");
         launch_chal_observe(chal, coeffs, 2 * final_len, 1, len, ctx->stream);
+        dbg_chal(ctx, chal, "after final");
         u64 *fin_out = proof + L.caps_words + L.per_q * (size_t)p->num_query_rounds;
         launch_ext_interleave(coeffs, len, final_len, fin_out, ctx->stream);
         // fri_proof_of_work
@@ -307,7 +321,9 @@ static int fri_proof_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracl
         }
         if (rc) break;
         cudaMemcpyAsync(fin_out + 2 * final_len, best, sizeof(u64), cudaMemcpyDeviceToDevice, ctx->stream);
+        dbg_chal(ctx, chal, "before finish");
         launch_chal_pow_finish(chal, best, best + 1, ctx->stream);
+        dbg_chal(ctx, chal, "after finish");
         // fri_prover_query_rounds
         const int nq = p->num_query_rounds;
         if (nq > 0) {

@@ -83,14 +83,10 @@ __global__ void __launch_bounds__(256) pow_kernel(const DevChallenger *c, u64 ba
 void launch_pow(const void *c, u64 base, u64 n, int pow_bits, u64 *best, cudaStream_t st) {
     BSX_COUNT_LAUNCH(); pow_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const DevChallenger *)c, base, n, pow_bits, best);
 }
-// observe the witness and draw the response (kept on device); single thread
-__global__ void chal_pow_finish_kernel(DevChallenger *c, const u64 *witness, u64 *response) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    chal_observe(c, *witness);
-    *response = chal_get(c);
-}
+// observe the witness and draw the response (kept on device)
 void launch_chal_pow_finish(void *c, const u64 *witness, u64 *response, cudaStream_t st) {
-    BSX_COUNT_LAUNCH(); chal_pow_finish_kernel<<<1, 32, 0, st>>>((DevChallenger *)c, witness, response);
+    launch_chal_observe(c, witness, 1, 0, 0, st);
+    launch_chal_get(c, response, 1, 0, st);
 }
 
 // ------------------------------------------------------------------ prove_openings combine
