@@ -441,7 +441,7 @@ extern "C" int32_t bsx_batch_export(bsx_batch *b, uint64_t *coeffs_host, uint64_
     if (coeffs_host) TRY(bsx_batch_coeffs(b, coeffs_host, BSX_HOST));
     if (leaves_host) {
         size_t nb = (size_t)1 << (b->log_n + b->rate_bits), w = (size_t)(b->n_cols + b->n_salt);
-        if (nb * w) {
+        if (nb != 0 && w != 0) {
             CU(ctx, cudaSetDevice(ctx->device));
             u64 *tmp;
             TRY(bsx_alloc(ctx, &tmp, nb * w));

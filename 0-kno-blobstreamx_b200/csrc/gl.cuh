@@ -60,6 +60,18 @@ __device__ __forceinline__ u64 gl_sqr(u64 a) { return gl_mul(a, a); }
 // carry chains for the reduction -- no IMAD.HI (quarter rate on B200, tools/microbench/pipes.cu)
 // and no compare+select sequences.  ~20 SASS instructions per multiply instead of ~36.
 
+// (e1:e0) = x * EPS = (x << 32) - x.  GL_EPS_ALU = 1: two carry-chain subtractions on the ALU pipe
+// instead of one quarter-rate IMAD.WIDE on the FMA-heavy pipe.  Measured on B200 (tools/microbench/
+// poseidon_bench.cu): slower, because the ALU pipe is co-critical (67-72 % busy) -- left off.
+#ifndef GL_EPS_ALU
+#define GL_EPS_ALU 0
+#endif
+#if GL_EPS_ALU
+#define GL_EPS_TIMES(x) "sub.cc.u32 e0, 0, " x ";\n\tsubc.u32 e1, " x ", 0;\n\t"
+#else
+#define GL_EPS_TIMES(x) "mul.wide.u32 e, " x ", 0xFFFFFFFF;\n\tmov.b64 {e0,e1}, e;\n\t"
+#endif
+
 // 128-bit product + 64-bit addend, reduced:  a * b + c  (mod p), all lazy.
 //   x = x0 + x1 2^32 + x2 2^64 + x3 2^96 == (x1:x0) - x3 + x2 * EPS   (2^64 == EPS, 2^96 == -1)
 __device__ __forceinline__ u64 gl_mul_add_lazy(u64 a, u64 b, u64 c) {
@@ -87,8 +99,7 @@ __device__ __forceinline__ u64 gl_mul_add_lazy(u64 a, u64 b, u64 c) {
         "subc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 x0, x0, m;\n\t"
         "subc.u32 x1, x1, 0;\n\t"
-        "mul.wide.u32 e, x2, 0xFFFFFFFF;\n\t"  // + x2 * EPS, wrapped 2^64 == EPS
-        "mov.b64 {e0,e1}, e;\n\t"
+        GL_EPS_TIMES("x2")  // + x2 * EPS, wrapped 2^64 == EPS
         "add.cc.u32 x0, x0, e0;\n\t"
         "addc.cc.u32 x1, x1, e1;\n\t"
         "addc.u32 t2, 0, 0;\n\t"
@@ -121,8 +132,7 @@ __device__ __forceinline__ u64 gl_mul_lazy(u64 a, u64 b) {
         "subc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 x0, x0, m;\n\t"
         "subc.u32 x1, x1, 0;\n\t"
-        "mul.wide.u32 e, x2, 0xFFFFFFFF;\n\t"
-        "mov.b64 {e0,e1}, e;\n\t"
+        GL_EPS_TIMES("x2")
         "add.cc.u32 x0, x0, e0;\n\t"
         "addc.cc.u32 x1, x1, e1;\n\t"
         "addc.u32 t2, 0, 0;\n\t"
@@ -186,8 +196,7 @@ __device__ __forceinline__ u64 gl_acc_reduce(const gl_acc160 &A) {
         "subc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 x0, x0, m;\n\t"
         "subc.u32 x1, x1, 0;\n\t"
-        "mul.wide.u32 e, %4, 0xFFFFFFFF;\n\t"
-        "mov.b64 {e0,e1}, e;\n\t"
+        GL_EPS_TIMES("%4")
         "add.cc.u32 x0, x0, e0;\n\t"
         "addc.cc.u32 x1, x1, e1;\n\t"
         "addc.u32 t2, 0, 0;\n\t"

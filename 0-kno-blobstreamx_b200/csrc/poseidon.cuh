@@ -16,11 +16,18 @@
 //    on instruction fetch for 12.6 warp-cycles per issue).
 #pragma once
 #include "gl.cuh"
+#include "poseidon_mds.cuh"
 #include "poseidon_rc.h"
+
+// 1: multiplication-free MDS on 22-bit limb planes (poseidon_mds.cuh); 0: IMAD.WIDE accumulation on halves
+#ifndef POSEIDON_MDS_FFT
+#define POSEIDON_MDS_FFT 1
+#endif
 
 __constant__ u64 POSEIDON_RC[POSEIDON_N_RC] = {POSEIDON_RC_LIST};
 __constant__ u64 POSEIDON_POST_LO[96] = {POSEIDON_POST_LO_LIST};
 __constant__ u64 POSEIDON_POST_HI[96] = {POSEIDON_POST_HI_LIST};
+__constant__ u32 POSEIDON_POST_L22[8 * 36] = {POSEIDON_POST_L22_LIST};
 __constant__ u64 POSEIDON_FAST_INIT[121] = {POSEIDON_FAST_INIT_LIST};
 __constant__ u64 POSEIDON_FAST_K[22] = {POSEIDON_FAST_K_LIST};
 __constant__ u64 POSEIDON_FAST_V[242] = {POSEIDON_FAST_V_LIST};
@@ -73,6 +80,47 @@ __device__ __forceinline__ void poseidon_mds_post(u64 s[12], const u64 *__restri
     }
 }
 
+// o0 + o1 2^22 + o2 2^44 (o_k < 2^32) -> lazy u64.  Three words w2:w1:w0 with w2 < 2^13, then
+// w2 2^64 == w2 EPS folded in by one IMAD.WIDE with carry-out; a wrap is worth EPS once more and the
+// wrapped value is < 2^45, so that add cannot wrap again.
+__device__ __forceinline__ u64 poseidon_merge22(u32 o0, u32 o1, u32 o2) {
+    u32 r0, r1;
+    asm("{\n\t.reg .u32 w0,w1,w2,a,b,c,m;\n\t"
+        "shl.b32 a, %3, 22;\n\t"
+        "add.cc.u32 w0, %2, a;\n\t"
+        "shr.b32 a, %3, 10;\n\t"
+        "shl.b32 b, %4, 12;\n\t"
+        "addc.cc.u32 w1, a, b;\n\t"
+        "shr.b32 a, %4, 20;\n\t"
+        "addc.u32 w2, a, 0;\n\t"
+        "mad.lo.cc.u32 w0, w2, 0xFFFFFFFF, w0;\n\t"
+        "madc.hi.cc.u32 w1, w2, 0xFFFFFFFF, w1;\n\t"
+        "addc.u32 c, 0, 0;\n\t"
+        "sub.u32 m, 0, c;\n\t"
+        "add.cc.u32 %0, w0, m;\n\t"
+        "addc.u32 %1, w1, 0;\n\t}"
+        : "=r"(r0), "=r"(r1)
+        : "r"(o0), "r"(o1), "r"(o2));
+    return ((u64)r1 << 32) | r0;
+}
+
+// s <- M s + post_j on three 22-bit limb planes; lazy in, lazy out
+__device__ __forceinline__ void poseidon_mds_post_fft(u64 s[12], const u32 *__restrict__ post) {
+    u32 x0[12], x1[12], x2[12], y0[12], y1[12], y2[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+        u32 lo = (u32)s[i], hi = (u32)(s[i] >> 32);
+        x0[i] = lo & POSEIDON_LIMB_MASK;
+        x1[i] = __funnelshift_r(lo, hi, POSEIDON_LIMB_BITS) & POSEIDON_LIMB_MASK;
+        x2[i] = hi >> 12;
+    }
+    poseidon_mds_plane(x0, post, y0);
+    poseidon_mds_plane(x1, post + 12, y1);
+    poseidon_mds_plane(x2, post + 24, y2);
+#pragma unroll
+    for (int i = 0; i < 12; i++) s[i] = poseidon_merge22(y0[i], y1[i], y2[i]);
+}
+
 // lazy in, lazy out
 __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
 #pragma unroll
@@ -84,7 +132,11 @@ __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
 #pragma unroll
             for (int i = 0; i < 12; i++) s[i] = poseidon_sbox(s[i]);
             const int j = half * 4 + r;
+#if POSEIDON_MDS_FFT
+            poseidon_mds_post_fft(s, POSEIDON_POST_L22 + 36 * j);
+#else
             poseidon_mds_post(s, POSEIDON_POST_LO + 12 * j, POSEIDON_POST_HI + 12 * j);
+#endif
         }
         if (half == 0) {
             // mds_partial_layer_init: x[1:] <- INIT x[1:] (dense 11x11, once per permutation).  Rows are

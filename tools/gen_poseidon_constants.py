@@ -202,6 +202,55 @@ def poseidon_fast(state, rc, fc):
     return s
 
 
+def mds_plane_fft(x, k):
+    """The multiplication-free MDS layer of csrc/poseidon_mds.cuh on one limb plane (wrapping u32):
+    4-point DFT over the index 3a + b, three tiny 3-convolutions, inverse DFT."""
+    A, Bm, R, I = [0] * 3, [0] * 3, [0] * 3, [0] * 3
+    for b in range(3):
+        x0, x1, x2, x3 = x[b], x[3 + b], x[6 + b], x[9 + b]
+        A[b], Bm[b], R[b], I[b] = x0 + x2 + x1 + x3, x0 + x2 - x1 - x3, x0 - x2, x1 - x3
+    T = sum(A)
+    P1 = [16 * (T + A[2]), 16 * (T + A[0]), 16 * (T + A[1])]
+    Pm = [8 * Bm[2] - Bm[0] - 2 * Bm[1], -8 * Bm[0] - Bm[1] - 2 * Bm[2], 2 * Bm[0] - 8 * Bm[1] - Bm[2]]
+    Pr = [2 * R[0] - I[0] + R[1] - 16 * I[1] + R[2] + 4 * I[2],
+          -4 * R[0] + I[0] + 2 * R[1] - I[1] + R[2] - 16 * I[2],
+          16 * R[0] + I[0] - 4 * R[1] + I[1] + 2 * R[2] - I[2]]
+    Pi = [R[0] + 2 * I[0] + 16 * R[1] + I[1] - 4 * R[2] + I[2],
+          -R[0] - 4 * I[0] + R[1] + 2 * I[1] + 16 * R[2] + I[2],
+          -R[0] + 16 * I[0] - R[1] - 4 * I[1] + R[2] + 2 * I[2]]
+    o = [0] * 12
+    for b in range(3):
+        p, q = P1[b] + Pm[b], P1[b] - Pm[b]
+        o[b], o[3 + b], o[6 + b], o[9 + b] = p + Pr[b] + k[b], q + Pi[b] + k[3 + b], p - Pr[b] + k[6 + b], q - Pi[b] + k[9 + b]
+    o[0] += 8 * x[0]
+    return [v & M32 for v in o]
+
+
+def mds_fft_check():
+    """Frequency-domain kernel of the circulant (must be the tiny integers the CUDA code hard-wires) and
+    the limb-plane transform against the dense form."""
+    K = [MDS_CIRC[(-m) % 12] for m in range(12)]
+    Kb = [[K[3 * a + b] for a in range(4)] for b in range(3)]
+    assert [sum(k) // 4 for k in Kb] == [16, 32, 16]
+    assert [(k[0] - k[1] + k[2] - k[3]) // 4 for k in Kb] == [-1, -8, 2]
+    assert [((k[0] - k[2]) // 2, (k[1] - k[3]) // 2) for k in Kb] == [(2, 1), (-4, -1), (16, -1)]
+    import random
+    rnd = random.Random(7)
+    for t in range(200):
+        x = [rnd.randrange(1 << 22) if t else (1 << 22) - 1 for _ in range(12)]
+        k = [rnd.randrange(1 << 22) if t else (1 << 22) - 1 for _ in range(12)]
+        want = [sum(MDS_CIRC[i] * x[(i + r) % 12] for i in range(12)) + MDS_DIAG[r] * x[r] + k[r] for r in range(12)]
+        assert max(want) <= M32 and want == mds_plane_fft(x, k)
+
+
+def c_list32(name, vals, per_line=8):
+    out = "#define %s \\\n" % name
+    for i in range(0, len(vals), per_line):
+        out += "  " + ", ".join("0x%06xu" % c for c in vals[i:i + per_line])
+        out += ", \\\n" if i + per_line < len(vals) else "\n"
+    return out
+
+
 def c_list(name, vals, per_line=4):
     out = "#define %s \\\n" % name
     for i in range(0, len(vals), per_line):
@@ -233,6 +282,9 @@ def emit(path, rc, guard, fc=None):
             flat = [x for row in post for x in row]
             f.write(c_list("POSEIDON_POST_LO_LIST", [x & M32 for x in flat]))  # [8][12]
             f.write(c_list("POSEIDON_POST_HI_LIST", [x >> 32 for x in flat]))  # [8][12]
+            # the same vectors cut into 22-bit limb planes for the multiplication-free MDS: [8][3][12]
+            l22 = [(x >> (22 * k)) & 0x3FFFFF for row in post for k in range(3) for x in row]
+            f.write(c_list32("POSEIDON_POST_L22_LIST", l22))
         f.write("#endif\n")
 
 
@@ -242,6 +294,7 @@ def main():
     assert max(rc) < 0xfffeeac900011537
     assert poseidon_naive([0] * 12, rc) == KAT_ZERO, "all-zeros KAT mismatch"
     fc = fast_partial_constants(rc)
+    mds_fft_check()
     import random
     rnd = random.Random(1)
     for t in range(6):
