@@ -109,6 +109,28 @@ int bsx_coset_tables(bsx_ctx *ctx, int log_n, int r_log, u64 shift, const u64 **
     return BSX_OK;
 }
 
+int bsx_post_table(bsx_ctx *ctx, NttPlan *plan, u64 shift, int n_cols) {
+    plan->post_full = nullptr;
+    int r_log = 0;
+    while ((1 << r_log) < plan->n_cosets) r_log++;
+    size_t words = (size_t)1 << (plan->log_n + r_log);
+    // worth building only when many columns share it; bounded so that it never rivals the data
+    if (plan->b == 0 || n_cols < 8 || words > ((size_t)1 << 28)) return BSX_OK;
+    CosetKey key = {plan->log_n, r_log, plan->pre_hi ? shift : 0};
+    if (plan->inverse) key.r_log |= 0x100;
+    auto it = ctx->post_tables.find(key);
+    if (it == ctx->post_tables.end()) {
+        u64 *t;
+        TRY(bsx_alloc(ctx, &t, words));
+        launch_ntt_post_table(t, plan->pre_hi ? plan->pre_lo : nullptr, plan->tw, plan->scale, plan->a, plan->b, r_log,
+                              ctx->stream);
+        CU(ctx, cudaGetLastError());
+        it = ctx->post_tables.emplace(key, (const u64 *)t).first;
+    }
+    plan->post_full = it->second;
+    return BSX_OK;
+}
+
 // ------------------------------------------------------------------------------------ context
 unsigned long long g_bsx_launches = 0;
 extern "C" uint64_t bsx_launch_count(void) { return g_bsx_launches; }
@@ -173,6 +195,7 @@ extern "C" void bsx_ctx_destroy(bsx_ctx *ctx) {
         bsx_free(ctx, (u64 *)kv.second.lo);
         bsx_free(ctx, (u64 *)kv.second.hi);
     }
+    for (auto &kv : ctx->post_tables) bsx_free(ctx, (u64 *)kv.second);
     for (auto &kv : ctx->coset_tables) {
         bsx_free(ctx, (u64 *)kv.second.first);
         bsx_free(ctx, (u64 *)kv.second.second);

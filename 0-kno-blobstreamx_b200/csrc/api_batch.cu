@@ -277,6 +277,7 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
             plan.pre_hi = plan.pre_lo = nullptr;
             if ((rc = bsx_pow_table(ctx, log_n, 1, &plan.tw))) break;
             plan.scale = gl_host_inv((u64)n % GL_P);
+            if ((rc = bsx_post_table(ctx, &plan, 0, n_cols))) break;
             launch_ntt(ctx->tables, plan, bt->coeffs, n, bt->coeffs, n, n_cols, ctx->stream);
             bt->coeffs_bitrev = true;
         } else {
@@ -291,6 +292,7 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
         if ((rc = bsx_coset_tables(ctx, log_n, rate_bits, 7, &plan.pre_hi, &plan.pre_lo))) break;
         if ((rc = bsx_pow_table(ctx, log_n, 0, &plan.tw))) break;
         plan.scale = 1;
+        if ((rc = bsx_post_table(ctx, &plan, 7, n_cols))) break;
         launch_ntt(ctx->tables, plan, bt->coeffs, n, bt->lde, nb, n_cols, ctx->stream);
         if (n_salt) {
             u64 *dst = bt->lde + nb * (size_t)n_cols;
@@ -498,6 +500,7 @@ extern "C" int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t lo
     if (kind == 2) TRY(bsx_coset_tables(ctx, log_n, 0, shift % GL_P, &plan.pre_hi, &plan.pre_lo));
     TRY(bsx_pow_table(ctx, log_n, plan.inverse, &plan.tw));
     plan.scale = plan.inverse ? gl_host_inv((u64)n % GL_P) : 1;
+    TRY(bsx_post_table(ctx, &plan, kind == 2 ? shift % GL_P : 0, n_cols));
     launch_ntt(ctx->tables, plan, buf, n, buf, n, n_cols, ctx->stream);
     launch_bitrev_copy(buf, n, tmp, n, log_n, n_cols, ctx->stream);
     CU(ctx, cudaGetLastError());

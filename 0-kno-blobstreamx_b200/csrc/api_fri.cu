@@ -240,6 +240,7 @@ static int ext_coset_ntt(bsx_ctx *ctx, const u64 *coeffs, u64 *values, int lg, i
     TRY(bsx_coset_tables(ctx, plan.log_n, rb, shift, &plan.pre_hi, &plan.pre_lo));
     TRY(bsx_pow_table(ctx, plan.log_n, 0, &plan.tw));
     plan.scale = 1;
+    plan.post_full = nullptr;  // two columns only: the two-level twiddle tables are cheaper than a full table
     const size_t len = (size_t)1 << lg;
     launch_ntt(ctx->tables, plan, coeffs, len, values, len, 2, ctx->stream);
     CU(ctx, cudaGetLastError());

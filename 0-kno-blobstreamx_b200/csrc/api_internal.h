@@ -25,6 +25,7 @@ struct bsx_ctx {
     NttTables tables;
     std::map<int, PowTable> pow_tables;
     std::map<CosetKey, std::pair<const u64 *, const u64 *>> coset_tables;
+    std::map<CosetKey, const u64 *> post_tables;  // key.shift = 0: inverse transform, no coset
 };
 
 // plonky2 hash/merkle_tree.rs MerkleTree { leaves, digests, cap }, device resident.
@@ -57,6 +58,9 @@ int bsx_copy_in(bsx_ctx *ctx, u64 *dst_dev, const u64 *src, size_t words, int me
 int bsx_copy_out(bsx_ctx *ctx, u64 *dst, const u64 *src_dev, size_t words, int mem);
 int bsx_pow_table(bsx_ctx *ctx, int log_n, int inverse, PowTable *out);
 int bsx_coset_tables(bsx_ctx *ctx, int log_n, int r_log, u64 shift, const u64 **pre_hi, const u64 **pre_lo);
+// full pass-HI output-factor table for a plan whose pre_* / tw / scale / a / b / n_cosets are set; sets
+// plan->post_full (left null when the table would not pay off: few columns, single pass, or too large)
+int bsx_post_table(bsx_ctx *ctx, NttPlan *plan, u64 shift, int n_cols);
 void bsx_split(int log_n, int *a, int *b);
 void ntt_init_device();
 

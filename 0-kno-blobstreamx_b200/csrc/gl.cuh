@@ -144,6 +144,40 @@ __device__ __forceinline__ u64 gl_mul_lazy(u64 a, u64 b) {
     return ((u64)r1 << 32) | r0;
 }
 
+// ---- canonical carry-chain forms for the NTT butterflies (inputs < p, outputs < p) ----
+// a - b: 5 SASS instructions (the compiler's compare+select form of gl_sub is 8)
+__device__ __forceinline__ u64 gl_sub_c(u64 a, u64 b) {
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32), r0, r1;
+    asm("{\n\t.reg .u32 m;\n\t"
+        "sub.cc.u32 %0, %2, %4;\n\t"
+        "subc.cc.u32 %1, %3, %5;\n\t"
+        "subc.u32 m, 0, 0;\n\t"       // 0xFFFFFFFF when a < b: add p == subtract EPS
+        "sub.cc.u32 %0, %0, m;\n\t"
+        "subc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+    return ((u64)r1 << 32) | r0;
+}
+// p - b in (0, p]: 2 instructions.  p itself (b == 0) is a valid SUBTRAHEND for gl_sub_c.
+__device__ __forceinline__ u64 gl_neg_p(u64 b) {
+    u32 b0 = (u32)b, b1 = (u32)(b >> 32), r0, r1;
+    asm("sub.cc.u32 %0, 1, %2;\n\tsubc.u32 %1, 0xFFFFFFFF, %3;" : "=r"(r0), "=r"(r1) : "r"(b0), "r"(b1));
+    return ((u64)r1 << 32) | r0;
+}
+// (a + b, a - b) in 12 instructions: a + b = a - (p - b)
+__device__ __forceinline__ void gl_butterfly_c(u64 &a, u64 &b) {
+    u64 nb = gl_neg_p(b);
+    u64 d = gl_sub_c(a, b);
+    a = gl_sub_c(a, nb);
+    b = d;
+}
+// lazy -> canonical: x >= p  <=>  hi == 0xFFFFFFFF and lo != 0, and then x - p = lo - 1
+__device__ __forceinline__ u64 gl_canon_fast(u64 x) {
+    u32 lo = (u32)x, hi = (u32)(x >> 32);
+    bool ge = (hi == 0xFFFFFFFFu) && (lo != 0);
+    return ge ? (u64)(lo - 1) : x;
+}
+
 // a + b (mod p): a lazy, b CANONICAL (< p) -> lazy.  One wrap fix suffices:
 // a + b - 2^64 + EPS <= (2^64-1) + (p-1) - 2^64 + EPS < 2^64.
 __device__ __forceinline__ u64 gl_add_lazy_canon(u64 a, u64 b) {

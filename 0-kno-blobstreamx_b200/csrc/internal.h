@@ -53,6 +53,9 @@ struct NttPlan {
     const u64 *pre_hi, *pre_lo;
     PowTable tw;   // powers of omega_N (or its inverse) for the inter-pass twiddle
     u64 scale;     // multiplied into every output (n^-1 for the inverse); 1 = none
+    // optional [n_cosets][2^a][2^b] table of scale * pre_lo * inter-pass twiddle (launch_ntt_post_table):
+    // one multiplication per output word in pass HI instead of three, and no scaling in pass LO
+    const u64 *post_full;
 };
 // Transforms n_cols columns.  src column c at src + c*src_stride (2^log_n words);
 // dst column c at dst + c*dst_stride; coset k is written to the block [bitrev_r(k) << log_n, +2^log_n)
@@ -64,6 +67,8 @@ void launch_fill_powers(u64 *out, u64 base, u64 first, size_t n, cudaStream_t st
 // dst[c][i] = src[c][bitrev_log_n(i)]
 void launch_bitrev_copy(const u64 *src, size_t src_stride, u64 *dst, size_t dst_stride, int log_n, int n_cols,
                         cudaStream_t st);
+void launch_ntt_post_table(u64 *out, const u64 *pre_lo, PowTable tw, u64 scale, int a, int b, int r_log,
+                           cudaStream_t st);
 int ntt_max_single_pass_log();
 void ntt_init_device();
 void launch_fill_random(u64 *out, size_t n, u64 seed, cudaStream_t st);

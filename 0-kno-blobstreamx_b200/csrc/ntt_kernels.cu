@@ -11,15 +11,27 @@
 // leaf order plonky2 reaches with transpose + reverse_index_bits_in_place, so no permutation pass
 // exists.  The LDE's zero padding is never materialised: the 2^r cosets of the big domain are 2^r
 // independent size-N transforms of c_i * (g * omega_NB^k)^i, each landing in the contiguous leaf
-// block bitrev_r(k).
+// block bitrev_r(k); one CTA produces all 2^r cosets of its tile, so the coefficients are read from
+// HBM once (the other 2^r - 1 reads hit L2).
+//
+// Inside a tile the stages run in groups of up to four: a thread pulls 2^rho points out of shared
+// memory, runs rho butterfly stages on them in registers (12-instruction canonical add/sub pair,
+// 20-instruction multiply) and puts them back, so a 2^10-point sub-transform makes three trips
+// through shared memory instead of ten.  Shared memory is padded by one word in 32 so that the
+// stride-2^rho accesses of the last group stay conflict-free.  The kernels are bound by integer
+// issue (ALU carry chains + IMAD.WIDE), not by HBM: see DESIGN.md section 3.4 and profiles/.
 #include "internal.h"
 #include "gl.cuh"
 
-#define NTT_THREADS 512
+#define NTT_THREADS 256
 #define NTT_MAX_A 12
-#define NTT_TILE_ELEMS 8192  // 64 KB of shared memory per tile
 
 __device__ __forceinline__ u32 bitrev32(u32 x, int bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
+
+struct NttGroups {
+    int n;
+    int rho[4];
+};
 
 struct NttKParams {
     const u64 *src;
@@ -28,123 +40,250 @@ struct NttKParams {
     const u64 *wtab;  // omega_4096^j (or inverse), j < 2048
     const u64 *pre_hi, *pre_lo;
     const u64 *tw_lo, *tw_hi;
+    const u64 *post_full;  // [n_cosets][2^a][2^b]: scale * pre_lo * inter-pass twiddle, or null
     u64 scale;
     int log_n, a, b, w_log;  // tile = 2^a points x 2^w_log adjacent i0
     int src_bitrev, r_log;   // r_log = log2(n_cosets)
-    int last;                // HI pass is the only pass: apply scale here
+    int pitch;               // words between tile columns in shared memory
+    NttGroups groups;
 };
 
-// DIF stages over `bits` index bits of a tile in shared memory.
-// J_FAST:  sm[p * W + j]  (pass HI: j = adjacent i0, contiguous in global memory)
-// !J_FAST: sm[j * R + p]  (pass LO: p contiguous in global memory)
-template <bool J_FAST>
-__device__ __forceinline__ void dif_stages(u64 *sm, const u64 *__restrict__ wtab, int bits, int w_log) {
-    const int R = 1 << bits, W = 1 << w_log;
-    const int n_bf = (R >> 1) << w_log;
-    for (int s = 0; s < bits; s++) {
-        const int h_log = bits - 1 - s;
-        for (int bf = threadIdx.x; bf < n_bf; bf += blockDim.x) {
-            int j, pp;
-            if (J_FAST) {
-                j = bf & (W - 1);
-                pp = bf >> w_log;
-            } else {
-                pp = bf & ((R >> 1) - 1);
-                j = bf >> (bits - 1);
+__device__ __forceinline__ u64 gl_mul_c(u64 a, u64 b) { return gl_canon_fast(gl_mul_lazy(a, b)); }
+
+// Tile layout in shared memory: W columns of 2^bits points, column j at j * pitch, point p at
+// p + (p >> 5) + (p >> 9).  The padding keeps the stride-2^rho accesses of the last stage group and the
+// bit-reversed scatter of the coefficient load conflict-free; pitch == 2 (mod 16) does the same for
+// the column-interleaved global loads / stores of pass HI.
+__device__ __forceinline__ int ntt_swz(int p) { return p + (p >> 5) + (p >> 9); }
+__device__ __forceinline__ int ntt_sm(int j, int p, int pitch) { return j * pitch + ntt_swz(p); }
+// Twiddle table position: stage s reads entries e = off << s, a stride-2^s walk across the lanes; XOR-ing
+// bits 5.. into the low bits spreads every such walk over all banks.
+__device__ __forceinline__ int ntt_tw_pos(int e) { return e ^ (e >> 5); }
+#define NTT_IO_UNROLL 8
+
+// One group of RHO DIF stages, starting at stage s0 of a 2^bits-point transform.  A work item owns
+// the 2^RHO points p = ((hi << RHO | m) << lobits) | lo of one column.  Butterfly (m0, m0 + half) of
+// local stage t has twiddle omega_{2^(bits - s0 - t)}^(mlow << lobits | lo)
+//   = omega_{2^bits}^((mlow << (bits - RHO + t)) + (lo << (s0 + t))), read from the table in shared memory.
+template <int RHO, bool LAST>
+__device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, int bits, int w_log, int s0,
+                                          int pitch) {
+    constexpr int R = 1 << RHO;
+    const int lobits = LAST ? 0 : bits - s0 - RHO;
+    const int n_items = 1 << (bits + w_log - RHO);
+    for (int it = threadIdx.x; it < n_items; it += blockDim.x) {
+        const int lo = it & ((1 << lobits) - 1);
+        const int r = it >> lobits;
+        const int hi = r & ((1 << s0) - 1);
+        const int j = r >> s0;
+        const int p0 = (hi << (RHO + lobits)) | lo;
+        u64 *col = sm + j * pitch;
+        u64 x[R];
+#pragma unroll
+        for (int m = 0; m < R; m++) {
+            int p = p0 + (m << lobits);
+            x[m] = col[ntt_swz(p)];
+        }
+#pragma unroll
+        for (int t = 0; t < RHO; t++) {
+            const int half = R >> (t + 1);
+            const int e_lo = LAST ? 0 : (lo << (s0 + t));
+#pragma unroll
+            for (int bf = 0; bf < R / 2; bf++) {
+                const int mlow = bf & (half - 1);
+                const int m0 = ((bf / half) * 2 * half) + mlow;
+                const int m1 = m0 + half;
+                gl_butterfly_c(x[m0], x[m1]);
+                if (!LAST || mlow != 0) x[m1] = gl_mul_c(x[m1], tws[ntt_tw_pos(e_lo | (mlow << (bits - RHO + t)))]);
             }
-            int off = pp & ((1 << h_log) - 1), blk = pp >> h_log;
-            int p0 = (blk << (h_log + 1)) + off;
-            u64 *pu, *pv;
-            if (J_FAST) {
-                pu = sm + ((size_t)p0 << w_log) + j;
-                pv = pu + ((size_t)1 << (h_log + w_log));
-            } else {
-                pu = sm + ((size_t)j << bits) + p0;
-                pv = pu + ((size_t)1 << h_log);
+        }
+#pragma unroll
+        for (int m = 0; m < R; m++) {
+            int p = p0 + (m << lobits);
+            col[ntt_swz(p)] = x[m];
+        }
+    }
+}
+
+__device__ __forceinline__ void dif_tile(u64 *sm, const u64 *__restrict__ tws, int bits, int w_log, int pitch,
+                                         const NttGroups &G) {
+    int s0 = 0;
+    for (int g = 0; g < G.n; g++) {
+        const int rho = G.rho[g];
+        if (g == G.n - 1) {
+            switch (rho) {
+                case 1: dif_group<1, true>(sm, tws, bits, w_log, s0, pitch); break;
+                case 2: dif_group<2, true>(sm, tws, bits, w_log, s0, pitch); break;
+                case 3: dif_group<3, true>(sm, tws, bits, w_log, s0, pitch); break;
+                default: dif_group<4, true>(sm, tws, bits, w_log, s0, pitch); break;
             }
-            u64 u = *pu, v = *pv;
-            *pu = gl_add(u, v);
-            u64 d = gl_sub(u, v);
-            // omega_R^(off * 2^s) = omega_4096^(off << (s + 12 - bits))
-            *pv = off ? gl_mul(d, wtab[off << (s + NTT_MAX_A - bits)]) : d;
+        } else {
+            switch (rho) {
+                case 1: dif_group<1, false>(sm, tws, bits, w_log, s0, pitch); break;
+                case 2: dif_group<2, false>(sm, tws, bits, w_log, s0, pitch); break;
+                case 3: dif_group<3, false>(sm, tws, bits, w_log, s0, pitch); break;
+                default: dif_group<4, false>(sm, tws, bits, w_log, s0, pitch); break;
+            }
+        }
+        __syncthreads();
+        s0 += rho;
+    }
+}
+
+// omega_{2^bits}^e, e < 2^(bits-1), from the omega_4096 table into shared memory
+__device__ __forceinline__ void load_twiddles(u64 *tws, const u64 *__restrict__ wtab, int bits) {
+    const int n = bits > 0 ? 1 << (bits - 1) : 0;
+    for (int e = threadIdx.x; e < n; e += blockDim.x)
+        tws[ntt_tw_pos(e)] = __ldg(wtab + ((size_t)e << (NTT_MAX_A - bits)));
+}
+
+// Pass HI: grid (n_cols, 2^b / W); the CTA loops over the 2^r_log cosets of its tile
+__global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
+    extern __shared__ u64 sm_all[];
+    const int a = P.a, b = P.b, w_log = P.w_log, pitch = P.pitch;
+    const int R = 1 << a, W = 1 << w_log;
+    u64 *tws = sm_all, *sm = sm_all + (R >> 1);
+    const int col = blockIdx.x;
+    const size_t i0_base = (size_t)blockIdx.y << w_log;
+    const u64 *src = P.src + (size_t)col * P.src_stride;
+    const int n_el = R << w_log;
+    const int n_cosets = 1 << P.r_log;
+    load_twiddles(tws, P.wtab, a);
+
+    for (int k = 0; k < n_cosets; k++) {
+        u64 *dst = P.dst + (size_t)col * P.dst_stride + ((size_t)bitrev32(k, P.r_log) << P.log_n);
+        for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
+            int i1, j;
+            size_t pos;
+            if (P.src_bitrev) {
+                // natural index i = i1 * S + i0 lives at bitrev_n(i) = bitrev_b(i0) * R + bitrev_a(i1):
+                // W runs of R contiguous words
+                j = e >> a;
+                int q = e & (R - 1);
+                i1 = bitrev32(q, a);
+                pos = ((size_t)bitrev32((u32)(i0_base + j), b) << a) + q;
+            } else {
+                i1 = e >> w_log;
+                j = e & (W - 1);
+                pos = ((size_t)i1 << b) + i0_base + j;
+            }
+            u64 v = src[pos];
+            if (P.pre_hi) {
+                u64 f = __ldg(P.pre_hi + ((size_t)k << a) + i1);
+                if (!P.post_full) f = gl_mul_lazy(f, __ldg(P.pre_lo + ((size_t)k << b) + i0_base + j));
+                v = gl_mul_c(v, f);
+            } else {
+                v = gl_canon_fast(v);
+            }
+            sm[ntt_sm(j, i1, pitch)] = v;
+        }
+        __syncthreads();
+        dif_tile(sm, tws, a, w_log, pitch, P.groups);
+        const u64 *post = P.post_full ? P.post_full + ((size_t)k << P.log_n) : nullptr;
+        for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
+            int p = e >> w_log, j = e & (W - 1);
+            u64 v = sm[ntt_sm(j, p, pitch)];
+            size_t o = ((size_t)p << b) + i0_base + j;
+            if (post) {
+                v = gl_mul_c(v, __ldg(post + o));
+            } else if (b > 0) {
+                // position p holds Y[k1], k1 = bitrev_a(p); twiddle omega_N^(i0 * k1)
+                u64 ex = (u64)(i0_base + j) * bitrev32(p, a);
+                u64 t = __ldg(P.tw_lo + (ex & 4095));
+                if (ex >> 12) t = gl_mul_lazy(t, __ldg(P.tw_hi + (ex >> 12)));
+                v = gl_mul_c(v, t);
+            } else if (P.scale != 1) {
+                v = gl_mul_c(v, P.scale);
+            }
+            dst[o] = v;
         }
         __syncthreads();
     }
 }
 
-// Pass HI: grid (2^b / W, n_cols, n_cosets)
-__global__ void __launch_bounds__(NTT_THREADS) ntt_pass_hi(NttKParams P) {
-    extern __shared__ u64 sm[];
-    const int a = P.a, b = P.b, w_log = P.w_log;
-    const int R = 1 << a, W = 1 << w_log;
-    const int col = blockIdx.y, k = blockIdx.z;
-    const size_t i0_base = (size_t)blockIdx.x << w_log;
-    const u64 *src = P.src + (size_t)col * P.src_stride;
-    u64 *dst = P.dst + (size_t)col * P.dst_stride + ((size_t)bitrev32(k, P.r_log) << P.log_n);
-    const int n_el = R << w_log;
-
-    for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
-        int i1, j;
-        size_t pos;
-        if (P.src_bitrev) {
-            // natural index i = i1 * S + i0 lives at bitrev_n(i) = bitrev_b(i0) * R + bitrev_a(i1):
-            // W runs of R contiguous words
-            j = e >> a;
-            int q = e & (R - 1);
-            i1 = bitrev32(q, a);
-            pos = ((size_t)bitrev32((u32)(i0_base + j), b) << a) + q;
-        } else {
-            i1 = e >> w_log;
-            j = e & (W - 1);
-            pos = ((size_t)i1 << b) + i0_base + j;
+// Pass LO: in place on rows of 2^b contiguous words; tile = 2^w_log rows.  grid (rows / W, n_cols)
+__global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
+    extern __shared__ u64 sm_all[];
+    const int b = P.b, w_log = P.w_log, pitch = P.pitch;
+    const int S = 1 << b;
+    u64 *tws = sm_all, *sm = sm_all + (S >> 1);
+    const int n_el = 1 << (b + w_log);
+    u64 *base = P.dst + (size_t)blockIdx.y * P.dst_stride + ((size_t)blockIdx.x << (b + w_log));
+    load_twiddles(tws, P.wtab, b);
+    for (int e0 = threadIdx.x; e0 < n_el; e0 += blockDim.x * NTT_IO_UNROLL) {
+        u64 v[NTT_IO_UNROLL];
+#pragma unroll
+        for (int u = 0; u < NTT_IO_UNROLL; u++) {
+            const int e = e0 + u * blockDim.x;
+            if (e < n_el) v[u] = base[e];
         }
-        u64 v = src[pos];
-        if (P.pre_hi) {
-            u64 f = gl_mul(P.pre_hi[((size_t)k << a) + i1], P.pre_lo[((size_t)k << b) + i0_base + j]);
-            v = gl_mul(v, f);
+#pragma unroll
+        for (int u = 0; u < NTT_IO_UNROLL; u++) {
+            const int e = e0 + u * blockDim.x;
+            if (e < n_el) sm[ntt_sm(e >> b, e & (S - 1), pitch)] = v[u];
         }
-        sm[((size_t)i1 << w_log) + j] = v;
     }
     __syncthreads();
-    dif_stages<true>(sm, P.wtab, a, w_log);
+    dif_tile(sm, tws, b, w_log, pitch, P.groups);
+    const bool scale = P.scale != 1 && !P.post_full;
     for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
-        int p = e >> w_log, j = e & (W - 1);
-        u64 v = sm[e];
-        if (b > 0) {
-            // position p holds Y[k1], k1 = bitrev_a(p); twiddle omega_N^(i0 * k1)
-            u64 ex = (u64)(i0_base + j) * bitrev32(p, a);
-            u64 t = P.tw_lo[ex & 4095];
-            if (ex >> 12) t = gl_mul(t, P.tw_hi[ex >> 12]);
-            v = gl_mul(v, t);
-        }
-        if (P.last && P.scale != 1) v = gl_mul(v, P.scale);
-        dst[((size_t)p << b) + i0_base + j] = v;
+        u64 v = sm[ntt_sm(e >> b, e & (S - 1), pitch)];
+        if (scale) v = gl_mul_c(v, P.scale);
+        base[e] = v;
     }
 }
 
-// Pass LO: in place on rows of 2^b contiguous words; tile = 2^w_log rows.  grid (rows / W, n_cols)
-__global__ void __launch_bounds__(NTT_THREADS) ntt_pass_lo(NttKParams P) {
-    extern __shared__ u64 sm[];
-    const int b = P.b, w_log = P.w_log;
-    const int S = 1 << b;
-    const int n_el = S << w_log;
-    u64 *base = P.dst + (size_t)blockIdx.y * P.dst_stride + ((size_t)blockIdx.x << (b + w_log));
-    for (int e = threadIdx.x; e < n_el; e += blockDim.x) sm[e] = base[e];
-    __syncthreads();
-    dif_stages<false>(sm, P.wtab, b, w_log);
-    for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
-        u64 v = sm[e];
-        if (P.scale != 1) v = gl_mul(v, P.scale);
-        base[e] = v;
-    }
+// post_full[k][p][i0] = scale * pre_lo[k][i0] * omega_N^(i0 * bitrev_a(p)): everything pass HI multiplies
+// into an output word besides the data, built once per (size, coset set) and cached in the context
+__global__ void ntt_post_table_kernel(u64 *out, const u64 *pre_lo, const u64 *tw_lo, const u64 *tw_hi, u64 scale,
+                                      int a, int b, int r_log) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >> (a + b + r_log)) return;
+    u32 i0 = (u32)(i & (((size_t)1 << b) - 1));
+    u32 p = (u32)((i >> b) & (((size_t)1 << a) - 1));
+    u32 k = (u32)(i >> (a + b));
+    u64 ex = (u64)i0 * bitrev32(p, a);
+    u64 t = tw_lo[ex & 4095];
+    if (ex >> 12) t = gl_mul(t, tw_hi[ex >> 12]);
+    if (pre_lo) t = gl_mul(t, pre_lo[((size_t)k << b) + i0]);
+    if (scale != 1) t = gl_mul(t, scale);
+    out[i] = t;
+}
+void launch_ntt_post_table(u64 *out, const u64 *pre_lo, PowTable tw, u64 scale, int a, int b, int r_log,
+                           cudaStream_t st) {
+    size_t n = (size_t)1 << (a + b + r_log);
+    BSX_COUNT_LAUNCH();
+    ntt_post_table_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, pre_lo, tw.lo, tw.hi, scale, a, b, r_log);
 }
 
 int ntt_max_single_pass_log() { return NTT_MAX_A; }
 
 // per-device opt-in to > 48 KB dynamic shared memory; called from bsx_ctx_create
 void ntt_init_device() {
-    cudaFuncSetAttribute(ntt_pass_hi, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
-    cudaFuncSetAttribute(ntt_pass_lo, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+    cudaFuncSetAttribute(ntt_pass_hi, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024);
+}
+
+// stage groups for a 2^bits-point tile transform: the last group (compile-time twiddles) takes up to
+// four stages, the rest is split evenly into groups of at most four
+static NttGroups plan_groups(int bits) {
+    NttGroups G;
+    G.n = 0;
+    for (int i = 0; i < 4; i++) G.rho[i] = 0;
+    if (bits <= 0) return G;
+    int last = bits < 4 ? bits : 4;
+    int rest = bits - last;
+    int g = (rest + 3) / 4;
+    for (int i = 0; i < g; i++) G.rho[G.n++] = rest / g + (i < rest % g ? 1 : 0);
+    G.rho[G.n++] = last;
+    return G;
+}
+
+// column pitch: 2^bits points + one pad word per 32, rounded up to 2 (mod 16)
+static int ntt_pitch(int bits) {
+    int p = (1 << bits) + ((1 << bits) >> 5) + ((1 << bits) >> 9);
+    while ((p & 15) != 2) p++;
+    return p;
 }
 
 void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t src_stride, u64 *dst,
@@ -168,17 +307,20 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
     int r_log = 0;
     while ((1 << r_log) < plan.n_cosets) r_log++;
     P.r_log = r_log;
-    P.last = plan.b == 0;
+    P.post_full = plan.b > 0 ? plan.post_full : nullptr;
     // pass HI: tile of 2^a points x W adjacent i0
     {
         int w_log = 13 - plan.a;  // 8192 elements per tile
         if (w_log < 2) w_log = 2;
         if (w_log > plan.b) w_log = plan.b;
         P.w_log = w_log;
-        dim3 grid((unsigned)(((size_t)1 << plan.b) >> w_log), (unsigned)n_cols, (unsigned)plan.n_cosets);
-        size_t smem = sizeof(u64) << (plan.a + w_log);
+        P.groups = plan_groups(plan.a);
+        dim3 grid((unsigned)n_cols, (unsigned)(((size_t)1 << plan.b) >> w_log));
+        size_t n_el = (size_t)1 << (plan.a + w_log);
+        P.pitch = ntt_pitch(plan.a);
+        size_t smem = sizeof(u64) * (((size_t)P.pitch << w_log) + ((size_t)1 << plan.a) / 2);
         int threads = NTT_THREADS;
-        while (threads > 32 && threads > (1 << (plan.a + w_log))) threads >>= 1;
+        while (threads > 32 && threads > (int)(n_el >> 1)) threads >>= 1;
         BSX_COUNT_LAUNCH(); ntt_pass_hi<<<grid, threads, smem, st>>>(P);
     }
     if (plan.b > 0) {
@@ -187,14 +329,16 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         if (w_log < 0) w_log = 0;
         while (((size_t)1 << w_log) > rows) w_log--;
         P.w_log = w_log;
+        P.groups = plan_groups(plan.b);
         dim3 grid((unsigned)(rows >> w_log), (unsigned)n_cols);
-        size_t smem = sizeof(u64) << (plan.b + w_log);
+        size_t n_el = (size_t)1 << (plan.b + w_log);
+        P.pitch = ntt_pitch(plan.b);
+        size_t smem = sizeof(u64) * (((size_t)P.pitch << w_log) + ((size_t)1 << plan.b) / 2);
         int threads = NTT_THREADS;
-        while (threads > 32 && threads > (1 << (plan.b + w_log))) threads >>= 1;
+        while (threads > 32 && threads > (int)(n_el >> 1)) threads >>= 1;
         BSX_COUNT_LAUNCH(); ntt_pass_lo<<<grid, threads, smem, st>>>(P);
     }
 }
-
 __global__ void fill_powers_kernel(u64 *out, u64 base, u64 first, size_t n) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = gl_mul(first, gl_pow(base, i));
