@@ -75,6 +75,7 @@ void launch_merkle_level(const u64 *children, u64 *parents, size_t n_parents, cu
 // memory while the block climbs `levels` levels; every layer is also written to its level-order
 // slot in global memory because `MerkleTree::prove` reads them later.
 #define SUB_LOG 9
+#define MERKLE_FLAT_MIN_LOG 15  // levels with more than 2^15 inputs run flat, the rest in per-block subtrees
 __global__ void __launch_bounds__(256) merkle_subtree_kernel(const u64 *__restrict__ in_level, u64 *__restrict__ out0,
                                                              size_t n_in, int levels, size_t level_stride_words,
                                                              u64 *__restrict__ cap, int cap_level) {
@@ -133,7 +134,17 @@ void launch_merkle_tree(u64 *digests, u64 *cap, int log_leaves, int cap_height, 
     while (done < levels) {
         int rem = levels - done;
         int log_in = log_leaves - done;
-        if (log_in >= SUB_LOG && rem >= 1) {
+        if (n_in > ((size_t)1 << MERKLE_FLAT_MIN_LOG) && rem >= 1) {
+            // wide levels: one thread per parent keeps every lane busy (the subtree kernel idles 7 of 8
+            // warps above its third level, which cost 8 ms at 2^23 leaves)
+            size_t n_par = n_in >> 1;
+            u64 *dst = (rem == 1) ? cap : out;
+            launch_merkle_level(in, dst, n_par, st);
+            in = dst;
+            out = dst + 4 * n_par;
+            n_in = n_par;
+            done += 1;
+        } else if (log_in >= SUB_LOG && rem >= 1) {
             int climb = rem < SUB_LOG ? rem : SUB_LOG;
             unsigned blocks = (unsigned)(n_in >> SUB_LOG);
             BSX_COUNT_LAUNCH(); merkle_subtree_kernel<<<blocks, 256, 0, st>>>(in, out, n_in, climb, 0, cap, rem <= SUB_LOG ? rem : -1);
