@@ -36,5 +36,12 @@ from .fri import (  # noqa: F401
     fri_reduction_arity_bits,
     prove_openings,
 )
+from .parallel import (  # noqa: F401
+    ShardPlan,
+    ShardedPolynomialBatch,
+    assemble_cap,
+    device_tensor,
+    exchange_staged,
+)
 
 P = 0xFFFFFFFF00000001

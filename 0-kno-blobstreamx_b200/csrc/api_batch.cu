@@ -226,6 +226,48 @@ struct PhaseTimer {
     }
 };
 
+// iNTT (unless the input already holds coefficients) and the coset LDE of n_cols columns: the common front
+// half of PolynomialBatch::from_values / from_coeffs, also used per rank by the row-sharded commit
+// (api_shard.cu), where `dests` redirects the final LDE words to the owning ranks' row slabs.
+// coeffs: n_cols x 2^log_n in place (left bit-reversed after the inverse transform);
+// lde: n_cols columns of stride lde_stride (the result, or only the inter-pass scratch when dests is set).
+int bsx_commit_transforms(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols, int rate_bits, bool input_is_coeffs,
+                          u64 *lde, size_t lde_stride, const BsxDests *dests, cudaEvent_t ev_after_ifft) {
+    const size_t n = (size_t)1 << log_n;
+    NttPlan plan;
+    plan.n_dest = 0;
+    plan.log_n = log_n;
+    bsx_split(log_n, &plan.a, &plan.b);
+    if (!input_is_coeffs) {
+        // PolynomialValues::ifft per column, in place; result is stored bit-reversed
+        plan.inverse = 1;
+        plan.src_bitrev = 0;
+        plan.n_cosets = 1;
+        plan.pre_hi = plan.pre_lo = nullptr;
+        TRY(bsx_pow_table(ctx, log_n, 1, &plan.tw));
+        plan.scale = gl_host_inv((u64)n % GL_P);
+        TRY(bsx_post_table(ctx, &plan, 0, n_cols));
+        launch_ntt(ctx->tables, plan, coeffs, n, coeffs, n, n_cols, ctx->stream);
+    }
+    if (ev_after_ifft) cudaEventRecord(ev_after_ifft, ctx->stream);
+    // lde_values: zero-pad + coset FFT(shift = 7) == 2^rate_bits coset transforms of size n
+    plan.inverse = 0;
+    plan.src_bitrev = input_is_coeffs ? 0 : 1;
+    plan.n_cosets = 1 << rate_bits;
+    TRY(bsx_coset_tables(ctx, log_n, rate_bits, 7, &plan.pre_hi, &plan.pre_lo));
+    TRY(bsx_pow_table(ctx, log_n, 0, &plan.tw));
+    plan.scale = 1;
+    TRY(bsx_post_table(ctx, &plan, 7, n_cols));
+    if (dests) {
+        plan.n_dest = dests->n;
+        plan.dest_lc = dests->lc;
+        for (int i = 0; i < dests->n; i++) plan.dest[i] = dests->ptr[i];
+    }
+    launch_ntt(ctx->tables, plan, coeffs, n, lde, lde_stride, n_cols, ctx->stream);
+    CU(ctx, cudaGetLastError());
+    return BSX_OK;
+}
+
 static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n_cols, int rate_bits, int cap_height,
                        int blinding, const u64 *salt, bool input_is_coeffs, bsx_batch **out, bsx_timing *timing) {
     if (!ctx || !out) return BSX_ERR_INVALID_ARG;
@@ -263,37 +305,11 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
         if ((rc = bsx_alloc(ctx, &bt->coeffs, n * n_cols))) break;
         if ((rc = bsx_copy_in(ctx, bt->coeffs, input, n * n_cols, mem))) break;
         pt.mark(1, ctx->stream);
-        int a, b;
-        bsx_split(log_n, &a, &b);
-        NttPlan plan;
-        plan.log_n = log_n;
-        plan.a = a;
-        plan.b = b;
-        if (!input_is_coeffs) {
-            // PolynomialValues::ifft per column, in place; result is stored bit-reversed
-            plan.inverse = 1;
-            plan.src_bitrev = 0;
-            plan.n_cosets = 1;
-            plan.pre_hi = plan.pre_lo = nullptr;
-            if ((rc = bsx_pow_table(ctx, log_n, 1, &plan.tw))) break;
-            plan.scale = gl_host_inv((u64)n % GL_P);
-            if ((rc = bsx_post_table(ctx, &plan, 0, n_cols))) break;
-            launch_ntt(ctx->tables, plan, bt->coeffs, n, bt->coeffs, n, n_cols, ctx->stream);
-            bt->coeffs_bitrev = true;
-        } else {
-            bt->coeffs_bitrev = false;
-        }
-        pt.mark(2, ctx->stream);
-        // lde_values: zero-pad + coset FFT(shift = 7) == 2^rate_bits coset transforms of size n
         if ((rc = bsx_alloc(ctx, &bt->lde, nb * (size_t)(n_cols + n_salt)))) break;
-        plan.inverse = 0;
-        plan.src_bitrev = bt->coeffs_bitrev ? 1 : 0;
-        plan.n_cosets = 1 << rate_bits;
-        if ((rc = bsx_coset_tables(ctx, log_n, rate_bits, 7, &plan.pre_hi, &plan.pre_lo))) break;
-        if ((rc = bsx_pow_table(ctx, log_n, 0, &plan.tw))) break;
-        plan.scale = 1;
-        if ((rc = bsx_post_table(ctx, &plan, 7, n_cols))) break;
-        launch_ntt(ctx->tables, plan, bt->coeffs, n, bt->lde, nb, n_cols, ctx->stream);
+        if ((rc = bsx_commit_transforms(ctx, bt->coeffs, log_n, n_cols, rate_bits, input_is_coeffs, bt->lde, nb, nullptr,
+                                        pt.on ? pt.ev[2] : nullptr)))
+            break;
+        bt->coeffs_bitrev = !input_is_coeffs;
         if (n_salt) {
             u64 *dst = bt->lde + nb * (size_t)n_cols;
             if (salt) {
@@ -491,6 +507,7 @@ extern "C" int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t lo
     TRY(bsx_alloc(ctx, &tmp, words));
     TRY(bsx_copy_in(ctx, buf, (const u64 *)data, words, mem));
     NttPlan plan;
+    plan.n_dest = 0;
     plan.log_n = log_n;
     bsx_split(log_n, &plan.a, &plan.b);
     plan.inverse = kind == 1;

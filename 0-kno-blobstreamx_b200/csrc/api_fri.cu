@@ -232,6 +232,7 @@ static void dbg_chal(bsx_ctx *ctx, const u64 *chal, const char *tag) {
 
 static int ext_coset_ntt(bsx_ctx *ctx, const u64 *coeffs, u64 *values, int lg, int rb, u64 shift) {
     NttPlan plan;
+    plan.n_dest = 0;
     plan.log_n = lg - rb;
     bsx_split(plan.log_n, &plan.a, &plan.b);
     plan.inverse = 0;

@@ -64,6 +64,13 @@ int bsx_post_table(bsx_ctx *ctx, NttPlan *plan, u64 shift, int n_cols);
 void bsx_split(int log_n, int *a, int *b);
 void ntt_init_device();
 
+struct BsxDests {
+    int n, lc;  // n row slabs of 2^lc leaves each
+    u64 *ptr[BSX_MAX_RANKS];
+};
+int bsx_commit_transforms(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols, int rate_bits, bool input_is_coeffs,
+                          u64 *lde, size_t lde_stride, const BsxDests *dests, cudaEvent_t ev_after_ifft);
+
 // builds digests + cap for a tree whose leaves/shape fields are set; allocates digests/cap_dev
 int bsx_tree_build(bsx_tree *t, cudaEvent_t ev_after_leaf_hash);
 void bsx_tree_release(bsx_tree *t);

@@ -1,0 +1,281 @@
+// api_shard.cu -- one PolynomialBatch commit sharded over the GPUs of a box.
+//
+// plonky2 has no multi-device path; this is the partitioning BASELINE.json's north star lays out for
+// `PolynomialBatch::from_values` (fri/oracle.rs):
+//   1. rank g owns the columns [c0_g, c1_g): iNTT + coset LDE per column need no communication;
+//   2. rank g owns the leaf rows [g * NB/G, (g+1) * NB/G) of EVERY column.  The DIF transforms leave each
+//      column in leaf order, so that slab is a contiguous range of every column -- no strided gather;
+//   3. the last NTT pass stores each output word straight into the owning rank's slab (`dests` of
+//      bsx_commit_transforms).  With peer pointers (CUDA IPC across processes, or peer access inside one
+//      process) the exchange is NVLink P2P stores issued by the transform kernel itself, overlapped with
+//      its arithmetic; with a staging buffer the slabs are laid out destination-major for one
+//      NCCL all-to-all issued by the host (torch.distributed / ncclSend+ncclRecv);
+//   4. each rank hashes its rows and builds its 2^cap_height / G cap subtrees; the host gathers the caps.
+// Every byte of the result is identical to the single-GPU batch: same LDE words, same digests, same cap.
+#include "api_internal.h"
+
+#include <cstring>
+
+struct bsx_shard {
+    bsx_ctx *ctx;
+    int log_n, n_cols_total, rate_bits, cap_height, rank, n_ranks, log_ranks;
+    int c0, c1;            // this rank's columns
+    size_t chunk;          // leaves per rank = 2^(log_n + rate_bits) / n_ranks
+    u64 *slab;             // n_cols_total x chunk, column-major: this rank's leaf rows (cudaMalloc: IPC-able)
+    u64 *peer[BSX_MAX_RANKS];   // every rank's slab as seen from this device (peer[rank] == slab)
+    bool peer_ipc[BSX_MAX_RANKS];
+    u64 *staging;          // optional destination-major send buffer: n_ranks x (c1 - c0) x chunk
+    u64 *coeffs;           // (c1 - c0) x 2^log_n
+    bool coeffs_bitrev;
+};
+
+extern "C" int32_t bsx_shard_column_range(int32_t n_cols_total, int32_t rank, int32_t n_ranks, int32_t *c0,
+                                          int32_t *c1) {
+    if (n_cols_total < 0 || n_ranks <= 0 || rank < 0 || rank >= n_ranks || !c0 || !c1) return BSX_ERR_INVALID_ARG;
+    // balanced contiguous ranges: the first (C mod G) ranks take one extra column (135 = 7 * 17 + 16)
+    int q = n_cols_total / n_ranks, r = n_cols_total % n_ranks;
+    *c0 = rank * q + (rank < r ? rank : r);
+    *c1 = *c0 + q + (rank < r ? 1 : 0);
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_shard_create(bsx_ctx *ctx, int32_t log_n, int32_t n_cols_total, int32_t rate_bits,
+                                    int32_t cap_height, int32_t rank, int32_t n_ranks, bsx_shard **out) {
+    if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    *out = nullptr;
+    if (log_n < 0 || log_n > 24) return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "degree_log=%d outside [0, 24]", log_n);
+    if (rate_bits < 0 || rate_bits > 8) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad rate_bits=%d", rate_bits);
+    if (n_cols_total < 0 || n_cols_total > 65535) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad n_cols=%d", n_cols_total);
+    int log_ranks = 0;
+    while ((1 << log_ranks) < n_ranks) log_ranks++;
+    if (n_ranks < 1 || n_ranks > BSX_MAX_RANKS || (1 << log_ranks) != n_ranks)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "n_ranks=%d must be a power of two <= %d", n_ranks, BSX_MAX_RANKS);
+    if (rank < 0 || rank >= n_ranks) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "rank %d of %d", rank, n_ranks);
+    const int log_nb = log_n + rate_bits;
+    if (cap_height < 0 || cap_height > log_nb)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "cap_height=%d should be at most log2(leaves.len())=%d", cap_height,
+                        log_nb);
+    if (log_ranks > log_nb) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "more ranks than leaves");
+    CU(ctx, cudaSetDevice(ctx->device));
+    bsx_shard *s = new bsx_shard();
+    s->ctx = ctx;
+    s->log_n = log_n;
+    s->n_cols_total = n_cols_total;
+    s->rate_bits = rate_bits;
+    s->cap_height = cap_height;
+    s->rank = rank;
+    s->n_ranks = n_ranks;
+    s->log_ranks = log_ranks;
+    bsx_shard_column_range(n_cols_total, rank, n_ranks, &s->c0, &s->c1);
+    s->chunk = (size_t)1 << (log_nb - log_ranks);
+    s->slab = s->staging = s->coeffs = nullptr;
+    s->coeffs_bitrev = false;
+    for (int i = 0; i < BSX_MAX_RANKS; i++) {
+        s->peer[i] = nullptr;
+        s->peer_ipc[i] = false;
+    }
+    size_t bytes = s->chunk * (size_t)n_cols_total * sizeof(u64);
+    if (bytes) {
+        cudaError_t e = cudaMalloc((void **)&s->slab, bytes);  // not the async pool: cudaIpcGetMemHandle needs cudaMalloc
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            delete s;
+            return bsx_fail(ctx, BSX_ERR_OOM, "row slab of %zu bytes: %s", bytes, cudaGetErrorString(e));
+        }
+    }
+    s->peer[rank] = s->slab;
+    *out = s;
+    return BSX_OK;
+}
+
+extern "C" void bsx_shard_free(bsx_shard *s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    cudaStreamSynchronize(s->ctx->stream);
+    for (int i = 0; i < s->n_ranks; i++)
+        if (s->peer_ipc[i] && s->peer[i]) cudaIpcCloseMemHandle(s->peer[i]);
+    if (s->slab) cudaFree(s->slab);
+    bsx_free(s->ctx, s->staging);
+    bsx_free(s->ctx, s->coeffs);
+    delete s;
+}
+
+extern "C" uint64_t *bsx_shard_slab_device(bsx_shard *s) { return s ? (uint64_t *)s->slab : nullptr; }
+extern "C" uint64_t *bsx_shard_staging_device(bsx_shard *s) { return s ? (uint64_t *)s->staging : nullptr; }
+extern "C" const uint64_t *bsx_shard_coeffs_device(const bsx_shard *s) { return s ? (const uint64_t *)s->coeffs : nullptr; }
+
+extern "C" int32_t bsx_shard_slab_ipc(bsx_shard *s, uint8_t *handle_out) {
+    if (!s || !handle_out) return BSX_ERR_INVALID_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == BSX_IPC_HANDLE_BYTES, "IPC handle size");
+    memset(handle_out, 0, BSX_IPC_HANDLE_BYTES);
+    if (!s->slab) return BSX_OK;
+    CU(s->ctx, cudaSetDevice(s->ctx->device));
+    cudaIpcMemHandle_t h;
+    CU(s->ctx, cudaIpcGetMemHandle(&h, s->slab));
+    memcpy(handle_out, &h, sizeof(h));
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_shard_set_peer_ipc(bsx_shard *s, int32_t peer_rank, const uint8_t *handle) {
+    if (!s || !handle || peer_rank < 0 || peer_rank >= s->n_ranks) return BSX_ERR_INVALID_ARG;
+    if (peer_rank == s->rank || !s->slab) return BSX_OK;
+    CU(s->ctx, cudaSetDevice(s->ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void *p = nullptr;
+    CU(s->ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    s->peer[peer_rank] = (u64 *)p;
+    s->peer_ipc[peer_rank] = true;
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_shard_set_peer_ptr(bsx_shard *s, int32_t peer_rank, uint64_t *slab_dev) {
+    if (!s || peer_rank < 0 || peer_rank >= s->n_ranks) return BSX_ERR_INVALID_ARG;
+    if (peer_rank == s->rank) return BSX_OK;
+    CU(s->ctx, cudaSetDevice(s->ctx->device));
+    if (slab_dev) {
+        cudaPointerAttributes at;
+        CU(s->ctx, cudaPointerGetAttributes(&at, slab_dev));
+        if (at.type == cudaMemoryTypeDevice && at.device != s->ctx->device) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                cudaGetLastError();
+                return bsx_fail(s->ctx, BSX_ERR_CUDA, "no peer access from device %d to %d: %s", s->ctx->device,
+                                at.device, cudaGetErrorString(e));
+            }
+            cudaGetLastError();
+        }
+    }
+    s->peer[peer_rank] = (u64 *)slab_dev;
+    s->peer_ipc[peer_rank] = false;
+    return BSX_OK;
+}
+
+// Transforms of the local columns.  use_staging == 0: every row slab must be known (bsx_shard_set_peer_*);
+// the LDE words go straight to their owners.  use_staging != 0: they go to a local destination-major
+// buffer, block d = this rank's columns x rank d's rows, for the host's all-to-all; block d must land at
+// slab_d + c0 * chunk on rank d.
+extern "C" int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
+                                       int32_t use_staging, bsx_timing *timing) {
+    if (!s) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = s->ctx;
+    const int n_local = s->c1 - s->c0;
+    if (!input && n_local > 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "input is NULL");
+    CU(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)1 << s->log_n, nb = n << s->rate_bits;
+    BsxDests D;
+    D.n = s->n_ranks;
+    D.lc = s->log_n + s->rate_bits - s->log_ranks;
+    if (use_staging) {
+        if (!s->staging) TRY(bsx_alloc(ctx, &s->staging, nb * (size_t)n_local));
+        for (int d = 0; d < s->n_ranks; d++) D.ptr[d] = s->staging + (size_t)d * s->chunk * n_local;
+    } else {
+        for (int d = 0; d < s->n_ranks; d++) {
+            if (!s->peer[d] && s->chunk != 0 && s->n_cols_total != 0)
+                return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "row slab of rank %d is not set", d);
+            D.ptr[d] = s->peer[d] + (size_t)s->c0 * s->chunk;
+        }
+    }
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+    if (timing)
+        for (auto &e : ev) cudaEventCreate(&e);
+    bsx_free(ctx, s->coeffs);
+    s->coeffs = nullptr;
+    u64 *scratch = nullptr;
+    int rc = BSX_OK;
+    do {
+        if (n_local == 0) break;
+        if ((rc = bsx_alloc(ctx, &s->coeffs, n * n_local))) break;
+        if ((rc = bsx_copy_in(ctx, s->coeffs, (const u64 *)input, n * n_local, mem))) break;
+        if (timing) cudaEventRecord(ev[0], ctx->stream);
+        // the two-pass transforms keep their intermediate in a local column-major scratch; single-pass
+        // sizes (log_n <= 12) write their only pass straight to the destinations
+        if ((rc = bsx_alloc(ctx, &scratch, nb * (size_t)n_local))) break;
+        if ((rc = bsx_commit_transforms(ctx, s->coeffs, s->log_n, n_local, s->rate_bits, input_is_coeffs != 0, scratch,
+                                        nb, &D, timing ? ev[1] : nullptr)))
+            break;
+        s->coeffs_bitrev = !input_is_coeffs;
+        if (timing) cudaEventRecord(ev[2], ctx->stream);
+    } while (0);
+    bsx_free(ctx, scratch);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);  // stores to peer slabs are complete and visible after this
+    if (rc == BSX_OK && e != cudaSuccess) rc = bsx_fail(ctx, BSX_ERR_CUDA, "sharded transform failed: %s", cudaGetErrorString(e));
+    if (timing) {
+        memset(timing, 0, sizeof(*timing));
+        if (rc == BSX_OK && n_local > 0) {
+            cudaEventElapsedTime(&timing->ifft_ms, ev[0], ev[1]);
+            cudaEventElapsedTime(&timing->lde_ms, ev[1], ev[2]);
+            timing->total_ms = timing->ifft_ms + timing->lde_ms;
+        }
+        for (auto &x : ev) cudaEventDestroy(x);
+    }
+    return rc;
+}
+
+// Leaf hashing and the local cap subtrees over this rank's row slab (all slabs must be complete: the
+// host puts a barrier, or the all-to-all, between bsx_shard_transform and this call).  The tree borrows
+// the slab; local cap height = max(cap_height - log2(n_ranks), 0).
+extern "C" int32_t bsx_shard_commit(bsx_shard *s, bsx_tree **out) {
+    if (!s || !out) return BSX_ERR_INVALID_ARG;
+    int local_cap = s->cap_height - s->log_ranks;
+    if (local_cap < 0) local_cap = 0;
+    return bsx_merkle_new_colmajor_device(s->ctx, (const uint64_t *)s->slab, s->chunk,
+                                          s->log_n + s->rate_bits - s->log_ranks, s->n_cols_total, local_cap, out);
+}
+
+extern "C" int32_t bsx_shard_shape(const bsx_shard *s, int32_t *c0, int32_t *c1, uint64_t *chunk, int32_t *local_cap) {
+    if (!s) return BSX_ERR_INVALID_ARG;
+    if (c0) *c0 = s->c0;
+    if (c1) *c1 = s->c1;
+    if (chunk) *chunk = s->chunk;
+    if (local_cap) *local_cap = s->cap_height > s->log_ranks ? s->cap_height - s->log_ranks : 0;
+    return BSX_OK;
+}
+
+// polynomials[c0..c1) of this rank in natural order, column-major
+extern "C" int32_t bsx_shard_coeffs(bsx_shard *s, uint64_t *out, int32_t mem) {
+    if (!s) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = s->ctx;
+    size_t n = (size_t)1 << s->log_n, words = n * (size_t)(s->c1 - s->c0);
+    if (words == 0) return BSX_OK;
+    if (!out || !s->coeffs) return BSX_ERR_INVALID_ARG;
+    CU(ctx, cudaSetDevice(ctx->device));
+    if (s->coeffs_bitrev) {
+        u64 *tmp;
+        TRY(bsx_alloc(ctx, &tmp, words));
+        launch_bitrev_copy(s->coeffs, n, tmp, n, s->log_n, s->c1 - s->c0, ctx->stream);
+        TRY(bsx_copy_out(ctx, (u64 *)out, tmp, words, mem));
+        bsx_free(ctx, tmp);
+    } else {
+        TRY(bsx_copy_out(ctx, (u64 *)out, s->coeffs, words, mem));
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
+// n_in digests (power of two) hashed pairwise `levels` times: the top of the tree when there are more
+// ranks than cap entries (cap_height < log2(n_ranks)), and a general two_to_one helper for hosts.
+extern "C" int32_t bsx_merkle_reduce(bsx_ctx *ctx, const uint64_t *digests_host, int32_t n_in, int32_t levels,
+                                     uint64_t *out_host) {
+    if (!ctx || !digests_host || !out_host || n_in <= 0 || levels < 0 || (n_in >> levels) == 0 ||
+        ((n_in >> levels) << levels) != n_in)
+        return BSX_ERR_INVALID_ARG;
+    CU(ctx, cudaSetDevice(ctx->device));
+    u64 *a, *b;
+    TRY(bsx_alloc(ctx, &a, (size_t)4 * n_in));
+    TRY(bsx_alloc(ctx, &b, (size_t)4 * n_in));
+    CU(ctx, cudaMemcpyAsync(a, digests_host, (size_t)32 * n_in, cudaMemcpyHostToDevice, ctx->stream));
+    size_t cur = (size_t)n_in;
+    for (int l = 0; l < levels; l++) {
+        launch_merkle_level(a, b, cur >> 1, ctx->stream);
+        u64 *t = a;
+        a = b;
+        b = t;
+        cur >>= 1;
+    }
+    CU(ctx, cudaMemcpyAsync(out_host, a, 32 * cur, cudaMemcpyDeviceToHost, ctx->stream));
+    bsx_free(ctx, a);
+    bsx_free(ctx, b);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}

@@ -35,6 +35,7 @@ void launch_gather_siblings(const u64 *digests, int log_leaves, int n_levels, u6
                             cudaStream_t st);
 
 // ---------------------------------------------------------------- NTT
+#define BSX_MAX_RANKS 16
 struct NttTables {
     // omega_{4096}^j, j < 2048 (forward / inverse): sub-transform twiddles
     const u64 *w_fwd, *w_inv;
@@ -56,6 +57,12 @@ struct NttPlan {
     // optional [n_cosets][2^a][2^b] table of scale * pre_lo * inter-pass twiddle (launch_ntt_post_table):
     // one multiplication per output word in pass HI instead of three, and no scaling in pass LO
     const u64 *post_full;
+    // Row-sharded output (multi-GPU commit): when n_dest > 0 the word at leaf position l of column c is
+    // stored to dest[l >> dest_lc] + c * 2^dest_lc + (l & (2^dest_lc - 1)) instead of dst + c * dst_stride
+    // + l; the pointers may be peer-GPU memory (NVLink P2P stores) or slices of a local send buffer.
+    // dst then only carries the intermediate between the two passes.
+    int n_dest, dest_lc;
+    u64 *dest[BSX_MAX_RANKS];
 };
 // Transforms n_cols columns.  src column c at src + c*src_stride (2^log_n words);
 // dst column c at dst + c*dst_stride; coset k is written to the block [bitrev_r(k) << log_n, +2^log_n)

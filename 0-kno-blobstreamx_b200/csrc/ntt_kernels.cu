@@ -46,7 +46,15 @@ struct NttKParams {
     int src_bitrev, r_log;   // r_log = log2(n_cosets)
     int pitch;               // words between tile columns in shared memory
     NttGroups groups;
+    int n_dest, dest_lc;     // row-sharded output (see NttPlan)
+    u64 *dest[BSX_MAX_RANKS];
 };
+
+// final position of leaf l of column col: local column-major buffer, or the owning rank's row slab
+__device__ __forceinline__ u64 *ntt_out(const NttKParams &P, int col, size_t l) {
+    if (P.n_dest == 0) return P.dst + (size_t)col * P.dst_stride + l;
+    return P.dest[l >> P.dest_lc] + ((size_t)col << P.dest_lc) + (l & (((size_t)1 << P.dest_lc) - 1));
+}
 
 __device__ __forceinline__ u64 gl_mul_c(u64 a, u64 b) { return gl_canon_fast(gl_mul_lazy(a, b)); }
 
@@ -151,7 +159,9 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
     load_twiddles(tws, P.wtab, a);
 
     for (int k = 0; k < n_cosets; k++) {
-        u64 *dst = P.dst + (size_t)col * P.dst_stride + ((size_t)bitrev32(k, P.r_log) << P.log_n);
+        const size_t blk = (size_t)bitrev32(k, P.r_log) << P.log_n;
+        u64 *dst = P.dst + (size_t)col * P.dst_stride + blk;
+        const bool remap = P.n_dest != 0 && b == 0;
         for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
             int i1, j;
             size_t pos;
@@ -195,7 +205,8 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
             } else if (P.scale != 1) {
                 v = gl_mul_c(v, P.scale);
             }
-            dst[o] = v;
+            if (remap) *ntt_out(P, col, blk + o) = v;
+            else dst[o] = v;
         }
         __syncthreads();
     }
@@ -208,7 +219,8 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
     const int S = 1 << b;
     u64 *tws = sm_all, *sm = sm_all + (S >> 1);
     const int n_el = 1 << (b + w_log);
-    u64 *base = P.dst + (size_t)blockIdx.y * P.dst_stride + ((size_t)blockIdx.x << (b + w_log));
+    const size_t l0 = (size_t)blockIdx.x << (b + w_log);
+    u64 *base = P.dst + (size_t)blockIdx.y * P.dst_stride + l0;
     load_twiddles(tws, P.wtab, b);
     for (int e0 = threadIdx.x; e0 < n_el; e0 += blockDim.x * NTT_IO_UNROLL) {
         u64 v[NTT_IO_UNROLL];
@@ -229,7 +241,8 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
     for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
         u64 v = sm[ntt_sm(e >> b, e & (S - 1), pitch)];
         if (scale) v = gl_mul_c(v, P.scale);
-        base[e] = v;
+        if (P.n_dest) *ntt_out(P, blockIdx.y, l0 + e) = v;
+        else base[e] = v;
     }
 }
 
@@ -308,6 +321,9 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
     while ((1 << r_log) < plan.n_cosets) r_log++;
     P.r_log = r_log;
     P.post_full = plan.b > 0 ? plan.post_full : nullptr;
+    P.n_dest = plan.n_dest;
+    P.dest_lc = plan.dest_lc;
+    for (int i = 0; i < BSX_MAX_RANKS; i++) P.dest[i] = i < plan.n_dest ? plan.dest[i] : nullptr;
     // pass HI: tile of 2^a points x W adjacent i0
     {
         int w_log = 13 - plan.a;  // 8192 elements per tile

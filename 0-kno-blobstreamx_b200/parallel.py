@@ -1,0 +1,261 @@
+"""One `PolynomialBatch::from_values` commit sharded over the GPUs of a box, one process per GPU.
+
+plonky2 has no multi-device path (fri/oracle.rs is single-process, rayon over columns); this is the
+partitioning BASELINE.json's north star lays out, on top of the `bsx_shard_*` entry points of
+include/bsx_b200.h:
+
+  columns -> ranks   iNTT + coset LDE of this rank's columns, no communication;
+  leaf rows -> ranks  rank g owns leaves [g * chunk, (g + 1) * chunk) of every column.  Because the
+                     device transforms leave every column in Merkle-leaf order, that is one contiguous
+                     range per column;
+  exchange           mode "p2p": the last NTT pass stores each LDE word into the owner's row slab over
+                     NVLink (slab addresses exchanged once as CUDA IPC handles), then one barrier;
+                     mode "nccl": the pass fills a destination-major staging buffer and the host runs one
+                     all-to-all over `torch.distributed`;
+  trees              every rank hashes its rows and builds its 2^cap_height / G cap subtrees; the caps
+                     are all-gathered (512 bytes at cap_height 4).
+
+`torch.distributed` is plumbing only: rendezvous, the handle/cap all-gathers, the barrier and (mode
+"nccl") the all-to-all.  All arithmetic is in libbsx_b200.so.
+"""
+import ctypes as C
+
+import numpy as np
+
+from .binding import BSX_DEVICE, BSX_HOST, BsxError, MerkleTree, Timing, _np, _ptr, lib
+
+IPC_BYTES = 64
+
+
+def _log2_strict(n):
+    if n <= 0 or n & (n - 1):
+        raise BsxError("Not a power of two: %d" % n)
+    return n.bit_length() - 1
+
+
+class ShardPlan:
+    """Who owns what.  Pure host arithmetic (covered by the CPU tests); must agree with api_shard.cu."""
+
+    def __init__(self, log_n, n_cols, rate_bits, cap_height, world):
+        self.log_n, self.n_cols, self.rate_bits, self.cap_height, self.world = log_n, n_cols, rate_bits, cap_height, world
+        self.log_world = _log2_strict(world)
+        self.log_nb = log_n + rate_bits
+        if self.log_world > self.log_nb:
+            raise BsxError("more ranks than leaves")
+        if not 0 <= cap_height <= self.log_nb:
+            raise BsxError("cap_height=%d should be at most log2(leaves.len())=%d" % (cap_height, self.log_nb))
+        self.chunk = 1 << (self.log_nb - self.log_world)  # leaf rows per rank
+
+    def column_range(self, rank):
+        """Balanced contiguous column ranges: the first (C mod G) ranks take one extra column."""
+        q, r = divmod(self.n_cols, self.world)
+        c0 = rank * q + min(rank, r)
+        return c0, c0 + q + (1 if rank < r else 0)
+
+    def owner(self, leaf):
+        return leaf >> (self.log_nb - self.log_world)
+
+    def local_leaf(self, leaf):
+        return leaf & (self.chunk - 1)
+
+    @property
+    def local_cap_height(self):
+        return max(self.cap_height - self.log_world, 0)
+
+    @property
+    def reduce_levels(self):
+        """two_to_one levels left above the per-rank roots when there are more ranks than cap entries."""
+        return max(self.log_world - self.cap_height, 0)
+
+    def staging_block_words(self, rank):
+        """Words of each of the G destination blocks in rank's staging buffer (all equal)."""
+        c0, c1 = self.column_range(rank)
+        return (c1 - c0) * self.chunk
+
+    def slab_offset_words(self, src_rank):
+        """Where src_rank's block lands in a destination's row slab."""
+        return self.column_range(src_rank)[0] * self.chunk
+
+    def staging_index(self, rank, col, leaf):
+        """Word index in rank's staging buffer of LDE word (col, leaf), col in rank's column range.
+        The contract between the transform kernel's store and the all-to-all."""
+        c0, c1 = self.column_range(rank)
+        assert c0 <= col < c1
+        return self.owner(leaf) * (c1 - c0) * self.chunk + (col - c0) * self.chunk + self.local_leaf(leaf)
+
+
+class _DevArray:
+    """A raw device pointer seen as a 1-D int64 CUDA array (for torch.as_tensor; zero copy)."""
+
+    def __init__(self, ptr, words):
+        self.__cuda_array_interface__ = {"shape": (int(words),), "typestr": "<i8", "data": (int(ptr), False),
+                                         "version": 2}
+
+
+def device_tensor(ptr, words, device):
+    import torch
+    if words == 0 or not ptr:
+        return torch.empty(0, dtype=torch.int64, device="cuda:%d" % device)
+    return torch.as_tensor(_DevArray(ptr, words), device="cuda:%d" % device)
+
+
+def exchange_staged(send, recv, plan, rank, group=None):
+    """The all-to-all of mode "nccl" on any pair of 1-D int64 torch tensors (CUDA for NCCL, CPU for the
+    gloo tests): block d of `send` -> rank d, landing at slab_offset_words(rank) in its `recv`."""
+    import torch.distributed as dist
+    n_in = [plan.staging_block_words(rank)] * plan.world
+    n_out = [plan.staging_block_words(s) for s in range(plan.world)]
+    assert send.numel() == sum(n_in) and recv.numel() == plan.n_cols * plan.chunk
+    if dist.get_backend(group) == "nccl":
+        dist.all_to_all_single(recv, send, output_split_sizes=n_out, input_split_sizes=n_in, group=group)
+        return
+    # gloo: paired point-to-point transfers, same layout
+    ops, off_in = [], 0
+    for peer in range(plan.world):
+        blk = send[off_in:off_in + n_in[peer]]
+        off_in += n_in[peer]
+        dst = recv[plan.slab_offset_words(peer):plan.slab_offset_words(peer) + n_out[peer]]
+        if peer == rank:
+            dst.copy_(blk)
+        else:
+            if n_in[peer]:
+                ops.append(dist.P2POp(dist.isend, blk.contiguous(), peer, group=group))
+            if n_out[peer]:
+                ops.append(dist.P2POp(dist.irecv, dst, peer, group=group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+
+
+def assemble_cap(local_caps, plan, ctx=None):
+    """Cap of the whole batch from the per-rank caps in rank order (merkle_tree.rs: the cap is the layer of
+    2^cap_height nodes, left to right).  More ranks than cap entries: hash the rank roots up."""
+    cap = np.concatenate([np.asarray(c, dtype=np.uint64).reshape(-1, 4) for c in local_caps], axis=0)
+    if plan.reduce_levels:
+        if ctx is None:
+            raise BsxError("cap_height < log2(world) needs a Context to hash the rank roots")
+        out = np.zeros((cap.shape[0] >> plan.reduce_levels, 4), dtype=np.uint64)
+        ctx.check(lib().bsx_merkle_reduce(ctx._h, _ptr(_np(cap)), cap.shape[0], plan.reduce_levels, _ptr(out)))
+        cap = out
+    assert cap.shape[0] == 1 << plan.cap_height
+    return cap
+
+
+class ShardedPolynomialBatch:
+    """This rank's part of one committed batch: its coefficient columns, its leaf rows and cap subtrees,
+    and the cap of the whole batch.  `merkle_tree.get / prove` answer for leaves this rank owns
+    (`plan.owner(leaf) == rank`, local index `plan.local_leaf(leaf)`); with cap_height >= log2(world) the
+    proof is word for word the single-GPU proof."""
+
+    def __init__(self, ctx, plan, rank, handle):
+        self.ctx, self.plan, self.rank, self._h = ctx, plan, rank, handle
+        self.merkle_tree = None
+        self.cap = None
+        self.timing = None
+
+    # ---- construction pieces (also used one by one by the single-process tests)
+    @classmethod
+    def create(cls, ctx, plan, rank):
+        h = C.c_void_p()
+        ctx.check(lib().bsx_shard_create(ctx._h, plan.log_n, plan.n_cols, plan.rate_bits, plan.cap_height, rank,
+                                         plan.world, C.byref(h)))
+        return cls(ctx, plan, rank, h)
+
+    @property
+    def slab_ptr(self):
+        return lib().bsx_shard_slab_device(self._h) or 0
+
+    @property
+    def staging_ptr(self):
+        return lib().bsx_shard_staging_device(self._h) or 0
+
+    def ipc_handle(self):
+        buf = (C.c_uint8 * IPC_BYTES)()
+        self.ctx.check(lib().bsx_shard_slab_ipc(self._h, buf))
+        return bytes(buf)
+
+    def set_peer_ipc(self, peer, handle):
+        buf = (C.c_uint8 * IPC_BYTES).from_buffer_copy(handle)
+        self.ctx.check(lib().bsx_shard_set_peer_ipc(self._h, peer, buf))
+
+    def set_peer_ptr(self, peer, ptr):
+        self.ctx.check(lib().bsx_shard_set_peer_ptr(self._h, peer, C.c_void_p(int(ptr))))
+
+    def transform(self, values_local, is_coeffs=False, use_staging=False, device_ptr=None, timing=False):
+        c0, c1 = self.plan.column_range(self.rank)
+        if device_ptr is not None:
+            src, mem = C.c_void_p(int(device_ptr)), BSX_DEVICE
+        else:
+            values_local = _np(values_local)
+            if values_local.shape != (c1 - c0, 1 << self.plan.log_n):
+                raise BsxError("rank %d expects columns [%d, %d) as a (%d, %d) array" %
+                               (self.rank, c0, c1, c1 - c0, 1 << self.plan.log_n))
+            src, mem = _ptr(values_local), BSX_HOST
+        t = Timing() if timing else None
+        self.ctx.check(lib().bsx_shard_transform(self._h, src, mem, 1 if is_coeffs else 0, 1 if use_staging else 0,
+                                                 C.byref(t) if t is not None else None))
+        self.timing = t
+
+    def commit(self):
+        h = C.c_void_p()
+        self.ctx.check(lib().bsx_shard_commit(self._h, C.byref(h)))
+        self.merkle_tree = MerkleTree(self.ctx, _handle=h)
+        return self.merkle_tree.cap
+
+    @property
+    def polynomials(self):
+        c0, c1 = self.plan.column_range(self.rank)
+        out = np.zeros((c1 - c0, 1 << self.plan.log_n), dtype=np.uint64)
+        self.ctx.check(lib().bsx_shard_coeffs(self._h, _ptr(out), BSX_HOST))
+        return out
+
+    # ---- the whole thing, one process per GPU
+    @classmethod
+    def from_values(cls, ctx, values_local, log_n, n_cols, rate_bits, cap_height, group=None, mode="p2p",
+                    device_ptr=None, is_coeffs=False, timing=False):
+        """Collective over `group` (default: the world group, NCCL): every rank passes ITS columns
+        (`ShardPlan.column_range(rank)`) and gets the cap of the whole batch plus its row slab's tree."""
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        plan = ShardPlan(log_n, n_cols, rate_bits, cap_height, world)
+        self = cls.create(ctx, plan, rank)
+        dev = "cuda:%d" % ctx.device
+        if mode == "p2p":
+            mine = torch.tensor(list(self.ipc_handle()), dtype=torch.uint8, device=dev)
+            allh = torch.empty(world * IPC_BYTES, dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(allh, mine, group=group)
+            allh = allh.cpu().numpy().tobytes()
+            for peer in range(world):
+                if peer != rank:
+                    self.set_peer_ipc(peer, allh[peer * IPC_BYTES:(peer + 1) * IPC_BYTES])
+            self.transform(values_local, is_coeffs, use_staging=False, device_ptr=device_ptr, timing=timing)
+            dist.barrier(group=group)  # every rank's stores into every slab are complete
+        elif mode == "nccl":
+            self.transform(values_local, is_coeffs, use_staging=True, device_ptr=device_ptr, timing=timing)
+            send = device_tensor(self.staging_ptr, plan.world * plan.staging_block_words(rank), ctx.device)
+            recv = device_tensor(self.slab_ptr, plan.n_cols * plan.chunk, ctx.device)
+            exchange_staged(send, recv, plan, rank, group)
+            torch.cuda.synchronize(ctx.device)
+        else:
+            raise BsxError("mode must be 'p2p' or 'nccl'")
+        local = torch.from_numpy(self.commit().astype(np.int64)).to(dev).reshape(-1)
+        caps = torch.empty(world * local.numel(), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(caps, local, group=group)
+        caps = caps.cpu().numpy().astype(np.uint64).reshape(world, -1, 4)
+        self.cap = assemble_cap(list(caps), plan, ctx)
+        return self
+
+    def close(self):
+        if self.merkle_tree is not None:
+            self.merkle_tree.close()
+            self.merkle_tree = None
+        if self._h is not None:
+            lib().bsx_shard_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -120,6 +120,46 @@ int32_t bsx_merkle_prove(bsx_tree *t, uint64_t leaf_index, uint64_t *siblings_ho
 int32_t bsx_merkle_digests(bsx_tree *t, uint64_t *out_host);
 int32_t bsx_merkle_shape(const bsx_tree *t, int32_t *log_leaves, int32_t *leaf_len, int32_t *cap_height);
 
+/* pairwise two_to_one reduction of n_in digests (host) `levels` times -> n_in >> levels digests (host).
+ * The top of a tree assembled from per-rank roots; PoseidonHash::two_to_one for host code. */
+int32_t bsx_merkle_reduce(bsx_ctx *ctx, const uint64_t *digests_host, int32_t n_in, int32_t levels,
+                          uint64_t *out_host);
+
+/* ---- one commit sharded over the GPUs of a box (no upstream counterpart; BASELINE.json north star) ------
+ * PolynomialBatch::from_values split as: columns -> ranks for the transforms, leaf rows -> ranks for
+ * hashing.  Rank g of G (a power of two, <= 16) owns columns bsx_shard_column_range() and the leaf rows
+ * [g * chunk, (g+1) * chunk), chunk = 2^(log_n + rate_bits) / G, of every column, held in its "row slab"
+ * (n_cols_total x chunk, column-major).  Call order on every rank:
+ *   bsx_shard_create -> exchange slab addresses (bsx_shard_slab_ipc / bsx_shard_set_peer_ipc across
+ *   processes, bsx_shard_set_peer_ptr inside one) -> bsx_shard_transform(use_staging = 0): the last NTT pass
+ *   stores every LDE word into its owner's slab over NVLink -> host barrier -> bsx_shard_commit.
+ * Without peer access: bsx_shard_transform(use_staging = 1) fills a destination-major staging buffer, the
+ * host runs one all-to-all (block d of n_local_cols * chunk words goes to rank d's slab at offset
+ * c0 * chunk words), then bsx_shard_commit.  The local caps, concatenated in rank order, are the cap of the
+ * whole batch (followed by bsx_merkle_reduce when cap_height < log2 G); every word equals the
+ * single-GPU result. */
+typedef struct bsx_shard bsx_shard;
+#define BSX_MAX_RANKS 16
+#define BSX_IPC_HANDLE_BYTES 64 /* sizeof(cudaIpcMemHandle_t) */
+int32_t bsx_shard_column_range(int32_t n_cols_total, int32_t rank, int32_t n_ranks, int32_t *c0, int32_t *c1);
+int32_t bsx_shard_create(bsx_ctx *ctx, int32_t log_n, int32_t n_cols_total, int32_t rate_bits, int32_t cap_height,
+                         int32_t rank, int32_t n_ranks, bsx_shard **out);
+void bsx_shard_free(bsx_shard *s);
+int32_t bsx_shard_shape(const bsx_shard *s, int32_t *c0, int32_t *c1, uint64_t *chunk, int32_t *local_cap_height);
+uint64_t *bsx_shard_slab_device(bsx_shard *s);
+uint64_t *bsx_shard_staging_device(bsx_shard *s);
+const uint64_t *bsx_shard_coeffs_device(const bsx_shard *s);
+int32_t bsx_shard_slab_ipc(bsx_shard *s, uint8_t *handle_out /* BSX_IPC_HANDLE_BYTES */);
+int32_t bsx_shard_set_peer_ipc(bsx_shard *s, int32_t peer_rank, const uint8_t *handle);
+int32_t bsx_shard_set_peer_ptr(bsx_shard *s, int32_t peer_rank, uint64_t *slab_dev);
+/* input: this rank's columns only, (c1 - c0) x 2^log_n column-major values (or coefficients) */
+int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
+                            int32_t use_staging, bsx_timing *timing);
+/* MerkleTree over this rank's slab (borrowed): 2^(cap_height - log2 G) local cap entries */
+int32_t bsx_shard_commit(bsx_shard *s, bsx_tree **out);
+/* this rank's polynomials in natural order, (c1 - c0) x 2^log_n */
+int32_t bsx_shard_coeffs(bsx_shard *s, uint64_t *out, int32_t mem);
+
 /* ---- Challenger (iop/challenger.rs) and FRI (fri/oracle.rs prove_openings, fri/prover.rs) -------------
  * bsx_challenger mirrors plonky2's `Challenger<F, PoseidonHash>`: sponge state, input buffer, output
  * buffer (outputs are popped from the BACK, as Vec::pop does).  The struct lives on the host between calls;

@@ -1,0 +1,52 @@
+"""torchrun worker: one process per GPU commits one batch with ShardedPolynomialBatch.from_values and
+checks cap, rows and Merkle paths against the single-GPU batch computed on rank 0's device."""
+import argparse
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import __graft_entry__ as G  # noqa: E402
+from conftest import splitmix_field  # noqa: E402
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mode", default="p2p")
+    ap.add_argument("--log-n", type=int, default=14)
+    ap.add_argument("--cols", type=int, default=135)
+    a = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = G.load_package()
+    ctx = pkg.Context(local)
+    vals = splitmix_field(4242, (a.cols, 1 << a.log_n))  # every rank generates the same witness
+    plan = pkg.ShardPlan(a.log_n, a.cols, 3, 4, world)
+    c0, c1 = plan.column_range(rank)
+    sb = pkg.ShardedPolynomialBatch.from_values(ctx, vals[c0:c1], a.log_n, a.cols, 3, 4, mode=a.mode)
+    ref = pkg.PolynomialBatch.from_values(ctx, vals, 3, False, 4)
+    assert (sb.cap == ref.cap).all(), "rank %d: sharded cap differs" % rank
+    tree = ref.merkle_tree
+    for k in range(16):
+        leaf = rank * plan.chunk + (k * 2654435761) % plan.chunk
+        assert (sb.merkle_tree.get(plan.local_leaf(leaf)) == tree.get(leaf)).all()
+        assert (sb.merkle_tree.prove(plan.local_leaf(leaf)) == tree.prove(leaf)).all()
+    assert (sb.polynomials == ref.polynomials[c0:c1]).all()
+    cap0 = int(sb.cap[0, 0])
+    dist.barrier()
+    sb.close()
+    ref.close()
+    ctx.close()
+    if rank == 0:
+        print("sharded commit ok: mode=%s world=%d cap0=%016x" % (a.mode, world, cap0))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
