@@ -152,6 +152,7 @@ class ShardedPolynomialBatch:
         self.merkle_tree = None
         self.cap = None
         self.timing = None
+        self.group, self.mode = None, "p2p"
 
     # ---- construction pieces (also used one by one by the single-process tests)
     @classmethod
@@ -211,17 +212,19 @@ class ShardedPolynomialBatch:
 
     # ---- the whole thing, one process per GPU
     @classmethod
-    def from_values(cls, ctx, values_local, log_n, n_cols, rate_bits, cap_height, group=None, mode="p2p",
-                    device_ptr=None, is_coeffs=False, timing=False):
-        """Collective over `group` (default: the world group, NCCL): every rank passes ITS columns
-        (`ShardPlan.column_range(rank)`) and gets the cap of the whole batch plus its row slab's tree."""
+    def setup(cls, ctx, log_n, n_cols, rate_bits, cap_height, group=None, mode="p2p"):
+        """Collective: allocate this rank's row slab and (mode "p2p") open every peer's slab through CUDA
+        IPC.  The returned object can commit any number of batches of this shape with `run`."""
         import torch
         import torch.distributed as dist
+        if mode not in ("p2p", "nccl"):
+            raise BsxError("mode must be 'p2p' or 'nccl'")
         rank, world = dist.get_rank(group), dist.get_world_size(group)
         plan = ShardPlan(log_n, n_cols, rate_bits, cap_height, world)
         self = cls.create(ctx, plan, rank)
-        dev = "cuda:%d" % ctx.device
+        self.group, self.mode = group, mode
         if mode == "p2p":
+            dev = "cuda:%d" % ctx.device
             mine = torch.tensor(list(self.ipc_handle()), dtype=torch.uint8, device=dev)
             allh = torch.empty(world * IPC_BYTES, dtype=torch.uint8, device=dev)
             dist.all_gather_into_tensor(allh, mine, group=group)
@@ -229,22 +232,41 @@ class ShardedPolynomialBatch:
             for peer in range(world):
                 if peer != rank:
                     self.set_peer_ipc(peer, allh[peer * IPC_BYTES:(peer + 1) * IPC_BYTES])
+        return self
+
+    def run(self, values_local, device_ptr=None, is_coeffs=False, timing=False):
+        """Collective: commit one batch.  Every rank passes ITS columns (`plan.column_range(rank)`); on
+        return `cap` is the cap of the whole batch and `merkle_tree` this rank's rows and subtrees.  The cap
+        all-gather at the end doubles as the barrier that makes the slabs safe to overwrite by the next run."""
+        import torch
+        import torch.distributed as dist
+        plan, ctx, group = self.plan, self.ctx, self.group
+        dev = "cuda:%d" % ctx.device
+        if self.merkle_tree is not None:
+            self.merkle_tree.close()
+            self.merkle_tree = None
+        if self.mode == "p2p":
             self.transform(values_local, is_coeffs, use_staging=False, device_ptr=device_ptr, timing=timing)
             dist.barrier(group=group)  # every rank's stores into every slab are complete
-        elif mode == "nccl":
-            self.transform(values_local, is_coeffs, use_staging=True, device_ptr=device_ptr, timing=timing)
-            send = device_tensor(self.staging_ptr, plan.world * plan.staging_block_words(rank), ctx.device)
-            recv = device_tensor(self.slab_ptr, plan.n_cols * plan.chunk, ctx.device)
-            exchange_staged(send, recv, plan, rank, group)
-            torch.cuda.synchronize(ctx.device)
         else:
-            raise BsxError("mode must be 'p2p' or 'nccl'")
+            self.transform(values_local, is_coeffs, use_staging=True, device_ptr=device_ptr, timing=timing)
+            send = device_tensor(self.staging_ptr, plan.world * plan.staging_block_words(self.rank), ctx.device)
+            recv = device_tensor(self.slab_ptr, plan.n_cols * plan.chunk, ctx.device)
+            exchange_staged(send, recv, plan, self.rank, group)
+            torch.cuda.synchronize(ctx.device)
         local = torch.from_numpy(self.commit().astype(np.int64)).to(dev).reshape(-1)
-        caps = torch.empty(world * local.numel(), dtype=torch.int64, device=dev)
+        caps = torch.empty(plan.world * local.numel(), dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(caps, local, group=group)
-        caps = caps.cpu().numpy().astype(np.uint64).reshape(world, -1, 4)
+        caps = caps.cpu().numpy().astype(np.uint64).reshape(plan.world, -1, 4)
         self.cap = assemble_cap(list(caps), plan, ctx)
         return self
+
+    @classmethod
+    def from_values(cls, ctx, values_local, log_n, n_cols, rate_bits, cap_height, group=None, mode="p2p",
+                    device_ptr=None, is_coeffs=False, timing=False):
+        """`PolynomialBatch::from_values` over `group` (default: the world group, NCCL): setup + run."""
+        return cls.setup(ctx, log_n, n_cols, rate_bits, cap_height, group, mode).run(values_local, device_ptr,
+                                                                                     is_coeffs, timing)
 
     def close(self):
         if self.merkle_tree is not None:

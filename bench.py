@@ -9,6 +9,10 @@ header_range map jobs of the north star share no state, so ranks exchange nothin
 the witness already in HBM; `e2e` = the same through the C ABI with the witness in pinned HOST
 memory (H2D inside the timed call, cap back on the host).
 
+At N > 1 the line also carries `sharded`: ONE commit of the same shape split over the N GPUs (strong
+scaling; column-sharded transforms whose last pass stores into the owners' row slabs over NVLink P2P, or a
+staged NCCL all-to-all; per-GPU cap subtrees; cap gathered) -- see 0-kno-blobstreamx_b200/parallel.py.
+
 `--impl reference` times the CPU arm instead: the in-repo oracle port of the plonky2 algorithm
 (the reference mount holds no source and there is no Rust toolchain) with all
 host threads on a bounded sample of the same workload.
@@ -31,13 +35,15 @@ LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT = 20, 135, 3, 4
 CPU_SAMPLE_LOG_N = 15  # bounded CPU sample: same columns / rate / cap, 2^15 rows
 
 
-def splitmix_field(seed, shape):
+def splitmix_field(seed, shape, offset=0):
+    """Counter-based SplitMix64 stream reduced mod p; `offset` starts the counter there, so a slice of a
+    larger array can be generated on its own (the column ranges of the sharded commit)."""
     n = int(np.prod(shape))
     out = np.empty(n, dtype=np.uint64)
     chunk = 1 << 24
     with np.errstate(over="ignore"):
         for lo in range(0, n, chunk):
-            idx = np.arange(lo + 1, min(lo + chunk, n) + 1, dtype=np.uint64)
+            idx = np.arange(offset + lo + 1, offset + min(lo + chunk, n) + 1, dtype=np.uint64)
             z = np.uint64(seed) + idx * np.uint64(0x9E3779B97F4A7C15)
             z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
             z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
@@ -137,6 +143,50 @@ def workload_config(n_gpus):
             "l2": "inputs (1.13 GB) and LDE (9.06 GB) exceed the 126 MB L2; no flush needed"}
 
 
+def sharded_arm(args, pkg, ctx, stream, rank, world, local_rank, cap_rank0):
+    """Strong-scaling leg at N > 1: ONE 2^20 x 135 commit sharded over the N GPUs (columns -> ranks for the
+    transforms, leaf rows -> ranks for hashing), in both exchange modes: "p2p" = the last NTT pass stores
+    into the owners' row slabs over NVLink, "nccl" = staged all-to-all.  The witness is rank 0's witness
+    of the independent-commit leg, so the cap must equal rank 0's cap there."""
+    import torch
+    import torch.distributed as dist
+    n = 1 << LOG_N
+    dev = "cuda:%d" % local_rank
+    plan = pkg.ShardPlan(LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT, world)
+    c0, c1 = plan.column_range(rank)
+    loc = torch.from_numpy(splitmix_field(0x5EED0001, (c1 - c0, n), offset=c0 * n).view(np.int64)).to(dev)
+    want = torch.from_numpy(np.ascontiguousarray(cap_rank0).view(np.int64).copy()).to(dev)
+    dist.broadcast(want, 0)
+    want = want.cpu().numpy().view(np.uint64)
+    out = {"scaling": "strong", "workload": "one 2^%d x %d commit over %d GPUs" % (LOG_N, N_COLS, world)}
+    with torch.cuda.stream(stream):
+        for mode in ("p2p", "nccl"):
+            sb = pkg.ShardedPolynomialBatch.setup(ctx, LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT, mode=mode)
+            for _ in range(2):
+                sb.run(None, device_ptr=loc.data_ptr())
+            assert (sb.cap == want).all(), "sharded cap (%s) differs from the single-GPU cap" % mode
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            tr = []
+            for _ in range(args.steps):
+                sb.run(None, device_ptr=loc.data_ptr(), timing=True)
+                tr.append(sb.timing.as_dict())
+            e1.record(stream)
+            dist.barrier()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / args.steps, float(np.mean([x["ifft_ms"] for x in tr])),
+                              float(np.mean([x["lde_ms"] for x in tr]))], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t[0])
+            out[mode] = {"ms_per_commit": ms, "value": n * N_COLS / (ms * 1e-3) / 1e6, "unit": "Melem/s",
+                         "ifft_ms_max": float(t[1]), "lde_ms_max": float(t[2]),
+                         "exchange_bytes_per_gpu": 8 * (c1 - c0) * (world - 1) * plan.chunk}
+            sb.close()
+    return out
+
+
 def gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -209,6 +259,7 @@ def gpu_arm(args, rank, world, local_rank):
         t = torch.tensor([ms, ms_e2e], device="cuda:%d" % local_rank, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(t[0]), float(t[1])
+    sharded = sharded_arm(args, pkg, ctx, stream, rank, world, local_rank, cap0) if world > 1 else None
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -249,6 +300,8 @@ def gpu_arm(args, rank, world, local_rank):
         "poseidon": {"permutations_per_step": perms,
                      "gperm_per_s": perms / ((avg["leaf_hash_ms"] + avg["tree_ms"]) * 1e-3) / 1e9},
     }
+    if sharded is not None:
+        out["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle as O
         ns = 1 << CPU_SAMPLE_LOG_N
