@@ -58,29 +58,41 @@ __device__ __forceinline__ u64 gl_sqr(u64 a) { return gl_mul(a, a); }
 // residue, not necessarily < p).  Everything below is branch-free inline PTX on 32-bit limbs so
 // that ptxas emits IMAD.WIDE.U32 (+carry-out / .X carry-in) for the products and IADD3/IMAD.X
 // carry chains for the reduction -- no IMAD.HI (quarter rate on B200, tools/microbench/pipes.cu)
-// and no compare+select sequences.  ~20 SASS instructions per multiply instead of ~36.
+// and no compare+select sequences.  16 SASS instructions per multiply instead of ~36.
 
-// (e1:e0) = x * EPS = (x << 32) - x.  GL_EPS_ALU = 1: two carry-chain subtractions on the ALU pipe
-// instead of one quarter-rate IMAD.WIDE on the FMA-heavy pipe.  Measured on B200 (tools/microbench/
-// poseidon_bench.cu): slower, because the ALU pipe is co-critical (67-72 % busy) -- left off.
-#ifndef GL_EPS_ALU
-#define GL_EPS_ALU 0
-#endif
-#if GL_EPS_ALU
-#define GL_EPS_TIMES(x) "sub.cc.u32 e0, 0, " x ";\n\tsubc.u32 e1, " x ", 0;\n\t"
-#else
-#define GL_EPS_TIMES(x) "mul.wide.u32 e, " x ", 0xFFFFFFFF;\n\tmov.b64 {e0,e1}, e;\n\t"
-#endif
+// EPS as a constant-bank operand: ptxas then keeps `x2 * EPS + (x1:x0)` as ONE IMAD.WIDE.U32 with carry-out
+// (with the literal 0xFFFFFFFF it strength-reduces the low half to a subtraction and adds an IMAD.HI).
+static __constant__ u32 GL_EPS32_C = 0xFFFFFFFFu;
 
-// 128-bit product + 64-bit addend, reduced:  a * b + c  (mod p), all lazy.
+// Tail shared by the multiplies: (x3:x2:x1:x0) -> lazy u64.
+//   r = (x1:x0) + x2 * EPS - x3  in 96-bit two's complement: the IMAD.WIDE's carry and the borrow of the
+//   subtraction meet in r2 in {-1, 0, 1}; one signed correction r2 * EPS = (r2 >> 31 : -r2) finishes.  It
+//   cannot wrap again: r2 = 1 means the low 64 bits are < 2^64 - 2^32, r2 = -1 means they are >= 2^64 - 2^32
+//   (x3 < 2^32).  11 SASS instructions after the four products (the two-fix form took 15).
+#define GL_REDUCE_TAIL(EPS_OPERAND, SUB_HI)                  \
+    "mad.lo.cc.u32 x0, x2, " EPS_OPERAND ", x0;\n\t"         \
+    "madc.hi.cc.u32 x1, x2, " EPS_OPERAND ", x1;\n\t"        \
+    "addc.u32 r2, 0, 0;\n\t"                                 \
+    "sub.cc.u32 x0, x0, x3;\n\t"                             \
+    "subc.cc.u32 x1, x1, " SUB_HI ";\n\t"                    \
+    "subc.u32 r2, r2, 0;\n\t"                                \
+    "sub.u32 n, 0, r2;\n\t"                                  \
+    "shr.s32 eh, r2, 31;\n\t"                                \
+    "add.cc.u32 %0, x0, n;\n\t"                              \
+    "addc.u32 %1, x1, eh;\n\t}"
+
+// 128-bit product + 64-bit addend, reduced:  a * b + c  (mod p), all lazy.  c is added to the partial
+// products a0*b0 and a0*b1 (neither sum can overflow 64 bits), so the addend costs no carry handling later.
 //   x = x0 + x1 2^32 + x2 2^64 + x3 2^96 == (x1:x0) - x3 + x2 * EPS   (2^64 == EPS, 2^96 == -1)
 __device__ __forceinline__ u64 gl_mul_add_lazy(u64 a, u64 b, u64 c) {
     u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32);
     u32 c0 = (u32)c, c1 = (u32)(c >> 32), r0, r1;
-    asm("{\n\t.reg .u32 x0,x1,x2,x3,t0,t1,t2,m,e0,e1;\n\t.reg .u64 w0,w3,t,e;\n\t"
-        "mul.wide.u32 w0, %2, %4;\n\t"
+    asm("{\n\t.reg .u32 x0,x1,x2,x3,t0,t1,t2,r2,n,eh;\n\t.reg .u64 w0,w3,t,cx0,cx1;\n\t"
+        "cvt.u64.u32 cx0, %7;\n\t"
+        "cvt.u64.u32 cx1, %8;\n\t"
+        "mad.wide.u32 w0, %2, %4, cx0;\n\t"
         "mul.wide.u32 w3, %3, %5;\n\t"
-        "mul.wide.u32 t, %2, %5;\n\t"
+        "mad.wide.u32 t, %2, %5, cx1;\n\t"
         "mov.b64 {t0,t1}, t;\n\t"
         "mad.lo.cc.u32 t0, %3, %4, t0;\n\t"
         "madc.hi.cc.u32 t1, %3, %4, t1;\n\t"
@@ -90,31 +102,16 @@ __device__ __forceinline__ u64 gl_mul_add_lazy(u64 a, u64 b, u64 c) {
         "add.cc.u32 x1, x1, t0;\n\t"
         "addc.cc.u32 x2, x2, t1;\n\t"
         "addc.u32 x3, x3, t2;\n\t"
-        "add.cc.u32 x0, x0, %6;\n\t"  // + c (cannot overflow 128 bits)
-        "addc.cc.u32 x1, x1, %7;\n\t"
-        "addc.cc.u32 x2, x2, 0;\n\t"
-        "addc.u32 x3, x3, 0;\n\t"
-        "sub.cc.u32 x0, x0, x3;\n\t"  // (x1:x0) - x3, borrowed 2^64 == EPS
-        "subc.cc.u32 x1, x1, 0;\n\t"
-        "subc.u32 m, 0, 0;\n\t"
-        "sub.cc.u32 x0, x0, m;\n\t"
-        "subc.u32 x1, x1, 0;\n\t"
-        GL_EPS_TIMES("x2")  // + x2 * EPS, wrapped 2^64 == EPS
-        "add.cc.u32 x0, x0, e0;\n\t"
-        "addc.cc.u32 x1, x1, e1;\n\t"
-        "addc.u32 t2, 0, 0;\n\t"
-        "sub.u32 m, 0, t2;\n\t"
-        "add.cc.u32 %0, x0, m;\n\t"
-        "addc.u32 %1, x1, 0;\n\t}"
+        GL_REDUCE_TAIL("%6", "0")
         : "=r"(r0), "=r"(r1)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(c0), "r"(c1));
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(GL_EPS32_C), "r"(c0), "r"(c1));
     return ((u64)r1 << 32) | r0;
 }
 
-// a * b (mod p), lazy in, lazy out
+// a * b (mod p), lazy in, lazy out: 5 IMAD.WIDE + 11 other instructions
 __device__ __forceinline__ u64 gl_mul_lazy(u64 a, u64 b) {
     u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32), r0, r1;
-    asm("{\n\t.reg .u32 x0,x1,x2,x3,t0,t1,t2,m,e0,e1;\n\t.reg .u64 w0,w3,t,e;\n\t"
+    asm("{\n\t.reg .u32 x0,x1,x2,x3,t0,t1,t2,r2,n,eh;\n\t.reg .u64 w0,w3,t;\n\t"
         "mul.wide.u32 w0, %2, %4;\n\t"
         "mul.wide.u32 w3, %3, %5;\n\t"
         "mul.wide.u32 t, %2, %5;\n\t"
@@ -127,20 +124,9 @@ __device__ __forceinline__ u64 gl_mul_lazy(u64 a, u64 b) {
         "add.cc.u32 x1, x1, t0;\n\t"
         "addc.cc.u32 x2, x2, t1;\n\t"
         "addc.u32 x3, x3, t2;\n\t"
-        "sub.cc.u32 x0, x0, x3;\n\t"
-        "subc.cc.u32 x1, x1, 0;\n\t"
-        "subc.u32 m, 0, 0;\n\t"
-        "sub.cc.u32 x0, x0, m;\n\t"
-        "subc.u32 x1, x1, 0;\n\t"
-        GL_EPS_TIMES("x2")
-        "add.cc.u32 x0, x0, e0;\n\t"
-        "addc.cc.u32 x1, x1, e1;\n\t"
-        "addc.u32 t2, 0, 0;\n\t"
-        "sub.u32 m, 0, t2;\n\t"
-        "add.cc.u32 %0, x0, m;\n\t"
-        "addc.u32 %1, x1, 0;\n\t}"
+        GL_REDUCE_TAIL("%6", "0")
         : "=r"(r0), "=r"(r1)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(GL_EPS32_C));
     return ((u64)r1 << 32) | r0;
 }
 
@@ -221,24 +207,18 @@ __device__ __forceinline__ void gl_acc_mac(gl_acc160 &A, u64 a, u64 b) {
         : "+r"(A.x0), "+r"(A.x1), "+r"(A.x2), "+r"(A.x3), "+r"(A.x4)
         : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
 }
-// x0 + x1 2^32 + x2 2^64 + x3 2^96 + x4 2^128 == (x1:x0) - (x4:x3) + x2 * EPS   (2^128 == -2^32)
+// x0 + x1 2^32 + x2 2^64 + x3 2^96 + x4 2^128 == (x1:x0) - (x4:x3) + x2 * EPS   (2^128 == -2^32).
+// x4 < 16 (at most 16 products), so (x4:x3) < 2^36 and the single signed correction is still exact.
 __device__ __forceinline__ u64 gl_acc_reduce(const gl_acc160 &A) {
     u32 r0, r1;
-    asm("{\n\t.reg .u32 x0,x1,m,t2,e0,e1;\n\t.reg .u64 e;\n\t"
-        "sub.cc.u32 x0, %2, %5;\n\t"
-        "subc.cc.u32 x1, %3, %6;\n\t"
-        "subc.u32 m, 0, 0;\n\t"
-        "sub.cc.u32 x0, x0, m;\n\t"
-        "subc.u32 x1, x1, 0;\n\t"
-        GL_EPS_TIMES("%4")
-        "add.cc.u32 x0, x0, e0;\n\t"
-        "addc.cc.u32 x1, x1, e1;\n\t"
-        "addc.u32 t2, 0, 0;\n\t"
-        "sub.u32 m, 0, t2;\n\t"
-        "add.cc.u32 %0, x0, m;\n\t"
-        "addc.u32 %1, x1, 0;\n\t}"
+    asm("{\n\t.reg .u32 x0,x1,x2,x3,r2,n,eh;\n\t"
+        "mov.u32 x0, %2;\n\t"
+        "mov.u32 x1, %3;\n\t"
+        "mov.u32 x2, %4;\n\t"
+        "mov.u32 x3, %5;\n\t"
+        GL_REDUCE_TAIL("%7", "%6")
         : "=r"(r0), "=r"(r1)
-        : "r"(A.x0), "r"(A.x1), "r"(A.x2), "r"(A.x3), "r"(A.x4));
+        : "r"(A.x0), "r"(A.x1), "r"(A.x2), "r"(A.x3), "r"(A.x4), "r"(GL_EPS32_C));
     return ((u64)r1 << 32) | r0;
 }
 

@@ -1,5 +1,5 @@
 // poseidon_bench.cu -- register-resident Poseidon throughput (no memory traffic) + KAT check.
-// Build variants with -DPOSEIDON_MDS_FFT=0/1 -DGL_EPS_ALU=0/1; run on the GPU box:
+// Build variants with -DPOSEIDON_MDS_FFT=0/1; run on the GPU box:
 //   nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o pb poseidon_bench.cu && ./pb
 #include <cstdio>
 #include <cstdlib>
@@ -68,7 +68,7 @@ int main(int argc, char **argv) {
         cudaEventElapsedTime(&ms, e0, e1);
         if (ms < best) best = ms;
     }
-    printf("MDS_FFT=%d EPS_ALU=%d : %.3f ms for %zu perms -> %.3f Gperm/s  (%s)\n", POSEIDON_MDS_FFT, GL_EPS_ALU, best,
+    printf("MDS_FFT=%d : %.3f ms for %zu perms -> %.3f Gperm/s  (%s)\n", POSEIDON_MDS_FFT, best,
            n * iters, n * (double)iters / best / 1e6, cudaGetErrorString(cudaGetLastError()));
     return bad != 0;
 }
