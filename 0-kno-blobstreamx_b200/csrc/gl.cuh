@@ -69,7 +69,7 @@ static __constant__ u32 GL_EPS32_C = 0xFFFFFFFFu;
 //   subtraction meet in r2 in {-1, 0, 1}; one signed correction r2 * EPS = (r2 >> 31 : -r2) finishes.  It
 //   cannot wrap again: r2 = 1 means the low 64 bits are < 2^64 - 2^32, r2 = -1 means they are >= 2^64 - 2^32
 //   (x3 < 2^32).  11 SASS instructions after the four products (the two-fix form took 15).
-#define GL_REDUCE_TAIL(EPS_OPERAND, SUB_HI)                  \
+#define GL_REDUCE_TAIL_WIDE(EPS_OPERAND, SUB_HI)             \
     "mad.lo.cc.u32 x0, x2, " EPS_OPERAND ", x0;\n\t"         \
     "madc.hi.cc.u32 x1, x2, " EPS_OPERAND ", x1;\n\t"        \
     "addc.u32 r2, 0, 0;\n\t"                                 \
@@ -80,6 +80,31 @@ static __constant__ u32 GL_EPS32_C = 0xFFFFFFFFu;
     "shr.s32 eh, r2, 31;\n\t"                                \
     "add.cc.u32 %0, x0, n;\n\t"                              \
     "addc.u32 %1, x1, eh;\n\t}"
+// Same tail with x2 * EPS = (x2 << 32) - x2 formed by two ALU subtractions instead of the fifth IMAD.WIDE:
+// +3 ALU instructions, -1 quarter-rate FMA-heavy instruction.  Pays when the FMA-heavy pipe is the busier one
+// (Poseidon after the MDS/accumulator rewrites: 86 % vs 57 % ALU).  Measured: 1.10 -> 1.02 Gperm/s, because the
+// kernel then issues 14 % more instructions at an unchanged ~0.6 IPC -- kept only as a documented dead end.
+#define GL_REDUCE_TAIL_ALU(EPS_OPERAND, SUB_HI)              \
+    "sub.cc.u32 n, 0, x2;\n\t"                               \
+    "subc.u32 eh, x2, 0;\n\t"                                \
+    "add.cc.u32 x0, x0, n;\n\t"                              \
+    "addc.cc.u32 x1, x1, eh;\n\t"                            \
+    "addc.u32 r2, 0, 0;\n\t"                                 \
+    "sub.cc.u32 x0, x0, x3;\n\t"                             \
+    "subc.cc.u32 x1, x1, " SUB_HI ";\n\t"                    \
+    "subc.u32 r2, r2, 0;\n\t"                                \
+    "sub.u32 n, 0, r2;\n\t"                                  \
+    "shr.s32 eh, r2, 31;\n\t"                                \
+    "add.cc.u32 %0, x0, n;\n\t"                              \
+    "addc.u32 %1, x1, eh;\n\t}"
+#ifndef GL_MUL_TAIL_ALU
+#define GL_MUL_TAIL_ALU 0
+#endif
+#if GL_MUL_TAIL_ALU
+#define GL_REDUCE_TAIL(E, S) GL_REDUCE_TAIL_ALU(E, S)
+#else
+#define GL_REDUCE_TAIL(E, S) GL_REDUCE_TAIL_WIDE(E, S)
+#endif
 
 // 128-bit product + 64-bit addend, reduced:  a * b + c  (mod p), all lazy.  c is added to the partial
 // products a0*b0 and a0*b1 (neither sum can overflow 64 bits), so the addend costs no carry handling later.
@@ -216,10 +241,51 @@ __device__ __forceinline__ u64 gl_acc_reduce(const gl_acc160 &A) {
         "mov.u32 x1, %3;\n\t"
         "mov.u32 x2, %4;\n\t"
         "mov.u32 x3, %5;\n\t"
-        GL_REDUCE_TAIL("%7", "%6")
+        GL_REDUCE_TAIL_WIDE("%7", "%6")
         : "=r"(r0), "=r"(r1)
         : "r"(A.x0), "r"(A.x1), "r"(A.x2), "r"(A.x3), "r"(A.x4), "r"(GL_EPS32_C));
     return ((u64)r1 << 32) | r0;
+}
+
+// Column accumulators for dot products: the partial products of weight 1, 2^32 and 2^64 are summed in
+// three separate 64-bit accumulators by the IMAD.WIDE addend itself, and each carry-out is counted in a
+// third word (one IADD3.X).  A term costs 4 IMAD.WIDE + 4 carry counts = 8 instructions (the five-limb
+// form above: 13); the columns are lined up once per dot product in gl_acc3_reduce.
+struct gl_acc3 {
+    u32 l0, h0, c0, l1, h1, c1, l2, h2, c2;
+};
+__device__ __forceinline__ gl_acc3 gl_acc3_zero() { return {0, 0, 0, 0, 0, 0, 0, 0, 0}; }
+__device__ __forceinline__ void gl_acc3_mac(gl_acc3 &A, u64 a, u64 b) {
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32);
+    asm("mad.lo.cc.u32 %0, %9, %11, %0;\n\t"
+        "madc.hi.cc.u32 %1, %9, %11, %1;\n\t"
+        "addc.u32 %2, %2, 0;\n\t"
+        "mad.lo.cc.u32 %3, %9, %12, %3;\n\t"
+        "madc.hi.cc.u32 %4, %9, %12, %4;\n\t"
+        "addc.u32 %5, %5, 0;\n\t"
+        "mad.lo.cc.u32 %3, %10, %11, %3;\n\t"
+        "madc.hi.cc.u32 %4, %10, %11, %4;\n\t"
+        "addc.u32 %5, %5, 0;\n\t"
+        "mad.lo.cc.u32 %6, %10, %12, %6;\n\t"
+        "madc.hi.cc.u32 %7, %10, %12, %7;\n\t"
+        "addc.u32 %8, %8, 0;"
+        : "+r"(A.l0), "+r"(A.h0), "+r"(A.c0), "+r"(A.l1), "+r"(A.h1), "+r"(A.c1), "+r"(A.l2), "+r"(A.h2), "+r"(A.c2)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+}
+// (c0:h0:l0) + (c1:h1:l1) 2^32 + (c2:h2:l2) 2^64 -> five limbs -> lazy u64 (at most 16 terms: limb 4 < 16)
+__device__ __forceinline__ u64 gl_acc3_reduce(const gl_acc3 &A) {
+    gl_acc160 X;
+    asm("add.cc.u32 %0, %5, %7;\n\t"          // x1 = h0 + l1
+        "addc.cc.u32 %1, %6, %8;\n\t"         // x2 = c0 + h1 + carry
+        "addc.cc.u32 %2, %9, 0;\n\t"          // x3 = c1 + carry
+        "addc.u32 %3, 0, 0;\n\t"              // x4 = carry
+        "add.cc.u32 %1, %1, %10;\n\t"         // x2 += l2
+        "addc.cc.u32 %2, %2, %11;\n\t"        // x3 += h2
+        "addc.u32 %3, %3, %12;"                // x4 += c2
+        : "=&r"(X.x1), "=&r"(X.x2), "=&r"(X.x3), "=&r"(X.x4)
+        : "r"(0), "r"(A.h0), "r"(A.c0), "r"(A.l1), "r"(A.h1), "r"(A.c1), "r"(A.l2), "r"(A.h2), "r"(A.c2));
+    X.x0 = A.l0;
+    return gl_acc_reduce(X);
 }
 
 // small-constant multiply: c < 2^32, a canonical

@@ -144,10 +144,10 @@ __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
             u64 t[11];
 #pragma unroll 1
             for (int r = 0; r < 11; r++) {
-                gl_acc160 A = {0, 0, 0, 0, 0};
+                gl_acc3 A = gl_acc3_zero();
 #pragma unroll
-                for (int c = 0; c < 11; c++) gl_acc_mac(A, s[1 + c], POSEIDON_FAST_INIT[11 * r + c]);
-                t[r] = gl_acc_reduce(A);
+                for (int c = 0; c < 11; c++) gl_acc3_mac(A, s[1 + c], POSEIDON_FAST_INIT[11 * r + c]);
+                t[r] = gl_acc3_reduce(A);
             }
 #pragma unroll
             for (int r = 0; r < 11; r++) s[1 + r] = t[r];
@@ -155,13 +155,13 @@ __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
             for (int p = 0; p < 22; p++) {
                 u64 s0 = gl_add_lazy_canon(poseidon_sbox(s[0]), POSEIDON_FAST_K[p]);
                 // d = 25 s0 + V[p] . x[1:]
-                gl_acc160 A = {0, 0, 0, 0, 0};
-                gl_acc_mac(A, s0, 25);
+                gl_acc3 A = gl_acc3_zero();
+                gl_acc3_mac(A, s0, 25);
 #pragma unroll
-                for (int i = 0; i < 11; i++) gl_acc_mac(A, s[1 + i], POSEIDON_FAST_V[11 * p + i]);
+                for (int i = 0; i < 11; i++) gl_acc3_mac(A, s[1 + i], POSEIDON_FAST_V[11 * p + i]);
 #pragma unroll
                 for (int i = 0; i < 11; i++) s[1 + i] = gl_mul_add_lazy(s0, POSEIDON_FAST_W[11 * p + i], s[1 + i]);
-                s[0] = gl_acc_reduce(A);
+                s[0] = gl_acc3_reduce(A);
             }
 #pragma unroll
             for (int i = 0; i < 12; i++) s[i] = gl_add_lazy_canon(s[i], POSEIDON_RC[12 * 26 + i]);
