@@ -273,8 +273,8 @@ int ntt_max_single_pass_log() { return NTT_MAX_A; }
 
 // per-device opt-in to > 48 KB dynamic shared memory; called from bsx_ctx_create
 void ntt_init_device() {
-    cudaFuncSetAttribute(ntt_pass_hi, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024);
-    cudaFuncSetAttribute(ntt_pass_lo, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024);
+    cudaFuncSetAttribute(ntt_pass_hi, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
 }
 
 // stage groups for a 2^bits-point tile transform: the last group (compile-time twiddles) takes up to

@@ -21,6 +21,14 @@ def ctx(pkg):
     c.close()
 
 
+def _add_mod(a, b):
+    """(a + b) mod p on canonical uint64 arrays without leaving uint64."""
+    with np.errstate(over="ignore"):
+        t = a + b
+        wrap = (t < a) | (t >= np.uint64(P))
+        return np.where(wrap, t - np.uint64(P), t)
+
+
 EDGE = [0, 1, 2, P - 1, P - 2, 2**32 - 1, 2**32, 2**32 + 1, 2**63, P - 2**32, 0xFFFFFFFF00000000, 0xFFFFFFFF]
 
 
@@ -57,6 +65,26 @@ def test_ntt_kinds(ctx, oracle, log_n):
     assert all((got[c] == oracle.coset_fft(v[c], 7)).all() for c in range(n_cols))
     got = ctx.ntt(v, "coset_fft", shift=pow(7, 16, P))
     assert (got[1] == oracle.coset_fft(v[1], pow(7, 16, P))).all()
+
+
+@pytest.mark.parametrize("log_n,n_cols", [(13, 9), (16, 8), (14, 17)])
+def test_ntt_many_columns_full_factor_table(ctx, oracle, log_n, n_cols):
+    """>= 8 columns at two-pass sizes take the cached full post-factor table path of pass HI."""
+    v = splitmix_field(300 + log_n, (n_cols, 1 << log_n))
+    for kind, ref in (("fft", oracle.fft), ("ifft", oracle.ifft), ("coset_fft", lambda a: oracle.coset_fft(a, 7))):
+        got = ctx.ntt(v, kind)
+        for c in (0, n_cols // 2, n_cols - 1):
+            assert (got[c] == ref(v[c])).all(), (kind, c)
+
+
+@pytest.mark.parametrize("log_n,n_cols", [(20, 8), (23, 2), (24, 1)])
+def test_ntt_roundtrip_up_to_max_size(ctx, log_n, n_cols):
+    """ifft(fft(x)) == x and coset_fft linearity at sizes the oracle would take minutes for."""
+    v = splitmix_field(900 + log_n, (n_cols, 1 << log_n))
+    assert (ctx.ntt(ctx.ntt(v, "fft"), "ifft") == v).all()
+    w = splitmix_field(901 + log_n, (1, 1 << log_n))
+    a, b, c = ctx.ntt(v[:1], "coset_fft"), ctx.ntt(w, "coset_fft"), ctx.ntt(_add_mod(v[:1], w), "coset_fft")
+    assert (_add_mod(a, b) == c).all()
 
 
 def test_ntt_roundtrip_large(ctx):
