@@ -159,6 +159,11 @@ extern "C" int32_t bsx_ctx_create(int32_t device, bsx_ctx **out) {
         delete ctx;
         return BSX_ERR_CUDA;
     }
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaStreamDestroy(ctx->stream);
+        delete ctx;
+        return BSX_ERR_CUDA;
+    }
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
         unsigned long long thr = ~0ULL;  // keep freed blocks cached: repeated commits reuse them
@@ -201,6 +206,7 @@ extern "C" void bsx_ctx_destroy(bsx_ctx *ctx) {
         bsx_free(ctx, (u64 *)kv.second.second);
     }
     cudaStreamSynchronize(ctx->stream);
+    cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -21,6 +21,7 @@ struct CosetKey {
 struct bsx_ctx {
     int device;
     cudaStream_t stream;
+    cudaStream_t copy_stream;  // host -> device copies of the pipelined from_values path
     char err[512];
     NttTables tables;
     std::map<int, PowTable> pow_tables;

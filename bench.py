@@ -29,6 +29,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries exactly one JSON line
 P = 0xFFFFFFFF00000001
 
 LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT = 20, 135, 3, 4
