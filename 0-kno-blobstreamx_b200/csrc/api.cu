@@ -94,7 +94,7 @@ int bsx_coset_tables(bsx_ctx *ctx, int log_n, int r_log, u64 shift, const u64 **
     bsx_split(log_n, &a, &b);
     int nc = 1 << r_log;
     u64 *hi, *lo;
-    TRY(bsx_alloc(ctx, &hi, (size_t)nc << a));
+    TRY(bsx_alloc(ctx, &hi, (size_t)2 * nc << a));  // natural order, then the same rows bit-reversed
     TRY(bsx_alloc(ctx, &lo, (size_t)nc << b));
     u64 w = gl_host_root(log_n + r_log);
     for (int k = 0; k < nc; k++) {
@@ -102,6 +102,9 @@ int bsx_coset_tables(bsx_ctx *ctx, int log_n, int r_log, u64 shift, const u64 **
         launch_fill_powers(hi + ((size_t)k << a), gl_host_pow(g, (u64)1 << b), 1, (size_t)1 << a, ctx->stream);
         launch_fill_powers(lo + ((size_t)k << b), g, 1, (size_t)1 << b, ctx->stream);
     }
+    // pass HI reads bit-reversed coefficient storage with consecutive lanes on consecutive words; the
+    // bit-reversed copy makes its factor loads contiguous too (the natural table costs 32 sectors per warp)
+    launch_bitrev_copy(hi, (size_t)1 << a, hi + ((size_t)nc << a), (size_t)1 << a, a, nc, ctx->stream);
     CU(ctx, cudaGetLastError());
     ctx->coset_tables[key] = std::make_pair((const u64 *)hi, (const u64 *)lo);
     *pre_hi = hi;

@@ -50,7 +50,8 @@ struct NttPlan {
     int inverse;   // use omega^-1 and scale by n^-1
     int src_bitrev;  // source holds coefficient i at position bitrev(i)
     int n_cosets;  // 1, or 2^rate_bits output cosets (LDE)
-    // coset k pre-factor g_k^i, i = i1 * 2^b + i0: pre_hi[k << a | i1] * pre_lo[k << b | i0]; null = none
+    // coset k pre-factor g_k^i, i = i1 * 2^b + i0: pre_hi[k << a | i1] * pre_lo[k << b | i0]; null = none.
+    // pre_hi is followed by a second copy with every row bit-reversed: pre_hi[(n_cosets + k) << a | bitrev_a(i1)]
     const u64 *pre_hi, *pre_lo;
     PowTable tw;   // powers of omega_N (or its inverse) for the inter-pass twiddle
     u64 scale;     // multiplied into every output (n^-1 for the inverse); 1 = none

@@ -68,6 +68,11 @@ __device__ __forceinline__ int ntt_sm(int j, int p, int pitch) { return j * pitc
 // bits 5.. into the low bits spreads every such walk over all banks.
 __device__ __forceinline__ int ntt_tw_pos(int e) { return e ^ (e >> 5); }
 #define NTT_IO_UNROLL 8
+#ifndef NTT_HI_UNROLL
+#define NTT_HI_UNROLL 4
+#endif
+#define NTT_PRAGMA(x) _Pragma(#x)
+#define NTT_UNROLL(n) NTT_PRAGMA(unroll n)
 
 // One group of RHO DIF stages, starting at stage s0 of a 2^bits-point transform.  A work item owns
 // the 2^RHO points p = ((hi << RHO | m) << lobits) | lo of one column.  Butterfly (m0, m0 + half) of
@@ -145,7 +150,36 @@ __device__ __forceinline__ void load_twiddles(u64 *tws, const u64 *__restrict__ 
         tws[ntt_tw_pos(e)] = __ldg(wtab + ((size_t)e << (NTT_MAX_A - bits)));
 }
 
-// Pass HI: grid (n_cols, 2^b / W); the CTA loops over the 2^r_log cosets of its tile
+#ifdef NTT_PROFILE
+// debug build only (make EXTRA=-DNTT_PROFILE): per-phase SM cycles of pass HI summed over CTAs and cosets
+__device__ unsigned long long ntt_prof[4];
+extern "C" void bsx_debug_ntt_profile(unsigned long long *out, int reset) {
+    cudaMemcpyFromSymbol(out, ntt_prof, sizeof(ntt_prof));
+    if (reset) {
+        unsigned long long z[4] = {0, 0, 0, 0};
+        cudaMemcpyToSymbol(ntt_prof, z, sizeof(z));
+    }
+}
+#define NTT_PROF_MARK(i)                                              \
+    do {                                                              \
+        __syncthreads();                                              \
+        if (threadIdx.x == 0) {                                       \
+            long long t_now = clock64();                              \
+            atomicAdd(&ntt_prof[i], (unsigned long long)(t_now - t_prev)); \
+            t_prev = t_now;                                           \
+        }                                                             \
+    } while (0)
+#else
+#define NTT_PROF_MARK(i)
+#endif
+
+// Pass HI: grid (n_cols, 2^b / W); the CTA loops over the 2^r_log cosets of its tile.
+// The source order, the presence of coset factors and the kind of output factor are template parameters so
+// that the load / store loops are branch-free and their global loads can be issued NTT_HI_UNROLL deep
+// (with the conditions as run-time branches ptxas kept one load in flight per thread and the pass spent
+// 72 % of its time in these two loops).  POST: 0 = none (single pass; optional scale), 1 = two-level
+// inter-pass twiddle, 2 = full post-factor table.
+template <bool SRC_BITREV, bool HAS_PRE, int POST>
 __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
     extern __shared__ u64 sm_all[];
     const int a = P.a, b = P.b, w_log = P.w_log, pitch = P.pitch;
@@ -153,63 +187,135 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
     u64 *tws = sm_all, *sm = sm_all + (R >> 1);
     const int col = blockIdx.x;
     const size_t i0_base = (size_t)blockIdx.y << w_log;
-    const u64 *src = P.src + (size_t)col * P.src_stride;
+    const u64 *__restrict__ src = P.src + (size_t)col * P.src_stride;
     const int n_el = R << w_log;
     const int n_cosets = 1 << P.r_log;
     load_twiddles(tws, P.wtab, a);
+#ifdef NTT_PROFILE
+    long long t_prev = clock64();
+#endif
 
     for (int k = 0; k < n_cosets; k++) {
         const size_t blk = (size_t)bitrev32(k, P.r_log) << P.log_n;
         u64 *dst = P.dst + (size_t)col * P.dst_stride + blk;
-        const bool remap = P.n_dest != 0 && b == 0;
-        for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
-            int i1, j;
-            size_t pos;
-            if (P.src_bitrev) {
-                // natural index i = i1 * S + i0 lives at bitrev_n(i) = bitrev_b(i0) * R + bitrev_a(i1):
-                // W runs of R contiguous words
-                j = e >> a;
-                int q = e & (R - 1);
-                i1 = bitrev32(q, a);
-                pos = ((size_t)bitrev32((u32)(i0_base + j), b) << a) + q;
-            } else {
-                i1 = e >> w_log;
-                j = e & (W - 1);
-                pos = ((size_t)i1 << b) + i0_base + j;
+        const bool remap = P.n_dest != 0 && POST == 0;
+        // bit-reversed source: index the bit-reversed copy of the factor row by q (contiguous across lanes)
+        const u64 *__restrict__ pre_hi = HAS_PRE ? P.pre_hi + ((size_t)(SRC_BITREV ? n_cosets + k : k) << a) : nullptr;
+        const u64 *__restrict__ pre_lo = HAS_PRE ? P.pre_lo + ((size_t)k << b) + i0_base : nullptr;
+        // LDE from bit-reversed coefficients (the from_values path): column j of the tile is one contiguous run
+        // of R words, and the coset factor depends only on the position q in the run.  A thread owns q = tid +
+        // t * blockDim (t < R / blockDim <= 4): factors and shared-memory offsets are computed once per coset and
+        // reused for all W columns, and each column costs one coalesced load, one multiply and one store per word.
+        const bool run_path = SRC_BITREV && HAS_PRE && POST == 2 && R >= (int)blockDim.x && R <= 4 * (int)blockDim.x;
+        if (run_path) {
+            const int qt = R / (int)blockDim.x;
+            u64 fq[4];
+            int sw[4];
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const int q = threadIdx.x + (t < qt ? t : 0) * blockDim.x;
+                fq[t] = __ldg(pre_hi + q);
+                sw[t] = ntt_swz(bitrev32(q, a));
             }
-            u64 v = src[pos];
-            if (P.pre_hi) {
-                u64 f = __ldg(P.pre_hi + ((size_t)k << a) + i1);
-                if (!P.post_full) f = gl_mul_lazy(f, __ldg(P.pre_lo + ((size_t)k << b) + i0_base + j));
-                v = gl_mul_c(v, f);
-            } else {
-                v = gl_canon_fast(v);
+            for (int j = 0; j < W; j += 2) {
+                const u64 *__restrict__ row0 = src + ((size_t)bitrev32((u32)(i0_base + j), b) << a) + threadIdx.x;
+                const u64 *__restrict__ row1 = src + ((size_t)bitrev32((u32)(i0_base + j + 1), b) << a) + threadIdx.x;
+                u64 v0[4], v1[4];
+#pragma unroll
+                for (int t = 0; t < 4; t++)
+                    if (t < qt) {
+                        v0[t] = row0[t * blockDim.x];
+                        v1[t] = row1[t * blockDim.x];
+                    }
+#pragma unroll
+                for (int t = 0; t < 4; t++)
+                    if (t < qt) {
+                        sm[j * pitch + sw[t]] = gl_mul_c(v0[t], fq[t]);
+                        sm[(j + 1) * pitch + sw[t]] = gl_mul_c(v1[t], fq[t]);
+                    }
             }
-            sm[ntt_sm(j, i1, pitch)] = v;
+        } else
+        for (int e0 = threadIdx.x; e0 < n_el; e0 += blockDim.x * NTT_HI_UNROLL) {
+            u64 v[NTT_HI_UNROLL], f[NTT_HI_UNROLL];
+            int si[NTT_HI_UNROLL];
+#pragma unroll
+            for (int u = 0; u < NTT_HI_UNROLL; u++) {
+                const int e_raw = e0 + u * blockDim.x;
+                const bool ok = e_raw < n_el;
+                const int e = ok ? e_raw : e0;  // out-of-range slots re-read a valid word and are not stored
+                int i1, j;
+                size_t pos;
+                if (SRC_BITREV) {
+                    // natural index i = i1 * S + i0 lives at bitrev_n(i) = bitrev_b(i0) * R + bitrev_a(i1):
+                    // W runs of R contiguous words
+                    j = e >> a;
+                    int q = e & (R - 1);
+                    i1 = bitrev32(q, a);
+                    pos = ((size_t)bitrev32((u32)(i0_base + j), b) << a) + q;
+                } else {
+                    i1 = e >> w_log;
+                    j = e & (W - 1);
+                    pos = ((size_t)i1 << b) + i0_base + j;
+                }
+                v[u] = src[pos];
+                if (HAS_PRE) {
+                    f[u] = __ldg(pre_hi + (SRC_BITREV ? (e & (R - 1)) : i1));
+                    if (POST != 2) f[u] = gl_mul_lazy(f[u], __ldg(pre_lo + j));
+                }
+                si[u] = ok ? ntt_sm(j, i1, pitch) : -1;
+            }
+#pragma unroll
+            for (int u = 0; u < NTT_HI_UNROLL; u++)
+                if (si[u] >= 0) sm[si[u]] = HAS_PRE ? gl_mul_c(v[u], f[u]) : gl_canon_fast(v[u]);
         }
         __syncthreads();
+        NTT_PROF_MARK(0);
         dif_tile(sm, tws, a, w_log, pitch, P.groups);
-        const u64 *post = P.post_full ? P.post_full + ((size_t)k << P.log_n) : nullptr;
-        for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
-            int p = e >> w_log, j = e & (W - 1);
-            u64 v = sm[ntt_sm(j, p, pitch)];
-            size_t o = ((size_t)p << b) + i0_base + j;
-            if (post) {
-                v = gl_mul_c(v, __ldg(post + o));
-            } else if (b > 0) {
-                // position p holds Y[k1], k1 = bitrev_a(p); twiddle omega_N^(i0 * k1)
-                u64 ex = (u64)(i0_base + j) * bitrev32(p, a);
-                u64 t = __ldg(P.tw_lo + (ex & 4095));
-                if (ex >> 12) t = gl_mul_lazy(t, __ldg(P.tw_hi + (ex >> 12)));
-                v = gl_mul_c(v, t);
-            } else if (P.scale != 1) {
-                v = gl_mul_c(v, P.scale);
+        NTT_PROF_MARK(1);
+        const u64 *__restrict__ post = POST == 2 ? P.post_full + ((size_t)k << P.log_n) + i0_base : nullptr;
+        for (int e0 = threadIdx.x; e0 < n_el; e0 += blockDim.x * NTT_HI_UNROLL) {
+            u64 v[NTT_HI_UNROLL], f[NTT_HI_UNROLL];
+            size_t oo[NTT_HI_UNROLL];
+#pragma unroll
+            for (int u = 0; u < NTT_HI_UNROLL; u++) {
+                const int e_raw = e0 + u * blockDim.x;
+                const int e = e_raw < n_el ? e_raw : e0;
+                const int p = e >> w_log, j = e & (W - 1);
+                v[u] = sm[ntt_sm(j, p, pitch)];
+                oo[u] = ((size_t)p << b) + j;
+                if (POST == 2) {
+                    f[u] = __ldg(post + oo[u]);
+                } else if (POST == 1) {
+                    // position p holds Y[k1], k1 = bitrev_a(p); twiddle omega_N^(i0 * k1)
+                    u64 ex = (u64)(i0_base + j) * bitrev32(p, a);
+                    f[u] = __ldg(P.tw_lo + (ex & 4095));
+                    if (ex >> 12) f[u] = gl_mul_lazy(f[u], __ldg(P.tw_hi + (ex >> 12)));
+                } else {
+                    f[u] = P.scale;
+                }
             }
-            if (remap) *ntt_out(P, col, blk + o) = v;
-            else dst[o] = v;
+#pragma unroll
+            for (int u = 0; u < NTT_HI_UNROLL; u++) {
+                if (e0 + u * blockDim.x >= n_el) continue;
+                u64 r = (POST != 0 || P.scale != 1) ? gl_mul_c(v[u], f[u]) : v[u];
+                // streaming stores: the LDE output is not read again before the whole pass is over
+                if (POST == 0 && remap) __stcs(ntt_out(P, col, blk + i0_base + oo[u]), r);
+                else __stcs(dst + i0_base + oo[u], r);
+            }
         }
         __syncthreads();
+        NTT_PROF_MARK(2);
     }
+}
+
+typedef void (*ntt_hi_fn)(NttKParams);
+static ntt_hi_fn ntt_hi_variant(bool src_bitrev, bool has_pre, int post) {
+    static const ntt_hi_fn tab[2][2][3] = {
+        {{ntt_pass_hi<false, false, 0>, ntt_pass_hi<false, false, 1>, ntt_pass_hi<false, false, 2>},
+         {ntt_pass_hi<false, true, 0>, ntt_pass_hi<false, true, 1>, ntt_pass_hi<false, true, 2>}},
+        {{ntt_pass_hi<true, false, 0>, ntt_pass_hi<true, false, 1>, ntt_pass_hi<true, false, 2>},
+         {ntt_pass_hi<true, true, 0>, ntt_pass_hi<true, true, 1>, ntt_pass_hi<true, true, 2>}}};
+    return tab[src_bitrev ? 1 : 0][has_pre ? 1 : 0][post];
 }
 
 // Pass LO: in place on rows of 2^b contiguous words; tile = 2^w_log rows.  grid (rows / W, n_cols)
@@ -227,7 +333,7 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
 #pragma unroll
         for (int u = 0; u < NTT_IO_UNROLL; u++) {
             const int e = e0 + u * blockDim.x;
-            if (e < n_el) v[u] = base[e];
+            if (e < n_el) v[u] = __ldcs(base + e);
         }
 #pragma unroll
         for (int u = 0; u < NTT_IO_UNROLL; u++) {
@@ -241,8 +347,8 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
     for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
         u64 v = sm[ntt_sm(e >> b, e & (S - 1), pitch)];
         if (scale) v = gl_mul_c(v, P.scale);
-        if (P.n_dest) *ntt_out(P, blockIdx.y, l0 + e) = v;
-        else base[e] = v;
+        if (P.n_dest) __stcs(ntt_out(P, blockIdx.y, l0 + e), v);
+        else __stcs(base + e, v);
     }
 }
 
@@ -273,7 +379,9 @@ int ntt_max_single_pass_log() { return NTT_MAX_A; }
 
 // per-device opt-in to > 48 KB dynamic shared memory; called from bsx_ctx_create
 void ntt_init_device() {
-    cudaFuncSetAttribute(ntt_pass_hi, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    for (int i = 0; i < 12; i++)
+        cudaFuncSetAttribute(ntt_hi_variant(i & 1, (i >> 1) & 1, i >> 2), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             220 * 1024);
     cudaFuncSetAttribute(ntt_pass_lo, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
 }
 
@@ -337,7 +445,8 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         size_t smem = sizeof(u64) * (((size_t)P.pitch << w_log) + ((size_t)1 << plan.a) / 2);
         int threads = NTT_THREADS;
         while (threads > 32 && threads > (int)(n_el >> 1)) threads >>= 1;
-        BSX_COUNT_LAUNCH(); ntt_pass_hi<<<grid, threads, smem, st>>>(P);
+        const int post = plan.b == 0 ? 0 : (P.post_full ? 2 : 1);
+        BSX_COUNT_LAUNCH(); ntt_hi_variant(plan.src_bitrev != 0, plan.pre_hi != nullptr, post)<<<grid, threads, smem, st>>>(P);
     }
     if (plan.b > 0) {
         size_t rows = ((size_t)plan.n_cosets << plan.log_n) >> plan.b;  // per column
