@@ -10,24 +10,39 @@ static inline size_t n_digest_words(int log_leaves, int cap_height) {
 }
 
 // ------------------------------------------------------------------------------------ MerkleTree
-int bsx_tree_build(bsx_tree *t, cudaEvent_t ev_after_leaf_hash) {
+int bsx_tree_alloc(bsx_tree *t) {
     bsx_ctx *ctx = t->ctx;
-    const size_t n = (size_t)1 << t->log_leaves;
-    const size_t cap_words = (size_t)4 << t->cap_height;
     t->digests = nullptr;
     t->cap_dev = nullptr;
-    TRY(bsx_alloc(ctx, &t->cap_dev, cap_words));
+    TRY(bsx_alloc(ctx, &t->cap_dev, (size_t)4 << t->cap_height));
     TRY(bsx_alloc(ctx, &t->digests, n_digest_words(t->log_leaves, t->cap_height)));
+    return BSX_OK;
+}
+
+// digests of the leaves [first, first + count) on stream st (the commit hashes finished LDE blocks on a second
+// stream while the next block is still being transformed)
+void bsx_tree_hash_leaves(bsx_tree *t, size_t first, size_t count, cudaStream_t st) {
     // cap_height == log2(leaves): the leaf digests are the cap (merkle_tree.rs fill_digests_buf)
     u64 *leaf_digests = t->cap_height == t->log_leaves ? t->cap_dev : t->digests;
-    launch_leaf_hash(t->leaves, t->col_stride, t->leaf_len, n, leaf_digests, ctx->stream);
-    if (ev_after_leaf_hash) cudaEventRecord(ev_after_leaf_hash, ctx->stream);
+    launch_leaf_hash(t->leaves + first, t->col_stride, t->leaf_len, count, leaf_digests + 4 * first, st);
+}
+
+int bsx_tree_finish(bsx_tree *t) {
+    bsx_ctx *ctx = t->ctx;
+    const size_t cap_words = (size_t)4 << t->cap_height;
     launch_merkle_tree(t->digests, t->cap_dev, t->log_leaves, t->cap_height, ctx->stream);
     CU(ctx, cudaGetLastError());
     t->cap_host.resize(cap_words);
     CU(ctx, cudaMemcpyAsync(t->cap_host.data(), t->cap_dev, cap_words * sizeof(u64), cudaMemcpyDeviceToHost,
                             ctx->stream));
     return BSX_OK;
+}
+
+int bsx_tree_build(bsx_tree *t, cudaEvent_t ev_after_leaf_hash) {
+    TRY(bsx_tree_alloc(t));
+    bsx_tree_hash_leaves(t, 0, (size_t)1 << t->log_leaves, t->ctx->stream);
+    if (ev_after_leaf_hash) cudaEventRecord(ev_after_leaf_hash, t->ctx->stream);
+    return bsx_tree_finish(t);
 }
 
 void bsx_tree_release(bsx_tree *t) {
@@ -231,28 +246,35 @@ struct PhaseTimer {
 // (api_shard.cu), where `dests` redirects the final LDE words to the owning ranks' row slabs.
 // coeffs: n_cols x 2^log_n in place (left bit-reversed after the inverse transform);
 // lde: n_cols columns of stride lde_stride (the result, or only the inter-pass scratch when dests is set).
-int bsx_commit_transforms(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols, int rate_bits, bool input_is_coeffs,
-                          u64 *lde, size_t lde_stride, const BsxDests *dests, cudaEvent_t ev_after_ifft) {
+int bsx_commit_ifft(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols) {
     const size_t n = (size_t)1 << log_n;
     NttPlan plan;
     plan.n_dest = 0;
     plan.log_n = log_n;
     bsx_split(log_n, &plan.a, &plan.b);
-    if (!input_is_coeffs) {
-        // PolynomialValues::ifft per column, in place; result is stored bit-reversed
-        plan.inverse = 1;
-        plan.src_bitrev = 0;
-        plan.n_cosets = 1;
-        plan.pre_hi = plan.pre_lo = nullptr;
-        TRY(bsx_pow_table(ctx, log_n, 1, &plan.tw));
-        plan.scale = gl_host_inv((u64)n % GL_P);
-        TRY(bsx_post_table(ctx, &plan, 0, n_cols));
-        launch_ntt(ctx->tables, plan, coeffs, n, coeffs, n, n_cols, ctx->stream);
-    }
-    if (ev_after_ifft) cudaEventRecord(ev_after_ifft, ctx->stream);
-    // lde_values: zero-pad + coset FFT(shift = 7) == 2^rate_bits coset transforms of size n
+    // PolynomialValues::ifft per column, in place; result is stored bit-reversed
+    plan.inverse = 1;
+    plan.src_bitrev = 0;
+    plan.n_cosets = 1;
+    plan.pre_hi = plan.pre_lo = nullptr;
+    TRY(bsx_pow_table(ctx, log_n, 1, &plan.tw));
+    plan.scale = gl_host_inv((u64)n % GL_P);
+    TRY(bsx_post_table(ctx, &plan, 0, n_cols));
+    launch_ntt(ctx->tables, plan, coeffs, n, coeffs, n, n_cols, ctx->stream);
+    CU(ctx, cudaGetLastError());
+    return BSX_OK;
+}
+
+// lde_values: zero-pad + coset FFT(shift = 7) == 2^rate_bits coset transforms of size n
+int bsx_commit_lde(bsx_ctx *ctx, const u64 *coeffs, bool coeffs_bitrev, int log_n, int n_cols, int rate_bits, u64 *lde,
+                   size_t lde_stride, const BsxDests *dests) {
+    const size_t n = (size_t)1 << log_n;
+    NttPlan plan;
+    plan.n_dest = 0;
+    plan.log_n = log_n;
+    bsx_split(log_n, &plan.a, &plan.b);
     plan.inverse = 0;
-    plan.src_bitrev = input_is_coeffs ? 0 : 1;
+    plan.src_bitrev = coeffs_bitrev ? 1 : 0;
     plan.n_cosets = 1 << rate_bits;
     TRY(bsx_coset_tables(ctx, log_n, rate_bits, 7, &plan.pre_hi, &plan.pre_lo));
     TRY(bsx_pow_table(ctx, log_n, 0, &plan.tw));
@@ -266,6 +288,13 @@ int bsx_commit_transforms(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols, int 
     launch_ntt(ctx->tables, plan, coeffs, n, lde, lde_stride, n_cols, ctx->stream);
     CU(ctx, cudaGetLastError());
     return BSX_OK;
+}
+
+int bsx_commit_transforms(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols, int rate_bits, bool input_is_coeffs,
+                          u64 *lde, size_t lde_stride, const BsxDests *dests, cudaEvent_t ev_after_ifft) {
+    if (!input_is_coeffs) TRY(bsx_commit_ifft(ctx, coeffs, log_n, n_cols));
+    if (ev_after_ifft) cudaEventRecord(ev_after_ifft, ctx->stream);
+    return bsx_commit_lde(ctx, coeffs, !input_is_coeffs, log_n, n_cols, rate_bits, lde, lde_stride, dests);
 }
 
 static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n_cols, int rate_bits, int cap_height,
@@ -306,6 +335,23 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
         pt.mark(0, ctx->stream);
         if ((rc = bsx_alloc(ctx, &bt->coeffs, n * n_cols))) break;
         if ((rc = bsx_alloc(ctx, &bt->lde, nb * (size_t)(n_cols + n_salt)))) break;
+        // salt columns first: nothing below depends on them except the leaf hashing
+        if (n_salt) {
+            u64 *dst = bt->lde + nb * (size_t)n_cols;
+            if (salt) {
+                u64 *tmp = nullptr;
+                const u64 *src = salt;
+                if (mem != BSX_DEVICE) {
+                    if ((rc = bsx_alloc(ctx, &tmp, nb * n_salt))) break;
+                    if ((rc = bsx_copy_in(ctx, tmp, salt, nb * n_salt, mem))) break;
+                    src = tmp;
+                }
+                launch_bitrev_copy(src, nb, dst, nb, log_nb, n_salt, ctx->stream);
+                bsx_free(ctx, tmp);
+            } else {
+                launch_fill_random(dst, nb * n_salt, 0x5A17C0DEULL ^ (u64)(uintptr_t)bt, ctx->stream);
+            }
+        }
         if (mem == BSX_HOST && n_cols >= 16 && log_n >= 13) {
             // Host witness: the copy is pipelined with the transforms in column chunks (copy engine and SMs
             // overlap; at the headline 20 ms of PCIe time hide behind 36 ms of NTT).  Chunks keep >= 8 columns
@@ -354,22 +400,6 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
                 break;
         }
         bt->coeffs_bitrev = !input_is_coeffs;
-        if (n_salt) {
-            u64 *dst = bt->lde + nb * (size_t)n_cols;
-            if (salt) {
-                u64 *tmp = nullptr;
-                const u64 *src = salt;
-                if (mem != BSX_DEVICE) {
-                    if ((rc = bsx_alloc(ctx, &tmp, nb * n_salt))) break;
-                    if ((rc = bsx_copy_in(ctx, tmp, salt, nb * n_salt, mem))) break;
-                    src = tmp;
-                }
-                launch_bitrev_copy(src, nb, dst, nb, log_nb, n_salt, ctx->stream);
-                bsx_free(ctx, tmp);
-            } else {
-                launch_fill_random(dst, nb * n_salt, 0x5A17C0DEULL ^ (u64)(uintptr_t)bt, ctx->stream);
-            }
-        }
         if (cudaGetLastError() != cudaSuccess) {
             rc = bsx_fail(ctx, BSX_ERR_CUDA, "NTT launch failed");
             break;

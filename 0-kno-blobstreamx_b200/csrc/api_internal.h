@@ -72,6 +72,13 @@ struct BsxDests {
 int bsx_commit_transforms(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols, int rate_bits, bool input_is_coeffs,
                           u64 *lde, size_t lde_stride, const BsxDests *dests, cudaEvent_t ev_after_ifft);
 
+int bsx_commit_ifft(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols);
+int bsx_commit_lde(bsx_ctx *ctx, const u64 *coeffs, bool coeffs_bitrev, int log_n, int n_cols, int rate_bits, u64 *lde,
+                   size_t lde_stride, const BsxDests *dests);
+int bsx_tree_alloc(bsx_tree *t);
+void bsx_tree_hash_leaves(bsx_tree *t, size_t first, size_t count, cudaStream_t st);
+int bsx_tree_finish(bsx_tree *t);
+
 // builds digests + cap for a tree whose leaves/shape fields are set; allocates digests/cap_dev
 int bsx_tree_build(bsx_tree *t, cudaEvent_t ev_after_leaf_hash);
 void bsx_tree_release(bsx_tree *t);
