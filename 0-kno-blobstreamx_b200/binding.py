@@ -13,7 +13,7 @@ EXPORTED_SYMBOLS = [
     "bsx_version", "bsx_device_count", "bsx_launch_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
     "bsx_ctx_sync", "bsx_batch_from_values", "bsx_batch_from_coeffs", "bsx_batch_free", "bsx_batch_cap",
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
-    "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
+    "bsx_batch_eval_ext", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
     "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
     "bsx_challenger_get", "bsx_fri_proof_words", "bsx_fri_prove_openings", "bsx_fri_proof", "bsx_fri_final_poly",
@@ -70,6 +70,7 @@ def lib():
         "bsx_batch_get_lde_values": (i32, [vp, u64, u64, vp]),
         "bsx_batch_coeffs": (i32, [vp, vp, i32]),
         "bsx_batch_export": (i32, [vp, vp, vp, vp]),
+        "bsx_batch_eval_ext": (i32, [vp, i32, i32, vp, i32, vp]),
         "bsx_batch_shape": (i32, [vp] + [C.POINTER(i32)] * 5),
         "bsx_batch_lde_device": (vp, [vp]),
         "bsx_batch_digests_device": (vp, [vp]),
@@ -333,6 +334,19 @@ class PolynomialBatch:
         self.ctx.check(lib().bsx_batch_get_lde_values(self._h, C.c_uint64(int(index)), C.c_uint64(int(step)),
                                                       _ptr(out)))
         return out
+
+    def eval_commitment(self, points, col_begin=0, n_cols=None):
+        """The `eval_commitment(z, c)` closure of plonk/proof.rs `OpeningSet::new`: every polynomial of the batch
+        evaluated at extension points.  points: (k, 2) or (2,); returns (k, n_cols, 2) or (n_cols, 2)."""
+        pts = np.ascontiguousarray(points, dtype=np.uint64)
+        single = pts.ndim == 1
+        pts = pts.reshape(-1, 2)
+        if n_cols is None:
+            n_cols = self.shape()["n_cols"] - col_begin
+        out = np.zeros((pts.shape[0], max(n_cols, 0), 2), dtype=np.uint64)
+        self.ctx.check(lib().bsx_batch_eval_ext(self._h, int(col_begin), int(n_cols), _ptr(pts), pts.shape[0],
+                                                _ptr(out)))
+        return out[0] if single else out
 
     def export(self, coeffs=True, leaves=True, digests=True):
         sh = self.shape()

@@ -414,3 +414,32 @@ extern "C" int32_t bsx_fri_proof(bsx_ctx *ctx, bsx_batch *const *oracles, int32_
     if (!lde_coeffs_host) return BSX_ERR_INVALID_ARG;
     return fri_run(ctx, oracles, n_oracles, nullptr, (const u64 *)lde_coeffs_host, challenger, params, (u64 *)proof_host);
 }
+
+// ------------------------------------------------------------------------------------ opening set
+extern "C" int32_t bsx_batch_eval_ext(bsx_batch *b, int32_t col_begin, int32_t n_cols, const uint64_t *points_host,
+                                      int32_t n_points, uint64_t *out_host) {
+    if (!b) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = b->ctx;
+    if (col_begin < 0 || n_cols < 0 || col_begin + n_cols > b->n_cols)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "polynomial range %d..%d outside the batch (%d polynomials)", col_begin,
+                        col_begin + n_cols, b->n_cols);
+    if (n_points < 0 || (n_points > 0 && !points_host) || (n_points > 0 && n_cols > 0 && !out_host))
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "null points / output");
+    if (n_points == 0 || n_cols == 0) return BSX_OK;
+    CU(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)1 << b->log_n, n_out = 2 * (size_t)n_points * n_cols;
+    u64 *pts, *work, *out;
+    TRY(bsx_alloc(ctx, &pts, 2 * (size_t)n_points));
+    TRY(bsx_alloc(ctx, &work, eval_workspace_words(b->log_n, n_cols, n_points)));
+    TRY(bsx_alloc(ctx, &out, n_out));
+    TRY(bsx_copy_in(ctx, pts, (const u64 *)points_host, 2 * (size_t)n_points, BSX_HOST));
+    launch_eval_ext(b->coeffs + (size_t)col_begin * n, n, b->log_n, b->coeffs_bitrev, n_cols, pts, n_points, work, out,
+                    ctx->stream);
+    CU(ctx, cudaGetLastError());
+    TRY(bsx_copy_out(ctx, (u64 *)out_host, out, n_out, BSX_HOST));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    bsx_free(ctx, pts);
+    bsx_free(ctx, work);
+    bsx_free(ctx, out);
+    return BSX_OK;
+}

@@ -101,3 +101,9 @@ void launch_fri_query_gather(const u64 *idx, int n_queries, int shift, const u64
 void launch_ext_interleave(const u64 *planar, size_t plane_stride, size_t n, u64 *out, cudaStream_t st);
 void launch_ext_deinterleave(const u64 *in, size_t n, u64 *planar, size_t plane_stride, cudaStream_t st);
 void launch_ext_pow(const u64 *a, u64 k, u64 *out, cudaStream_t st);
+
+// ---------------------------------------------------------------- opening-set evaluation (eval_kernels.cu)
+#define BSX_EVAL_MAX_BITS 64
+size_t eval_workspace_words(int log_n, int n_cols, int n_points);
+void launch_eval_ext(const u64 *coeffs, size_t col_stride, int log_n, bool bitrev, int n_cols, const u64 *points,
+                     int n_points, u64 *work, u64 *out, cudaStream_t st);

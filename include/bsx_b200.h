@@ -214,6 +214,13 @@ int32_t bsx_fri_proof(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles
 int32_t bsx_fri_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
                            const bsx_fri_instance *instance, const uint64_t alpha[2], uint64_t *out_host);
 
+/* Replaces the `eval_commitment` closure of plonk/proof.rs OpeningSet::new: every polynomial
+ * col_begin .. col_begin + n_cols - 1 of the batch (salt columns are not polynomials) evaluated at n_points
+ * extension-field points, `PolynomialCoeffs::to_extension().eval(z)`.  points_host = n_points x [c0, c1];
+ * out_host = [n_points][n_cols][2].  The coefficients are read from HBM once for all points. */
+int32_t bsx_batch_eval_ext(bsx_batch *batch, int32_t col_begin, int32_t n_cols, const uint64_t *points_host,
+                           int32_t n_points, uint64_t *out_host);
+
 /* ---- test hooks -----------------------------------------------------------------------------
  * Poseidon::poseidon on n states (n x 12 words, in place). */
 int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n);
