@@ -548,6 +548,97 @@ extern "C" int32_t bsx_batch_export(bsx_batch *b, uint64_t *coeffs_host, uint64_
     return BSX_OK;
 }
 
+// plonky2's recursive `digests` layout -> level order (inverse of to_plonky2_layout)
+static void from_plonky2_layout(u64 *lv, size_t n, int height, size_t node, const u64 *buf, size_t buf_len) {
+    if (buf_len == 0) return;
+    size_t half = buf_len / 2, off = 0;
+    for (int k = 0; k < height - 1; k++) off += n >> k;
+    memcpy(lv + 4 * (off + 2 * node), buf + 4 * (half - 1), 4 * sizeof(u64));
+    memcpy(lv + 4 * (off + 2 * node + 1), buf + 4 * half, 4 * sizeof(u64));
+    from_plonky2_layout(lv, n, height - 1, 2 * node, buf, half - 1);
+    from_plonky2_layout(lv, n, height - 1, 2 * node + 1, buf + 4 * (half + 1), half - 1);
+}
+
+// A batch restored from its serialised parts (the constants + sigmas commitment stored with the circuit):
+// nothing is recomputed, exactly like upstream's reader.
+extern "C" int32_t bsx_batch_import(bsx_ctx *ctx, const uint64_t *coeffs_host, const uint64_t *leaves_host,
+                                    const uint64_t *digests_host, const uint64_t *cap_host, int32_t log_n,
+                                    int32_t n_cols, int32_t n_salt, int32_t rate_bits, int32_t cap_height,
+                                    bsx_batch **out) {
+    if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    *out = nullptr;
+    if (log_n < 0 || log_n > 24)
+        return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "degree_log=%d outside the supported range [0, 24]", log_n);
+    if (rate_bits < 0 || rate_bits > 8 || log_n + rate_bits > 32)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad rate_bits=%d", rate_bits);
+    if (n_cols < 0 || n_cols > 65535 || (n_salt != 0 && n_salt != BSX_SALT_SIZE))
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad n_cols=%d / n_salt=%d", n_cols, n_salt);
+    const int log_nb = log_n + rate_bits;
+    if (cap_height < 0 || cap_height > log_nb)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "cap_height=%d should be at most log2(leaves.len())=%d",
+                        cap_height, log_nb);
+    const size_t n = (size_t)1 << log_n, nb = (size_t)1 << log_nb, w = (size_t)(n_cols + n_salt);
+    const size_t dig_words = n_digest_words(log_nb, cap_height), cap_words = (size_t)4 << cap_height;
+    if ((n_cols > 0 && !coeffs_host) || (w > 0 && !leaves_host) || (dig_words > 0 && !digests_host) || !cap_host)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "a serialised part is NULL");
+    CU(ctx, cudaSetDevice(ctx->device));
+
+    bsx_batch *bt = new bsx_batch();
+    bt->ctx = ctx;
+    bt->log_n = log_n;
+    bt->n_cols = n_cols;
+    bt->n_salt = n_salt;
+    bt->rate_bits = rate_bits;
+    bt->coeffs = bt->lde = nullptr;
+    bt->coeffs_bitrev = false;
+    bt->tree.ctx = ctx;
+    bt->tree.leaves = nullptr;
+    bt->tree.digests = bt->tree.cap_dev = nullptr;
+    bt->tree.owns_leaves = false;
+    bt->tree.embedded = true;
+    bt->tree.log_leaves = log_nb;
+    bt->tree.leaf_len = (int)w;
+    bt->tree.cap_height = cap_height;
+    bt->tree.col_stride = nb;
+    u64 *tmp = nullptr;
+    int rc = BSX_OK;
+    do {
+        if ((rc = bsx_alloc(ctx, &bt->coeffs, n * n_cols))) break;
+        if ((rc = bsx_alloc(ctx, &bt->lde, nb * w))) break;
+        if ((rc = bsx_tree_alloc(&bt->tree))) break;
+        bt->tree.leaves = bt->lde;
+        if ((rc = bsx_copy_in(ctx, bt->coeffs, (const u64 *)coeffs_host, n * n_cols, BSX_HOST))) break;
+        if (w > 0) {
+            if ((rc = bsx_alloc(ctx, &tmp, nb * w))) break;
+            if ((rc = bsx_copy_in(ctx, tmp, (const u64 *)leaves_host, nb * w, BSX_HOST))) break;
+            launch_transpose(tmp, bt->lde, nb, w, ctx->stream);  // (nb x w) row-major leaves -> column-major LDE
+        }
+        std::vector<u64> lv(dig_words);
+        if (dig_words > 0) {
+            const int height = log_nb - cap_height;
+            const size_t sub = ((size_t)2 << height) - 2;
+            for (size_t c = 0; c < ((size_t)1 << cap_height); c++)
+                from_plonky2_layout(lv.data(), nb, height, c, (const u64 *)digests_host + 4 * c * sub, sub);
+            if ((rc = bsx_copy_in(ctx, bt->tree.digests, lv.data(), dig_words, BSX_HOST))) break;
+        }
+        bt->tree.cap_host.assign((const u64 *)cap_host, (const u64 *)cap_host + cap_words);
+        if ((rc = bsx_copy_in(ctx, bt->tree.cap_dev, bt->tree.cap_host.data(), cap_words, BSX_HOST))) break;
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);  // lv and the caller's buffers may go away now
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) rc = bsx_fail(ctx, BSX_ERR_CUDA, "import failed: %s", cudaGetErrorString(e));
+    } while (0);
+    bsx_free(ctx, tmp);
+    if (rc != BSX_OK) {
+        bsx_tree_release(&bt->tree);
+        bsx_free(ctx, bt->coeffs);
+        bsx_free(ctx, bt->lde);
+        delete bt;
+        return rc;
+    }
+    *out = bt;
+    return BSX_OK;
+}
+
 // ------------------------------------------------------------------------------------ test hooks
 extern "C" int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n) {
     if (!ctx || (!states && n)) return BSX_ERR_INVALID_ARG;

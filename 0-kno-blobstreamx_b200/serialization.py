@@ -1,0 +1,85 @@
+"""Byte layout of a serialised PolynomialBatch (the circuit artefact stores the constants +
+sigmas commitment and the prover reloads it instead of recommitting).
+
+Restates plonky2 util/serialization/mod.rs `Write::write_polynomial_batch` / `write_merkle_tree` and their `Read`
+counterparts from the public crate; like the rest of the oracle this layout is unpinned (no reference bytes exist
+in the mount).  usize -> u64 LE, field element -> canonical u64 LE, hash -> 4 elements, bool -> one byte:
+
+    n_polys, then per polynomial { len, coeffs[len] }
+    merkle tree: n_leaves, per leaf { len, elements[len] }, n_digests, digests[n_digests][4], cap_height, cap[2^h][4]
+    degree_log, rate_bits, blinding
+
+Pure host-side packing (numpy); the device parts come from / go to `bsx_batch_export` / `bsx_batch_import`.
+"""
+import numpy as np
+
+SALT_SIZE = 4
+
+
+def _u(x):
+    return np.array([x], dtype="<u8").tobytes()
+
+
+def write_polynomial_batch(coeffs, leaves, digests, cap, degree_log, rate_bits, blinding):
+    coeffs, leaves = np.asarray(coeffs, dtype=np.uint64), np.asarray(leaves, dtype=np.uint64)
+    digests, cap = np.asarray(digests, dtype=np.uint64).reshape(-1, 4), np.asarray(cap, dtype=np.uint64).reshape(-1, 4)
+    out = [_u(coeffs.shape[0])]
+    for c in coeffs:
+        out += [_u(c.shape[0]), c.astype("<u8").tobytes()]
+    rows = np.empty((leaves.shape[0], leaves.shape[1] + 1), dtype="<u8")
+    rows[:, 0] = leaves.shape[1]
+    rows[:, 1:] = leaves
+    cap_height = int(cap.shape[0]).bit_length() - 1
+    out += [_u(leaves.shape[0]), rows.tobytes(), _u(digests.shape[0]), digests.astype("<u8").tobytes(), _u(cap_height),
+            cap.astype("<u8").tobytes(), _u(degree_log), _u(rate_bits), bytes([1 if blinding else 0])]
+    return b"".join(out)
+
+
+def read_polynomial_batch(data):
+    """-> dict(coeffs, leaves, digests, cap, degree_log, rate_bits, blinding); ValueError on malformed input."""
+    buf = memoryview(data).cast("B")
+    pos = 0
+
+    def take(n_words):
+        nonlocal pos
+        end = pos + 8 * n_words
+        if n_words < 0 or end > len(buf):
+            raise ValueError("polynomial batch bytes truncated")
+        a = np.frombuffer(buf[pos:end], dtype="<u8")
+        pos = end
+        return a
+
+    n_polys = int(take(1)[0])
+    if n_polys == 0 or n_polys > 1 << 16:
+        raise ValueError("polynomial batch bytes: bad polynomial count")
+    coeffs, n = [], None
+    for _ in range(n_polys):
+        ln = int(take(1)[0])
+        if n is not None and ln != n:
+            raise ValueError("polynomials of different lengths")
+        n = ln
+        coeffs.append(take(ln))
+    n_leaves = int(take(1)[0])
+    if n_leaves == 0:
+        raise ValueError("polynomial batch bytes: no leaves")
+    width = int(take(1)[0])
+    pos -= 8
+    rows = take(n_leaves * (width + 1)).reshape(n_leaves, width + 1)
+    if not (rows[:, 0] == width).all():
+        raise ValueError("leaves of different lengths")
+    n_dig = int(take(1)[0])
+    digests = take(4 * n_dig).reshape(n_dig, 4)
+    cap_height = int(take(1)[0])
+    if cap_height > 32:
+        raise ValueError("polynomial batch bytes: bad cap height")
+    cap = take(4 << cap_height).reshape(1 << cap_height, 4)
+    degree_log, rate_bits = int(take(1)[0]), int(take(1)[0])
+    if pos + 1 != len(buf):
+        raise ValueError("polynomial batch bytes: wrong length")
+    blinding = buf[pos] != 0
+    if degree_log > 40 or rate_bits > 8 or n != 1 << degree_log or n_leaves != n << rate_bits or \
+            width != n_polys + (SALT_SIZE if blinding else 0) or n_dig != 2 * (n_leaves - (1 << cap_height)):
+        raise ValueError("polynomial batch bytes: inconsistent shape")
+    return {"coeffs": np.stack(coeffs).astype(np.uint64), "leaves": np.ascontiguousarray(rows[:, 1:]).astype(np.uint64),
+            "digests": digests.astype(np.uint64), "cap": cap.astype(np.uint64), "degree_log": degree_log,
+            "rate_bits": rate_bits, "blinding": blinding}

@@ -95,6 +95,12 @@ int32_t bsx_batch_coeffs(bsx_batch *b, uint64_t *out, int32_t mem);
  * leaves: row-major 2^(log_n+rate_bits) x (n_cols+salt), rows in leaf (bit-reversed) order;
  * digests: plonky2's `digests` Vec layout (fill_subtree order), 2*(leaves - 2^cap_height) x 4 words. */
 int32_t bsx_batch_export(bsx_batch *b, uint64_t *coeffs_host, uint64_t *leaves_host, uint64_t *digests_host);
+/* The inverse of bsx_batch_export (upstream: the circuit-artefact reader restoring the constants + sigmas
+ * PolynomialBatch, util/serialization `read_polynomial_batch`): same layouts as export, nothing is recomputed
+ * or verified.  n_salt = 0 or 4 (`blinding`).  All four parts are required. */
+int32_t bsx_batch_import(bsx_ctx *ctx, const uint64_t *coeffs_host, const uint64_t *leaves_host,
+                         const uint64_t *digests_host, const uint64_t *cap_host, int32_t log_n, int32_t n_cols,
+                         int32_t n_salt, int32_t rate_bits, int32_t cap_height, bsx_batch **out);
 int32_t bsx_batch_shape(const bsx_batch *b, int32_t *log_n, int32_t *n_cols, int32_t *rate_bits,
                         int32_t *cap_height, int32_t *n_salt);
 /* device pointers for callers that keep working on the GPU (quotient evaluation, multi-GPU exchange):

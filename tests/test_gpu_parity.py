@@ -208,3 +208,69 @@ def test_linearity_full_size(pkg, ctx):
         assert (((ra.astype(object) + rb.astype(object)) % P).astype(np.uint64) == rs).all()
     for t in (ba, bb, bs):
         t.close()
+
+
+@pytest.mark.parametrize("blinding", [False, True])
+def test_batch_import_and_bytes_roundtrip(pkg, ctx, oracle, blinding):
+    """export -> bsx_batch_import gives a batch that answers every accessor identically; the serialised bytes
+    equal the bytes written from the oracle's parts."""
+    ser = __import__(pkg.__name__ + ".serialization", fromlist=["x"])
+    log_n, n_cols, rate_bits, cap_height = 9, 7, 2, 3
+    vals = splitmix_field(401, (n_cols, 1 << log_n))
+    salt = splitmix_field(402, (4, 1 << (log_n + rate_bits))) if blinding else None
+    a = pkg.PolynomialBatch.from_values(ctx, vals, rate_bits, blinding, cap_height, salt=salt)
+    ob = oracle.batch_from_values(vals, rate_bits, cap_height, salt=salt)
+    data = a.to_bytes()
+    want = ser.write_polynomial_batch(ob["coeffs"], ob["leaves"],
+                                      oracle.merkle_digests_to_plonky2(ob["digests"], log_n + rate_bits, cap_height),
+                                      ob["cap"], log_n, rate_bits, blinding)
+    assert data == want
+    b = pkg.PolynomialBatch.from_bytes(ctx, data)
+    assert a.shape() == b.shape()
+    assert (a.cap == b.cap).all() and (a.polynomials == b.polynomials).all()
+    ea, eb = a.export(), b.export()
+    for k in ("coeffs", "leaves", "digests", "cap"):
+        assert (ea[k] == eb[k]).all(), k
+    for i in (0, 1, 777, (1 << (log_n + rate_bits)) - 1):
+        assert (a.get_lde_values(i) == b.get_lde_values(i)).all()
+        pa, pb = a.merkle_tree.prove(i), b.merkle_tree.prove(i)
+        assert (np.asarray(pa) == np.asarray(pb)).all()
+        assert oracle.merkle_verify(b.merkle_tree.get(i), i, pb, b.cap)
+    z = splitmix_field(403, (2,))
+    assert (a.eval_commitment(z) == b.eval_commitment(z)).all()
+    with pytest.raises(pkg.BsxError):
+        pkg.PolynomialBatch.from_bytes(ctx, data[:-9])
+    a.close()
+    b.close()
+
+
+def test_fri_proof_from_imported_batch(pkg, ctx, oracle):
+    """prove_openings on a restored batch (coefficients held in natural order) = on the freshly built one."""
+    log_n, rate_bits, cap_height = 10, 1, 1
+    vals = [splitmix_field(411 + i, (w, 1 << log_n)) for i, w in enumerate((4, 3))]
+    fresh = [pkg.PolynomialBatch.from_values(ctx, v, rate_bits, False, cap_height) for v in vals]
+    restored = [pkg.PolynomialBatch.from_bytes(ctx, f.to_bytes()) for f in fresh]
+    zeta = splitmix_field(420, (1, 2))
+    polys = [[(o, j) for o, v in enumerate(vals) for j in range(v.shape[0])]]
+    inst = pkg.FriInstanceInfo(zeta, polys)
+    params = pkg.FriConfig(rate_bits=rate_bits, cap_height=cap_height, proof_of_work_bits=6,
+                           num_query_rounds=5).fri_params(log_n)
+    proofs = []
+    for bs in (fresh, restored):
+        ch = pkg.Challenger(ctx)
+        ch.observe_elements(splitmix_field(421, (8,)))
+        proofs.append(pkg.prove_openings(inst, bs, ch, params))
+    assert (np.asarray(proofs[0]) == np.asarray(proofs[1])).all()
+    for x in fresh + restored:
+        x.close()
+
+
+def test_transpose_tall_matrix(pkg, ctx, oracle):
+    """MerkleTree::new on 2^22 row-major leaves: the transpose grid is one-dimensional (2^17 row tiles)."""
+    n, w = 1 << 22, 2
+    leaves = splitmix_field(431, (n, w))
+    t = pkg.MerkleTree(ctx, leaves, 0)
+    for i in (0, 12345, n - 1):
+        assert (t.get(i) == leaves[i]).all()
+        assert oracle.merkle_verify(leaves[i], i, t.prove(i), t.cap)
+    t.close()

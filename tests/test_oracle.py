@@ -171,3 +171,25 @@ def test_batch_salt_columns(oracle):
     assert out["leaves"].shape == (16, 6)
     rev = [int(oracle.lib().orc_reverse_bits(l, 4)) for l in range(16)]
     assert (out["leaves"][:, 2:] == salt[:, rev].T).all()
+
+
+def test_polynomial_batch_bytes_roundtrip(oracle):
+    """Host-side wire format (serialization.py) on oracle-produced parts: write -> read is the identity."""
+    import __graft_entry__ as G
+    pkg = G.load_package()
+    ser = __import__(pkg.__name__ + ".serialization", fromlist=["x"])
+    vals = splitmix_field(77, (3, 32))
+    salt = splitmix_field(78, (4, 64))
+    for s in (None, salt):
+        ob = oracle.batch_from_values(vals, 1, 2, salt=s)
+        dg = oracle.merkle_digests_to_plonky2(ob["digests"], 6, 2)
+        data = ser.write_polynomial_batch(ob["coeffs"], ob["leaves"], dg, ob["cap"], 5, 1, s is not None)
+        n_lv, w = 64, 3 + (4 if s is not None else 0)
+        assert len(data) == 8 * (1 + 3 * 33 + 1 + n_lv * (w + 1) + 1 + 4 * 2 * (64 - 4) + 1 + 16 + 2) + 1
+        back = ser.read_polynomial_batch(data)
+        assert (back["coeffs"] == ob["coeffs"]).all() and (back["leaves"] == ob["leaves"]).all()
+        assert (back["digests"] == dg).all() and (back["cap"] == ob["cap"]).all()
+        assert (back["degree_log"], back["rate_bits"], back["blinding"]) == (5, 1, s is not None)
+        for bad in (data[:-1], data[:100], data + b"\0", b""):
+            with pytest.raises(ValueError):
+                ser.read_polynomial_batch(bad)
