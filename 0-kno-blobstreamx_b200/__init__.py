@@ -42,6 +42,7 @@ from .parallel import (  # noqa: F401
     assemble_cap,
     device_tensor,
     exchange_staged,
+    top_siblings,
 )
 
 P = 0xFFFFFFFF00000001

@@ -342,177 +342,6 @@ class PolynomialBatch:
         return cls.from_parts(ctx, d["coeffs"], d["leaves"], d["digests"], d["cap"], d["rate_bits"])
 
     def shape(self):
-        a, b, c = C.c_int32(), C.c_int32(), C.c_int32()
-        self.ctx.check(lib().bsx_merkle_shape(self._h, C.byref(a), C.byref(b), C.byref(c)))
-        return a.value, b.value, c.value
-
-    @property
-    def cap(self):
-        _, _, ch = self.shape()
-        out = np.zeros((1 << ch, 4), dtype=np.uint64)
-        self.ctx.check(lib().bsx_merkle_cap(self._h, _ptr(out)))
-        return out
-
-    def get(self, leaf_index):
-        """`MerkleTree::get(i)` for one index or a list of indices."""
-        _, leaf_len, _ = self.shape()
-        idx = _np(np.atleast_1d(leaf_index))
-        out = np.zeros((idx.size, leaf_len), dtype=np.uint64)
-        self.ctx.check(lib().bsx_merkle_get(self._h, _ptr(idx), idx.size, _ptr(out)))
-        return out[0] if np.isscalar(leaf_index) else out
-
-    def prove(self, leaf_index):
-        """`MerkleTree::prove(leaf_index).siblings`, bottom-up."""
-        log_leaves, _, ch = self.shape()
-        out = np.zeros((log_leaves - ch, 4), dtype=np.uint64)
-        self.ctx.check(lib().bsx_merkle_prove(self._h, C.c_uint64(int(leaf_index)), _ptr(out)))
-        return out
-
-    @property
-    def digests(self):
-        """`MerkleTree.digests` in plonky2's Vec layout."""
-        log_leaves, _, ch = self.shape()
-        out = np.zeros((2 * ((1 << log_leaves) - (1 << ch)), 4), dtype=np.uint64)
-        self.ctx.check(lib().bsx_merkle_digests(self._h, _ptr(out)))
-        return out
-
-    def close(self):
-        if self._h is not None and self._owner is None:
-            lib().bsx_merkle_free(self._h)
-        self._h = None
-
-    def __del__(self):
-        try:
-            self.close()
-        except Exception:
-            pass
-
-
-class PolynomialBatch:
-    """plonky2 fri/oracle.rs `PolynomialBatch<GoldilocksField, PoseidonGoldilocksConfig, 2>`."""
-
-    def __init__(self, ctx, handle, timing=None):
-        self.ctx = ctx
-        self._h = handle
-        self.timing = timing
-
-    @staticmethod
-    def _build(fn, ctx, cols, rate_bits, blinding, cap_height, salt, device_ptr, shape, timing):
-        if device_ptr is not None:
-            n_cols, n = shape
-            src, mem = C.c_void_p(int(device_ptr)), BSX_DEVICE
-        else:
-            cols = _np(cols)
-            if cols.ndim != 2:
-                raise BsxError("expected (n_cols, n) column vectors")
-            n_cols, n = cols.shape
-            src, mem = _ptr(cols), BSX_HOST
-        log_n = _log2_strict(n)
-        if salt is not None and mem == BSX_HOST:
-            salt = _np(salt)
-        h = C.c_void_p()
-        t = Timing() if timing else None
-        ctx.check(fn(ctx._h, src, mem, log_n, n_cols, int(rate_bits), int(cap_height), 1 if blinding else 0,
-                     _ptr(salt), C.byref(h), C.byref(t) if t is not None else None))
-        return PolynomialBatch(ctx, h, t)
-
-    @classmethod
-    def from_values(cls, ctx, values, rate_bits, blinding, cap_height, salt=None, device_ptr=None, shape=None,
-                    timing=False):
-        """`PolynomialBatch::from_values(values, rate_bits, blinding, cap_height, timing, fft_root_table)`.
-        values: (n_cols, n) -- one row per PolynomialValues.  `device_ptr`/`shape` pass a device buffer."""
-        return cls._build(lib().bsx_batch_from_values, ctx, values, rate_bits, blinding, cap_height, salt,
-                          device_ptr, shape, timing)
-
-    @classmethod
-    def from_coeffs(cls, ctx, coeffs, rate_bits, blinding, cap_height, salt=None, device_ptr=None, shape=None,
-                    timing=False):
-        """`PolynomialBatch::from_coeffs(polynomials, rate_bits, blinding, cap_height, timing, fft_root_table)`."""
-        return cls._build(lib().bsx_batch_from_coeffs, ctx, coeffs, rate_bits, blinding, cap_height, salt,
-                          device_ptr, shape, timing)
-
-    @classmethod
-    def from_parts(cls, ctx, coeffs, leaves, digests, cap, rate_bits):
-        """Restore a batch from `export()`'s parts without recomputing anything (the circuit-artefact reader,
-        plonky2 util/serialization `read_polynomial_batch`).  coeffs (n_cols, n) natural order; leaves
-        (n << rate_bits, n_cols + salt) in leaf order; digests in plonky2's `digests` layout; cap (2^h, 4)."""
-        coeffs, leaves, digests, cap = _np(coeffs), _np(leaves), _np(digests), _np(cap)
-        n_cols, n = coeffs.shape
-        log_n, cap_height = _log2_strict(n), _log2_strict(cap.shape[0])
-        if leaves.shape[0] != n << rate_bits:
-            raise BsxError("leaves.len() = %d, expected %d" % (leaves.shape[0], n << rate_bits))
-        n_salt = leaves.shape[1] - n_cols
-        want = 2 * ((n << rate_bits) - (1 << cap_height))
-        if digests.reshape(-1, 4).shape[0] != want:
-            raise BsxError("digests.len() = %d, expected %d" % (digests.reshape(-1, 4).shape[0], want))
-        h = C.c_void_p()
-        ctx.check(lib().bsx_batch_import(ctx._h, _ptr(coeffs), _ptr(leaves), _ptr(digests), _ptr(cap), log_n, n_cols,
-                                         n_salt, int(rate_bits), cap_height, C.byref(h)))
-        return PolynomialBatch(ctx, h, None)
-
-    def to_bytes(self):
-        """plonky2 util/serialization `Write::write_polynomial_batch` (upstream layout restated from the public
-        crate, unpinned like the rest of the oracle): usize as u64 LE, field elements as u64 LE, bool as u8.
-          n_polys, then per polynomial { len, coeffs }; merkle tree { n_leaves, per leaf { len, elements },
-          n_digests, digests, cap_height, cap }; degree_log; rate_bits; blinding."""
-        sh, parts = self.shape(), self.export()
-        u = lambda x: np.uint64(x).tobytes()  # noqa: E731
-        out = [u(sh["n_cols"])]
-        for c in parts["coeffs"]:
-            out += [u(c.shape[0]), c.astype("<u8").tobytes()]
-        lv = parts["leaves"]
-        rows = np.empty((lv.shape[0], lv.shape[1] + 1), dtype="<u8")
-        rows[:, 0] = lv.shape[1]
-        rows[:, 1:] = lv
-        out += [u(lv.shape[0]), rows.tobytes(), u(parts["digests"].shape[0]), parts["digests"].astype("<u8").tobytes(),
-                u(sh["cap_height"]), parts["cap"].astype("<u8").tobytes(), u(sh["degree_log"]), u(sh["rate_bits"]),
-                bytes([1 if sh["n_salt"] else 0])]
-        return b"".join(out)
-
-    @classmethod
-    def from_bytes(cls, ctx, data):
-        """`Read::read_polynomial_batch`: the inverse of `to_bytes`; malformed input raises BsxError."""
-        buf = memoryview(data)
-        pos = 0
-
-        def take(n_words):
-            nonlocal pos
-            end = pos + 8 * n_words
-            if end > len(buf):
-                raise BsxError("polynomial batch bytes truncated")
-            a = np.frombuffer(buf[pos:end], dtype="<u8")
-            pos = end
-            return a
-
-        n_polys = int(take(1)[0])
-        coeffs, n = [], None
-        for _ in range(n_polys):
-            ln = int(take(1)[0])
-            if n is not None and ln != n:
-                raise BsxError("polynomials of different lengths")
-            n = ln
-            coeffs.append(take(ln))
-        n_leaves = int(take(1)[0])
-        width = int(np.frombuffer(buf[pos:pos + 8], dtype="<u8")[0]) if n_leaves else 0
-        rows = take(n_leaves * (width + 1)).reshape(n_leaves, width + 1)
-        if n_leaves and not (rows[:, 0] == width).all():
-            raise BsxError("leaves of different lengths")
-        n_dig = int(take(1)[0])
-        digests = take(4 * n_dig).reshape(n_dig, 4)
-        cap_height = int(take(1)[0])
-        if cap_height > 32:
-            raise BsxError("bad cap height")
-        cap = take(4 << cap_height).reshape(1 << cap_height, 4)
-        degree_log, rate_bits = int(take(1)[0]), int(take(1)[0])
-        if pos + 1 != len(buf):
-            raise BsxError("polynomial batch bytes: wrong length")
-        blinding = buf[pos] != 0
-        if n_polys == 0 or n != 1 << degree_log or n_leaves != n << rate_bits or \
-                width != n_polys + (4 if blinding else 0):
-            raise BsxError("polynomial batch bytes: inconsistent shape")
-        return cls.from_parts(ctx, np.stack(coeffs), rows[:, 1:], digests, cap, rate_bits)
-
-    def shape(self):
         v = [C.c_int32() for _ in range(5)]
         self.ctx.check(lib().bsx_batch_shape(self._h, *[C.byref(x) for x in v]))
         return dict(zip(("degree_log", "n_cols", "rate_bits", "cap_height", "n_salt"), [x.value for x in v]))

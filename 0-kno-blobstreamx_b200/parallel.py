@@ -141,6 +141,19 @@ def assemble_cap(local_caps, plan, ctx=None):
     return cap
 
 
+def top_siblings(rank_caps, plan, rank, ctx):
+    """Merkle siblings above `rank`'s local root when there are more ranks than cap entries (bottom-up,
+    `plan.reduce_levels` digests): what the owner appends to its local proof to make it the whole-tree proof."""
+    level = np.concatenate([np.asarray(c, dtype=np.uint64).reshape(-1, 4) for c in rank_caps], axis=0)
+    sib, idx = [], rank
+    for _ in range(plan.reduce_levels):
+        sib.append(level[idx ^ 1].copy())
+        out = np.zeros((level.shape[0] >> 1, 4), dtype=np.uint64)
+        ctx.check(lib().bsx_merkle_reduce(ctx._h, _ptr(_np(level)), level.shape[0], 1, _ptr(out)))
+        level, idx = out, idx >> 1
+    return np.array(sib, dtype=np.uint64).reshape(-1, 4)
+
+
 class ShardedPolynomialBatch:
     """This rank's part of one committed batch: its coefficient columns, its leaf rows and cap subtrees,
     and the cap of the whole batch.  `merkle_tree.get / prove` answer for leaves this rank owns
@@ -153,6 +166,7 @@ class ShardedPolynomialBatch:
         self.cap = None
         self.timing = None
         self.group, self.mode = None, "p2p"
+        self.rank_caps = None  # every rank's local cap (set by `run`; needed for proofs when world > 2^cap_height)
 
     # ---- construction pieces (also used one by one by the single-process tests)
     @classmethod
@@ -258,8 +272,57 @@ class ShardedPolynomialBatch:
         caps = torch.empty(plan.world * local.numel(), dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(caps, local, group=group)
         caps = caps.cpu().numpy().astype(np.uint64).reshape(plan.world, -1, 4)
-        self.cap = assemble_cap(list(caps), plan, ctx)
+        self.rank_caps = list(caps)
+        self.cap = assemble_cap(self.rank_caps, plan, ctx)
         return self
+
+    # ---- openings: served by the owning rank (row l lives on rank l >> log2(chunk))
+    @property
+    def proof_len(self):
+        return self.plan.log_nb - self.plan.cap_height
+
+    def get(self, leaf):
+        """`MerkleTree::get(leaf)` for a leaf this rank owns (global index)."""
+        if self.plan.owner(leaf) != self.rank:
+            raise BsxError("leaf %d lives on rank %d" % (leaf, self.plan.owner(leaf)))
+        return self.merkle_tree.get(self.plan.local_leaf(leaf))
+
+    def prove(self, leaf):
+        """`MerkleTree::prove(leaf)` against the cap of the WHOLE batch, for a leaf this rank owns."""
+        if self.plan.owner(leaf) != self.rank:
+            raise BsxError("leaf %d lives on rank %d" % (leaf, self.plan.owner(leaf)))
+        sib = np.asarray(self.merkle_tree.prove(self.plan.local_leaf(leaf)), dtype=np.uint64).reshape(-1, 4)
+        if self.plan.reduce_levels:
+            if self.rank_caps is None:
+                raise BsxError("rank caps unknown: commit with run() or set rank_caps")
+            sib = np.concatenate([sib, top_siblings(self.rank_caps, self.plan, self.rank, self.ctx)], axis=0)
+        return sib
+
+    def local_openings(self, leaves):
+        """Rows and proofs of the listed (global) leaves this rank owns, zeros elsewhere: summing the arrays of
+        all ranks gives every opening exactly once."""
+        leaves = [int(x) for x in leaves]
+        width = self.merkle_tree.shape()[1]
+        rows = np.zeros((len(leaves), width), dtype=np.uint64)
+        proofs = np.zeros((len(leaves), self.proof_len, 4), dtype=np.uint64)
+        for k, leaf in enumerate(leaves):
+            if self.plan.owner(leaf) == self.rank:
+                rows[k] = self.get(leaf)
+                proofs[k] = self.prove(leaf)
+        return rows, proofs
+
+    def open(self, leaves):
+        """Collective: every rank gets the rows and Merkle proofs of `leaves` (the same list on every rank), each
+        answered by its owner; one all-reduce of a few KB (the FRI query phase opens 28 rows per tree)."""
+        import torch
+        import torch.distributed as dist
+        rows, proofs = self.local_openings(leaves)
+        dev = "cuda:%d" % self.ctx.device
+        flat = np.concatenate([rows.reshape(-1), proofs.reshape(-1)]).view(np.int64)
+        t = torch.from_numpy(flat.copy()).to(dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)  # exactly one non-zero contribution per word
+        flat = t.cpu().numpy().view(np.uint64)
+        return flat[:rows.size].reshape(rows.shape), flat[rows.size:].reshape(proofs.shape)
 
     @classmethod
     def from_values(cls, ctx, values_local, log_n, n_cols, rate_bits, cap_height, group=None, mode="p2p",

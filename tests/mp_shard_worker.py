@@ -38,6 +38,13 @@ def main():
         assert (sb.merkle_tree.get(plan.local_leaf(leaf)) == tree.get(leaf)).all()
         assert (sb.merkle_tree.prove(plan.local_leaf(leaf)) == tree.prove(leaf)).all()
     assert (sb.polynomials == ref.polynomials[c0:c1]).all()
+    # collective openings: every rank asks for the same leaves, each answered by its owner
+    nb = 1 << plan.log_nb
+    leaves = [(k * 40503 + 17) % nb for k in range(28)]
+    rows, proofs = sb.open(leaves)
+    for k, leaf in enumerate(leaves):
+        assert (rows[k] == tree.get(leaf)).all()
+        assert (proofs[k] == np.asarray(tree.prove(leaf)).reshape(-1, 4)).all()
     cap0 = int(sb.cap[0, 0])
     dist.barrier()
     sb.close()

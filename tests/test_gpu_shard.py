@@ -80,6 +80,21 @@ def test_sharded_equals_single_gpu(pkg, ctx, oracle, log_n, n_cols, rate_bits, c
         assert (s.merkle_tree.get(plan.local_leaf(leaf)) == tree.get(leaf)).all()
         if plan.reduce_levels == 0:
             assert (s.merkle_tree.prove(plan.local_leaf(leaf)) == tree.prove(leaf)).all()
+    # the same openings as the collective `open` assembles them: every rank contributes the leaves it owns,
+    # with the proof extended to the cap of the whole batch when there are more ranks than cap entries
+    leaves = sorted({0, 1, nb - 1, nb // 2, (nb // 3) | 1, plan.chunk - 1, plan.chunk % nb})
+    caps = [s.merkle_tree.cap for s in shards]
+    rows = proofs = 0
+    for s in shards:
+        s.rank_caps = caps
+        r, pr = s.local_openings(leaves)
+        rows, proofs = rows + r, proofs + pr
+    for k, leaf in enumerate(leaves):
+        assert (rows[k] == tree.get(leaf)).all()
+        assert (proofs[k] == np.asarray(tree.prove(leaf)).reshape(-1, 4)).all()
+        assert oracle.merkle_verify(rows[k], leaf, proofs[k], cap)
+        with pytest.raises(pkg.BsxError):
+            shards[(plan.owner(leaf) + 1) % world].get(leaf) if world > 1 else shards[0].get(nb)
     for s in shards:
         s.close()
     ref.close()
