@@ -13,6 +13,9 @@ At N > 1 the line also carries `sharded`: ONE commit of the same shape split ove
 scaling; column-sharded transforms whose last pass stores into the owners' row slabs over NVLink P2P, or a
 staged NCCL all-to-all; per-GPU cap subtrees; cap gathered) -- see 0-kno-blobstreamx_b200/parallel.py.
 
+`prove` (skip with --no-prove): wall seconds of one shape-equivalent synthetic proof per GPU (three commits
+from pinned host memory, the opening set, prove_openings) -- BASELINE.json's second metric on random columns.
+
 `--impl reference` times the CPU arm instead: the in-repo oracle port of the plonky2 algorithm
 (the reference mount holds no source and there is no Rust toolchain) with all
 host threads on a bounded sample of the same workload.
@@ -200,6 +203,86 @@ def sharded_arm(args, pkg, ctx, stream, rank, world, local_rank, cap_rank0):
     return out
 
 
+PROVE_WIDTHS = (84, 135, 20, 16)  # constants+sigmas | wires | Zs+partial products | quotient chunks (8 x 2 challenges)
+
+
+def prove_arm(args, pkg, ctx, stream, rank, world, local_rank, wires_np):
+    """BASELINE.json's second metric, as far as it can exist here: the commitment-phase call sequence of ONE plonky2
+    proof at 2^20 rows, standard_recursion_config, on random columns (the plonky2x circuits and their witness
+    generators are not in the mount: SURVEY.md 8(d)).  Per proof: commit wires (from_values, pinned host), commit
+    Zs (from_values), commit quotient chunks (from_coeffs), evaluate the opening set at zeta / g*zeta, prove_openings
+    (alpha-combine, FRI commit rounds, proof of work, 28 query rounds) -> proof words on host.  The constants+sigmas
+    batch is circuit data and is committed before the clock starts.  Every rank runs its own proofs (header_range
+    map jobs: replicas, no communication); the time is device time on the library's stream, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    n = 1 << LOG_N
+    cfg = pkg.FriConfig()
+    fp = cfg.fri_params(LOG_N)
+
+    def pinned(seed, w):
+        t = torch.empty((w, n), dtype=torch.int64).pin_memory()
+        a = t.numpy().view(np.uint64)
+        a[:] = splitmix_field(seed + rank, (w, n))
+        return t, a
+
+    keep0, cs = pinned(0x5EED0200, PROVE_WIDTHS[0])
+    keep2, zs = pinned(0x5EED0300, PROVE_WIDTHS[2])
+    keep3, qs = pinned(0x5EED0400, PROVE_WIDTHS[3])
+    constants_sigmas = pkg.PolynomialBatch.from_values(ctx, cs, cfg.rate_bits, False, cfg.cap_height)
+    g = pow(7, (P - 1) >> LOG_N, P)
+
+    def one_proof():
+        ch = pkg.Challenger(ctx)
+        ch.observe_cap(constants_sigmas.cap)
+        wires = pkg.PolynomialBatch.from_values(ctx, wires_np, cfg.rate_bits, False, cfg.cap_height)
+        ch.observe_cap(wires.cap)
+        ch.get_n_challenges(4)  # betas, gammas
+        zb = pkg.PolynomialBatch.from_values(ctx, zs, cfg.rate_bits, False, cfg.cap_height)
+        ch.observe_cap(zb.cap)
+        ch.get_n_challenges(2)  # alphas
+        qb = pkg.PolynomialBatch.from_coeffs(ctx, qs, cfg.rate_bits, False, cfg.cap_height)
+        ch.observe_cap(qb.cap)
+        zeta = ch.get_extension_challenge()
+        gzeta = np.array([int(zeta[0]) * g % P, int(zeta[1]) * g % P], dtype=np.uint64)
+        batches = [constants_sigmas, wires, zb, qb]
+        openings = [b.eval_commitment(zeta) for b in batches] + [zb.eval_commitment(gzeta, 0, 2)]
+        for o in openings:
+            ch.observe_elements(o.reshape(-1))
+        polys0 = [(o, j) for o, w in enumerate(PROVE_WIDTHS) for j in range(w)]
+        inst = pkg.FriInstanceInfo(np.array([zeta, gzeta]), [polys0, [(2, 0), (2, 1)]])
+        proof = pkg.prove_openings(inst, batches, ch, fp)
+        for b in batches[1:]:
+            b.close()
+        return proof
+
+    first = one_proof()
+    reps = max(1, min(args.steps, 3))
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(reps):
+        proof = one_proof()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    assert (proof == first).all(), "identical proofs differ"
+    s_per = e0.elapsed_time(e1) / reps / 1e3
+    if world > 1:
+        t = torch.tensor([s_per], device="cuda:%d" % local_rank, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        s_per = float(t[0])
+    constants_sigmas.close()
+    del keep0, keep2, keep3
+    return {"wall_s_per_proof": s_per, "proofs_per_s": world / s_per, "n_gpus": world, "reps": reps,
+            "proof_words": int(proof.size), "fri_arity_bits": list(fp.reduction_arity_bits),
+            "workload": "shape-equivalent synthetic prove, 2^%d rows: commits of %d/%d/%d columns (+%d precommitted), "
+                        "opening set at zeta and g*zeta, prove_openings; standard_recursion_config; random columns, "
+                        "NOT a real header_range proof; one proof per GPU, replicas" %
+                        (LOG_N, PROVE_WIDTHS[1], PROVE_WIDTHS[2], PROVE_WIDTHS[3], PROVE_WIDTHS[0])}
+
+
 def gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -273,6 +356,9 @@ def gpu_arm(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(t[0]), float(t[1])
     sharded = sharded_arm(args, pkg, ctx, stream, rank, world, local_rank, cap0) if world > 1 else None
+    del dev
+    torch.cuda.empty_cache()
+    prove = None if args.no_prove else prove_arm(args, pkg, ctx, stream, rank, world, local_rank, host_np)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -310,7 +396,7 @@ def gpu_arm(args, rank, world, local_rank):
             "ifft": dict(roof(16 * elems, avg["ifft_ms"], traffic.get("ifft")), algorithmic_bytes=16 * elems),
             "lde": dict(roof(8 * elems + 8 * nb * N_COLS, avg["lde_ms"], traffic.get("lde")),
                         algorithmic_bytes=8 * elems + 8 * nb * N_COLS),
-            "note": "two kernels each (pass HI + pass LO); bound by integer issue (ALU pipe 56-78 % busy, DRAM 8-19 %), "
+            "note": "two kernels each (pass HI + pass LO); bound by integer issue (ALU pipe 74-76 % busy in both passes), "
                     "not by HBM: a Goldilocks butterfly is ~36 integer instructions per 16 bytes moved (DESIGN.md 3.4)",
         },
         "whole_commit": dict(roof(8 * elems * (2 + (1 << RATE_BITS)) + 64 * nb, ms),
@@ -320,6 +406,8 @@ def gpu_arm(args, rank, world, local_rank):
     }
     if sharded is not None:
         out["sharded"] = sharded
+    if prove is not None:
+        out["prove"] = prove
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle as O
         ns = 1 << CPU_SAMPLE_LOG_N
@@ -347,6 +435,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prove", action="store_true", help="skip the shape-equivalent synthetic prove leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get("RANK", "0"))
