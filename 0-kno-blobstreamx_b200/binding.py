@@ -13,7 +13,7 @@ EXPORTED_SYMBOLS = [
     "bsx_version", "bsx_device_count", "bsx_launch_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
     "bsx_ctx_sync", "bsx_batch_from_values", "bsx_batch_from_coeffs", "bsx_batch_free", "bsx_batch_cap",
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
-    "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
+    "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
     "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
     "bsx_challenger_get", "bsx_fri_proof_words", "bsx_fri_prove_openings", "bsx_fri_proof", "bsx_fri_final_poly",
@@ -68,6 +68,7 @@ def lib():
         "bsx_batch_cap": (i32, [vp, vp]),
         "bsx_batch_tree": (vp, [vp]),
         "bsx_batch_get_lde_values": (i32, [vp, u64, u64, vp]),
+        "bsx_batch_get_lde_values_packed": (i32, [vp, u64, u64, u64, vp, i32]),
         "bsx_batch_coeffs": (i32, [vp, vp, i32]),
         "bsx_batch_export": (i32, [vp, vp, vp, vp]),
         "bsx_batch_eval_ext": (i32, [vp, i32, i32, vp, i32, vp]),
@@ -371,6 +372,15 @@ class PolynomialBatch:
         self.ctx.check(lib().bsx_batch_get_lde_values(self._h, C.c_uint64(int(index)), C.c_uint64(int(step)),
                                                       _ptr(out)))
         return out
+
+    def get_lde_values_packed(self, index_start, step=1, width=4):
+        """`PolynomialBatch::get_lde_values_packed::<P>(index_start, step)` with P::WIDTH = width: (n_cols, width),
+        lane i of every column = get_lde_values(index_start + i, step)."""
+        rows = np.zeros((int(width), self.shape()["n_cols"]), dtype=np.uint64)
+        self.ctx.check(lib().bsx_batch_get_lde_values_packed(self._h, C.c_uint64(int(index_start)),
+                                                             C.c_uint64(int(width)), C.c_uint64(int(step)),
+                                                             _ptr(rows), BSX_HOST))
+        return np.ascontiguousarray(rows.T)
 
     def eval_commitment(self, points, col_begin=0, n_cols=None):
         """The `eval_commitment(z, c)` closure of plonk/proof.rs `OpeningSet::new`: every polynomial of the batch

@@ -507,6 +507,40 @@ extern "C" int32_t bsx_batch_get_lde_values(bsx_batch *b, uint64_t index, uint64
     return BSX_OK;
 }
 
+// fri/oracle.rs get_lde_values_packed: the rows get_lde_values(index_start + i, step) for i < count (upstream
+// transposes them into P::WIDTH-lane packed columns; the ABI returns them row by row, `mem` side).
+extern "C" int32_t bsx_batch_get_lde_values_packed(bsx_batch *b, uint64_t index_start, uint64_t count, uint64_t step,
+                                                   uint64_t *out, int32_t mem) {
+    if (!b) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = b->ctx;
+    const int log_nb = b->log_n + b->rate_bits;
+    if (count == 0 || b->n_cols == 0) return BSX_OK;
+    if (!out) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "output is NULL");
+    if (count > ((u64)1 << log_nb) || step > ((u64)1 << log_nb) || ((index_start + count - 1) * step) >> log_nb)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "index * step out of range");
+    CU(ctx, cudaSetDevice(ctx->device));
+    std::vector<u64> leaf(count);
+    for (u64 i = 0; i < count; i++) leaf[i] = host_bitrev((index_start + i) * step, log_nb);
+    u64 *idx_dev, *rows_dev = (u64 *)out;
+    TRY(bsx_alloc(ctx, &idx_dev, count));
+    if (mem != BSX_DEVICE) TRY(bsx_alloc(ctx, &rows_dev, count * (size_t)b->n_cols));
+    CU(ctx, cudaMemcpyAsync(idx_dev, leaf.data(), count * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+    const u64 max_chunk = 1 << 20;  // rows per gather launch
+    for (u64 r = 0; r < count; r += max_chunk) {
+        u64 k = count - r < max_chunk ? count - r : max_chunk;
+        launch_gather_rows(b->lde, (size_t)1 << log_nb, b->n_cols, idx_dev + r, (int)k, rows_dev + r * b->n_cols,
+                           ctx->stream);
+    }
+    CU(ctx, cudaGetLastError());
+    if (mem != BSX_DEVICE) {
+        TRY(bsx_copy_out(ctx, (u64 *)out, rows_dev, count * (size_t)b->n_cols, mem));
+        bsx_free(ctx, rows_dev);
+    }
+    bsx_free(ctx, idx_dev);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));  // leaf[] is read by the async copy
+    return BSX_OK;
+}
+
 extern "C" int32_t bsx_batch_coeffs(bsx_batch *b, uint64_t *out, int32_t mem) {
     if (!b || (!out && b->n_cols > 0)) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = b->ctx;

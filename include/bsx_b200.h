@@ -89,6 +89,11 @@ bsx_tree *bsx_batch_tree(bsx_batch *b);
  * the salt stripped -> out[n_cols].  `index` counts in the degree * 2^log2(step)... domain exactly as
  * upstream: leaf = reverse_bits(index * step, log_n + rate_bits). */
 int32_t bsx_batch_get_lde_values(bsx_batch *b, uint64_t index, uint64_t step, uint64_t *out_host);
+/* Replaces PolynomialBatch::get_lde_values_packed(index_start, step): the `count` rows
+ * get_lde_values(index_start + i, step), i < count, row-major -> out[count][n_cols] on the `mem` side
+ * (upstream packs P::WIDTH of them into SIMD lanes; the quotient loop reads every row this way). */
+int32_t bsx_batch_get_lde_values_packed(bsx_batch *b, uint64_t index_start, uint64_t count, uint64_t step,
+                                        uint64_t *out, int32_t mem);
 /* polynomials[c].coeffs in natural order -> out[n_cols * 2^log_n] (column-major), `mem` side */
 int32_t bsx_batch_coeffs(bsx_batch *b, uint64_t *out, int32_t mem);
 /* Full export for serialisation (circuit artefacts): any pointer may be NULL.

@@ -274,3 +274,17 @@ def test_transpose_tall_matrix(pkg, ctx, oracle):
         assert (t.get(i) == leaves[i]).all()
         assert oracle.merkle_verify(leaves[i], i, t.prove(i), t.cap)
     t.close()
+
+
+def test_get_lde_values_packed(pkg, ctx):
+    log_n, rate_bits = 10, 3
+    vals = splitmix_field(501, (6, 1 << log_n))
+    b = pkg.PolynomialBatch.from_values(ctx, vals, rate_bits, True, 2)
+    for start, step, width in ((0, 1, 4), (12, 8, 8), ((1 << (log_n + rate_bits)) - 4, 1, 4), (5, 3, 1)):
+        got = b.get_lde_values_packed(start, step, width)
+        assert got.shape == (6, width)
+        for i in range(width):
+            assert (got[:, i] == b.get_lde_values(start + i, step)).all()
+    with pytest.raises(pkg.BsxError):
+        b.get_lde_values_packed((1 << (log_n + rate_bits)) - 2, 1, 4)
+    b.close()
