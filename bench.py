@@ -128,6 +128,8 @@ def cpu_reference_arm(args, rank, world):
     from oracle import oracle as O
     n = 1 << CPU_SAMPLE_LOG_N
     vals = splitmix_field(0x5EED0001, (N_COLS, n))
+    # torchrun exports OMP_NUM_THREADS=1 to every worker; the reference arm is meant to use the whole host
+    O.set_num_threads(len(os.sched_getaffinity(0)))
     cores = O.num_threads()
     for _ in range(args.warmup):
         O.batch_from_values(vals, RATE_BITS, CAP_HEIGHT, want=())
@@ -232,50 +234,74 @@ def prove_arm(args, pkg, ctx, stream, rank, world, local_rank, wires_np):
     constants_sigmas = pkg.PolynomialBatch.from_values(ctx, cs, cfg.rate_bits, False, cfg.cap_height)
     g = pow(7, (P - 1) >> LOG_N, P)
 
+    debug = os.environ.get("BSX_BENCH_DEBUG") == "1"
+
     def one_proof():
+        marks = [("start", time.perf_counter())]
+
+        def mark(name):
+            if debug:
+                ctx.sync()
+                marks.append((name, time.perf_counter()))
+
         ch = pkg.Challenger(ctx)
         ch.observe_cap(constants_sigmas.cap)
         wires = pkg.PolynomialBatch.from_values(ctx, wires_np, cfg.rate_bits, False, cfg.cap_height)
+        mark("commit_wires")
         ch.observe_cap(wires.cap)
         ch.get_n_challenges(4)  # betas, gammas
         zb = pkg.PolynomialBatch.from_values(ctx, zs, cfg.rate_bits, False, cfg.cap_height)
+        mark("commit_zs")
         ch.observe_cap(zb.cap)
         ch.get_n_challenges(2)  # alphas
         qb = pkg.PolynomialBatch.from_coeffs(ctx, qs, cfg.rate_bits, False, cfg.cap_height)
+        mark("commit_quotient")
         ch.observe_cap(qb.cap)
         zeta = ch.get_extension_challenge()
         gzeta = np.array([int(zeta[0]) * g % P, int(zeta[1]) * g % P], dtype=np.uint64)
         batches = [constants_sigmas, wires, zb, qb]
         openings = [b.eval_commitment(zeta) for b in batches] + [zb.eval_commitment(gzeta, 0, 2)]
+        mark("opening_set")
         for o in openings:
             ch.observe_elements(o.reshape(-1))
         polys0 = [(o, j) for o, w in enumerate(PROVE_WIDTHS) for j in range(w)]
         inst = pkg.FriInstanceInfo(np.array([zeta, gzeta]), [polys0, [(2, 0), (2, 1)]])
         proof = pkg.prove_openings(inst, batches, ch, fp)
+        mark("prove_openings")
         for b in batches[1:]:
             b.close()
+        mark("free")
+        if debug:
+            print("rank %d proof phases ms: %s" % (rank, ", ".join(
+                "%s %.1f" % (marks[i][0], (marks[i][1] - marks[i - 1][1]) * 1e3) for i in range(1, len(marks)))),
+                file=sys.stderr)
         return proof
 
     first = one_proof()
-    reps = max(1, min(args.steps, 3))
+    one_proof()  # second warm-up: the stream-ordered pool is still growing during the first two proofs
+    reps = max(3, min(args.steps, 5))
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
+    times = []
     for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
         proof = one_proof()
-    e1.record(stream)
-    torch.cuda.synchronize()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1) / 1e3)
     assert (proof == first).all(), "identical proofs differ"
-    s_per = e0.elapsed_time(e1) / reps / 1e3
+    s_per = float(np.median(times))
+    s_max = max(times)
     if world > 1:
-        t = torch.tensor([s_per], device="cuda:%d" % local_rank, dtype=torch.float64)
+        t = torch.tensor([s_per, s_max], device="cuda:%d" % local_rank, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        s_per = float(t[0])
+        s_per, s_max = float(t[0]), float(t[1])
     constants_sigmas.close()
     del keep0, keep2, keep3
-    return {"wall_s_per_proof": s_per, "proofs_per_s": world / s_per, "n_gpus": world, "reps": reps,
+    return {"wall_s_per_proof": s_per, "wall_s_per_proof_max": s_max, "proofs_per_s": world / s_per, "n_gpus": world,
+            "reps": reps, "statistic": "median of reps, max over ranks",
             "proof_words": int(proof.size), "fri_arity_bits": list(fp.reduction_arity_bits),
             "workload": "shape-equivalent synthetic prove, 2^%d rows: commits of %d/%d/%d columns (+%d precommitted), "
                         "opening set at zeta and g*zeta, prove_openings; standard_recursion_config; random columns, "
