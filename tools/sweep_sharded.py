@@ -1,0 +1,75 @@
+#!/usr/bin/env python3
+"""BASELINE.json configs[4] at G > 1: the row-sharded commit (column-sharded transforms, NVLink P2P stores into the
+owners' row slabs, per-GPU cap subtrees) over rows x columns x rate_bits.  Launch under torchrun, one rank per GPU.
+Device-resident random columns (every rank draws its own column range); CUDA-event time per commit, max over
+ranks, best of --reps.  Points that do not fit `--max-gb` per GPU are skipped and listed."""
+import argparse, json, os, sys
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+import __graft_entry__ as G
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--log-n", default="18,20,22,24")
+ap.add_argument("--cols", default="80,135,256,400")
+ap.add_argument("--rate-bits", default="1,3")
+ap.add_argument("--reps", type=int, default=2)
+ap.add_argument("--mode", default="p2p")
+ap.add_argument("--max-gb", type=float, default=110.0)
+a = ap.parse_args()
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+pkg = G.load_package()
+ctx = pkg.Context(local)
+stream = torch.cuda.ExternalStream(ctx.stream, device=local)
+dev = "cuda:%d" % local
+gen = torch.Generator(device=dev)
+gen.manual_seed(0x5EED0005 + rank)
+for log_n in [int(x) for x in a.log_n.split(",")]:
+    n = 1 << log_n
+    for cols in [int(x) for x in a.cols.split(",")]:
+        for rb in [int(x) for x in a.rate_bits.split(",")]:
+            nb = n << rb
+            cl = -(-cols // world)
+            # per GPU: local columns (witness + coeffs) + inter-pass scratch of the local columns + row slab + digests
+            need = 8 * (2 * n * cl + nb * cl + nb * cols // world) + 64 * nb // world + 8 * nb
+            if need > a.max_gb * 1e9:
+                if rank == 0:
+                    print(json.dumps({"gpus": world, "log_n": log_n, "cols": cols, "rate_bits": rb,
+                                      "skipped": "needs %.0f GB per GPU" % (need / 1e9)}), flush=True)
+                continue
+            plan = pkg.ShardPlan(log_n, cols, rb, 4, world)
+            c0, c1 = plan.column_range(rank)
+            loc = torch.randint(0, 1 << 62, (max(c1 - c0, 1), n), dtype=torch.int64, device=dev, generator=gen)
+            torch.cuda.synchronize()
+            with torch.cuda.stream(stream):
+                sb = pkg.ShardedPolynomialBatch.setup(ctx, log_n, cols, rb, 4, mode=a.mode)
+                best, cap0 = None, None
+                for rep in range(a.reps + 1):
+                    dist.barrier()
+                    torch.cuda.synchronize()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(stream)
+                    sb.run(None, device_ptr=loc.data_ptr())
+                    e1.record(stream)
+                    torch.cuda.synchronize()
+                    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    c = int(sb.cap[0, 0])
+                    assert cap0 in (None, c)
+                    cap0 = c
+                    if rep and (best is None or float(t[0]) < best):
+                        best = float(t[0])
+                sb.close()
+            del loc
+            torch.cuda.empty_cache()
+            if rank == 0:
+                print(json.dumps({"gpus": world, "mode": a.mode, "log_n": log_n, "cols": cols, "rate_bits": rb,
+                                  "ms": round(best, 3), "melem_per_s": round(n * cols / best / 1e3, 1),
+                                  "lde_melem_per_s": round(nb * cols / best / 1e3, 1)}), flush=True)
+dist.barrier()
+ctx.close()
+dist.destroy_process_group()
