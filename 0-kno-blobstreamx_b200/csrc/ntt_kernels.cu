@@ -25,6 +25,9 @@
 
 #define NTT_THREADS 256
 #define NTT_MAX_A 12
+#ifndef NTT_W_MIN_A12
+#define NTT_W_MIN_A12 1
+#endif
 
 __device__ __forceinline__ u32 bitrev32(u32 x, int bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
 
@@ -435,7 +438,10 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
     // pass HI: tile of 2^a points x W adjacent i0
     {
         int w_log = 13 - plan.a;  // 8192 elements per tile
-        if (w_log < 2) w_log = 2;
+        // 2^12-point tiles: two columns per tile (16-byte row pieces, completed in L2 by the neighbouring CTA)
+        // keep the tile at 66 KB and three CTAs per SM; four columns would leave one 8-warp CTA per SM
+        const int w_min = plan.a >= 12 ? NTT_W_MIN_A12 : 2;
+        if (w_log < w_min) w_log = w_min;
         if (w_log > plan.b) w_log = plan.b;
         P.w_log = w_log;
         P.groups = plan_groups(plan.a);

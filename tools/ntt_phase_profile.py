@@ -11,14 +11,17 @@ pkg = G.load_package()
 L = pkg.lib()
 ctx = pkg.Context(0)
 cols = int(sys.argv[1]) if len(sys.argv) > 1 else 135
-vals = splitmix_field(1, (cols, 1 << 20))
+log_n = int(sys.argv[2]) if len(sys.argv) > 2 else 20
+rate_bits = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+vals = splitmix_field(1, (cols, 1 << log_n))
 out = (C.c_ulonglong * 4)()
 for rep in range(2):
     L.bsx_debug_ntt_profile(out, 1)
-    b = pkg.PolynomialBatch.from_values(ctx, vals, 3, False, 4, timing=True)
+    b = pkg.PolynomialBatch.from_values(ctx, vals, rate_bits, False, 4, timing=True)
     L.bsx_debug_ntt_profile(out, 0)
     t = b.timing.as_dict()
     b.close()
 tot = sum(out[:3])
+print("2^%d x %d, rate_bits %d:" % (log_n, cols, rate_bits), end=" ")
 print("pass HI cycles summed over CTAs (iNTT + LDE): load %.1f%%  stages %.1f%%  store %.1f%%   (lde %.2f ms, ifft %.2f ms)"
       % (100 * out[0] / tot, 100 * out[1] / tot, 100 * out[2] / tot, t["lde_ms"], t["ifft_ms"]))
