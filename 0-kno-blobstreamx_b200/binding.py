@@ -11,7 +11,7 @@ _SO = os.path.join(_DIR, "csrc", "libbsx_b200.so")
 # every symbol include/bsx_b200.h declares (checked by tests/test_abi.py against the header text)
 EXPORTED_SYMBOLS = [
     "bsx_version", "bsx_device_count", "bsx_launch_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
-    "bsx_ctx_sync", "bsx_batch_from_values", "bsx_batch_from_coeffs", "bsx_batch_free", "bsx_batch_cap",
+    "bsx_ctx_sync", "bsx_ctx_mem_used", "bsx_batch_from_values", "bsx_batch_from_coeffs", "bsx_batch_free", "bsx_batch_cap",
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
@@ -62,6 +62,7 @@ def lib():
         "bsx_last_error": (C.c_char_p, [vp]),
         "bsx_ctx_stream": (vp, [vp]),
         "bsx_ctx_sync": (i32, [vp]),
+        "bsx_ctx_mem_used": (i32, [vp, C.POINTER(C.c_uint64)]),
         "bsx_batch_from_values": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_from_coeffs": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_free": (None, [vp]),
@@ -157,6 +158,12 @@ class Context:
     @property
     def stream(self):
         return lib().bsx_ctx_stream(self._h)
+
+    def mem_used(self):
+        """Bytes of device memory the library currently holds allocations for (pool `used`, not `reserved`)."""
+        v = C.c_uint64()
+        self.check(lib().bsx_ctx_mem_used(self._h, C.byref(v)))
+        return v.value
 
     def sync(self):
         self.check(lib().bsx_ctx_sync(self._h))

@@ -20,7 +20,7 @@ int bsx_fail(bsx_ctx *ctx, int code, const char *fmt, ...) {
     return code;
 }
 
-int bsx_alloc(bsx_ctx *ctx, u64 **p, size_t words) {
+int bsx_alloc_owned(bsx_ctx *ctx, u64 **p, size_t words) {
     *p = nullptr;
     if (words == 0) return BSX_OK;
     cudaError_t e = cudaMallocAsync((void **)p, words * sizeof(u64), ctx->stream);
@@ -32,8 +32,29 @@ int bsx_alloc(bsx_ctx *ctx, u64 **p, size_t words) {
     }
     return BSX_OK;
 }
+int bsx_alloc(bsx_ctx *ctx, u64 **p, size_t words) {
+    TRY(bsx_alloc_owned(ctx, p, words));
+    if (*p && ctx->scope_depth > 0) ctx->scratch.emplace_back(*p, ctx->scratch_seq++);
+    return BSX_OK;
+}
 void bsx_free(bsx_ctx *ctx, u64 *p) {
-    if (p) cudaFreeAsync(p, ctx->stream);
+    if (!p) return;
+    for (size_t i = ctx->scratch.size(); i-- > 0;)
+        if (ctx->scratch[i].first == p) {
+            ctx->scratch.erase(ctx->scratch.begin() + (long)i);
+            break;
+        }
+    cudaFreeAsync(p, ctx->stream);
+}
+// stream-ordered frees: everything the call enqueued before this point has the buffers it needs
+BsxScope::~BsxScope() {
+    if (!ctx) return;
+    for (size_t i = ctx->scratch.size(); i-- > 0;)
+        if (ctx->scratch[i].second >= first) {
+            cudaFreeAsync(ctx->scratch[i].first, ctx->stream);
+            ctx->scratch.erase(ctx->scratch.begin() + (long)i);
+        }
+    ctx->scope_depth--;
 }
 
 int bsx_copy_in(bsx_ctx *ctx, u64 *dst_dev, const u64 *src, size_t words, int mem) {
@@ -60,8 +81,8 @@ int bsx_pow_table(bsx_ctx *ctx, int log_n, int inverse, PowTable *out) {
     u64 w = gl_host_root(log_n);
     if (inverse) w = gl_host_inv(w);
     u64 *lo, *hi;
-    TRY(bsx_alloc(ctx, &lo, 4096));
-    TRY(bsx_alloc(ctx, &hi, 4096));
+    TRY(bsx_alloc_owned(ctx, &lo, 4096));
+    TRY(bsx_alloc_owned(ctx, &hi, 4096));
     launch_fill_powers(lo, w, 1, 4096, ctx->stream);
     launch_fill_powers(hi, gl_host_pow(w, 4096), 1, 4096, ctx->stream);
     CU(ctx, cudaGetLastError());
@@ -94,8 +115,8 @@ int bsx_coset_tables(bsx_ctx *ctx, int log_n, int r_log, u64 shift, const u64 **
     bsx_split(log_n, &a, &b);
     int nc = 1 << r_log;
     u64 *hi, *lo;
-    TRY(bsx_alloc(ctx, &hi, (size_t)2 * nc << a));  // natural order, then the same rows bit-reversed
-    TRY(bsx_alloc(ctx, &lo, (size_t)nc << b));
+    TRY(bsx_alloc_owned(ctx, &hi, (size_t)2 * nc << a));  // natural order, then the same rows bit-reversed
+    TRY(bsx_alloc_owned(ctx, &lo, (size_t)nc << b));
     u64 w = gl_host_root(log_n + r_log);
     for (int k = 0; k < nc; k++) {
         u64 g = gl_host_mul(shift, gl_host_pow(w, (u64)k));
@@ -124,7 +145,7 @@ int bsx_post_table(bsx_ctx *ctx, NttPlan *plan, u64 shift, int n_cols) {
     auto it = ctx->post_tables.find(key);
     if (it == ctx->post_tables.end()) {
         u64 *t;
-        TRY(bsx_alloc(ctx, &t, words));
+        TRY(bsx_alloc_owned(ctx, &t, words));
         launch_ntt_post_table(t, plan->pre_hi ? plan->pre_lo : nullptr, plan->tw, plan->scale, plan->a, plan->b, r_log,
                               ctx->stream);
         CU(ctx, cudaGetLastError());
@@ -174,7 +195,7 @@ extern "C" int32_t bsx_ctx_create(int32_t device, bsx_ctx **out) {
     }
     ntt_init_device();
     u64 *wf = nullptr, *wi = nullptr;
-    if (bsx_alloc(ctx, &wf, 2048) || bsx_alloc(ctx, &wi, 2048)) {
+    if (bsx_alloc_owned(ctx, &wf, 2048) || bsx_alloc_owned(ctx, &wi, 2048)) {
         cudaStreamDestroy(ctx->stream);
         delete ctx;
         return BSX_ERR_OOM;
@@ -216,6 +237,18 @@ extern "C" void bsx_ctx_destroy(bsx_ctx *ctx) {
 
 extern "C" const char *bsx_last_error(const bsx_ctx *ctx) { return ctx ? ctx->err : "null context"; }
 extern "C" void *bsx_ctx_stream(const bsx_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+// bytes of the device's stream-ordered pool currently handed out (all contexts of this process on the device)
+extern "C" int32_t bsx_ctx_mem_used(bsx_ctx *ctx, uint64_t *bytes) {
+    if (!ctx || !bytes) return BSX_ERR_INVALID_ARG;
+    CU(ctx, cudaSetDevice(ctx->device));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaMemPool_t pool;
+    CU(ctx, cudaDeviceGetDefaultMemPool(&pool, ctx->device));
+    unsigned long long used = 0;
+    CU(ctx, cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used));
+    *bytes = used;
+    return BSX_OK;
+}
 extern "C" int32_t bsx_ctx_sync(bsx_ctx *ctx) {
     if (!ctx) return BSX_ERR_INVALID_ARG;
     CU(ctx, cudaStreamSynchronize(ctx->stream));

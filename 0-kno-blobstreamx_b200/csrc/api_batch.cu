@@ -14,8 +14,8 @@ int bsx_tree_alloc(bsx_tree *t) {
     bsx_ctx *ctx = t->ctx;
     t->digests = nullptr;
     t->cap_dev = nullptr;
-    TRY(bsx_alloc(ctx, &t->cap_dev, (size_t)4 << t->cap_height));
-    TRY(bsx_alloc(ctx, &t->digests, n_digest_words(t->log_leaves, t->cap_height)));
+    TRY(bsx_alloc_owned(ctx, &t->cap_dev, (size_t)4 << t->cap_height));
+    TRY(bsx_alloc_owned(ctx, &t->digests, n_digest_words(t->log_leaves, t->cap_height)));
     return BSX_OK;
 }
 
@@ -65,6 +65,7 @@ static int tree_check_shape(bsx_ctx *ctx, int log_leaves, int leaf_len, int cap_
 extern "C" int32_t bsx_merkle_new(bsx_ctx *ctx, const uint64_t *leaves, int32_t mem, int32_t log_leaves,
                                   int32_t leaf_len, int32_t cap_height, bsx_tree **out) {
     if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     *out = nullptr;
     TRY(tree_check_shape(ctx, log_leaves, leaf_len, cap_height));
     if (!leaves && leaf_len > 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "leaves is NULL");
@@ -77,7 +78,7 @@ extern "C" int32_t bsx_merkle_new(bsx_ctx *ctx, const uint64_t *leaves, int32_t 
         TRY(bsx_copy_in(ctx, rowmajor, (const u64 *)leaves, words, mem));
         src = rowmajor;
     }
-    TRY(bsx_alloc(ctx, &colmajor, words));
+    TRY(bsx_alloc_owned(ctx, &colmajor, words));
     launch_transpose(src, colmajor, n, (size_t)leaf_len, ctx->stream);
     bsx_free(ctx, rowmajor);
     bsx_tree *t = new bsx_tree();
@@ -105,6 +106,7 @@ extern "C" int32_t bsx_merkle_new_colmajor_device(bsx_ctx *ctx, const uint64_t *
                                                   int32_t log_leaves, int32_t leaf_len, int32_t cap_height,
                                                   bsx_tree **out) {
     if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     *out = nullptr;
     TRY(tree_check_shape(ctx, log_leaves, leaf_len, cap_height));
     if (col_stride < ((size_t)1 << log_leaves)) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "col_stride too small");
@@ -154,6 +156,7 @@ extern "C" int32_t bsx_merkle_shape(const bsx_tree *t, int32_t *log_leaves, int3
 extern "C" int32_t bsx_merkle_get(bsx_tree *t, const uint64_t *idx_host, int32_t k, uint64_t *out_host) {
     if (!t || k < 0 || (k > 0 && (!idx_host || !out_host))) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = t->ctx;
+    BsxScope scope(ctx);
     if (k == 0 || t->leaf_len == 0) return BSX_OK;
     for (int i = 0; i < k; i++)
         if (idx_host[i] >> t->log_leaves)
@@ -175,6 +178,7 @@ extern "C" int32_t bsx_merkle_get(bsx_tree *t, const uint64_t *idx_host, int32_t
 extern "C" int32_t bsx_merkle_prove(bsx_tree *t, uint64_t leaf_index, uint64_t *siblings_host) {
     if (!t) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = t->ctx;
+    BsxScope scope(ctx);
     if (leaf_index >> t->log_leaves)
         return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "leaf index %llu out of range", (unsigned long long)leaf_index);
     int levels = t->log_leaves - t->cap_height;
@@ -205,6 +209,7 @@ static void to_plonky2_layout(const u64 *lv, size_t n, int height, size_t node, 
 extern "C" int32_t bsx_merkle_digests(bsx_tree *t, uint64_t *out_host) {
     if (!t) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = t->ctx;
+    BsxScope scope(ctx);
     size_t words = n_digest_words(t->log_leaves, t->cap_height);
     if (words == 0) return BSX_OK;
     if (!out_host) return BSX_ERR_INVALID_ARG;
@@ -300,6 +305,7 @@ int bsx_commit_transforms(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols, int 
 static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n_cols, int rate_bits, int cap_height,
                        int blinding, const u64 *salt, bool input_is_coeffs, bsx_batch **out, bsx_timing *timing) {
     if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     *out = nullptr;
     if (log_n < 0 || log_n > 24)
         return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "degree_log=%d outside the supported range [0, 24]", log_n);
@@ -333,8 +339,8 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
     float piped_ifft_ms = 0, piped_lde_ms = 0;
     do {
         pt.mark(0, ctx->stream);
-        if ((rc = bsx_alloc(ctx, &bt->coeffs, n * n_cols))) break;
-        if ((rc = bsx_alloc(ctx, &bt->lde, nb * (size_t)(n_cols + n_salt)))) break;
+        if ((rc = bsx_alloc_owned(ctx, &bt->coeffs, n * n_cols))) break;
+        if ((rc = bsx_alloc_owned(ctx, &bt->lde, nb * (size_t)(n_cols + n_salt)))) break;
         // salt columns first: nothing below depends on them except the leaf hashing
         if (n_salt) {
             u64 *dst = bt->lde + nb * (size_t)n_cols;
@@ -489,6 +495,7 @@ static inline u64 host_bitrev(u64 x, int bits) {
 extern "C" int32_t bsx_batch_get_lde_values(bsx_batch *b, uint64_t index, uint64_t step, uint64_t *out_host) {
     if (!b) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = b->ctx;
+    BsxScope scope(ctx);
     int log_nb = b->log_n + b->rate_bits;
     u64 i = index * step;
     if (i >> log_nb) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "index * step out of range");
@@ -513,6 +520,7 @@ extern "C" int32_t bsx_batch_get_lde_values_packed(bsx_batch *b, uint64_t index_
                                                    uint64_t *out, int32_t mem) {
     if (!b) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = b->ctx;
+    BsxScope scope(ctx);
     const int log_nb = b->log_n + b->rate_bits;
     if (count == 0 || b->n_cols == 0) return BSX_OK;
     if (!out) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "output is NULL");
@@ -544,6 +552,7 @@ extern "C" int32_t bsx_batch_get_lde_values_packed(bsx_batch *b, uint64_t index_
 extern "C" int32_t bsx_batch_coeffs(bsx_batch *b, uint64_t *out, int32_t mem) {
     if (!b || (!out && b->n_cols > 0)) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = b->ctx;
+    BsxScope scope(ctx);
     size_t n = (size_t)1 << b->log_n, words = n * (size_t)b->n_cols;
     if (words == 0) return BSX_OK;
     CU(ctx, cudaSetDevice(ctx->device));
@@ -564,6 +573,7 @@ extern "C" int32_t bsx_batch_export(bsx_batch *b, uint64_t *coeffs_host, uint64_
                                     uint64_t *digests_host) {
     if (!b) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = b->ctx;
+    BsxScope scope(ctx);
     if (coeffs_host) TRY(bsx_batch_coeffs(b, coeffs_host, BSX_HOST));
     if (leaves_host) {
         size_t nb = (size_t)1 << (b->log_n + b->rate_bits), w = (size_t)(b->n_cols + b->n_salt);
@@ -600,6 +610,7 @@ extern "C" int32_t bsx_batch_import(bsx_ctx *ctx, const uint64_t *coeffs_host, c
                                     int32_t n_cols, int32_t n_salt, int32_t rate_bits, int32_t cap_height,
                                     bsx_batch **out) {
     if (!ctx || !out) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     *out = nullptr;
     if (log_n < 0 || log_n > 24)
         return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "degree_log=%d outside the supported range [0, 24]", log_n);
@@ -637,8 +648,8 @@ extern "C" int32_t bsx_batch_import(bsx_ctx *ctx, const uint64_t *coeffs_host, c
     u64 *tmp = nullptr;
     int rc = BSX_OK;
     do {
-        if ((rc = bsx_alloc(ctx, &bt->coeffs, n * n_cols))) break;
-        if ((rc = bsx_alloc(ctx, &bt->lde, nb * w))) break;
+        if ((rc = bsx_alloc_owned(ctx, &bt->coeffs, n * n_cols))) break;
+        if ((rc = bsx_alloc_owned(ctx, &bt->lde, nb * w))) break;
         if ((rc = bsx_tree_alloc(&bt->tree))) break;
         bt->tree.leaves = bt->lde;
         if ((rc = bsx_copy_in(ctx, bt->coeffs, (const u64 *)coeffs_host, n * n_cols, BSX_HOST))) break;
@@ -676,6 +687,7 @@ extern "C" int32_t bsx_batch_import(bsx_ctx *ctx, const uint64_t *coeffs_host, c
 // ------------------------------------------------------------------------------------ test hooks
 extern "C" int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n) {
     if (!ctx || (!states && n)) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     if (n == 0) return BSX_OK;
     CU(ctx, cudaSetDevice(ctx->device));
     u64 *d = (u64 *)states;
@@ -696,6 +708,7 @@ extern "C" int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t 
 extern "C" int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t log_n, int32_t n_cols, int32_t kind,
                            uint64_t shift) {
     if (!ctx || (!data && n_cols > 0)) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     if (log_n < 0 || log_n > 24) return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "log_n=%d outside [0, 24]", log_n);
     if (kind < 0 || kind > 2 || n_cols < 0 || n_cols > 65535) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad kind/n_cols");
     if (n_cols == 0) return BSX_OK;

@@ -89,6 +89,7 @@ static int chal_download(bsx_ctx *ctx, bsx_challenger *ch, u64 *dev) {
 
 extern "C" int32_t bsx_challenger_observe(bsx_ctx *ctx, bsx_challenger *ch, const uint64_t *elems_host, size_t n) {
     if (!ctx || !ch || (!elems_host && n)) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     if (n == 0) return BSX_OK;
     CU(ctx, cudaSetDevice(ctx->device));
     u64 *dev, *data;
@@ -102,6 +103,7 @@ extern "C" int32_t bsx_challenger_observe(bsx_ctx *ctx, bsx_challenger *ch, cons
 
 extern "C" int32_t bsx_challenger_get(bsx_ctx *ctx, bsx_challenger *ch, uint64_t *out_host, int32_t n) {
     if (!ctx || !ch || n < 0 || (!out_host && n)) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     if (n == 0) return BSX_OK;
     CU(ctx, cudaSetDevice(ctx->device));
     u64 *dev, *out;
@@ -197,6 +199,7 @@ static int final_poly_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_orac
 extern "C" int32_t bsx_fri_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
                                       const bsx_fri_instance *instance, const uint64_t alpha[2], uint64_t *out_host) {
     if (!ctx || !oracles || n_oracles <= 0 || !alpha || !out_host) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     CU(ctx, cudaSetDevice(ctx->device));
     const int log_n = oracles[0]->log_n;
     const size_t n = (size_t)1 << log_n;
@@ -360,6 +363,7 @@ static int fri_proof_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracl
 static int fri_run(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracles, const bsx_fri_instance *inst,
                    const u64 *lde_coeffs_host, bsx_challenger *ch, const bsx_fri_params *p, u64 *proof_host) {
     if (!ctx || !ch || !p || !proof_host) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     FriLayout L;
     TRY(fri_layout(ctx, oracles, n_oracles, p, &L));
     CU(ctx, cudaSetDevice(ctx->device));
@@ -420,6 +424,7 @@ extern "C" int32_t bsx_batch_eval_ext(bsx_batch *b, int32_t col_begin, int32_t n
                                       int32_t n_points, uint64_t *out_host) {
     if (!b) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = b->ctx;
+    BsxScope scope(ctx);
     if (col_begin < 0 || n_cols < 0 || col_begin + n_cols > b->n_cols)
         return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "polynomial range %d..%d outside the batch (%d polynomials)", col_begin,
                         col_begin + n_cols, b->n_cols);

@@ -27,6 +27,10 @@ struct bsx_ctx {
     std::map<int, PowTable> pow_tables;
     std::map<CosetKey, std::pair<const u64 *, const u64 *>> coset_tables;
     std::map<CosetKey, const u64 *> post_tables;  // key.shift = 0: inverse transform, no coset
+    // scratch allocations of the ABI call in progress (see BsxScope): pointer + sequence number
+    std::vector<std::pair<u64 *, unsigned long long>> scratch;
+    unsigned long long scratch_seq = 0;
+    int scope_depth = 0;
 };
 
 // plonky2 hash/merkle_tree.rs MerkleTree { leaves, digests, cap }, device resident.
@@ -53,8 +57,22 @@ struct bsx_batch {
 };
 
 int bsx_fail(bsx_ctx *ctx, int code, const char *fmt, ...);
+// bsx_alloc: temporaries of the running ABI call -- whatever is still allocated when the call's BsxScope ends
+// (an early return on an error path) is freed there.  bsx_alloc_owned: buffers that outlive the call (batch, tree,
+// table and shard members); their owners free them.  bsx_free takes either kind.
 int bsx_alloc(bsx_ctx *ctx, u64 **p, size_t words);
+int bsx_alloc_owned(bsx_ctx *ctx, u64 **p, size_t words);
 void bsx_free(bsx_ctx *ctx, u64 *p);
+struct BsxScope {
+    bsx_ctx *ctx;
+    unsigned long long first;
+    explicit BsxScope(bsx_ctx *c) : ctx(c), first(c ? c->scratch_seq : 0) {
+        if (ctx) ctx->scope_depth++;
+    }
+    ~BsxScope();
+    BsxScope(const BsxScope &) = delete;
+    BsxScope &operator=(const BsxScope &) = delete;
+};
 int bsx_copy_in(bsx_ctx *ctx, u64 *dst_dev, const u64 *src, size_t words, int mem);
 int bsx_copy_out(bsx_ctx *ctx, u64 *dst, const u64 *src_dev, size_t words, int mem);
 int bsx_pow_table(bsx_ctx *ctx, int log_n, int inverse, PowTable *out);

@@ -167,7 +167,7 @@ extern "C" int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int3
     D.n = s->n_ranks;
     D.lc = s->log_n + s->rate_bits - s->log_ranks;
     if (use_staging) {
-        if (!s->staging) TRY(bsx_alloc(ctx, &s->staging, nb * (size_t)n_local));
+        if (!s->staging) TRY(bsx_alloc_owned(ctx, &s->staging, nb * (size_t)n_local));
         for (int d = 0; d < s->n_ranks; d++) D.ptr[d] = s->staging + (size_t)d * s->chunk * n_local;
     } else {
         for (int d = 0; d < s->n_ranks; d++) {
@@ -185,7 +185,7 @@ extern "C" int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int3
     int rc = BSX_OK;
     do {
         if (n_local == 0) break;
-        if ((rc = bsx_alloc(ctx, &s->coeffs, n * n_local))) break;
+        if ((rc = bsx_alloc_owned(ctx, &s->coeffs, n * n_local))) break;
         if ((rc = bsx_copy_in(ctx, s->coeffs, (const u64 *)input, n * n_local, mem))) break;
         if (timing) cudaEventRecord(ev[0], ctx->stream);
         // the two-pass transforms keep their intermediate in a local column-major scratch; single-pass
@@ -236,6 +236,7 @@ extern "C" int32_t bsx_shard_shape(const bsx_shard *s, int32_t *c0, int32_t *c1,
 extern "C" int32_t bsx_shard_coeffs(bsx_shard *s, uint64_t *out, int32_t mem) {
     if (!s) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = s->ctx;
+    BsxScope scope(ctx);
     size_t n = (size_t)1 << s->log_n, words = n * (size_t)(s->c1 - s->c0);
     if (words == 0) return BSX_OK;
     if (!out || !s->coeffs) return BSX_ERR_INVALID_ARG;
@@ -260,6 +261,7 @@ extern "C" int32_t bsx_merkle_reduce(bsx_ctx *ctx, const uint64_t *digests_host,
     if (!ctx || !digests_host || !out_host || n_in <= 0 || levels < 0 || (n_in >> levels) == 0 ||
         ((n_in >> levels) << levels) != n_in)
         return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
     CU(ctx, cudaSetDevice(ctx->device));
     u64 *a, *b;
     TRY(bsx_alloc(ctx, &a, (size_t)4 * n_in));

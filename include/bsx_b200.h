@@ -63,6 +63,9 @@ const char *bsx_last_error(const bsx_ctx *ctx);
 /* the CUDA stream all work of this ctx runs on (cudaStream_t as void*), for event timing */
 void *bsx_ctx_stream(const bsx_ctx *ctx);
 int32_t bsx_ctx_sync(bsx_ctx *ctx);
+/* Device memory currently handed out by the stream-ordered pool the library allocates from (bytes; batches,
+ * trees, cached tables).  A failed call leaves this unchanged: its temporaries are released on every path. */
+int32_t bsx_ctx_mem_used(bsx_ctx *ctx, uint64_t *bytes);
 
 /* ---- PolynomialBatch (fri/oracle.rs) ------------------------------------------------------
  * from_values: values = n_cols column vectors of 2^log_n evaluations on the subgroup, column-major

@@ -119,3 +119,25 @@ def test_fri_errors(pkg, ctx):
     fp = pkg.FriConfig(rate_bits=1, cap_height=0, proof_of_work_bits=1, num_query_rounds=1).fri_params(6)
     with pytest.raises(pkg.BsxError, match="does not exist"):
         pkg.prove_openings(inst, [b], pkg.Challenger(ctx), fp)
+
+
+def test_failed_calls_release_their_temporaries(pkg, ctx, oracle):
+    """Error paths (upstream: panics) must not leak device memory: pool usage is unchanged after a failed call."""
+    ob, gb, points, polys = _setup(pkg, ctx, oracle, 10, 1, 0, [3, 2])
+    params = pkg.FriConfig(rate_bits=1, cap_height=0, proof_of_work_bits=4, num_query_rounds=3).fri_params(10)
+    good = pkg.FriInstanceInfo(points, polys)
+    ch = pkg.Challenger(ctx)
+    pkg.prove_openings(good, gb, ch, params)  # warm: cached tables are allocated once
+    used = ctx.mem_used()
+    bad = pkg.FriInstanceInfo(points, [polys[0][:-1] + [(0, 99)], polys[1]])  # polynomial index out of range
+    for _ in range(3):
+        with pytest.raises(pkg.BsxError):
+            pkg.prove_openings(bad, gb, pkg.Challenger(ctx), params)
+    assert ctx.mem_used() == used
+    with pytest.raises(pkg.BsxError):  # 2^24 x 60000 words cannot be allocated
+        pkg.PolynomialBatch.from_values(ctx, None, 3, False, 4, device_ptr=1 << 40, shape=(60000, 1 << 24))
+    assert ctx.mem_used() == used
+    pkg.prove_openings(good, gb, pkg.Challenger(ctx), params)
+    assert ctx.mem_used() == used
+    for b in gb:
+        b.close()
