@@ -1,0 +1,135 @@
+/* abi_harness.c -- a plain C11 caller of include/bsx_b200.h: what a non-Python host (the Rust shim's FFI, a C++
+ * prover) does through the drop-in boundary.  No Python, no torch; links libbsx_b200.so only.
+ *
+ *   abi_harness <log_n> <n_cols> <rate_bits> <cap_height> <seed>
+ *
+ * Commits a SplitMix64 witness from host memory, then prints, one record per line (hex words):
+ *   cap <2^cap_height x 4 words>
+ *   row <leaf> <n_cols words>          for three leaves
+ *   path <leaf> <siblings x 4 words>
+ *   eval <n_cols x 2 words>            all polynomials at the extension point (seed, seed + 1)
+ *   proof <words>                      prove_openings of every polynomial at that point
+ * tests/test_gpu_c_abi.py recomputes every record with the oracle. */
+#include <inttypes.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "bsx_b200.h"
+
+#define P 0xFFFFFFFF00000001ULL
+
+static uint64_t splitmix(uint64_t seed, uint64_t i) {
+    uint64_t z = seed + (i + 1) * 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    z ^= z >> 31;
+    return z % P;
+}
+
+#define CHECK(ctx, call)                                                                 \
+    do {                                                                                 \
+        int32_t rc_ = (call);                                                            \
+        if (rc_ != BSX_OK) {                                                             \
+            fprintf(stderr, "%s -> %d: %s\n", #call, (int)rc_, bsx_last_error(ctx));     \
+            return 1;                                                                    \
+        }                                                                                \
+    } while (0)
+
+static void print_words(const char *tag, long long k, const uint64_t *w, size_t n) {
+    if (k >= 0) printf("%s %lld", tag, k);
+    else printf("%s", tag);
+    for (size_t i = 0; i < n; i++) printf(" %016" PRIx64, w[i]);
+    printf("\n");
+}
+
+int main(int argc, char **argv) {
+    if (argc != 6) {
+        fprintf(stderr, "usage: %s log_n n_cols rate_bits cap_height seed\n", argv[0]);
+        return 2;
+    }
+    const int log_n = atoi(argv[1]), n_cols = atoi(argv[2]), rate_bits = atoi(argv[3]), cap_height = atoi(argv[4]);
+    const uint64_t seed = strtoull(argv[5], NULL, 0);
+    const size_t n = (size_t)1 << log_n, nb = n << rate_bits;
+
+    bsx_ctx *ctx = NULL;
+    if (bsx_ctx_create(0, &ctx) != BSX_OK) {
+        fprintf(stderr, "bsx_ctx_create failed (no CUDA device? there is no CPU fallback)\n");
+        return 1;
+    }
+    uint64_t *values = malloc(sizeof(uint64_t) * n * (size_t)n_cols);
+    for (size_t i = 0; i < n * (size_t)n_cols; i++) values[i] = splitmix(seed, i);
+
+    bsx_batch *batch = NULL;
+    bsx_timing tm;
+    CHECK(ctx, bsx_batch_from_values(ctx, values, BSX_HOST, log_n, n_cols, rate_bits, cap_height, 0, NULL, &batch, &tm));
+    free(values);
+
+    uint64_t *cap = malloc(sizeof(uint64_t) * ((size_t)4 << cap_height));
+    CHECK(ctx, bsx_batch_cap(batch, cap));
+    print_words("cap", -1, cap, (size_t)4 << cap_height);
+
+    bsx_tree *tree = bsx_batch_tree(batch);
+    const int n_sib = log_n + rate_bits - cap_height;
+    uint64_t *row = malloc(sizeof(uint64_t) * (size_t)n_cols), *sib = malloc(sizeof(uint64_t) * 4 * (size_t)(n_sib + 1));
+    const uint64_t leaves[3] = {0, nb / 3, nb - 1};
+    for (int k = 0; k < 3; k++) {
+        CHECK(ctx, bsx_merkle_get(tree, &leaves[k], 1, row));
+        print_words("row", (long long)leaves[k], row, (size_t)n_cols);
+        CHECK(ctx, bsx_merkle_prove(tree, leaves[k], sib));
+        print_words("path", (long long)leaves[k], sib, 4 * (size_t)n_sib);
+    }
+
+    const uint64_t z[2] = {seed % P, (seed + 1) % P};
+    uint64_t *ev = malloc(sizeof(uint64_t) * 2 * (size_t)n_cols);
+    CHECK(ctx, bsx_batch_eval_ext(batch, 0, n_cols, z, 1, ev));
+    print_words("eval", -1, ev, 2 * (size_t)n_cols);
+
+    /* prove_openings: one opening batch holding every polynomial, standard FRI shape scaled to this size */
+    bsx_fri_params fp;
+    memset(&fp, 0, sizeof(fp));
+    fp.degree_bits = log_n;
+    fp.rate_bits = rate_bits;
+    fp.cap_height = cap_height;
+    fp.proof_of_work_bits = 8;
+    fp.num_query_rounds = 4;
+    int db = log_n;
+    while (db > 5 && db + rate_bits - 4 >= cap_height && fp.n_arity < 16) { /* ConstantArityBits(4, 5) */
+        fp.arity_bits[fp.n_arity++] = 4;
+        db -= 4;
+    }
+    bsx_fri_instance inst;
+    memset(&inst, 0, sizeof(inst));
+    int32_t *po = malloc(sizeof(int32_t) * (size_t)n_cols), *pi = malloc(sizeof(int32_t) * (size_t)n_cols);
+    for (int j = 0; j < n_cols; j++) {
+        po[j] = 0;
+        pi[j] = j;
+    }
+    int32_t n_polys[1] = {n_cols};
+    inst.n_batches = 1;
+    inst.points = z;
+    inst.n_polys = n_polys;
+    inst.poly_oracle = po;
+    inst.poly_index = pi;
+    bsx_challenger ch;
+    bsx_challenger_init(&ch);
+    CHECK(ctx, bsx_challenger_observe(ctx, &ch, cap, (size_t)4 << cap_height));
+    CHECK(ctx, bsx_challenger_observe(ctx, &ch, ev, 2 * (size_t)n_cols));
+    bsx_batch *oracles[1] = {batch};
+    size_t words = 0;
+    CHECK(ctx, bsx_fri_proof_words(oracles, 1, &fp, &words));
+    uint64_t *proof = malloc(sizeof(uint64_t) * words);
+    CHECK(ctx, bsx_fri_prove_openings(ctx, oracles, 1, &inst, &ch, &fp, proof));
+    print_words("proof", -1, proof, words);
+
+    /* misuse is reported, not fatal: upstream panics with this message */
+    bsx_batch *bad = NULL;
+    uint64_t one = 1;
+    int32_t rc = bsx_batch_from_values(ctx, &one, BSX_HOST, 0, 1, 1, 5, 0, NULL, &bad, NULL);
+    printf("misuse %d %s\n", (int)rc, bsx_last_error(ctx));
+
+    free(proof); free(po); free(pi); free(ev); free(row); free(sib); free(cap);
+    bsx_batch_free(batch);
+    bsx_ctx_destroy(ctx);
+    return 0;
+}

@@ -60,3 +60,16 @@ def test_fri_reduction_strategy(pkg):
     assert pkg.fri_reduction_arity_bits(5, 3, 4) == []
     p = pkg.FriConfig().fri_params(20)
     assert p.lde_bits() == 23 and p.final_poly_len() == 16
+
+
+def test_header_is_plain_c_and_links():
+    """include/bsx_b200.h compiles as C11 (-Wall -Wextra -Werror) and a C program links against the library using
+    nothing else.  Without a GPU the program must fail loudly at bsx_ctx_create (no CPU fallback)."""
+    import subprocess
+    import c_harness_build
+    exe = c_harness_build.build()
+    r = subprocess.run([exe, "5", "3", "1", "1", "7"], capture_output=True, text=True, timeout=120)
+    if r.returncode != 0:
+        assert r.returncode == 1 and "no CPU fallback" in r.stderr, r.stderr
+    else:
+        assert r.stdout.startswith("cap ")

@@ -1,0 +1,57 @@
+"""The drop-in boundary driven from plain C (tests/c_harness/abi_harness.c): every record the C program prints is
+recomputed with the oracle -- commit, openings, Merkle paths, the opening set and a whole FRI proof."""
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import P, splitmix_field
+import c_harness_build
+
+pytestmark = pytest.mark.gpu
+
+
+def _words(tok):
+    return np.array([int(t, 16) for t in tok], dtype=np.uint64)
+
+
+@pytest.mark.parametrize("log_n,n_cols,rate_bits,cap_height,seed", [(10, 5, 3, 4, 11), (13, 20, 1, 0, 12), (6, 1, 2, 2, 13)])
+def test_c_program_matches_oracle(oracle, log_n, n_cols, rate_bits, cap_height, seed):
+    exe = c_harness_build.build()
+    r = subprocess.run([exe, str(log_n), str(n_cols), str(rate_bits), str(cap_height), str(seed)], capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    rec = [ln.split() for ln in r.stdout.strip().splitlines()]
+    vals = splitmix_field(seed, (n_cols, 1 << log_n))  # same SplitMix64 stream as the C program
+    want = oracle.batch_from_values(vals, rate_bits, cap_height)
+    log_nb = log_n + rate_bits
+    by = {}
+    for t in rec:
+        by.setdefault(t[0], []).append(t[1:])
+    assert (_words(by["cap"][0]).reshape(-1, 4) == want["cap"]).all()
+    assert len(by["row"]) == 3 and len(by["path"]) == 3
+    for row, path in zip(by["row"], by["path"]):
+        leaf = int(row[0])
+        assert int(path[0]) == leaf
+        assert (_words(row[1:]) == want["leaves"][leaf]).all()
+        sib = _words(path[1:]).reshape(-1, 4)
+        if want["digests"] is not None and sib.size:
+            assert (sib == np.asarray(oracle.merkle_prove(want["digests"], log_nb, cap_height, leaf)).reshape(-1, 4)).all()
+        assert oracle.merkle_verify(want["leaves"][leaf], leaf, sib, want["cap"])
+    z = np.array([seed % P, (seed + 1) % P], dtype=np.uint64)
+    ev = _words(by["eval"][0]).reshape(n_cols, 2)
+    for j in range(n_cols):
+        assert (ev[j] == oracle.eval_poly_ext(want, j, z, rate_bits, cap_height)).all()
+    # the FRI proof: same challenger transcript as the C program
+    ch = oracle.Challenger()
+    ch.observe(want["cap"].reshape(-1))
+    ch.observe(ev.reshape(-1))
+    arity, db = [], log_n
+    while db > 5 and db + rate_bits - 4 >= cap_height:
+        arity.append(4)
+        db -= 4
+    points, polys = z.reshape(1, 2), [[(0, j) for j in range(n_cols)]]
+    proof = oracle.fri_prove_openings([want], points, polys, ch, log_n, rate_bits, cap_height, 8, 4, arity)
+    assert (_words(by["proof"][0]) == proof).all()
+    misuse = by["misuse"][0]
+    assert int(misuse[0]) == -1 and "cap_height=5 should be at most log2(leaves.len())=1" in " ".join(misuse[1:])
