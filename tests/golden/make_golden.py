@@ -1,0 +1,119 @@
+#!/usr/bin/env python3
+"""Writes tests/golden/golden_vectors.json from the CPU oracle.
+
+What these vectors are: FROZEN outputs of the in-repo restatement of the plonky2 algorithm (oracle/), so that
+(a) the oracle cannot drift silently, (b) the CUDA path is checked against committed numbers and not only against
+whatever the oracle computes today, and (c) a maintainer with a plonky2 checkout can diff them against the real
+crate (the reference mount holds no source: SURVEY.md section 0).  Only `poseidon.zeros` is independently pinned
+(the published plonky2 known-answer vector); everything else is the oracle's own output -- "parity unpinned".
+
+Inputs are SplitMix64 streams reduced mod p (tests/conftest.py `splitmix_field`), so any implementation can
+regenerate them from the seeds stored with each case.  Run:  python tests/golden/make_golden.py"""
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from conftest import P, splitmix_field  # noqa: E402
+from oracle import oracle as O  # noqa: E402
+
+
+def hx(a):
+    return ["%016x" % int(x) for x in np.asarray(a, dtype=np.uint64).reshape(-1)]
+
+
+def digest(a):
+    return hashlib.sha256(np.ascontiguousarray(a, dtype="<u8").tobytes()).hexdigest()
+
+
+def arity_bits(degree_bits, rate_bits, cap_height, arity=4, final=5):
+    out = []
+    while degree_bits > final and degree_bits + rate_bits - arity >= cap_height:
+        out.append(arity)
+        degree_bits -= arity
+    return out
+
+
+def main():
+    g = {"p": "%016x" % P, "note": "see make_golden.py; only poseidon.zeros is pinned by a published vector"}
+    g["field"] = {"root_of_unity_32": "%016x" % O.lib().orc_root_of_unity(32),
+                  "root_of_unity_20": "%016x" % O.lib().orc_root_of_unity(20),
+                  "inv_7": "%016x" % O.lib().orc_inv(7), "mul_edge": "%016x" % O.lib().orc_mul(P - 1, P - 2)}
+    g["poseidon"] = {"zeros": hx(O.poseidon(np.zeros(12, np.uint64))),
+                     "iota": hx(O.poseidon(np.arange(12, dtype=np.uint64))),
+                     "neg_one": hx(O.poseidon(np.full(12, P - 1, dtype=np.uint64))),
+                     "seed_41": hx(O.poseidon(splitmix_field(41, (12,))))}
+    x = splitmix_field(42, (8,))
+    g["ntt"] = {"seed": 42, "n": 8, "fft": hx(O.fft(x)), "ifft": hx(O.ifft(x)), "coset_fft_7": hx(O.coset_fft(x, 7)),
+                "lde_rate1": hx(O.lde(x, 1, 7))}
+    x = splitmix_field(43, (1 << 12,))
+    g["ntt_4096"] = {"seed": 43, "fft_sha256": digest(O.fft(x)), "ifft_sha256": digest(O.ifft(x)),
+                     "coset_fft_sha256": digest(O.coset_fft(x, 7))}
+    data = splitmix_field(44, (23,))
+    g["hash_no_pad"] = {"seed": 44, "by_len": {str(k): hx(O.hash_no_pad(data[:k])) for k in (0, 1, 4, 5, 8, 9, 16, 17, 23)}}
+    g["hash_or_noop"] = {"seed": 44, "by_len": {str(k): hx(O.hash_or_noop(data[:k])) for k in (0, 3, 4, 5)}}
+    g["two_to_one"] = {"seed": 44, "out": hx(O.two_to_one(data[:4], data[4:8]))}
+    g["merkle"] = []
+    for log_leaves, leaf_len, cap_height in ((0, 3, 0), (3, 2, 0), (4, 7, 2), (6, 135, 4), (5, 4, 5)):
+        leaves = splitmix_field(45 + log_leaves, (1 << log_leaves, leaf_len))
+        digests, cap = O.merkle_build(leaves, cap_height)
+        case = {"seed": 45 + log_leaves, "log_leaves": log_leaves, "leaf_len": leaf_len, "cap_height": cap_height,
+                "cap": hx(cap), "digests_plonky2_sha256": digest(O.merkle_digests_to_plonky2(digests, log_leaves, cap_height))}
+        if log_leaves > cap_height:
+            case["proof_leaf_1"] = hx(O.merkle_prove(digests, log_leaves, cap_height, 1))
+        g["merkle"].append(case)
+    g["commit"] = []
+    for log_n, n_cols, rate_bits, cap_height, from_coeffs, salted in (
+            (3, 2, 1, 0, False, False), (5, 7, 2, 1, False, False), (8, 135, 3, 4, False, False),
+            (10, 9, 3, 4, True, False), (6, 5, 1, 2, False, True), (12, 20, 3, 4, False, False)):
+        seed = 0x5EED0000 + log_n
+        vals = splitmix_field(seed, (n_cols, 1 << log_n))
+        salt = splitmix_field(seed + 1, (4, 1 << (log_n + rate_bits))) if salted else None
+        b = O.batch_from_values(vals, rate_bits, cap_height, salt=salt, from_coeffs=from_coeffs)
+        z = splitmix_field(seed + 2, (2,))
+        g["commit"].append({
+            "seed": seed, "log_n": log_n, "n_cols": n_cols, "rate_bits": rate_bits, "cap_height": cap_height,
+            "from_coeffs": from_coeffs, "salt_seed": seed + 1 if salted else None, "cap": hx(b["cap"]),
+            "coeffs_sha256": digest(b["coeffs"]), "leaves_sha256": digest(b["leaves"]),
+            "digests_plonky2_sha256": digest(O.merkle_digests_to_plonky2(b["digests"], log_n + rate_bits, cap_height)),
+            "leaf_1": hx(b["leaves"][1]), "eval_point": hx(z), "eval_poly_0": hx(O.eval_poly_ext(b, 0, z, rate_bits, cap_height))})
+    ch = O.Challenger()
+    xs = splitmix_field(46, (29,))
+    tr = []
+    for lo, hi, k in ((0, 3, 2), (3, 11, 1), (11, 12, 9), (12, 29, 3)):
+        ch.observe(xs[lo:hi])
+        tr.append({"observe": [lo, hi], "challenges": hx([ch.get_challenge() for _ in range(k)])})
+    g["challenger"] = {"seed": 46, "transcript": tr, "ext_challenge": hx(ch.get_extension_challenge())}
+    g["fri"] = []
+    for degree_bits, widths, rate_bits, cap_height, pow_bits, nq in ((5, (2, 2), 1, 0, 4, 3), (10, (5, 3, 2), 3, 2, 8, 5),
+                                                                      (13, (9, 4), 1, 4, 10, 28)):
+        batches = [O.batch_from_values(splitmix_field(47 + degree_bits + i, (w, 1 << degree_bits)), rate_bits, cap_height)
+                   for i, w in enumerate(widths)]
+        zeta = splitmix_field(48 + degree_bits, (2,))
+        gen = O.lib().orc_root_of_unity(degree_bits)
+        gz = np.array([O.lib().orc_mul(int(zeta[0]), gen), O.lib().orc_mul(int(zeta[1]), gen)], dtype=np.uint64)
+        points = np.stack([zeta, gz])
+        polys = [[(o, j) for o, w in enumerate(widths) for j in range(w)], [(0, j) for j in range(min(2, widths[0]))]]
+        ch = O.Challenger()
+        for b in batches:
+            ch.observe(b["cap"].reshape(-1))
+        ab = arity_bits(degree_bits, rate_bits, cap_height)
+        proof = O.fri_prove_openings(batches, points, polys, ch, degree_bits, rate_bits, cap_height, pow_bits, nq, ab)
+        g["fri"].append({"degree_bits": degree_bits, "widths": list(widths), "seed_base": 47 + degree_bits,
+                         "zeta_seed": 48 + degree_bits, "rate_bits": rate_bits, "cap_height": cap_height,
+                         "proof_of_work_bits": pow_bits, "num_query_rounds": nq, "arity_bits": ab,
+                         "proof_words": int(proof.size), "proof_sha256": digest(proof), "first_cap_word": hx(proof[:1]),
+                         "pow_witness": hx(proof[-1:]), "challenger_after": hx(list(ch.state))})
+    with open(os.path.join(HERE, "golden_vectors.json"), "w") as f:
+        json.dump(g, f, indent=1)
+    print("wrote golden_vectors.json: %d commit cases, %d fri cases" % (len(g["commit"]), len(g["fri"])))
+
+
+if __name__ == "__main__":
+    main()
