@@ -6,7 +6,7 @@
 #include "internal.h"
 #include "poseidon.cuh"
 
-// ------------------------------------------------------------------ challenger (single thread)
+// ------------------------------------------------------------------ challenger (one warp)
 // Layout identical to include/bsx_b200.h bsx_challenger.
 struct DevChallenger {
     u64 state[12];
@@ -15,38 +15,106 @@ struct DevChallenger {
     int n_in, n_out;
 };
 
-__device__ void chal_duplex(DevChallenger *c) {
-    u64 s[12];
-    for (int i = 0; i < 12; i++) s[i] = c->state[i];
-    for (int i = 0; i < c->n_in; i++) s[i] = c->in[i];  // overwrite mode
-    c->n_in = 0;
-    poseidon_permute(s);
-    for (int i = 0; i < 12; i++) c->state[i] = s[i];
-    for (int i = 0; i < 8; i++) c->out[i] = s[i];
-    c->n_out = 8;
+// The Fiat-Shamir transcript is a chain of dependent permutations, so what counts is the LATENCY of one
+// permutation: a single thread takes ~39 us (30 rounds x 12 S-boxes back to back).  Here lane i < 12 of one warp
+// owns state word i: the twelve S-boxes of a full round run side by side and the MDS row of every lane is
+// gathered with shuffles (Poseidon::poseidon in its naive form, hash/poseidon.rs `poseidon_naive`; all words
+// canonical).  ~5 us per permutation.
+__device__ __forceinline__ u64 poseidon_permute_warp(u64 x, int lane) {
+    const u32 C[12] = {17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20};
+    const int me = lane < 12 ? lane : 0;
+    for (int r = 0; r < 30; r++) {
+        x = gl_add(x, POSEIDON_RC[12 * r + me]);
+        const bool full = r < 4 || r >= 26;
+        if (full || lane == 0) {
+            u64 x2 = gl_mul(x, x), x4 = gl_mul(x2, x2);
+            x = gl_mul(gl_mul(x, x2), x4);
+        }
+        // y[lane] = sum_i C[i] x[(lane + i) % 12] (+ 8 x[0] for lane 0), on 32-bit halves
+        const u32 lo = (u32)x, hi = (u32)(x >> 32);
+        u64 al = 0, ah = 0;
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            int src = me + i;
+            src = src >= 12 ? src - 12 : src;
+            al += (u64)C[i] * __shfl_sync(0xFFFFFFFFu, lo, src);
+            ah += (u64)C[i] * __shfl_sync(0xFFFFFFFFu, hi, src);
+        }
+        if (lane == 0) {
+            al += (u64)8 * lo;
+            ah += (u64)8 * hi;
+        }
+        x = gl_canon(poseidon_fold96(al, ah));
+    }
+    return x;
 }
-__device__ void chal_observe(DevChallenger *c, u64 x) {
-    c->n_out = 0;
-    c->in[c->n_in++] = x;
-    if (c->n_in == 8) chal_duplex(c);
+
+// every function below is executed by all 32 lanes of the kernel's single warp on a challenger in shared memory
+__device__ void chal_duplex(DevChallenger *c, int lane) {
+    __syncwarp();
+    u64 x = lane < 12 ? c->state[lane] : 0;
+    if (lane < c->n_in) x = c->in[lane];  // overwrite mode
+    x = poseidon_permute_warp(x, lane);
+    __syncwarp();
+    if (lane < 12) c->state[lane] = x;
+    if (lane < 8) c->out[lane] = x;
+    if (lane == 0) {
+        c->n_in = 0;
+        c->n_out = 8;
+    }
+    __syncwarp();
 }
-__device__ u64 chal_get(DevChallenger *c) {
-    if (c->n_in != 0 || c->n_out == 0) chal_duplex(c);
-    return c->out[--c->n_out];
+__device__ void chal_observe(DevChallenger *c, u64 x, int lane) {
+    const int n_in = c->n_in;  // uniform
+    __syncwarp();
+    if (lane == 0) {
+        c->n_out = 0;
+        c->in[n_in] = x;
+        c->n_in = n_in + 1;
+    }
+    __syncwarp();
+    if (n_in + 1 == 8) chal_duplex(c, lane);
+}
+__device__ u64 chal_get(DevChallenger *c, int lane) {
+    if (c->n_in != 0 || c->n_out == 0) chal_duplex(c, lane);
+    const int n_out = c->n_out;  // uniform
+    const u64 v = c->out[n_out - 1];
+    __syncwarp();
+    if (lane == 0) c->n_out = n_out - 1;
+    __syncwarp();
+    return v;
+}
+__device__ void chal_load(DevChallenger *sc, const DevChallenger *c, int lane) {
+    const u64 *src = (const u64 *)c;
+    u64 *dst = (u64 *)sc;
+    for (int i = lane; i < (int)(sizeof(DevChallenger) / 8); i += 32) dst[i] = src[i];
+    __syncwarp();
+}
+__device__ void chal_store(DevChallenger *c, const DevChallenger *sc, int lane) {
+    __syncwarp();
+    const u64 *src = (const u64 *)sc;
+    u64 *dst = (u64 *)c;
+    for (int i = lane; i < (int)(sizeof(DevChallenger) / 8); i += 32) dst[i] = src[i];
 }
 
 // mode 0: n contiguous words.  mode 1: n words of an interleaved extension stream read from planar
 // storage: word i = plane (i & 1), index i >> 1.
 __global__ void chal_observe_kernel(DevChallenger *c, const u64 *data, size_t n, int mode, size_t plane_stride) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    for (size_t i = 0; i < n; i++) chal_observe(c, mode ? data[(i & 1) * plane_stride + (i >> 1)] : data[i]);
+    __shared__ DevChallenger sc;
+    const int lane = threadIdx.x;
+    chal_load(&sc, c, lane);
+    for (size_t i = 0; i < n; i++) chal_observe(&sc, mode ? data[(i & 1) * plane_stride + (i >> 1)] : data[i], lane);
+    chal_store(c, &sc, lane);
 }
 __global__ void chal_get_kernel(DevChallenger *c, u64 *out, int n, u64 modulus) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    __shared__ DevChallenger sc;
+    const int lane = threadIdx.x;
+    chal_load(&sc, c, lane);
     for (int i = 0; i < n; i++) {
-        u64 v = chal_get(c);
-        out[i] = modulus ? v % modulus : v;
+        u64 v = chal_get(&sc, lane);
+        if (lane == 0) out[i] = modulus ? v % modulus : v;
     }
+    chal_store(c, &sc, lane);
 }
 void launch_chal_observe(void *c, const u64 *data, size_t n, int mode, size_t plane_stride, cudaStream_t st) {
     if (n == 0) return;
