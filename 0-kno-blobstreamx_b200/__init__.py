@@ -32,6 +32,8 @@ from .fri import (  # noqa: F401
     FriParams,
     final_poly,
     fri_proof,
+    fri_proof_struct,
+    fri_proof_to_bytes,
     fri_proof_words,
     fri_reduction_arity_bits,
     prove_openings,

@@ -163,6 +163,21 @@ def prove_openings(instance, oracles, challenger, fri_params):
     return proof
 
 
+def fri_proof_struct(proof_words, oracles, fri_params):
+    """The flat proof as plonky2's `FriProof` fields (serialization.fri_proof_struct with the oracles' shapes)."""
+    from .serialization import fri_proof_struct as cut
+    widths = [b.shape()["n_cols"] + b.shape()["n_salt"] for b in oracles]
+    c = fri_params.config
+    return cut(proof_words, widths, fri_params.degree_bits, c.rate_bits, c.cap_height,
+               list(fri_params.reduction_arity_bits), c.num_query_rounds)
+
+
+def fri_proof_to_bytes(proof_words, oracles, fri_params):
+    """`Write::write_fri_proof` bytes of a proof returned by prove_openings / fri_proof."""
+    from .serialization import write_fri_proof
+    return write_fri_proof(fri_proof_struct(proof_words, oracles, fri_params))
+
+
 def fri_proof(oracles, lde_polynomial_coeffs, challenger, fri_params):
     """`fri::prover::fri_proof(initial_merkle_trees, lde_polynomial_coeffs, lde_polynomial_values, ..)`;
     coefficients: (2^(degree_bits + rate_bits), 2) extension elements.  The values are recomputed on device."""

@@ -83,3 +83,106 @@ def read_polynomial_batch(data):
     return {"coeffs": np.stack(coeffs).astype(np.uint64), "leaves": np.ascontiguousarray(rows[:, 1:]).astype(np.uint64),
             "digests": digests.astype(np.uint64), "cap": cap.astype(np.uint64), "degree_log": degree_log,
             "rate_bits": rate_bits, "blinding": blinding}
+
+
+# ---------------------------------------------------------------------------------------------
+# FriProof: the flat word stream of bsx_fri_prove_openings <-> plonky2's struct and byte layout
+def fri_proof_struct(words, leaf_widths, degree_bits, rate_bits, cap_height, arity_bits, num_query_rounds):
+    """Cuts the flat proof (include/bsx_b200.h: layout of bsx_fri_proof_words) into plonky2's `FriProof` fields:
+    {commit_phase_merkle_caps: [cap (2^h, 4)], query_round_proofs: [{initial_trees_proof: [(leaf, siblings)],
+    steps: [(evals (2^arity, 2), siblings)]}], final_poly: (len, 2), pow_witness}.
+    leaf_widths: per oracle, polynomials + salt columns."""
+    w = np.asarray(words, dtype=np.uint64).reshape(-1)
+    pos = 0
+
+    def take(n, shape=None):
+        nonlocal pos
+        if pos + n > w.size:
+            raise ValueError("FRI proof words truncated")
+        a = w[pos:pos + n]
+        pos += n
+        return a.reshape(shape) if shape else a
+
+    log_nb = degree_bits + rate_bits
+    caps = [take(4 << cap_height, (1 << cap_height, 4)) for _ in arity_bits]
+    rounds = []
+    for _ in range(num_query_rounds):
+        init = [(take(width), take(4 * (log_nb - cap_height), (log_nb - cap_height, 4))) for width in leaf_widths]
+        steps, lg = [], log_nb
+        for ab in arity_bits:
+            lg -= ab
+            steps.append((take(2 << ab, (1 << ab, 2)), take(4 * (lg - cap_height), (lg - cap_height, 4))))
+        rounds.append({"initial_trees_proof": init, "steps": steps})
+    final_poly = take(2 << (degree_bits - sum(arity_bits)), (1 << (degree_bits - sum(arity_bits)), 2))
+    pow_witness = int(take(1)[0])
+    if pos != w.size:
+        raise ValueError("FRI proof words: %d trailing words" % (w.size - pos))
+    return {"commit_phase_merkle_caps": caps, "query_round_proofs": rounds, "final_poly": final_poly,
+            "pow_witness": pow_witness}
+
+
+def write_fri_proof(proof):
+    """plonky2 util/serialization `Write::write_fri_proof` (restated from the public crate, unpinned): caps as
+    hashes, per query round the initial-tree openings (`write_field_vec` leaf, `write_merkle_proof` = u8 sibling
+    count + hashes) then per step the evals (`write_field_ext_vec`) and its Merkle proof, the final polynomial's
+    coefficients, the proof-of-work witness.  Vectors carry no length prefix: the reader knows them from
+    `CommonCircuitData` (`read_fri_proof`)."""
+    out = []
+
+    def merkle_proof(sib):
+        if sib.shape[0] > 255:
+            raise ValueError("Merkle proof longer than a u8 length")
+        out.append(bytes([sib.shape[0]]))
+        out.append(sib.astype("<u8").tobytes())
+
+    for cap in proof["commit_phase_merkle_caps"]:
+        out.append(np.asarray(cap).astype("<u8").tobytes())
+    for qr in proof["query_round_proofs"]:
+        for leaf, sib in qr["initial_trees_proof"]:
+            out.append(np.asarray(leaf).astype("<u8").tobytes())
+            merkle_proof(np.asarray(sib))
+        for evals, sib in qr["steps"]:
+            out.append(np.asarray(evals).astype("<u8").tobytes())
+            merkle_proof(np.asarray(sib))
+    out.append(np.asarray(proof["final_poly"]).astype("<u8").tobytes())
+    out.append(np.array([proof["pow_witness"]], dtype="<u8").tobytes())
+    return b"".join(out)
+
+
+def read_fri_proof(data, leaf_widths, degree_bits, rate_bits, cap_height, arity_bits, num_query_rounds):
+    """`Read::read_fri_proof`: bytes -> the flat word stream (inverse of write_fri_proof . fri_proof_struct)."""
+    buf = memoryview(data).cast("B")
+    pos, words = 0, []
+
+    def take(n_words):
+        nonlocal pos
+        end = pos + 8 * n_words
+        if end > len(buf):
+            raise ValueError("FRI proof bytes truncated")
+        words.append(np.frombuffer(buf[pos:end], dtype="<u8"))
+        pos = end
+
+    def merkle_proof(n_sib):
+        nonlocal pos
+        if pos >= len(buf) or buf[pos] != n_sib:
+            raise ValueError("FRI proof bytes: unexpected Merkle proof length")
+        pos += 1
+        take(4 * n_sib)
+
+    log_nb = degree_bits + rate_bits
+    for _ in arity_bits:
+        take(4 << cap_height)
+    for _ in range(num_query_rounds):
+        for width in leaf_widths:
+            take(width)
+            merkle_proof(log_nb - cap_height)
+        lg = log_nb
+        for ab in arity_bits:
+            lg -= ab
+            take(2 << ab)
+            merkle_proof(lg - cap_height)
+    take(2 << (degree_bits - sum(arity_bits)))
+    take(1)
+    if pos != len(buf):
+        raise ValueError("FRI proof bytes: wrong length")
+    return np.concatenate(words).astype(np.uint64)

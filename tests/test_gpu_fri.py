@@ -141,3 +141,20 @@ def test_failed_calls_release_their_temporaries(pkg, ctx, oracle):
     assert ctx.mem_used() == used
     for b in gb:
         b.close()
+
+
+def test_fri_proof_bytes_from_device_proof(pkg, ctx, oracle):
+    """write_fri_proof bytes of a device proof = bytes of the oracle's proof; read_fri_proof restores the words."""
+    ser = __import__(pkg.__name__ + ".serialization", fromlist=["x"])
+    ob, gb, points, polys = _setup(pkg, ctx, oracle, 10, 2, 1, [4, 3])
+    cfg = pkg.FriConfig(rate_bits=2, cap_height=1, proof_of_work_bits=6, num_query_rounds=5)
+    fp = cfg.fri_params(10)
+    proof = pkg.prove_openings(pkg.FriInstanceInfo(points, polys), gb, pkg.Challenger(ctx), fp)
+    want = oracle.fri_prove_openings(ob, points, polys, oracle.Challenger(), 10, 2, 1, 6, 5, list(fp.reduction_arity_bits))
+    data = pkg.fri_proof_to_bytes(proof, gb, fp)
+    st = ser.fri_proof_struct(want, [4, 3], 10, 2, 1, list(fp.reduction_arity_bits), 5)
+    assert data == ser.write_fri_proof(st)
+    assert (ser.read_fri_proof(data, [4, 3], 10, 2, 1, list(fp.reduction_arity_bits), 5) == proof).all()
+    assert pkg.fri_proof_struct(proof, gb, fp)["pow_witness"] == int(want[-1])
+    for b in gb:
+        b.close()

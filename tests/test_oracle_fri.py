@@ -112,3 +112,40 @@ def test_final_poly_is_low_degree_quotient(oracle):
         total = emul(total, sh)
         total = ((total[0] + q[0]) % P, (total[1] + q[1]) % P)
     assert acc == emul(total, x)
+
+
+def test_fri_proof_struct_and_bytes_roundtrip(oracle):
+    """Host-side wire format of a FriProof (serialization.py) on an oracle proof: words -> struct -> bytes -> words,
+    and the struct's Merkle openings verify against the caps."""
+    import __graft_entry__ as G
+    pkg = G.load_package()
+    ser = __import__(pkg.__name__ + ".serialization", fromlist=["x"])
+    degree_bits, rate_bits, cap_height, pow_bits, nq, widths = 10, 2, 1, 5, 4, (3, 2)
+    batches = [oracle.batch_from_values(splitmix_field(90 + i, (w, 1 << degree_bits)), rate_bits, cap_height)
+               for i, w in enumerate(widths)]
+    points = splitmix_field(95, (1, 2))
+    polys = [[(o, j) for o, w in enumerate(widths) for j in range(w)]]
+    ch = oracle.Challenger()
+    arity = [4, 4]
+    words = oracle.fri_prove_openings(batches, points, polys, ch, degree_bits, rate_bits, cap_height, pow_bits, nq, arity)
+    st = ser.fri_proof_struct(words, widths, degree_bits, rate_bits, cap_height, arity, nq)
+    assert len(st["commit_phase_merkle_caps"]) == 2 and len(st["query_round_proofs"]) == nq
+    assert st["final_poly"].shape == (1 << (degree_bits - 8), 2) and st["pow_witness"] == int(words[-1])
+    log_nb = degree_bits + rate_bits
+    for qr in st["query_round_proofs"]:
+        for (leaf, sib), b in zip(qr["initial_trees_proof"], batches):
+            # the opened leaf is one of the committed rows and its path verifies against the oracle's cap
+            idx = np.where((b["leaves"] == leaf).all(axis=1))[0]
+            assert idx.size >= 1 and oracle.merkle_verify(leaf, int(idx[0]), sib, b["cap"])
+        assert [e.shape for e, _ in qr["steps"]] == [(16, 2), (16, 2)]
+        assert [s.shape[0] for _, s in qr["steps"]] == [log_nb - 4 - cap_height, log_nb - 8 - cap_height]
+    data = ser.write_fri_proof(st)
+    n_paths = nq * (len(widths) + len(arity))
+    assert len(data) == 8 * words.size + n_paths
+    back = ser.read_fri_proof(data, widths, degree_bits, rate_bits, cap_height, arity, nq)
+    assert (back == words).all()
+    for bad in (data[:-1], data + b"\0", data[:40]):
+        with pytest.raises(ValueError):
+            ser.read_fri_proof(bad, widths, degree_bits, rate_bits, cap_height, arity, nq)
+    with pytest.raises(ValueError):
+        ser.fri_proof_struct(words[:-1], widths, degree_bits, rate_bits, cap_height, arity, nq)
