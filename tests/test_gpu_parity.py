@@ -288,3 +288,32 @@ def test_get_lde_values_packed(pkg, ctx):
     with pytest.raises(pkg.BsxError):
         b.get_lde_values_packed((1 << (log_n + rate_bits)) - 2, 1, 4)
     b.close()
+
+
+def test_noncanonical_inputs_are_residues(pkg, ctx, oracle):
+    """plonky2's GoldilocksField(u64) may hold a non-canonical representative (x + p < 2^64 for x < 2^32 - 1); a
+    `Vec<F>` handed over by the Rust shim can contain such words.  Every entry point treats a word as its residue."""
+    log_n, n_cols, rate_bits, cap_height = 9, 6, 2, 3
+    vals = splitmix_field(601, (n_cols, 1 << log_n))
+    small = (vals % np.uint64(2**32 - 1))
+    vals[:, ::3] = small[:, ::3]                      # canonical small values ...
+    alias = vals.copy()
+    alias[:, ::3] = small[:, ::3] + np.uint64(P)      # ... and their non-canonical aliases
+    assert (alias[:, ::3] >= np.uint64(P)).all()
+    for mk in (pkg.PolynomialBatch.from_values, pkg.PolynomialBatch.from_coeffs):
+        a, b = mk(ctx, vals, rate_bits, False, cap_height), mk(ctx, alias, rate_bits, False, cap_height)
+        assert (a.cap == b.cap).all()
+        ea, eb = a.export(), b.export()
+        assert (ea["leaves"] == eb["leaves"]).all() and (ea["digests"] == eb["digests"]).all()
+        assert (eb["coeffs"] % np.uint64(P) == ea["coeffs"]).all()
+        a.close()
+        b.close()
+    rows_a, rows_b = vals.T.copy(), alias.T.copy()
+    ta, tb = pkg.MerkleTree(ctx, rows_a, 2), pkg.MerkleTree(ctx, rows_b, 2)
+    assert (ta.cap == tb.cap).all()
+    ta.close()
+    tb.close()
+    st = np.stack([small[0, :12], small[0, :12] + np.uint64(P)])
+    out = ctx.poseidon_permute(st)
+    assert (out[0] == out[1]).all()
+    assert (ctx.ntt(alias[:2], "fft") == ctx.ntt(vals[:2], "fft")).all()
