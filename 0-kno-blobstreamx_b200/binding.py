@@ -11,7 +11,8 @@ _SO = os.path.join(_DIR, "csrc", "libbsx_b200.so")
 # every symbol include/bsx_b200.h declares (checked by tests/test_abi.py against the header text)
 EXPORTED_SYMBOLS = [
     "bsx_version", "bsx_device_count", "bsx_launch_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
-    "bsx_ctx_sync", "bsx_ctx_mem_used", "bsx_batch_from_values", "bsx_batch_from_coeffs", "bsx_batch_free", "bsx_batch_cap",
+    "bsx_ctx_sync", "bsx_ctx_mem_used", "bsx_batch_from_values", "bsx_batch_from_coeffs",
+    "bsx_batch_from_values_cols", "bsx_batch_from_coeffs_cols", "bsx_batch_free", "bsx_batch_cap",
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
@@ -65,6 +66,8 @@ def lib():
         "bsx_ctx_mem_used": (i32, [vp, C.POINTER(C.c_uint64)]),
         "bsx_batch_from_values": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_from_coeffs": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
+        "bsx_batch_from_values_cols": (i32, [vp, vp, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
+        "bsx_batch_from_coeffs_cols": (i32, [vp, vp, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_free": (None, [vp]),
         "bsx_batch_cap": (i32, [vp, vp]),
         "bsx_batch_tree": (vp, [vp]),
@@ -280,6 +283,20 @@ class PolynomialBatch:
 
     @staticmethod
     def _build(fn, ctx, cols, rate_bits, blinding, cap_height, salt, device_ptr, shape, timing):
+        if device_ptr is None and isinstance(cols, (list, tuple)):
+            # one separately allocated vector per polynomial: `Vec<PolynomialValues<F>>` as the Rust shim sees it
+            vecs = [_np(c).reshape(-1) for c in cols]
+            n = vecs[0].shape[0] if vecs else 1
+            if any(v.shape[0] != n for v in vecs):
+                raise BsxError("polynomials of different lengths")
+            ptrs = (C.c_void_p * max(len(vecs), 1))(*[v.ctypes.data for v in vecs])
+            fn_cols = lib().bsx_batch_from_coeffs_cols if fn is lib().bsx_batch_from_coeffs else lib().bsx_batch_from_values_cols
+            h = C.c_void_p()
+            t = Timing() if timing else None
+            ctx.check(fn_cols(ctx._h, ptrs, _log2_strict(n), len(vecs), int(rate_bits), int(cap_height),
+                              1 if blinding else 0, _ptr(_np(salt)) if salt is not None else None, C.byref(h),
+                              C.byref(t) if t is not None else None))
+            return PolynomialBatch(ctx, h, t)
         if device_ptr is not None:
             n_cols, n = shape
             src, mem = C.c_void_p(int(device_ptr)), BSX_DEVICE

@@ -230,6 +230,9 @@ extern "C" void bsx_ctx_destroy(bsx_ctx *ctx) {
         bsx_free(ctx, (u64 *)kv.second.second);
     }
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->stage_ring) cudaFreeHost(ctx->stage_ring);
+    for (auto &e : ctx->stage_done)
+        if (e) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;

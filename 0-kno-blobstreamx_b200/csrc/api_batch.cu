@@ -3,7 +3,10 @@
 // hash/merkle_tree.rs (MerkleTree::new, get, prove).
 #include "api_internal.h"
 
+#include <atomic>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
 
 static inline size_t n_digest_words(int log_leaves, int cap_height) {
     return 4 * 2 * (((size_t)1 << log_leaves) - ((size_t)1 << cap_height));
@@ -302,7 +305,113 @@ int bsx_commit_transforms(bsx_ctx *ctx, u64 *coeffs, int log_n, int n_cols, int 
     return bsx_commit_lde(ctx, coeffs, !input_is_coeffs, log_n, n_cols, rate_bits, lde, lde_stride, dests);
 }
 
-static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n_cols, int rate_bits, int cap_height,
+// ---- host witness sources -------------------------------------------------------------------------------------
+// A witness arrives either as one column-major buffer or as one pointer per column (`Vec<PolynomialValues<F>>`:
+// every column its own heap allocation).  Pinned contiguous memory is copied by the DMA engine directly.  Pageable
+// memory (what a Rust Vec is) would make cudaMemcpyAsync stage through the driver at ~10 GB/s on the calling
+// thread; instead a few host threads copy slot-sized pieces into a pinned ring owned by the context while the DMA
+// engine drains the previous slots, and the transforms of the finished column chunks run underneath.
+struct HostColumns {
+    const u64 *contig;         // n_cols x n, or null
+    const u64 *const *cols;    // n_cols pointers, or null
+    size_t n;
+    const u64 *col(int c) const { return cols ? cols[c] : contig + (size_t)c * n; }
+};
+
+static bool host_is_pinned(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+static int stage_threads() {
+    static int t = 0;
+    if (t == 0) {
+        const char *e = getenv("BSX_COPY_THREADS");
+        int hw = (int)std::thread::hardware_concurrency();
+        t = e ? atoi(e) : (hw >= 16 ? 8 : hw >= 4 ? hw / 2 : 1);
+        if (t < 1) t = 1;
+        if (t > 32) t = 32;
+    }
+    return t;
+}
+
+// columns [c0, c0 + cc) -> dst (pinned), split into 1 MiB pieces taken by `threads` workers
+static void stage_copy(u64 *dst, const HostColumns &src, int c0, int cc, int threads) {
+    const size_t piece = (size_t)1 << 17;  // words
+    const size_t per_col = (src.n + piece - 1) / piece, total = per_col * (size_t)cc;
+    std::atomic<size_t> next(0);
+    auto work = [&]() {
+        for (;;) {
+            size_t t = next.fetch_add(1);
+            if (t >= total) return;
+            size_t c = t / per_col, off = (t % per_col) * piece;
+            size_t len = src.n - off < piece ? src.n - off : piece;
+            memcpy(dst + c * src.n + off, src.col(c0 + (int)c) + off, len * sizeof(u64));
+        }
+    };
+    if ((size_t)threads > total) threads = (int)total;
+    std::vector<std::thread> pool;
+    for (int i = 1; i < threads; i++) pool.emplace_back(work);
+    work();
+    for (auto &th : pool) th.join();
+}
+
+static int stage_ring_reserve(bsx_ctx *ctx, size_t slot_words) {
+    if (ctx->stage_slot_words >= slot_words) return BSX_OK;
+    if (ctx->stage_ring) {
+        cudaStreamSynchronize(ctx->copy_stream);
+        cudaFreeHost(ctx->stage_ring);
+        ctx->stage_ring = nullptr;
+        ctx->stage_slot_words = 0;
+    }
+    cudaError_t e = cudaHostAlloc((void **)&ctx->stage_ring, slot_words * BSX_STAGE_SLOTS * sizeof(u64), cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        ctx->stage_ring = nullptr;
+        return bsx_fail(ctx, BSX_ERR_OOM, "pinned staging ring of %zu bytes: %s", slot_words * BSX_STAGE_SLOTS * sizeof(u64),
+                        cudaGetErrorString(e));
+    }
+    ctx->stage_slot_words = slot_words;
+    for (auto &ev : ctx->stage_done)
+        if (!ev) cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    return BSX_OK;
+}
+
+// Enqueues on copy_stream the upload of columns [c0, c0 + cc) to dst (device, column stride n).  `seq` counts the
+// ring slots used so far in this call.
+static int upload_columns(bsx_ctx *ctx, const HostColumns &src, bool direct, int c0, int cc, u64 *dst, size_t *seq) {
+    const size_t n = src.n;
+    if (direct) {
+        if (src.contig) {
+            CU(ctx, cudaMemcpyAsync(dst, src.contig + (size_t)c0 * n, (size_t)cc * n * sizeof(u64), cudaMemcpyHostToDevice,
+                                    ctx->copy_stream));
+        } else {
+            for (int c = 0; c < cc; c++)
+                CU(ctx, cudaMemcpyAsync(dst + (size_t)c * n, src.cols[c0 + c], n * sizeof(u64), cudaMemcpyHostToDevice,
+                                        ctx->copy_stream));
+        }
+        return BSX_OK;
+    }
+    const int per_slot = (int)(ctx->stage_slot_words / n);
+    for (int c = 0; c < cc; c += per_slot) {
+        const int k = cc - c < per_slot ? cc - c : per_slot;
+        const int slot = (int)(*seq % BSX_STAGE_SLOTS);
+        u64 *buf = ctx->stage_ring + (size_t)slot * ctx->stage_slot_words;
+        if (*seq >= BSX_STAGE_SLOTS) CU(ctx, cudaEventSynchronize(ctx->stage_done[slot]));  // its previous DMA is over
+        stage_copy(buf, src, c0 + c, k, stage_threads());
+        CU(ctx, cudaMemcpyAsync(dst + (size_t)c * n, buf, (size_t)k * n * sizeof(u64), cudaMemcpyHostToDevice,
+                                ctx->copy_stream));
+        CU(ctx, cudaEventRecord(ctx->stage_done[slot], ctx->copy_stream));
+        (*seq)++;
+    }
+    return BSX_OK;
+}
+
+static int batch_build(bsx_ctx *ctx, const u64 *input, const u64 *const *col_ptrs, int mem, int log_n, int n_cols, int rate_bits, int cap_height,
                        int blinding, const u64 *salt, bool input_is_coeffs, bsx_batch **out, bsx_timing *timing) {
     if (!ctx || !out) return BSX_ERR_INVALID_ARG;
     BsxScope scope(ctx);
@@ -316,7 +425,12 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
     if (cap_height < 0 || cap_height > log_nb)
         return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "cap_height=%d should be at most log2(leaves.len())=%d",
                         cap_height, log_nb);
-    if (!input && n_cols > 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "input is NULL");
+    if (!input && !col_ptrs && n_cols > 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "input is NULL");
+    if (col_ptrs) {
+        if (mem != BSX_HOST) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "column pointers must be host memory");
+        for (int c = 0; c < n_cols; c++)
+            if (!col_ptrs[c] && log_n >= 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "column %d is NULL", c);
+    }
     CU(ctx, cudaSetDevice(ctx->device));
     const size_t n = (size_t)1 << log_n, nb = (size_t)1 << log_nb;
     const int n_salt = blinding ? BSX_SALT_SIZE : 0;
@@ -358,22 +472,38 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
                 launch_fill_random(dst, nb * n_salt, 0x5A17C0DEULL ^ (u64)(uintptr_t)bt, ctx->stream);
             }
         }
+        const HostColumns host = {col_ptrs ? nullptr : input, col_ptrs, n};
         if (mem == BSX_HOST && n_cols >= 16 && log_n >= 13) {
             // Host witness: the copy is pipelined with the transforms in column chunks (copy engine and SMs
             // overlap; at the headline 20 ms of PCIe time hide behind 36 ms of NTT).  Chunks keep >= 8 columns
             // so that every launch still shares the full post-factor table.
             const int chunk = n_cols / 8 >= 8 ? (n_cols + 7) / 8 : 8;
             const int n_chunks = (n_cols + chunk - 1) / chunk;
+            // pinned contiguous memory goes straight to the DMA engine; anything else through the staging ring
+            const bool direct = !col_ptrs && host_is_pinned(input);
+            if (!direct) {
+                size_t per_slot = ((size_t)4 << 20) / n;  // ~32 MiB slots, at least one column
+                if (per_slot < 1) per_slot = 1;
+                if (per_slot > (size_t)chunk) per_slot = (size_t)chunk;
+                if ((rc = stage_ring_reserve(ctx, per_slot * n))) break;
+            }
             std::vector<cudaEvent_t> ev((size_t)n_chunks * 4 + 1);
             for (auto &e : ev) cudaEventCreateWithFlags(&e, pt.on ? cudaEventDefault : cudaEventDisableTiming);
             cudaEventRecord(ev[(size_t)n_chunks * 4], ctx->stream);  // the buffers exist (stream-ordered allocation)
             cudaStreamWaitEvent(ctx->copy_stream, ev[(size_t)n_chunks * 4], 0);
-            for (int k = 0; k < n_chunks; k++) {
+            size_t seq = 0;
+            auto upload = [&](int k) -> int {
                 const int c0 = k * chunk, cc = n_cols - c0 < chunk ? n_cols - c0 : chunk;
-                cudaMemcpyAsync(bt->coeffs + (size_t)c0 * n, input + (size_t)c0 * n, (size_t)cc * n * sizeof(u64),
-                                cudaMemcpyHostToDevice, ctx->copy_stream);
-                cudaEventRecord(ev[4 * k], ctx->copy_stream);
-            }
+                int r = upload_columns(ctx, host, direct, c0, cc, bt->coeffs + (size_t)c0 * n, &seq);
+                if (r == BSX_OK) cudaEventRecord(ev[4 * k], ctx->copy_stream);
+                return r;
+            };
+            // direct: all copies are queued up front.  staged: chunk k + 1 is copied by the host threads after the
+            // transforms of chunk k have been queued, so the GPU always has work while the host copies
+            if (direct)
+                for (int k = 0; k < n_chunks && rc == BSX_OK; k++) rc = upload(k);
+            else
+                rc = upload(0);
             for (int k = 0; k < n_chunks && rc == BSX_OK; k++) {
                 const int c0 = k * chunk, cc = n_cols - c0 < chunk ? n_cols - c0 : chunk;
                 cudaStreamWaitEvent(ctx->stream, ev[4 * k], 0);
@@ -382,6 +512,7 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
                 rc = bsx_commit_transforms(ctx, bt->coeffs + (size_t)c0 * n, log_n, cc, rate_bits, input_is_coeffs,
                                            bt->lde + (size_t)c0 * nb, nb, nullptr, ev[4 * k + 2]);
                 cudaEventRecord(ev[4 * k + 3], ctx->stream);
+                if (!direct && rc == BSX_OK && k + 1 < n_chunks) rc = upload(k + 1);
             }
             pt.mark(2, ctx->stream);
             cudaError_t e = cudaStreamSynchronize(ctx->stream);  // `input` may be released by the caller after return
@@ -399,7 +530,11 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
             if (rc) break;
             pipelined = true;
         } else {
-            if ((rc = bsx_copy_in(ctx, bt->coeffs, input, n * n_cols, mem))) break;
+            if (col_ptrs) {
+                for (int c = 0; c < n_cols && rc == BSX_OK; c++) rc = bsx_copy_in(ctx, bt->coeffs + (size_t)c * n, col_ptrs[c], n, mem);
+                if (rc) break;
+            } else if ((rc = bsx_copy_in(ctx, bt->coeffs, input, n * n_cols, mem)))
+                break;
             pt.mark(1, ctx->stream);
             if ((rc = bsx_commit_transforms(ctx, bt->coeffs, log_n, n_cols, rate_bits, input_is_coeffs, bt->lde, nb,
                                             nullptr, pt.on ? pt.ev[2] : nullptr)))
@@ -446,13 +581,27 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, int mem, int log_n, int n
 extern "C" int32_t bsx_batch_from_values(bsx_ctx *ctx, const uint64_t *values, int32_t mem, int32_t log_n,
                                          int32_t n_cols, int32_t rate_bits, int32_t cap_height, int32_t blinding,
                                          const uint64_t *salt, bsx_batch **out, bsx_timing *timing) {
-    return batch_build(ctx, (const u64 *)values, mem, log_n, n_cols, rate_bits, cap_height, blinding,
+    return batch_build(ctx, (const u64 *)values, nullptr, mem, log_n, n_cols, rate_bits, cap_height, blinding,
                        (const u64 *)salt, false, out, timing);
+}
+extern "C" int32_t bsx_batch_from_values_cols(bsx_ctx *ctx, const uint64_t *const *cols_host, int32_t log_n, int32_t n_cols,
+                                              int32_t rate_bits, int32_t cap_height, int32_t blinding,
+                                              const uint64_t *salt_host, bsx_batch **out, bsx_timing *timing) {
+    if (!cols_host && n_cols > 0) return BSX_ERR_INVALID_ARG;
+    return batch_build(ctx, nullptr, (const u64 *const *)cols_host, BSX_HOST, log_n, n_cols, rate_bits, cap_height,
+                       blinding, (const u64 *)salt_host, false, out, timing);
+}
+extern "C" int32_t bsx_batch_from_coeffs_cols(bsx_ctx *ctx, const uint64_t *const *cols_host, int32_t log_n, int32_t n_cols,
+                                              int32_t rate_bits, int32_t cap_height, int32_t blinding,
+                                              const uint64_t *salt_host, bsx_batch **out, bsx_timing *timing) {
+    if (!cols_host && n_cols > 0) return BSX_ERR_INVALID_ARG;
+    return batch_build(ctx, nullptr, (const u64 *const *)cols_host, BSX_HOST, log_n, n_cols, rate_bits, cap_height,
+                       blinding, (const u64 *)salt_host, true, out, timing);
 }
 extern "C" int32_t bsx_batch_from_coeffs(bsx_ctx *ctx, const uint64_t *coeffs, int32_t mem, int32_t log_n,
                                          int32_t n_cols, int32_t rate_bits, int32_t cap_height, int32_t blinding,
                                          const uint64_t *salt, bsx_batch **out, bsx_timing *timing) {
-    return batch_build(ctx, (const u64 *)coeffs, mem, log_n, n_cols, rate_bits, cap_height, blinding,
+    return batch_build(ctx, (const u64 *)coeffs, nullptr, mem, log_n, n_cols, rate_bits, cap_height, blinding,
                        (const u64 *)salt, true, out, timing);
 }
 

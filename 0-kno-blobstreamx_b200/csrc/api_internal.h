@@ -8,6 +8,8 @@
 #include "gl.cuh"
 #include "internal.h"
 
+#define BSX_STAGE_SLOTS 4
+
 struct CosetKey {
     int log_n, r_log;
     u64 shift;
@@ -31,6 +33,10 @@ struct bsx_ctx {
     std::vector<std::pair<u64 *, unsigned long long>> scratch;
     unsigned long long scratch_seq = 0;
     int scope_depth = 0;
+    // pinned staging ring for witnesses in pageable host memory (api_batch.cu HostStager); grown on demand
+    u64 *stage_ring = nullptr;
+    size_t stage_slot_words = 0;
+    cudaEvent_t stage_done[BSX_STAGE_SLOTS] = {};
 };
 
 // plonky2 hash/merkle_tree.rs MerkleTree { leaves, digests, cap }, device resident.

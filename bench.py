@@ -377,10 +377,29 @@ def gpu_arm(args, rank, world, local_rank):
     h1.record(stream)
     barrier()
     ms_e2e = h0.elapsed_time(h1) / args.steps
+    # ---- the same from PAGEABLE memory, one separately allocated vector per column (what a Rust
+    # Vec<PolynomialValues<F>> is): host threads stage the columns through the context's pinned ring
+    vecs = [host_np[c].copy() for c in range(N_COLS)]
+    cap_p = None
+    for _ in range(2):
+        b = pkg.PolynomialBatch.from_values(ctx, vecs, RATE_BITS, False, CAP_HEIGHT)
+        cap_p = b.cap
+        b.close()
+    assert (cap_p == cap0).all(), "pageable column-vector path disagrees"
+    barrier()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record(stream)
+    n_p = max(1, min(args.steps, 3))
+    for _ in range(n_p):
+        pkg.PolynomialBatch.from_values(ctx, vecs, RATE_BITS, False, CAP_HEIGHT).close()
+    p1.record(stream)
+    barrier()
+    ms_pageable = p0.elapsed_time(p1) / n_p
+    del vecs
     if world > 1:
-        t = torch.tensor([ms, ms_e2e], device="cuda:%d" % local_rank, dtype=torch.float64)
+        t = torch.tensor([ms, ms_e2e, ms_pageable], device="cuda:%d" % local_rank, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ms_e2e = float(t[0]), float(t[1])
+        ms, ms_e2e, ms_pageable = float(t[0]), float(t[1]), float(t[2])
     sharded = sharded_arm(args, pkg, ctx, stream, rank, world, local_rank, cap0) if world > 1 else None
     del dev
     torch.cuda.empty_cache()
@@ -416,6 +435,9 @@ def gpu_arm(args, rank, world, local_rank):
         "lde_melem_per_s": value * (1 << RATE_BITS),
         "e2e": {"value": e2e, "unit": "Melem/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": 8 * elems,
                 "d2h_bytes_per_step": 32 << CAP_HEIGHT},
+        "e2e_pageable": {"value": world * elems / (ms_pageable * 1e-3) / 1e6, "unit": "Melem/s", "ms_per_step": ms_pageable,
+                         "source": "%d separately allocated pageable host vectors per commit (Vec<PolynomialValues<F>>), "
+                                   "staged by host threads through a pinned ring" % N_COLS},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
         "phases_ms": avg,
         "roofline_ntt": {

@@ -79,6 +79,16 @@ int32_t bsx_ctx_mem_used(bsx_ctx *ctx, uint64_t *bytes);
 int32_t bsx_batch_from_values(bsx_ctx *ctx, const uint64_t *values, int32_t mem, int32_t log_n, int32_t n_cols,
                               int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt,
                               bsx_batch **out, bsx_timing *timing);
+/* The same with one HOST pointer per column -- `Vec<PolynomialValues<F>>` as it lies in the caller's heap, every
+ * column its own allocation, no gather on the caller's side.  Pageable memory is fine: host threads
+ * (BSX_COPY_THREADS, default 8) stage the columns through a pinned ring owned by the context while the DMA engine
+ * and the transforms of the finished column chunks run underneath. */
+int32_t bsx_batch_from_values_cols(bsx_ctx *ctx, const uint64_t *const *cols_host, int32_t log_n, int32_t n_cols,
+                                   int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt_host,
+                                   bsx_batch **out, bsx_timing *timing);
+int32_t bsx_batch_from_coeffs_cols(bsx_ctx *ctx, const uint64_t *const *cols_host, int32_t log_n, int32_t n_cols,
+                                   int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt_host,
+                                   bsx_batch **out, bsx_timing *timing);
 /* Replaces PolynomialBatch::from_coeffs: coeffs = n_cols coefficient vectors of length 2^log_n. */
 int32_t bsx_batch_from_coeffs(bsx_ctx *ctx, const uint64_t *coeffs, int32_t mem, int32_t log_n, int32_t n_cols,
                               int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt,

@@ -317,3 +317,23 @@ def test_noncanonical_inputs_are_residues(pkg, ctx, oracle):
     out = ctx.poseidon_permute(st)
     assert (out[0] == out[1]).all()
     assert (ctx.ntt(alias[:2], "fft") == ctx.ntt(vals[:2], "fft")).all()
+
+
+@pytest.mark.parametrize("log_n,n_cols", [(13, 40), (14, 17), (9, 5), (13, 16)])
+def test_separately_allocated_pageable_columns(pkg, ctx, oracle, log_n, n_cols):
+    """`Vec<PolynomialValues<F>>`: one pageable heap vector per column (pointer-array entry point, staged through the
+    pinned ring by host threads) and a pageable contiguous buffer give the cap of the pinned/contiguous path."""
+    vals = splitmix_field(701 + log_n, (n_cols, 1 << log_n))
+    want = oracle.batch_from_values(vals, 2, 3, want=())["cap"]
+    vecs = [vals[c].copy() for c in range(n_cols)]
+    for mk, src in ((pkg.PolynomialBatch.from_values, vecs), (pkg.PolynomialBatch.from_values, vals)):
+        for rep in range(2):  # second pass reuses the ring
+            b = mk(ctx, src, 2, False, 3, timing=True)
+            assert (b.cap == want).all()
+            b.close()
+    co = pkg.PolynomialBatch.from_coeffs(ctx, vecs, 2, False, 3)
+    assert (co.cap == oracle.batch_from_values(vals, 2, 3, want=(), from_coeffs=True)["cap"]).all()
+    assert (co.polynomials == vals).all()
+    co.close()
+    with pytest.raises(pkg.BsxError):
+        pkg.PolynomialBatch.from_values(ctx, [vals[0], vals[1][:8]], 2, False, 3)
