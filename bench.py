@@ -423,6 +423,8 @@ def gpu_arm(args, rank, world, local_rank):
     leaf_bytes = 8 * nb * N_COLS + 32 * nb
     roofline = roof(leaf_bytes, avg["leaf_hash_ms"], traffic.get("leaf_hash_kernel"))
     roofline["traffic_source"] = traffic_src
+    # the bound that actually applies (integer pipes), from the same committed ncu capture
+    roofline["pipes"] = (traffic.get("pipes") or {}).get("leaf_hash_kernel")
     roofline.update({"kernel": "leaf_hash_kernel", "ms_per_launch": avg["leaf_hash_ms"], "peak_source": peak_src,
                      "algorithmic_bytes": leaf_bytes,
                      "note": "dominant kernel by time; Poseidon is integer-pipe bound, so its HBM fraction is low "
@@ -444,6 +446,7 @@ def gpu_arm(args, rank, world, local_rank):
             "ifft": dict(roof(16 * elems, avg["ifft_ms"], traffic.get("ifft")), algorithmic_bytes=16 * elems),
             "lde": dict(roof(8 * elems + 8 * nb * N_COLS, avg["lde_ms"], traffic.get("lde")),
                         algorithmic_bytes=8 * elems + 8 * nb * N_COLS),
+            "pipes": {k: v for k, v in (traffic.get("pipes") or {}).items() if k.startswith("ntt")},
             "note": "two kernels each (pass HI + pass LO); bound by integer issue (ALU pipe 74-76 % busy in both passes), "
                     "not by HBM: a Goldilocks butterfly is ~36 integer instructions per 16 bytes moved (DESIGN.md 3.4)",
         },
