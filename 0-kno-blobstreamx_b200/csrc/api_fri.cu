@@ -311,8 +311,11 @@ static int fri_proof_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracl
         if ((rc = bsx_alloc(ctx, &best, 2))) break;
         cudaMemsetAsync(best, 0xFF, sizeof(u64), ctx->stream);
         u64 found = ~0ULL;
-        const u64 span = (u64)1 << 20;
-        for (u64 base = 0; found == ~0ULL; base += span) {
+        // candidates are tried in growing spans from 0, the smallest valid one of the first successful span wins
+        // (= the smallest valid witness overall).  First span = 4 x the expected waiting time 2^pow_bits (98 % hit
+        // rate) instead of a fixed 2^20: 0.25 ms instead of 1 ms at 16 bits
+        u64 span = (u64)1 << (p->proof_of_work_bits + 2 < 14 ? 14 : p->proof_of_work_bits + 2 > 22 ? 22 : p->proof_of_work_bits + 2);
+        for (u64 base = 0; found == ~0ULL; base += span, span = span < ((u64)1 << 22) ? span << 1 : span) {
             launch_pow(chal, base, span, p->proof_of_work_bits, best, ctx->stream);
             if (cudaMemcpyAsync(&found, best, sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
                 cudaStreamSynchronize(ctx->stream) != cudaSuccess) {

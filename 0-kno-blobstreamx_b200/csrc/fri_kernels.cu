@@ -27,8 +27,8 @@ __device__ __forceinline__ u64 poseidon_permute_warp(u64 x, int lane) {
         x = gl_add(x, POSEIDON_RC[12 * r + me]);
         const bool full = r < 4 || r >= 26;
         if (full || lane == 0) {
-            u64 x2 = gl_mul(x, x), x4 = gl_mul(x2, x2);
-            x = gl_mul(gl_mul(x, x2), x4);
+            u64 x2 = gl_mul_lazy(x, x), x4 = gl_mul_lazy(x2, x2);  // lazy words are fine for the halves below
+            x = gl_mul_lazy(gl_mul_lazy(x, x2), x4);
         }
         // y[lane] = sum_i C[i] x[(lane + i) % 12] (+ 8 x[0] for lane 0), on 32-bit halves
         const u32 lo = (u32)x, hi = (u32)(x >> 32);
