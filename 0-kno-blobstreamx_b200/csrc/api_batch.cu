@@ -355,7 +355,11 @@ static void stage_copy(u64 *dst, const HostColumns &src, int c0, int cc, int thr
     };
     if ((size_t)threads > total) threads = (int)total;
     std::vector<std::thread> pool;
-    for (int i = 1; i < threads; i++) pool.emplace_back(work);
+    try {
+        for (int i = 1; i < threads; i++) pool.emplace_back(work);
+    } catch (...) {
+        // thread creation refused (resource limits): the workers that exist and this thread finish the copy
+    }
     work();
     for (auto &th : pool) th.join();
 }
