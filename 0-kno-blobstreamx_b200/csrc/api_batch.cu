@@ -722,25 +722,103 @@ extern "C" int32_t bsx_batch_coeffs(bsx_batch *b, uint64_t *out, int32_t mem) {
     return BSX_OK;
 }
 
+// Row-major leaves to host memory, pipelined in row slabs: the slab is transposed on the device (LDE viewed as a
+// w x nb matrix -> rows), DMA'd into the context's pinned ring on copy_stream, and copied from there into the
+// caller's (pageable) buffer by the staging threads while the next slabs are in flight.  Device scratch is two
+// slabs, not a second copy of the LDE; a 9 GB export used to need 9 GB of scratch and a driver-staged copy.
+static void scatter_copy(u64 *dst, const u64 *src, size_t words, int threads) {
+    const size_t piece = (size_t)1 << 17;
+    const size_t total = (words + piece - 1) / piece;
+    std::atomic<size_t> next(0);
+    auto work = [&]() {
+        for (;;) {
+            size_t t = next.fetch_add(1);
+            if (t >= total) return;
+            size_t off = t * piece, len = words - off < piece ? words - off : piece;
+            memcpy(dst + off, src + off, len * sizeof(u64));
+        }
+    };
+    if ((size_t)threads > total) threads = (int)total;
+    std::vector<std::thread> pool;
+    try {
+        for (int i = 1; i < threads; i++) pool.emplace_back(work);
+    } catch (...) {
+    }
+    work();
+    for (auto &th : pool) th.join();
+}
+
+static int export_leaves(bsx_batch *b, u64 *leaves_host) {
+    bsx_ctx *ctx = b->ctx;
+    const size_t nb = (size_t)1 << (b->log_n + b->rate_bits), w = (size_t)(b->n_cols + b->n_salt);
+    if (nb == 0 || w == 0) return BSX_OK;
+    CU(ctx, cudaSetDevice(ctx->device));
+    const bool direct = host_is_pinned(leaves_host);
+    size_t rows = ((size_t)4 << 20) / w;  // ~32 MiB slabs
+    if (rows < 1) rows = 1;
+    if (rows > nb) rows = nb;
+    if (!direct) TRY(stage_ring_reserve(ctx, rows * w));
+    u64 *dbuf[2];
+    TRY(bsx_alloc(ctx, &dbuf[0], rows * w));
+    TRY(bsx_alloc(ctx, &dbuf[1], rows * w));
+    cudaEvent_t transposed[2], drained[2];
+    for (int i = 0; i < 2; i++) {
+        cudaEventCreateWithFlags(&transposed[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&drained[i], cudaEventDisableTiming);
+    }
+    const size_t n_slabs = (nb + rows - 1) / rows;
+    int rc = BSX_OK;
+    // slab i: device buffer i % 2, ring slot i % BSX_STAGE_SLOTS; the host copy of slab i - 2 runs while slab i - 1 is
+    // on the bus and slab i is being transposed
+    auto host_part = [&](size_t i) {
+        const size_t r0 = i * rows, r = nb - r0 < rows ? nb - r0 : rows;
+        const int slot = (int)(i % BSX_STAGE_SLOTS);
+        if (cudaEventSynchronize(ctx->stage_done[slot]) != cudaSuccess) return bsx_fail(ctx, BSX_ERR_CUDA, "export copy failed");
+        scatter_copy(leaves_host + r0 * w, ctx->stage_ring + (size_t)slot * ctx->stage_slot_words, r * w, stage_threads());
+        return (int)BSX_OK;
+    };
+    for (size_t i = 0; i < n_slabs && rc == BSX_OK; i++) {
+        const size_t r0 = i * rows, r = nb - r0 < rows ? nb - r0 : rows;
+        const int d = (int)(i & 1);
+        if (i >= 2) cudaStreamWaitEvent(ctx->stream, drained[d], 0);  // the DMA out of this device buffer is over
+        launch_transpose_strided(b->lde + r0, nb, dbuf[d], w, r, ctx->stream);
+        cudaEventRecord(transposed[d], ctx->stream);
+        cudaStreamWaitEvent(ctx->copy_stream, transposed[d], 0);
+        if (direct) {
+            cudaMemcpyAsync(leaves_host + r0 * w, dbuf[d], r * w * sizeof(u64), cudaMemcpyDeviceToHost, ctx->copy_stream);
+        } else {
+            const int slot = (int)(i % BSX_STAGE_SLOTS);
+            if (i >= BSX_STAGE_SLOTS) rc = host_part(i - BSX_STAGE_SLOTS);  // frees the slot
+            if (rc) break;
+            cudaMemcpyAsync(ctx->stage_ring + (size_t)slot * ctx->stage_slot_words, dbuf[d], r * w * sizeof(u64),
+                            cudaMemcpyDeviceToHost, ctx->copy_stream);
+            cudaEventRecord(ctx->stage_done[slot], ctx->copy_stream);
+        }
+        cudaEventRecord(drained[d], ctx->copy_stream);
+    }
+    if (!direct)
+        for (size_t i = n_slabs > BSX_STAGE_SLOTS ? n_slabs - BSX_STAGE_SLOTS : 0; i < n_slabs && rc == BSX_OK; i++)
+            rc = host_part(i);
+    cudaError_t e = cudaStreamSynchronize(ctx->copy_stream);
+    if (rc == BSX_OK && (e != cudaSuccess || cudaGetLastError() != cudaSuccess))
+        rc = bsx_fail(ctx, BSX_ERR_CUDA, "leaf export failed: %s", cudaGetErrorString(e));
+    cudaStreamSynchronize(ctx->stream);
+    for (int i = 0; i < 2; i++) {
+        cudaEventDestroy(transposed[i]);
+        cudaEventDestroy(drained[i]);
+    }
+    bsx_free(ctx, dbuf[0]);
+    bsx_free(ctx, dbuf[1]);
+    return rc;
+}
+
 extern "C" int32_t bsx_batch_export(bsx_batch *b, uint64_t *coeffs_host, uint64_t *leaves_host,
                                     uint64_t *digests_host) {
     if (!b) return BSX_ERR_INVALID_ARG;
     bsx_ctx *ctx = b->ctx;
     BsxScope scope(ctx);
     if (coeffs_host) TRY(bsx_batch_coeffs(b, coeffs_host, BSX_HOST));
-    if (leaves_host) {
-        size_t nb = (size_t)1 << (b->log_n + b->rate_bits), w = (size_t)(b->n_cols + b->n_salt);
-        if (nb != 0 && w != 0) {
-            CU(ctx, cudaSetDevice(ctx->device));
-            u64 *tmp;
-            TRY(bsx_alloc(ctx, &tmp, nb * w));
-            // LDE viewed as a (w x nb) row-major matrix -> (nb x w) row-major leaves
-            launch_transpose(b->lde, tmp, w, nb, ctx->stream);
-            TRY(bsx_copy_out(ctx, (u64 *)leaves_host, tmp, nb * w, BSX_HOST));
-            bsx_free(ctx, tmp);
-            CU(ctx, cudaStreamSynchronize(ctx->stream));
-        }
-    }
+    if (leaves_host) TRY(export_leaves(b, (u64 *)leaves_host));
     if (digests_host) TRY(bsx_merkle_digests(&b->tree, digests_host));
     return BSX_OK;
 }

@@ -189,14 +189,15 @@ void launch_poseidon_permute(u64 *states, size_t n, cudaStream_t st) {
 }
 
 // 32x32 tiled transpose through shared memory, both sides coalesced.
-__global__ void transpose_kernel(const u64 *__restrict__ src, u64 *__restrict__ dst, size_t n_rows, size_t n_cols) {
+__global__ void transpose_kernel(const u64 *__restrict__ src, size_t src_stride, u64 *__restrict__ dst, size_t n_rows,
+                                 size_t n_cols) {
     __shared__ u64 tile[32][33];
     // tiles on a one-dimensional grid: either side may exceed the 65535 limit of grid.y
     const size_t tiles_x = (n_cols + 31) / 32;
     size_t c0 = (blockIdx.x % tiles_x) * 32, r0 = (blockIdx.x / tiles_x) * 32;
     for (int j = threadIdx.y; j < 32; j += blockDim.y) {
         size_t r = r0 + j, c = c0 + threadIdx.x;
-        if (r < n_rows && c < n_cols) tile[j][threadIdx.x] = src[r * n_cols + c];
+        if (r < n_rows && c < n_cols) tile[j][threadIdx.x] = src[r * src_stride + c];
     }
     __syncthreads();
     for (int j = threadIdx.y; j < 32; j += blockDim.y) {
@@ -205,9 +206,13 @@ __global__ void transpose_kernel(const u64 *__restrict__ src, u64 *__restrict__ 
     }
 }
 void launch_transpose(const u64 *src, u64 *dst, size_t n_rows, size_t n_cols, cudaStream_t st) {
+    launch_transpose_strided(src, n_cols, dst, n_rows, n_cols, st);
+}
+// src row r at src + r * src_stride (n_cols words used) -> dst (n_cols x n_rows), dense
+void launch_transpose_strided(const u64 *src, size_t src_stride, u64 *dst, size_t n_rows, size_t n_cols, cudaStream_t st) {
     if (n_rows == 0 || n_cols == 0) return;
     const size_t tiles = ((n_cols + 31) / 32) * ((n_rows + 31) / 32);
-    BSX_COUNT_LAUNCH(); transpose_kernel<<<(unsigned)tiles, dim3(32, 8), 0, st>>>(src, dst, n_rows, n_cols);
+    BSX_COUNT_LAUNCH(); transpose_kernel<<<(unsigned)tiles, dim3(32, 8), 0, st>>>(src, src_stride, dst, n_rows, n_cols);
 }
 
 __global__ void gather_rows_kernel(const u64 *__restrict__ data, size_t col_stride, int n_cols,

@@ -27,6 +27,7 @@ void launch_merkle_tree(u64 *digests, u64 *cap, int log_leaves, int cap_height, 
 void launch_poseidon_permute(u64 *states, size_t n, cudaStream_t st);
 // row-major (n_rows x n_cols) <-> column-major (n_cols x n_rows, stride n_rows)
 void launch_transpose(const u64 *src, u64 *dst, size_t n_rows, size_t n_cols, cudaStream_t st);
+void launch_transpose_strided(const u64 *src, size_t src_stride, u64 *dst, size_t n_rows, size_t n_cols, cudaStream_t st);
 // out[r * n_cols + c] = data[c * col_stride + idx[r]]
 void launch_gather_rows(const u64 *data, size_t col_stride, int n_cols, const u64 *idx, int n_idx, u64 *out,
                         cudaStream_t st);

@@ -337,3 +337,20 @@ def test_separately_allocated_pageable_columns(pkg, ctx, oracle, log_n, n_cols):
     co.close()
     with pytest.raises(pkg.BsxError):
         pkg.PolynomialBatch.from_values(ctx, [vals[0], vals[1][:8]], 2, False, 3)
+
+
+def test_export_leaves_in_slabs(pkg, ctx, oracle):
+    """Row-major leaf export runs in ~32 MiB row slabs through the pinned ring: five slabs at 2^17 x 135, so the
+    ring (four slots) wraps and the two device buffers are reused."""
+    import torch
+    vals = splitmix_field(801, (135, 1 << 14))
+    b = pkg.PolynomialBatch.from_values(ctx, vals, 3, False, 4)
+    want = oracle.batch_from_values(vals, 3, 4, want=("leaves",))
+    ex = b.export(coeffs=False, digests=False)
+    assert (ex["leaves"] == want["leaves"]).all()
+    # pinned destination: DMA straight into the caller's buffer
+    pinned = torch.empty((1 << 17, 135), dtype=torch.int64).pin_memory()
+    out = pinned.numpy().view(np.uint64)
+    ctx.check(pkg.lib().bsx_batch_export(b._h, None, out.ctypes.data, None))
+    assert (out == want["leaves"]).all()
+    b.close()
