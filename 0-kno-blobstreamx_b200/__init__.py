@@ -44,6 +44,10 @@ from .parallel import (  # noqa: F401
     assemble_cap,
     device_tensor,
     exchange_staged,
+    final_poly_part,
+    fri_from_final_poly,
+    sharded_prove_openings,
+    sum_parts,
     top_siblings,
 )
 

@@ -17,7 +17,8 @@ EXPORTED_SYMBOLS = [
     "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
     "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
-    "bsx_challenger_get", "bsx_fri_proof_words", "bsx_fri_prove_openings", "bsx_fri_proof", "bsx_fri_final_poly",
+    "bsx_challenger_get", "bsx_fri_proof_words", "bsx_fri_prove_openings", "bsx_fri_proof", "bsx_fri_final_poly", "bsx_fri_final_poly_part", "bsx_shard_final_poly_part", "bsx_field_sum",
+    "bsx_fri_proof_from_final_poly",
     "bsx_merkle_reduce", "bsx_shard_column_range", "bsx_shard_create", "bsx_shard_free", "bsx_shard_shape",
     "bsx_shard_slab_device", "bsx_shard_staging_device", "bsx_shard_coeffs_device", "bsx_shard_slab_ipc",
     "bsx_shard_set_peer_ipc", "bsx_shard_set_peer_ptr", "bsx_shard_transform", "bsx_shard_commit", "bsx_shard_coeffs",
@@ -97,6 +98,10 @@ def lib():
         "bsx_fri_prove_openings": (i32, [vp, vp, i32, vp, vp, vp, vp]),
         "bsx_fri_proof": (i32, [vp, vp, i32, vp, vp, vp, vp]),
         "bsx_fri_final_poly": (i32, [vp, vp, i32, vp, vp, vp]),
+        "bsx_fri_final_poly_part": (i32, [vp, vp, i32, vp, vp, i32, vp, i32]),
+        "bsx_shard_final_poly_part": (i32, [vp, i32, vp, vp, vp, i32]),
+        "bsx_field_sum": (i32, [vp, vp, i32, i32, sz, vp, i32]),
+        "bsx_fri_proof_from_final_poly": (i32, [vp, vp, i32, vp, i32, vp, vp, vp, vp]),
         "bsx_merkle_reduce": (i32, [vp, vp, i32, i32, vp]),
         "bsx_shard_column_range": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
         "bsx_shard_create": (i32, [vp, i32, i32, i32, i32, i32, i32, pp]),

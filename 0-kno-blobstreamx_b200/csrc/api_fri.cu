@@ -129,6 +129,7 @@ static int final_poly_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_orac
     }
     for (int i = 0; i < total; i++) {
         int o = inst->poly_oracle[i];
+        if (o == -1) continue;  // held by another rank (sharded prove): keeps its place in the alpha powers
         if (o < 0 || o >= n_oracles || inst->poly_index[i] < 0 || inst->poly_index[i] >= oracles[o]->n_cols)
             return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "instance names polynomial %d of oracle %d, which does not exist",
                             inst->poly_index[i], o);
@@ -160,6 +161,7 @@ static int final_poly_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_orac
             ptrs.clear();
             pidx.clear();
             for (int j = 0; j < k; j++) {
+                if (inst->poly_oracle[pos + j] < 0) continue;
                 const bsx_batch *o = oracles[inst->poly_oracle[pos + j]];
                 if ((o->coeffs_bitrev ? 1 : 0) != order) continue;
                 ptrs.push_back(o->coeffs + (size_t)inst->poly_index[pos + j] * n);
@@ -253,7 +255,7 @@ static int ext_coset_ntt(bsx_ctx *ctx, const u64 *coeffs, u64 *values, int lg, i
 
 // coeffs: planar [2][2^log_nb] natural order on device (consumed).  chal: device challenger.
 static int fri_proof_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracles, u64 *coeffs, u64 *chal,
-                            const bsx_fri_params *p, const FriLayout &L, u64 *proof) {
+                            const bsx_fri_params *p, const FriLayout &L, u64 *proof, u64 *idx_out_host) {
     const int rb = L.rb, cap = L.cap;
     int lg = L.log_nb;
     size_t len = (size_t)1 << lg;
@@ -337,6 +339,8 @@ static int fri_proof_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracl
         if (nq > 0) {
             if ((rc = bsx_alloc(ctx, &idx, (size_t)nq))) break;
             launch_chal_get(chal, idx, nq, (u64)1 << L.log_nb, ctx->stream);
+            if (idx_out_host)  // read after the caller's final synchronisation
+                cudaMemcpyAsync(idx_out_host, idx, (size_t)nq * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream);
             u64 *qbase = proof + L.caps_words;
             for (int o = 0; o < n_oracles; o++) {
                 const bsx_batch *b = oracles[o];
@@ -364,7 +368,8 @@ static int fri_proof_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracl
 }
 
 static int fri_run(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracles, const bsx_fri_instance *inst,
-                   const u64 *lde_coeffs_host, bsx_challenger *ch, const bsx_fri_params *p, u64 *proof_host) {
+                   const u64 *lde_coeffs_host, bsx_challenger *ch, const bsx_fri_params *p, u64 *proof_host,
+                   const u64 *final_poly = nullptr, int final_mem = BSX_HOST, u64 *idx_out_host = nullptr) {
     if (!ctx || !ch || !p || !proof_host) return BSX_ERR_INVALID_ARG;
     BsxScope scope(ctx);
     FriLayout L;
@@ -390,6 +395,14 @@ static int fri_run(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracles, const
         }
         bsx_free(ctx, alpha);
         bsx_free(ctx, fin);
+    } else if (final_poly) {
+        // the final polynomial itself (2^degree_bits interleaved extension coefficients), zero-padded here
+        u64 *tmp;
+        TRY(bsx_alloc(ctx, &tmp, 2 * n));
+        TRY(bsx_copy_in(ctx, tmp, final_poly, 2 * n, final_mem));
+        CU(ctx, cudaMemsetAsync(coeffs, 0, 2 * nb * sizeof(u64), ctx->stream));
+        launch_ext_deinterleave(tmp, n, coeffs, nb, ctx->stream);
+        bsx_free(ctx, tmp);
     } else {
         u64 *tmp;
         TRY(bsx_alloc(ctx, &tmp, 2 * nb));
@@ -397,7 +410,7 @@ static int fri_run(bsx_ctx *ctx, bsx_batch *const *oracles, int n_oracles, const
         launch_ext_deinterleave(tmp, nb, coeffs, nb, ctx->stream);
         bsx_free(ctx, tmp);
     }
-    if (rc == BSX_OK) rc = fri_proof_device(ctx, oracles, n_oracles, coeffs, chal, p, L, proof);
+    if (rc == BSX_OK) rc = fri_proof_device(ctx, oracles, n_oracles, coeffs, chal, p, L, proof, idx_out_host);
     else bsx_free(ctx, coeffs);
     if (rc == BSX_OK) {
         cudaError_t e = cudaMemcpyAsync(proof_host, proof, L.total * sizeof(u64), cudaMemcpyDeviceToHost, ctx->stream);
@@ -420,6 +433,67 @@ extern "C" int32_t bsx_fri_proof(bsx_ctx *ctx, bsx_batch *const *oracles, int32_
                                  const bsx_fri_params *params, uint64_t *proof_host) {
     if (!lde_coeffs_host) return BSX_ERR_INVALID_ARG;
     return fri_run(ctx, oracles, n_oracles, nullptr, (const u64 *)lde_coeffs_host, challenger, params, (u64 *)proof_host);
+}
+
+// fri_proof from the final polynomial of prove_openings (2^degree_bits extension coefficients, `mem` side) instead of
+// its zero-padded LDE form, with the query indices returned: the building block of a prove over row-sharded
+// oracles, where the initial-tree openings come from the owning ranks (n_oracles may be 0).
+extern "C" int32_t bsx_fri_proof_from_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
+                                                 const uint64_t *final_poly, int32_t mem, bsx_challenger *challenger,
+                                                 const bsx_fri_params *params, uint64_t *proof_host,
+                                                 uint64_t *query_indices_host) {
+    if (!final_poly) return BSX_ERR_INVALID_ARG;
+    return fri_run(ctx, oracles, n_oracles, nullptr, nullptr, challenger, params, (u64 *)proof_host,
+                   (const u64 *)final_poly, mem, (u64 *)query_indices_host);
+}
+
+// out[i] = sum_k parts[k * words + i] (mod p): the partial final polynomials of the ranks added up
+extern "C" int32_t bsx_field_sum(bsx_ctx *ctx, const uint64_t *parts, int32_t mem, int32_t k, size_t words, uint64_t *out,
+                                 int32_t mem_out) {
+    if (!ctx || k < 0 || (words && k && (!parts || !out))) return BSX_ERR_INVALID_ARG;
+    if (words == 0) return BSX_OK;
+    BsxScope scope(ctx);
+    CU(ctx, cudaSetDevice(ctx->device));
+    const u64 *src = (const u64 *)parts;
+    u64 *tmp = nullptr, *dst = (u64 *)out;
+    if (mem != BSX_DEVICE && k > 0) {
+        TRY(bsx_alloc(ctx, &tmp, (size_t)k * words));
+        TRY(bsx_copy_in(ctx, tmp, (const u64 *)parts, (size_t)k * words, mem));
+        src = tmp;
+    }
+    if (mem_out != BSX_DEVICE) TRY(bsx_alloc(ctx, &dst, words));
+    launch_field_sum(src, k, words, dst, ctx->stream);
+    CU(ctx, cudaGetLastError());
+    if (mem_out != BSX_DEVICE) TRY(bsx_copy_out(ctx, (u64 *)out, dst, words, mem_out));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
+// The part of prove_openings' final polynomial that the listed polynomials contribute: `instance` names every
+// polynomial of the opening batches, with poly_oracle == -1 for those not in `oracles`; they keep their place in
+// the powers of alpha.  Division by (X - z), the shift between batches and the multiplication by X are linear, so the
+// sum of the parts over any partition of the polynomials is the final polynomial.  out = 2^degree_bits x [c0, c1].
+extern "C" int32_t bsx_fri_final_poly_part(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
+                                           const bsx_fri_instance *instance, const uint64_t alpha[2], int32_t degree_bits,
+                                           uint64_t *out, int32_t mem_out) {
+    if (!ctx || !instance || !alpha || !out || degree_bits < 0 || degree_bits > 24 || n_oracles < 0 ||
+        (n_oracles > 0 && !oracles))
+        return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
+    CU(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)1 << degree_bits;
+    for (int o = 0; o < n_oracles; o++)
+        if (!oracles[o] || oracles[o]->log_n != degree_bits) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "oracles differ in degree");
+    u64 *a, *fin, *inter = (u64 *)out;
+    TRY(bsx_alloc(ctx, &a, 2));
+    TRY(bsx_alloc(ctx, &fin, 2 * n));
+    if (mem_out != BSX_DEVICE) TRY(bsx_alloc(ctx, &inter, 2 * n));
+    CU(ctx, cudaMemcpyAsync(a, alpha, 2 * sizeof(u64), cudaMemcpyHostToDevice, ctx->stream));
+    TRY(final_poly_device(ctx, oracles, n_oracles, instance, a, degree_bits, fin));
+    launch_ext_interleave(fin, n, n, inter, ctx->stream);
+    if (mem_out != BSX_DEVICE) TRY(bsx_copy_out(ctx, (u64 *)out, inter, 2 * n, mem_out));
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
 }
 
 // ------------------------------------------------------------------------------------ opening set

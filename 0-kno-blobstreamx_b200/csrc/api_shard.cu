@@ -15,6 +15,7 @@
 #include "api_internal.h"
 
 #include <cstring>
+#include <vector>
 
 struct bsx_shard {
     bsx_ctx *ctx;
@@ -280,4 +281,50 @@ extern "C" int32_t bsx_merkle_reduce(bsx_ctx *ctx, const uint64_t *digests_host,
     bsx_free(ctx, b);
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     return BSX_OK;
+}
+
+// prove_openings over row-sharded oracles, step 1 ("run FRI after gathering the small final-poly
+// inputs").  `instance` is the instance of the whole proof: poly_oracle indexes `shards`, poly_index is the GLOBAL
+// column of that oracle.  This rank contributes the polynomials whose coefficient columns it holds; the parts of all
+// ranks add up (bsx_field_sum) to the final polynomial, which then goes to bsx_fri_proof_from_final_poly.
+extern "C" int32_t bsx_shard_final_poly_part(bsx_shard *const *shards, int32_t n_shards, const bsx_fri_instance *instance,
+                                             const uint64_t alpha[2], uint64_t *out, int32_t mem_out) {
+    if (!shards || n_shards <= 0 || n_shards > 64 || !instance || !alpha || !out || !shards[0]) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = shards[0]->ctx;
+    if (instance->n_batches < 0 || instance->n_batches > 16) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad instance");
+    std::vector<bsx_batch> views((size_t)n_shards);
+    std::vector<bsx_batch *> ptrs((size_t)n_shards);
+    for (int o = 0; o < n_shards; o++) {
+        const bsx_shard *s = shards[o];
+        if (!s || s->ctx != ctx || s->log_n != shards[0]->log_n)
+            return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "shard %d does not match the first one", o);
+        if (s->c1 > s->c0 && !s->coeffs) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "shard %d has not been transformed", o);
+        views[o].ctx = ctx;
+        views[o].log_n = s->log_n;
+        views[o].n_cols = s->c1 - s->c0;
+        views[o].n_salt = 0;
+        views[o].rate_bits = s->rate_bits;
+        views[o].coeffs = s->coeffs;
+        views[o].coeffs_bitrev = s->coeffs_bitrev;
+        views[o].lde = nullptr;
+        ptrs[o] = &views[o];
+    }
+    int total = 0;
+    for (int b = 0; b < instance->n_batches; b++) {
+        if (instance->n_polys[b] < 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad instance");
+        total += instance->n_polys[b];
+    }
+    std::vector<int32_t> po((size_t)total), pi((size_t)total);
+    for (int i = 0; i < total; i++) {
+        const int o = instance->poly_oracle[i], j = instance->poly_index[i];
+        if (o < 0 || o >= n_shards || j < 0 || j >= shards[o]->n_cols_total)
+            return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "instance names polynomial %d of oracle %d, which does not exist", j, o);
+        const bool mine = j >= shards[o]->c0 && j < shards[o]->c1;
+        po[i] = mine ? o : -1;
+        pi[i] = mine ? j - shards[o]->c0 : 0;
+    }
+    bsx_fri_instance local = *instance;
+    local.poly_oracle = po.data();
+    local.poly_index = pi.data();
+    return bsx_fri_final_poly_part(ctx, ptrs.data(), n_shards, &local, alpha, shards[0]->log_n, out, mem_out);
 }

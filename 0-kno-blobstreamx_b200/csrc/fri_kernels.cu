@@ -389,3 +389,16 @@ __global__ void ext_pow_kernel(const u64 *a, u64 k, u64 *out) {
 void launch_ext_pow(const u64 *a, u64 k, u64 *out, cudaStream_t st) {
     BSX_COUNT_LAUNCH(); ext_pow_kernel<<<1, 32, 0, st>>>(a, k, out);
 }
+
+// ------------------------------------------------------------------ sum of k vectors (mod p)
+__global__ void __launch_bounds__(256) field_sum_kernel(const u64 *__restrict__ parts, int k, size_t words, u64 *__restrict__ out) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= words) return;
+    u64 acc = 0;
+    for (int j = 0; j < k; j++) acc = gl_add(acc, gl_canon(parts[(size_t)j * words + i]));
+    out[i] = acc;
+}
+void launch_field_sum(const u64 *parts, int k, size_t words, u64 *out, cudaStream_t st) {
+    if (words == 0) return;
+    BSX_COUNT_LAUNCH(); field_sum_kernel<<<(unsigned)((words + 255) / 256), 256, 0, st>>>(parts, k, words, out);
+}

@@ -102,6 +102,7 @@ void launch_fri_query_gather(const u64 *idx, int n_queries, int shift, const u64
 void launch_ext_interleave(const u64 *planar, size_t plane_stride, size_t n, u64 *out, cudaStream_t st);
 void launch_ext_deinterleave(const u64 *in, size_t n, u64 *planar, size_t plane_stride, cudaStream_t st);
 void launch_ext_pow(const u64 *a, u64 k, u64 *out, cudaStream_t st);
+void launch_field_sum(const u64 *parts, int k, size_t words, u64 *out, cudaStream_t st);
 
 // ---------------------------------------------------------------- opening-set evaluation (eval_kernels.cu)
 #define BSX_EVAL_MAX_BITS 64

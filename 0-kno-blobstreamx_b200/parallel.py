@@ -344,3 +344,73 @@ class ShardedPolynomialBatch:
             self.close()
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------------------------------------
+# prove_openings over row-sharded oracles
+def final_poly_part(sbatches, instance, alpha):
+    """This rank's part of the final polynomial (2^degree_bits, 2): the polynomials whose coefficient columns it
+    holds, at their alpha powers in the whole instance.  `instance` uses GLOBAL column indices."""
+    ctx = sbatches[0].ctx
+    n = 1 << sbatches[0].plan.log_n
+    hs = (C.c_void_p * len(sbatches))(*[b._h for b in sbatches])
+    a = _np(alpha)
+    out = np.zeros((n, 2), dtype=np.uint64)
+    ctx.check(lib().bsx_shard_final_poly_part(hs, len(sbatches), C.byref(instance.struct), _ptr(a), _ptr(out), BSX_HOST))
+    return out
+
+
+def sum_parts(ctx, parts):
+    """Field sum of the ranks' parts."""
+    parts = _np(np.stack([np.asarray(p, dtype=np.uint64).reshape(-1) for p in parts]))
+    out = np.zeros(parts.shape[1], dtype=np.uint64)
+    ctx.check(lib().bsx_field_sum(ctx._h, _ptr(parts), BSX_HOST, parts.shape[0], parts.shape[1], _ptr(out), BSX_HOST))
+    return out.reshape(-1, 2)
+
+
+def fri_from_final_poly(ctx, final_poly, challenger, fri_params):
+    """Commit phase, proof of work and FRI-tree openings from the final polynomial -> (FRI-only words, indices)."""
+    from .fri import _params_struct
+    p = _params_struct(fri_params)
+    n_words = C.c_size_t()
+    ctx.check(lib().bsx_fri_proof_words(None, 0, C.byref(p), C.byref(n_words)))
+    proof = np.zeros(n_words.value, dtype=np.uint64)
+    idx = np.zeros(fri_params.config.num_query_rounds, dtype=np.uint64)
+    fp = _np(final_poly)
+    ctx.check(lib().bsx_fri_proof_from_final_poly(ctx._h, None, 0, _ptr(fp), BSX_HOST, C.byref(challenger._s), C.byref(p),
+                                                  _ptr(proof), _ptr(idx)))
+    return proof, idx
+
+
+def sharded_prove_openings(instance, sbatches, challenger, fri_params, gather=None, opener=None):
+    """`PolynomialBatch::prove_openings` for oracles committed with ShardedPolynomialBatch.  Collective: every rank
+    calls it with the same instance (GLOBAL column indices) and an identical challenger; every rank returns the same
+    proof, word for word the single-GPU one.  Only 16 bytes x 2^degree_bits per rank (the parts of the final
+    polynomial) and the 28 opened rows with their paths cross the ranks; the FRI rounds themselves are not sharded
+    (< 2 % of the work, serialised by Fiat-Shamir) and run redundantly on every rank, which keeps the transcripts
+    in step without a broadcast.
+    gather(part) -> list of all ranks' parts and opener(sbatch, leaves) -> (rows, proofs) default to
+    torch.distributed collectives; the single-process tests pass their own."""
+    from .serialization import splice_initial_openings
+    ctx = sbatches[0].ctx
+    alpha = challenger.get_extension_challenge()
+    part = final_poly_part(sbatches, instance, alpha)
+    if gather is None:
+        import torch
+        import torch.distributed as dist
+        group = sbatches[0].group
+        world = dist.get_world_size(group)
+        dev = "cuda:%d" % ctx.device
+        mine = torch.from_numpy(part.view(np.int64).reshape(-1).copy()).to(dev)
+        allp = torch.empty(world * mine.numel(), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allp, mine, group=group)
+        parts = list(allp.cpu().numpy().view(np.uint64).reshape(world, -1))
+    else:
+        parts = gather(part)
+    final_poly = sum_parts(ctx, parts)
+    fri_words, idx = fri_from_final_poly(ctx, final_poly, challenger, fri_params)
+    leaves = [int(x) for x in idx]
+    openings = [(opener(sb, leaves) if opener is not None else sb.open(leaves)) for sb in sbatches]
+    c = fri_params.config
+    return splice_initial_openings(fri_words, openings, fri_params.degree_bits, c.rate_bits, c.cap_height,
+                                   list(fri_params.reduction_arity_bits), c.num_query_rounds)

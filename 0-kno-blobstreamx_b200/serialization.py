@@ -186,3 +186,30 @@ def read_fri_proof(data, leaf_widths, degree_bits, rate_bits, cap_height, arity_
     if pos != len(buf):
         raise ValueError("FRI proof bytes: wrong length")
     return np.concatenate(words).astype(np.uint64)
+
+
+def splice_initial_openings(fri_words, openings, degree_bits, rate_bits, cap_height, arity_bits, num_query_rounds):
+    """The flat proof of a prove over row-sharded oracles: `fri_words` is the stream of
+    bsx_fri_proof_from_final_poly with n_oracles = 0 (caps, per query round the FRI steps only, final polynomial,
+    witness); `openings` = per oracle (rows (num_query_rounds, width), siblings (num_query_rounds, n_sib, 4)) as the
+    owning ranks served them.  Returns the stream bsx_fri_prove_openings produces on one GPU."""
+    w = np.asarray(fri_words, dtype=np.uint64).reshape(-1)
+    log_nb = degree_bits + rate_bits
+    caps_words = len(arity_bits) * (4 << cap_height)
+    per_q, lg = 0, log_nb
+    for ab in arity_bits:
+        lg -= ab
+        per_q += (2 << ab) + 4 * (lg - cap_height)
+    tail = (2 << (degree_bits - sum(arity_bits))) + 1
+    if w.size != caps_words + per_q * num_query_rounds + tail:
+        raise ValueError("FRI-only proof stream has the wrong length")
+    out = [w[:caps_words]]
+    for q in range(num_query_rounds):
+        for rows, sib in openings:
+            rows, sib = np.asarray(rows, dtype=np.uint64), np.asarray(sib, dtype=np.uint64)
+            if sib.shape[1:] != (log_nb - cap_height, 4):
+                raise ValueError("initial-tree proof of the wrong length")
+            out += [rows[q].reshape(-1), sib[q].reshape(-1)]
+        out.append(w[caps_words + q * per_q:caps_words + (q + 1) * per_q])
+    out.append(w[w.size - tail:])
+    return np.concatenate(out)

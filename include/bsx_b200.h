@@ -234,6 +234,27 @@ int32_t bsx_fri_prove_openings(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t 
  * non-zero); the values are recomputed on the device. */
 int32_t bsx_fri_proof(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles, const uint64_t *lde_coeffs_host,
                       bsx_challenger *challenger, const bsx_fri_params *params, uint64_t *proof_host);
+/* ---- prove_openings over row-sharded oracles (FRI after gathering the small final-poly inputs) ----
+ * 1. every rank: alpha = challenger.get_extension_challenge() (identical transcripts), then its part of the final
+ *    polynomial from the coefficient columns it holds: bsx_shard_final_poly_part (or bsx_fri_final_poly_part on
+ *    whole batches, with poly_oracle = -1 for polynomials held elsewhere -- they keep their alpha power);
+ * 2. the parts are gathered (16 bytes x 2^degree_bits per rank) and added: bsx_field_sum;
+ * 3. bsx_fri_proof_from_final_poly runs the commit phase, proof of work and the FRI-tree query openings and returns
+ *    the query indices; with n_oracles = 0 the proof stream has no initial-tree openings;
+ * 4. the owning ranks serve the initial-tree openings of those indices (bsx_merkle_get / bsx_merkle_prove on their
+ *    row slabs) and the host splices them in (0-kno-blobstreamx_b200/serialization.py splice_initial_openings). */
+int32_t bsx_fri_final_poly_part(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
+                                const bsx_fri_instance *instance, const uint64_t alpha[2], int32_t degree_bits,
+                                uint64_t *out, int32_t mem_out);
+int32_t bsx_shard_final_poly_part(bsx_shard *const *shards, int32_t n_shards, const bsx_fri_instance *instance,
+                                  const uint64_t alpha[2], uint64_t *out, int32_t mem_out);
+/* out[i] = sum over k vectors of `words` words (mod p) */
+int32_t bsx_field_sum(bsx_ctx *ctx, const uint64_t *parts, int32_t mem, int32_t k, size_t words, uint64_t *out,
+                      int32_t mem_out);
+/* final_poly: 2^degree_bits x [c0, c1] on the `mem` side; query_indices_host: num_query_rounds words or NULL */
+int32_t bsx_fri_proof_from_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
+                                      const uint64_t *final_poly, int32_t mem, bsx_challenger *challenger,
+                                      const bsx_fri_params *params, uint64_t *proof_host, uint64_t *query_indices_host);
 /* test hook: the final polynomial of prove_openings for a given alpha -> out_host[2^degree_bits][2] */
 int32_t bsx_fri_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
                            const bsx_fri_instance *instance, const uint64_t alpha[2], uint64_t *out_host);

@@ -45,6 +45,17 @@ def main():
     for k, leaf in enumerate(leaves):
         assert (rows[k] == tree.get(leaf)).all()
         assert (proofs[k] == np.asarray(tree.prove(leaf)).reshape(-1, 4)).all()
+    # prove_openings over the sharded oracle: every rank ends with the single-GPU proof
+    zeta = splitmix_field(4243, (1, 2))
+    inst = pkg.FriInstanceInfo(zeta, [[(0, j) for j in range(a.cols)]])
+    fp = pkg.FriConfig(rate_bits=3, cap_height=4, proof_of_work_bits=8, num_query_rounds=10).fri_params(a.log_n)
+    ch_s, ch_r = pkg.Challenger(ctx), pkg.Challenger(ctx)
+    ch_s.observe_cap(sb.cap)
+    ch_r.observe_cap(ref.cap)
+    proof_s = pkg.sharded_prove_openings(inst, [sb], ch_s, fp)
+    proof_r = pkg.prove_openings(inst, [ref], ch_r, fp)
+    assert (proof_s == proof_r).all(), "rank %d: sharded proof differs" % rank
+    assert ch_s.snapshot() == ch_r.snapshot()
     cap0 = int(sb.cap[0, 0])
     dist.barrier()
     sb.close()

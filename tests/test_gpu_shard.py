@@ -144,3 +144,58 @@ def test_multiprocess_ipc_and_nccl(mode):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "sharded commit ok" in r.stdout
+
+
+@pytest.mark.parametrize("world,cap_height", [(2, 2), (4, 1), (8, 4)])
+def test_sharded_prove_openings_equals_single_gpu(pkg, ctx, world, cap_height):
+    """prove_openings over row-sharded oracles (ranks emulated on one device): parts of the final polynomial from the
+    ranks' coefficient columns, summed; FRI from the final polynomial; initial-tree openings served by the owners and
+    spliced in.  Word for word the single-GPU proof, including world > 2^cap_height (paths extended above the rank
+    roots)."""
+    log_n, rate_bits, widths = 10, 2, (9, 5)
+    vals = [splitmix_field(7300 + i, (w, 1 << log_n)) for i, w in enumerate(widths)]
+    fresh = [pkg.PolynomialBatch.from_values(ctx, v, rate_bits, False, cap_height) for v in vals]
+    sets = []  # sets[o][rank]
+    for v in vals:
+        plan, shards, cap = _sharded(pkg, ctx, v, rate_bits, cap_height, world, "p2p")
+        caps = [s.merkle_tree.cap for s in shards]
+        for s in shards:
+            s.rank_caps, s.cap = caps, cap
+        sets.append(shards)
+    zeta = splitmix_field(7310, (2,))
+    w = pow(7, (P - 1) >> log_n, P)
+    gz = np.array([int(zeta[0]) * w % P, int(zeta[1]) * w % P], dtype=np.uint64)
+    polys = [[(o, j) for o, wd in enumerate(widths) for j in range(wd)], [(0, 1), (1, 4)]]
+    inst = pkg.FriInstanceInfo(np.stack([zeta, gz]), polys)
+    fp = pkg.FriConfig(rate_bits=rate_bits, cap_height=cap_height, proof_of_work_bits=5, num_query_rounds=6).fri_params(log_n)
+
+    def transcript():
+        ch = pkg.Challenger(ctx)
+        for b in fresh:
+            ch.observe_cap(b.cap)
+        return ch
+
+    want = pkg.prove_openings(inst, fresh, transcript(), fp)
+    # every rank's part, with the challenger every rank would hold
+    alpha = transcript().get_extension_challenge()
+    parts = [pkg.final_poly_part([sets[o][r] for o in range(len(widths))], inst, alpha) for r in range(world)]
+    assert (pkg.sum_parts(ctx, parts) == pkg.final_poly(inst, fresh, alpha)).all()
+
+    def opener(sb, leaves):  # what the all-reduce in ShardedPolynomialBatch.open adds up
+        o = [k for k in range(len(widths)) if sb in sets[k]][0]
+        rows = proofs = 0
+        for s in sets[o]:
+            r, pr = s.local_openings(leaves)
+            rows, proofs = rows + r, proofs + pr
+        return rows, proofs
+
+    for rank in (0, world - 1):
+        mine = [sets[o][rank] for o in range(len(widths))]
+        ch = transcript()
+        got = pkg.sharded_prove_openings(inst, mine, ch, fp, gather=lambda part: parts, opener=opener)
+        assert got.shape == want.shape and (got == want).all()
+    for shards in sets:
+        for s in shards:
+            s.close()
+    for b in fresh:
+        b.close()

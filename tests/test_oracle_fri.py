@@ -149,3 +149,28 @@ def test_fri_proof_struct_and_bytes_roundtrip(oracle):
             ser.read_fri_proof(bad, widths, degree_bits, rate_bits, cap_height, arity, nq)
     with pytest.raises(ValueError):
         ser.fri_proof_struct(words[:-1], widths, degree_bits, rate_bits, cap_height, arity, nq)
+
+
+def test_splice_initial_openings_rebuilds_the_proof(oracle):
+    """serialization.splice_initial_openings (sharded prove): FRI-only stream + per-oracle openings -> the full stream."""
+    import __graft_entry__ as G
+    pkg = G.load_package()
+    ser = __import__(pkg.__name__ + ".serialization", fromlist=["x"])
+    degree_bits, rate_bits, cap_height, nq, widths, arity = 9, 1, 2, 3, (4, 2), [4]
+    batches = [oracle.batch_from_values(splitmix_field(120 + i, (w, 1 << degree_bits)), rate_bits, cap_height)
+               for i, w in enumerate(widths)]
+    polys = [[(o, j) for o, w in enumerate(widths) for j in range(w)]]
+    words = oracle.fri_prove_openings(batches, splitmix_field(125, (1, 2)), polys, oracle.Challenger(), degree_bits,
+                                      rate_bits, cap_height, 3, nq, arity)
+    st = ser.fri_proof_struct(words, widths, degree_bits, rate_bits, cap_height, arity, nq)
+    fri_only = [np.concatenate([c.reshape(-1) for c in st["commit_phase_merkle_caps"]])]
+    for qr in st["query_round_proofs"]:
+        for evals, sib in qr["steps"]:
+            fri_only += [evals.reshape(-1), sib.reshape(-1)]
+    fri_only += [st["final_poly"].reshape(-1), np.array([st["pow_witness"]], dtype=np.uint64)]
+    openings = [(np.stack([qr["initial_trees_proof"][o][0] for qr in st["query_round_proofs"]]),
+                 np.stack([qr["initial_trees_proof"][o][1] for qr in st["query_round_proofs"]])) for o in range(len(widths))]
+    back = ser.splice_initial_openings(np.concatenate(fri_only), openings, degree_bits, rate_bits, cap_height, arity, nq)
+    assert (back == words).all()
+    with pytest.raises(ValueError):
+        ser.splice_initial_openings(np.concatenate(fri_only)[:-1], openings, degree_bits, rate_bits, cap_height, arity, nq)
