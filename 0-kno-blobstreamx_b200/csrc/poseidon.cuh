@@ -24,6 +24,14 @@
 #define POSEIDON_MDS_FFT 1
 #endif
 
+// 1: partial rounds keep lanes 1..11 as 22-bit limb planes from round to round and use the same
+//    multiplication-free dense MDS as the full rounds (only lane 0 is merged for its S-box);
+// 0: sparse factorisation of the partial rounds (23 full-width multiplies per round).
+#ifndef POSEIDON_PARTIAL_PLANES
+#define POSEIDON_PARTIAL_PLANES 1
+#endif
+
+__constant__ u32 POSEIDON_POST30_L22[30 * 36] = {POSEIDON_POST30_L22_LIST};
 __constant__ u64 POSEIDON_RC[POSEIDON_N_RC] = {POSEIDON_RC_LIST};
 __constant__ u64 POSEIDON_POST_LO[96] = {POSEIDON_POST_LO_LIST};
 __constant__ u64 POSEIDON_POST_HI[96] = {POSEIDON_POST_HI_LIST};
@@ -121,6 +129,72 @@ __device__ __forceinline__ void poseidon_mds_post_fft(u64 s[12], const u32 *__re
     for (int i = 0; i < 12; i++) s[i] = poseidon_merge22(y0[i], y1[i], y2[i]);
 }
 
+// u64 -> three 22-bit limbs (22, 22, 20 bits)
+__device__ __forceinline__ void poseidon_split22(u64 v, u32 &x0, u32 &x1, u32 &x2) {
+    u32 lo = (u32)v, hi = (u32)(v >> 32);
+    x0 = lo & POSEIDON_LIMB_MASK;
+    x1 = __funnelshift_r(lo, hi, POSEIDON_LIMB_BITS) & POSEIDON_LIMB_MASK;
+    x2 = hi >> 12;
+}
+
+// Limb normalisation between two plane-resident partial rounds.  In: plane outputs y_k in [0, 2^31).
+// The bits of y2 above 2^20 are worth top * 2^64 == top * (2^32 - 1): + top << 10 on limb 1, - top on limb 0
+// (which may go negative: the carries below use arithmetic shifts).  Out: y0, y1 < 2^22, y2 < 2^20 + 2^11,
+// so the next layer's outputs stay below 264 * 2^22 + 2^22 < 2^31 (model and bounds checked in
+// tools/gen_poseidon_constants.py `poseidon_planes`).  10 ALU instructions; merge + split is 18 + 1 IMAD.WIDE.
+__device__ __forceinline__ void poseidon_norm22(u32 &y0, u32 &y1, u32 &y2) {
+    u32 top = y2 >> 20;
+    y2 &= 0xFFFFFu;
+    y1 += top << 10;
+    y0 -= top;
+    int c0 = (int)y0 >> POSEIDON_LIMB_BITS;
+    y0 &= POSEIDON_LIMB_MASK;
+    y1 += (u32)c0;
+    int c1 = (int)y1 >> POSEIDON_LIMB_BITS;
+    y1 &= POSEIDON_LIMB_MASK;
+    y2 += (u32)c1;
+}
+
+#if POSEIDON_PARTIAL_PLANES
+// lazy in, lazy out.  Round r: S-box, then s <- M s + RC[r + 1] (the constants ride as third addends).
+__device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
+#pragma unroll
+    for (int i = 0; i < 12; i++) s[i] = gl_add_lazy_canon(s[i], POSEIDON_RC[i]);
+#pragma unroll 1
+    for (int half = 0; half < 2; half++) {
+#pragma unroll 1
+        for (int r = 0; r < 4; r++) {
+#pragma unroll
+            for (int i = 0; i < 12; i++) s[i] = poseidon_sbox(s[i]);
+            poseidon_mds_post_fft(s, POSEIDON_POST30_L22 + 36 * (half * 26 + r));
+        }
+        if (half == 0) {
+            u32 x0[12], x1[12], x2[12], a0, a1, a2;
+#pragma unroll
+            for (int i = 1; i < 12; i++) poseidon_split22(s[i], x0[i], x1[i], x2[i]);
+            poseidon_split22(s[0], a0, a1, a2);
+#pragma unroll 1
+            for (int p = 4; p < 26; p++) {
+                const u32 *post = POSEIDON_POST30_L22 + 36 * p;
+                poseidon_split22(poseidon_sbox(poseidon_merge22(a0, a1, a2)), x0[0], x1[0], x2[0]);
+                u32 y0[12], y1[12], y2[12];
+                poseidon_mds_plane(x0, post, y0);
+                poseidon_mds_plane(x1, post + 12, y1);
+                poseidon_mds_plane(x2, post + 24, y2);
+                a0 = y0[0], a1 = y1[0], a2 = y2[0];
+#pragma unroll
+                for (int i = 1; i < 12; i++) {
+                    poseidon_norm22(y0[i], y1[i], y2[i]);
+                    x0[i] = y0[i], x1[i] = y1[i], x2[i] = y2[i];
+                }
+            }
+            s[0] = poseidon_merge22(a0, a1, a2);
+#pragma unroll
+            for (int i = 1; i < 12; i++) s[i] = poseidon_merge22(x0[i], x1[i], x2[i]);
+        }
+    }
+}
+#else
 // lazy in, lazy out
 __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
 #pragma unroll
@@ -168,6 +242,8 @@ __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
         }
     }
 }
+
+#endif
 
 // state canonical (or lazy) in, canonical out
 __device__ __forceinline__ void poseidon_permute(u64 s[12]) {

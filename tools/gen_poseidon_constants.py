@@ -243,6 +243,78 @@ def mds_fft_check():
         assert max(want) <= M32 and want == mds_plane_fft(x, k)
 
 
+
+def split22(v):
+    return [v & 0x3FFFFF, (v >> 22) & 0x3FFFFF, v >> 44]
+
+
+def merge22_lazy(o):
+    """poseidon_merge22 of csrc/poseidon.cuh: o0 + o1 2^22 + o2 2^44 (each < 2^32) -> some u64 representative"""
+    assert all(0 <= v <= M32 for v in o)
+    w = o[0] + (o[1] << 22) + (o[2] << 44)
+    lo, w2 = w & ((1 << 64) - 1), w >> 64
+    assert w2 < (1 << 13)
+    lo += w2 * 0xFFFFFFFF
+    if lo >> 64:
+        lo = (lo & ((1 << 64) - 1)) + 0xFFFFFFFF
+    assert lo < (1 << 64)
+    return lo
+
+
+def s32(v):
+    v &= M32
+    return v - (1 << 32) if v >> 31 else v
+
+
+def norm22(y):
+    """Limb normalisation between two plane-resident partial rounds (wrapping u32, arithmetic shifts):
+    fold the bits above 2^64 back with 2^64 == 2^32 - 1, then propagate the limb carries."""
+    y0, y1, y2 = y
+    assert 0 <= y2 < (1 << 31)
+    top = y2 >> 20
+    y2 &= 0xFFFFF
+    y1 = (y1 + (top << 10)) & M32
+    y0 = (y0 - top) & M32
+    c0 = s32(y0) >> 22
+    y0 &= 0x3FFFFF
+    y1 = (y1 + c0) & M32
+    c1 = s32(y1) >> 22
+    y1 &= 0x3FFFFF
+    y2 = (y2 + c1) & M32
+    assert 0 <= y2 < (1 << 20) + (1 << 11)
+    return [y0, y1, y2]
+
+
+def poseidon_planes(state, rc, stats=None):
+    """The shipped device schedule: full rounds on u64 lanes with the limb-plane MDS; the 22 partial rounds keep
+    lanes 1..11 as 22-bit limb planes from round to round (dense MDS, no multiplications), only lane 0 is merged
+    for its S-box.  post constants = the next round's RC as third addends of the planes."""
+    post = [[split22(c) for c in rc[12 * (r + 1):12 * (r + 2)]] if r < 29 else [[0, 0, 0]] * 12 for r in range(30)]
+
+    def planes(x, r):  # x: 12 x 3 limbs -> 12 x 3 limbs (unnormalised)
+        ys = [mds_plane_fft([x[i][k] for i in range(12)], [post[r][i][k] for i in range(12)]) for k in range(3)]
+        return [[ys[k][i] for k in range(3)] for i in range(12)]
+
+    s = [(state[i] + rc[i]) % P for i in range(12)]
+    for r in range(4):
+        s = [pow(v, 7, P) for v in s]
+        s = [merge22_lazy(y) % P for y in planes([split22(v) for v in s], r)]
+    x = [split22(v) for v in s]
+    y0 = x[0]
+    for r in range(4, 26):
+        x[0] = split22(pow(merge22_lazy(y0) % P, 7, P))
+        y = planes(x, r)
+        if stats is not None:
+            stats[0] = max(stats[0], max(max(l) for l in y))
+        y0 = y[0]
+        x = [None] + [norm22(l) for l in y[1:]]
+    s = [merge22_lazy(y0) % P] + [merge22_lazy(l) % P for l in x[1:]]
+    for r in range(26, 30):
+        s = [pow(v, 7, P) for v in s]
+        s = [merge22_lazy(y) % P for y in planes([split22(v) for v in s], r)]
+    return s
+
+
 def c_list32(name, vals, per_line=8):
     out = "#define %s \\\n" % name
     for i in range(0, len(vals), per_line):
@@ -285,6 +357,10 @@ def emit(path, rc, guard, fc=None):
             # the same vectors cut into 22-bit limb planes for the multiplication-free MDS: [8][3][12]
             l22 = [(x >> (22 * k)) & 0x3FFFFF for row in post for k in range(3) for x in row]
             f.write(c_list32("POSEIDON_POST_L22_LIST", l22))
+            # plane-resident schedule: after the MDS of round r (all 30) the next round's RC, [30][3][12]
+            post30 = [rc[12 * (r + 1):12 * (r + 2)] if r < 29 else [0] * 12 for r in range(30)]
+            f.write(c_list32("POSEIDON_POST30_L22_LIST",
+                             [(x >> (22 * k)) & 0x3FFFFF for row in post30 for k in range(3) for x in row]))
         f.write("#endif\n")
 
 
@@ -300,6 +376,11 @@ def main():
     for t in range(6):
         st = [0] * 12 if t == 0 else [P - 1] * 12 if t == 1 else [rnd.randrange(P) for _ in range(12)]
         assert poseidon_fast(st, rc, fc) == poseidon_naive(st, rc), "fast partial rounds differ from naive"
+    stats = [0]
+    for t in range(300):
+        st = [0] * 12 if t == 0 else [P - 1] * 12 if t == 1 else [rnd.randrange(P) for _ in range(12)]
+        assert poseidon_planes(st, rc, stats) == poseidon_naive(st, rc), "plane-resident partial rounds differ from naive"
+    assert stats[0] < (1 << 31)
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     emit(os.path.join(root, "oracle", "poseidon_rc.h"), rc, "ORACLE_POSEIDON_RC_H")
     emit(os.path.join(root, "0-kno-blobstreamx_b200", "csrc", "poseidon_rc.h"), rc, "BSX_POSEIDON_RC_H", fc)
