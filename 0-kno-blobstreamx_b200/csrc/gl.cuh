@@ -155,6 +155,52 @@ __device__ __forceinline__ u64 gl_mul_lazy(u64 a, u64 b) {
     return ((u64)r1 << 32) | r0;
 }
 
+// a * a (mod p), lazy in, lazy out: the cross product once, doubled on the ALU (GL_SQR_MODE 1: by shifts,
+// 2: added twice) -- three IMAD.WIDE for the product instead of four.
+#ifndef GL_SQR_MODE
+#define GL_SQR_MODE 1
+#endif
+#ifndef GL_SQR_TAIL_ALU
+#define GL_SQR_TAIL_ALU 0
+#endif
+__device__ __forceinline__ u64 gl_sqr_lazy(u64 a) {
+#if GL_SQR_MODE == 0
+    return gl_mul_lazy(a, a);
+#else
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), r0, r1;
+    asm("{\n\t.reg .u32 x0,x1,x2,x3,t0,t1,d0,d1,d2,r2,n,eh;\n\t.reg .u64 w0,w3,t;\n\t"
+        "mul.wide.u32 w0, %2, %2;\n\t"
+        "mul.wide.u32 w3, %3, %3;\n\t"
+        "mul.wide.u32 t, %2, %3;\n\t"
+        "mov.b64 {t0,t1}, t;\n\t"
+        "mov.b64 {x0,x1}, w0;\n\t"
+        "mov.b64 {x2,x3}, w3;\n\t"
+#if GL_SQR_MODE == 1
+        "shf.l.wrap.b32 d1, t0, t1, 1;\n\t"
+        "shl.b32 d0, t0, 1;\n\t"
+        "shr.b32 d2, t1, 31;\n\t"
+        "add.cc.u32 x1, x1, d0;\n\t"
+        "addc.cc.u32 x2, x2, d1;\n\t"
+        "addc.u32 x3, x3, d2;\n\t"
+#else
+        "add.cc.u32 x1, x1, t0;\n\t"
+        "addc.cc.u32 x2, x2, t1;\n\t"
+        "addc.u32 x3, x3, 0;\n\t"
+        "add.cc.u32 x1, x1, t0;\n\t"
+        "addc.cc.u32 x2, x2, t1;\n\t"
+        "addc.u32 x3, x3, 0;\n\t"
+#endif
+#if GL_SQR_TAIL_ALU
+        GL_REDUCE_TAIL_ALU("%4", "0")
+#else
+        GL_REDUCE_TAIL("%4", "0")
+#endif
+        : "=r"(r0), "=r"(r1)
+        : "r"(a0), "r"(a1), "r"(GL_EPS32_C));
+    return ((u64)r1 << 32) | r0;
+#endif
+}
+
 // ---- canonical carry-chain forms for the NTT butterflies (inputs < p, outputs < p) ----
 // a - b: 5 SASS instructions (the compiler's compare+select form of gl_sub is 8)
 __device__ __forceinline__ u64 gl_sub_c(u64 a, u64 b) {

@@ -42,7 +42,7 @@ __constant__ u64 POSEIDON_FAST_V[242] = {POSEIDON_FAST_V_LIST};
 __constant__ u64 POSEIDON_FAST_W[242] = {POSEIDON_FAST_W_LIST};
 
 __device__ __forceinline__ u64 poseidon_sbox(u64 x) {
-    u64 x2 = gl_mul_lazy(x, x), x4 = gl_mul_lazy(x2, x2), x3 = gl_mul_lazy(x, x2);
+    u64 x2 = gl_sqr_lazy(x), x4 = gl_sqr_lazy(x2), x3 = gl_mul_lazy(x, x2);
     return gl_mul_lazy(x3, x4);
 }
 
