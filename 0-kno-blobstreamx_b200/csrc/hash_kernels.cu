@@ -8,7 +8,7 @@
 // One thread per leaf row.  The LDE buffer is column-major, so lane l of a warp reads word
 // (col, row0 + l): 32 lanes x 8 B = 256 contiguous bytes per column -- the "transpose" of
 // plonky2's fri/oracle.rs (transpose + reverse_index_bits_in_place) never materialises.
-__global__ void __launch_bounds__(256) leaf_hash_kernel(const u64 *__restrict__ data, size_t col_stride, int n_cols,
+__global__ void __launch_bounds__(256, 3) leaf_hash_kernel(const u64 *__restrict__ data, size_t col_stride, int n_cols,
                                                         size_t n_rows, u64 *__restrict__ digests) {
     size_t row = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_rows) return;

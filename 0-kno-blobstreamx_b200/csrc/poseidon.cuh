@@ -31,7 +31,16 @@
 #define POSEIDON_PARTIAL_PLANES 1
 #endif
 
-__constant__ u32 POSEIDON_POST30_L22[30 * 36] = {POSEIDON_POST30_L22_LIST};
+__constant__ __align__(16) u32 POSEIDON_POST30_L22[30 * 36] = {POSEIDON_POST30_L22_LIST};
+// one round's 36 plane constants through nine 128-bit uniform loads (36 LDCU otherwise: issue slots)
+__device__ __forceinline__ void poseidon_load_post(int round, u32 k[36]) {
+    const uint4 *q = reinterpret_cast<const uint4 *>(POSEIDON_POST30_L22 + 36 * round);
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        uint4 v = q[i];
+        k[4 * i] = v.x, k[4 * i + 1] = v.y, k[4 * i + 2] = v.z, k[4 * i + 3] = v.w;
+    }
+}
 __constant__ u64 POSEIDON_RC[POSEIDON_N_RC] = {POSEIDON_RC_LIST};
 __constant__ u64 POSEIDON_POST_LO[96] = {POSEIDON_POST_LO_LIST};
 __constant__ u64 POSEIDON_POST_HI[96] = {POSEIDON_POST_HI_LIST};
@@ -166,7 +175,9 @@ __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
         for (int r = 0; r < 4; r++) {
 #pragma unroll
             for (int i = 0; i < 12; i++) s[i] = poseidon_sbox(s[i]);
-            poseidon_mds_post_fft(s, POSEIDON_POST30_L22 + 36 * (half * 26 + r));
+            u32 k[36];
+            poseidon_load_post(half * 26 + r, k);
+            poseidon_mds_post_fft(s, k);
         }
         if (half == 0) {
             u32 x0[12], x1[12], x2[12], a0, a1, a2;
@@ -175,7 +186,8 @@ __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
             poseidon_split22(s[0], a0, a1, a2);
 #pragma unroll 1
             for (int p = 4; p < 26; p++) {
-                const u32 *post = POSEIDON_POST30_L22 + 36 * p;
+                u32 post[36];
+                poseidon_load_post(p, post);
                 poseidon_split22(poseidon_sbox(poseidon_merge22(a0, a1, a2)), x0[0], x1[0], x2[0]);
                 u32 y0[12], y1[12], y2[12];
                 poseidon_mds_plane(x0, post, y0);
