@@ -112,7 +112,12 @@ def measured_peak_gbs():
 def measured_traffic():
     """DRAM bytes per launch from the newest committed `ncu --set full` capture (profiles/*_traffic.json)."""
     import glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")))
+    import re
+
+    def version(path):  # r01_v10_traffic.json after r01_v8_traffic.json
+        m = re.search(r"r(\d+)_v(\d+)", os.path.basename(path))
+        return (int(m.group(1)), int(m.group(2))) if m else (0, 0)
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), key=version)
     if not files:
         return {}, None
     try:
