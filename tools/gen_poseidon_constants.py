@@ -273,6 +273,7 @@ def norm22(y):
     assert 0 <= y2 < (1 << 31)
     top = y2 >> 20
     y2 &= 0xFFFFF
+    assert y1 + (top << 10) + (1 << 10) < (1 << 31)  # the carry out of limb 1 is read with an arithmetic shift
     y1 = (y1 + (top << 10)) & M32
     y0 = (y0 - top) & M32
     c0 = s32(y0) >> 22
