@@ -16,6 +16,10 @@ staged NCCL all-to-all; per-GPU cap subtrees; cap gathered) -- see 0-kno-blobstr
 `prove` (skip with --no-prove): wall seconds of one shape-equivalent synthetic proof per GPU (three commits
 from pinned host memory, the opening set, prove_openings) -- BASELINE.json's second metric on random columns.
 
+`roofline` is the leaf-hash kernel (72 % of the step) against the measured HBM copy rate, as the contract asks; its
+`issue` member is the bound that actually applies to Poseidon: warp-instruction issue slots (static SASS counts from
+profiles/*_sass_cost.json x the measured permutation rate, against 148 SMs x 4 schedulers x SM clock).
+
 `--impl reference` times the CPU arm instead: the in-repo oracle port of the plonky2 algorithm
 (the reference mount holds no source and there is no Rust toolchain) with all
 host threads on a bounded sample of the same workload.
@@ -124,6 +128,39 @@ def measured_traffic():
         return json.load(open(files[-1])), os.path.basename(files[-1])
     except Exception:
         return {}, None
+
+
+def sass_cost():
+    """Static instructions per permutation of the shipped leaf-hash kernel (tools/sass_cost.py, profiles/*_sass_cost.json)."""
+    import glob
+    import re
+
+    def version(path):
+        m = re.search(r"r(\d+)_v(\d+)", os.path.basename(path))
+        return (int(m.group(1)), int(m.group(2))) if m else (0, 0)
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_sass_cost.json")), key=version)
+    try:
+        return json.load(open(files[-1]))["per_permutation"], os.path.basename(files[-1])
+    except Exception:
+        return None, None
+
+
+def issue_roofline(n_perms, ms, sm_mhz):
+    """The bound that applies to Poseidon: warp-instruction issue slots.  One slot per instruction, an IMAD.WIDE
+    worth three; peak = 148 SMs x 4 schedulers x SM clock."""
+    cost, src = sass_cost()
+    if not cost:
+        return None
+    clk = (sm_mhz or 1965.0) * 1e6
+    peak = 148 * 4 * clk
+    warps = n_perms / 32.0 / (ms * 1e-3)
+    inst, slots = warps * cost["instructions"], warps * cost["issue_slots_n_plus_2w"]
+    return {"bound": "issue", "unit": "G warp-instruction slots/s", "peak": peak / 1e9, "achieved": slots / 1e9,
+            "frac": slots / peak, "instructions_issued_frac": inst / peak,
+            "instructions_per_permutation": cost["instructions"], "wide_multiplies_per_permutation": cost["wide"],
+            "source": src, "sm_mhz": clk / 1e6,
+            "note": "static SASS counts x measured permutation rate; instructions_issued_frac is what ncu reports "
+                    "as smsp__issue_active (70.8 % in profiles/r01_v10_leafhash_ncu_summary.txt)"}
 
 
 def cpu_reference_arm(args, rank, world):
@@ -434,6 +471,7 @@ def gpu_arm(args, rank, world, local_rank):
     roofline["traffic_source"] = traffic_src
     # the bound that actually applies (integer pipes), from the same committed ncu capture
     roofline["pipes"] = (traffic.get("pipes") or {}).get("leaf_hash_kernel")
+    roofline["issue"] = issue_roofline(nb * ((N_COLS + 7) // 8), avg["leaf_hash_ms"], (clocks or {}).get("sm_mhz"))
     roofline.update({"kernel": "leaf_hash_kernel", "ms_per_launch": avg["leaf_hash_ms"], "peak_source": peak_src,
                      "algorithmic_bytes": leaf_bytes,
                      "note": "dominant kernel by time; Poseidon is integer-pipe bound, so its HBM fraction is low "
