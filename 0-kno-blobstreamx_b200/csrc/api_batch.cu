@@ -482,7 +482,24 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, const u64 *const *col_ptr
             // overlap; at the headline 20 ms of PCIe time hide behind 36 ms of NTT).  Chunks keep >= 8 columns
             // so that every launch still shares the full post-factor table.
             const int chunk = n_cols / 8 >= 8 ? (n_cols + 7) / 8 : 8;
-            const int n_chunks = (n_cols + chunk - 1) / chunk;
+            // Only the first chunk's copy is exposed, so the schedule starts small (8, then 12 columns) and
+            // reaches the full chunk once the transforms of a chunk outlast the copy of the next one.
+            std::vector<int> cstart;  // chunk k covers columns [cstart[k], cstart[k + 1])
+            {
+                int c = 0;
+                if (n_cols >= 64 && chunk > 12)
+                    for (int r : {8, 12}) {
+                        cstart.push_back(c);
+                        c += r;
+                    }
+                while (c < n_cols) {
+                    cstart.push_back(c);
+                    c += chunk;
+                }
+                if (cstart.size() > 1 && n_cols - cstart.back() < 8) cstart.pop_back();  // no tile-starved tail
+                cstart.push_back(n_cols);
+            }
+            const int n_chunks = (int)cstart.size() - 1;
             // pinned contiguous memory goes straight to the DMA engine; anything else through the staging ring
             const bool direct = !col_ptrs && host_is_pinned(input);
             if (!direct) {
@@ -497,7 +514,7 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, const u64 *const *col_ptr
             cudaStreamWaitEvent(ctx->copy_stream, ev[(size_t)n_chunks * 4], 0);
             size_t seq = 0;
             auto upload = [&](int k) -> int {
-                const int c0 = k * chunk, cc = n_cols - c0 < chunk ? n_cols - c0 : chunk;
+                const int c0 = cstart[k], cc = cstart[k + 1] - c0;
                 int r = upload_columns(ctx, host, direct, c0, cc, bt->coeffs + (size_t)c0 * n, &seq);
                 if (r == BSX_OK) cudaEventRecord(ev[4 * k], ctx->copy_stream);
                 return r;
@@ -509,7 +526,7 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, const u64 *const *col_ptr
             else
                 rc = upload(0);
             for (int k = 0; k < n_chunks && rc == BSX_OK; k++) {
-                const int c0 = k * chunk, cc = n_cols - c0 < chunk ? n_cols - c0 : chunk;
+                const int c0 = cstart[k], cc = cstart[k + 1] - c0;
                 cudaStreamWaitEvent(ctx->stream, ev[4 * k], 0);
                 cudaEventRecord(ev[4 * k + 1], ctx->stream);
                 if (k == 0) pt.mark(1, ctx->stream);
