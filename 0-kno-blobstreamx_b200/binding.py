@@ -12,7 +12,7 @@ _SO = os.path.join(_DIR, "csrc", "libbsx_b200.so")
 EXPORTED_SYMBOLS = [
     "bsx_version", "bsx_device_count", "bsx_launch_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
     "bsx_ctx_sync", "bsx_ctx_mem_used", "bsx_batch_from_values", "bsx_batch_from_coeffs",
-    "bsx_batch_from_values_cols", "bsx_batch_from_coeffs_cols", "bsx_batch_free", "bsx_batch_cap",
+    "bsx_batch_from_values_cols", "bsx_batch_from_coeffs_cols", "bsx_batch_from_quotient_values", "bsx_batch_free", "bsx_batch_cap",
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
@@ -69,6 +69,8 @@ def lib():
         "bsx_batch_from_coeffs": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_from_values_cols": (i32, [vp, vp, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_from_coeffs_cols": (i32, [vp, vp, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
+        "bsx_batch_from_quotient_values": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, pp,
+                                                 C.POINTER(Timing)]),
         "bsx_batch_free": (None, [vp]),
         "bsx_batch_cap": (i32, [vp, vp]),
         "bsx_batch_tree": (vp, [vp]),
@@ -198,7 +200,7 @@ class Context:
         """cols: (n_cols, n) column vectors; natural order in and out."""
         a = _np(cols).copy()
         two_d = a.reshape(-1, a.shape[-1])
-        k = {"fft": 0, "ifft": 1, "coset_fft": 2}[kind]
+        k = {"fft": 0, "ifft": 1, "coset_fft": 2, "coset_ifft": 3}[kind]
         self.check(lib().bsx_ntt(self._h, _ptr(two_d), BSX_HOST, _log2_strict(two_d.shape[1]), two_d.shape[0], k,
                                  C.c_uint64(shift)))
         return a
@@ -334,6 +336,34 @@ class PolynomialBatch:
         """`PolynomialBatch::from_coeffs(polynomials, rate_bits, blinding, cap_height, timing, fft_root_table)`."""
         return cls._build(lib().bsx_batch_from_coeffs, ctx, coeffs, rate_bits, blinding, cap_height, salt,
                           device_ptr, shape, timing)
+
+    @classmethod
+    def from_quotient_values(cls, ctx, quotient_values, degree_log, quotient_degree_factor, rate_bits, blinding,
+                             cap_height, salt=None, device_ptr=None, shape=None, timing=False):
+        """plonk/prover.rs, between quotient evaluation and the quotient commitment: every row of `quotient_values`
+        (the values of one challenge's quotient on the coset 7 * <omega> of size 2^degree_log * 2^q, natural order) goes
+        through `coset_ifft(F::coset_shift())`, `trim_to_len(quotient_degree_factor * 2^degree_log)` and
+        `.chunks(2^degree_log)`; the chunks are committed with `PolynomialBatch::from_coeffs`.  Raises where upstream
+        panics (coefficients beyond the quotient degree)."""
+        if device_ptr is not None:
+            n_polys, big = shape
+            src, mem = C.c_void_p(int(device_ptr)), BSX_DEVICE
+        else:
+            vals = _np(quotient_values)
+            if vals.ndim != 2:
+                raise BsxError("expected (n_polys, 2^(degree_log + q)) value vectors")
+            n_polys, big = vals.shape
+            src, mem = _ptr(vals), BSX_HOST
+        q_bits = _log2_strict(big) - int(degree_log)
+        if q_bits < 0:
+            raise BsxError("quotient value vectors are shorter than the degree")
+        h = C.c_void_p()
+        t = Timing() if timing else None
+        ctx.check(lib().bsx_batch_from_quotient_values(
+            ctx._h, src, mem, int(degree_log), q_bits, int(quotient_degree_factor), int(n_polys), int(rate_bits),
+            int(cap_height), 1 if blinding else 0, _ptr(_np(salt)) if salt is not None else None, C.byref(h),
+            C.byref(t) if t is not None else None))
+        return PolynomialBatch(ctx, h, t)
 
     @classmethod
     def from_parts(cls, ctx, coeffs, leaves, digests, cap, rate_bits):

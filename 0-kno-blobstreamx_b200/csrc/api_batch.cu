@@ -953,24 +953,15 @@ extern "C" int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t 
     return BSX_OK;
 }
 
-extern "C" int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t log_n, int32_t n_cols, int32_t kind,
-                           uint64_t shift) {
-    if (!ctx || (!data && n_cols > 0)) return BSX_ERR_INVALID_ARG;
-    BsxScope scope(ctx);
-    if (log_n < 0 || log_n > 24) return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "log_n=%d outside [0, 24]", log_n);
-    if (kind < 0 || kind > 2 || n_cols < 0 || n_cols > 65535) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad kind/n_cols");
-    if (n_cols == 0) return BSX_OK;
-    CU(ctx, cudaSetDevice(ctx->device));
-    size_t n = (size_t)1 << log_n, words = n * (size_t)n_cols;
-    u64 *buf, *tmp;
-    TRY(bsx_alloc(ctx, &buf, words));
-    TRY(bsx_alloc(ctx, &tmp, words));
-    TRY(bsx_copy_in(ctx, buf, (const u64 *)data, words, mem));
+// values (natural order) -> coefficients (natural order) of the polynomial that takes them on shift * H:
+// PolynomialValues::coset_ifft = ifft, then c_i *= shift^-i.  In place on the device buffer `buf`; `tmp` is scratch.
+static int coset_or_plain_ntt(bsx_ctx *ctx, u64 *buf, u64 *tmp, int log_n, int n_cols, int kind, u64 shift) {
+    size_t n = (size_t)1 << log_n;
     NttPlan plan;
     plan.n_dest = 0;
     plan.log_n = log_n;
     bsx_split(log_n, &plan.a, &plan.b);
-    plan.inverse = kind == 1;
+    plan.inverse = kind == 1 || kind == 3;
     plan.src_bitrev = 0;
     plan.n_cosets = 1;
     plan.pre_hi = plan.pre_lo = nullptr;
@@ -980,10 +971,86 @@ extern "C" int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t lo
     TRY(bsx_post_table(ctx, &plan, kind == 2 ? shift % GL_P : 0, n_cols));
     launch_ntt(ctx->tables, plan, buf, n, buf, n, n_cols, ctx->stream);
     launch_bitrev_copy(buf, n, tmp, n, log_n, n_cols, ctx->stream);
+    if (kind == 3) {
+        const u64 *hi, *lo;
+        TRY(bsx_coset_tables(ctx, log_n, 0, gl_host_inv(shift % GL_P), &hi, &lo));
+        launch_scale_two_level(tmp, n, log_n, plan.b, n_cols, hi, lo, ctx->stream);
+    }
     CU(ctx, cudaGetLastError());
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t log_n, int32_t n_cols, int32_t kind,
+                           uint64_t shift) {
+    if (!ctx || (!data && n_cols > 0)) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
+    if (log_n < 0 || log_n > 24) return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "log_n=%d outside [0, 24]", log_n);
+    if (kind < 0 || kind > 3 || n_cols < 0 || n_cols > 65535) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad kind/n_cols");
+    if (kind == 3 && shift % GL_P == 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "coset shift must be non-zero");
+    if (n_cols == 0) return BSX_OK;
+    CU(ctx, cudaSetDevice(ctx->device));
+    size_t n = (size_t)1 << log_n, words = n * (size_t)n_cols;
+    u64 *buf, *tmp;
+    TRY(bsx_alloc(ctx, &buf, words));
+    TRY(bsx_alloc(ctx, &tmp, words));
+    TRY(bsx_copy_in(ctx, buf, (const u64 *)data, words, mem));
+    TRY(coset_or_plain_ntt(ctx, buf, tmp, log_n, n_cols, kind, shift));
     TRY(bsx_copy_out(ctx, (u64 *)data, tmp, words, mem));
     bsx_free(ctx, buf);
     bsx_free(ctx, tmp);
     CU(ctx, cudaStreamSynchronize(ctx->stream));
     return BSX_OK;
+}
+
+// plonk/prover.rs: the tail of compute_quotient_polys (`values.coset_ifft(F::coset_shift())` per challenge) and the
+// commit that follows it in prove() (`quotient_poly.trim_to_len(quotient_degree)`, `.chunks(degree)`,
+// `PolynomialBatch::from_coeffs(all_quotient_poly_chunks, ...)`), without the coefficients leaving the device.
+extern "C" int32_t bsx_batch_from_quotient_values(bsx_ctx *ctx, const uint64_t *values, int32_t mem, int32_t degree_log,
+                                                  int32_t quotient_degree_bits, int32_t quotient_degree_factor,
+                                                  int32_t n_polys, int32_t rate_bits, int32_t cap_height,
+                                                  int32_t blinding, const uint64_t *salt, bsx_batch **out,
+                                                  bsx_timing *timing) {
+    if (!ctx || !out || (!values && n_polys > 0)) return BSX_ERR_INVALID_ARG;
+    *out = nullptr;
+    BsxScope scope(ctx);
+    const int log_big = degree_log + quotient_degree_bits;
+    if (degree_log < 0 || quotient_degree_bits < 0 || log_big > 24)
+        return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "degree_log=%d + quotient_degree_bits=%d outside [0, 24]", degree_log,
+                        quotient_degree_bits);
+    if (quotient_degree_factor < 1 || quotient_degree_factor > (1 << quotient_degree_bits))
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "quotient_degree_factor=%d does not fit 2^%d", quotient_degree_factor,
+                        quotient_degree_bits);
+    if (n_polys < 1 || n_polys * quotient_degree_factor > 65535) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad n_polys");
+    CU(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)1 << degree_log, big = (size_t)1 << log_big, words = big * (size_t)n_polys;
+    u64 *buf, *tmp;
+    int *flag;
+    TRY(bsx_alloc(ctx, &buf, words));
+    TRY(bsx_alloc(ctx, &tmp, words));
+    TRY(bsx_alloc(ctx, (u64 **)&flag, 1));
+    TRY(bsx_copy_in(ctx, buf, (const u64 *)values, words, mem));
+    TRY(coset_or_plain_ntt(ctx, buf, tmp, log_big, n_polys, 3, 7));  // F::coset_shift() = 7
+    const size_t keep = (size_t)quotient_degree_factor * n;
+    if (keep < big) {
+        // trim_to_len: the dropped coefficients must all be zero ("Quotient has failed, the vanishing polynomial
+        // is not divisible by Z_H" upstream); the kept chunks are packed to factor * N words per polynomial
+        CU(ctx, cudaMemsetAsync(flag, 0, sizeof(u64), ctx->stream));
+        launch_any_nonzero(tmp, big, keep, big, n_polys, flag, ctx->stream);
+        int host_flag = 0;
+        CU(ctx, cudaMemcpyAsync(&host_flag, flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(ctx, cudaStreamSynchronize(ctx->stream));
+        if (host_flag)
+            return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "quotient polynomial has degree >= %d * 2^%d (trim_to_len fails upstream)",
+                            quotient_degree_factor, degree_log);
+        for (int c = 1; c < n_polys; c++)
+            CU(ctx, cudaMemcpyAsync(tmp + (size_t)c * keep, tmp + (size_t)c * big, keep * sizeof(u64),
+                                    cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    // polynomial c, chunk j = words [(c * factor + j) * N, +N): exactly a column-major (n_polys * factor) x N matrix
+    int32_t rc = bsx_batch_from_coeffs(ctx, (const uint64_t *)tmp, BSX_DEVICE, degree_log, n_polys * quotient_degree_factor, rate_bits,
+                                       cap_height, blinding, salt, out, timing);
+    bsx_free(ctx, buf);
+    bsx_free(ctx, tmp);
+    bsx_free(ctx, (u64 *)flag);
+    return rc;
 }

@@ -73,6 +73,9 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
                 size_t dst_stride, int n_cols, cudaStream_t st);
 // out[i] = first * base^(i * step_mul) for i < n
 void launch_fill_powers(u64 *out, u64 base, u64 first, size_t n, cudaStream_t st);
+void launch_scale_two_level(u64 *data, size_t stride, int log_n, int b, int n_cols, const u64 *hi, const u64 *lo,
+                            cudaStream_t st);
+void launch_any_nonzero(const u64 *data, size_t stride, size_t begin, size_t end, int n_cols, int *flag, cudaStream_t st);
 // dst[c][i] = src[c][bitrev_log_n(i)]
 void launch_bitrev_copy(const u64 *src, size_t src_stride, u64 *dst, size_t dst_stride, int log_n, int n_cols,
                         cudaStream_t st);

@@ -479,6 +479,35 @@ void launch_fill_powers(u64 *out, u64 base, u64 first, size_t n, cudaStream_t st
     BSX_COUNT_LAUNCH(); fill_powers_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, base, first, n);
 }
 
+// data[c][i] *= hi[i >> b] * lo[i & (2^b - 1)]: the coefficient scaling of PolynomialValues::coset_ifft
+// (c_i *= shift^-i) from the two-level power tables of bsx_coset_tables
+__global__ void scale_two_level_kernel(u64 *__restrict__ data, size_t stride, int log_n, int b,
+                                       const u64 *__restrict__ hi, const u64 *__restrict__ lo) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >> log_n) return;
+    u64 f = gl_mul_lazy(__ldg(hi + (i >> b)), __ldg(lo + (i & (((size_t)1 << b) - 1))));
+    u64 *q = data + (size_t)blockIdx.y * stride + i;
+    *q = gl_canon_fast(gl_mul_lazy(*q, f));
+}
+void launch_scale_two_level(u64 *data, size_t stride, int log_n, int b, int n_cols, const u64 *hi, const u64 *lo,
+                            cudaStream_t st) {
+    if (n_cols <= 0) return;
+    size_t n = (size_t)1 << log_n;
+    dim3 grid((unsigned)((n + 255) / 256), (unsigned)n_cols);
+    BSX_COUNT_LAUNCH(); scale_two_level_kernel<<<grid, 256, 0, st>>>(data, stride, log_n, b, hi, lo);
+}
+
+// *flag |= 1 when any word of data[c][begin .. end) is non-zero (PolynomialCoeffs::trim_to_len's check)
+__global__ void any_nonzero_kernel(const u64 *__restrict__ data, size_t stride, size_t begin, size_t end, int *flag) {
+    size_t i = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < end && data[(size_t)blockIdx.y * stride + i] != 0) atomicOr(flag, 1);
+}
+void launch_any_nonzero(const u64 *data, size_t stride, size_t begin, size_t end, int n_cols, int *flag, cudaStream_t st) {
+    if (n_cols <= 0 || end <= begin) return;
+    dim3 grid((unsigned)((end - begin + 255) / 256), (unsigned)n_cols);
+    BSX_COUNT_LAUNCH(); any_nonzero_kernel<<<grid, 256, 0, st>>>(data, stride, begin, end, flag);
+}
+
 __global__ void bitrev_copy_kernel(const u64 *__restrict__ src, size_t src_stride, u64 *__restrict__ dst,
                                    size_t dst_stride, int log_n) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -266,12 +266,25 @@ int32_t bsx_fri_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_or
 int32_t bsx_batch_eval_ext(bsx_batch *batch, int32_t col_begin, int32_t n_cols, const uint64_t *points_host,
                            int32_t n_points, uint64_t *out_host);
 
+/* Replaces the hand-over from quotient evaluation to the quotient commitment in plonk/prover.rs: the tail of
+ * compute_quotient_polys (`PolynomialValues::coset_ifft(F::coset_shift())` of every challenge's quotient values) and,
+ * in prove(), `quotient_poly.trim_to_len(quotient_degree)`, `.chunks(degree)` and
+ * `PolynomialBatch::from_coeffs(all_quotient_poly_chunks, rate_bits, blinding, cap_height, ..)`.
+ * values = n_polys x 2^(degree_log + quotient_degree_bits) words, column-major, natural order: the quotient's values on
+ * the coset 7 * <omega_{N 2^q}>.  quotient_degree_factor <= 2^quotient_degree_bits chunks of 2^degree_log coefficients are
+ * kept per polynomial; non-zero coefficients beyond them fail with BSX_ERR_INVALID_ARG (upstream `trim_to_len` returns
+ * Err and prove() panics "Quotient has failed ...").  The batch has n_polys * quotient_degree_factor polynomials. */
+int32_t bsx_batch_from_quotient_values(bsx_ctx *ctx, const uint64_t *values, int32_t mem, int32_t degree_log,
+                                       int32_t quotient_degree_bits, int32_t quotient_degree_factor, int32_t n_polys,
+                                       int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt,
+                                       bsx_batch **out, bsx_timing *timing);
+
 /* ---- test hooks -----------------------------------------------------------------------------
  * Poseidon::poseidon on n states (n x 12 words, in place). */
 int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n);
 /* Batched transforms on n_cols columns of 2^log_n words, column-major, in place, natural order in and
  * out.  kind: 0 = fft (PolynomialCoeffs::fft), 1 = ifft (PolynomialValues::ifft),
- * 2 = coset_fft(shift) (PolynomialCoeffs::coset_fft). */
+ * 2 = coset_fft(shift) (PolynomialCoeffs::coset_fft), 3 = coset_ifft(shift) (PolynomialValues::coset_ifft). */
 int32_t bsx_ntt(bsx_ctx *ctx, uint64_t *data, int32_t mem, int32_t log_n, int32_t n_cols, int32_t kind,
                 uint64_t shift);
 

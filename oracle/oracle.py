@@ -72,6 +72,27 @@ def coset_fft(a, shift=7):
     return a
 
 
+def coset_ifft(a, shift=7):
+    """PolynomialValues::coset_ifft (field/src/polynomial/mod.rs)"""
+    a = _a(a).copy()
+    lib().orc_coset_ifft(_ptr(a), C.c_int(int(np.log2(a.size))), C.c_uint64(shift))
+    return a
+
+
+def quotient_chunks(quotient_values, degree_log, quotient_degree_factor):
+    """plonk/prover.rs: `values.coset_ifft(F::coset_shift())` per quotient polynomial, `trim_to_len(quotient_degree)`
+    (raises where upstream's expect() panics), `.chunks(degree)`: (n_polys * factor, 2^degree_log) coefficient rows."""
+    n = 1 << degree_log
+    out = []
+    for v in _a(quotient_values):
+        c = coset_ifft(v)
+        keep = quotient_degree_factor * n
+        if c[keep:].any():
+            raise ValueError("Quotient has failed, the vanishing polynomial is not divisible by Z_H")
+        out.extend(c[j * n:(j + 1) * n] for j in range(quotient_degree_factor))
+    return np.stack(out)
+
+
 def lde(coeffs, rate_bits, shift=7):
     coeffs = _a(coeffs)
     out = np.empty(coeffs.size << rate_bits, dtype=np.uint64)

@@ -138,6 +138,16 @@ void orc_coset_fft(uint64_t *a, int log_n, uint64_t shift) {
     }
     orc_fft(a, log_n);
 }
+/* field/src/polynomial/mod.rs PolynomialValues::coset_ifft: ifft, then c_j *= shift^-j */
+void orc_coset_ifft(uint64_t *a, int log_n, uint64_t shift) {
+    size_t n = (size_t)1 << log_n;
+    orc_ifft(a, log_n);
+    uint64_t sinv = orc_inv(shift % P), s = 1;
+    for (size_t i = 0; i < n; i++) {
+        a[i] = mul_(a[i], s);
+        s = mul_(s, sinv);
+    }
+}
 /* PolynomialCoeffs::lde (zero pad) followed by coset_fft (fri/oracle.rs lde_values) */
 void orc_lde(const uint64_t *coeffs, int log_n, int rate_bits, uint64_t shift, uint64_t *out) {
     size_t n = (size_t)1 << log_n, nb = n << rate_bits;

@@ -41,6 +41,7 @@ void orc_ext_inv(const uint64_t a[2], uint64_t out[2]);
 void orc_fft(uint64_t *a, int log_n);                       /* natural in, natural out */
 void orc_ifft(uint64_t *a, int log_n);
 void orc_coset_fft(uint64_t *a, int log_n, uint64_t shift); /* a_j *= shift^j ; fft */
+void orc_coset_ifft(uint64_t *a, int log_n, uint64_t shift); /* ifft ; a_j *= shift^-j */
 /* PolynomialCoeffs::lde(rate_bits).coset_fft(shift): out has 2^(log_n+rate_bits) entries */
 void orc_lde(const uint64_t *coeffs, int log_n, int rate_bits, uint64_t shift, uint64_t *out);
 /* strided variants for extension polynomials stored interleaved [c0,c1,...] */

@@ -193,3 +193,29 @@ def test_polynomial_batch_bytes_roundtrip(oracle):
         for bad in (data[:-1], data[:100], data + b"\0", b""):
             with pytest.raises(ValueError):
                 ser.read_polynomial_batch(bad)
+
+
+def test_coset_ifft_inverts_coset_fft_and_interpolates(oracle):
+    """PolynomialValues::coset_ifft: the inverse of PolynomialCoeffs::coset_fft, and the interpolant on shift * H."""
+    for log_n in (0, 1, 4, 9):
+        c = splitmix_field(40 + log_n, (1 << log_n,))
+        for shift in (7, 0x123456789ABCDEF):
+            assert (oracle.coset_ifft(oracle.coset_fft(c, shift), shift) == c).all()
+    n, shift = 8, 7
+    c = [int(x) for x in splitmix_field(5, (n,))]
+    w = pow(7, (P - 1) // n, P)
+    vals = np.array([sum(ci * pow(shift * pow(w, k, P) % P, i, P) for i, ci in enumerate(c)) % P for k in range(n)],
+                    dtype=np.uint64)
+    assert [int(x) for x in oracle.coset_ifft(vals, shift)] == c
+
+
+def test_quotient_chunks_trim_and_panic(oracle):
+    n, q, factor = 16, 3, 6
+    coeffs = np.zeros((2, n << q), dtype=np.uint64)
+    coeffs[:, :factor * n] = splitmix_field(8, (2, factor * n))
+    vals = np.stack([oracle.coset_fft(c, 7) for c in coeffs])
+    ch = oracle.quotient_chunks(vals, 4, factor)
+    assert ch.shape == (2 * factor, n) and (ch.reshape(2, -1) == coeffs[:, :factor * n]).all()
+    coeffs[0, -1] = 5
+    with pytest.raises(ValueError):
+        oracle.quotient_chunks(np.stack([oracle.coset_fft(c, 7) for c in coeffs]), 4, factor)
