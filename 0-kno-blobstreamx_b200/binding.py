@@ -12,7 +12,7 @@ _SO = os.path.join(_DIR, "csrc", "libbsx_b200.so")
 EXPORTED_SYMBOLS = [
     "bsx_version", "bsx_device_count", "bsx_launch_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
     "bsx_ctx_sync", "bsx_ctx_mem_used", "bsx_batch_from_values", "bsx_batch_from_coeffs",
-    "bsx_batch_from_values_cols", "bsx_batch_from_coeffs_cols", "bsx_batch_from_quotient_values", "bsx_batch_free", "bsx_batch_cap",
+    "bsx_batch_from_values_cols", "bsx_batch_from_coeffs_cols", "bsx_batch_from_quotient_values", "bsx_partial_products_and_zs", "bsx_batch_free", "bsx_batch_cap",
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
@@ -71,6 +71,7 @@ def lib():
         "bsx_batch_from_coeffs_cols": (i32, [vp, vp, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_from_quotient_values": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, pp,
                                                  C.POINTER(Timing)]),
+        "bsx_partial_products_and_zs": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, vp, vp, i32, vp, i32]),
         "bsx_batch_free": (None, [vp]),
         "bsx_batch_cap": (i32, [vp, vp]),
         "bsx_batch_tree": (vp, [vp]),
@@ -188,6 +189,34 @@ class Context:
             self.close()
         except Exception:
             pass
+
+    def partial_products_and_zs(self, wires, sigmas, k_is, betas, gammas, max_degree, out_device_ptr=None,
+                                device_ptrs=None, shape=None):
+        """plonk/prover.rs `all_wires_permutation_partial_products`, columns ordered as the Zs commitment wants them
+        (Zs first, then each challenge's partial products).  wires, sigmas: (n_routed, n) values (or `device_ptrs` =
+        (wires_ptr, sigmas_ptr) with `shape`); returns the (n_challenges * ceil(n_routed / max_degree), n) array, or
+        writes it to `out_device_ptr`."""
+        if device_ptrs is not None:
+            n_routed, n = shape
+            w, s, mem = C.c_void_p(int(device_ptrs[0])), C.c_void_p(int(device_ptrs[1])), BSX_DEVICE
+        else:
+            wires, sigmas = _np(wires), _np(sigmas)
+            if wires.ndim != 2 or wires.shape != sigmas.shape:
+                raise BsxError("wires and sigmas must both be (n_routed, n)")
+            n_routed, n = wires.shape
+            w, s, mem = _ptr(wires), _ptr(sigmas), BSX_HOST
+        k_is, betas, gammas = _np(k_is).reshape(-1), _np(betas).reshape(-1), _np(gammas).reshape(-1)
+        if k_is.shape[0] != n_routed or betas.shape != gammas.shape:
+            raise BsxError("k_is / betas / gammas do not match the wires")
+        n_chunks = -(-n_routed // int(max_degree)) if max_degree > 0 else 0
+        out = None
+        if out_device_ptr is None:
+            out = np.zeros((betas.shape[0] * n_chunks, n), dtype=np.uint64)
+        self.check(lib().bsx_partial_products_and_zs(
+            self._h, w, s, mem, _log2_strict(n), int(n_routed), int(max_degree), _ptr(k_is), _ptr(betas), _ptr(gammas),
+            int(betas.shape[0]), _ptr(out) if out is not None else C.c_void_p(int(out_device_ptr)),
+            BSX_HOST if out is not None else BSX_DEVICE))
+        return out
 
     # ---- test hooks
     def poseidon_permute(self, states):

@@ -279,6 +279,23 @@ int32_t bsx_batch_from_quotient_values(bsx_ctx *ctx, const uint64_t *values, int
                                        int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt,
                                        bsx_batch **out, bsx_timing *timing);
 
+/* Replaces plonk/prover.rs `all_wires_permutation_partial_products` (per challenge
+ * `wires_permutation_partial_products_and_zs`, with `quotient_chunk_products` and `partial_products_and_z_gx` of
+ * plonk/permutation_argument.rs / util/partial_products.rs): the prover step between the wires commitment and the
+ * Zs commitment.  wires, sigmas = n_routed x 2^log_n words, column-major, natural order: the routed wire values of
+ * the witness and the values of the sigma polynomials on the subgroup (`prover_data.sigmas`, transposed).
+ * Row i (x = omega^i), challenge c, chunk m of max_degree (= quotient_degree_factor) wires:
+ *   q_m = prod_j (w_j + beta_c k_is[j] x + gamma_c) / prod_j (w_j + beta_c sigma_j + gamma_c);
+ *   Z_c(1) = 1, Z_c(g x) = Z_c(x) prod_m q_m, partial product m = Z_c(x) q_0 .. q_m  (m < num_partial_products).
+ * out = (n_challenges * ceil(n_routed / max_degree)) x 2^log_n values in the column order of the commitment that
+ * follows ("Z is expected at the front of our batch"): Z_0 .. Z_{n_challenges - 1}, then the num_partial_products
+ * columns of challenge 0, of challenge 1, ...  -- ready for bsx_batch_from_values.  A zero denominator fails with
+ * BSX_ERR_INVALID_ARG (upstream panics in batch_multiplicative_inverse). */
+int32_t bsx_partial_products_and_zs(bsx_ctx *ctx, const uint64_t *wires, const uint64_t *sigmas, int32_t mem,
+                                    int32_t log_n, int32_t n_routed, int32_t max_degree, const uint64_t *k_is_host,
+                                    const uint64_t *betas_host, const uint64_t *gammas_host, int32_t n_challenges,
+                                    uint64_t *out, int32_t out_mem);
+
 /* ---- test hooks -----------------------------------------------------------------------------
  * Poseidon::poseidon on n states (n x 12 words, in place). */
 int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n);

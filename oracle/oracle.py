@@ -93,6 +93,26 @@ def quotient_chunks(quotient_values, degree_log, quotient_degree_factor):
     return np.stack(out)
 
 
+def partial_products_and_zs(wires, sigmas, k_is, betas, gammas, max_degree):
+    """plonk/prover.rs all_wires_permutation_partial_products followed by prove()'s reordering ("Z is expected at the
+    front of our batch"): rows Z_0 .. Z_{c-1}, then every challenge's partial products."""
+    wires, sigmas, k_is = _a(wires), _a(sigmas), _a(k_is)
+    n_routed, n = wires.shape
+    n_chunks = -(-n_routed // max_degree)
+    zs, pps = [], []
+    for beta, gamma in zip(betas, gammas):
+        z = np.empty(n, dtype=np.uint64)
+        pp = np.empty((n_chunks - 1, n), dtype=np.uint64)
+        rc = lib().orc_partial_products_and_z(_ptr(wires), _ptr(sigmas), C.c_int(int(np.log2(n))), C.c_int(n_routed),
+                                              C.c_int(max_degree), _ptr(k_is), C.c_uint64(int(beta) % P),
+                                              C.c_uint64(int(gamma) % P), _ptr(z), _ptr(pp))
+        if rc != 0:
+            raise ZeroDivisionError("Tried to invert zero")
+        zs.append(z)
+        pps.append(pp)
+    return np.concatenate([np.stack(zs)] + pps, axis=0)
+
+
 def lde(coeffs, rate_bits, shift=7):
     coeffs = _a(coeffs)
     out = np.empty(coeffs.size << rate_bits, dtype=np.uint64)

@@ -378,3 +378,38 @@ void orc_set_num_threads(int n) {
     (void)n;
 #endif
 }
+
+/* ------------------------------------------------- permutation argument: Zs and partial products
+ * plonk/prover.rs wires_permutation_partial_products_and_zs, for one challenge (beta, gamma):
+ *   per row i: numerators (w_j + beta k_j x_i + gamma), denominators (w_j + beta sigma_j + gamma), quotients,
+ *   quotient_chunk_products(quotients, max_degree)  (util/partial_products.rs: products of chunks of max_degree);
+ *   partial_products_and_z_gx(z_x, chunk_products): running products starting from z_x; the last one is Z(g x) and is
+ *   swapped with Z(x) so that row i holds [pp_1 .. pp_{num_prods}, Z(x_i)].
+ * wires, sigmas: n_routed x n column-major.  out_z[n], out_pp[num_prods][n].  Returns -1 on a zero denominator
+ * (upstream panics in batch_multiplicative_inverse). */
+int orc_partial_products_and_z(const uint64_t *wires, const uint64_t *sigmas, int log_n, int n_routed, int max_degree,
+                               const uint64_t *k_is, uint64_t beta, uint64_t gamma, uint64_t *out_z, uint64_t *out_pp) {
+    size_t n = (size_t)1 << log_n;
+    int n_chunks = (n_routed + max_degree - 1) / max_degree, num_prods = n_chunks - 1;
+    uint64_t g = orc_root_of_unity(log_n), x = 1, z_x = 1;
+    for (size_t i = 0; i < n; i++) {
+        uint64_t acc = z_x;
+        for (int m = 0; m < n_chunks; m++) {
+            uint64_t chunk = 1;
+            for (int j = m * max_degree; j < n_routed && j < (m + 1) * max_degree; j++) {
+                uint64_t w = wires[(size_t)j * n + i] % P;
+                uint64_t s_id = mul_(k_is[j] % P, x);
+                uint64_t num = add_(add_(w, mul_(beta, s_id)), gamma);
+                uint64_t den = add_(add_(w, mul_(beta, sigmas[(size_t)j * n + i] % P)), gamma);
+                if (den == 0) return -1;
+                chunk = mul_(chunk, mul_(num, orc_inv(den)));
+            }
+            acc = mul_(acc, chunk);
+            if (m < num_prods) out_pp[(size_t)m * n + i] = acc;
+        }
+        out_z[i] = z_x; /* the swap: Z(x) stays in this row, Z(g x) moves on */
+        z_x = acc;
+        x = mul_(x, g);
+    }
+    return 0;
+}

@@ -141,4 +141,7 @@ void orc_set_num_threads(int n);
 #ifdef __cplusplus
 }
 #endif
+/* plonk/prover.rs wires_permutation_partial_products_and_zs for one challenge; -1 on a zero denominator */
+int orc_partial_products_and_z(const uint64_t *wires, const uint64_t *sigmas, int log_n, int n_routed, int max_degree,
+                               const uint64_t *k_is, uint64_t beta, uint64_t gamma, uint64_t *out_z, uint64_t *out_pp);
 #endif

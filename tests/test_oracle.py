@@ -219,3 +219,59 @@ def test_quotient_chunks_trim_and_panic(oracle):
     coeffs[0, -1] = 5
     with pytest.raises(ValueError):
         oracle.quotient_chunks(np.stack([oracle.coset_fft(c, 7) for c in coeffs]), 4, factor)
+
+
+def _perm_instance(seed, log_n, n_routed, swaps):
+    """Routed wire values with copy constraints and the sigma values of the matching permutation:
+    sigma_j(x_i) = k_{j'} x_{i'} for the position (j', i') that (j, i) is wired to."""
+    n = 1 << log_n
+    rng = np.random.default_rng(seed)
+    wires = splitmix_field(seed, (n_routed, n)).copy()
+    k_is = np.array([pow(7, j, P) for j in range(n_routed)], dtype=np.uint64)  # distinct coset representatives
+    w = pow(7, (P - 1) >> log_n, P)
+    xs = [pow(w, i, P) for i in range(n)]
+    target = {(j, i): (j, i) for j in range(n_routed) for i in range(n)}
+    for _ in range(swaps):
+        a = (int(rng.integers(n_routed)), int(rng.integers(n)))
+        b = (int(rng.integers(n_routed)), int(rng.integers(n)))
+        if a == b or target[a] != a or target[b] != b:
+            continue
+        target[a], target[b] = b, a
+        wires[b] = wires[a]
+    sigmas = np.array([[int(k_is[target[(j, i)][0]]) * xs[target[(j, i)][1]] % P for i in range(n)]
+                       for j in range(n_routed)], dtype=np.uint64)
+    return wires, sigmas, k_is, xs
+
+
+def test_partial_products_and_zs_against_direct_formula(oracle):
+    """wires_permutation_partial_products_and_zs restated with Python integers on a tiny instance."""
+    log_n, n_routed, deg = 3, 5, 2
+    wires, sigmas, k_is, xs = _perm_instance(11, log_n, n_routed, 6)
+    betas, gammas = [0x1234567, 99], [0xABCDEF01, 5]
+    got = oracle.partial_products_and_zs(wires, sigmas, k_is, betas, gammas, deg)
+    n, n_chunks = 1 << log_n, 3
+    assert got.shape == (2 * n_chunks, n)
+    for c, (beta, gamma) in enumerate(zip(betas, gammas)):
+        z = 1
+        for i in range(n):
+            assert int(got[c, i]) == z
+            acc = z
+            for m in range(n_chunks):
+                for j in range(m * deg, min(n_routed, (m + 1) * deg)):
+                    num = (int(wires[j, i]) + beta * int(k_is[j]) * xs[i] + gamma) % P
+                    den = (int(wires[j, i]) + beta * int(sigmas[j, i]) + gamma) % P
+                    acc = acc * num * pow(den, P - 2, P) % P
+                if m < n_chunks - 1:
+                    assert int(got[2 + c * (n_chunks - 1) + m, i]) == acc
+            z = acc
+        assert z == 1  # the copy constraints hold, so the grand product closes
+
+
+def test_partial_products_identity_permutation_and_zero_denominator(oracle):
+    wires, sigmas, k_is, xs = _perm_instance(12, 4, 9, 0)
+    got = oracle.partial_products_and_zs(wires, sigmas, k_is, [3, 4], [5, 6], 4)
+    assert got.shape == (2 * 3, 16) and (got == 1).all()
+    beta, gamma = 7, 9
+    wires[2, 5] = np.uint64((-(beta * int(sigmas[2, 5]) + gamma)) % P)
+    with pytest.raises(ZeroDivisionError):
+        oracle.partial_products_and_zs(wires, sigmas, k_is, [beta], [gamma], 4)
