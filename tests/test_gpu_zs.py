@@ -48,6 +48,17 @@ def test_random_sigmas_and_noncanonical_words(ctx, oracle):
     assert (ctx.partial_products_and_zs(big, sigmas, k_is, [11, 12, 13], [14, 15, 16], 8) == got).all()
 
 
+def test_long_scan_many_blocks(ctx, oracle):
+    """2^19 rows: the scan of the block products runs over more than one 256-block pass."""
+    n_routed, log_n = 3, 19
+    wires = splitmix_field(50, (n_routed, 1 << log_n))
+    sigmas = splitmix_field(51, (n_routed, 1 << log_n))
+    k_is = splitmix_field(52, (n_routed,))
+    got = ctx.partial_products_and_zs(wires, sigmas, k_is, [21, 22], [23, 24], 2)
+    want = oracle.partial_products_and_zs(wires, sigmas, k_is, [21, 22], [23, 24], 2)
+    assert got.shape == (4, 1 << log_n) and (got == want).all()
+
+
 def test_device_in_device_out_feeds_the_zs_commitment(pkg, ctx, oracle):
     import torch
     log_n, n_routed, deg = 12, 80, 8
