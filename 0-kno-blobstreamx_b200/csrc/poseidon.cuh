@@ -42,6 +42,7 @@ __device__ __forceinline__ void poseidon_load_post(int round, u32 k[36]) {
     }
 }
 __constant__ u64 POSEIDON_RC[POSEIDON_N_RC] = {POSEIDON_RC_LIST};
+#if !POSEIDON_PARTIAL_PLANES  // constants of the sparse partial rounds (v7 path, kept for A/B builds)
 __constant__ u64 POSEIDON_POST_LO[96] = {POSEIDON_POST_LO_LIST};
 __constant__ u64 POSEIDON_POST_HI[96] = {POSEIDON_POST_HI_LIST};
 __constant__ u32 POSEIDON_POST_L22[8 * 36] = {POSEIDON_POST_L22_LIST};
@@ -49,6 +50,7 @@ __constant__ u64 POSEIDON_FAST_INIT[121] = {POSEIDON_FAST_INIT_LIST};
 __constant__ u64 POSEIDON_FAST_K[22] = {POSEIDON_FAST_K_LIST};
 __constant__ u64 POSEIDON_FAST_V[242] = {POSEIDON_FAST_V_LIST};
 __constant__ u64 POSEIDON_FAST_W[242] = {POSEIDON_FAST_W_LIST};
+#endif
 
 __device__ __forceinline__ u64 poseidon_sbox(u64 x) {
     u64 x2 = gl_sqr_lazy(x), x4 = gl_sqr_lazy(x2), x3 = gl_mul_lazy(x, x2);
