@@ -110,6 +110,20 @@ def main():
                          "proof_of_work_bits": pow_bits, "num_query_rounds": nq, "arity_bits": ab,
                          "proof_words": int(proof.size), "proof_sha256": digest(proof), "first_cap_word": hx(proof[:1]),
                          "pow_witness": hx(proof[-1:]), "challenger_after": hx(list(ch.state))})
+    # the prover steps either side of quotient evaluation (plonk/prover.rs): coset_ifft + chunks + commit, Zs + partial products
+    x = splitmix_field(42, (8,))
+    g["ntt"]["coset_ifft_7"] = hx(O.coset_ifft(x, 7))
+    qv = splitmix_field(60, (2, 1 << 9))
+    chunks = O.quotient_chunks(qv, 6, 8)
+    qb = O.batch_from_values(chunks, 3, 2, from_coeffs=True)
+    g["quotient"] = {"seed": 60, "degree_log": 6, "quotient_degree_bits": 3, "quotient_degree_factor": 8, "n_polys": 2,
+                     "rate_bits": 3, "cap_height": 2, "chunks_sha256": digest(chunks), "chunk_0_head": hx(chunks[0][:4]),
+                     "cap": hx(qb["cap"])}
+    zw, zs_, zk = splitmix_field(61, (10, 64)), splitmix_field(62, (10, 64)), splitmix_field(63, (10,))
+    zb, zg = splitmix_field(64, (2,)), splitmix_field(65, (2,))
+    zz = O.partial_products_and_zs(zw, zs_, zk, zb, zg, 4)
+    g["zs"] = {"wires_seed": 61, "sigmas_seed": 62, "k_is_seed": 63, "betas_seed": 64, "gammas_seed": 65, "log_n": 6,
+               "n_routed": 10, "max_degree": 4, "shape": list(zz.shape), "sha256": digest(zz), "row_1": hx(zz[:, 1])}
     with open(os.path.join(HERE, "golden_vectors.json"), "w") as f:
         json.dump(g, f, indent=1)
     print("wrote golden_vectors.json: %d commit cases, %d fri cases" % (len(g["commit"]), len(g["fri"])))

@@ -72,6 +72,26 @@ def test_oracle_reproduces_golden_commits_and_fri(oracle):
     assert digest(proof) == c["proof_sha256"]
 
 
+def _zs_inputs():
+    z = G["zs"]
+    n = 1 << z["log_n"]
+    return (splitmix_field(z["wires_seed"], (z["n_routed"], n)), splitmix_field(z["sigmas_seed"], (z["n_routed"], n)),
+            splitmix_field(z["k_is_seed"], (z["n_routed"],)), splitmix_field(z["betas_seed"], (2,)),
+            splitmix_field(z["gammas_seed"], (2,)), z["max_degree"])
+
+
+def test_oracle_reproduces_golden_quotient_and_zs(oracle):
+    O = oracle
+    assert hx(O.coset_ifft(splitmix_field(G["ntt"]["seed"], (8,)), 7)) == G["ntt"]["coset_ifft_7"]
+    q = G["quotient"]
+    chunks = O.quotient_chunks(splitmix_field(q["seed"], (q["n_polys"], 1 << (q["degree_log"] + q["quotient_degree_bits"]))),
+                               q["degree_log"], q["quotient_degree_factor"])
+    assert digest(chunks) == q["chunks_sha256"] and hx(chunks[0][:4]) == q["chunk_0_head"]
+    assert hx(O.batch_from_values(chunks, q["rate_bits"], q["cap_height"], from_coeffs=True)["cap"]) == q["cap"]
+    zz = O.partial_products_and_zs(*_zs_inputs())
+    assert list(zz.shape) == G["zs"]["shape"] and digest(zz) == G["zs"]["sha256"] and hx(zz[:, 1]) == G["zs"]["row_1"]
+
+
 # ------------------------------------------------------------------ GPU: the CUDA path vs the committed vectors
 @pytest.fixture(scope="module")
 def pkg():
@@ -108,6 +128,19 @@ def test_device_reproduces_golden_primitives(pkg, ctx):
         if "proof_leaf_1" in c:
             assert hx(t.prove(1)) == c["proof_leaf_1"]
         t.close()
+
+
+@pytest.mark.gpu
+def test_device_reproduces_golden_quotient_and_zs(pkg, ctx):
+    assert hx(ctx.ntt(splitmix_field(G["ntt"]["seed"], (1, 8)), "coset_ifft", 7)) == G["ntt"]["coset_ifft_7"]
+    q = G["quotient"]
+    vals = splitmix_field(q["seed"], (q["n_polys"], 1 << (q["degree_log"] + q["quotient_degree_bits"])))
+    b = pkg.PolynomialBatch.from_quotient_values(ctx, vals, q["degree_log"], q["quotient_degree_factor"], q["rate_bits"],
+                                                 False, q["cap_height"])
+    assert hx(b.cap) == q["cap"] and digest(b.polynomials) == q["chunks_sha256"]
+    b.close()
+    zz = ctx.partial_products_and_zs(*_zs_inputs())
+    assert list(zz.shape) == G["zs"]["shape"] and digest(zz) == G["zs"]["sha256"] and hx(zz[:, 1]) == G["zs"]["row_1"]
 
 
 @pytest.mark.gpu
