@@ -25,14 +25,15 @@ __global__ void __launch_bounds__(256) zs_rows_kernel(const u64 *__restrict__ wi
     const int c = blockIdx.y;
     const u64 beta = betas[c], gamma = gammas[c];
     const u64 bx = gl_mul(beta, xs[i]);
+    // lazy arithmetic (any u64 representative) inside the row, canonical words at the stores
     u64 num[ZS_MAX_CHUNKS], den[ZS_MAX_CHUNKS];
     for (int m = 0; m < n_chunks; m++) {
         u64 a = 1, d = 1;
         const int j1 = min(n_routed, (m + 1) * max_degree);
         for (int j = m * max_degree; j < j1; j++) {
-            u64 w = gl_add(gl_canon(wires[(size_t)j * n + i]), gamma);
-            a = gl_mul(a, gl_add(w, gl_mul(bx, k_is[j])));
-            d = gl_mul(d, gl_add(w, gl_mul(beta, gl_canon(sigmas[(size_t)j * n + i]))));
+            u64 wg = gl_add_lazy_canon(wires[(size_t)j * n + i], gamma);            // w + gamma
+            a = gl_mul_lazy(a, gl_mul_add_lazy(bx, k_is[j], wg));                   // . (w + beta k x + gamma)
+            d = gl_mul_lazy(d, gl_mul_add_lazy(beta, sigmas[(size_t)j * n + i], wg));  // . (w + beta sigma + gamma)
         }
         num[m] = a;
         den[m] = d;
@@ -43,20 +44,25 @@ __global__ void __launch_bounds__(256) zs_rows_kernel(const u64 *__restrict__ wi
     u64 acc = 1;
     for (int m = 0; m < n_chunks; m++) {
         pre[m] = acc;
-        acc = gl_mul(acc, den[m]);
+        acc = gl_mul_lazy(acc, den[m]);
     }
-    if (acc == 0) atomicOr(zero_flag, 1);
-    u64 inv = gl_inv(acc);
+    if (gl_canon_fast(acc) == 0) atomicOr(zero_flag, 1);
+    u64 inv = 1, sq = acc;  // acc^(p - 2), p - 2 = 0xFFFFFFFEFFFFFFFF
+    for (int bit = 0; bit < 64; bit++) {
+        if (bit != 32) inv = gl_mul_lazy(inv, sq);
+        sq = gl_mul_lazy(sq, sq);
+    }
     for (int m = n_chunks - 1; m >= 0; m--) {
-        u64 dinv = gl_mul(inv, pre[m]);
-        inv = gl_mul(inv, den[m]);
-        num[m] = gl_mul(num[m], dinv);  // q_m
+        u64 dinv = gl_mul_lazy(inv, pre[m]);
+        inv = gl_mul_lazy(inv, den[m]);
+        num[m] = gl_mul_lazy(num[m], dinv);  // q_m
     }
     acc = 1;
     for (int m = 0; m < n_chunks; m++) {
-        acc = gl_mul(acc, num[m]);
-        if (m + 1 < n_chunks) running[((size_t)c * (n_chunks - 1) + m) * n + i] = acc;
+        acc = gl_mul_lazy(acc, num[m]);
+        if (m + 1 < n_chunks) running[((size_t)c * (n_chunks - 1) + m) * n + i] = gl_canon_fast(acc);
     }
+    acc = gl_canon_fast(acc);
     row_prod[(size_t)c * n + i] = acc;
 }
 
