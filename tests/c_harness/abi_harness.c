@@ -122,6 +122,41 @@ int main(int argc, char **argv) {
     CHECK(ctx, bsx_fri_prove_openings(ctx, oracles, 1, &inst, &ch, &fp, proof));
     print_words("proof", -1, proof, words);
 
+    /* the prover steps either side of quotient evaluation: Zs + partial products of the permutation argument from
+     * the first min(n_cols, 5) columns taken as routed wires (sigma values = a second SplitMix stream), and the
+     * quotient hand-over coset_ifft -> chunks -> commitment on two value vectors of 8 n words */
+    {
+        const int n_routed = n_cols < 5 ? n_cols : 5, max_degree = 2, n_chunks = (n_routed + 1) / 2;
+        uint64_t *w = malloc(sizeof(uint64_t) * n * (size_t)n_routed), *sg = malloc(sizeof(uint64_t) * n * (size_t)n_routed);
+        for (size_t i = 0; i < n * (size_t)n_routed; i++) {
+            w[i] = splitmix(seed, i);
+            sg[i] = splitmix(seed + 100, i);
+        }
+        uint64_t k_is[5], betas[2] = {seed % P + 2, seed % P + 3}, gammas[2] = {seed % P + 4, seed % P + 5};
+        for (int j = 0; j < n_routed; j++) k_is[j] = splitmix(seed + 200, (uint64_t)j);
+        uint64_t *zs = malloc(sizeof(uint64_t) * n * 2 * (size_t)n_chunks);
+        CHECK(ctx, bsx_partial_products_and_zs(ctx, w, sg, BSX_HOST, log_n, n_routed, max_degree, k_is, betas, gammas, 2, zs,
+                                               BSX_HOST));
+        print_words("zs_row", 1 % (long long)n, NULL, 0);
+        for (int c = 0; c < 2 * n_chunks; c++) print_words("zs", c, zs + (size_t)c * n + (1 % n), 1);
+        uint64_t zsum = 0;
+        for (size_t i = 0; i < n * 2 * (size_t)n_chunks; i++) zsum = zsum * 0x100000001B3ULL ^ zs[i];
+        print_words("zs_fnv", -1, &zsum, 1);
+        free(w); free(sg); free(zs);
+
+        const int q_bits = 3, factor = 8, q_log_n = log_n > 10 ? 10 : log_n;  /* keeps 2^(log_n + 3) <= 2^24 words small */
+        const size_t big = (size_t)1 << (q_log_n + q_bits);
+        uint64_t *qv = malloc(sizeof(uint64_t) * 2 * big);
+        for (size_t i = 0; i < 2 * big; i++) qv[i] = splitmix(seed + 300, i);
+        bsx_batch *qb = NULL;
+        CHECK(ctx, bsx_batch_from_quotient_values(ctx, qv, BSX_HOST, q_log_n, q_bits, factor, 2, rate_bits, 0, 0, NULL, &qb, NULL));
+        uint64_t qcap[4];
+        CHECK(ctx, bsx_batch_cap(qb, qcap));
+        print_words("qcap", q_log_n, qcap, 4);
+        bsx_batch_free(qb);
+        free(qv);
+    }
+
     /* misuse is reported, not fatal: upstream panics with this message */
     bsx_batch *bad = NULL;
     uint64_t one = 1;

@@ -53,5 +53,22 @@ def test_c_program_matches_oracle(oracle, log_n, n_cols, rate_bits, cap_height, 
     points, polys = z.reshape(1, 2), [[(0, j) for j in range(n_cols)]]
     proof = oracle.fri_prove_openings([want], points, polys, ch, log_n, rate_bits, cap_height, 8, 4, arity)
     assert (_words(by["proof"][0]) == proof).all()
+    # Zs / partial products and the quotient hand-over, same SplitMix streams as the C program
+    n = 1 << log_n
+    n_routed = min(n_cols, 5)
+    zs = oracle.partial_products_and_zs(splitmix_field(seed, (n_routed, n)), splitmix_field(seed + 100, (n_routed, n)),
+                                        splitmix_field(seed + 200, (n_routed,)), [seed % P + 2, seed % P + 3],
+                                        [seed % P + 4, seed % P + 5], 2)
+    assert len(by["zs"]) == zs.shape[0]
+    for t in by["zs"]:
+        assert int(t[1], 16) == int(zs[int(t[0]), 1 % n])
+    fnv = 0
+    for v in zs.reshape(-1):
+        fnv = ((fnv * 0x100000001B3) ^ int(v)) & 0xFFFFFFFFFFFFFFFF
+    assert int(by["zs_fnv"][0][0], 16) == fnv
+    q_log_n = min(log_n, 10)
+    chunks = oracle.quotient_chunks(splitmix_field(seed + 300, (2, 1 << (q_log_n + 3))), q_log_n, 8)
+    qcap = oracle.batch_from_values(chunks, rate_bits, 0, from_coeffs=True, want=())["cap"]
+    assert int(by["qcap"][0][0]) == q_log_n and (_words(by["qcap"][0][1:]).reshape(-1, 4) == qcap).all()
     misuse = by["misuse"][0]
     assert int(misuse[0]) == -1 and "cap_height=5 should be at most log2(leaves.len())=1" in " ".join(misuse[1:])
