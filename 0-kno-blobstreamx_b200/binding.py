@@ -16,7 +16,7 @@ EXPORTED_SYMBOLS = [
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
-    "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
+    "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_debug_salt_stream", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
     "bsx_challenger_get", "bsx_fri_proof_words", "bsx_fri_prove_openings", "bsx_fri_proof", "bsx_fri_final_poly", "bsx_fri_final_poly_part", "bsx_shard_final_poly_part", "bsx_field_sum",
     "bsx_fri_proof_from_final_poly",
     "bsx_merkle_reduce", "bsx_shard_column_range", "bsx_shard_create", "bsx_shard_free", "bsx_shard_shape",
@@ -93,6 +93,7 @@ def lib():
         "bsx_merkle_digests": (i32, [vp, vp]),
         "bsx_merkle_shape": (i32, [vp] + [C.POINTER(i32)] * 3),
         "bsx_poseidon_permute": (i32, [vp, vp, i32, sz]),
+        "bsx_debug_salt_stream": (i32, [vp, vp, i32, vp, sz]),
         "bsx_ntt": (i32, [vp, vp, i32, i32, i32, i32, u64]),
         "bsx_challenger_init": (None, [vp]),
         "bsx_challenger_observe": (i32, [vp, vp, vp, sz]),
@@ -224,6 +225,13 @@ class Context:
         flat = s.reshape(-1, 12)
         self.check(lib().bsx_poseidon_permute(self._h, _ptr(flat), BSX_HOST, flat.shape[0]))
         return s
+
+    def salt_stream(self, key, n, raw=False):
+        """n words of the ChaCha20 stream blinding salts come from, under `key` (8 x u32); raw: no rejection mod p."""
+        k = np.ascontiguousarray(key, dtype=np.uint32).reshape(8)
+        out = np.zeros(int(n), dtype=np.uint64)
+        self.check(lib().bsx_debug_salt_stream(self._h, C.c_void_p(k.ctypes.data), 1 if raw else 0, _ptr(out), out.size))
+        return out
 
     def ntt(self, cols, kind="fft", shift=7):
         """cols: (n_cols, n) column vectors; natural order in and out."""

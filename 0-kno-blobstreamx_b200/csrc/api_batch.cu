@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <thread>
+#include <sys/random.h>
 
 static inline size_t n_digest_words(int log_leaves, int cap_height) {
     return 4 * 2 * (((size_t)1 << log_leaves) - ((size_t)1 << cap_height));
@@ -473,7 +474,20 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, const u64 *const *col_ptr
                 launch_bitrev_copy(src, nb, dst, nb, log_nb, n_salt, ctx->stream);
                 bsx_free(ctx, tmp);
             } else {
-                launch_fill_random(dst, nb * n_salt, 0x5A17C0DEULL ^ (u64)(uintptr_t)bt, ctx->stream);
+                // F::rand_vec upstream (a CSPRNG): a fresh 256-bit ChaCha20 key from the kernel's entropy pool per batch
+                u32 key[8];
+                size_t got = 0;
+                while (got < sizeof(key)) {
+                    ssize_t r = getrandom((char *)key + got, sizeof(key) - got, 0);
+                    if (r <= 0) break;
+                    got += (size_t)r;
+                }
+                if (got != sizeof(key)) {
+                    rc = bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "getrandom failed: no entropy for the blinding salts");
+                    break;
+                }
+                launch_fill_random(dst, nb * n_salt, key, 0, ctx->stream);
+                memset(key, 0, sizeof(key));
             }
         }
         const HostColumns host = {col_ptrs ? nullptr : input, col_ptrs, n};
@@ -953,6 +967,21 @@ extern "C" int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t 
     return BSX_OK;
 }
 
+// test hook: n words of the ChaCha20 key stream the blinding salts are drawn from (raw: no rejection mod p)
+extern "C" int32_t bsx_debug_salt_stream(bsx_ctx *ctx, const uint32_t key[8], int32_t raw, uint64_t *out_host, size_t n) {
+    if (!ctx || !key || (!out_host && n)) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
+    if (n == 0) return BSX_OK;
+    CU(ctx, cudaSetDevice(ctx->device));
+    u64 *d;
+    TRY(bsx_alloc(ctx, &d, n));
+    launch_fill_random(d, n, key, raw, ctx->stream);
+    TRY(bsx_copy_out(ctx, (u64 *)out_host, d, n, BSX_HOST));
+    bsx_free(ctx, d);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
 // values (natural order) -> coefficients (natural order) of the polynomial that takes them on shift * H:
 // PolynomialValues::coset_ifft = ifft, then c_i *= shift^-i.  In place on the device buffer `buf`; `tmp` is scratch.
 static int coset_or_plain_ntt(bsx_ctx *ctx, u64 *buf, u64 *tmp, int log_n, int n_cols, int kind, u64 shift) {
@@ -1042,13 +1071,24 @@ extern "C" int32_t bsx_batch_from_quotient_values(bsx_ctx *ctx, const uint64_t *
         if (host_flag)
             return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "quotient polynomial has degree >= %d * 2^%d (trim_to_len fails upstream)",
                             quotient_degree_factor, degree_log);
-        for (int c = 1; c < n_polys; c++)
-            CU(ctx, cudaMemcpyAsync(tmp + (size_t)c * keep, tmp + (size_t)c * big, keep * sizeof(u64),
-                                    cudaMemcpyDeviceToDevice, ctx->stream));
+        // compaction into the other buffer (`buf` is free after the transform): in place the ranges of
+        // polynomial c overlap whenever keep > big / 2, which cudaMemcpy does not allow
+        CU(ctx, cudaMemcpy2DAsync(buf, keep * sizeof(u64), tmp, big * sizeof(u64), keep * sizeof(u64), (size_t)n_polys,
+                                  cudaMemcpyDeviceToDevice, ctx->stream));
+        std::swap(buf, tmp);
+    }
+    // `salt` lives on the `mem` side like `values`; the commit below takes device pointers
+    u64 *salt_dev = nullptr;
+    if (blinding && salt && mem != BSX_DEVICE) {
+        const size_t sw = ((size_t)BSX_SALT_SIZE << (degree_log + rate_bits));
+        TRY(bsx_alloc(ctx, &salt_dev, sw));
+        TRY(bsx_copy_in(ctx, salt_dev, (const u64 *)salt, sw, mem));
+        salt = (const uint64_t *)salt_dev;
     }
     // polynomial c, chunk j = words [(c * factor + j) * N, +N): exactly a column-major (n_polys * factor) x N matrix
     int32_t rc = bsx_batch_from_coeffs(ctx, (const uint64_t *)tmp, BSX_DEVICE, degree_log, n_polys * quotient_degree_factor, rate_bits,
                                        cap_height, blinding, salt, out, timing);
+    bsx_free(ctx, salt_dev);
     bsx_free(ctx, buf);
     bsx_free(ctx, tmp);
     bsx_free(ctx, (u64 *)flag);

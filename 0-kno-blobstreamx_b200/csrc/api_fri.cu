@@ -124,6 +124,10 @@ static int final_poly_device(bsx_ctx *ctx, bsx_batch *const *oracles, int n_orac
     int kmax = 0, total = 0;
     for (int b = 0; b < inst->n_batches; b++) {
         if (inst->n_polys[b] < 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad instance");
+        // combine_kernel's column accumulators are exact for sums of up to 2^12 products (gl_acc_reduce)
+        if (inst->n_polys[b] > 4096)
+            return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "opening batch %d holds %d polynomials; at most 4096 are supported", b,
+                            inst->n_polys[b]);
         if (inst->n_polys[b] > kmax) kmax = inst->n_polys[b];
         total += inst->n_polys[b];
     }

@@ -251,7 +251,7 @@ __device__ __forceinline__ u64 gl_add_lazy_canon(u64 a, u64 b) {
     return ((u64)r1 << 32) | r0;
 }
 
-// Five-limb accumulator for sums of up to 16 products: acc += a * b.
+// Five-limb accumulator for sums of products (up to 2^12, see gl_acc_reduce): acc += a * b.
 struct gl_acc160 {
     u32 x0, x1, x2, x3, x4;
 };
@@ -279,7 +279,9 @@ __device__ __forceinline__ void gl_acc_mac(gl_acc160 &A, u64 a, u64 b) {
         : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
 }
 // x0 + x1 2^32 + x2 2^64 + x3 2^96 + x4 2^128 == (x1:x0) - (x4:x3) + x2 * EPS   (2^128 == -2^32).
-// x4 < 16 (at most 16 products), so (x4:x3) < 2^36 and the single signed correction is still exact.
+// x4 counts the products (each < 2^128): callers keep a sum below 2^12 products (x4 < 2^12, checked where the
+// term count comes from outside: api_fri.cu final_poly_device), so (x4:x3) < 2^44 and the single signed
+// correction is still exact: r2 in {-1, 0, 1} only needs the subtrahend's high word below 2^32 - 2.
 __device__ __forceinline__ u64 gl_acc_reduce(const gl_acc160 &A) {
     u32 r0, r1;
     asm("{\n\t.reg .u32 x0,x1,x2,x3,r2,n,eh;\n\t"
@@ -318,7 +320,7 @@ __device__ __forceinline__ void gl_acc3_mac(gl_acc3 &A, u64 a, u64 b) {
         : "+r"(A.l0), "+r"(A.h0), "+r"(A.c0), "+r"(A.l1), "+r"(A.h1), "+r"(A.c1), "+r"(A.l2), "+r"(A.h2), "+r"(A.c2)
         : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
 }
-// (c0:h0:l0) + (c1:h1:l1) 2^32 + (c2:h2:l2) 2^64 -> five limbs -> lazy u64 (at most 16 terms: limb 4 < 16)
+// (c0:h0:l0) + (c1:h1:l1) 2^32 + (c2:h2:l2) 2^64 -> five limbs -> lazy u64 (at most 2^12 terms, see gl_acc_reduce)
 __device__ __forceinline__ u64 gl_acc3_reduce(const gl_acc3 &A) {
     gl_acc160 X;
     asm("add.cc.u32 %0, %5, %7;\n\t"          // x1 = h0 + l1

@@ -23,15 +23,21 @@ __global__ void __launch_bounds__(256, LEAF_BLOCKS)
 #pragma unroll
     for (int i = 0; i < 12; i++) s[i] = 0;
     if (n_cols <= 4) {  // hash_or_noop: zero-extend, no permutation
-        for (int c = 0; c < n_cols; c++) s[c] = p[(size_t)c * col_stride];
+#pragma unroll
+        for (int c = 0; c < 4; c++)  // static indices: a run-time index would put the state in local memory
+            if (c < n_cols) s[c] = p[(size_t)c * col_stride];
     } else {
-        // One permutation call site (code size).  A short last chunk overwrites only its own lanes
-        // (no padding, hashing.rs).
+        // One permutation call site (code size).  A short last chunk overwrites only its own lanes (no padding,
+        // hashing.rs): its missing columns re-read the last one and are dropped by a select, so the loads stay
+        // unconditional and the state never leaves the registers (predicated loads parked it on the stack).
+        const int last = n_cols - 1;
 #pragma unroll 1
         for (int c = 0; c < n_cols; c += 8) {
+            u64 v[8];
 #pragma unroll
-            for (int i = 0; i < 8; i++)
-                if (c + i < n_cols) s[i] = __ldg(p + (size_t)(c + i) * col_stride);
+            for (int i = 0; i < 8; i++) v[i] = __ldg(p + (size_t)min(c + i, last) * col_stride);
+#pragma unroll
+            for (int i = 0; i < 8; i++) s[i] = (c + i <= last) ? v[i] : s[i];
             poseidon_permute_lazy(s);
         }
 #pragma unroll

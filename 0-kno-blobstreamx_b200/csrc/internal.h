@@ -83,7 +83,7 @@ void launch_ntt_post_table(u64 *out, const u64 *pre_lo, PowTable tw, u64 scale, 
                            cudaStream_t st);
 int ntt_max_single_pass_log();
 void ntt_init_device();
-void launch_fill_random(u64 *out, size_t n, u64 seed, cudaStream_t st);
+void launch_fill_random(u64 *out, size_t n, const u32 key[8], int raw, cudaStream_t st);
 
 // ---------------------------------------------------------------- FRI / challenger (fri_kernels.cu)
 void launch_chal_observe(void *chal_dev, const u64 *data, size_t n, int mode, size_t plane_stride, cudaStream_t st);

@@ -523,17 +523,61 @@ void launch_bitrev_copy(const u64 *src, size_t src_stride, u64 *dst, size_t dst_
     BSX_COUNT_LAUNCH(); bitrev_copy_kernel<<<grid, 256, 0, st>>>(src, src_stride, dst, dst_stride, log_n);
 }
 
-// counter-based SplitMix64 stream reduced mod p: salt columns when the caller supplies none
-__global__ void fill_random_kernel(u64 *out, size_t n, u64 seed) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    u64 z = seed + (i + 1) * 0x9E3779B97F4A7C15ULL;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
-    z ^= z >> 31;
-    out[i] = z % GL_P;
+// Salt columns when the caller supplies none (fri/oracle.rs lde_values: `F::rand_vec`, a CSPRNG upstream).
+// ChaCha20 (RFC 8439 block function) in counter mode under a 256-bit key the host draws from the kernel's
+// entropy pool per batch (api_batch.cu).  Block t yields the eight 64-bit candidates of outputs 8t .. 8t+7;
+// a candidate >= p is rejected and replaced from that output's own spare stream (block counters with the
+// top bit set), so the words are uniform in [0, p) and no opened salt word reveals anything about another.
+__device__ __forceinline__ void chacha20_block(const u32 key[8], u64 counter, u32 out[16]) {
+    u32 x[16] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u, key[0], key[1], key[2], key[3],
+                 key[4], key[5], key[6], key[7], (u32)counter, (u32)(counter >> 32), 0u, 0u};
+    u32 s[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) s[i] = x[i];
+#define CHACHA_QR(a, b, c, d)                               \
+    x[a] += x[b]; x[d] = __funnelshift_l(x[d] ^ x[a], x[d] ^ x[a], 16); \
+    x[c] += x[d]; x[b] = __funnelshift_l(x[b] ^ x[c], x[b] ^ x[c], 12); \
+    x[a] += x[b]; x[d] = __funnelshift_l(x[d] ^ x[a], x[d] ^ x[a], 8);  \
+    x[c] += x[d]; x[b] = __funnelshift_l(x[b] ^ x[c], x[b] ^ x[c], 7);
+#pragma unroll 1
+    for (int r = 0; r < 10; r++) {
+        CHACHA_QR(0, 4, 8, 12) CHACHA_QR(1, 5, 9, 13) CHACHA_QR(2, 6, 10, 14) CHACHA_QR(3, 7, 11, 15)
+        CHACHA_QR(0, 5, 10, 15) CHACHA_QR(1, 6, 11, 12) CHACHA_QR(2, 7, 8, 13) CHACHA_QR(3, 4, 9, 14)
+    }
+#undef CHACHA_QR
+#pragma unroll
+    for (int i = 0; i < 16; i++) out[i] = x[i] + s[i];
 }
-void launch_fill_random(u64 *out, size_t n, u64 seed, cudaStream_t st) {
+struct ChaChaKey {
+    u32 w[8];
+};
+__global__ void fill_random_kernel(u64 *out, size_t n, ChaChaKey key, int raw) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t * 8 >= n) return;
+    u32 blk[16];
+    chacha20_block(key.w, (u64)t, blk);
+#pragma unroll 1
+    for (int j = 0; j < 8; j++) {
+        const size_t i = t * 8 + j;
+        if (i >= n) break;
+        u64 v = ((u64)blk[2 * j + 1] << 32) | blk[2 * j];
+        if (!raw) {
+            u64 spare = 0;
+            while (v >= GL_P) {  // probability 2^-32 per draw
+                u32 ex[16];
+                chacha20_block(key.w, (1ULL << 63) | ((u64)i << 8) | (spare >> 3), ex);
+                v = ((u64)ex[2 * (spare & 7) + 1] << 32) | ex[2 * (spare & 7)];
+                spare++;
+            }
+        }
+        out[i] = v;
+    }
+}
+// key: 8 words.  raw != 0: the key stream itself (test hook: RFC 8439 vectors), no rejection.
+void launch_fill_random(u64 *out, size_t n, const u32 key[8], int raw, cudaStream_t st) {
     if (n == 0) return;
-    BSX_COUNT_LAUNCH(); fill_random_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(out, n, seed);
+    ChaChaKey k;
+    for (int i = 0; i < 8; i++) k.w[i] = key[i];
+    const size_t blocks = (n + 7) / 8;
+    BSX_COUNT_LAUNCH(); fill_random_kernel<<<(unsigned)((blocks + 127) / 128), 128, 0, st>>>(out, n, k, raw);
 }

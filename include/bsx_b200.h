@@ -273,7 +273,8 @@ int32_t bsx_batch_eval_ext(bsx_batch *batch, int32_t col_begin, int32_t n_cols, 
  * values = n_polys x 2^(degree_log + quotient_degree_bits) words, column-major, natural order: the quotient's values on
  * the coset 7 * <omega_{N 2^q}>.  quotient_degree_factor <= 2^quotient_degree_bits chunks of 2^degree_log coefficients are
  * kept per polynomial; non-zero coefficients beyond them fail with BSX_ERR_INVALID_ARG (upstream `trim_to_len` returns
- * Err and prove() panics "Quotient has failed ...").  The batch has n_polys * quotient_degree_factor polynomials. */
+ * Err and prove() panics "Quotient has failed ...").  The batch has n_polys * quotient_degree_factor polynomials.
+ * `salt` (optional, with `blinding`) lives on the same side as `values` (`mem`), laid out as for bsx_batch_from_coeffs. */
 int32_t bsx_batch_from_quotient_values(bsx_ctx *ctx, const uint64_t *values, int32_t mem, int32_t degree_log,
                                        int32_t quotient_degree_bits, int32_t quotient_degree_factor, int32_t n_polys,
                                        int32_t rate_bits, int32_t cap_height, int32_t blinding, const uint64_t *salt,
@@ -299,6 +300,11 @@ int32_t bsx_partial_products_and_zs(bsx_ctx *ctx, const uint64_t *wires, const u
 /* ---- test hooks -----------------------------------------------------------------------------
  * Poseidon::poseidon on n states (n x 12 words, in place). */
 int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n);
+/* n words of the ChaCha20 (RFC 8439 block function, 64-bit block counter) key stream that the blinding salts are
+ * drawn from under `key`; raw != 0 returns the stream itself (eight little-endian u64 per block, block t at words
+ * 8t .. 8t+7), raw == 0 the salt words (candidates >= p rejected and redrawn).  In a commit the key is 256 bits from
+ * getrandom(2) per batch and never leaves the call. */
+int32_t bsx_debug_salt_stream(bsx_ctx *ctx, const uint32_t key[8], int32_t raw, uint64_t *out_host, size_t n);
 /* Batched transforms on n_cols columns of 2^log_n words, column-major, in place, natural order in and
  * out.  kind: 0 = fft (PolynomialCoeffs::fft), 1 = ifft (PolynomialValues::ifft),
  * 2 = coset_fft(shift) (PolynomialCoeffs::coset_fft), 3 = coset_ifft(shift) (PolynomialValues::coset_ifft). */

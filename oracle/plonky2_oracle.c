@@ -328,15 +328,23 @@ int orc_batch_from_coeffs(const uint64_t *coeffs, int log_n, int n_cols, int rat
     uint64_t *rows = leaves ? leaves : (uint64_t *)malloc(sizeof(uint64_t) * nb * (width ? width : 1));
     if (!rows) return -2;
     int bad = 0;
+    /* columns in groups of ORC_COL_GROUP per thread: the transpose then writes ORC_COL_GROUP adjacent words of a
+     * row at a time (one cache line) instead of one word per 8 * width bytes */
+#define ORC_COL_GROUP 8
+    int n_groups = (n_cols + ORC_COL_GROUP - 1) / ORC_COL_GROUP;
 #pragma omp parallel
     {
-        uint64_t *col = (uint64_t *)malloc(sizeof(uint64_t) * nb);
+        uint64_t *col = (uint64_t *)malloc(sizeof(uint64_t) * nb * ORC_COL_GROUP);
 #pragma omp for schedule(dynamic, 1)
-        for (int c = 0; c < n_cols; c++) {
+        for (int g = 0; g < n_groups; g++) {
             if (!col) { bad = 1; continue; }
-            orc_lde(coeffs + (size_t)c * n, log_n, rate_bits, 7, col);
+            int c0 = g * ORC_COL_GROUP, k = n_cols - c0 < ORC_COL_GROUP ? n_cols - c0 : ORC_COL_GROUP;
+            for (int j = 0; j < k; j++) orc_lde(coeffs + (size_t)(c0 + j) * n, log_n, rate_bits, 7, col + (size_t)j * nb);
             /* transpose + bit-reverse rows: leaf l = evaluation index bitrev(l) */
-            for (size_t l = 0; l < nb; l++) rows[l * width + c] = col[orc_reverse_bits(l, log_nb)];
+            for (size_t i = 0; i < nb; i++) {
+                uint64_t *row = rows + (size_t)orc_reverse_bits(i, log_nb) * width + c0;
+                for (int j = 0; j < k; j++) row[j] = col[(size_t)j * nb + i];
+            }
         }
         free(col);
     }

@@ -13,6 +13,7 @@ P = 0xFFFFFFFF00000001
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "slow: full-size oracle comparisons (tens of seconds of host time each)")
 
 
 def splitmix_field(seed, shape):

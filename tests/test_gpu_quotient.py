@@ -82,3 +82,36 @@ def test_trimmed_quotient_and_upstream_panic(pkg, ctx, oracle):
     with pytest.raises(pkg.BsxError):
         pkg.PolynomialBatch.from_quotient_values(ctx, bad, degree_log, factor, 3, False, 4)
     assert ctx.mem_used() == used  # failing calls release their device temporaries
+
+
+@pytest.mark.parametrize("factor", [5, 6, 7])
+def test_trim_compaction_does_not_overlap(pkg, ctx, oracle, factor):
+    """trim_to_len with keep > big / 2 at a size where the packed and the unpacked ranges of polynomial 1, 2 overlap
+    and a copy runs on many CTAs (the in-place cudaMemcpy of round 1 was undefined there)."""
+    degree_log, q_bits, n_polys = 16, 3, 3
+    n = 1 << degree_log
+    coeffs = np.zeros((n_polys, n << q_bits), dtype=np.uint64)
+    coeffs[:, :factor * n] = splitmix_field(40 + factor, (n_polys, factor * n))
+    vals = ctx.ntt(coeffs, "coset_fft", 7)
+    b = pkg.PolynomialBatch.from_quotient_values(ctx, vals, degree_log, factor, 1, False, 4)
+    want = coeffs[:, :factor * n].reshape(n_polys * factor, n)
+    assert (b.polynomials == want).all()
+    same = pkg.PolynomialBatch.from_coeffs(ctx, want, 1, False, 4)
+    assert (b.cap == same.cap).all()
+    b.close()
+    same.close()
+
+
+def test_from_quotient_values_with_caller_salt(pkg, ctx, oracle):
+    """`salt` on the host side (what the Python mirror always passes) must reach the commit as device memory."""
+    degree_log, q_bits, factor, rate_bits, cap_height = 8, 3, 8, 2, 3
+    vals = splitmix_field(611, (2, 1 << (degree_log + q_bits)))
+    salt = splitmix_field(612, (4, 1 << (degree_log + rate_bits)))
+    b = pkg.PolynomialBatch.from_quotient_values(ctx, vals, degree_log, factor, rate_bits, True, cap_height, salt=salt)
+    chunks = oracle.quotient_chunks(vals, degree_log, factor)
+    want = oracle.batch_from_values(chunks, rate_bits, cap_height, salt=salt, from_coeffs=True)
+    assert (b.cap == want["cap"]).all()
+    same = pkg.PolynomialBatch.from_coeffs(ctx, chunks, rate_bits, True, cap_height, salt=salt)
+    assert (same.cap == b.cap).all()
+    b.close()
+    same.close()
