@@ -38,6 +38,14 @@ from .fri import (  # noqa: F401
     fri_reduction_arity_bits,
     prove_openings,
 )
+from .proof import (  # noqa: F401
+    FriLayout,
+    OpeningSet,
+    Proof,
+    ProofWithPublicInputs,
+    fri_proof_bytes,
+    fri_proof_layout,
+)
 from .parallel import (  # noqa: F401
     ShardPlan,
     ShardedPolynomialBatch,

@@ -259,6 +259,53 @@ int32_t bsx_fri_proof_from_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, i
 int32_t bsx_fri_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
                            const bsx_fri_instance *instance, const uint64_t alpha[2], uint64_t *out_host);
 
+/* ---- typed view of the flat FriProof stream, and proof bytes (plonk/proof.rs, util/serialization/mod.rs) -------
+ * bsx_fri_proof_layout: word offsets of every plonky2 `FriProof` field inside the stream of bsx_fri_proof_words, so a
+ * caller (the Rust shim building `FriProof { commit_phase_merkle_caps, query_round_proofs, final_poly, pow_witness }`)
+ * can slice it without knowing the packing.  Offsets inside a query round are relative to
+ * query_offset + q * query_stride.  leaf_widths[o] = polynomials + salt columns of oracle o. */
+#define BSX_MAX_ORACLES 16
+typedef struct bsx_fri_layout {
+    uint64_t total_words;
+    uint64_t caps_offset, cap_words;          /* commit_phase_merkle_caps[r] at caps_offset + r * cap_words */
+    uint64_t query_offset, query_stride;      /* query_round_proofs[q] */
+    uint64_t initial_leaf_offset[BSX_MAX_ORACLES], initial_leaf_words[BSX_MAX_ORACLES]; /* initial_trees_proof.evals_proofs[o].0 */
+    uint64_t initial_proof_offset[BSX_MAX_ORACLES];                                      /* .1.siblings, initial_siblings x 4 */
+    uint64_t step_evals_offset[16], step_evals_words[16];                               /* steps[r].evals, [c0, c1] pairs */
+    uint64_t step_proof_offset[16];                                                      /* steps[r].merkle_proof.siblings */
+    uint64_t final_poly_offset, final_poly_words; /* final_poly.coeffs, [c0, c1] pairs */
+    uint64_t pow_witness_offset;
+    int32_t n_oracles, n_rounds, n_query_rounds, initial_siblings;
+    int32_t step_siblings[16];
+} bsx_fri_layout;
+int32_t bsx_fri_proof_layout(const bsx_fri_params *params, const int32_t *leaf_widths, int32_t n_oracles,
+                             bsx_fri_layout *out);
+/* `Write::write_fri_proof` of the stream.  out == NULL only counts (out_len); BSX_ERR_INVALID_ARG when out_cap is short. */
+int32_t bsx_fri_proof_bytes(const uint64_t *proof_words, const bsx_fri_params *params, const int32_t *leaf_widths,
+                            int32_t n_oracles, uint8_t *out, size_t out_cap, size_t *out_len);
+/* `ProofWithPublicInputs::to_bytes()`: Proof { wires_cap, plonk_zs_partial_products_cap, quotient_polys_cap, openings,
+ * opening_proof } then the public inputs.  openings[k]: n_openings[k] extension elements [c0, c1] in `OpeningSet` field
+ * order (BSX_OPEN_*).  All pointers are host memory. */
+#define BSX_OPENING_SET_FIELDS 7
+#define BSX_OPEN_CONSTANTS 0
+#define BSX_OPEN_PLONK_SIGMAS 1
+#define BSX_OPEN_WIRES 2
+#define BSX_OPEN_PLONK_ZS 3
+#define BSX_OPEN_PLONK_ZS_NEXT 4
+#define BSX_OPEN_PARTIAL_PRODUCTS 5
+#define BSX_OPEN_QUOTIENT_POLYS 6
+typedef struct bsx_proof_parts {
+    const uint64_t *wires_cap, *plonk_zs_partial_products_cap, *quotient_polys_cap; /* 2^cap_height x 4 each */
+    const uint64_t *openings[BSX_OPENING_SET_FIELDS];
+    int32_t n_openings[BSX_OPENING_SET_FIELDS];
+    const uint64_t *opening_proof_words; /* stream of bsx_fri_prove_openings */
+    const uint64_t *public_inputs;
+    int32_t n_public_inputs;
+} bsx_proof_parts;
+int32_t bsx_proof_with_public_inputs_bytes(const bsx_proof_parts *parts, const bsx_fri_params *params,
+                                           const int32_t *leaf_widths, int32_t n_oracles, uint8_t *out, size_t out_cap,
+                                           size_t *out_len);
+
 /* Replaces the `eval_commitment` closure of plonk/proof.rs OpeningSet::new: every polynomial
  * col_begin .. col_begin + n_cols - 1 of the batch (salt columns are not polynomials) evaluated at n_points
  * extension-field points, `PolynomialCoeffs::to_extension().eval(z)`.  points_host = n_points x [c0, c1];

@@ -16,7 +16,7 @@ u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
 
 
 def build(force=False):
-    srcs = [os.path.join(_DIR, f) for f in ("plonky2_oracle.c", "plonky2_fri_oracle.c", "plonky2_oracle.h",
+    srcs = [os.path.join(_DIR, f) for f in ("plonky2_oracle.c", "plonky2_fri_oracle.c", "plonky2_plonk_oracle.c", "plonky2_oracle.h",
                                               "poseidon_rc.h", "Makefile")]
     if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
         subprocess.check_call(["make", "-C", _DIR, "-s"])
@@ -358,3 +358,69 @@ def fri_verify(batches, points, polys, openings, challenger, degree_bits, rate_b
     op, pr = _a(openings), _a(proof)
     return bool(lib().orc_fri_verify(v, len(batches), C.byref(inst), _ptr(op), C.byref(challenger), C.byref(fp),
                                      _ptr(pr)))
+
+
+# ---- quotient evaluation and proof bytes (plonky2_plonk_oracle.c) ----
+GATE_NOOP, GATE_CONSTANT, GATE_PUBLIC_INPUT, GATE_ARITHMETIC = 0, 1, 2, 3
+
+
+class _Gate(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("param", C.c_int32), ("row", C.c_int32), ("selector_index", C.c_int32),
+                ("group_start", C.c_int32), ("group_end", C.c_int32)]
+
+
+class _Circuit(C.Structure):
+    _fields_ = [("degree_bits", C.c_int32), ("rate_bits", C.c_int32), ("quotient_degree_factor", C.c_int32),
+                ("num_challenges", C.c_int32), ("num_wires", C.c_int32), ("num_routed_wires", C.c_int32),
+                ("num_constants", C.c_int32), ("num_selectors", C.c_int32), ("num_partial_products", C.c_int32),
+                ("num_gate_constraints", C.c_int32), ("n_gates", C.c_int32), ("gates", C.c_void_p), ("k_is", C.c_void_p)]
+
+
+def _circuit(circuit):
+    """circuit: dict with the `orc_circuit` fields; gates = list of (kind, param, row, selector_index, group_start,
+    group_end); k_is = per routed wire."""
+    gates = (_Gate * max(len(circuit["gates"]), 1))(*[_Gate(*g) for g in circuit["gates"]])
+    k_is = _a(circuit["k_is"])
+    c = _Circuit(circuit["degree_bits"], circuit["rate_bits"], circuit["quotient_degree_factor"],
+                 circuit["num_challenges"], circuit["num_wires"], circuit["num_routed_wires"], circuit["num_constants"],
+                 circuit["num_selectors"], circuit["num_partial_products"], circuit["num_gate_constraints"],
+                 len(circuit["gates"]), C.cast(gates, C.c_void_p), k_is.ctypes.data)
+    return c, [gates, k_is]
+
+
+def quotient_values(circuit, constants_sigmas, wires, zs_partial_products, public_inputs_hash, betas, gammas, alphas,
+                    cap_height=0):
+    """compute_quotient_polys before its `coset_ifft`: (num_challenges, 2^(degree_bits + q)) values on the coset.
+    The three batches are dicts from batch_from_values (with leaves)."""
+    c, keep = _circuit(circuit)
+    v, k1 = _views([constants_sigmas, wires, zs_partial_products], circuit["rate_bits"], cap_height)
+    qdb = int(np.ceil(np.log2(circuit["quotient_degree_factor"])))
+    out = np.zeros((circuit["num_challenges"], 1 << (circuit["degree_bits"] + qdb)), dtype=np.uint64)
+    pih, b, g, al = _a(public_inputs_hash), _a(betas), _a(gammas), _a(alphas)
+    vp = C.cast(v, C.c_void_p).value
+    sz = C.sizeof(_BatchView)
+    rc = lib().orc_quotient_values(C.byref(c), C.c_void_p(vp), C.c_void_p(vp + sz), C.c_void_p(vp + 2 * sz), _ptr(pih),
+                                   _ptr(b), _ptr(g), _ptr(al), _ptr(out))
+    if rc != 0:
+        raise ValueError("orc_quotient_values failed rc=%d" % rc)
+    return out
+
+
+def write_proof_with_public_inputs(wires_cap, zs_cap, quotient_cap, openings, fri_words, degree_bits, rate_bits,
+                                   cap_height, pow_bits, num_queries, arity_bits, widths, public_inputs):
+    """`ProofWithPublicInputs::to_bytes`; openings = the seven OpeningSet vectors, each (n, 2)."""
+    fp = _params(degree_bits, rate_bits, cap_height, pow_bits, num_queries, arity_bits)
+    ops = [_a(o).reshape(-1, 2) for o in openings]
+    op_ptrs = (C.c_void_p * 7)(*[o.ctypes.data for o in ops])
+    n_ops = (C.c_int * 7)(*[o.shape[0] for o in ops])
+    w = np.ascontiguousarray(widths, dtype=np.int32)
+    caps = [_a(wires_cap), _a(zs_cap), _a(quotient_cap)]
+    words, pis = _a(fri_words), _a(public_inputs)
+    f = lib().orc_write_proof_with_public_inputs
+    f.restype = C.c_size_t
+    args = [_ptr(caps[0]), _ptr(caps[1]), _ptr(caps[2]), op_ptrs, n_ops, _ptr(words), C.byref(fp),
+            C.c_void_p(w.ctypes.data), C.c_int(len(widths)), _ptr(pis), C.c_int(pis.size)]
+    n = f(*args, None)
+    buf = np.zeros(n, dtype=np.uint8)
+    f(*args, C.c_void_p(buf.ctypes.data))
+    return buf.tobytes()

@@ -138,10 +138,43 @@ void orc_eval_poly_ext(const orc_batch_view *o, int poly_index, const uint64_t z
 int orc_num_threads(void);
 void orc_set_num_threads(int n);
 
-#ifdef __cplusplus
-}
-#endif
 /* plonk/prover.rs wires_permutation_partial_products_and_zs for one challenge; -1 on a zero denominator */
 int orc_partial_products_and_z(const uint64_t *wires, const uint64_t *sigmas, int log_n, int n_routed, int max_degree,
                                const uint64_t *k_is, uint64_t beta, uint64_t gamma, uint64_t *out_z, uint64_t *out_pp);
+
+/* ---- quotient evaluation (plonky2_plonk_oracle.c): plonk/prover.rs compute_quotient_polys,
+ * plonk/vanishing_poly.rs eval_vanishing_poly_base_batch, the gates of gates/ ---- */
+#define ORC_GATE_NOOP 0         /* gates/noop.rs NoopGate */
+#define ORC_GATE_CONSTANT 1     /* gates/constant.rs ConstantGate { num_consts = param } */
+#define ORC_GATE_PUBLIC_INPUT 2 /* gates/public_input.rs PublicInputGate */
+#define ORC_GATE_ARITHMETIC 3   /* gates/arithmetic_base.rs ArithmeticGate { num_ops = param } */
+typedef struct orc_gate { /* one entry of common_data.gates with its share of common_data.selectors_info */
+    int32_t kind, param;
+    int32_t row;                    /* index in common_data.gates: the selector value that switches it on */
+    int32_t selector_index;         /* selectors_info.selector_indices[row] */
+    int32_t group_start, group_end; /* selectors_info.groups[selector_index] */
+} orc_gate;
+typedef struct orc_circuit { /* the fields of CommonCircuitData / CircuitConfig compute_quotient_polys reads */
+    int32_t degree_bits, rate_bits, quotient_degree_factor, num_challenges;
+    int32_t num_wires, num_routed_wires;
+    int32_t num_constants; /* common_data.num_constants: selectors first, then the gates' constants */
+    int32_t num_selectors; /* selectors_info.num_selectors() */
+    int32_t num_partial_products, num_gate_constraints, n_gates;
+    const orc_gate *gates;
+    const uint64_t *k_is;
+} orc_circuit;
+int orc_gate_num_constraints(const orc_gate *g);
+/* the quotient values on the coset before `coset_ifft`: out[a][i], a < num_challenges, i < 2^(degree_bits + q) */
+int orc_quotient_values(const orc_circuit *c, const orc_batch_view *constants_sigmas, const orc_batch_view *wires_b,
+                        const orc_batch_view *zs_b, const uint64_t public_inputs_hash[4], const uint64_t *betas,
+                        const uint64_t *gammas, const uint64_t *alphas, uint64_t *out);
+/* util/serialization write_proof_with_public_inputs over the flat FriProof stream; returns the byte count */
+size_t orc_write_proof_with_public_inputs(const uint64_t *wires_cap, const uint64_t *zs_cap, const uint64_t *quotient_cap,
+                                          const uint64_t *const openings[7], const int n_openings[7],
+                                          const uint64_t *fri_words, const orc_fri_params *fp, const int *widths,
+                                          int n_oracles, const uint64_t *public_inputs, int n_public_inputs, uint8_t *out);
+
+#ifdef __cplusplus
+}
+#endif
 #endif

@@ -1,0 +1,233 @@
+/* plonky2_plonk_oracle.c -- CPU restatement of the prover steps either side of the commitments:
+ *   plonk/prover.rs `compute_quotient_polys` with plonk/vanishing_poly.rs `eval_vanishing_poly_base_batch`
+ *   (the vanishing polynomial on the quotient coset) for circuits built from NoopGate, ConstantGate,
+ *   PublicInputGate and ArithmeticGate (gates/{noop,constant,public_input,arithmetic_base}.rs), and
+ *   util/serialization/mod.rs `write_proof_with_public_inputs` (`ProofWithPublicInputs::to_bytes`).
+ * TEST INFRASTRUCTURE ONLY; "parity unpinned" against the real prover -- see plonky2_oracle.h. */
+#include "plonky2_oracle.h"
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define P ORC_P
+
+/* plonk/plonk_common.rs ZeroPolyOnCoset::new(n_log, rate_bits): evals[i] = g^n * v^i - 1, v a primitive
+ * rate-th root of unity; eval(i) = evals[i % rate] */
+typedef struct {
+    uint64_t n;
+    size_t rate;
+    uint64_t *evals, *inverses;
+} zero_poly_on_coset;
+static void zpoc_new(zero_poly_on_coset *z, int n_log, int rate_bits) {
+    z->n = orc_pow(2, (uint64_t)n_log) % P; /* F::from_canonical_usize(1 << n_log) */
+    z->rate = (size_t)1 << rate_bits;
+    z->evals = (uint64_t *)malloc(sizeof(uint64_t) * z->rate);
+    z->inverses = (uint64_t *)malloc(sizeof(uint64_t) * z->rate);
+    uint64_t g_pow_n = 7; /* F::coset_shift().exp_power_of_2(n_log) */
+    for (int i = 0; i < n_log; i++) g_pow_n = orc_mul(g_pow_n, g_pow_n);
+    uint64_t v = orc_root_of_unity(rate_bits), x = 1;
+    for (size_t i = 0; i < z->rate; i++) {
+        z->evals[i] = orc_sub(orc_mul(g_pow_n, x), 1);
+        z->inverses[i] = orc_inv(z->evals[i]);
+        x = orc_mul(x, v);
+    }
+}
+static void zpoc_free(zero_poly_on_coset *z) {
+    free(z->evals);
+    free(z->inverses);
+}
+/* eval_l_0(index, x) = eval(index) * (n * (x - 1)).inverse() */
+static uint64_t zpoc_eval_l_0(const zero_poly_on_coset *z, size_t index, uint64_t x) {
+    return orc_mul(z->evals[index % z->rate], orc_inv(orc_mul(z->n, orc_sub(x, 1))));
+}
+
+/* fri/oracle.rs get_lde_values(index, step): leaf reverse_bits(index * step, lde_bits), salt stripped */
+static const uint64_t *lde_row(const orc_batch_view *b, size_t index, size_t step) {
+    int bits = b->log_n + b->rate_bits;
+    return b->leaves + orc_reverse_bits(index * step, bits) * (size_t)(b->n_cols + b->n_salt);
+}
+
+/* gates/gate.rs compute_filter(row, group_range, s, many_selector) */
+static uint64_t compute_filter(int row, int g0, int g1, uint64_t s, int many_selector) {
+    uint64_t f = 1;
+    for (int i = g0; i < g1; i++)
+        if (i != row) f = orc_mul(f, orc_sub((uint64_t)i, s));
+    if (many_selector) f = orc_mul(f, orc_sub(0xFFFFFFFFULL /* UNUSED_SELECTOR = u32::MAX */, s));
+    return f;
+}
+
+/* eval_unfiltered of the four gates; out[j] for j < num_constraints(gate); returns the constraint count.
+ * consts = local_constants with the selector prefix removed (vars.remove_prefix(num_selectors)). */
+static int gate_eval_unfiltered(const orc_gate *g, const uint64_t *consts, const uint64_t *wires,
+                                const uint64_t pi_hash[4], uint64_t *out) {
+    switch (g->kind) {
+        case ORC_GATE_NOOP:
+            return 0;
+        case ORC_GATE_CONSTANT: /* constants[const_input(i)] - wires[wire_output(i)], both = i */
+            for (int i = 0; i < g->param; i++) out[i] = orc_sub(consts[i], wires[i]);
+            return g->param;
+        case ORC_GATE_PUBLIC_INPUT: /* wires[i] - public_inputs_hash.elements[i] */
+            for (int i = 0; i < 4; i++) out[i] = orc_sub(wires[i], pi_hash[i]);
+            return 4;
+        case ORC_GATE_ARITHMETIC: /* output - (m0 * m1 * const_0 + addend * const_1), wires 4i .. 4i+3 */
+            for (int i = 0; i < g->param; i++) {
+                uint64_t m0 = wires[4 * i], m1 = wires[4 * i + 1], ad = wires[4 * i + 2], o = wires[4 * i + 3];
+                uint64_t computed = orc_add(orc_mul(orc_mul(m0, m1), consts[0]), orc_mul(ad, consts[1]));
+                out[i] = orc_sub(o, computed);
+            }
+            return g->param;
+        default:
+            return -1;
+    }
+}
+
+int orc_gate_num_constraints(const orc_gate *g) {
+    switch (g->kind) {
+        case ORC_GATE_NOOP: return 0;
+        case ORC_GATE_CONSTANT: return g->param;
+        case ORC_GATE_PUBLIC_INPUT: return 4;
+        case ORC_GATE_ARITHMETIC: return g->param;
+        default: return -1;
+    }
+}
+
+/* plonk/prover.rs compute_quotient_polys up to (not including) the final coset_ifft:
+ * out[a * lde_size + i] = quotient value of challenge alpha_a at point i of the coset 7 * <omega_{n 2^q}>. */
+int orc_quotient_values(const orc_circuit *c, const orc_batch_view *constants_sigmas, const orc_batch_view *wires_b,
+                        const orc_batch_view *zs_b, const uint64_t public_inputs_hash[4], const uint64_t *betas,
+                        const uint64_t *gammas, const uint64_t *alphas, uint64_t *out) {
+    const int nc = c->num_challenges, max_degree = c->quotient_degree_factor, num_prods = c->num_partial_products;
+    int qdb = 0;
+    while ((1 << qdb) < c->quotient_degree_factor) qdb++; /* log2_ceil */
+    if (qdb > c->rate_bits) return -1;                     /* upstream assert */
+    if (max_degree < 2 || nc < 1) return -1;
+    const int n_chunks = (c->num_routed_wires + max_degree - 1) / max_degree;
+    if (num_prods != n_chunks - 1) return -1;
+    if (constants_sigmas->n_cols != c->num_constants + c->num_routed_wires || wires_b->n_cols != c->num_wires ||
+        zs_b->n_cols != nc * (1 + num_prods))
+        return -1;
+    const size_t step = (size_t)1 << (c->rate_bits - qdb), next_step = (size_t)1 << qdb;
+    const size_t lde_size = (size_t)1 << (c->degree_bits + qdb);
+    zero_poly_on_coset zh;
+    zpoc_new(&zh, c->degree_bits, qdb);
+    const uint64_t w = orc_root_of_unity(c->degree_bits + qdb);
+    const int n_terms = nc + nc * n_chunks + c->num_gate_constraints;
+    int bad = 0;
+#pragma omp parallel
+    {
+        uint64_t *terms = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(n_terms + 1));
+        uint64_t *gate_out = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(c->num_gate_constraints + 4));
+#pragma omp for schedule(static)
+        for (size_t i = 0; i < lde_size; i++) {
+            const uint64_t x = orc_pow(w, i), shifted_x = orc_mul(7, x);
+            const size_t i_next = (i + next_step) % lde_size;
+            const uint64_t *local_cs = lde_row(constants_sigmas, i, step);
+            const uint64_t *local_constants = local_cs, *s_sigmas = local_cs + c->num_constants;
+            const uint64_t *local_wires = lde_row(wires_b, i, step);
+            const uint64_t *local_zs_pp = lde_row(zs_b, i, step), *next_zs_pp = lde_row(zs_b, i_next, step);
+            const uint64_t *partial_products = local_zs_pp + nc; /* partial_products_range */
+            int t = 0;
+            /* vanishing_z_1_terms */
+            const uint64_t l_0_x = zpoc_eval_l_0(&zh, i, shifted_x);
+            for (int k = 0; k < nc; k++) terms[t++] = orc_mul(l_0_x, orc_sub(local_zs_pp[k], 1));
+            /* vanishing_partial_products_terms: check_partial_products per challenge */
+            for (int k = 0; k < nc; k++) {
+                const uint64_t z_x = local_zs_pp[k], z_gx = next_zs_pp[k];
+                const uint64_t *pp = partial_products + (size_t)k * num_prods;
+                for (int m = 0; m < n_chunks; m++) {
+                    uint64_t num = 1, den = 1;
+                    for (int j = m * max_degree; j < c->num_routed_wires && j < (m + 1) * max_degree; j++) {
+                        const uint64_t wv = local_wires[j], s_id = orc_mul(c->k_is[j] % P, shifted_x);
+                        num = orc_mul(num, orc_add(orc_add(wv, orc_mul(betas[k], s_id)), gammas[k]));
+                        den = orc_mul(den, orc_add(orc_add(wv, orc_mul(betas[k], s_sigmas[j])), gammas[k]));
+                    }
+                    const uint64_t prev_acc = m == 0 ? z_x : pp[m - 1], next_acc = m == n_chunks - 1 ? z_gx : pp[m];
+                    terms[t++] = orc_sub(orc_mul(prev_acc, num), orc_mul(next_acc, den));
+                }
+            }
+            /* evaluate_gate_constraints_base_batch: filtered constraints of every gate summed per slot */
+            uint64_t *cons = terms + t;
+            for (int j = 0; j < c->num_gate_constraints; j++) cons[j] = 0;
+            for (int gi = 0; gi < c->n_gates; gi++) {
+                const orc_gate *g = &c->gates[gi];
+                const uint64_t filter = compute_filter(g->row, g->group_start, g->group_end,
+                                                       local_constants[g->selector_index], c->num_selectors > 1);
+                int k = gate_eval_unfiltered(g, local_constants + c->num_selectors, local_wires, public_inputs_hash, gate_out);
+                if (k < 0 || k > c->num_gate_constraints) { bad = 1; k = 0; }
+                for (int j = 0; j < k; j++) cons[j] = orc_add(cons[j], orc_mul(filter, gate_out[j]));
+            }
+            t += c->num_gate_constraints;
+            /* reduce_with_powers_multi(terms, alphas), then * z_h_on_coset.eval_inverse(i) */
+            const uint64_t denominator_inv = zh.inverses[i % zh.rate];
+            for (int a = 0; a < nc; a++) {
+                uint64_t acc = 0;
+                for (int j = t - 1; j >= 0; j--) acc = orc_add(terms[j], orc_mul(acc, alphas[a]));
+                out[(size_t)a * lde_size + i] = orc_mul(acc, denominator_inv);
+            }
+        }
+        free(terms);
+        free(gate_out);
+    }
+    zpoc_free(&zh);
+    return bad ? -1 : 0;
+}
+
+/* ------------------------------------------------------------ ProofWithPublicInputs::to_bytes */
+typedef struct {
+    uint8_t *buf;
+    size_t pos;
+} wr;
+static void w_u64s(wr *w, const uint64_t *v, size_t n) { /* field elements / hashes: u64 little-endian */
+    for (size_t i = 0; i < n; i++) {
+        if (w->buf)
+            for (int b = 0; b < 8; b++) w->buf[w->pos + b] = (uint8_t)(v[i] >> (8 * b));
+        w->pos += 8;
+    }
+}
+static const uint64_t *w_merkle_proof(wr *w, const uint64_t *p, int n_sib) { /* write_merkle_proof */
+    if (w->buf) w->buf[w->pos] = (uint8_t)n_sib;
+    w->pos += 1;
+    w_u64s(w, p, 4 * (size_t)n_sib);
+    return p + 4 * (size_t)n_sib;
+}
+/* write_fri_proof over the flat stream of orc_fri_prove_openings (field order of FriProof) */
+static const uint64_t *w_fri_proof(wr *w, const uint64_t *p, const orc_fri_params *fp, const int *widths, int n_oracles) {
+    const int log_nb = fp->degree_bits + fp->rate_bits;
+    for (int r = 0; r < fp->n_arity; r++) { /* commit_phase_merkle_caps */
+        w_u64s(w, p, (size_t)4 << fp->cap_height);
+        p += (size_t)4 << fp->cap_height;
+    }
+    for (int q = 0; q < fp->num_query_rounds; q++) { /* write_fri_query_round */
+        for (int o = 0; o < n_oracles; o++) {        /* write_fri_initial_proof */
+            w_u64s(w, p, (size_t)widths[o]);
+            p = w_merkle_proof(w, p + widths[o], log_nb - fp->cap_height);
+        }
+        int lg = log_nb;
+        for (int r = 0; r < fp->n_arity; r++) { /* write_fri_query_step */
+            lg -= fp->arity_bits[r];
+            w_u64s(w, p, (size_t)2 << fp->arity_bits[r]);
+            p = w_merkle_proof(w, p + ((size_t)2 << fp->arity_bits[r]), lg - fp->cap_height);
+        }
+    }
+    int tot = 0;
+    for (int r = 0; r < fp->n_arity; r++) tot += fp->arity_bits[r];
+    w_u64s(w, p, ((size_t)2 << (fp->degree_bits - tot)) + 1); /* final_poly.coeffs, pow_witness */
+    return p + ((size_t)2 << (fp->degree_bits - tot)) + 1;
+}
+/* returns the byte count; out == NULL only counts */
+size_t orc_write_proof_with_public_inputs(const uint64_t *wires_cap, const uint64_t *zs_cap, const uint64_t *quotient_cap,
+                                          const uint64_t *const openings[7], const int n_openings[7],
+                                          const uint64_t *fri_words, const orc_fri_params *fp, const int *widths,
+                                          int n_oracles, const uint64_t *public_inputs, int n_public_inputs, uint8_t *out) {
+    wr w = {out, 0};
+    const size_t cap_words = (size_t)4 << fp->cap_height;
+    w_u64s(&w, wires_cap, cap_words); /* write_proof */
+    w_u64s(&w, zs_cap, cap_words);
+    w_u64s(&w, quotient_cap, cap_words);
+    for (int k = 0; k < 7; k++) w_u64s(&w, openings[k], 2 * (size_t)n_openings[k]); /* write_opening_set */
+    w_fri_proof(&w, fri_words, fp, widths, n_oracles);
+    w_u64s(&w, public_inputs, (size_t)n_public_inputs); /* write_field_vec(public_inputs) */
+    return w.pos;
+}
