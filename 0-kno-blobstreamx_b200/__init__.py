@@ -46,6 +46,18 @@ from .proof import (  # noqa: F401
     fri_proof_bytes,
     fri_proof_layout,
 )
+from .plonk import (  # noqa: F401
+    GATE_ARITHMETIC,
+    GATE_CONSTANT,
+    GATE_NOOP,
+    GATE_PUBLIC_INPUT,
+    CircuitDescription,
+    Gate,
+    SyntheticCircuit,
+    compute_quotient_polys,
+    quotient_values,
+    synthetic_circuit,
+)
 from .parallel import (  # noqa: F401
     ShardPlan,
     ShardedPolynomialBatch,

@@ -23,6 +23,7 @@ EXPORTED_SYMBOLS = [
     "bsx_shard_slab_device", "bsx_shard_staging_device", "bsx_shard_coeffs_device", "bsx_shard_slab_ipc",
     "bsx_shard_set_peer_ipc", "bsx_shard_set_peer_ptr", "bsx_shard_transform", "bsx_shard_commit", "bsx_shard_coeffs",
     "bsx_fri_proof_layout", "bsx_fri_proof_bytes", "bsx_proof_with_public_inputs_bytes",
+    "bsx_quotient_values", "bsx_compute_quotient_polys",
 ]
 
 

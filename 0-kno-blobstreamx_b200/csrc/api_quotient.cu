@@ -1,0 +1,345 @@
+// api_quotient.cu -- the vanishing polynomial on the quotient coset, on the device.
+// Replaces plonky2 plonk/prover.rs `compute_quotient_polys` and plonk/vanishing_poly.rs
+// `eval_vanishing_poly_base_batch` / `evaluate_gate_constraints_base_batch` (with plonk/plonk_common.rs
+// `ZeroPolyOnCoset`, `reduce_with_powers_multi`, plonk/vanishing_poly.rs `check_partial_products`, gates/gate.rs
+// `compute_filter`) for circuits made of NoopGate, ConstantGate, PublicInputGate and ArithmeticGate.
+//
+// Upstream walks the quotient domain in batches of 32 points and gathers, per point i, the rows
+// get_lde_values(i, step) of the constants+sigmas, wires and Zs commitments -- on the CPU that means the whole LDE
+// has to be in host memory (9 GB over PCIe at the headline shape).  Here the LDEs never leave HBM: they sit
+// column-major in LEAF order, and the rows the quotient needs, reverse_bits(i * step), are exactly the first
+// 2^(degree_bits + q) leaves, so thread l reads leaf l of every column (coalesced) and handles the domain point
+// i = reverse_bits(l).  Only Z(g x) lives in another row (2 gathered words of ~240).
+//
+// Field arithmetic is exact, so the order of operations is free: every vanishing term is folded straight into one
+// three-column accumulator per alpha with its precomputed power (reduce_with_powers_multi = sum_j alpha^j term_j),
+// products run in lazy form, and L_0(x) = Z_H(x) / (n (x - 1)) costs one Fermat inversion per point.
+#include "api_internal.h"
+
+#define QV_MAX_CHALLENGES 4
+#define QV_MAX_TERMS 4096  // gl_acc3 is exact for sums of up to 2^12 products
+
+struct QvParams {
+    const u64 *cs, *wires, *zs;  // LDE buffers, column-major, leaf order
+    size_t stride;               // words per column (2^(degree_bits + rate_bits)), the same for the three batches
+    int log_q, qdb;              // quotient domain = 2^log_q points, log_q = degree_bits + qdb
+    int nc, n_routed, max_degree, n_chunks, num_constants, num_selectors, n_gates, many_selector;
+    int n_terms, gate_base;
+    const bsx_gate *gates;
+    const u64 *k_is;
+    const u64 *apow;  // [nc][n_terms]: alpha_a^j
+    const u64 *zh;    // [2^qdb] Z_H on the coset, then [2^qdb] its inverses
+    u64 betas[QV_MAX_CHALLENGES], gammas[QV_MAX_CHALLENGES], pi_hash[4];
+    u64 n_field;      // F::from_canonical_usize(n)
+    PowTable tw;      // powers of omega_{2^log_q}
+    u64 *out;         // [nc][2^log_q], natural order
+};
+
+__device__ __forceinline__ u64 qv_inv(u64 a) {  // a^(p - 2), p - 2 = 2^64 - 2^32 - 1: bits 63..33 and 31..0 set
+    u64 t = a;                                   // t_k = a^(2^k - 1)
+    u64 t2 = gl_mul_lazy(gl_sqr_lazy(t), a);     // 2 bits
+    u64 t4 = gl_mul_lazy(gl_sqr_lazy(gl_sqr_lazy(t2)), t2);
+    u64 t8 = t4;
+    for (int i = 0; i < 4; i++) t8 = gl_sqr_lazy(t8);
+    t8 = gl_mul_lazy(t8, t4);
+    u64 t16 = t8;
+    for (int i = 0; i < 8; i++) t16 = gl_sqr_lazy(t16);
+    t16 = gl_mul_lazy(t16, t8);
+    u64 t24 = t16;
+    for (int i = 0; i < 8; i++) t24 = gl_sqr_lazy(t24);
+    t24 = gl_mul_lazy(t24, t8);
+    u64 t28 = t24;
+    for (int i = 0; i < 4; i++) t28 = gl_sqr_lazy(t28);
+    t28 = gl_mul_lazy(t28, t4);
+    u64 t30 = gl_mul_lazy(gl_sqr_lazy(gl_sqr_lazy(t28)), t2);
+    u64 t31 = gl_mul_lazy(gl_sqr_lazy(t30), a);
+    u64 t32 = gl_mul_lazy(gl_sqr_lazy(t31), a);
+    u64 r = t31;  // a^(2^31 - 1) -> shifted up by 33 bits, then the low 32 ones
+    for (int i = 0; i < 33; i++) r = gl_sqr_lazy(r);
+    return gl_mul_lazy(r, t32);
+}
+
+// term (lazy) times alpha_a^idx into every accumulator
+__device__ __forceinline__ void qv_fold(gl_acc3 *res, const QvParams &P, u64 term, int idx) {
+#pragma unroll
+    for (int a = 0; a < QV_MAX_CHALLENGES; a++)
+        if (a < P.nc) gl_acc3_mac(res[a], term, __ldg(P.apow + (size_t)a * P.n_terms + idx));
+}
+
+__global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) {
+    const size_t l = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // leaf = row of the LDE buffers
+    const size_t q_size = (size_t)1 << P.log_q;
+    if (l >= q_size) return;
+    const u32 i = __brev((u32)l) >> (32 - P.log_q);                   // domain index, x = omega^i
+    const u32 i_next = (i + (1u << P.qdb)) & (u32)(q_size - 1);
+    const size_t l_next = __brev(i_next) >> (32 - P.log_q);
+    const int nc = P.nc;
+    u64 x = __ldg(P.tw.lo + (i & 4095));
+    if (i >> 12) x = gl_mul_lazy(x, __ldg(P.tw.hi + (i >> 12)));
+    const u64 sx = gl_canon_fast(gl_mul_lazy(x, 7));  // F::coset_shift() * x
+    gl_acc3 res[QV_MAX_CHALLENGES];
+#pragma unroll
+    for (int a = 0; a < QV_MAX_CHALLENGES; a++) res[a] = gl_acc3_zero();
+
+    // ---- vanishing_z_1_terms: L_0(x) (Z(x) - 1), L_0(x) = Z_H(x) / (n (x - 1))
+    const u64 zh = __ldg(P.zh + (i & ((1u << P.qdb) - 1)));
+    const u64 l0 = gl_mul_lazy(zh, qv_inv(gl_mul_lazy(P.n_field, gl_sub_c(sx, 1))));
+    const u64 *zrow = P.zs + l;
+#pragma unroll
+    for (int k = 0; k < QV_MAX_CHALLENGES; k++)
+        if (k < nc) qv_fold(res, P, gl_mul_lazy(l0, gl_sub_c(__ldg(zrow + (size_t)k * P.stride), 1)), k);
+
+    // ---- vanishing_partial_products_terms: check_partial_products for every challenge, one pass over the wires
+    u64 bx[QV_MAX_CHALLENGES];
+#pragma unroll
+    for (int k = 0; k < QV_MAX_CHALLENGES; k++) bx[k] = k < nc ? gl_mul_lazy(P.betas[k], sx) : 0;
+    const u64 *wrow = P.wires + l, *srow = P.cs + (size_t)P.num_constants * P.stride + l;
+    for (int m = 0; m < P.n_chunks; m++) {
+        u64 num[QV_MAX_CHALLENGES], den[QV_MAX_CHALLENGES];
+#pragma unroll
+        for (int k = 0; k < QV_MAX_CHALLENGES; k++) num[k] = den[k] = 1;
+        const int j1 = min(P.n_routed, (m + 1) * P.max_degree);
+        for (int j = m * P.max_degree; j < j1; j++) {
+            const u64 w = __ldg(wrow + (size_t)j * P.stride), s = __ldg(srow + (size_t)j * P.stride), kj = __ldg(P.k_is + j);
+#pragma unroll
+            for (int k = 0; k < QV_MAX_CHALLENGES; k++)
+                if (k < nc) {
+                    const u64 wg = gl_add_lazy_canon(w, P.gammas[k]);                 // w + gamma (w < p: no second wrap)
+                    num[k] = gl_mul_lazy(num[k], gl_mul_add_lazy(bx[k], kj, wg));     // w + beta k_j x + gamma
+                    den[k] = gl_mul_lazy(den[k], gl_mul_add_lazy(P.betas[k], s, wg)); // w + beta sigma_j + gamma
+                }
+        }
+#pragma unroll
+        for (int k = 0; k < QV_MAX_CHALLENGES; k++)
+            if (k < nc) {
+                // product_accs = z_x, partial products of challenge k, z_gx; window (m, m + 1)
+                const u64 *pp = zrow + (size_t)(nc + k * (P.n_chunks - 1)) * P.stride;
+                const u64 prev = m == 0 ? __ldg(zrow + (size_t)k * P.stride) : __ldg(pp + (size_t)(m - 1) * P.stride);
+                const u64 next = m == P.n_chunks - 1 ? __ldg(P.zs + (size_t)k * P.stride + l_next) : __ldg(pp + (size_t)m * P.stride);
+                const u64 t = gl_sub_c(gl_canon_fast(gl_mul_lazy(prev, num[k])), gl_canon_fast(gl_mul_lazy(next, den[k])));
+                qv_fold(res, P, t, nc + k * P.n_chunks + m);
+            }
+    }
+
+    // ---- evaluate_gate_constraints_base_batch: filter * constraint, slot j of every gate shares alpha^(gate_base + j)
+    const u64 *crow = P.cs + l;                                          // local_constants (selectors first)
+    const u64 *gconst = P.cs + (size_t)P.num_selectors * P.stride + l;   // vars.remove_prefix(num_selectors)
+    for (int gi = 0; gi < P.n_gates; gi++) {
+        const bsx_gate g = P.gates[gi];
+        if (g.kind == BSX_GATE_NOOP) continue;
+        const u64 s = __ldg(crow + (size_t)g.selector_index * P.stride);
+        u64 f = 1;  // compute_filter
+        for (int r = g.group_start; r < g.group_end; r++)
+            if (r != g.row) f = gl_mul_lazy(f, gl_sub_c((u64)r, s));
+        if (P.many_selector) f = gl_mul_lazy(f, gl_sub_c(0xFFFFFFFFULL, s));  // UNUSED_SELECTOR
+        if (g.kind == BSX_GATE_CONSTANT) {
+            for (int t = 0; t < g.param; t++) {
+                const u64 c = gl_sub_c(__ldg(gconst + (size_t)t * P.stride), __ldg(wrow + (size_t)t * P.stride));
+                qv_fold(res, P, gl_mul_lazy(f, c), P.gate_base + t);
+            }
+        } else if (g.kind == BSX_GATE_PUBLIC_INPUT) {
+            for (int t = 0; t < 4; t++)
+                qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(__ldg(wrow + (size_t)t * P.stride), P.pi_hash[t])), P.gate_base + t);
+        } else {  // BSX_GATE_ARITHMETIC: output - (m0 m1 const_0 + addend const_1)
+            const u64 c0 = __ldg(gconst), c1 = __ldg(gconst + P.stride);
+            for (int t = 0; t < g.param; t++) {
+                const u64 *wq = wrow + (size_t)(4 * t) * P.stride;
+                const u64 m0 = __ldg(wq), m1 = __ldg(wq + P.stride), ad = __ldg(wq + 2 * P.stride), o = __ldg(wq + 3 * P.stride);
+                const u64 computed = gl_mul_add_lazy(gl_mul_lazy(m0, m1), c0, gl_mul_lazy(ad, c1));
+                qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(o, gl_canon_fast(computed))), P.gate_base + t);
+            }
+        }
+    }
+
+    // ---- * z_h_on_coset.eval_inverse(i)
+    const u64 zh_inv = __ldg(P.zh + (1u << P.qdb) + (i & ((1u << P.qdb) - 1)));
+#pragma unroll
+    for (int a = 0; a < QV_MAX_CHALLENGES; a++)
+        if (a < nc) P.out[(size_t)a * q_size + i] = gl_canon_fast(gl_mul_lazy(gl_acc3_reduce(res[a]), zh_inv));
+}
+
+static int gate_constraints(const bsx_gate &g) {
+    switch (g.kind) {
+        case BSX_GATE_NOOP: return 0;
+        case BSX_GATE_CONSTANT: return g.param;
+        case BSX_GATE_PUBLIC_INPUT: return 4;
+        case BSX_GATE_ARITHMETIC: return g.param;
+        default: return -1;
+    }
+}
+
+static int log2_ceil(int x) {
+    int b = 0;
+    while ((1 << b) < x) b++;
+    return b;
+}
+
+// values on the device: out_dev[a][i]
+static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch *cs, bsx_batch *wires, bsx_batch *zs,
+                                  const uint64_t *pi_hash, const uint64_t *betas, const uint64_t *gammas,
+                                  const uint64_t *alphas, u64 *out_dev) {
+    const int nc = c->num_challenges, max_degree = c->quotient_degree_factor;
+    if (nc < 1 || nc > QV_MAX_CHALLENGES)
+        return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "num_challenges=%d outside [1, %d]", nc, QV_MAX_CHALLENGES);
+    if (max_degree < 2) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "quotient_degree_factor=%d: check_partial_products needs > 1", max_degree);
+    const int qdb = log2_ceil(max_degree);
+    if (qdb > c->rate_bits)  // upstream assert
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "Having constraints of degree higher than the rate is not supported yet.");
+    if (c->degree_bits < 0 || c->degree_bits + qdb > 24 || c->degree_bits + qdb < 1)
+        return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "degree_bits=%d + quotient_degree_bits=%d outside [1, 24]", c->degree_bits, qdb);
+    if (c->num_routed_wires < 1 || c->num_routed_wires > c->num_wires || !c->k_is || (c->n_gates > 0 && !c->gates))
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad circuit description");
+    const int n_chunks = (c->num_routed_wires + max_degree - 1) / max_degree;
+    if (c->num_partial_products != n_chunks - 1)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "num_partial_products=%d, expected %d", c->num_partial_products, n_chunks - 1);
+    bsx_batch *bs[3] = {cs, wires, zs};
+    const int want_cols[3] = {c->num_constants + c->num_routed_wires, c->num_wires, nc * n_chunks};
+    for (int k = 0; k < 3; k++) {
+        if (!bs[k] || bs[k]->ctx != ctx) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "commitment %d belongs to another context", k);
+        if (bs[k]->log_n != c->degree_bits || bs[k]->rate_bits != c->rate_bits || bs[k]->n_cols != want_cols[k])
+            return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "commitment %d has shape 2^%d x %d rate_bits %d, the circuit wants 2^%d x %d rate_bits %d",
+                            k, bs[k]->log_n, bs[k]->n_cols, bs[k]->rate_bits, c->degree_bits, want_cols[k], c->rate_bits);
+    }
+    if (c->num_selectors < 0 || c->num_selectors > c->num_constants) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad selector count");
+    const int n_gate_consts = c->num_constants - c->num_selectors;
+    for (int g = 0; g < c->n_gates; g++) {
+        const bsx_gate &G = c->gates[g];
+        const int k = gate_constraints(G);
+        bool ok = k >= 0 && k <= c->num_gate_constraints && G.selector_index >= 0 && G.selector_index < c->num_selectors &&
+                  G.group_start <= G.row && G.row < G.group_end && G.group_end - G.group_start <= 64;
+        if (ok && G.kind == BSX_GATE_CONSTANT) ok = G.param <= n_gate_consts && G.param <= c->num_wires;
+        if (ok && G.kind == BSX_GATE_PUBLIC_INPUT) ok = c->num_wires >= 4;
+        if (ok && G.kind == BSX_GATE_ARITHMETIC) ok = 4 * G.param <= c->num_wires && n_gate_consts >= 2;
+        if (!ok) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "gate %d (kind %d, param %d) does not fit the circuit", g, G.kind, G.param);
+    }
+    QvParams P;
+    P.nc = nc;
+    P.n_terms = nc + nc * n_chunks + c->num_gate_constraints;
+    P.gate_base = nc + nc * n_chunks;
+    if (P.n_terms > QV_MAX_TERMS) return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "%d vanishing terms (at most %d)", P.n_terms, QV_MAX_TERMS);
+    CU(ctx, cudaSetDevice(ctx->device));
+    // host-side tables: alpha powers, Z_H on the coset and its inverses (ZeroPolyOnCoset::new), k_is, gates
+    const int rate = 1 << qdb;
+    std::vector<u64> h((size_t)nc * P.n_terms + 2 * rate + c->num_routed_wires);
+    for (int a = 0; a < nc; a++) {
+        u64 pw = 1, al = alphas[a] % GL_P;
+        for (int j = 0; j < P.n_terms; j++) {
+            h[(size_t)a * P.n_terms + j] = pw;
+            pw = gl_host_mul(pw, al);
+        }
+    }
+    u64 g_pow_n = 7;
+    for (int k = 0; k < c->degree_bits; k++) g_pow_n = gl_host_mul(g_pow_n, g_pow_n);
+    const u64 v = gl_host_root(qdb);
+    u64 xv = 1;
+    u64 *zh = h.data() + (size_t)nc * P.n_terms;
+    for (int k = 0; k < rate; k++) {
+        const u64 e = gl_host_mul(g_pow_n, xv);
+        zh[k] = e ? e - 1 : GL_P - 1;
+        if (zh[k] == 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "Z_H vanishes on the coset");
+        zh[rate + k] = gl_host_inv(zh[k]);
+        xv = gl_host_mul(xv, v);
+    }
+    for (int j = 0; j < c->num_routed_wires; j++) zh[2 * rate + j] = c->k_is[j] % GL_P;
+    u64 *tab;
+    bsx_gate *gates_dev = nullptr;
+    TRY(bsx_alloc(ctx, &tab, h.size()));
+    TRY(bsx_copy_in(ctx, tab, h.data(), h.size(), BSX_HOST));
+    if (c->n_gates > 0) {
+        const size_t gw = ((size_t)c->n_gates * sizeof(bsx_gate) + 7) / 8;
+        TRY(bsx_alloc(ctx, (u64 **)&gates_dev, gw));
+        CU(ctx, cudaMemcpyAsync(gates_dev, c->gates, (size_t)c->n_gates * sizeof(bsx_gate), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    P.cs = cs->lde;
+    P.wires = wires->lde;
+    P.zs = zs->lde;
+    P.stride = (size_t)1 << (c->degree_bits + c->rate_bits);
+    P.log_q = c->degree_bits + qdb;
+    P.qdb = qdb;
+    P.n_routed = c->num_routed_wires;
+    P.max_degree = max_degree;
+    P.n_chunks = n_chunks;
+    P.num_constants = c->num_constants;
+    P.num_selectors = c->num_selectors;
+    P.n_gates = c->n_gates;
+    P.many_selector = c->num_selectors > 1;
+    P.gates = gates_dev;
+    P.apow = tab;
+    P.zh = tab + (size_t)nc * P.n_terms;
+    P.k_is = P.zh + 2 * rate;
+    for (int k = 0; k < QV_MAX_CHALLENGES; k++) {
+        P.betas[k] = k < nc ? betas[k] % GL_P : 0;
+        P.gammas[k] = k < nc ? gammas[k] % GL_P : 0;
+    }
+    for (int k = 0; k < 4; k++) P.pi_hash[k] = pi_hash ? pi_hash[k] % GL_P : 0;
+    P.n_field = ((u64)1 << c->degree_bits) % GL_P;
+    TRY(bsx_pow_table(ctx, P.log_q, 0, &P.tw));
+    P.out = out_dev;
+    const size_t q_size = (size_t)1 << P.log_q;
+    BSX_COUNT_LAUNCH();
+    quotient_values_kernel<<<(unsigned)((q_size + 255) / 256), 256, 0, ctx->stream>>>(P);
+    CU(ctx, cudaGetLastError());
+    bsx_free(ctx, tab);
+    bsx_free(ctx, (u64 *)gates_dev);
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_quotient_values(bsx_ctx *ctx, const bsx_circuit *circuit, bsx_batch *constants_sigmas,
+                                       bsx_batch *wires, bsx_batch *zs_partial_products,
+                                       const uint64_t *public_inputs_hash, const uint64_t *betas, const uint64_t *gammas,
+                                       const uint64_t *alphas, uint64_t *out, int32_t out_mem) {
+    if (!ctx || !circuit || !betas || !gammas || !alphas || !out) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
+    const int qdb = log2_ceil(circuit->quotient_degree_factor < 1 ? 1 : circuit->quotient_degree_factor);
+    if (circuit->num_challenges < 1 || circuit->degree_bits < 0 || circuit->degree_bits + qdb > 24)
+        return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "bad circuit shape");
+    const size_t words = ((size_t)circuit->num_challenges << (circuit->degree_bits + qdb));
+    u64 *dev = (u64 *)out;
+    if (out_mem != BSX_DEVICE) TRY(bsx_alloc(ctx, &dev, words));
+    TRY(quotient_values_device(ctx, circuit, constants_sigmas, wires, zs_partial_products, public_inputs_hash, betas,
+                               gammas, alphas, dev));
+    if (out_mem != BSX_DEVICE) {
+        TRY(bsx_copy_out(ctx, (u64 *)out, dev, words, out_mem));
+        bsx_free(ctx, dev);
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
+extern "C" int32_t bsx_compute_quotient_polys(bsx_ctx *ctx, const bsx_circuit *circuit, bsx_batch *constants_sigmas,
+                                              bsx_batch *wires, bsx_batch *zs_partial_products,
+                                              const uint64_t *public_inputs_hash, const uint64_t *betas,
+                                              const uint64_t *gammas, const uint64_t *alphas, int32_t cap_height,
+                                              int32_t blinding, bsx_batch **out, bsx_timing *timing, float *eval_ms) {
+    if (!ctx || !circuit || !betas || !gammas || !alphas || !out) return BSX_ERR_INVALID_ARG;
+    *out = nullptr;
+    BsxScope scope(ctx);
+    const int qdb = log2_ceil(circuit->quotient_degree_factor < 1 ? 1 : circuit->quotient_degree_factor);
+    if (circuit->num_challenges < 1 || circuit->degree_bits < 0 || circuit->degree_bits + qdb > 24)
+        return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "bad circuit shape");
+    const size_t words = ((size_t)circuit->num_challenges << (circuit->degree_bits + qdb));
+    u64 *dev;
+    TRY(bsx_alloc(ctx, &dev, words));
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (eval_ms) {
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        cudaEventRecord(e0, ctx->stream);
+    }
+    int rc = quotient_values_device(ctx, circuit, constants_sigmas, wires, zs_partial_products, public_inputs_hash, betas,
+                                    gammas, alphas, dev);
+    if (eval_ms) cudaEventRecord(e1, ctx->stream);
+    // the tail of compute_quotient_polys (coset_ifft) and, in prove(), trim_to_len / chunks / from_coeffs
+    if (rc == BSX_OK)
+        rc = bsx_batch_from_quotient_values(ctx, (const uint64_t *)dev, BSX_DEVICE, circuit->degree_bits, qdb,
+                                            circuit->quotient_degree_factor, circuit->num_challenges, circuit->rate_bits,
+                                            cap_height, blinding, nullptr, out, timing);
+    if (eval_ms) {
+        *eval_ms = 0;
+        if (rc == BSX_OK && cudaEventSynchronize(e1) == cudaSuccess) cudaEventElapsedTime(eval_ms, e0, e1);
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+    }
+    bsx_free(ctx, dev);
+    return rc;
+}

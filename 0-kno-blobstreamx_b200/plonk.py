@@ -1,0 +1,216 @@
+"""Host mirror of the prover steps around the commitments (plonky2 plonk/prover.rs): the circuit description that
+`compute_quotient_polys` reads from `CommonCircuitData`, and the device quotient evaluation behind
+bsx_quotient_values / bsx_compute_quotient_polys.  Also a synthetic circuit of the four built-in gates with a
+satisfying witness (the plonky2x circuits of BlobstreamX are not in the reference mount), used by tests and bench."""
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import List
+
+import numpy as np
+
+from .binding import BsxError, PolynomialBatch, Timing, lib, _np, _ptr
+
+P = 0xFFFFFFFF00000001
+GATE_NOOP, GATE_CONSTANT, GATE_PUBLIC_INPUT, GATE_ARITHMETIC = 0, 1, 2, 3
+
+
+class _Gate(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("param", C.c_int32), ("row", C.c_int32), ("selector_index", C.c_int32),
+                ("group_start", C.c_int32), ("group_end", C.c_int32)]
+
+
+class _Circuit(C.Structure):
+    _fields_ = [("degree_bits", C.c_int32), ("rate_bits", C.c_int32), ("quotient_degree_factor", C.c_int32),
+                ("num_challenges", C.c_int32), ("num_wires", C.c_int32), ("num_routed_wires", C.c_int32),
+                ("num_constants", C.c_int32), ("num_selectors", C.c_int32), ("num_partial_products", C.c_int32),
+                ("num_gate_constraints", C.c_int32), ("n_gates", C.c_int32), ("gates", C.c_void_p), ("k_is", C.c_void_p)]
+
+
+@dataclass
+class Gate:
+    """One entry of `common_data.gates` with its share of `selectors_info`."""
+    kind: int
+    param: int = 0
+    row: int = 0
+    selector_index: int = 0
+    group_start: int = 0
+    group_end: int = 1
+
+    def num_constraints(self):
+        return {GATE_NOOP: 0, GATE_CONSTANT: self.param, GATE_PUBLIC_INPUT: 4, GATE_ARITHMETIC: self.param}[self.kind]
+
+
+@dataclass
+class CircuitDescription:
+    """The fields of `CommonCircuitData` / `CircuitConfig` the quotient evaluation reads.  Defaults are
+    `CircuitConfig::standard_recursion_config()`."""
+    degree_bits: int
+    gates: List[Gate]
+    rate_bits: int = 3
+    quotient_degree_factor: int = 8
+    num_challenges: int = 2
+    num_wires: int = 135
+    num_routed_wires: int = 80
+    num_constants: int = 3          # selectors first, then the gates' constants
+    num_selectors: int = 1
+    k_is: np.ndarray = field(default=None)
+
+    def __post_init__(self):
+        if self.k_is is None:  # plonk/plonk_common.rs get_unique_coset_shifts: g^j, g = 7
+            self.k_is = np.array([pow(7, j, P) for j in range(self.num_routed_wires)], dtype=np.uint64)
+
+    @property
+    def num_partial_products(self):
+        return -(-self.num_routed_wires // self.quotient_degree_factor) - 1
+
+    @property
+    def num_gate_constraints(self):
+        return max([g.num_constraints() for g in self.gates] + [0])
+
+    @property
+    def quotient_degree_bits(self):
+        return max(self.quotient_degree_factor - 1, 0).bit_length()
+
+    def as_dict(self):
+        """The oracle's view of the same description (oracle.quotient_values)."""
+        return {"degree_bits": self.degree_bits, "rate_bits": self.rate_bits,
+                "quotient_degree_factor": self.quotient_degree_factor, "num_challenges": self.num_challenges,
+                "num_wires": self.num_wires, "num_routed_wires": self.num_routed_wires,
+                "num_constants": self.num_constants, "num_selectors": self.num_selectors,
+                "num_partial_products": self.num_partial_products, "num_gate_constraints": self.num_gate_constraints,
+                "gates": [(g.kind, g.param, g.row, g.selector_index, g.group_start, g.group_end) for g in self.gates],
+                "k_is": self.k_is}
+
+    def _struct(self):
+        gates = (_Gate * max(len(self.gates), 1))(*[_Gate(g.kind, g.param, g.row, g.selector_index, g.group_start,
+                                                          g.group_end) for g in self.gates])
+        k_is = _np(self.k_is)
+        c = _Circuit(self.degree_bits, self.rate_bits, self.quotient_degree_factor, self.num_challenges, self.num_wires,
+                     self.num_routed_wires, self.num_constants, self.num_selectors, self.num_partial_products,
+                     self.num_gate_constraints, len(self.gates), C.cast(gates, C.c_void_p), k_is.ctypes.data)
+        return c, (gates, k_is)
+
+
+def _declare():
+    L = lib()
+    if getattr(L, "_bsx_plonk_declared", False):
+        return L
+    vp, i32 = C.c_void_p, C.c_int32
+    L.bsx_quotient_values.restype = i32
+    L.bsx_quotient_values.argtypes = [vp, C.POINTER(_Circuit), vp, vp, vp, vp, vp, vp, vp, vp, i32]
+    L.bsx_compute_quotient_polys.restype = i32
+    L.bsx_compute_quotient_polys.argtypes = [vp, C.POINTER(_Circuit), vp, vp, vp, vp, vp, vp, vp, i32, i32,
+                                             C.POINTER(vp), C.POINTER(Timing), C.POINTER(C.c_float)]
+    L._bsx_plonk_declared = True
+    return L
+
+
+def _challenges(circuit, public_inputs_hash, betas, gammas, alphas):
+    pih = _np(public_inputs_hash if public_inputs_hash is not None else np.zeros(4, dtype=np.uint64)).reshape(4)
+    b, g, a = _np(betas).reshape(-1), _np(gammas).reshape(-1), _np(alphas).reshape(-1)
+    if not (b.size == g.size == a.size == circuit.num_challenges):
+        raise BsxError("betas / gammas / alphas must each hold num_challenges elements")
+    return pih, b, g, a
+
+
+def quotient_values(ctx, circuit, constants_sigmas, wires, zs_partial_products, public_inputs_hash, betas, gammas, alphas,
+                    out_device_ptr=None):
+    """`quotient_values` of plonk/prover.rs compute_quotient_polys, transposed: (num_challenges, 2^(degree_bits + q))
+    values on the coset, before `coset_ifft`.  The commitments are device-resident PolynomialBatch objects."""
+    c, keep = circuit._struct()
+    pih, b, g, a = _challenges(circuit, public_inputs_hash, betas, gammas, alphas)
+    out = None
+    if out_device_ptr is None:
+        out = np.zeros((circuit.num_challenges, 1 << (circuit.degree_bits + circuit.quotient_degree_bits)), dtype=np.uint64)
+    ctx.check(_declare().bsx_quotient_values(
+        ctx._h, C.byref(c), constants_sigmas._h, wires._h, zs_partial_products._h, _ptr(pih), _ptr(b), _ptr(g), _ptr(a),
+        _ptr(out) if out is not None else C.c_void_p(int(out_device_ptr)), 0 if out is not None else 1))
+    return out
+
+
+def compute_quotient_polys(ctx, circuit, constants_sigmas, wires, zs_partial_products, public_inputs_hash, betas, gammas,
+                           alphas, cap_height, blinding=False, timing=False):
+    """plonk/prover.rs: `compute_quotient_polys(..)` followed by prove()'s `trim_to_len`, `.chunks(degree)` and
+    `PolynomialBatch::from_coeffs(all_quotient_poly_chunks, ..)` -> the quotient commitment.  Raises where upstream
+    panics (a witness that does not satisfy the circuit: "Quotient has failed").  The batch gets `.eval_ms`."""
+    c, keep = circuit._struct()
+    pih, b, g, a = _challenges(circuit, public_inputs_hash, betas, gammas, alphas)
+    h = C.c_void_p()
+    t = Timing() if timing else None
+    ms = C.c_float()
+    ctx.check(_declare().bsx_compute_quotient_polys(
+        ctx._h, C.byref(c), constants_sigmas._h, wires._h, zs_partial_products._h, _ptr(pih), _ptr(b), _ptr(g), _ptr(a),
+        int(cap_height), 1 if blinding else 0, C.byref(h), C.byref(t) if t is not None else None, C.byref(ms)))
+    batch = PolynomialBatch(ctx, h, t)
+    batch.eval_ms = float(ms.value)
+    return batch
+
+
+# ---------------------------------------------------------------------------------------------
+def _mulmod(a, b):
+    """elementwise a * b mod p on uint64 arrays (python ints under the hood: host-side test data only)."""
+    return np.array([(int(x) * int(y)) % P for x, y in zip(np.ravel(a), np.ravel(b))], dtype=np.uint64).reshape(np.shape(a))
+
+
+@dataclass
+class SyntheticCircuit:
+    circuit: CircuitDescription
+    constants: np.ndarray       # (num_constants, n): selector column, then const_0, const_1
+    sigmas: np.ndarray          # (num_routed_wires, n): sigma_j(omega^r) = k_j' omega^r'
+    wires: np.ndarray           # (num_wires, n): a witness that satisfies every gate and every copy constraint
+    public_inputs_hash: np.ndarray
+
+
+def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_routed_wires=80, num_ops=20,
+                      quotient_degree_factor=8, rate_bits=3, num_challenges=2):
+    """A circuit of NoopGate / ConstantGate / PublicInputGate / ArithmeticGate rows (one selector group) with random
+    constants, `n_copies` copy constraints between free arithmetic inputs, and a witness that satisfies all of it."""
+    n = 1 << degree_bits
+    rng = np.random.default_rng(seed)
+    gates = [Gate(GATE_NOOP, 0, 0, 0, 0, 4), Gate(GATE_CONSTANT, 2, 1, 0, 0, 4), Gate(GATE_PUBLIC_INPUT, 0, 2, 0, 0, 4),
+             Gate(GATE_ARITHMETIC, num_ops, 3, 0, 0, 4)]
+    circ = CircuitDescription(degree_bits, gates, rate_bits=rate_bits, quotient_degree_factor=quotient_degree_factor,
+                              num_challenges=num_challenges, num_wires=num_wires, num_routed_wires=num_routed_wires)
+    sel = np.full(n, 3, dtype=np.uint64)          # arithmetic rows ...
+    sel[0] = 2                                    # ... one public-input row,
+    n_const = max(1, n // 16) if n > 2 else 0
+    sel[1:1 + n_const] = 1                        # some constant rows,
+    if n > 4:
+        sel[n - max(1, n // 32):] = 0             # and padding rows at the end
+    rand = lambda shape: rng.integers(0, P, size=shape, dtype=np.uint64)
+    constants = np.stack([sel, rand(n), rand(n)])
+    wires = rand((num_wires, n))
+    pih = rand(4)
+    # copy constraints: disjoint pairs of free cells (multiplicands / addends of arithmetic rows)
+    arith_rows = np.nonzero(sel == 3)[0]
+    free = [(4 * i + t, r) for r in arith_rows[: 4096] for i in range(num_ops) for t in range(3)]
+    if n_copies is None:
+        n_copies = min(len(free) // 2, 4 * n)
+    pick = rng.permutation(len(free))[: 2 * n_copies]
+    ident = np.arange(num_routed_wires * n, dtype=np.int64).reshape(num_routed_wires, n)
+    perm = ident.copy()
+    for a, b in zip(pick[0::2], pick[1::2]):
+        (ja, ra), (jb, rb) = free[a], free[b]
+        wires[jb, rb] = wires[ja, ra]
+        perm[ja, ra], perm[jb, rb] = ident[jb, rb], ident[ja, ra]
+    # satisfy the gates
+    w = pow(1753635133440165772, 1 << (32 - degree_bits), P)  # plonky2 primitive_root_of_unity(degree_bits)
+    c_rows = np.nonzero(sel == 1)[0]
+    wires[0, c_rows], wires[1, c_rows] = constants[1, c_rows], constants[2, c_rows]
+    wires[0:4, 0] = pih
+    for i in range(num_ops):
+        m = _mulmod(_mulmod(wires[4 * i, arith_rows], wires[4 * i + 1, arith_rows]), constants[1, arith_rows])
+        a = _mulmod(wires[4 * i + 2, arith_rows], constants[2, arith_rows])
+        wires[4 * i + 3, arith_rows] = np.array([(int(x) + int(y)) % P for x, y in zip(m, a)], dtype=np.uint64)
+    # sigma polynomials' values: cell (j', r') -> k_j' * omega^r'
+    omegas = np.empty(n, dtype=object)
+    acc = 1
+    for r in range(n):
+        omegas[r] = acc
+        acc = acc * w % P
+    k = [int(x) for x in circ.k_is]
+    sig = np.empty((num_routed_wires, n), dtype=np.uint64)
+    flat = perm.reshape(-1)
+    jj, rr = flat // n, flat % n
+    sig.reshape(-1)[:] = np.array([k[j] * omegas[r] % P for j, r in zip(jj, rr)], dtype=np.uint64)
+    return SyntheticCircuit(circ, constants, sig, wires, pih)

@@ -344,6 +344,45 @@ int32_t bsx_partial_products_and_zs(bsx_ctx *ctx, const uint64_t *wires, const u
                                     const uint64_t *betas_host, const uint64_t *gammas_host, int32_t n_challenges,
                                     uint64_t *out, int32_t out_mem);
 
+/* ---- quotient evaluation on the device (plonk/prover.rs compute_quotient_polys) ------------------------------
+ * The circuit as compute_quotient_polys and plonk/vanishing_poly.rs eval_vanishing_poly_base_batch read it from
+ * CommonCircuitData / CircuitConfig.  Gates are data, not code: a table of (kind, parameter, selector info); the four
+ * kinds below are built in (gates/noop.rs, constant.rs, public_input.rs, arithmetic_base.rs).  `row` is the gate's index
+ * in common_data.gates (the value its selector polynomial takes on rows that use it), selector_index / group_* are
+ * selectors_info.selector_indices[row] and selectors_info.groups[selector_index]. */
+#define BSX_GATE_NOOP 0
+#define BSX_GATE_CONSTANT 1     /* param = num_consts: constants[i] - wires[i] */
+#define BSX_GATE_PUBLIC_INPUT 2 /* wires[i] - public_inputs_hash[i], i < 4 */
+#define BSX_GATE_ARITHMETIC 3   /* param = num_ops: wires[4i+3] - (wires[4i] wires[4i+1] const_0 + wires[4i+2] const_1) */
+typedef struct bsx_gate {
+    int32_t kind, param, row, selector_index, group_start, group_end;
+} bsx_gate;
+typedef struct bsx_circuit {
+    int32_t degree_bits, rate_bits, quotient_degree_factor, num_challenges;
+    int32_t num_wires, num_routed_wires;
+    int32_t num_constants; /* common_data.num_constants: selector columns first, then the gates' constants */
+    int32_t num_selectors;
+    int32_t num_partial_products, num_gate_constraints, n_gates;
+    const bsx_gate *gates;  /* host */
+    const uint64_t *k_is;   /* host, num_routed_wires */
+} bsx_circuit;
+/* The quotient's values on the coset 7 <omega_{N 2^q}> (q = log2_ceil(quotient_degree_factor)) before coset_ifft:
+ * out[a][i], a < num_challenges, natural order -- `quotient_values` of compute_quotient_polys, transposed.  The three
+ * commitments stay in HBM: constants_sigmas (num_constants + num_routed_wires polynomials), wires (num_wires), Zs and
+ * partial products (num_challenges * (1 + num_partial_products), Zs first), all of 2^degree_bits rows at rate_bits. */
+int32_t bsx_quotient_values(bsx_ctx *ctx, const bsx_circuit *circuit, bsx_batch *constants_sigmas, bsx_batch *wires,
+                            bsx_batch *zs_partial_products, const uint64_t *public_inputs_hash /* 4, host */,
+                            const uint64_t *betas, const uint64_t *gammas, const uint64_t *alphas /* host */,
+                            uint64_t *out, int32_t out_mem);
+/* compute_quotient_polys and the quotient commitment of prove() in one call: the values above, coset_ifft,
+ * trim_to_len(quotient_degree_factor * N) (fails where upstream panics "Quotient has failed"), chunks of N,
+ * PolynomialBatch::from_coeffs.  eval_ms (optional): device milliseconds of the evaluation kernel alone. */
+int32_t bsx_compute_quotient_polys(bsx_ctx *ctx, const bsx_circuit *circuit, bsx_batch *constants_sigmas, bsx_batch *wires,
+                                   bsx_batch *zs_partial_products, const uint64_t *public_inputs_hash,
+                                   const uint64_t *betas, const uint64_t *gammas, const uint64_t *alphas,
+                                   int32_t cap_height, int32_t blinding, bsx_batch **out, bsx_timing *timing,
+                                   float *eval_ms);
+
 /* ---- test hooks -----------------------------------------------------------------------------
  * Poseidon::poseidon on n states (n x 12 words, in place). */
 int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n);

@@ -406,6 +406,32 @@ def quotient_values(circuit, constants_sigmas, wires, zs_partial_products, publi
     return out
 
 
+def vanishing_at(circuit, x, constants_sigmas_row, wires_row, zs_pp_row, next_zs_row, public_inputs_hash, betas, gammas,
+                 alphas):
+    """The reduced vanishing polynomial(s) at base-field point x from the committed polynomials' values at x (and the
+    Zs at g x): what plonky2's verifier computes from the opening set."""
+    c, keep = _circuit(circuit)
+    rows = [_a(r) for r in (constants_sigmas_row, wires_row, zs_pp_row, next_zs_row)]
+    pih, b, g, al = _a(public_inputs_hash), _a(betas), _a(gammas), _a(alphas)
+    out = np.zeros(circuit["num_challenges"], dtype=np.uint64)
+    rc = lib().orc_vanishing_at(C.byref(c), C.c_uint64(int(x)), _ptr(rows[0]), _ptr(rows[1]), _ptr(rows[2]), _ptr(rows[3]),
+                                _ptr(pih), _ptr(b), _ptr(g), _ptr(al), _ptr(out))
+    if rc != 0:
+        raise ValueError("orc_vanishing_at failed")
+    return out
+
+
+def eval_polys_base(coeffs, x):
+    """coeffs (k, n) -> values at the base-field point x (Horner on python ints; small test sizes only)."""
+    out = []
+    for c in _a(coeffs):
+        acc = 0
+        for v in c[::-1]:
+            acc = (acc * int(x) + int(v)) % P
+        out.append(acc)
+    return np.array(out, dtype=np.uint64)
+
+
 def write_proof_with_public_inputs(wires_cap, zs_cap, quotient_cap, openings, fri_words, degree_bits, rate_bits,
                                    cap_height, pow_bits, num_queries, arity_bits, widths, public_inputs):
     """`ProofWithPublicInputs::to_bytes`; openings = the seven OpeningSet vectors, each (n, 2)."""

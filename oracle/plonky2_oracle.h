@@ -168,6 +168,11 @@ int orc_gate_num_constraints(const orc_gate *g);
 int orc_quotient_values(const orc_circuit *c, const orc_batch_view *constants_sigmas, const orc_batch_view *wires_b,
                         const orc_batch_view *zs_b, const uint64_t public_inputs_hash[4], const uint64_t *betas,
                         const uint64_t *gammas, const uint64_t *alphas, uint64_t *out);
+/* the vanishing polynomial at a base-field point from the polynomials' values there (verifier side: V(x) must equal
+ * Z_H(x) * sum_i x^(n i) quotient_chunk_i(x)); res[num_challenges] */
+int orc_vanishing_at(const orc_circuit *c, uint64_t x, const uint64_t *constants_sigmas_row, const uint64_t *wires_row,
+                     const uint64_t *zs_pp_row, const uint64_t *next_zs_row, const uint64_t pi_hash[4],
+                     const uint64_t *betas, const uint64_t *gammas, const uint64_t *alphas, uint64_t *res);
 /* util/serialization write_proof_with_public_inputs over the flat FriProof stream; returns the byte count */
 size_t orc_write_proof_with_public_inputs(const uint64_t *wires_cap, const uint64_t *zs_cap, const uint64_t *quotient_cap,
                                           const uint64_t *const openings[7], const int n_openings[7],

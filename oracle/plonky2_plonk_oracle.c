@@ -93,6 +93,79 @@ int orc_gate_num_constraints(const orc_gate *g) {
     }
 }
 
+/* plonk/vanishing_poly.rs eval_vanishing_poly_base_batch for ONE point: the vanishing terms in upstream's order
+ * (vanishing_z_1_terms, vanishing_partial_products_terms, gate constraint terms) reduced with the powers of every
+ * alpha (plonk_common.rs reduce_with_powers_multi).  l_0_x = L_0 at the point.  terms / gate_out: scratch of
+ * n_terms + 1 and num_gate_constraints + 4 words.  Returns -1 on a gate that does not fit the description. */
+static int vanishing_at_point(const orc_circuit *c, uint64_t x, uint64_t l_0_x, const uint64_t *local_constants,
+                              const uint64_t *s_sigmas, const uint64_t *local_wires, const uint64_t *local_zs_pp,
+                              const uint64_t *next_zs, const uint64_t pi_hash[4], const uint64_t *betas,
+                              const uint64_t *gammas, const uint64_t *alphas, uint64_t *terms, uint64_t *gate_out,
+                              uint64_t *res) {
+    const int nc = c->num_challenges, max_degree = c->quotient_degree_factor, num_prods = c->num_partial_products;
+    const int n_chunks = num_prods + 1;
+    const uint64_t *partial_products = local_zs_pp + nc; /* partial_products_range */
+    int t = 0, bad = 0;
+    /* vanishing_z_1_terms */
+    for (int k = 0; k < nc; k++) terms[t++] = orc_mul(l_0_x, orc_sub(local_zs_pp[k], 1));
+    /* vanishing_partial_products_terms: check_partial_products per challenge */
+    for (int k = 0; k < nc; k++) {
+        const uint64_t z_x = local_zs_pp[k], z_gx = next_zs[k];
+        const uint64_t *pp = partial_products + (size_t)k * num_prods;
+        for (int m = 0; m < n_chunks; m++) {
+            uint64_t num = 1, den = 1;
+            for (int j = m * max_degree; j < c->num_routed_wires && j < (m + 1) * max_degree; j++) {
+                const uint64_t wv = local_wires[j], s_id = orc_mul(c->k_is[j] % P, x);
+                num = orc_mul(num, orc_add(orc_add(wv, orc_mul(betas[k], s_id)), gammas[k]));
+                den = orc_mul(den, orc_add(orc_add(wv, orc_mul(betas[k], s_sigmas[j])), gammas[k]));
+            }
+            const uint64_t prev_acc = m == 0 ? z_x : pp[m - 1], next_acc = m == n_chunks - 1 ? z_gx : pp[m];
+            terms[t++] = orc_sub(orc_mul(prev_acc, num), orc_mul(next_acc, den));
+        }
+    }
+    /* evaluate_gate_constraints_base_batch: filtered constraints of every gate summed per slot */
+    uint64_t *cons = terms + t;
+    for (int j = 0; j < c->num_gate_constraints; j++) cons[j] = 0;
+    for (int gi = 0; gi < c->n_gates; gi++) {
+        const orc_gate *g = &c->gates[gi];
+        const uint64_t filter = compute_filter(g->row, g->group_start, g->group_end, local_constants[g->selector_index],
+                                               c->num_selectors > 1);
+        int k = gate_eval_unfiltered(g, local_constants + c->num_selectors, local_wires, pi_hash, gate_out);
+        if (k < 0 || k > c->num_gate_constraints) { bad = 1; k = 0; }
+        for (int j = 0; j < k; j++) cons[j] = orc_add(cons[j], orc_mul(filter, gate_out[j]));
+    }
+    t += c->num_gate_constraints;
+    for (int a = 0; a < nc; a++) { /* reduce_with_powers_multi */
+        uint64_t acc = 0;
+        for (int j = t - 1; j >= 0; j--) acc = orc_add(terms[j], orc_mul(acc, alphas[a]));
+        res[a] = acc;
+    }
+    return bad ? -1 : 0;
+}
+
+static int circuit_terms(const orc_circuit *c) {
+    return c->num_challenges * (2 + c->num_partial_products) + c->num_gate_constraints;
+}
+
+/* The vanishing polynomial at an arbitrary base-field point x from the polynomials' values there (what the verifier
+ * does with the opening set, plonk/vanishing_poly.rs eval_vanishing_poly): Z_H(x) = x^n - 1,
+ * L_0(x) = (x^n - 1) / (n (x - 1)).  rows: constants then sigmas | wires | zs then partial products | zs at g x. */
+int orc_vanishing_at(const orc_circuit *c, uint64_t x, const uint64_t *constants_sigmas_row, const uint64_t *wires_row,
+                     const uint64_t *zs_pp_row, const uint64_t *next_zs_row, const uint64_t pi_hash[4],
+                     const uint64_t *betas, const uint64_t *gammas, const uint64_t *alphas, uint64_t *res) {
+    uint64_t xn = x % P;
+    for (int i = 0; i < c->degree_bits; i++) xn = orc_mul(xn, xn);
+    const uint64_t z_h = orc_sub(xn, 1), n = orc_pow(2, (uint64_t)c->degree_bits);
+    const uint64_t l_0_x = orc_mul(z_h, orc_inv(orc_mul(n, orc_sub(x % P, 1))));
+    uint64_t *terms = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(circuit_terms(c) + 1));
+    uint64_t *gate_out = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(c->num_gate_constraints + 4));
+    int rc = vanishing_at_point(c, x % P, l_0_x, constants_sigmas_row, constants_sigmas_row + c->num_constants, wires_row,
+                                zs_pp_row, next_zs_row, pi_hash, betas, gammas, alphas, terms, gate_out, res);
+    free(terms);
+    free(gate_out);
+    return rc;
+}
+
 /* plonk/prover.rs compute_quotient_polys up to (not including) the final coset_ifft:
  * out[a * lde_size + i] = quotient value of challenge alpha_a at point i of the coset 7 * <omega_{n 2^q}>. */
 int orc_quotient_values(const orc_circuit *c, const orc_batch_view *constants_sigmas, const orc_batch_view *wires_b,
@@ -113,59 +186,29 @@ int orc_quotient_values(const orc_circuit *c, const orc_batch_view *constants_si
     zero_poly_on_coset zh;
     zpoc_new(&zh, c->degree_bits, qdb);
     const uint64_t w = orc_root_of_unity(c->degree_bits + qdb);
-    const int n_terms = nc + nc * n_chunks + c->num_gate_constraints;
     int bad = 0;
 #pragma omp parallel
     {
-        uint64_t *terms = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(n_terms + 1));
+        uint64_t *terms = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(circuit_terms(c) + 1));
         uint64_t *gate_out = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(c->num_gate_constraints + 4));
+        uint64_t res[64];
 #pragma omp for schedule(static)
         for (size_t i = 0; i < lde_size; i++) {
             const uint64_t x = orc_pow(w, i), shifted_x = orc_mul(7, x);
             const size_t i_next = (i + next_step) % lde_size;
             const uint64_t *local_cs = lde_row(constants_sigmas, i, step);
-            const uint64_t *local_constants = local_cs, *s_sigmas = local_cs + c->num_constants;
             const uint64_t *local_wires = lde_row(wires_b, i, step);
             const uint64_t *local_zs_pp = lde_row(zs_b, i, step), *next_zs_pp = lde_row(zs_b, i_next, step);
-            const uint64_t *partial_products = local_zs_pp + nc; /* partial_products_range */
-            int t = 0;
-            /* vanishing_z_1_terms */
             const uint64_t l_0_x = zpoc_eval_l_0(&zh, i, shifted_x);
-            for (int k = 0; k < nc; k++) terms[t++] = orc_mul(l_0_x, orc_sub(local_zs_pp[k], 1));
-            /* vanishing_partial_products_terms: check_partial_products per challenge */
-            for (int k = 0; k < nc; k++) {
-                const uint64_t z_x = local_zs_pp[k], z_gx = next_zs_pp[k];
-                const uint64_t *pp = partial_products + (size_t)k * num_prods;
-                for (int m = 0; m < n_chunks; m++) {
-                    uint64_t num = 1, den = 1;
-                    for (int j = m * max_degree; j < c->num_routed_wires && j < (m + 1) * max_degree; j++) {
-                        const uint64_t wv = local_wires[j], s_id = orc_mul(c->k_is[j] % P, shifted_x);
-                        num = orc_mul(num, orc_add(orc_add(wv, orc_mul(betas[k], s_id)), gammas[k]));
-                        den = orc_mul(den, orc_add(orc_add(wv, orc_mul(betas[k], s_sigmas[j])), gammas[k]));
-                    }
-                    const uint64_t prev_acc = m == 0 ? z_x : pp[m - 1], next_acc = m == n_chunks - 1 ? z_gx : pp[m];
-                    terms[t++] = orc_sub(orc_mul(prev_acc, num), orc_mul(next_acc, den));
-                }
+            if (nc > 64 || vanishing_at_point(c, shifted_x, l_0_x, local_cs, local_cs + c->num_constants, local_wires,
+                                              local_zs_pp, next_zs_pp, public_inputs_hash, betas, gammas, alphas, terms,
+                                              gate_out, res) != 0) {
+                bad = 1;
+                continue;
             }
-            /* evaluate_gate_constraints_base_batch: filtered constraints of every gate summed per slot */
-            uint64_t *cons = terms + t;
-            for (int j = 0; j < c->num_gate_constraints; j++) cons[j] = 0;
-            for (int gi = 0; gi < c->n_gates; gi++) {
-                const orc_gate *g = &c->gates[gi];
-                const uint64_t filter = compute_filter(g->row, g->group_start, g->group_end,
-                                                       local_constants[g->selector_index], c->num_selectors > 1);
-                int k = gate_eval_unfiltered(g, local_constants + c->num_selectors, local_wires, public_inputs_hash, gate_out);
-                if (k < 0 || k > c->num_gate_constraints) { bad = 1; k = 0; }
-                for (int j = 0; j < k; j++) cons[j] = orc_add(cons[j], orc_mul(filter, gate_out[j]));
-            }
-            t += c->num_gate_constraints;
-            /* reduce_with_powers_multi(terms, alphas), then * z_h_on_coset.eval_inverse(i) */
+            /* quotient_values *= z_h_on_coset.eval_inverse(i) */
             const uint64_t denominator_inv = zh.inverses[i % zh.rate];
-            for (int a = 0; a < nc; a++) {
-                uint64_t acc = 0;
-                for (int j = t - 1; j >= 0; j--) acc = orc_add(terms[j], orc_mul(acc, alphas[a]));
-                out[(size_t)a * lde_size + i] = orc_mul(acc, denominator_inv);
-            }
+            for (int a = 0; a < nc; a++) out[(size_t)a * lde_size + i] = orc_mul(res[a], denominator_inv);
         }
         free(terms);
         free(gate_out);
