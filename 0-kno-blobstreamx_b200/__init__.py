@@ -59,6 +59,9 @@ from .plonk import (  # noqa: F401
     synthetic_circuit,
 )
 from .parallel import (  # noqa: F401
+    Comm,
+    CommShardedBatch,
+    comm_prove_openings,
     ShardPlan,
     ShardedPolynomialBatch,
     assemble_cap,

@@ -11,7 +11,7 @@ _SO = os.path.join(_DIR, "csrc", "libbsx_b200.so")
 # every symbol include/bsx_b200.h declares (checked by tests/test_abi.py against the header text)
 EXPORTED_SYMBOLS = [
     "bsx_version", "bsx_device_count", "bsx_launch_count", "bsx_ctx_create", "bsx_ctx_destroy", "bsx_last_error", "bsx_ctx_stream",
-    "bsx_ctx_sync", "bsx_ctx_mem_used", "bsx_batch_from_values", "bsx_batch_from_coeffs",
+    "bsx_ctx_sync", "bsx_ctx_mem_used", "bsx_ctx_trim", "bsx_batch_from_values", "bsx_batch_from_coeffs",
     "bsx_batch_from_values_cols", "bsx_batch_from_coeffs_cols", "bsx_batch_from_quotient_values", "bsx_partial_products_and_zs", "bsx_batch_free", "bsx_batch_cap",
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
@@ -24,6 +24,9 @@ EXPORTED_SYMBOLS = [
     "bsx_shard_set_peer_ipc", "bsx_shard_set_peer_ptr", "bsx_shard_transform", "bsx_shard_commit", "bsx_shard_coeffs",
     "bsx_fri_proof_layout", "bsx_fri_proof_bytes", "bsx_proof_with_public_inputs_bytes",
     "bsx_quotient_values", "bsx_compute_quotient_polys",
+    "bsx_comm_create", "bsx_comm_destroy", "bsx_comm_size", "bsx_comm_ctx", "bsx_comm_last_error",
+    "bsx_sharded_from_values", "bsx_sharded_from_values_parts", "bsx_sharded_free", "bsx_sharded_cap", "bsx_sharded_get",
+    "bsx_sharded_prove", "bsx_sharded_proof_len", "bsx_sharded_shard", "bsx_sharded_tree", "bsx_sharded_prove_openings",
 ]
 
 
@@ -67,6 +70,7 @@ def lib():
         "bsx_ctx_stream": (vp, [vp]),
         "bsx_ctx_sync": (i32, [vp]),
         "bsx_ctx_mem_used": (i32, [vp, C.POINTER(C.c_uint64)]),
+        "bsx_ctx_trim": (i32, [vp]),
         "bsx_batch_from_values": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_from_coeffs": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
         "bsx_batch_from_values_cols": (i32, [vp, vp, i32, i32, i32, i32, i32, vp, pp, C.POINTER(Timing)]),
@@ -181,6 +185,10 @@ class Context:
 
     def sync(self):
         self.check(lib().bsx_ctx_sync(self._h))
+
+    def trim(self):
+        """Give the large buffers the context keeps for reuse back to the device."""
+        self.check(lib().bsx_ctx_trim(self._h))
 
     def close(self):
         if self._h is not None:

@@ -20,22 +20,61 @@ int bsx_fail(bsx_ctx *ctx, int code, const char *fmt, ...) {
     return code;
 }
 
+// Buffers of BSX_BIG_BLOCK_BYTES and more (coefficients, LDEs, digest levels, transform scratch) are recycled by
+// EXACT size through a per-context cache instead of going back to the stream-ordered pool: a prover commits the same
+// shapes proof after proof, and a 9 GB request that finds its old block split by smaller allocations makes the pool
+// map new physical memory (tens to hundreds of ms).  Reuse is ordered by ctx->stream like cudaFreeAsync / cudaMallocAsync
+// on that stream would be.  The cache is dropped when an allocation fails (and on bsx_ctx_trim / destroy).
+#define BSX_BIG_BLOCK_BYTES ((size_t)64 << 20)
+void bsx_ctx_drop_cache(bsx_ctx *ctx) {
+    for (auto &e : ctx->big_cache) cudaFreeAsync(e.first, ctx->stream);
+    ctx->big_cache.clear();
+    ctx->big_cache_bytes = 0;
+}
 int bsx_alloc_owned(bsx_ctx *ctx, u64 **p, size_t words) {
     *p = nullptr;
     if (words == 0) return BSX_OK;
-    cudaError_t e = cudaMallocAsync((void **)p, words * sizeof(u64), ctx->stream);
+    const size_t bytes = words * sizeof(u64);
+    if (bytes >= BSX_BIG_BLOCK_BYTES) {
+        for (size_t i = ctx->big_cache.size(); i-- > 0;)
+            if (ctx->big_cache[i].second == bytes) {
+                *p = ctx->big_cache[i].first;
+                ctx->big_cache.erase(ctx->big_cache.begin() + (long)i);
+                ctx->big_cache_bytes -= bytes;
+                ctx->big_live[*p] = bytes;
+                return BSX_OK;
+            }
+    }
+    cudaError_t e = cudaMallocAsync((void **)p, bytes, ctx->stream);
+    if (e == cudaErrorMemoryAllocation && !ctx->big_cache.empty()) {  // give the cached blocks back and try again
+        cudaGetLastError();
+        bsx_ctx_drop_cache(ctx);
+        cudaStreamSynchronize(ctx->stream);
+        e = cudaMallocAsync((void **)p, bytes, ctx->stream);
+    }
     if (e != cudaSuccess) {
         cudaGetLastError();
         *p = nullptr;
         return bsx_fail(ctx, e == cudaErrorMemoryAllocation ? BSX_ERR_OOM : BSX_ERR_CUDA,
-                        "device allocation of %zu bytes failed: %s", words * sizeof(u64), cudaGetErrorString(e));
+                        "device allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
     }
+    if (bytes >= BSX_BIG_BLOCK_BYTES) ctx->big_live[*p] = bytes;
     return BSX_OK;
 }
 int bsx_alloc(bsx_ctx *ctx, u64 **p, size_t words) {
     TRY(bsx_alloc_owned(ctx, p, words));
     if (*p && ctx->scope_depth > 0) ctx->scratch.emplace_back(*p, ctx->scratch_seq++);
     return BSX_OK;
+}
+static void release_block(bsx_ctx *ctx, u64 *p) {
+    auto it = ctx->big_live.find(p);
+    if (it == ctx->big_live.end()) {
+        cudaFreeAsync(p, ctx->stream);
+        return;
+    }
+    ctx->big_cache.emplace_back(p, it->second);
+    ctx->big_cache_bytes += it->second;
+    ctx->big_live.erase(it);
 }
 void bsx_free(bsx_ctx *ctx, u64 *p) {
     if (!p) return;
@@ -44,14 +83,14 @@ void bsx_free(bsx_ctx *ctx, u64 *p) {
             ctx->scratch.erase(ctx->scratch.begin() + (long)i);
             break;
         }
-    cudaFreeAsync(p, ctx->stream);
+    release_block(ctx, p);
 }
 // stream-ordered frees: everything the call enqueued before this point has the buffers it needs
 BsxScope::~BsxScope() {
     if (!ctx) return;
     for (size_t i = ctx->scratch.size(); i-- > 0;)
         if (ctx->scratch[i].second >= first) {
-            cudaFreeAsync(ctx->scratch[i].first, ctx->stream);
+            release_block(ctx, ctx->scratch[i].first);
             ctx->scratch.erase(ctx->scratch.begin() + (long)i);
         }
     ctx->scope_depth--;
@@ -229,6 +268,7 @@ extern "C" void bsx_ctx_destroy(bsx_ctx *ctx) {
         bsx_free(ctx, (u64 *)kv.second.first);
         bsx_free(ctx, (u64 *)kv.second.second);
     }
+    bsx_ctx_drop_cache(ctx);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->stage_ring) cudaFreeHost(ctx->stage_ring);
     for (auto &e : ctx->stage_done)
@@ -249,7 +289,14 @@ extern "C" int32_t bsx_ctx_mem_used(bsx_ctx *ctx, uint64_t *bytes) {
     CU(ctx, cudaDeviceGetDefaultMemPool(&pool, ctx->device));
     unsigned long long used = 0;
     CU(ctx, cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used));
-    *bytes = used;
+    *bytes = used - ctx->big_cache_bytes;  // blocks parked for reuse are not in use
+    return BSX_OK;
+}
+extern "C" int32_t bsx_ctx_trim(bsx_ctx *ctx) {
+    if (!ctx) return BSX_ERR_INVALID_ARG;
+    CU(ctx, cudaSetDevice(ctx->device));
+    bsx_ctx_drop_cache(ctx);
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
     return BSX_OK;
 }
 extern "C" int32_t bsx_ctx_sync(bsx_ctx *ctx) {

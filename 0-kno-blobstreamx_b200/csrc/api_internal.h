@@ -37,6 +37,10 @@ struct bsx_ctx {
     u64 *stage_ring = nullptr;
     size_t stage_slot_words = 0;
     cudaEvent_t stage_done[BSX_STAGE_SLOTS] = {};
+    // exact-size recycling of large device buffers (api.cu bsx_alloc_owned)
+    std::map<u64 *, size_t> big_live;
+    std::vector<std::pair<u64 *, size_t>> big_cache;
+    size_t big_cache_bytes = 0;
 };
 
 // plonky2 hash/merkle_tree.rs MerkleTree { leaves, digests, cap }, device resident.
@@ -69,6 +73,7 @@ int bsx_fail(bsx_ctx *ctx, int code, const char *fmt, ...);
 int bsx_alloc(bsx_ctx *ctx, u64 **p, size_t words);
 int bsx_alloc_owned(bsx_ctx *ctx, u64 **p, size_t words);
 void bsx_free(bsx_ctx *ctx, u64 *p);
+void bsx_ctx_drop_cache(bsx_ctx *ctx);
 struct BsxScope {
     bsx_ctx *ctx;
     unsigned long long first;

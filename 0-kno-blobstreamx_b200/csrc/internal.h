@@ -10,7 +10,8 @@ typedef unsigned int u32;
 
 // process-wide count of kernel launches issued by this library (bench.py reports it)
 extern unsigned long long g_bsx_launches;
-#define BSX_COUNT_LAUNCH() (++g_bsx_launches)
+// relaxed atomic: several host threads (one per rank of a bsx_comm) launch concurrently
+#define BSX_COUNT_LAUNCH() ((void)__atomic_fetch_add(&g_bsx_launches, 1ULL, __ATOMIC_RELAXED))
 
 // ---------------------------------------------------------------- hashing / Merkle
 // Leaves are COLUMN-major on device: element (row, col) at data[col * col_stride + row].

@@ -414,3 +414,117 @@ def sharded_prove_openings(instance, sbatches, challenger, fri_params, gather=No
     c = fri_params.config
     return splice_initial_openings(fri_words, openings, fri_params.degree_bits, c.rate_bits, c.cap_height,
                                    list(fri_params.reduction_arity_bits), c.num_query_rounds)
+
+
+# ---------------------------------------------------------------------------------------------
+# one process driving G devices through the C ABI (bsx_comm_create / bsx_sharded_*): what the Rust shim would call
+class Comm:
+    """`bsx_comm`: one context per rank; `devices` may repeat a device (emulated ranks share it)."""
+
+    def __init__(self, devices):
+        L = _declare_comm()
+        devs = np.ascontiguousarray(devices, dtype=np.int32)
+        h = C.c_void_p()
+        rc = L.bsx_comm_create(int(devs.size), C.c_void_p(devs.ctypes.data), C.byref(h))
+        if rc != 0:
+            raise BsxError("bsx_comm_create(%r) failed with %d" % (list(devices), rc))
+        self._h, self.size = h, int(devs.size)
+
+    def check(self, rc):
+        if rc != 0:
+            raise BsxError("%s (code %d)" % (lib().bsx_comm_last_error(self._h).decode(), rc))
+
+    def close(self):
+        if self._h is not None:
+            lib().bsx_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class CommShardedBatch:
+    """`bsx_sharded_batch`: one PolynomialBatch spread over the ranks of a Comm; indices are global."""
+
+    def __init__(self, comm, handle, shape, timing=None):
+        self.comm, self._h, self.shape, self.timing = comm, handle, shape, timing
+
+    @classmethod
+    def from_values(cls, comm, values, rate_bits, cap_height, is_coeffs=False, timing=False):
+        L = _declare_comm()
+        v = _np(values)
+        n_cols, n = v.shape
+        h = C.c_void_p()
+        t = Timing() if timing else None
+        comm.check(L.bsx_sharded_from_values(comm._h, _ptr(v), _log2_strict(n), int(n_cols), int(rate_bits),
+                                             int(cap_height), 1 if is_coeffs else 0, C.byref(h),
+                                             C.byref(t) if t is not None else None))
+        return cls(comm, h, (int(n_cols), _log2_strict(n), int(rate_bits), int(cap_height)), t)
+
+    @property
+    def cap(self):
+        out = np.zeros((1 << self.shape[3], 4), dtype=np.uint64)
+        self.comm.check(lib().bsx_sharded_cap(self._h, _ptr(out)))
+        return out
+
+    def get(self, leaves):
+        idx = _np(np.atleast_1d(leaves))
+        out = np.zeros((idx.size, self.shape[0]), dtype=np.uint64)
+        self.comm.check(lib().bsx_sharded_get(self._h, _ptr(idx), int(idx.size), _ptr(out)))
+        return out[0] if np.isscalar(leaves) else out
+
+    def prove(self, leaf):
+        out = np.zeros((lib().bsx_sharded_proof_len(self._h), 4), dtype=np.uint64)
+        self.comm.check(lib().bsx_sharded_prove(self._h, C.c_uint64(int(leaf)), _ptr(out)))
+        return out
+
+    def close(self):
+        if self._h is not None:
+            lib().bsx_sharded_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def comm_prove_openings(comm, instance, oracles, challenger, fri_params):
+    """`PolynomialBatch::prove_openings` over CommShardedBatch oracles (bsx_sharded_prove_openings)."""
+    from .fri import _params_struct
+    from .proof import fri_proof_layout
+    L = _declare_comm()
+    p = _params_struct(fri_params)
+    words = fri_proof_layout(fri_params, [o.shape[0] for o in oracles]).total_words
+    proof = np.zeros(words, dtype=np.uint64)
+    hs = (C.c_void_p * len(oracles))(*[o._h for o in oracles])
+    comm.check(L.bsx_sharded_prove_openings(comm._h, hs, len(oracles), C.byref(instance.struct), C.byref(challenger._s),
+                                            C.byref(p), _ptr(proof)))
+    return proof
+
+
+def _declare_comm():
+    L = lib()
+    if getattr(L, "_bsx_comm_declared", False):
+        return L
+    vp, i32, u64 = C.c_void_p, C.c_int32, C.c_uint64
+    pp = C.POINTER(C.c_void_p)
+    sig = {
+        "bsx_comm_create": (i32, [i32, vp, pp]), "bsx_comm_destroy": (None, [vp]), "bsx_comm_size": (i32, [vp]),
+        "bsx_comm_ctx": (vp, [vp, i32]), "bsx_comm_last_error": (C.c_char_p, [vp]),
+        "bsx_sharded_from_values": (i32, [vp, vp, i32, i32, i32, i32, i32, pp, C.POINTER(Timing)]),
+        "bsx_sharded_from_values_parts": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, pp, C.POINTER(Timing)]),
+        "bsx_sharded_free": (None, [vp]), "bsx_sharded_cap": (i32, [vp, vp]), "bsx_sharded_get": (i32, [vp, vp, i32, vp]),
+        "bsx_sharded_prove": (i32, [vp, u64, vp]), "bsx_sharded_proof_len": (i32, [vp]),
+        "bsx_sharded_shard": (vp, [vp, i32]), "bsx_sharded_tree": (vp, [vp, i32]),
+        "bsx_sharded_prove_openings": (i32, [vp, vp, i32, vp, vp, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    L._bsx_comm_declared = True
+    return L

@@ -36,6 +36,7 @@ extern "C" {
 #define BSX_DEVICE 1
 
 #define BSX_SALT_SIZE 4 /* plonky2 plonk/plonk_common.rs SALT_SIZE */
+#define BSX_MAX_ORACLES 16 /* oracles per prove_openings call */
 
 typedef struct bsx_ctx bsx_ctx;
 typedef struct bsx_tree bsx_tree;   /* plonky2 hash/merkle_tree.rs MerkleTree<F, PoseidonHash> */
@@ -66,6 +67,10 @@ int32_t bsx_ctx_sync(bsx_ctx *ctx);
 /* Device memory currently handed out by the stream-ordered pool the library allocates from (bytes; batches,
  * trees, cached tables).  A failed call leaves this unchanged: its temporaries are released on every path. */
 int32_t bsx_ctx_mem_used(bsx_ctx *ctx, uint64_t *bytes);
+/* Large buffers (>= 64 MiB) released by batches and calls are kept by the context and reused by exact size, so that a
+ * prover committing the same shapes proof after proof never waits for the allocator; bsx_ctx_trim gives them back to
+ * the device (they are also given back automatically when an allocation would otherwise fail). */
+int32_t bsx_ctx_trim(bsx_ctx *ctx);
 
 /* ---- PolynomialBatch (fri/oracle.rs) ------------------------------------------------------
  * from_values: values = n_cols column vectors of 2^log_n evaluations on the subgroup, column-major
@@ -184,6 +189,39 @@ int32_t bsx_shard_commit(bsx_shard *s, bsx_tree **out);
 /* this rank's polynomials in natural order, (c1 - c0) x 2^log_n */
 int32_t bsx_shard_coeffs(bsx_shard *s, uint64_t *out, int32_t mem);
 
+/* ---- the same, driven by ONE process over the GPUs of a box (SURVEY.md 8b bsx_comm_create) -------------------
+ * A communicator owns one bsx_ctx per rank (devices[r]; n_ranks a power of two <= BSX_MAX_RANKS; a device may appear
+ * more than once, the ranks then share it).  bsx_sharded_from_values runs the call order above with one host thread
+ * per rank and peer pointers between the devices (NVLink peer access); no collective library is involved.  The result
+ * is word for word the single-GPU PolynomialBatch: same cap, same rows, same Merkle paths, same FRI proof. */
+typedef struct bsx_comm bsx_comm;
+typedef struct bsx_sharded_batch bsx_sharded_batch;
+int32_t bsx_comm_create(int32_t n_ranks, const int32_t *devices, bsx_comm **out);
+void bsx_comm_destroy(bsx_comm *comm);
+int32_t bsx_comm_size(const bsx_comm *comm);
+bsx_ctx *bsx_comm_ctx(bsx_comm *comm, int32_t rank);
+const char *bsx_comm_last_error(const bsx_comm *comm);
+/* PolynomialBatch::from_values (or from_coeffs) over the communicator.  values_host: n_cols x 2^log_n, column-major,
+ * host memory (pinned or pageable).  timing: the slowest rank of every phase. */
+int32_t bsx_sharded_from_values(bsx_comm *comm, const uint64_t *values_host, int32_t log_n, int32_t n_cols,
+                                int32_t rate_bits, int32_t cap_height, int32_t input_is_coeffs, bsx_sharded_batch **out,
+                                bsx_timing *timing);
+/* the same with one pointer per rank to that rank's columns (bsx_shard_column_range), host memory or memory of that
+ * rank's device (`mem`) */
+int32_t bsx_sharded_from_values_parts(bsx_comm *comm, const uint64_t *const *parts, int32_t mem, int32_t log_n,
+                                      int32_t n_cols, int32_t rate_bits, int32_t cap_height, int32_t input_is_coeffs,
+                                      bsx_sharded_batch **out, bsx_timing *timing);
+void bsx_sharded_free(bsx_sharded_batch *b);
+int32_t bsx_sharded_cap(const bsx_sharded_batch *b, uint64_t *out_host /* 2^cap_height x 4 */);
+/* MerkleTree::get / prove with GLOBAL leaf indices, answered by the owning rank; the proof verifies against the cap of
+ * the whole batch and has bsx_sharded_proof_len() = log2(leaves) - cap_height siblings */
+int32_t bsx_sharded_get(bsx_sharded_batch *b, const uint64_t *leaf_idx_host, int32_t k, uint64_t *out_host);
+int32_t bsx_sharded_prove(bsx_sharded_batch *b, uint64_t leaf_index, uint64_t *siblings_host);
+int32_t bsx_sharded_proof_len(const bsx_sharded_batch *b);
+/* this rank's part, for the lower-level calls (bsx_shard_coeffs, bsx_merkle_*) */
+bsx_shard *bsx_sharded_shard(bsx_sharded_batch *b, int32_t rank);
+bsx_tree *bsx_sharded_tree(bsx_sharded_batch *b, int32_t rank);
+
 /* ---- Challenger (iop/challenger.rs) and FRI (fri/oracle.rs prove_openings, fri/prover.rs) -------------
  * bsx_challenger mirrors plonky2's `Challenger<F, PoseidonHash>`: sponge state, input buffer, output
  * buffer (outputs are popped from the BACK, as Vec::pop does).  The struct lives on the host between calls;
@@ -259,12 +297,17 @@ int32_t bsx_fri_proof_from_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, i
 int32_t bsx_fri_final_poly(bsx_ctx *ctx, bsx_batch *const *oracles, int32_t n_oracles,
                            const bsx_fri_instance *instance, const uint64_t alpha[2], uint64_t *out_host);
 
+/* PolynomialBatch::prove_openings over sharded oracles in one call (steps 1-4 above inside one process): the proof
+ * equals bsx_fri_prove_openings on the unsharded batches word for word.  `instance` uses GLOBAL polynomial indices. */
+int32_t bsx_sharded_prove_openings(bsx_comm *comm, bsx_sharded_batch *const *oracles, int32_t n_oracles,
+                                   const bsx_fri_instance *instance, bsx_challenger *challenger,
+                                   const bsx_fri_params *params, uint64_t *proof_host);
+
 /* ---- typed view of the flat FriProof stream, and proof bytes (plonk/proof.rs, util/serialization/mod.rs) -------
  * bsx_fri_proof_layout: word offsets of every plonky2 `FriProof` field inside the stream of bsx_fri_proof_words, so a
  * caller (the Rust shim building `FriProof { commit_phase_merkle_caps, query_round_proofs, final_poly, pow_witness }`)
  * can slice it without knowing the packing.  Offsets inside a query round are relative to
  * query_offset + q * query_stride.  leaf_widths[o] = polynomials + salt columns of oracle o. */
-#define BSX_MAX_ORACLES 16
 typedef struct bsx_fri_layout {
     uint64_t total_words;
     uint64_t caps_offset, cap_words;          /* commit_phase_merkle_caps[r] at caps_offset + r * cap_words */

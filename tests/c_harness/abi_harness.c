@@ -9,6 +9,9 @@
  *   path <leaf> <siblings x 4 words>
  *   eval <n_cols x 2 words>            all polynomials at the extension point (seed, seed + 1)
  *   proof <words>                      prove_openings of every polynomial at that point
+ *   comm <G> <same_cap> <same_rows_paths> <same_proof>   the same commit and proof through bsx_comm_create with G ranks
+ *                                      emulated on device 0 (bsx_sharded_from_values / bsx_sharded_prove_openings)
+ *   fribytes <len> <fnv64>             bsx_fri_proof_bytes of that proof; layout <total_words> from bsx_fri_proof_layout
  * tests/test_gpu_c_abi.py recomputes every record with the oracle. */
 #include <inttypes.h>
 #include <stdio.h>
@@ -155,6 +158,69 @@ int main(int argc, char **argv) {
         print_words("qcap", q_log_n, qcap, 4);
         bsx_batch_free(qb);
         free(qv);
+    }
+
+    /* the same batch and proof with the commit sharded over G ranks of one process (all on device 0 here) */
+    for (int G = 2; G <= 8; G *= 4) {
+        if ((log_n + rate_bits) < 3) break;
+        int32_t devs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        bsx_comm *comm = NULL;
+        if (bsx_comm_create(G, devs, &comm) != BSX_OK) {
+            fprintf(stderr, "bsx_comm_create failed\n");
+            return 1;
+        }
+        uint64_t *v2 = malloc(sizeof(uint64_t) * n * (size_t)n_cols);
+        for (size_t i = 0; i < n * (size_t)n_cols; i++) v2[i] = splitmix(seed, i);
+        bsx_sharded_batch *sb = NULL;
+        if (bsx_sharded_from_values(comm, v2, log_n, n_cols, rate_bits, cap_height, 0, &sb, NULL) != BSX_OK) {
+            fprintf(stderr, "bsx_sharded_from_values: %s\n", bsx_comm_last_error(comm));
+            return 1;
+        }
+        free(v2);
+        uint64_t *cap2 = malloc(sizeof(uint64_t) * ((size_t)4 << cap_height));
+        bsx_sharded_cap(sb, cap2);
+        const int same_cap = memcmp(cap, cap2, sizeof(uint64_t) * ((size_t)4 << cap_height)) == 0;
+        int same_rows = bsx_sharded_proof_len(sb) == n_sib;
+        uint64_t *row2 = malloc(sizeof(uint64_t) * (size_t)n_cols), *sib2 = malloc(sizeof(uint64_t) * 4 * (size_t)(n_sib + 1));
+        for (int k = 0; k < 3; k++) {
+            CHECK(ctx, bsx_merkle_get(tree, &leaves[k], 1, row));
+            CHECK(ctx, bsx_merkle_prove(tree, leaves[k], sib));
+            if (bsx_sharded_get(sb, &leaves[k], 1, row2) != BSX_OK || bsx_sharded_prove(sb, leaves[k], sib2) != BSX_OK) {
+                fprintf(stderr, "sharded opening: %s\n", bsx_comm_last_error(comm));
+                return 1;
+            }
+            same_rows = same_rows && memcmp(row, row2, sizeof(uint64_t) * (size_t)n_cols) == 0 &&
+                        memcmp(sib, sib2, sizeof(uint64_t) * 4 * (size_t)n_sib) == 0;
+        }
+        bsx_challenger ch2;
+        bsx_challenger_init(&ch2);
+        CHECK(ctx, bsx_challenger_observe(ctx, &ch2, cap, (size_t)4 << cap_height));
+        CHECK(ctx, bsx_challenger_observe(ctx, &ch2, ev, 2 * (size_t)n_cols));
+        uint64_t *proof2 = malloc(sizeof(uint64_t) * words);
+        bsx_sharded_batch *sbs[1] = {sb};
+        if (bsx_sharded_prove_openings(comm, sbs, 1, &inst, &ch2, &fp, proof2) != BSX_OK) {
+            fprintf(stderr, "bsx_sharded_prove_openings: %s\n", bsx_comm_last_error(comm));
+            return 1;
+        }
+        printf("comm %d %d %d %d\n", G, same_cap, same_rows, memcmp(proof, proof2, sizeof(uint64_t) * words) == 0);
+        free(proof2); free(row2); free(sib2); free(cap2);
+        bsx_sharded_free(sb);
+        bsx_comm_destroy(comm);
+    }
+
+    /* typed view and bytes of the proof stream */
+    {
+        bsx_fri_layout lay;
+        int32_t width = n_cols;
+        if (bsx_fri_proof_layout(&fp, &width, 1, &lay) != BSX_OK) return 1;
+        size_t len = 0;
+        if (bsx_fri_proof_bytes(proof, &fp, &width, 1, NULL, 0, &len) != BSX_OK) return 1;
+        uint8_t *bytes = malloc(len ? len : 1);
+        if (bsx_fri_proof_bytes(proof, &fp, &width, 1, bytes, len, &len) != BSX_OK) return 1;
+        uint64_t fnv = 0xcbf29ce484222325ULL;
+        for (size_t i = 0; i < len; i++) fnv = (fnv ^ bytes[i]) * 0x100000001B3ULL;
+        printf("fribytes %zu %016" PRIx64 " %" PRIu64 " %" PRIu64 "\n", len, fnv, lay.total_words, proof[lay.pow_witness_offset]);
+        free(bytes);
     }
 
     /* misuse is reported, not fatal: upstream panics with this message */

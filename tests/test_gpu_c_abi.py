@@ -70,5 +70,17 @@ def test_c_program_matches_oracle(oracle, log_n, n_cols, rate_bits, cap_height, 
     chunks = oracle.quotient_chunks(splitmix_field(seed + 300, (2, 1 << (q_log_n + 3))), q_log_n, 8)
     qcap = oracle.batch_from_values(chunks, rate_bits, 0, from_coeffs=True, want=())["cap"]
     assert int(by["qcap"][0][0]) == q_log_n and (_words(by["qcap"][0][1:]).reshape(-1, 4) == qcap).all()
+    # the sharded commit and proof through bsx_comm (2 and 8 emulated ranks) equal the single-GPU ones word for word
+    assert [t for t in by["comm"]] == [["2", "1", "1", "1"], ["8", "1", "1", "1"]]
+    # bytes of the proof stream: the C ABI writer against the Python writer over the oracle's proof
+    import __graft_entry__ as G
+    pkg = G.load_package()
+    ser = __import__(pkg.__name__ + ".serialization", fromlist=["x"])
+    data = ser.write_fri_proof(ser.fri_proof_struct(proof, [n_cols], log_n, rate_bits, cap_height, arity, 4))
+    fnv = 0xcbf29ce484222325
+    for b in data:
+        fnv = ((fnv ^ b) * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
+    fb = by["fribytes"][0]
+    assert int(fb[0]) == len(data) and int(fb[1], 16) == fnv and int(fb[2]) == proof.size and int(fb[3]) == int(proof[-1])
     misuse = by["misuse"][0]
     assert int(misuse[0]) == -1 and "cap_height=5 should be at most log2(leaves.len())=1" in " ".join(misuse[1:])
