@@ -28,7 +28,13 @@ struct bsx_shard {
     u64 *staging;          // optional destination-major send buffer: n_ranks x (c1 - c0) x chunk
     u64 *coeffs;           // (c1 - c0) x 2^log_n
     bool coeffs_bitrev;
+    // Mailbox behind the slab (same allocation, so a peer that mapped the slab sees it): G arrival flags, G cap flags,
+    // G local caps.  Written by the peers' barrier kernels (bsx_shard_run_p2p), epochs only grow.
+    size_t slab_words, cap_words;
+    u64 epoch;
+    int *timeout_flag;     // pinned host word the barrier kernel raises when a peer never arrives
 };
+static inline u64 *shard_mail(const bsx_shard *s, int rank) { return s->peer[rank] ? s->peer[rank] + s->slab_words : nullptr; }
 
 extern "C" int32_t bsx_shard_column_range(int32_t n_cols_total, int32_t rank, int32_t n_ranks, int32_t *c0,
                                           int32_t *c1) {
@@ -75,7 +81,12 @@ extern "C" int32_t bsx_shard_create(bsx_ctx *ctx, int32_t log_n, int32_t n_cols_
         s->peer[i] = nullptr;
         s->peer_ipc[i] = false;
     }
-    size_t bytes = s->chunk * (size_t)n_cols_total * sizeof(u64);
+    s->slab_words = s->chunk * (size_t)n_cols_total;
+    s->cap_words = (size_t)4 << (cap_height > log_ranks ? cap_height - log_ranks : 0);
+    s->epoch = 0;
+    s->timeout_flag = nullptr;
+    const size_t mail_words = (size_t)n_ranks * (2 + s->cap_words);
+    size_t bytes = (s->slab_words + mail_words) * sizeof(u64);
     if (bytes) {
         cudaError_t e = cudaMalloc((void **)&s->slab, bytes);  // not the async pool: cudaIpcGetMemHandle needs cudaMalloc
         if (e != cudaSuccess) {
@@ -83,6 +94,8 @@ extern "C" int32_t bsx_shard_create(bsx_ctx *ctx, int32_t log_n, int32_t n_cols_
             delete s;
             return bsx_fail(ctx, BSX_ERR_OOM, "row slab of %zu bytes: %s", bytes, cudaGetErrorString(e));
         }
+        cudaMemsetAsync(s->slab + s->slab_words, 0, mail_words * sizeof(u64), ctx->stream);
+        cudaStreamSynchronize(ctx->stream);  // before any peer can learn the address
     }
     s->peer[rank] = s->slab;
     *out = s;
@@ -96,6 +109,7 @@ extern "C" void bsx_shard_free(bsx_shard *s) {
     for (int i = 0; i < s->n_ranks; i++)
         if (s->peer_ipc[i] && s->peer[i]) cudaIpcCloseMemHandle(s->peer[i]);
     if (s->slab) cudaFree(s->slab);
+    if (s->timeout_flag) cudaFreeHost(s->timeout_flag);
     bsx_free(s->ctx, s->staging);
     bsx_free(s->ctx, s->coeffs);
     delete s;
@@ -156,13 +170,14 @@ extern "C" int32_t bsx_shard_set_peer_ptr(bsx_shard *s, int32_t peer_rank, uint6
 // the LDE words go straight to their owners.  use_staging != 0: they go to a local destination-major
 // buffer, block d = this rank's columns x rank d's rows, for the host's all-to-all; block d must land at
 // slab_d + c0 * chunk on rank d.
-extern "C" int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
-                                       int32_t use_staging, bsx_timing *timing) {
-    if (!s) return BSX_ERR_INVALID_ARG;
+// Enqueues copy-in and transforms on ctx->stream (a pinned host input is uploaded in column chunks on the copy stream,
+// chunk k + 1 under the transforms of chunk k); no host synchronisation.  ev: optional [after copy-in of the first
+// chunk, after the last iNTT, after the last LDE].
+static int shard_transform_enqueue(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
+                                   int32_t use_staging, cudaEvent_t *ev, float *ifft_ms_acc, std::vector<cudaEvent_t> *chunk_ev) {
     bsx_ctx *ctx = s->ctx;
     const int n_local = s->c1 - s->c0;
     if (!input && n_local > 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "input is NULL");
-    CU(ctx, cudaSetDevice(ctx->device));
     const size_t n = (size_t)1 << s->log_n, nb = n << s->rate_bits;
     BsxDests D;
     D.n = s->n_ranks;
@@ -177,33 +192,77 @@ extern "C" int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int3
             D.ptr[d] = s->peer[d] + (size_t)s->c0 * s->chunk;
         }
     }
+    bsx_free(ctx, s->coeffs);
+    s->coeffs = nullptr;
+    (void)ifft_ms_acc;
+    if (n_local == 0) return BSX_OK;
+    TRY(bsx_alloc_owned(ctx, &s->coeffs, n * n_local));
+    // the two-pass transforms keep their intermediate in a local column-major scratch; single-pass
+    // sizes (log_n <= 12) write their only pass straight to the destinations
+    u64 *scratch = nullptr;
+    TRY(bsx_alloc(ctx, &scratch, nb * (size_t)n_local));
+    cudaPointerAttributes at;
+    const bool pinned = mem == BSX_HOST && cudaPointerGetAttributes(&at, input) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    int rc = BSX_OK;
+    if (pinned && n_local >= 8 && s->log_n >= 13) {
+        const int n_chunks = n_local >= 16 ? 4 : 2, per = (n_local + n_chunks - 1) / n_chunks;
+        std::vector<cudaEvent_t> &e = *chunk_ev;
+        e.resize((size_t)n_chunks + 1);
+        for (auto &x : e) cudaEventCreateWithFlags(&x, cudaEventDisableTiming);
+        cudaEventRecord(e[(size_t)n_chunks], ctx->stream);  // the buffers exist (stream-ordered allocation)
+        cudaStreamWaitEvent(ctx->copy_stream, e[(size_t)n_chunks], 0);
+        for (int k = 0; k < n_chunks; k++) {
+            const int c0 = k * per, cc = (n_local - c0) < per ? (n_local - c0) : per;
+            if (cc <= 0) continue;
+            CU(ctx, cudaMemcpyAsync(s->coeffs + (size_t)c0 * n, (const u64 *)input + (size_t)c0 * n, (size_t)cc * n * sizeof(u64),
+                                    cudaMemcpyHostToDevice, ctx->copy_stream));
+            cudaEventRecord(e[(size_t)k], ctx->copy_stream);
+        }
+        for (int k = 0; k < n_chunks && rc == BSX_OK; k++) {
+            const int c0 = k * per, cc = (n_local - c0) < per ? (n_local - c0) : per;
+            if (cc <= 0) continue;
+            cudaStreamWaitEvent(ctx->stream, e[(size_t)k], 0);
+            if (k == 0 && ev) cudaEventRecord(ev[0], ctx->stream);
+            BsxDests Dk = D;
+            for (int d = 0; d < D.n; d++) Dk.ptr[d] = D.ptr[d] + (size_t)c0 * s->chunk;
+            rc = bsx_commit_transforms(ctx, s->coeffs + (size_t)c0 * n, s->log_n, cc, s->rate_bits, input_is_coeffs != 0,
+                                       scratch + (size_t)c0 * nb, nb, &Dk, nullptr);
+        }
+        if (ev) cudaEventRecord(ev[1], ctx->stream);  // chunked: iNTT and LDE interleave, reported together as lde
+    } else {
+        TRY(bsx_copy_in(ctx, s->coeffs, (const u64 *)input, n * n_local, mem));
+        if (ev) cudaEventRecord(ev[0], ctx->stream);
+        rc = bsx_commit_transforms(ctx, s->coeffs, s->log_n, n_local, s->rate_bits, input_is_coeffs != 0, scratch, nb, &D,
+                                   ev ? ev[1] : nullptr);
+    }
+    if (rc == BSX_OK) s->coeffs_bitrev = !input_is_coeffs;
+    if (ev) cudaEventRecord(ev[2], ctx->stream);
+    bsx_free(ctx, scratch);
+    return rc;
+}
+
+// Transforms of the local columns.  use_staging == 0: every row slab must be known (bsx_shard_set_peer_*);
+// the LDE words go straight to their owners.  use_staging != 0: they go to a local destination-major
+// buffer, block d = this rank's columns x rank d's rows, for the host's all-to-all; block d must land at
+// slab_d + c0 * chunk on rank d.
+extern "C" int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
+                                       int32_t use_staging, bsx_timing *timing) {
+    if (!s) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = s->ctx;
+    BsxScope scope(ctx);
+    CU(ctx, cudaSetDevice(ctx->device));
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
     if (timing)
         for (auto &e : ev) cudaEventCreate(&e);
-    bsx_free(ctx, s->coeffs);
-    s->coeffs = nullptr;
-    u64 *scratch = nullptr;
-    int rc = BSX_OK;
-    do {
-        if (n_local == 0) break;
-        if ((rc = bsx_alloc_owned(ctx, &s->coeffs, n * n_local))) break;
-        if ((rc = bsx_copy_in(ctx, s->coeffs, (const u64 *)input, n * n_local, mem))) break;
-        if (timing) cudaEventRecord(ev[0], ctx->stream);
-        // the two-pass transforms keep their intermediate in a local column-major scratch; single-pass
-        // sizes (log_n <= 12) write their only pass straight to the destinations
-        if ((rc = bsx_alloc(ctx, &scratch, nb * (size_t)n_local))) break;
-        if ((rc = bsx_commit_transforms(ctx, s->coeffs, s->log_n, n_local, s->rate_bits, input_is_coeffs != 0, scratch,
-                                        nb, &D, timing ? ev[1] : nullptr)))
-            break;
-        s->coeffs_bitrev = !input_is_coeffs;
-        if (timing) cudaEventRecord(ev[2], ctx->stream);
-    } while (0);
-    bsx_free(ctx, scratch);
+    std::vector<cudaEvent_t> chunk_ev;
+    int rc = shard_transform_enqueue(s, input, mem, input_is_coeffs, use_staging, timing ? ev : nullptr, nullptr, &chunk_ev);
     cudaError_t e = cudaStreamSynchronize(ctx->stream);  // stores to peer slabs are complete and visible after this
     if (rc == BSX_OK && e != cudaSuccess) rc = bsx_fail(ctx, BSX_ERR_CUDA, "sharded transform failed: %s", cudaGetErrorString(e));
+    for (auto &x : chunk_ev) cudaEventDestroy(x);
     if (timing) {
         memset(timing, 0, sizeof(*timing));
-        if (rc == BSX_OK && n_local > 0) {
+        if (rc == BSX_OK && s->c1 > s->c0) {
             cudaEventElapsedTime(&timing->ifft_ms, ev[0], ev[1]);
             cudaEventElapsedTime(&timing->lde_ms, ev[1], ev[2]);
             timing->total_ms = timing->ifft_ms + timing->lde_ms;
@@ -211,6 +270,124 @@ extern "C" int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int3
         for (auto &x : ev) cudaEventDestroy(x);
     }
     return rc;
+}
+
+// ---- device-side barrier over the mailboxes (one rank per GPU) ------------------------------------------------
+// Thread p tells rank p "rank `rank` has reached `epoch`" (slot 0: its stores into your slab are complete -- they were
+// issued by kernels that finished earlier on this stream; slot 1: its local cap is in your mailbox), then waits for
+// rank p's word in this rank's own mailbox.  Ranks run on different GPUs, so every peer's kernel is resident or will
+// be launched regardless of this one spinning; a peer that never arrives (a crashed process) raises *timeout instead
+// of hanging the GPU.
+struct ShardMail {
+    u64 *mail[BSX_MAX_RANKS];
+};
+__global__ void shard_barrier_kernel(ShardMail M, int rank, int n_ranks, u64 epoch, int slot, const u64 *cap_src,
+                                     int cap_words, int *timeout) {
+    const int p = threadIdx.x;
+    if (p >= n_ranks) return;
+    if (cap_src) {
+        u64 *dst = M.mail[p] + 2 * n_ranks + (size_t)rank * cap_words;
+        for (int i = 0; i < cap_words; i++) dst[i] = cap_src[i];
+    }
+    __threadfence_system();
+    *((volatile u64 *)(M.mail[p] + slot * n_ranks + rank)) = epoch;
+    volatile u64 *mine = (volatile u64 *)(M.mail[rank] + slot * n_ranks + p);
+    const long long t0 = clock64();
+    while (*mine < epoch) {
+        if (clock64() - t0 > 20000000000LL) {  // ~10 s
+            *timeout = 1;
+            break;
+        }
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+
+// One sharded commit with NO host synchronisation between its phases (one process per GPU, peers mapped through
+// bsx_shard_set_peer_ipc): transforms whose last pass stores into the owners' slabs -> device barrier -> leaf hashing
+// and cap subtrees -> every rank's local cap published into every mailbox -> rank_caps_host (n_ranks x local cap,
+// rank order).  The second barrier also makes the slabs safe to overwrite by the next call.
+extern "C" int32_t bsx_shard_run_p2p(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
+                                     bsx_tree **tree_out, uint64_t *rank_caps_host, bsx_timing *timing) {
+    if (!s || !tree_out || !rank_caps_host) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = s->ctx;
+    BsxScope scope(ctx);
+    *tree_out = nullptr;
+    CU(ctx, cudaSetDevice(ctx->device));
+    ShardMail M;
+    for (int p = 0; p < BSX_MAX_RANKS; p++) M.mail[p] = nullptr;
+    for (int p = 0; p < s->n_ranks; p++) {
+        if (!s->peer[p]) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "row slab of rank %d is not set", p);
+        if (p != s->rank) {
+            cudaPointerAttributes at;
+            CU(ctx, cudaPointerGetAttributes(&at, s->peer[p]));
+            if (at.device == ctx->device)  // two ranks on one GPU: their barrier kernels could wait on each other forever
+                return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "rank %d shares device %d with rank %d: the device-side barrier needs "
+                                "one GPU per rank (use bsx_shard_transform / bsx_shard_commit with a host barrier)", p, ctx->device, s->rank);
+        }
+        M.mail[p] = shard_mail(s, p);
+    }
+    if (!s->timeout_flag) {
+        CU(ctx, cudaHostAlloc((void **)&s->timeout_flag, sizeof(int), cudaHostAllocMapped));
+        *s->timeout_flag = 0;
+    }
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (timing)
+        for (auto &e : ev) cudaEventCreate(&e);
+    std::vector<cudaEvent_t> chunk_ev;
+    const u64 epoch = ++s->epoch;
+    int rc = shard_transform_enqueue(s, input, mem, input_is_coeffs, 0, timing ? ev : nullptr, nullptr, &chunk_ev);
+    bsx_tree *t = nullptr;
+    if (rc == BSX_OK) {
+        BSX_COUNT_LAUNCH();
+        shard_barrier_kernel<<<1, BSX_MAX_RANKS, 0, ctx->stream>>>(M, s->rank, s->n_ranks, epoch, 0, nullptr, 0, s->timeout_flag);
+        if (timing) cudaEventRecord(ev[3], ctx->stream);
+        t = new bsx_tree();
+        t->ctx = ctx;
+        t->log_leaves = s->log_n + s->rate_bits - s->log_ranks;
+        t->leaf_len = s->n_cols_total;
+        t->cap_height = s->cap_height > s->log_ranks ? s->cap_height - s->log_ranks : 0;
+        t->leaves = s->slab;
+        t->col_stride = s->chunk;
+        t->owns_leaves = false;
+        t->embedded = false;
+        rc = bsx_tree_build(t, timing ? ev[4] : nullptr);
+    }
+    if (rc == BSX_OK) {
+        BSX_COUNT_LAUNCH();
+        shard_barrier_kernel<<<1, BSX_MAX_RANKS, 0, ctx->stream>>>(M, s->rank, s->n_ranks, epoch, 1, t->cap_dev, (int)s->cap_words,
+                                                                  s->timeout_flag);
+        if (timing) cudaEventRecord(ev[5], ctx->stream);
+        rc = bsx_copy_out(ctx, (u64 *)rank_caps_host, M.mail[s->rank] + 2 * s->n_ranks, (size_t)s->n_ranks * s->cap_words, BSX_HOST);
+    }
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (rc == BSX_OK && e != cudaSuccess) rc = bsx_fail(ctx, BSX_ERR_CUDA, "sharded commit failed: %s", cudaGetErrorString(e));
+    if (rc == BSX_OK && *s->timeout_flag) {
+        *s->timeout_flag = 0;
+        rc = bsx_fail(ctx, BSX_ERR_CUDA, "a peer rank did not reach the device barrier within its time limit");
+    }
+    for (auto &x : chunk_ev) cudaEventDestroy(x);
+    if (timing) {
+        memset(timing, 0, sizeof(*timing));
+        if (rc == BSX_OK && s->c1 > s->c0) {
+            cudaEventElapsedTime(&timing->ifft_ms, ev[0], ev[1]);
+            cudaEventElapsedTime(&timing->lde_ms, ev[1], ev[2]);
+            cudaEventElapsedTime(&timing->h2d_ms, ev[2], ev[3]);  // here: the wait for the slowest peer's stores
+            cudaEventElapsedTime(&timing->leaf_hash_ms, ev[3], ev[4]);
+            cudaEventElapsedTime(&timing->tree_ms, ev[4], ev[5]);
+            cudaEventElapsedTime(&timing->total_ms, ev[0], ev[5]);
+        }
+        for (auto &x : ev) cudaEventDestroy(x);
+    }
+    if (rc != BSX_OK) {
+        if (t) {
+            bsx_tree_release(t);
+            delete t;
+        }
+        return rc;
+    }
+    *tree_out = t;
+    return BSX_OK;
 }
 
 // Leaf hashing and the local cap subtrees over this rank's row slab (all slabs must be complete: the

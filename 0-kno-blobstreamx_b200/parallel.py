@@ -231,13 +231,13 @@ class ShardedPolynomialBatch:
         IPC.  The returned object can commit any number of batches of this shape with `run`."""
         import torch
         import torch.distributed as dist
-        if mode not in ("p2p", "nccl"):
-            raise BsxError("mode must be 'p2p' or 'nccl'")
+        if mode not in ("p2p", "p2p_host", "nccl"):
+            raise BsxError("mode must be 'p2p' (device-side barrier), 'p2p_host' (host barrier) or 'nccl'")
         rank, world = dist.get_rank(group), dist.get_world_size(group)
         plan = ShardPlan(log_n, n_cols, rate_bits, cap_height, world)
         self = cls.create(ctx, plan, rank)
         self.group, self.mode = group, mode
-        if mode == "p2p":
+        if mode in ("p2p", "p2p_host"):
             dev = "cuda:%d" % ctx.device
             mine = torch.tensor(list(self.ipc_handle()), dtype=torch.uint8, device=dev)
             allh = torch.empty(world * IPC_BYTES, dtype=torch.uint8, device=dev)
@@ -260,6 +260,29 @@ class ShardedPolynomialBatch:
             self.merkle_tree.close()
             self.merkle_tree = None
         if self.mode == "p2p":
+            # the whole commit inside the library: peer stores, device-side flag barrier, hashing, caps exchanged through
+            # the mailboxes behind the slabs -- no NCCL call and one host synchronisation per commit
+            c0, c1 = plan.column_range(self.rank)
+            if device_ptr is not None:
+                src, mem = C.c_void_p(int(device_ptr)), BSX_DEVICE
+            else:
+                values_local = _np(values_local)
+                if values_local.shape != (c1 - c0, 1 << plan.log_n):
+                    raise BsxError("rank %d expects columns [%d, %d)" % (self.rank, c0, c1))
+                src, mem = _ptr(values_local), BSX_HOST
+            caps = np.zeros((plan.world, 1 << plan.local_cap_height, 4), dtype=np.uint64)
+            h = C.c_void_p()
+            t = Timing() if timing else None
+            f = lib().bsx_shard_run_p2p
+            f.restype, f.argtypes = C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p),
+                                                C.c_void_p, C.POINTER(Timing)]
+            ctx.check(f(self._h, src, mem, 1 if is_coeffs else 0, C.byref(h), _ptr(caps), C.byref(t) if t is not None else None))
+            self.timing = t
+            self.merkle_tree = MerkleTree(ctx, _handle=h)
+            self.rank_caps = list(caps)
+            self.cap = assemble_cap(self.rank_caps, plan, ctx)
+            return self
+        if self.mode == "p2p_host":
             self.transform(values_local, is_coeffs, use_staging=False, device_ptr=device_ptr, timing=timing)
             dist.barrier(group=group)  # every rank's stores into every slab are complete
         else:

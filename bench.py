@@ -9,9 +9,12 @@ header_range map jobs of the north star share no state, so ranks exchange nothin
 the witness already in HBM; `e2e` = the same through the C ABI with the witness in pinned HOST
 memory (H2D inside the timed call, cap back on the host).
 
-At N > 1 the line also carries `sharded`: ONE commit of the same shape split over the N GPUs (strong
-scaling; column-sharded transforms whose last pass stores into the owners' row slabs over NVLink P2P, or a
-staged NCCL all-to-all; per-GPU cap subtrees; cap gathered) -- see 0-kno-blobstreamx_b200/parallel.py.
+At N > 1 the line's `value` / `e2e` are ONE commit of the same shape split over the N GPUs (`"scaling": "strong"`:
+column-sharded transforms whose last pass stores into the owners' row slabs over NVLink P2P, a device-side flag
+barrier, per-GPU leaf hashing and cap subtrees, caps exchanged through mailboxes behind the slabs; see
+0-kno-blobstreamx_b200/csrc/api_shard.cu bsx_shard_run_p2p).  The N independent commits (weak scaling) move to
+`replicas`, and `sharded` holds every exchange mode (p2p, p2p with a host barrier, staged NCCL all-to-all, p2p from
+pinned host memory).
 
 `prove` (skip with --no-prove): wall seconds of one shape-equivalent synthetic proof per GPU (three commits
 from pinned host memory, the opening set, prove_openings) -- BASELINE.json's second metric on random columns.
@@ -217,26 +220,37 @@ def workload_config(n_gpus, log_n=LOG_N):
 
 
 def sharded_arm(args, pkg, ctx, stream, rank, world, local_rank, cap_rank0):
-    """Strong-scaling leg at N > 1: ONE 2^20 x 135 commit sharded over the N GPUs (columns -> ranks for the
-    transforms, leaf rows -> ranks for hashing), in both exchange modes: "p2p" = the last NTT pass stores
-    into the owners' row slabs over NVLink, "nccl" = staged all-to-all.  The witness is rank 0's witness
-    of the independent-commit leg, so the cap must equal rank 0's cap there."""
+    """Strong-scaling leg at N > 1 -- the line's `value` there: ONE 2^20 x 135 commit sharded over the N GPUs (columns
+    -> ranks for the transforms, leaf rows -> ranks for hashing).  Exchange modes: "p2p" = the last NTT pass stores into
+    the owners' row slabs over NVLink and the ranks meet at a device-side flag barrier (no NCCL call, one host sync per
+    commit); "p2p_host" = the same stores with a host barrier (torch.distributed) and an NCCL cap gather; "nccl" =
+    staged all-to-all.  "p2p" is also timed end to end: every rank uploads ITS columns from pinned host memory inside
+    the timed call.  The witness is rank 0's witness of the independent-commit leg, so the cap must equal rank 0's cap."""
     import torch
     import torch.distributed as dist
     n = 1 << LOG_N
     dev = "cuda:%d" % local_rank
     plan = pkg.ShardPlan(LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT, world)
     c0, c1 = plan.column_range(rank)
-    loc = torch.from_numpy(splitmix_field(0x5EED0001, (c1 - c0, n), offset=c0 * n).view(np.int64)).to(dev)
+    host = torch.empty((c1 - c0, n), dtype=torch.int64).pin_memory()
+    host_np = host.numpy().view(np.uint64)
+    host_np[:] = splitmix_field(0x5EED0001, (c1 - c0, n), offset=c0 * n)
+    loc = host.to(dev)
     want = torch.from_numpy(np.ascontiguousarray(cap_rank0).view(np.int64).copy()).to(dev)
     dist.broadcast(want, 0)
     want = want.cpu().numpy().view(np.uint64)
     out = {"scaling": "strong", "workload": "one 2^%d x %d commit over %d GPUs" % (LOG_N, N_COLS, world)}
     with torch.cuda.stream(stream):
-        for mode in ("p2p", "nccl"):
-            sb = pkg.ShardedPolynomialBatch.setup(ctx, LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT, mode=mode)
-            for _ in range(2):
-                sb.run(None, device_ptr=loc.data_ptr())
+        for mode in ("p2p", "p2p_host", "nccl", "p2p_e2e"):
+            sb = pkg.ShardedPolynomialBatch.setup(ctx, LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT, mode=mode.split("_e2e")[0])
+
+            def step(timing=False):
+                if mode == "p2p_e2e":
+                    sb.run(host_np, timing=timing)
+                else:
+                    sb.run(None, device_ptr=loc.data_ptr(), timing=timing)
+            for _ in range(max(2, min(args.warmup, 3))):
+                step()
             assert (sb.cap == want).all(), "sharded cap (%s) differs from the single-GPU cap" % mode
             dist.barrier()
             torch.cuda.synchronize()
@@ -244,19 +258,26 @@ def sharded_arm(args, pkg, ctx, stream, rank, world, local_rank, cap_rank0):
             e0.record(stream)
             tr = []
             for _ in range(args.steps):
-                sb.run(None, device_ptr=loc.data_ptr(), timing=True)
+                step(True)
                 tr.append(sb.timing.as_dict())
             e1.record(stream)
             dist.barrier()
             torch.cuda.synchronize()
-            t = torch.tensor([e0.elapsed_time(e1) / args.steps, float(np.mean([x["ifft_ms"] for x in tr])),
-                              float(np.mean([x["lde_ms"] for x in tr]))], device=dev, dtype=torch.float64)
+            assert (sb.cap == want).all(), "sharded cap (%s) differs from the single-GPU cap" % mode
+            keys = ["ifft_ms", "lde_ms", "h2d_ms", "leaf_hash_ms", "tree_ms"]
+            t = torch.tensor([e0.elapsed_time(e1) / args.steps] + [float(np.mean([x[k] for x in tr])) for k in keys],
+                             device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t[0])
             out[mode] = {"ms_per_commit": ms, "value": n * N_COLS / (ms * 1e-3) / 1e6, "unit": "Melem/s",
-                         "ifft_ms_max": float(t[1]), "lde_ms_max": float(t[2]),
+                         "transforms_ms_max": float(t[1]) + float(t[2]),
                          "exchange_bytes_per_gpu": 8 * (c1 - c0) * (world - 1) * plan.chunk}
+            if mode.startswith("p2p") and mode != "p2p_host":
+                out[mode].update({"peer_wait_ms_max": float(t[3]), "leaf_hash_ms_max": float(t[4]), "tree_and_cap_exchange_ms_max": float(t[5])})
+            if mode == "p2p_e2e":
+                out[mode]["h2d_bytes_per_step_all_ranks"] = 8 * n * N_COLS
             sb.close()
+    del loc
     return out
 
 
@@ -583,6 +604,21 @@ def gpu_arm(args, rank, world, local_rank):
                      "gperm_per_s": perms / ((avg["leaf_hash_ms"] + avg["tree_ms"]) * 1e-3) / 1e9},
     }
     if sharded is not None:
+        # N > 1: the headline of the line is ONE commit sharded over the N GPUs (strong scaling, the north star's
+        # "column-sharded NTT + NVLink exchange + per-GPU subtrees"); the N independent commits stay as `replicas`
+        out["replicas"] = {"scaling": "weak", "value": out["value"], "ms_per_step": out["ms_per_step"], "e2e": out["e2e"],
+                           "e2e_pageable": out["e2e_pageable"], "lde_melem_per_s": out["lde_melem_per_s"],
+                           "workload": "one independent 2^%d x %d commit per GPU (header_range map jobs)" % (LOG_N, N_COLS)}
+        sh, she = sharded["p2p"], sharded["p2p_e2e"]
+        out.update({"value": sh["value"], "ms_per_step": sh["ms_per_commit"], "scaling": "strong",
+                    "lde_melem_per_s": sh["value"] * (1 << RATE_BITS),
+                    "e2e": {"value": she["value"], "unit": "Melem/s", "ms_per_step": she["ms_per_commit"],
+                            "h2d_bytes_per_step": 8 * elems, "d2h_bytes_per_step": world * world * (32 << max(CAP_HEIGHT - (world.bit_length() - 1), 0))}})
+        del out["e2e_pageable"]
+        out["config"]["sharding"] = ("ONE commit over %d GPUs: columns -> ranks for iNTT + LDE, the last NTT pass stores into the "
+                                     "owners' row slabs over NVLink P2P, device-side flag barrier, per-GPU leaf hashing and cap "
+                                     "subtrees, caps exchanged through the slabs' mailboxes (no NCCL on the data path)" % world)
+        out["config"]["workload"] = out["config"]["workload"].replace(" per GPU", ", one commit over all GPUs")
         out["sharded"] = sharded
     if prove is not None:
         out["prove"] = prove

@@ -184,6 +184,15 @@ int32_t bsx_shard_set_peer_ptr(bsx_shard *s, int32_t peer_rank, uint64_t *slab_d
 /* input: this rank's columns only, (c1 - c0) x 2^log_n column-major values (or coefficients) */
 int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
                             int32_t use_staging, bsx_timing *timing);
+/* The whole commit of one rank with no host synchronisation between its phases, for one process per GPU with every
+ * peer slab mapped (bsx_shard_set_peer_ipc): transforms -> device-side barrier over flags in the peers' slabs -> leaf
+ * hashing and cap subtrees -> the local caps published to every rank -> rank_caps_host (n_ranks x 2^(local cap height)
+ * x 4 words, rank order; equal on every rank).  A pinned host input is uploaded in column chunks under the transforms.
+ * Collective: every rank must call it the same number of times.  BSX_ERR_UNSUPPORTED when two ranks share a device
+ * (their barrier kernels could wait on each other): use bsx_shard_transform / host barrier / bsx_shard_commit there.
+ * timing->h2d_ms carries the wait for the slowest peer. */
+int32_t bsx_shard_run_p2p(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs, bsx_tree **tree_out,
+                          uint64_t *rank_caps_host, bsx_timing *timing);
 /* MerkleTree over this rank's slab (borrowed): 2^(cap_height - log2 G) local cap entries */
 int32_t bsx_shard_commit(bsx_shard *s, bsx_tree **out);
 /* this rank's polynomials in natural order, (c1 - c0) x 2^log_n */

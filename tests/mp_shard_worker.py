@@ -38,6 +38,15 @@ def main():
         assert (sb.merkle_tree.get(plan.local_leaf(leaf)) == tree.get(leaf)).all()
         assert (sb.merkle_tree.prove(plan.local_leaf(leaf)) == tree.prove(leaf)).all()
     assert (sb.polynomials == ref.polynomials[c0:c1]).all()
+    # repeated commits on the same slabs (epochs of the device-side barrier), once from pinned host memory (the chunked
+    # upload under the transforms) and once from device memory
+    pin = torch.from_numpy(vals[c0:c1].view(np.int64).copy()).pin_memory()
+    sb.run(pin.numpy().view(np.uint64))
+    assert (sb.cap == ref.cap).all(), "rank %d: second commit (pinned host input) differs" % rank
+    devt = pin.to("cuda:%d" % local)
+    torch.cuda.synchronize()
+    sb.run(None, device_ptr=devt.data_ptr())
+    assert (sb.cap == ref.cap).all(), "rank %d: third commit (device input) differs" % rank
     # collective openings: every rank asks for the same leaves, each answered by its owner
     nb = 1 << plan.log_nb
     leaves = [(k * 40503 + 17) % nb for k in range(28)]

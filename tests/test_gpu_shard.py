@@ -131,7 +131,7 @@ def test_merkle_reduce(pkg, ctx, oracle):
     assert (out == np.array(want, dtype=np.uint64)).all()
 
 
-@pytest.mark.parametrize("mode", ["p2p", "nccl"])
+@pytest.mark.parametrize("mode", ["p2p", "p2p_host", "nccl"])
 def test_multiprocess_ipc_and_nccl(mode):
     import torch
     n = torch.cuda.device_count()
