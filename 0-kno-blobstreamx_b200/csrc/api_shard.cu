@@ -206,22 +206,36 @@ static int shard_transform_enqueue(bsx_shard *s, const uint64_t *input, int32_t 
     cudaGetLastError();
     int rc = BSX_OK;
     if (pinned && n_local >= 8 && s->log_n >= 13) {
-        const int n_chunks = n_local >= 16 ? 4 : 2, per = (n_local + n_chunks - 1) / n_chunks;
+        // only the first chunk's copy is exposed: start small (4 columns, then 8), then thirds of the rest
+        std::vector<int> cstart;
+        {
+            int c = 0;
+            for (int r : {4, 8})
+                if (n_local - c >= 2 * r) {
+                    cstart.push_back(c);
+                    c += r;
+                }
+            const int rest = n_local - c, parts = rest >= 24 ? 3 : rest >= 12 ? 2 : 1, per = (rest + parts - 1) / parts;
+            while (c < n_local) {
+                cstart.push_back(c);
+                c += per;
+            }
+            cstart.push_back(n_local);
+        }
+        const int n_chunks = (int)cstart.size() - 1;
         std::vector<cudaEvent_t> &e = *chunk_ev;
         e.resize((size_t)n_chunks + 1);
         for (auto &x : e) cudaEventCreateWithFlags(&x, cudaEventDisableTiming);
         cudaEventRecord(e[(size_t)n_chunks], ctx->stream);  // the buffers exist (stream-ordered allocation)
         cudaStreamWaitEvent(ctx->copy_stream, e[(size_t)n_chunks], 0);
         for (int k = 0; k < n_chunks; k++) {
-            const int c0 = k * per, cc = (n_local - c0) < per ? (n_local - c0) : per;
-            if (cc <= 0) continue;
+            const int c0 = cstart[k], cc = cstart[k + 1] - c0;
             CU(ctx, cudaMemcpyAsync(s->coeffs + (size_t)c0 * n, (const u64 *)input + (size_t)c0 * n, (size_t)cc * n * sizeof(u64),
                                     cudaMemcpyHostToDevice, ctx->copy_stream));
             cudaEventRecord(e[(size_t)k], ctx->copy_stream);
         }
         for (int k = 0; k < n_chunks && rc == BSX_OK; k++) {
-            const int c0 = k * per, cc = (n_local - c0) < per ? (n_local - c0) : per;
-            if (cc <= 0) continue;
+            const int c0 = cstart[k], cc = cstart[k + 1] - c0;
             cudaStreamWaitEvent(ctx->stream, e[(size_t)k], 0);
             if (k == 0 && ev) cudaEventRecord(ev[0], ctx->stream);
             BsxDests Dk = D;
@@ -318,7 +332,7 @@ extern "C" int32_t bsx_shard_run_p2p(bsx_shard *s, const uint64_t *input, int32_
     for (int p = 0; p < BSX_MAX_RANKS; p++) M.mail[p] = nullptr;
     for (int p = 0; p < s->n_ranks; p++) {
         if (!s->peer[p]) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "row slab of rank %d is not set", p);
-        if (p != s->rank) {
+        if (p != s->rank && !s->peer_ipc[p]) {  // (an IPC mapping always reports the mapping device: one process per GPU is the caller's contract there)
             cudaPointerAttributes at;
             CU(ctx, cudaPointerGetAttributes(&at, s->peer[p]));
             if (at.device == ctx->device)  // two ranks on one GPU: their barrier kernels could wait on each other forever
