@@ -6,7 +6,8 @@ import numpy as np
 
 BSX_HOST, BSX_DEVICE = 0, 1
 _DIR = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_DIR, "csrc", "libbsx_b200.so")
+# BSX_B200_LIB: another build of the same library (A/B builds of a kernel under tools/); never a different backend
+_SO = os.environ.get("BSX_B200_LIB") or os.path.join(_DIR, "csrc", "libbsx_b200.so")
 
 # every symbol include/bsx_b200.h declares (checked by tests/test_abi.py against the header text)
 EXPORTED_SYMBOLS = [

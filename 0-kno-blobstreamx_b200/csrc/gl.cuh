@@ -235,6 +235,94 @@ __device__ __forceinline__ u64 gl_canon_fast(u64 x) {
     return ge ? (u64)(lo - 1) : x;
 }
 
+// ---- pipe-balanced forms for the transforms (ntt_kernels.cu) ----
+// The NTT kernels are bound by the ALU pipe (76 % busy) while the FMA-heavy pipe idles at ~40 %: carry-OUT adds exist
+// only as IADD3 on the ALU, and ptxas also puts most of the carry-IN-only adds there (IADD3.X 710 : IMAD.X 269 in
+// pass LO).  An add written as a multiply-add by a run-time 1 (constant bank, opaque to ptxas) can only be an IMAD /
+// IMAD.X, i.e. it moves to the FMA pipe at the same instruction count.  GL_FMA_* select which sites are moved.
+// Measured on B200 (profiles/r02_ntt_variants.txt): LDE 25.89 -> 24.03 ms, iNTT 3.27 -> 3.03 ms with both on.  Only
+// add-type carries are handed to madc: after sub.cc ptxas passes the HARDWARE carry (no borrow = 1) to a following
+// madc, not PTX's documented borrow, so a subtraction rewritten that way computes the wrong value (tried, rejected).
+static __constant__ u32 GL_ONE_C = 1u, GL_ZERO_C = 0u, GL_MINUS1_C = 0xFFFFFFFFu;
+#ifndef GL_FMA_MUL
+#define GL_FMA_MUL 0
+#endif
+#ifndef GL_FMA_CANON
+#define GL_FMA_CANON 0
+#endif
+
+// a * b -> CANONICAL.  Same product and reduction as gl_mul_lazy; with GL_FMA_MUL the five carry-in-only adds are
+// IMAD.X, with GL_FMA_CANON the final canonicalisation is 2 ALU + 3 FMA instructions instead of 2 ISETP + 2 SEL:
+//   r >= p  <=>  r + EPS carries out of 64 bits; then r - p = (r1 + 1 : r0 - 1) (r1 = 0xFFFFFFFF wraps to 0, r0 >= 1).
+__device__ __forceinline__ u64 gl_mul_canon(u64 a, u64 b) {
+#if !GL_FMA_MUL && !GL_FMA_CANON
+    return gl_canon_fast(gl_mul_lazy(a, b));
+#else
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32), r0, r1;
+    asm("{\n\t.reg .u32 x0,x1,x2,x3,t0,t1,t2,r2,n,eh,c0,c1,g;\n\t.reg .u64 w0,w3,t;\n\t"
+        "mul.wide.u32 w0, %2, %4;\n\t"
+        "mul.wide.u32 w3, %3, %5;\n\t"
+        "mul.wide.u32 t, %2, %5;\n\t"
+        "mov.b64 {t0,t1}, t;\n\t"
+        "mad.lo.cc.u32 t0, %3, %4, t0;\n\t"
+        "madc.hi.cc.u32 t1, %3, %4, t1;\n\t"
+#if GL_FMA_MUL
+        "madc.lo.u32 t2, %8, %7, 0;\n\t"         // 0 * 1 + 0 + carry
+#else
+        "addc.u32 t2, 0, 0;\n\t"
+#endif
+        "mov.b64 {x0,x1}, w0;\n\t"
+        "mov.b64 {x2,x3}, w3;\n\t"
+        "add.cc.u32 x1, x1, t0;\n\t"
+        "addc.cc.u32 x2, x2, t1;\n\t"
+#if GL_FMA_MUL
+        "madc.lo.u32 x3, t2, %7, x3;\n\t"
+#else
+        "addc.u32 x3, x3, t2;\n\t"
+#endif
+        "mad.lo.cc.u32 x0, x2, %6, x0;\n\t"
+        "madc.hi.cc.u32 x1, x2, %6, x1;\n\t"
+#if GL_FMA_MUL
+        "madc.lo.u32 r2, %8, %7, 0;\n\t"
+#else
+        "addc.u32 r2, 0, 0;\n\t"
+#endif
+        "sub.cc.u32 x0, x0, x3;\n\t"
+        "subc.cc.u32 x1, x1, 0;\n\t"
+        "subc.u32 r2, r2, 0;\n\t"
+#if GL_FMA_MUL
+        "mul.lo.u32 n, r2, %9;\n\t"               // -r2
+#else
+        "sub.u32 n, 0, r2;\n\t"
+#endif
+        "shr.s32 eh, r2, 31;\n\t"
+        "add.cc.u32 x0, x0, n;\n\t"
+#if GL_FMA_MUL
+        "madc.lo.u32 x1, eh, %7, x1;\n\t"
+#else
+        "addc.u32 x1, x1, eh;\n\t"
+#endif
+#if GL_FMA_CANON
+        "add.cc.u32 c0, x0, 0xFFFFFFFF;\n\t"     // carries iff x0 != 0
+        "addc.cc.u32 c1, x1, 0;\n\t"             // carries iff x1 == 0xFFFFFFFF and x0 != 0, i.e. x >= p
+        "madc.lo.u32 g, %8, %7, 0;\n\t"          // g = 1 iff x >= p
+        "mad.lo.u32 %0, g, %9, x0;\n\t"          // x0 - g
+        "mad.lo.u32 %1, g, %7, x1;\n\t}"         // x1 + g (0xFFFFFFFF wraps to 0)
+#else
+        "mov.u32 %0, x0;\n\t"
+        "mov.u32 %1, x1;\n\t}"
+#endif
+        : "=r"(r0), "=r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(GL_EPS32_C), "r"(GL_ONE_C), "r"(GL_ZERO_C), "r"(GL_MINUS1_C));
+    u64 r = ((u64)r1 << 32) | r0;
+#if GL_FMA_CANON
+    return r;
+#else
+    return gl_canon_fast(r);
+#endif
+#endif
+}
+
 // a + b (mod p): a lazy, b CANONICAL (< p) -> lazy.  One wrap fix suffices:
 // a + b - 2^64 + EPS <= (2^64-1) + (p-1) - 2^64 + EPS < 2^64.
 __device__ __forceinline__ u64 gl_add_lazy_canon(u64 a, u64 b) {

@@ -21,6 +21,13 @@
 // stride-2^rho accesses of the last group stay conflict-free.  The kernels are bound by integer
 // issue (ALU carry chains + IMAD.WIDE), not by HBM: see DESIGN.md section 3.4 and profiles/.
 #include "internal.h"
+// pipe-balanced multiply + canonicalisation for the butterflies (gl.cuh gl_mul_canon): the transforms are ALU-pipe bound
+#ifndef GL_FMA_MUL
+#define GL_FMA_MUL 1
+#endif
+#ifndef GL_FMA_CANON
+#define GL_FMA_CANON 1
+#endif
 #include "gl.cuh"
 
 #define NTT_THREADS 256
@@ -59,7 +66,7 @@ __device__ __forceinline__ u64 *ntt_out(const NttKParams &P, int col, size_t l) 
     return P.dest[l >> P.dest_lc] + ((size_t)col << P.dest_lc) + (l & (((size_t)1 << P.dest_lc) - 1));
 }
 
-__device__ __forceinline__ u64 gl_mul_c(u64 a, u64 b) { return gl_canon_fast(gl_mul_lazy(a, b)); }
+__device__ __forceinline__ u64 gl_mul_c(u64 a, u64 b) { return gl_mul_canon(a, b); }
 
 // Tile layout in shared memory: W columns of 2^bits points, column j at j * pitch, point p at
 // p + (p >> 5) + (p >> 9).  The padding keeps the stride-2^rho accesses of the last stage group and the
@@ -71,6 +78,12 @@ __device__ __forceinline__ int ntt_sm(int j, int p, int pitch) { return j * pitc
 // bits 5.. into the low bits spreads every such walk over all banks.
 __device__ __forceinline__ int ntt_tw_pos(int e) { return e ^ (e >> 5); }
 #define NTT_IO_UNROLL 8
+#ifndef NTT_LO_VEC
+#define NTT_LO_VEC 1
+#endif
+#ifndef NTT_HI_VEC
+#define NTT_HI_VEC 1
+#endif
 #ifndef NTT_HI_UNROLL
 #define NTT_HI_UNROLL 4
 #endif
@@ -276,6 +289,34 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
         dif_tile(sm, tws, a, w_log, pitch, P.groups);
         NTT_PROF_MARK(1);
         const u64 *__restrict__ post = POST == 2 ? P.post_full + ((size_t)k << P.log_n) + i0_base : nullptr;
+#if NTT_HI_VEC
+        // 128-bit post-factor loads and output stores: a thread takes the pair of adjacent tile columns (j, j + 1) of one
+        // row p, i.e. 16 contiguous bytes of the factor table and of the output
+        if (POST == 2 && w_log >= 1 && !remap) {
+            const int half = n_el >> 1;
+            for (int q0 = threadIdx.x; q0 < half; q0 += blockDim.x * NTT_HI_UNROLL) {
+                u64 v0[NTT_HI_UNROLL], v1[NTT_HI_UNROLL];
+                ulonglong2 f[NTT_HI_UNROLL];
+                size_t oo[NTT_HI_UNROLL];
+#pragma unroll
+                for (int u = 0; u < NTT_HI_UNROLL; u++) {
+                    const int q_raw = q0 + u * blockDim.x;
+                    const int q = q_raw < half ? q_raw : q0;
+                    const int p = q >> (w_log - 1), j = (q & ((W >> 1) - 1)) << 1;
+                    v0[u] = sm[ntt_sm(j, p, pitch)];
+                    v1[u] = sm[ntt_sm(j + 1, p, pitch)];
+                    oo[u] = ((size_t)p << b) + j;
+                    f[u] = __ldg(reinterpret_cast<const ulonglong2 *>(post + oo[u]));
+                }
+#pragma unroll
+                for (int u = 0; u < NTT_HI_UNROLL; u++) {
+                    if (q0 + u * blockDim.x >= half) continue;
+                    __stcs(reinterpret_cast<ulonglong2 *>(dst + i0_base + oo[u]),
+                           make_ulonglong2(gl_mul_c(v0[u], f[u].x), gl_mul_c(v1[u], f[u].y)));
+                }
+            }
+        } else
+#endif
         for (int e0 = threadIdx.x; e0 < n_el; e0 += blockDim.x * NTT_HI_UNROLL) {
             u64 v[NTT_HI_UNROLL], f[NTT_HI_UNROLL];
             size_t oo[NTT_HI_UNROLL];
@@ -331,6 +372,31 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
     const size_t l0 = (size_t)blockIdx.x << (b + w_log);
     u64 *base = P.dst + (size_t)blockIdx.y * P.dst_stride + l0;
     load_twiddles(tws, P.wtab, b);
+#if NTT_LO_VEC
+    // 128-bit global accesses: a thread moves two adjacent points (they stay adjacent in the padded tile: the pad
+    // words sit in front of multiples of 32 and the second point of a pair is odd)
+    const bool vec = b >= 1 && n_el >= 2;
+    if (vec) {
+        const ulonglong2 *__restrict__ base2 = reinterpret_cast<const ulonglong2 *>(base);
+        for (int q0 = threadIdx.x; q0 < n_el / 2; q0 += blockDim.x * NTT_IO_UNROLL) {
+            ulonglong2 v[NTT_IO_UNROLL];
+#pragma unroll
+            for (int u = 0; u < NTT_IO_UNROLL; u++) {
+                const int q = q0 + u * blockDim.x;
+                if (q < n_el / 2) v[u] = __ldcs(base2 + q);
+            }
+#pragma unroll
+            for (int u = 0; u < NTT_IO_UNROLL; u++) {
+                const int e = 2 * (q0 + u * blockDim.x);
+                if (e < n_el) {
+                    u64 *d = sm + ntt_sm(e >> b, e & (S - 1), pitch);
+                    d[0] = v[u].x;
+                    d[1] = v[u].y;
+                }
+            }
+        }
+    } else
+#endif
     for (int e0 = threadIdx.x; e0 < n_el; e0 += blockDim.x * NTT_IO_UNROLL) {
         u64 v[NTT_IO_UNROLL];
 #pragma unroll
@@ -347,6 +413,22 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
     __syncthreads();
     dif_tile(sm, tws, b, w_log, pitch, P.groups);
     const bool scale = P.scale != 1 && !P.post_full;
+#if NTT_LO_VEC
+    if (vec && (P.n_dest == 0 || P.dest_lc >= 1)) {
+        for (int q = threadIdx.x; q < n_el / 2; q += blockDim.x) {
+            const int e = 2 * q;
+            const u64 *srcp = sm + ntt_sm(e >> b, e & (S - 1), pitch);
+            u64 v0 = srcp[0], v1 = srcp[1];
+            if (scale) {
+                v0 = gl_mul_c(v0, P.scale);
+                v1 = gl_mul_c(v1, P.scale);
+            }
+            u64 *o = P.n_dest ? ntt_out(P, blockIdx.y, l0 + e) : base + e;
+            __stcs(reinterpret_cast<ulonglong2 *>(o), make_ulonglong2(v0, v1));
+        }
+        return;
+    }
+#endif
     for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
         u64 v = sm[ntt_sm(e >> b, e & (S - 1), pitch)];
         if (scale) v = gl_mul_c(v, P.scale);
