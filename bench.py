@@ -165,7 +165,27 @@ def issue_roofline(n_perms, ms, sm_mhz):
             "instructions_per_permutation": cost["instructions"], "wide_multiplies_per_permutation": cost["wide"],
             "source": src, "sm_mhz": clk / 1e6,
             "note": "static SASS counts x measured permutation rate; instructions_issued_frac is what ncu reports "
-                    "as smsp__issue_active (70.8 % in profiles/r01_v10_leafhash_ncu_summary.txt)"}
+                    "as smsp__issue_active (70.4 % in profiles/r02_v5_leafhash_ncu_summary.txt, sm__throughput 83.8 %)"}
+
+
+def ntt_issue_roofline(traffic, n_in, n_out, ifft_ms, lde_ms, sm_mhz):
+    """The bound that applies to the transforms, same method as the Poseidon one: warp instructions issued (per-element
+    counts from the committed ncu capture x the elements of the live launch) / live time, against 148 SMs x 4 schedulers x
+    SM clock; `slots` weighs an IMAD.WIDE as three."""
+    ins = (traffic or {}).get("ntt_instructions")
+    if not ins:
+        return None
+    clk = (sm_mhz or 1965.0) * 1e6
+    peak = 148 * 4 * clk
+    w = 1.0 + 2.0 * ins.get("wide_multiply_share", 0.0)
+
+    def one(per_elem, n, ms):
+        warps = per_elem * n / 32.0 / (ms * 1e-3)
+        return {"instructions_per_element": per_elem, "instructions_issued_frac": warps / peak, "frac": warps * w / peak}
+    return {"bound": "issue", "unit": "fraction of 592 schedulers x SM clock", "sm_mhz": clk / 1e6,
+            "ifft": one(ins["ifft_pass_hi_per_element"] + ins["ifft_pass_lo_per_element"], n_in, ifft_ms),
+            "lde": one(ins["lde_pass_hi_per_output_element"] + ins["lde_pass_lo_per_output_element"], n_out, lde_ms),
+            "source": ins.get("source")}
 
 
 def cpu_reference_arm(args, rank, world):
@@ -595,8 +615,10 @@ def gpu_arm(args, rank, world, local_rank):
             "lde": dict(roof(8 * elems + 8 * nb * N_COLS, avg["lde_ms"], traffic.get("lde")),
                         algorithmic_bytes=8 * elems + 8 * nb * N_COLS),
             "pipes": {k: v for k, v in (traffic.get("pipes") or {}).items() if k.startswith("ntt")},
-            "note": "two kernels each (pass HI + pass LO); bound by integer issue (ALU pipe 74-76 % busy in both passes), "
-                    "not by HBM: a Goldilocks butterfly is ~36 integer instructions per 16 bytes moved (DESIGN.md 3.4)",
+            "issue": ntt_issue_roofline(traffic, elems, nb * N_COLS, avg["ifft_ms"], avg["lde_ms"], (clocks or {}).get("sm_mhz")),
+            "note": "two kernels each (pass HI + pass LO); bound by integer issue / dispatch slots, not by HBM: a Goldilocks "
+                    "butterfly is ~33 integer instructions per 16 bytes moved, ~500 instructions per element (DESIGN.md 3.4); "
+                    "`issue` is the bound that applies, the HBM fractions are low by construction",
         },
         "whole_commit": dict(roof(8 * elems * (2 + (1 << RATE_BITS)) + 64 * nb, ms),
                              algorithmic_bytes=8 * elems * (2 + (1 << RATE_BITS)) + 64 * nb),
