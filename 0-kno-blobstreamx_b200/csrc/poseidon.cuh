@@ -6,30 +6,18 @@
 //
 // B200 shape of the computation (measured choices):
 //  * state lives in registers as LAZY u64 (any representative), canonicalised only on output;
-//  * full rounds: x^7 by four lazy multiplies; the MDS layer runs on 32-bit halves with
-//    IMAD.WIDE accumulation, and the NEXT round's constants are the accumulators' initial values,
-//    so constant addition costs no instruction;
-//  * partial rounds use the sparse factorisation (23 multiplies instead of a dense 12x12 layer);
-//    its constants are derived by tools/gen_poseidon_constants.py and checked against the naive form;
+//  * full rounds: x^7 by two squarings and two multiplies (lazy); every MDS layer is multiplication-free on three
+//    22-bit limb planes (poseidon_mds.cuh), the NEXT round's constants riding as third addends;
+//  * partial rounds keep lanes 1..11 as limb planes from round to round (only lane 0 is merged for its S-box);
+//    the CPU provers' sparse factorisation (23 full-width multiplies per round) is dearer on a machine whose only
+//    multiplier is 32x32->64 at quarter rate -- that variant lives in tools/microbench/poseidon_v7_sparse.cuh;
 //  * one shared full-round body and one partial-round body (no unrolling over rounds): the whole
-//    permutation is ~30 KB of SASS and stays inside the instruction cache (v1 was 112 KB and stalled
+//    permutation is ~34 KB of SASS and stays inside the instruction cache (v1 was 112 KB and stalled
 //    on instruction fetch for 12.6 warp-cycles per issue).
 #pragma once
 #include "gl.cuh"
 #include "poseidon_mds.cuh"
 #include "poseidon_rc.h"
-
-// 1: multiplication-free MDS on 22-bit limb planes (poseidon_mds.cuh); 0: IMAD.WIDE accumulation on halves
-#ifndef POSEIDON_MDS_FFT
-#define POSEIDON_MDS_FFT 1
-#endif
-
-// 1: partial rounds keep lanes 1..11 as 22-bit limb planes from round to round and use the same
-//    multiplication-free dense MDS as the full rounds (only lane 0 is merged for its S-box);
-// 0: sparse factorisation of the partial rounds (23 full-width multiplies per round).
-#ifndef POSEIDON_PARTIAL_PLANES
-#define POSEIDON_PARTIAL_PLANES 1
-#endif
 
 __constant__ __align__(16) u32 POSEIDON_POST30_L22[30 * 36] = {POSEIDON_POST30_L22_LIST};
 // one round's 36 plane constants through nine 128-bit uniform loads (36 LDCU otherwise: issue slots)
@@ -42,15 +30,6 @@ __device__ __forceinline__ void poseidon_load_post(int round, u32 k[36]) {
     }
 }
 __constant__ u64 POSEIDON_RC[POSEIDON_N_RC] = {POSEIDON_RC_LIST};
-#if !POSEIDON_PARTIAL_PLANES  // constants of the sparse partial rounds (v7 path, kept for A/B builds)
-__constant__ u64 POSEIDON_POST_LO[96] = {POSEIDON_POST_LO_LIST};
-__constant__ u64 POSEIDON_POST_HI[96] = {POSEIDON_POST_HI_LIST};
-__constant__ u32 POSEIDON_POST_L22[8 * 36] = {POSEIDON_POST_L22_LIST};
-__constant__ u64 POSEIDON_FAST_INIT[121] = {POSEIDON_FAST_INIT_LIST};
-__constant__ u64 POSEIDON_FAST_K[22] = {POSEIDON_FAST_K_LIST};
-__constant__ u64 POSEIDON_FAST_V[242] = {POSEIDON_FAST_V_LIST};
-__constant__ u64 POSEIDON_FAST_W[242] = {POSEIDON_FAST_W_LIST};
-#endif
 
 __device__ __forceinline__ u64 poseidon_sbox(u64 x) {
     u64 x2 = gl_sqr_lazy(x), x4 = gl_sqr_lazy(x2), x3 = gl_mul_lazy(x, x2);
@@ -71,32 +50,6 @@ __device__ __forceinline__ u64 poseidon_fold96(u64 al, u64 ah) {
         : "=&r"(r0), "=&r"(r1)
         : "r"(t0), "r"(t1), "r"(hl));
     return ((u64)r1 << 32) | r0;
-}
-
-// MDS layer with the following constant vector fused: s <- M s + post, post given as 32-bit halves.
-__device__ __forceinline__ void poseidon_mds_post(u64 s[12], const u64 *__restrict__ post_lo,
-                                                  const u64 *__restrict__ post_hi) {
-    const u32 C[12] = {17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20};
-    u32 lo[12], hi[12];
-#pragma unroll
-    for (int i = 0; i < 12; i++) {
-        lo[i] = (u32)s[i];
-        hi[i] = (u32)(s[i] >> 32);
-    }
-#pragma unroll
-    for (int r = 0; r < 12; r++) {
-        u64 al = post_lo[r], ah = post_hi[r];
-#pragma unroll
-        for (int i = 0; i < 12; i++) {
-            al += (u64)C[i] * lo[(i + r) % 12];
-            ah += (u64)C[i] * hi[(i + r) % 12];
-        }
-        if (r == 0) {
-            al += (u64)8 * lo[0];
-            ah += (u64)8 * hi[0];
-        }
-        s[r] = poseidon_fold96(al, ah);
-    }
 }
 
 // o0 + o1 2^22 + o2 2^44 (o_k < 2^32) -> lazy u64.  Three words w2:w1:w0 with w2 < 2^13, then
@@ -166,7 +119,6 @@ __device__ __forceinline__ void poseidon_norm22(u32 &y0, u32 &y1, u32 &y2) {
     y2 += (u32)c1;
 }
 
-#if POSEIDON_PARTIAL_PLANES
 // lazy in, lazy out.  Round r: S-box, then s <- M s + RC[r + 1] (the constants ride as third addends).
 __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
 #pragma unroll
@@ -208,56 +160,6 @@ __device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
         }
     }
 }
-#else
-// lazy in, lazy out
-__device__ __forceinline__ void poseidon_permute_lazy(u64 s[12]) {
-#pragma unroll
-    for (int i = 0; i < 12; i++) s[i] = gl_add_lazy_canon(s[i], POSEIDON_RC[i]);
-#pragma unroll 1
-    for (int half = 0; half < 2; half++) {
-#pragma unroll 1
-        for (int r = 0; r < 4; r++) {
-#pragma unroll
-            for (int i = 0; i < 12; i++) s[i] = poseidon_sbox(s[i]);
-            const int j = half * 4 + r;
-#if POSEIDON_MDS_FFT
-            poseidon_mds_post_fft(s, POSEIDON_POST_L22 + 36 * j);
-#else
-            poseidon_mds_post(s, POSEIDON_POST_LO + 12 * j, POSEIDON_POST_HI + 12 * j);
-#endif
-        }
-        if (half == 0) {
-            // mds_partial_layer_init: x[1:] <- INIT x[1:] (dense 11x11, once per permutation).  Rows are
-            // produced by a rolled loop into a small local array to keep the code short.
-            u64 t[11];
-#pragma unroll 1
-            for (int r = 0; r < 11; r++) {
-                gl_acc3 A = gl_acc3_zero();
-#pragma unroll
-                for (int c = 0; c < 11; c++) gl_acc3_mac(A, s[1 + c], POSEIDON_FAST_INIT[11 * r + c]);
-                t[r] = gl_acc3_reduce(A);
-            }
-#pragma unroll
-            for (int r = 0; r < 11; r++) s[1 + r] = t[r];
-#pragma unroll 1
-            for (int p = 0; p < 22; p++) {
-                u64 s0 = gl_add_lazy_canon(poseidon_sbox(s[0]), POSEIDON_FAST_K[p]);
-                // d = 25 s0 + V[p] . x[1:]
-                gl_acc3 A = gl_acc3_zero();
-                gl_acc3_mac(A, s0, 25);
-#pragma unroll
-                for (int i = 0; i < 11; i++) gl_acc3_mac(A, s[1 + i], POSEIDON_FAST_V[11 * p + i]);
-#pragma unroll
-                for (int i = 0; i < 11; i++) s[1 + i] = gl_mul_add_lazy(s0, POSEIDON_FAST_W[11 * p + i], s[1 + i]);
-                s[0] = gl_acc3_reduce(A);
-            }
-#pragma unroll
-            for (int i = 0; i < 12; i++) s[i] = gl_add_lazy_canon(s[i], POSEIDON_RC[12 * 26 + i]);
-        }
-    }
-}
-
-#endif
 
 // state canonical (or lazy) in, canonical out
 __device__ __forceinline__ void poseidon_permute(u64 s[12]) {

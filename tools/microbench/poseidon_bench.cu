@@ -1,10 +1,17 @@
 // poseidon_bench.cu -- register-resident Poseidon throughput (no memory traffic) + KAT check.
-// Build variants with -DPOSEIDON_MDS_FFT=0/1; run on the GPU box:
+// -DPOSEIDON_V7=1 times the round-1 sparse-partial-round permutation (poseidon_v7_sparse.cuh) instead of the shipped one.
 //   nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o pb poseidon_bench.cu && ./pb
 #include <cstdio>
 #include <cstdlib>
 #include <cuda_runtime.h>
 #include "../../0-kno-blobstreamx_b200/csrc/poseidon.cuh"
+#ifndef POSEIDON_V7
+#define POSEIDON_V7 0
+#endif
+#if POSEIDON_V7
+#include "poseidon_v7_sparse.cuh"
+#define poseidon_permute_lazy poseidon_permute_lazy_v7
+#endif
 
 __global__ void __launch_bounds__(256) chain(u64 *out, int iters) {
     size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -68,7 +75,7 @@ int main(int argc, char **argv) {
         cudaEventElapsedTime(&ms, e0, e1);
         if (ms < best) best = ms;
     }
-    printf("MDS_FFT=%d : %.3f ms for %zu perms -> %.3f Gperm/s  (%s)\n", POSEIDON_MDS_FFT, best,
+    printf("V7=%d : %.3f ms for %zu perms -> %.3f Gperm/s  (%s)\n", POSEIDON_V7, best,
            n * iters, n * (double)iters / best / 1e6, cudaGetErrorString(cudaGetLastError()));
     return bad != 0;
 }
