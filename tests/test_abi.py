@@ -73,3 +73,55 @@ def test_header_is_plain_c_and_links():
         assert r.returncode == 1 and "no CPU fallback" in r.stderr, r.stderr
     else:
         assert r.stdout.startswith("cap ")
+
+
+def _gen_rust_sys():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("gen_rust_sys", os.path.join(ROOT, "tools", "gen_rust_sys.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_rust_sys_bindings_match_the_header():
+    """rust/bsx-b200-sys/src/lib.rs is what tools/gen_rust_sys.py derives from the header (no rustc here to run
+    bindgen): one `pub fn` per exported symbol, nothing stale."""
+    g = _gen_rust_sys()
+    text, names = g.render()
+    assert open(g.OUT).read() == text, "run `python tools/gen_rust_sys.py`: the committed bindings are stale"
+    assert sorted(names) == _header_symbols()
+    for name in names:
+        assert len(re.findall(r"pub fn %s\(" % name, text)) == 1
+
+
+def test_rust_shim_calls_exist_with_the_header_arity():
+    """Every `sys::bsx_*(..)` call in rust/plonky2-bsx-shim names a function of the header and passes as many arguments
+    as the header declares (the crate cannot be compiled in this image)."""
+    import glob
+    g = _gen_rust_sys()
+    consts, opaque, structs, funcs = g.parse(open(g.HEADER).read())
+    arity = {n: len(p) for n, p, _ in funcs}
+    types = {o[1] for o in opaque} | {s[0] for s in structs}
+    n_calls = 0
+    for path in glob.glob(os.path.join(ROOT, "rust", "plonky2-bsx-shim", "src", "*.rs")):
+        src = open(path).read()
+        for m in re.finditer(r"sys::(bsx_\w+)\s*\(", src):
+            name = m.group(1)
+            if name in types:
+                continue
+            assert name in arity, "%s calls %s, which the header does not declare" % (os.path.basename(path), name)
+            i, depth, commas, body = m.end(), 1, 0, ""
+            while depth:
+                ch = src[i]
+                depth += ch in "([{"
+                depth -= ch in ")]}"
+                if depth == 1 and ch == ",":
+                    commas += 1
+                elif depth >= 1:
+                    body += ch
+                i += 1
+            n_args = commas + (1 if body.strip() else 0)
+            assert n_args == arity[name], "%s: %s called with %d arguments, declared with %d" % (
+                os.path.basename(path), name, n_args, arity[name])
+            n_calls += 1
+    assert n_calls >= 20
