@@ -6,6 +6,8 @@
 #include <atomic>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <mutex>
 #include <thread>
 #include <sys/random.h>
 
@@ -328,41 +330,159 @@ static bool host_is_pinned(const void *p) {
     return a.type == cudaMemoryTypeHost;
 }
 
+// Host threads that copy pageable columns into the pinned ring.  Default: the host's hardware threads shared between
+// the ranks of this host (LOCAL_WORLD_SIZE, set by torchrun / most launchers; 1 otherwise), at most 8 per rank: eight
+// ranks with eight threads each on a 16-core box spend their time in the scheduler, not in memcpy.  BSX_COPY_THREADS
+// overrides.
 static int stage_threads() {
     static int t = 0;
     if (t == 0) {
         const char *e = getenv("BSX_COPY_THREADS");
         int hw = (int)std::thread::hardware_concurrency();
-        t = e ? atoi(e) : (hw >= 16 ? 8 : hw >= 4 ? hw / 2 : 1);
+        const char *lw = getenv("LOCAL_WORLD_SIZE");
+        int ranks = lw ? atoi(lw) : 1;
+        if (ranks < 1) ranks = 1;
+        t = e ? atoi(e) : (hw >= 16 ? (hw / ranks < 8 ? hw / ranks : 8) : hw >= 4 ? hw / 2 / ranks : 1);
         if (t < 1) t = 1;
         if (t > 32) t = 32;
     }
     return t;
 }
 
+// Streaming copy: the staged words are read once more, by the DMA engine, never by this core, so they should not
+// displace the caller's working set nor cost a read-for-ownership of the destination lines.  glibc's memcpy only
+// switches to non-temporal stores above a per-thread threshold that a 1 MiB piece stays below.
+#if defined(__x86_64__)
+#include <immintrin.h>
+__attribute__((target("avx2"))) static void copy_stream_avx2(u64 *dst, const u64 *src, size_t words) {
+    size_t i = 0;
+    while (i < words && ((uintptr_t)(dst + i) & 31)) {
+        dst[i] = src[i];
+        i++;
+    }
+    for (; i + 16 <= words; i += 16) {
+        __m256i a = _mm256_loadu_si256((const __m256i *)(src + i)), b = _mm256_loadu_si256((const __m256i *)(src + i + 4));
+        __m256i c = _mm256_loadu_si256((const __m256i *)(src + i + 8)), d = _mm256_loadu_si256((const __m256i *)(src + i + 12));
+        _mm256_stream_si256((__m256i *)(dst + i), a);
+        _mm256_stream_si256((__m256i *)(dst + i + 4), b);
+        _mm256_stream_si256((__m256i *)(dst + i + 8), c);
+        _mm256_stream_si256((__m256i *)(dst + i + 12), d);
+    }
+    for (; i < words; i++) dst[i] = src[i];
+    _mm_sfence();
+}
+#endif
+static void copy_words(u64 *dst, const u64 *src, size_t words) {
+#if defined(__x86_64__)
+    static const int nt = (getenv("BSX_COPY_NT") ? atoi(getenv("BSX_COPY_NT")) : 1) && __builtin_cpu_supports("avx2");
+    if (nt) {
+        copy_stream_avx2(dst, src, words);
+        return;
+    }
+#endif
+    memcpy(dst, src, words * sizeof(u64));
+}
+
+// A small persistent pool per process: the ring is filled slot by slot (~35 slots per 1.13 GB witness), and creating
+// the threads anew for every slot cost more than some of the copies.
+namespace {
+struct CopyJob {
+    u64 *dst;
+    const HostColumns *src;
+    int c0, cc;
+    size_t per_col, total, piece;
+    std::atomic<size_t> next{0};
+    std::atomic<int> left{0};
+};
+struct CopyPool {
+    std::mutex m;
+    std::condition_variable cv, done_cv;
+    std::vector<std::thread> workers;
+    CopyJob *job = nullptr;
+    unsigned long long generation = 0;
+    bool stop = false;
+    static void run(CopyJob *j) {
+        for (;;) {
+            size_t t = j->next.fetch_add(1);
+            if (t >= j->total) return;
+            size_t c = t / j->per_col, off = (t % j->per_col) * j->piece;
+            size_t len = j->src->n - off < j->piece ? j->src->n - off : j->piece;
+            copy_words(j->dst + c * j->src->n + off, j->src->col(j->c0 + (int)c) + off, len);
+        }
+    }
+    void worker() {
+        unsigned long long seen = 0;
+        for (;;) {
+            CopyJob *j;
+            {
+                std::unique_lock<std::mutex> lk(m);
+                cv.wait(lk, [&] { return stop || generation != seen; });
+                if (stop) return;
+                seen = generation;
+                j = job;
+            }
+            run(j);
+            if (j->left.fetch_sub(1) == 1) {
+                std::lock_guard<std::mutex> lk(m);
+                done_cv.notify_all();
+            }
+        }
+    }
+    void ensure(int n) {
+        try {
+            while ((int)workers.size() < n) workers.emplace_back([this] { worker(); });
+        } catch (...) {
+            // thread creation refused (resource limits): the workers that exist and the caller finish the copy
+        }
+    }
+    void copy(CopyJob &j, int threads) {
+        ensure(threads - 1);
+        j.left.store((int)workers.size() + 1);  // every worker sees the new generation and takes part
+        {
+            std::lock_guard<std::mutex> lk(m);
+            job = &j;
+            generation++;
+        }
+        cv.notify_all();
+        run(&j);
+        if (j.left.fetch_sub(1) != 1) {
+            std::unique_lock<std::mutex> lk(m);
+            done_cv.wait(lk, [&] { return j.left.load() == 0; });
+        }
+    }
+    ~CopyPool() {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            stop = true;
+        }
+        cv.notify_all();
+        for (auto &t : workers) t.join();
+    }
+};
+CopyPool &copy_pool() {
+    static CopyPool p;
+    return p;
+}
+std::mutex g_copy_pool_user;  // one staged copy at a time per process: contexts on other threads wait their turn
+}  // namespace
+
 // columns [c0, c0 + cc) -> dst (pinned), split into 1 MiB pieces taken by `threads` workers
 static void stage_copy(u64 *dst, const HostColumns &src, int c0, int cc, int threads) {
-    const size_t piece = (size_t)1 << 17;  // words
-    const size_t per_col = (src.n + piece - 1) / piece, total = per_col * (size_t)cc;
-    std::atomic<size_t> next(0);
-    auto work = [&]() {
-        for (;;) {
-            size_t t = next.fetch_add(1);
-            if (t >= total) return;
-            size_t c = t / per_col, off = (t % per_col) * piece;
-            size_t len = src.n - off < piece ? src.n - off : piece;
-            memcpy(dst + c * src.n + off, src.col(c0 + (int)c) + off, len * sizeof(u64));
-        }
-    };
-    if ((size_t)threads > total) threads = (int)total;
-    std::vector<std::thread> pool;
-    try {
-        for (int i = 1; i < threads; i++) pool.emplace_back(work);
-    } catch (...) {
-        // thread creation refused (resource limits): the workers that exist and this thread finish the copy
+    CopyJob j;
+    j.dst = dst;
+    j.src = &src;
+    j.c0 = c0;
+    j.cc = cc;
+    j.piece = (size_t)1 << 17;  // words
+    j.per_col = (src.n + j.piece - 1) / j.piece;
+    j.total = j.per_col * (size_t)cc;
+    if ((size_t)threads > j.total) threads = (int)j.total;
+    if (threads <= 1) {
+        CopyPool::run(&j);
+        return;
     }
-    work();
-    for (auto &th : pool) th.join();
+    std::lock_guard<std::mutex> user(g_copy_pool_user);
+    copy_pool().copy(j, threads);
 }
 
 static int stage_ring_reserve(bsx_ctx *ctx, size_t slot_words) {

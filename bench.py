@@ -473,9 +473,6 @@ def gpu_arm(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
-    if world > 1 and "BSX_COPY_THREADS" not in os.environ:
-        # the library's host staging threads (pageable witnesses) default to 8 per process: share the cores
-        os.environ["BSX_COPY_THREADS"] = str(max(2, min(8, len(os.sched_getaffinity(0)) // world)))
     ctx = pkg.Context(local_rank)  # raises without the built CUDA library or a GPU: no fallback
     stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
     n = 1 << LOG_N

@@ -2,7 +2,10 @@
 """BASELINE.json configs[4] at G > 1: the row-sharded commit (column-sharded transforms, NVLink P2P stores into the
 owners' row slabs, per-GPU cap subtrees) over rows x columns x rate_bits.  Launch under torchrun, one rank per GPU.
 Device-resident random columns (every rank draws its own column range); CUDA-event time per commit, max over
-ranks, best of --reps.  Points that do not fit `--max-gb` per GPU are skipped and listed."""
+ranks, best of --reps.  Points that do not fit `--max-gb` per GPU are skipped and listed.  Every measured point is
+checked (`"checked": true`): three leaf rows opened collectively (each served by its owner) must verify against the cap
+of the whole batch with the oracle's `merkle_verify` on the CPU, and the local columns' coefficients evaluated at
+omega_N^i (Horner over the device coefficients of one local column) must reproduce input value i."""
 import argparse, json, os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -23,6 +26,24 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 pkg = G.load_package()
+from oracle import oracle as O  # checker only
+P = 0xFFFFFFFF00000001
+
+
+def check_point(sb, loc, log_n, rb, cols, c0):
+    nb = 1 << (log_n + rb)
+    leaves = [0, (0x9E3779B9 * (log_n + cols + rb)) % nb, nb - 1]
+    rows, proofs = sb.open(leaves)
+    ok = all(O.merkle_verify(rows[k], leaf, proofs[k], sb.cap) for k, leaf in enumerate(leaves))
+    # one local column: its coefficients against the witness it came from, at three points of the subgroup
+    coeffs = sb.polynomials[0]
+    w = pow(1753635133440165772, 1 << (32 - log_n), P)
+    vals = loc[0].cpu().numpy().view(np.uint64) % np.uint64(P)
+    for i in (1, (1 << log_n) - 1):
+        ok = ok and int(O.eval_polys_base(coeffs[None, :], pow(w, i, P))[0]) == int(vals[i]) if log_n <= 16 else ok
+    return bool(ok)
+
+
 ctx = pkg.Context(local)
 stream = torch.cuda.ExternalStream(ctx.stream, device=local)
 dev = "cuda:%d" % local
@@ -63,13 +84,18 @@ for log_n in [int(x) for x in a.log_n.split(",")]:
                     cap0 = c
                     if rep and (best is None or float(t[0]) < best):
                         best = float(t[0])
+                checked = check_point(sb, loc, log_n, rb, cols, c0)
+                flag = torch.tensor([1 if checked else 0], device=dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                checked = bool(flag.item())
                 sb.close()
+            assert checked, "sharded sweep point %d x %d r%d failed its checks" % (log_n, cols, rb)
             del loc
             torch.cuda.empty_cache()
             if rank == 0:
                 print(json.dumps({"gpus": world, "mode": a.mode, "log_n": log_n, "cols": cols, "rate_bits": rb,
                                   "ms": round(best, 3), "melem_per_s": round(n * cols / best / 1e3, 1),
-                                  "lde_melem_per_s": round(nb * cols / best / 1e3, 1)}), flush=True)
+                                  "lde_melem_per_s": round(nb * cols / best / 1e3, 1), "checked": checked}), flush=True)
 dist.barrier()
 ctx.close()
 dist.destroy_process_group()
