@@ -206,19 +206,20 @@ static int shard_transform_enqueue(bsx_shard *s, const uint64_t *input, int32_t 
     cudaGetLastError();
     int rc = BSX_OK;
     if (pinned && n_local >= 8 && s->log_n >= 13) {
-        // only the first chunk's copy is exposed: start small (4 columns, then 8), then thirds of the rest
+        // Only the first chunk's copy is exposed, so the schedule starts small; chunk sizes follow the transform grid
+        // (128 tiles per column at 2^20 rows against 444 resident CTAs: 3 or 7 columns fill whole waves, 4 would leave
+        // the second wave 15 % full): 3, 3, 4, then sevens.
         std::vector<int> cstart;
         {
             int c = 0;
-            for (int r : {4, 8})
-                if (n_local - c >= 2 * r) {
+            for (int r : {3, 3, 4})
+                if (n_local - c >= r + 3) {
                     cstart.push_back(c);
                     c += r;
                 }
-            const int rest = n_local - c, parts = rest >= 24 ? 3 : rest >= 12 ? 2 : 1, per = (rest + parts - 1) / parts;
             while (c < n_local) {
                 cstart.push_back(c);
-                c += per;
+                c += (n_local - c >= 10) ? 7 : n_local - c;
             }
             cstart.push_back(n_local);
         }

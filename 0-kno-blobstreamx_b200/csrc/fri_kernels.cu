@@ -15,40 +15,6 @@ struct DevChallenger {
     int n_in, n_out;
 };
 
-// The Fiat-Shamir transcript is a chain of dependent permutations, so what counts is the LATENCY of one
-// permutation: a single thread takes ~39 us (30 rounds x 12 S-boxes back to back).  Here lane i < 12 of one warp
-// owns state word i: the twelve S-boxes of a full round run side by side and the MDS row of every lane is
-// gathered with shuffles (Poseidon::poseidon in its naive form, hash/poseidon.rs `poseidon_naive`; all words
-// canonical).  ~5 us per permutation.
-__device__ __forceinline__ u64 poseidon_permute_warp(u64 x, int lane) {
-    const u32 C[12] = {17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20};
-    const int me = lane < 12 ? lane : 0;
-    for (int r = 0; r < 30; r++) {
-        x = gl_add(x, POSEIDON_RC[12 * r + me]);
-        const bool full = r < 4 || r >= 26;
-        if (full || lane == 0) {
-            u64 x2 = gl_mul_lazy(x, x), x4 = gl_mul_lazy(x2, x2);  // lazy words are fine for the halves below
-            x = gl_mul_lazy(gl_mul_lazy(x, x2), x4);
-        }
-        // y[lane] = sum_i C[i] x[(lane + i) % 12] (+ 8 x[0] for lane 0), on 32-bit halves
-        const u32 lo = (u32)x, hi = (u32)(x >> 32);
-        u64 al = 0, ah = 0;
-#pragma unroll
-        for (int i = 0; i < 12; i++) {
-            int src = me + i;
-            src = src >= 12 ? src - 12 : src;
-            al += (u64)C[i] * __shfl_sync(0xFFFFFFFFu, lo, src);
-            ah += (u64)C[i] * __shfl_sync(0xFFFFFFFFu, hi, src);
-        }
-        if (lane == 0) {
-            al += (u64)8 * lo;
-            ah += (u64)8 * hi;
-        }
-        x = gl_canon(poseidon_fold96(al, ah));
-    }
-    return x;
-}
-
 // every function below is executed by all 32 lanes of the kernel's single warp on a challenger in shared memory
 __device__ void chal_duplex(DevChallenger *c, int lane) {
     __syncwarp();

@@ -466,6 +466,9 @@ def prove_arm(args, pkg, ctx, stream, rank, world, local_rank, wires_np):
 
 
 def gpu_arm(args, rank, world, local_rank):
+    # stdout carries exactly one JSON line: whatever libraries print there (NCCL's version banner) goes to stderr
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     import __graft_entry__ as G
@@ -664,7 +667,7 @@ def gpu_arm(args, rank, world, local_rank):
             "sample": "the whole 2^%d rows x %d cols commit, once (rate_bits %d, cap_height %d), scalar OpenMP C oracle; "
                       "a CPU restatement, not the plonky2 crate (no AVX2/AVX-512 Poseidon)" % (LOG_N, N_COLS, RATE_BITS, CAP_HEIGHT)}
         assert out["parity"]["cap_equal"] and rows_ok and paths_ok, "device commit differs from the oracle at the headline size"
-    print(json.dumps(out))
+    print(json.dumps(out), file=real_stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
