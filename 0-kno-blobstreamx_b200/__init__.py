@@ -54,7 +54,10 @@ from .plonk import (  # noqa: F401
     CircuitDescription,
     Gate,
     SyntheticCircuit,
+    circuit_digest,
     compute_quotient_polys,
+    hash_no_pad,
+    prove,
     quotient_values,
     synthetic_circuit,
 )

@@ -162,7 +162,7 @@ class SyntheticCircuit:
 
 
 def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_routed_wires=80, num_ops=20,
-                      quotient_degree_factor=8, rate_bits=3, num_challenges=2):
+                      quotient_degree_factor=8, rate_bits=3, num_challenges=2, public_inputs_hash=None):
     """A circuit of NoopGate / ConstantGate / PublicInputGate / ArithmeticGate rows (one selector group) with random
     constants, `n_copies` copy constraints between free arithmetic inputs, and a witness that satisfies all of it."""
     n = 1 << degree_bits
@@ -180,7 +180,7 @@ def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_rou
     rand = lambda shape: rng.integers(0, P, size=shape, dtype=np.uint64)
     constants = np.stack([sel, rand(n), rand(n)])
     wires = rand((num_wires, n))
-    pih = rand(4)
+    pih = rand(4) if public_inputs_hash is None else np.array(public_inputs_hash, dtype=np.uint64).reshape(4).copy()
     # copy constraints: disjoint pairs of free cells (multiplicands / addends of arithmetic rows)
     arith_rows = np.nonzero(sel == 3)[0]
     free = [(4 * i + t, r) for r in arith_rows[: 4096] for i in range(num_ops) for t in range(3)]
@@ -214,3 +214,74 @@ def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_rou
     jj, rr = flat // n, flat % n
     sig.reshape(-1)[:] = np.array([k[j] * omegas[r] % P for j, r in zip(jj, rr)], dtype=np.uint64)
     return SyntheticCircuit(circ, constants, sig, wires, pih)
+
+
+# ---------------------------------------------------------------------------------------------
+def hash_no_pad(ctx, elems):
+    """plonky2 hash/hashing.rs `hash_n_to_hash_no_pad` (overwrite-mode sponge, rate 8) with the permutations on the
+    device: host-side glue for the few small hashes of prove() (public inputs, circuit digest)."""
+    state = np.zeros(12, dtype=np.uint64)
+    e = _np(elems).reshape(-1)
+    for off in range(0, e.size, 8):
+        chunk = e[off:off + 8]
+        state[:chunk.size] = chunk
+        state = ctx.poseidon_permute(state)
+    return state[:4].copy()
+
+
+def circuit_digest(ctx, constants_sigmas_cap, degree_bits):
+    """plonk/circuit_builder.rs: `circuit_digest = hash_no_pad(constants_sigmas_cap.flatten() ++ [degree_bits])` (the
+    revisions BlobstreamX could pin differ in what else they append; the synthetic prove uses this form)."""
+    parts = np.concatenate([_np(constants_sigmas_cap).reshape(-1), np.array([degree_bits], dtype=np.uint64)])
+    return hash_no_pad(ctx, parts)
+
+
+def prove(ctx, sc, fri_config, public_inputs, constants_sigmas=None):
+    """plonk/prover.rs `prove()` for a SyntheticCircuit, commitment phase on the device end to end: wires commitment,
+    challenges, Zs and partial products (device), their commitment, the quotient evaluated from the resident LDEs and
+    committed, the opening set at zeta and g zeta, prove_openings.  The witness is given (sc.wires): witness generation is
+    upstream's sequential generator pass and out of scope.  Returns (ProofWithPublicInputs, dict of what a verifier needs
+    besides the proof: circuit digest, constants_sigmas cap, FRI parameters, oracle widths)."""
+    from .fri import Challenger, FriInstanceInfo, prove_openings
+    from .proof import OpeningSet, Proof, ProofWithPublicInputs
+    c = sc.circuit
+    n, nc = 1 << c.degree_bits, c.num_challenges
+    fp = fri_config.fri_params(c.degree_bits)
+    own_cs = constants_sigmas is None
+    if own_cs:  # circuit data: committed at build time upstream
+        constants_sigmas = PolynomialBatch.from_values(ctx, np.concatenate([sc.constants, sc.sigmas]), fri_config.rate_bits,
+                                                       False, fri_config.cap_height)
+    digest = circuit_digest(ctx, constants_sigmas.cap, c.degree_bits)
+    pih = hash_no_pad(ctx, public_inputs)
+    if not (pih == _np(sc.public_inputs_hash)).all():
+        raise BsxError("the witness was built for another public-input hash")
+    ch = Challenger(ctx)
+    ch.observe_hash(digest)
+    ch.observe_hash(pih)
+    wires = PolynomialBatch.from_values(ctx, sc.wires, fri_config.rate_bits, False, fri_config.cap_height)
+    ch.observe_cap(wires.cap)
+    betas, gammas = ch.get_n_challenges(nc), ch.get_n_challenges(nc)
+    zs_vals = ctx.partial_products_and_zs(sc.wires[:c.num_routed_wires], sc.sigmas, c.k_is, betas, gammas,
+                                          c.quotient_degree_factor)
+    zs = PolynomialBatch.from_values(ctx, zs_vals, fri_config.rate_bits, False, fri_config.cap_height)
+    ch.observe_cap(zs.cap)
+    alphas = ch.get_n_challenges(nc)
+    quotient = compute_quotient_polys(ctx, c, constants_sigmas, wires, zs, pih, betas, gammas, alphas, fri_config.cap_height)
+    ch.observe_cap(quotient.cap)
+    zeta = ch.get_extension_challenge()
+    g = pow(1753635133440165772, 1 << (32 - c.degree_bits), P)  # F::primitive_root_of_unity(degree_bits)
+    openings = OpeningSet.new(zeta, g, constants_sigmas, wires, zs, quotient, c.num_constants, nc)
+    for batch in openings.to_fri_openings():  # challenger.observe_openings
+        ch.observe_extension_elements(batch.reshape(-1))
+    widths = [c.num_constants + c.num_routed_wires, c.num_wires, nc * (1 + c.num_partial_products),
+              nc * c.quotient_degree_factor]
+    gz = np.array([int(zeta[0]) * g % P, int(zeta[1]) * g % P], dtype=np.uint64)
+    instance = FriInstanceInfo(np.stack([zeta, gz]), [[(o, j) for o, w in enumerate(widths) for j in range(w)],
+                                                      [(2, j) for j in range(nc)]])
+    oracles = [constants_sigmas, wires, zs, quotient]
+    opening_proof = prove_openings(instance, oracles, ch, fp)
+    pw = ProofWithPublicInputs(Proof(wires.cap, zs.cap, quotient.cap, openings, opening_proof), _np(public_inputs).reshape(-1))
+    aux = {"circuit_digest": digest, "constants_sigmas_cap": constants_sigmas.cap, "fri_params": fp, "widths": widths}
+    for b in oracles[1:] + ([constants_sigmas] if own_cs else []):
+        b.close()
+    return pw, aux

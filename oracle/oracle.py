@@ -421,6 +421,27 @@ def vanishing_at(circuit, x, constants_sigmas_row, wires_row, zs_pp_row, next_zs
     return out
 
 
+def vanishing_at_ext(circuit, zeta, openings, public_inputs_hash, betas, gammas, alphas):
+    """plonk/vanishing_poly.rs eval_vanishing_poly at the extension point zeta from an opening set (dict or object with
+    constants, plonk_sigmas, wires, plonk_zs, plonk_zs_next, partial_products: (n, 2) arrays) -> (num_challenges, 2)."""
+    c, keep = _circuit(circuit)
+    get = (lambda k: openings[k]) if isinstance(openings, dict) else (lambda k: getattr(openings, k))
+    ops = [_a(get(k)).reshape(-1) for k in ("constants", "plonk_sigmas", "wires", "plonk_zs", "plonk_zs_next", "partial_products")]
+    z, pih, b, g, al = _a(zeta), _a(public_inputs_hash), _a(betas), _a(gammas), _a(alphas)
+    out = np.zeros((circuit["num_challenges"], 2), dtype=np.uint64)
+    rc = lib().orc_vanishing_at_ext(C.byref(c), _ptr(z), *[_ptr(o) for o in ops], _ptr(pih), _ptr(b), _ptr(g), _ptr(al), _ptr(out))
+    if rc != 0:
+        raise ValueError("orc_vanishing_at_ext failed")
+    return out
+
+
+def ext_mul(a, b):
+    out = np.zeros(2, dtype=np.uint64)
+    aa, bb = _a(a), _a(b)
+    lib().orc_ext_mul(_ptr(aa), _ptr(bb), _ptr(out))
+    return out
+
+
 def eval_polys_base(coeffs, x):
     """coeffs (k, n) -> values at the base-field point x (Horner on python ints; small test sizes only)."""
     out = []

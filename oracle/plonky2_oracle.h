@@ -173,6 +173,12 @@ int orc_quotient_values(const orc_circuit *c, const orc_batch_view *constants_si
 int orc_vanishing_at(const orc_circuit *c, uint64_t x, const uint64_t *constants_sigmas_row, const uint64_t *wires_row,
                      const uint64_t *zs_pp_row, const uint64_t *next_zs_row, const uint64_t pi_hash[4],
                      const uint64_t *betas, const uint64_t *gammas, const uint64_t *alphas, uint64_t *res);
+/* verifier side (plonk/vanishing_poly.rs eval_vanishing_poly): the reduced vanishing polynomial at an EXTENSION point from
+ * the opening set; openings are [n][2] extension elements, res[num_challenges][2] */
+int orc_vanishing_at_ext(const orc_circuit *c, const uint64_t zeta[2], const uint64_t *constants, const uint64_t *sigmas,
+                         const uint64_t *wires, const uint64_t *zs, const uint64_t *zs_next, const uint64_t *partial_products,
+                         const uint64_t pi_hash[4], const uint64_t *betas, const uint64_t *gammas, const uint64_t *alphas,
+                         uint64_t *res);
 /* util/serialization write_proof_with_public_inputs over the flat FriProof stream; returns the byte count */
 size_t orc_write_proof_with_public_inputs(const uint64_t *wires_cap, const uint64_t *zs_cap, const uint64_t *quotient_cap,
                                           const uint64_t *const openings[7], const int n_openings[7],

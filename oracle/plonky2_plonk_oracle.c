@@ -166,6 +166,90 @@ int orc_vanishing_at(const orc_circuit *c, uint64_t x, const uint64_t *constants
     return rc;
 }
 
+/* ------------------------------------------------------------ verifier side, extension field
+ * plonk/vanishing_poly.rs eval_vanishing_poly at an EXTENSION point from the opening set, as plonk/verifier.rs
+ * verify_with_challenges uses it.  Written separately from the base-field prover path above (different arithmetic,
+ * no shared helper beyond the gate table), so that it checks that path rather than repeats it. */
+typedef struct { uint64_t c[2]; } e2;
+static e2 e2_of(uint64_t x) { e2 r = {{x % P, 0}}; return r; }
+static e2 e2_add(e2 a, e2 b) { e2 r = {{orc_add(a.c[0], b.c[0]), orc_add(a.c[1], b.c[1])}}; return r; }
+static e2 e2_sub(e2 a, e2 b) { e2 r = {{orc_sub(a.c[0], b.c[0]), orc_sub(a.c[1], b.c[1])}}; return r; }
+static e2 e2_mul(e2 a, e2 b) { e2 r; orc_ext_mul(a.c, b.c, r.c); return r; }
+static e2 e2_inv(e2 a) { e2 r; orc_ext_inv(a.c, r.c); return r; }
+static e2 e2_scale(e2 a, uint64_t k) { e2 r = {{orc_mul(a.c[0], k % P), orc_mul(a.c[1], k % P)}}; return r; }
+
+/* openings: constants | plonk_sigmas | wires | plonk_zs | plonk_zs_next | partial_products, each [n][2].
+ * res[num_challenges][2] = reduce_with_powers_multi(vanishing terms, alphas) at zeta. */
+int orc_vanishing_at_ext(const orc_circuit *c, const uint64_t zeta[2], const uint64_t *constants, const uint64_t *sigmas,
+                         const uint64_t *wires, const uint64_t *zs, const uint64_t *zs_next, const uint64_t *partial_products,
+                         const uint64_t pi_hash[4], const uint64_t *betas, const uint64_t *gammas, const uint64_t *alphas,
+                         uint64_t *res) {
+    const int nc = c->num_challenges, max_degree = c->quotient_degree_factor, num_prods = c->num_partial_products;
+    const int n_chunks = num_prods + 1, n_terms = nc * (1 + n_chunks) + c->num_gate_constraints;
+    if (n_chunks != (c->num_routed_wires + max_degree - 1) / max_degree) return -1;
+    e2 *terms = (e2 *)malloc(sizeof(e2) * (size_t)(n_terms + 1));
+    const e2 x = {{zeta[0] % P, zeta[1] % P}}, one = e2_of(1);
+#define EXT_AT(arr, i) (*(const e2 *)((arr) + 2 * (size_t)(i)))
+    /* plonk_common.rs eval_l_0(n, x) = (x^n - 1) / (n (x - 1)) */
+    e2 xn = x;
+    for (int i = 0; i < c->degree_bits; i++) xn = e2_mul(xn, xn);
+    const e2 l_0_x = e2_mul(e2_sub(xn, one), e2_inv(e2_scale(e2_sub(x, one), orc_pow(2, (uint64_t)c->degree_bits))));
+    int t = 0;
+    for (int k = 0; k < nc; k++) terms[t++] = e2_mul(l_0_x, e2_sub(EXT_AT(zs, k), one)); /* vanishing_z_1_terms */
+    for (int k = 0; k < nc; k++) { /* check_partial_products */
+        for (int m = 0; m < n_chunks; m++) {
+            e2 num = one, den = one;
+            for (int j = m * max_degree; j < c->num_routed_wires && j < (m + 1) * max_degree; j++) {
+                const e2 w = EXT_AT(wires, j), s_id = e2_scale(x, c->k_is[j]);
+                num = e2_mul(num, e2_add(e2_add(w, e2_scale(s_id, betas[k])), e2_of(gammas[k])));
+                den = e2_mul(den, e2_add(e2_add(w, e2_scale(EXT_AT(sigmas, j), betas[k])), e2_of(gammas[k])));
+            }
+            const e2 prev = m == 0 ? EXT_AT(zs, k) : EXT_AT(partial_products, k * num_prods + m - 1);
+            const e2 next = m == n_chunks - 1 ? EXT_AT(zs_next, k) : EXT_AT(partial_products, k * num_prods + m);
+            terms[t++] = e2_sub(e2_mul(prev, num), e2_mul(next, den));
+        }
+    }
+    /* evaluate_gate_constraints: every gate's filtered constraints summed per slot */
+    for (int j = 0; j < c->num_gate_constraints; j++) terms[t + j] = e2_of(0);
+    int bad = 0;
+    for (int gi = 0; gi < c->n_gates; gi++) {
+        const orc_gate *g = &c->gates[gi];
+        const e2 s = EXT_AT(constants, g->selector_index);
+        e2 f = one; /* compute_filter */
+        for (int i = g->group_start; i < g->group_end; i++)
+            if (i != g->row) f = e2_mul(f, e2_sub(e2_of((uint64_t)i), s));
+        if (c->num_selectors > 1) f = e2_mul(f, e2_sub(e2_of(0xFFFFFFFFULL), s));
+        const uint64_t *gc = constants + 2 * (size_t)c->num_selectors; /* constants after the selector prefix */
+        switch (g->kind) {
+            case ORC_GATE_NOOP: break;
+            case ORC_GATE_CONSTANT:
+                for (int i = 0; i < g->param; i++) terms[t + i] = e2_add(terms[t + i], e2_mul(f, e2_sub(EXT_AT(gc, i), EXT_AT(wires, i))));
+                break;
+            case ORC_GATE_PUBLIC_INPUT:
+                for (int i = 0; i < 4; i++) terms[t + i] = e2_add(terms[t + i], e2_mul(f, e2_sub(EXT_AT(wires, i), e2_of(pi_hash[i]))));
+                break;
+            case ORC_GATE_ARITHMETIC:
+                for (int i = 0; i < g->param; i++) {
+                    const e2 prod = e2_mul(e2_mul(EXT_AT(wires, 4 * i), EXT_AT(wires, 4 * i + 1)), EXT_AT(gc, 0));
+                    const e2 computed = e2_add(prod, e2_mul(EXT_AT(wires, 4 * i + 2), EXT_AT(gc, 1)));
+                    terms[t + i] = e2_add(terms[t + i], e2_mul(f, e2_sub(EXT_AT(wires, 4 * i + 3), computed)));
+                }
+                break;
+            default: bad = 1;
+        }
+    }
+    t += c->num_gate_constraints;
+    for (int a = 0; a < nc; a++) {
+        e2 acc = e2_of(0);
+        for (int j = t - 1; j >= 0; j--) acc = e2_add(terms[j], e2_scale(acc, alphas[a]));
+        res[2 * a] = acc.c[0];
+        res[2 * a + 1] = acc.c[1];
+    }
+#undef EXT_AT
+    free(terms);
+    return bad ? -1 : 0;
+}
+
 /* plonk/prover.rs compute_quotient_polys up to (not including) the final coset_ifft:
  * out[a * lde_size + i] = quotient value of challenge alpha_a at point i of the coset 7 * <omega_{n 2^q}>. */
 int orc_quotient_values(const orc_circuit *c, const orc_batch_view *constants_sigmas, const orc_batch_view *wires_b,

@@ -177,3 +177,120 @@ def test_quotient_rejects_mismatched_shapes(pkg, ctx):
     assert ctx.mem_used() == used
     for b in gb:
         b.close()
+
+
+# ------------------------------------------------------------------------------------------ whole proofs
+def _pis_and_circuit(pkg, oracle, degree_bits, seed, **kw):
+    public_inputs = splitmix_field(900 + seed, (5,))
+    pih = oracle.hash_no_pad(public_inputs)
+    return public_inputs, pkg.synthetic_circuit(degree_bits, seed=seed, public_inputs_hash=pih, **kw)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("degree_bits,kw", [(6, {}), (10, {}), (12, {}),
+                                            (8, dict(num_wires=30, num_routed_wires=22, num_ops=5, quotient_degree_factor=5, num_challenges=3))])
+def test_device_proof_is_accepted_by_the_verifier_restatement(pkg, ctx, oracle, degree_bits, kw):
+    """plonk/prover.rs prove() on the device for a satisfying synthetic witness -> ProofWithPublicInputs; the oracle-side
+    verifier (tests/plonk_verifier.py: transcript, vanishing identity at zeta in the extension field, FRI) accepts it;
+    the bytes round-trip; a proof for a broken witness is rejected at the vanishing identity."""
+    import plonk_verifier
+    public_inputs, sc = _pis_and_circuit(pkg, oracle, degree_bits, 7, **kw)
+    cfg = pkg.FriConfig(rate_bits=sc.circuit.rate_bits, cap_height=2, proof_of_work_bits=8, num_query_rounds=6)
+    assert (pkg.hash_no_pad(ctx, public_inputs) == oracle.hash_no_pad(public_inputs)).all()
+    pw, aux = pkg.prove(ctx, sc, cfg, public_inputs)
+    ok, why = plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)
+    assert ok, why
+    c = sc.circuit
+    n_open = [c.num_constants, c.num_routed_wires, c.num_wires, c.num_challenges, c.num_challenges,
+              c.num_challenges * c.num_partial_products, c.num_challenges * c.quotient_degree_factor]
+    data = pw.to_bytes(aux["fri_params"], aux["widths"])
+    back = pkg.ProofWithPublicInputs.from_bytes(data, aux["fri_params"], aux["widths"], n_open)
+    ok, why = plonk_verifier.verify(oracle, c.as_dict(), back, aux)
+    assert ok, why
+    # a wrong public input changes the transcript and the PublicInputGate's constraint
+    back.public_inputs[0] ^= np.uint64(1)
+    assert not plonk_verifier.verify(oracle, c.as_dict(), back, aux)[0]
+    # a witness that breaks one gate: with quotient_degree_factor = 2^q the prover cannot notice (upstream's neither);
+    # the verifier must
+    if c.quotient_degree_factor == 1 << c.quotient_degree_bits:
+        row = int(np.nonzero(sc.constants[0] == 3)[0][0])
+        sc.wires[3, row] = (int(sc.wires[3, row]) + 1) % P
+        pw_bad, aux_bad = pkg.prove(ctx, sc, cfg, public_inputs)
+        ok, why = plonk_verifier.verify(oracle, c.as_dict(), pw_bad, aux_bad)
+        assert not ok and "vanishing" in why
+
+
+def _oracle_prove(pkg, oracle, sc, cfg, public_inputs):
+    """The same prove() flow as pkg.prove, every step on the CPU oracle (the reference arm of the whole-proof tests)."""
+    c = sc.circuit
+    nc, rb, chh = c.num_challenges, cfg.rate_bits, cfg.cap_height
+    fp = cfg.fri_params(c.degree_bits)
+    cs = oracle.batch_from_values(np.concatenate([sc.constants, sc.sigmas]), rb, chh)
+    digest = oracle.hash_no_pad(np.concatenate([cs["cap"].reshape(-1), np.array([c.degree_bits], dtype=np.uint64)]))
+    pih = oracle.hash_no_pad(public_inputs)
+    ch = oracle.Challenger()
+    ch.observe(digest)
+    ch.observe(pih)
+    wires = oracle.batch_from_values(sc.wires, rb, chh)
+    ch.observe(wires["cap"].reshape(-1))
+    betas = [ch.get_challenge() for _ in range(nc)]
+    gammas = [ch.get_challenge() for _ in range(nc)]
+    zs_vals = oracle.partial_products_and_zs(sc.wires[:c.num_routed_wires], sc.sigmas, c.k_is, betas, gammas, c.quotient_degree_factor)
+    zs = oracle.batch_from_values(zs_vals, rb, chh)
+    ch.observe(zs["cap"].reshape(-1))
+    alphas = [ch.get_challenge() for _ in range(nc)]
+    qv = oracle.quotient_values(c.as_dict(), cs, wires, zs, pih, betas, gammas, alphas, chh)
+    quotient = oracle.batch_from_values(oracle.quotient_chunks(qv, c.degree_bits, c.quotient_degree_factor), rb, chh, from_coeffs=True)
+    ch.observe(quotient["cap"].reshape(-1))
+    zeta = ch.get_extension_challenge()
+    g = pow(1753635133440165772, 1 << (32 - c.degree_bits), P)
+    gz = np.array([int(zeta[0]) * g % P, int(zeta[1]) * g % P], dtype=np.uint64)
+    ev = lambda b, z: np.array([oracle.eval_poly_ext(b, j, z, rb, chh) for j in range(b["coeffs"].shape[0])], dtype=np.uint64).reshape(-1, 2)
+    e_cs, e_w, e_z, e_q, e_zn = ev(cs, zeta), ev(wires, zeta), ev(zs, zeta), ev(quotient, zeta), ev(zs, gz)
+    openings = pkg.OpeningSet(e_cs[:c.num_constants], e_cs[c.num_constants:], e_w, e_z[:nc], e_zn[:nc], e_z[nc:], e_q)
+    for batch in openings.to_fri_openings():
+        ch.observe(batch.reshape(-1))
+    batches = [cs, wires, zs, quotient]
+    widths = [b["coeffs"].shape[0] for b in batches]
+    polys = [[(o, j) for o, w in enumerate(widths) for j in range(w)], [(2, j) for j in range(nc)]]
+    words = oracle.fri_prove_openings(batches, np.stack([zeta, gz]), polys, ch, c.degree_bits, rb, chh, cfg.proof_of_work_bits,
+                                      cfg.num_query_rounds, list(fp.reduction_arity_bits))
+    pw = pkg.ProofWithPublicInputs(pkg.Proof(wires["cap"], zs["cap"], quotient["cap"], openings, words), np.asarray(public_inputs, dtype=np.uint64))
+    return pw, {"circuit_digest": digest, "constants_sigmas_cap": cs["cap"], "fri_params": fp, "widths": widths}
+
+
+@pytest.mark.parametrize("degree_bits,kw", [(5, {}), (6, dict(num_wires=30, num_routed_wires=22, num_ops=5, quotient_degree_factor=5, num_challenges=3))])
+def test_oracle_proof_is_accepted_by_the_verifier_restatement(pkg, oracle, degree_bits, kw):
+    """CPU tier of the whole-proof check: prover steps and verifier are separate restatements (base-field batch evaluation
+    on the coset vs extension-field evaluation of the opening set); they must agree on a satisfying witness and disagree
+    on a broken one."""
+    import plonk_verifier
+    public_inputs, sc = _pis_and_circuit(pkg, oracle, degree_bits, 3, **kw)
+    cfg = pkg.FriConfig(rate_bits=sc.circuit.rate_bits, cap_height=1, proof_of_work_bits=4, num_query_rounds=4)
+    pw, aux = _oracle_prove(pkg, oracle, sc, cfg, public_inputs)
+    ok, why = plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)
+    assert ok, why
+    # an opening that is not the polynomial's value: FRI rejects; a tampered cap: the transcript diverges
+    pw.proof.openings.wires[0, 0] ^= np.uint64(1)
+    assert not plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)[0]
+    pw.proof.openings.wires[0, 0] ^= np.uint64(1)
+    pw.proof.wires_cap = pw.proof.wires_cap.copy()
+    pw.proof.wires_cap[0, 0] ^= np.uint64(1)
+    assert not plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)[0]
+    if sc.circuit.quotient_degree_factor == 8:  # broken gate, unnoticed by the prover: rejected at the vanishing identity
+        row = int(np.nonzero(sc.constants[0] == 3)[0][0])
+        sc.wires[3, row] = (int(sc.wires[3, row]) + 1) % P
+        pw_bad, aux_bad = _oracle_prove(pkg, oracle, sc, cfg, public_inputs)
+        ok, why = plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw_bad, aux_bad)
+        assert not ok and "vanishing" in why
+
+
+@pytest.mark.gpu
+def test_device_proof_equals_the_oracle_proof(pkg, ctx, oracle):
+    """Same witness, same transcript: the device proof is the oracle's proof, byte for byte."""
+    public_inputs, sc = _pis_and_circuit(pkg, oracle, 7, 5)
+    cfg = pkg.FriConfig(rate_bits=3, cap_height=2, proof_of_work_bits=6, num_query_rounds=5)
+    pw_o, aux_o = _oracle_prove(pkg, oracle, sc, cfg, public_inputs)
+    pw_d, aux_d = pkg.prove(ctx, sc, cfg, public_inputs)
+    assert (aux_o["circuit_digest"] == aux_d["circuit_digest"]).all() and aux_o["widths"] == aux_d["widths"]
+    assert pw_d.to_bytes(aux_d["fri_params"], aux_d["widths"]) == pw_o.to_bytes(aux_o["fri_params"], aux_o["widths"])
