@@ -77,66 +77,52 @@ void launch_merkle_level(const u64 *children, u64 *parents, size_t n_parents, cu
     BSX_COUNT_LAUNCH(); merkle_level_kernel<<<blocks, 256, 0, st>>>(children, parents, n_parents);
 }
 
-// One block per subtree of 2^sub_log nodes at the input level: digest layers stay in shared
+// One block per subtree of 2^SUB_LOG nodes at the input level: digest layers stay in shared
 // memory while the block climbs `levels` levels; every layer is also written to its level-order
-// slot in global memory because `MerkleTree::prove` reads them later.  Layers of more than MERKLE_COOP_MAX parents
-// per block take one thread per parent (throughput); the narrow layers above them are latency-bound -- one thread needs
-// ~39 us per permutation whatever the layer's size -- so there each warp computes one parent with the warp-wide
-// permutation (poseidon_permute_warp, ~5 us): a 2^9-input subtree climbs in ~0.17 ms instead of 0.35 ms.
+// slot in global memory because `MerkleTree::prove` reads them later.
+// (Round 2 tried the warp-wide permutation of poseidon.cuh for the narrow layers -- one parent per warp instead of per
+// thread -- and a single launch up to the cap: tree 0.374 -> 0.439 ms at 2^17 leaves, 1.088 -> 1.153 ms at 2^20.  The
+// naive shuffle form is slower per layer than one thread per parent on an otherwise idle SM; reverted.)
 #define SUB_LOG 9
-#define MERKLE_COOP_MAX 32
 #define MERKLE_FLAT_MIN_LOG 15  // levels with more than 2^15 inputs run flat, the rest in per-block subtrees
 __global__ void __launch_bounds__(256) merkle_subtree_kernel(const u64 *__restrict__ in_level, u64 *__restrict__ out0,
-                                                             size_t n_in, int levels, int sub_log,
+                                                             size_t n_in, int levels, size_t level_stride_words,
                                                              u64 *__restrict__ cap, int cap_level) {
-    // in_level: n_in digests.  Block b owns inputs [b << sub_log, (b+1) << sub_log).
+    // in_level: n_in digests.  Block b owns inputs [b << SUB_LOG, (b+1) << SUB_LOG).
     // Level j (1-based) output goes to out_j = out0 + sum_{t<j-1} (n_in >> (t+1)) * 4 words, unless
     // j == cap_level, which goes to `cap`.
     __shared__ u64 sm[2][(1 << (SUB_LOG - 1)) * 4];
-    size_t base_in = (size_t)blockIdx.x << sub_log;
-    size_t n_par = (size_t)1 << (sub_log - 1);
+    size_t base_in = (size_t)blockIdx.x << SUB_LOG;
+    size_t n_par = (size_t)1 << (SUB_LOG - 1);
     const u64 *src = in_level + 4 * base_in;
     u64 *out = out0;
     size_t lvl_n = n_in >> 1;  // digests in the level being produced (whole tree)
     int buf = 0;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    (void)level_stride_words;
     for (int j = 1; j <= levels; j++) {
         u64 *dst_g = (j == cap_level) ? cap : out;
-        size_t base_out = ((size_t)blockIdx.x << sub_log) >> j;
-        if (n_par <= MERKLE_COOP_MAX) {
-            // one parent per warp at a time: lane t < 8 holds word t of the two children, lanes 8..11 the zero capacity
-            for (size_t i = warp; i < n_par; i += n_warps) {
-                const u64 *c = (j == 1) ? src + 8 * i : sm[buf ^ 1] + 8 * i;
-                u64 x = lane < 8 ? c[lane] : 0;
-                x = poseidon_permute_warp(x, lane);
-                if (lane < 4) {
-                    sm[buf][4 * i + lane] = x;
-                    dst_g[4 * (base_out + i) + lane] = x;
-                }
-            }
-        } else {
-            for (size_t i = threadIdx.x; i < n_par; i += blockDim.x) {
-                u64 s[12];
-                if (j == 1) {
-                    const ulonglong2 *c = reinterpret_cast<const ulonglong2 *>(src + 8 * i);
-                    ulonglong2 a = c[0], b = c[1], d = c[2], e = c[3];
-                    s[0] = a.x; s[1] = a.y; s[2] = b.x; s[3] = b.y;
-                    s[4] = d.x; s[5] = d.y; s[6] = e.x; s[7] = e.y;
-                } else {
-                    const u64 *c = sm[buf ^ 1] + 8 * i;
+        size_t base_out = ((size_t)blockIdx.x << SUB_LOG) >> j;
+        for (size_t i = threadIdx.x; i < n_par; i += blockDim.x) {
+            u64 s[12];
+            if (j == 1) {
+                const ulonglong2 *c = reinterpret_cast<const ulonglong2 *>(src + 8 * i);
+                ulonglong2 a = c[0], b = c[1], d = c[2], e = c[3];
+                s[0] = a.x; s[1] = a.y; s[2] = b.x; s[3] = b.y;
+                s[4] = d.x; s[5] = d.y; s[6] = e.x; s[7] = e.y;
+            } else {
+                const u64 *c = sm[buf ^ 1] + 8 * i;
 #pragma unroll
-                    for (int t = 0; t < 8; t++) s[t] = c[t];
-                }
-                s[8] = s[9] = s[10] = s[11] = 0;
-                poseidon_permute_lazy(s);
-#pragma unroll
-                for (int t = 0; t < 4; t++) s[t] = gl_canon(s[t]);
-                u64 *d_s = sm[buf] + 4 * i;
-                d_s[0] = s[0]; d_s[1] = s[1]; d_s[2] = s[2]; d_s[3] = s[3];
-                ulonglong2 *o = reinterpret_cast<ulonglong2 *>(dst_g + 4 * (base_out + i));
-                o[0] = make_ulonglong2(s[0], s[1]);
-                o[1] = make_ulonglong2(s[2], s[3]);
+                for (int t = 0; t < 8; t++) s[t] = c[t];
             }
+            s[8] = s[9] = s[10] = s[11] = 0;
+            poseidon_permute_lazy(s);
+#pragma unroll
+            for (int t = 0; t < 4; t++) s[t] = gl_canon(s[t]);
+            u64 *d_s = sm[buf] + 4 * i;
+            d_s[0] = s[0]; d_s[1] = s[1]; d_s[2] = s[2]; d_s[3] = s[3];
+            ulonglong2 *o = reinterpret_cast<ulonglong2 *>(dst_g + 4 * (base_out + i));
+            o[0] = make_ulonglong2(s[0], s[1]);
+            o[1] = make_ulonglong2(s[2], s[3]);
         }
         __syncthreads();
         out += 4 * lvl_n;
@@ -167,12 +153,10 @@ void launch_merkle_tree(u64 *digests, u64 *cap, int log_leaves, int cap_height, 
             out = dst + 4 * n_par;
             n_in = n_par;
             done += 1;
-        } else {
-            // per-block subtrees; the last stretch (fewer than 2^SUB_LOG inputs left) is one block climbing to the cap
-            const int sub_log = log_in < SUB_LOG ? log_in : SUB_LOG;
-            int climb = rem < sub_log ? rem : sub_log;
-            unsigned blocks = (unsigned)(n_in >> sub_log);
-            BSX_COUNT_LAUNCH(); merkle_subtree_kernel<<<blocks, 256, 0, st>>>(in, out, n_in, climb, sub_log, cap, rem <= sub_log ? rem : -1);
+        } else if (log_in >= SUB_LOG && rem >= 1) {
+            int climb = rem < SUB_LOG ? rem : SUB_LOG;
+            unsigned blocks = (unsigned)(n_in >> SUB_LOG);
+            BSX_COUNT_LAUNCH(); merkle_subtree_kernel<<<blocks, 256, 0, st>>>(in, out, n_in, climb, 0, cap, rem <= SUB_LOG ? rem : -1);
             // advance: the last produced level becomes the next input
             size_t words = 0, ln = n_in >> 1;
             for (int j = 1; j < climb; j++) {
@@ -184,6 +168,15 @@ void launch_merkle_tree(u64 *digests, u64 *cap, int log_leaves, int cap_height, 
             out = last + 4 * ln;
             n_in >>= climb;
             done += climb;
+        } else {
+            // small remainder: one launch per level
+            size_t n_par = n_in >> 1;
+            u64 *dst = (rem == 1) ? cap : out;
+            launch_merkle_level(in, dst, n_par, st);
+            in = dst;
+            out = dst + 4 * n_par;
+            n_in = n_par;
+            done += 1;
         }
     }
 }
