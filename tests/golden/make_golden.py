@@ -124,6 +124,27 @@ def main():
     zz = O.partial_products_and_zs(zw, zs_, zk, zb, zg, 4)
     g["zs"] = {"wires_seed": 61, "sigmas_seed": 62, "k_is_seed": 63, "betas_seed": 64, "gammas_seed": 65, "log_n": 6,
                "n_routed": 10, "max_degree": 4, "shape": list(zz.shape), "sha256": digest(zz), "row_1": hx(zz[:, 1])}
+    # a whole proof of a small synthetic circuit (16 rows, 20 wires of which 12 routed, NoopGate / ConstantGate(2) /
+    # PublicInputGate / ArithmeticGate(3) in one selector group): the circuit data and the witness are stored in full, so
+    # that a maintainer can replay them through plonky2's prove(); quotient values, caps and proof bytes are the oracle's
+    import __graft_entry__ as GE
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_quotient as TQ
+    pkg = GE.load_package()
+    pis = splitmix_field(70, (5,))
+    kw = dict(num_wires=20, num_routed_wires=12, num_ops=3, quotient_degree_factor=8)
+    sc = pkg.synthetic_circuit(4, seed=71, public_inputs_hash=O.hash_no_pad(pis), **kw)
+    cfg = pkg.FriConfig(rate_bits=3, cap_height=1, proof_of_work_bits=5, num_query_rounds=4)
+    pw, aux = TQ._oracle_prove(pkg, O, sc, cfg, pis)
+    c = sc.circuit
+    g["plonk"] = {"degree_bits": 4, "config": kw, "rate_bits": 3, "cap_height": 1, "proof_of_work_bits": 5, "num_query_rounds": 4,
+                  "gates": [[gt.kind, gt.param, gt.row, gt.selector_index, gt.group_start, gt.group_end] for gt in c.gates],
+                  "public_inputs": hx(pis), "constants": hx(sc.constants), "sigmas": hx(sc.sigmas), "wires": hx(sc.wires),
+                  "circuit_digest": hx(aux["circuit_digest"]), "wires_cap": hx(pw.proof.wires_cap),
+                  "zs_cap": hx(pw.proof.plonk_zs_partial_products_cap), "quotient_cap": hx(pw.proof.quotient_polys_cap),
+                  "openings_sha256": digest(np.concatenate([f.reshape(-1) for f in pw.proof.openings.fields()])),
+                  "proof_bytes_sha256": hashlib.sha256(pw.to_bytes(aux["fri_params"], aux["widths"])).hexdigest(),
+                  "proof_bytes_len": len(pw.to_bytes(aux["fri_params"], aux["widths"]))}
     with open(os.path.join(HERE, "golden_vectors.json"), "w") as f:
         json.dump(g, f, indent=1)
     print("wrote golden_vectors.json: %d commit cases, %d fri cases" % (len(g["commit"]), len(g["fri"])))

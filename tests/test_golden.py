@@ -92,6 +92,47 @@ def test_oracle_reproduces_golden_quotient_and_zs(oracle):
     assert list(zz.shape) == G["zs"]["shape"] and digest(zz) == G["zs"]["sha256"] and hx(zz[:, 1]) == G["zs"]["row_1"]
 
 
+def _golden_circuit(pkg):
+    import __graft_entry__ as GE
+    q = G["plonk"]
+    un = lambda h, shape: np.array([int(x, 16) for x in h], dtype=np.uint64).reshape(shape)
+    n = 1 << q["degree_bits"]
+    kw = q["config"]
+    gates = [pkg.Gate(*g) for g in q["gates"]]
+    circ = pkg.CircuitDescription(q["degree_bits"], gates, rate_bits=q["rate_bits"], quotient_degree_factor=kw["quotient_degree_factor"],
+                                  num_wires=kw["num_wires"], num_routed_wires=kw["num_routed_wires"])
+    pis = un(q["public_inputs"], (-1,))
+    sc = pkg.SyntheticCircuit(circ, un(q["constants"], (3, n)), un(q["sigmas"], (kw["num_routed_wires"], n)),
+                              un(q["wires"], (kw["num_wires"], n)), None)
+    cfg = pkg.FriConfig(rate_bits=q["rate_bits"], cap_height=q["cap_height"], proof_of_work_bits=q["proof_of_work_bits"],
+                        num_query_rounds=q["num_query_rounds"])
+    return sc, cfg, pis
+
+
+def _check_golden_proof(pw, aux):
+    import hashlib
+    q = G["plonk"]
+    assert hx(aux["circuit_digest"]) == q["circuit_digest"]
+    assert hx(pw.proof.wires_cap) == q["wires_cap"] and hx(pw.proof.plonk_zs_partial_products_cap) == q["zs_cap"]
+    assert hx(pw.proof.quotient_polys_cap) == q["quotient_cap"]
+    assert digest(np.concatenate([f.reshape(-1) for f in pw.proof.openings.fields()])) == q["openings_sha256"]
+    data = pw.to_bytes(aux["fri_params"], aux["widths"])
+    assert len(data) == q["proof_bytes_len"] and hashlib.sha256(data).hexdigest() == q["proof_bytes_sha256"]
+
+
+def test_oracle_reproduces_golden_proof(oracle):
+    """The whole prove() flow of a stored circuit + witness on the oracle: caps, opening set and ProofWithPublicInputs bytes."""
+    import __graft_entry__ as GE
+    import plonk_verifier
+    import test_quotient as TQ
+    pkg = GE.load_package()
+    sc, cfg, pis = _golden_circuit(pkg)
+    sc.public_inputs_hash = oracle.hash_no_pad(pis)
+    pw, aux = TQ._oracle_prove(pkg, oracle, sc, cfg, pis)
+    _check_golden_proof(pw, aux)
+    assert plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)[0]
+
+
 # ------------------------------------------------------------------ GPU: the CUDA path vs the committed vectors
 @pytest.fixture(scope="module")
 def pkg():
@@ -187,3 +228,11 @@ def test_device_reproduces_golden_challenger_and_fri(pkg, ctx):
         assert hx(ch.snapshot()[0]) == c["challenger_after"]
         for b in batches:
             b.close()
+
+
+@pytest.mark.gpu
+def test_device_reproduces_golden_proof(pkg, ctx):
+    sc, cfg, pis = _golden_circuit(pkg)
+    sc.public_inputs_hash = pkg.hash_no_pad(ctx, pis)
+    pw, aux = pkg.prove(ctx, sc, cfg, pis)
+    _check_golden_proof(pw, aux)
