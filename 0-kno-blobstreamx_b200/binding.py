@@ -22,7 +22,7 @@ EXPORTED_SYMBOLS = [
     "bsx_fri_proof_from_final_poly",
     "bsx_merkle_reduce", "bsx_shard_column_range", "bsx_shard_create", "bsx_shard_free", "bsx_shard_shape",
     "bsx_shard_slab_device", "bsx_shard_staging_device", "bsx_shard_coeffs_device", "bsx_shard_slab_ipc",
-    "bsx_shard_set_peer_ipc", "bsx_shard_set_peer_ptr", "bsx_shard_transform", "bsx_shard_commit", "bsx_shard_coeffs", "bsx_shard_run_p2p",
+    "bsx_shard_set_peer_ipc", "bsx_shard_set_peer_ptr", "bsx_shard_transform", "bsx_shard_commit", "bsx_shard_coeffs", "bsx_shard_run_p2p", "bsx_shard_transform_cols",
     "bsx_fri_proof_layout", "bsx_fri_proof_bytes", "bsx_proof_with_public_inputs_bytes",
     "bsx_quotient_values", "bsx_compute_quotient_polys",
     "bsx_comm_create", "bsx_comm_destroy", "bsx_comm_size", "bsx_comm_ctx", "bsx_comm_last_error",

@@ -287,6 +287,50 @@ extern "C" int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int3
     return rc;
 }
 
+// The transforms of the local columns [col_begin, col_begin + col_count) only (input: those columns), so that a host
+// running the staged exchange can send the finished columns of one chunk while the next chunk is being transformed.
+// Call with increasing col_begin starting at 0; sync == 0 returns with the work enqueued on the context's stream.
+extern "C" int32_t bsx_shard_transform_cols(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
+                                            int32_t use_staging, int32_t col_begin, int32_t col_count, int32_t sync) {
+    if (!s) return BSX_ERR_INVALID_ARG;
+    bsx_ctx *ctx = s->ctx;
+    BsxScope scope(ctx);
+    const int n_local = s->c1 - s->c0;
+    if (col_begin < 0 || col_count < 0 || col_begin + col_count > n_local)
+        return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "columns [%d, %d) outside this rank's %d columns", col_begin, col_begin + col_count, n_local);
+    if (!input && col_count > 0) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "input is NULL");
+    CU(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)1 << s->log_n, nb = n << s->rate_bits;
+    if (col_begin == 0) {
+        bsx_free(ctx, s->coeffs);
+        s->coeffs = nullptr;
+        if (n_local > 0) TRY(bsx_alloc_owned(ctx, &s->coeffs, n * n_local));
+    }
+    if (col_count > 0) {
+        if (!s->coeffs) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "start with col_begin = 0");
+        BsxDests D;
+        D.n = s->n_ranks;
+        D.lc = s->log_n + s->rate_bits - s->log_ranks;
+        if (use_staging) {
+            if (!s->staging) TRY(bsx_alloc_owned(ctx, &s->staging, nb * (size_t)n_local));
+            for (int d = 0; d < s->n_ranks; d++) D.ptr[d] = s->staging + (size_t)d * s->chunk * n_local + (size_t)col_begin * s->chunk;
+        } else {
+            for (int d = 0; d < s->n_ranks; d++) {
+                if (!s->peer[d]) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "row slab of rank %d is not set", d);
+                D.ptr[d] = s->peer[d] + (size_t)(s->c0 + col_begin) * s->chunk;
+            }
+        }
+        u64 *cf = s->coeffs + (size_t)col_begin * n, *scratch;
+        TRY(bsx_copy_in(ctx, cf, (const u64 *)input, n * (size_t)col_count, mem));
+        TRY(bsx_alloc(ctx, &scratch, nb * (size_t)col_count));
+        TRY(bsx_commit_transforms(ctx, cf, s->log_n, col_count, s->rate_bits, input_is_coeffs != 0, scratch, nb, &D, nullptr));
+        bsx_free(ctx, scratch);
+        s->coeffs_bitrev = !input_is_coeffs;
+    }
+    if (sync) CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
 // ---- device-side barrier over the mailboxes (one rank per GPU) ------------------------------------------------
 // Thread p tells rank p "rank `rank` has reached `epoch`" (slot 0: its stores into your slab are complete -- they were
 // issued by kernels that finished earlier on this stream; slot 1: its local cap is in your mailbox), then waits for

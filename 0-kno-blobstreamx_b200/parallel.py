@@ -286,11 +286,7 @@ class ShardedPolynomialBatch:
             self.transform(values_local, is_coeffs, use_staging=False, device_ptr=device_ptr, timing=timing)
             dist.barrier(group=group)  # every rank's stores into every slab are complete
         else:
-            self.transform(values_local, is_coeffs, use_staging=True, device_ptr=device_ptr, timing=timing)
-            send = device_tensor(self.staging_ptr, plan.world * plan.staging_block_words(self.rank), ctx.device)
-            recv = device_tensor(self.slab_ptr, plan.n_cols * plan.chunk, ctx.device)
-            exchange_staged(send, recv, plan, self.rank, group)
-            torch.cuda.synchronize(ctx.device)
+            self._run_nccl_chunked(values_local, device_ptr, is_coeffs)
         local = torch.from_numpy(self.commit().astype(np.int64)).to(dev).reshape(-1)
         caps = torch.empty(plan.world * local.numel(), dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(caps, local, group=group)
@@ -298,6 +294,49 @@ class ShardedPolynomialBatch:
         self.rank_caps = list(caps)
         self.cap = assemble_cap(self.rank_caps, plan, ctx)
         return self
+
+    def _run_nccl_chunked(self, values_local, device_ptr, is_coeffs):
+        """Mode "nccl": the local columns are transformed in a few chunks into the destination-major staging buffer, and
+        the all-to-all of chunk k (grouped NCCL send/recv between views of the staging buffer and of the row slabs) runs
+        on NCCL's stream while chunk k + 1 is being transformed on the library's."""
+        import torch
+        import torch.distributed as dist
+        plan, ctx, group = self.plan, self.ctx, self.group
+        c0, c1 = plan.column_range(self.rank)
+        n_local, n = c1 - c0, 1 << plan.log_n
+        if device_ptr is not None:
+            base, mem = int(device_ptr), BSX_DEVICE
+        else:
+            values_local = _np(values_local)
+            if values_local.shape != (n_local, n):
+                raise BsxError("rank %d expects columns [%d, %d)" % (self.rank, c0, c1))
+            base, mem = values_local.ctypes.data, BSX_HOST
+        # every rank must post the same number of exchanges: the count comes from the smallest column range
+        nl_min = plan.n_cols // plan.world
+        n_chunks = 1 if nl_min < 6 else (2 if nl_min < 12 else 3)
+        bounds = [(k * n_local) // n_chunks for k in range(n_chunks + 1)]
+        f = lib().bsx_shard_transform_cols
+        f.restype, f.argtypes = C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+        lib_stream = torch.cuda.ExternalStream(ctx.stream, device=ctx.device)
+        works, keep = [], []
+        with torch.cuda.stream(lib_stream):
+            for k in range(n_chunks):
+                cb, cc = bounds[k], bounds[k + 1] - bounds[k]
+                ctx.check(f(self._h, C.c_void_p(base + 8 * cb * n), mem, 1 if is_coeffs else 0, 1, cb, cc, 0))
+                send = device_tensor(self.staging_ptr, plan.world * plan.staging_block_words(self.rank), ctx.device)
+                recv = device_tensor(self.slab_ptr, plan.n_cols * plan.chunk, ctx.device)
+                ins, outs = [], []
+                for peer in range(plan.world):
+                    ins.append(send[peer * n_local * plan.chunk + cb * plan.chunk:][:cc * plan.chunk])
+                    p0, p1 = plan.column_range(peer)
+                    pb = [(j * (p1 - p0)) // n_chunks for j in range(n_chunks + 1)]
+                    outs.append(recv[(p0 + pb[k]) * plan.chunk:][:(pb[k + 1] - pb[k]) * plan.chunk])
+                keep.append((ins, outs))
+                works.append(dist.all_to_all(outs, ins, group=group, async_op=True))
+            for w in works:
+                w.wait()
+        torch.cuda.synchronize(ctx.device)
+        self.timing = Timing()  # phases interleave with the exchange: no per-phase split in this mode
 
     # ---- openings: served by the owning rank (SURVEY.md 8(e): row l lives on rank l >> log2(chunk))
     @property

@@ -184,6 +184,11 @@ int32_t bsx_shard_set_peer_ptr(bsx_shard *s, int32_t peer_rank, uint64_t *slab_d
 /* input: this rank's columns only, (c1 - c0) x 2^log_n column-major values (or coefficients) */
 int32_t bsx_shard_transform(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
                             int32_t use_staging, bsx_timing *timing);
+/* The transforms of the local columns [col_begin, col_begin + col_count) only (`input` = those columns): a host running
+ * the staged exchange sends the finished columns of one chunk while the next chunk is transformed.  Call with increasing
+ * col_begin starting at 0.  sync == 0 returns with the work enqueued on the context's stream. */
+int32_t bsx_shard_transform_cols(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs,
+                                 int32_t use_staging, int32_t col_begin, int32_t col_count, int32_t sync);
 /* The whole commit of one rank with no host synchronisation between its phases, for one process per GPU with every
  * peer slab mapped (bsx_shard_set_peer_ipc): transforms -> device-side barrier over flags in the peers' slabs -> leaf
  * hashing and cap subtrees -> the local caps published to every rank -> rank_caps_host (n_ranks x 2^(local cap height)
