@@ -208,7 +208,7 @@ static int shard_transform_enqueue(bsx_shard *s, const uint64_t *input, int32_t 
     if (pinned && n_local >= 8 && s->log_n >= 13) {
         // Only the first chunk's copy is exposed, so the schedule starts small; chunk sizes follow the transform grid
         // (128 tiles per column at 2^20 rows against 444 resident CTAs: 3 or 7 columns fill whole waves, 4 would leave
-        // the second wave 15 % full): 3, 3, 4, then sevens.
+        // the second wave 15 % full): 3, 3, 4, then about three chunks of a multiple of seven.
         std::vector<int> cstart;
         {
             int c = 0;
@@ -217,9 +217,12 @@ static int shard_transform_enqueue(bsx_shard *s, const uint64_t *input, int32_t 
                     cstart.push_back(c);
                     c += r;
                 }
+            // the rest in about three chunks, each a multiple of seven columns
+            int per = ((n_local - c + 2) / 3 + 6) / 7 * 7;
+            if (per < 7) per = 7;
             while (c < n_local) {
                 cstart.push_back(c);
-                c += (n_local - c >= 10) ? 7 : n_local - c;
+                c += (n_local - c >= per + 3) ? per : n_local - c;
             }
             cstart.push_back(n_local);
         }
