@@ -20,7 +20,7 @@ EXPORTED_SYMBOLS = [
     "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_debug_salt_stream", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
     "bsx_challenger_get", "bsx_fri_proof_words", "bsx_fri_prove_openings", "bsx_fri_proof", "bsx_fri_final_poly", "bsx_fri_final_poly_part", "bsx_shard_final_poly_part", "bsx_field_sum",
     "bsx_fri_proof_from_final_poly",
-    "bsx_merkle_reduce", "bsx_shard_column_range", "bsx_shard_create", "bsx_shard_free", "bsx_shard_shape",
+    "bsx_merkle_reduce", "bsx_merkle_reduce_noalloc", "bsx_shard_column_range", "bsx_shard_create", "bsx_shard_free", "bsx_shard_shape",
     "bsx_shard_slab_device", "bsx_shard_staging_device", "bsx_shard_coeffs_device", "bsx_shard_slab_ipc",
     "bsx_shard_set_peer_ipc", "bsx_shard_set_peer_ptr", "bsx_shard_transform", "bsx_shard_commit", "bsx_shard_coeffs", "bsx_shard_run_p2p", "bsx_shard_transform_cols",
     "bsx_fri_proof_layout", "bsx_fri_proof_bytes", "bsx_proof_with_public_inputs_bytes",
@@ -114,6 +114,7 @@ def lib():
         "bsx_field_sum": (i32, [vp, vp, i32, i32, sz, vp, i32]),
         "bsx_fri_proof_from_final_poly": (i32, [vp, vp, i32, vp, i32, vp, vp, vp, vp]),
         "bsx_merkle_reduce": (i32, [vp, vp, i32, i32, vp]),
+        "bsx_merkle_reduce_noalloc": (i32, [vp, vp, i32, i32, i32, vp, i32]),
         "bsx_shard_column_range": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
         "bsx_shard_create": (i32, [vp, i32, i32, i32, i32, i32, i32, pp]),
         "bsx_shard_free": (None, [vp]),

@@ -154,6 +154,17 @@ int32_t bsx_merkle_shape(const bsx_tree *t, int32_t *log_leaves, int32_t *leaf_l
 int32_t bsx_merkle_reduce(bsx_ctx *ctx, const uint64_t *digests_host, int32_t n_in, int32_t levels,
                           uint64_t *out_host);
 
+/* The same reduction WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The ping-pong scratch is a static device array of the library (3 MiB per GPU that loads it, held until exit), so
+ * n_in is limited to BSX_NOALLOC_MAX_DIGESTS; more fails with BSX_ERR_UNSUPPORTED and a message.  `digests` and `out`
+ * may each be host or device memory of ctx's device (mem_in / mem_out).  All calls on one GPU share the scratch, which
+ * keeps the previous call's contents (nothing in it needs clearing: every word read was written by the same call);
+ * calls that overlap on one GPU race and must be serialised by the caller.  Synchronous at return. */
+#define BSX_NOALLOC_MAX_DIGESTS 65536
+int32_t bsx_merkle_reduce_noalloc(bsx_ctx *ctx, const uint64_t *digests, int32_t mem_in, int32_t n_in, int32_t levels,
+                                  uint64_t *out, int32_t mem_out);
+
 /* ---- one commit sharded over the GPUs of a box (no upstream counterpart; BASELINE.json north star) ------
  * PolynomialBatch::from_values split as: columns -> ranks for the transforms, leaf rows -> ranks for
  * hashing.  Rank g of G (a power of two, <= 16) owns columns bsx_shard_column_range() and the leaf rows

@@ -28,7 +28,7 @@ fn main() {
             .flag("arch=compute_100a,code=sm_100a")
             .include(&include);
         for f in ["api.cu", "api_batch.cu", "hash_kernels.cu", "ntt_kernels.cu", "fri_kernels.cu", "api_fri.cu",
-                  "api_shard.cu", "eval_kernels.cu", "api_zs.cu", "api_proof.cu", "api_quotient.cu", "api_comm.cu"] {
+                  "api_shard.cu", "eval_kernels.cu", "api_zs.cu", "api_proof.cu", "api_quotient.cu", "api_comm.cu", "api_noalloc.cu"] {
             println!("cargo:rerun-if-changed={}", csrc.join(f).display());
             b.file(csrc.join(f));
         }
