@@ -323,6 +323,45 @@ __device__ __forceinline__ u64 gl_mul_canon(u64 a, u64 b) {
 #endif
 }
 
+// ---- multiplication by a power of two (twiddles of the small roots of unity) ----
+// In Goldilocks 2 has order 192 (2^96 == -1) and plonky2's omega_16 = omega_{2^32}^(2^28) is 2^156 = -2^60, so every
+// power of omega_16 (and of omega_8, omega_4) is +-2^k, k a multiple of 12: a shift into four 32-bit limbs and one
+// reduction instead of a 64 x 64 product (1 IMAD.WIDE instead of 5, no table read).
+// (x3:x2:x1:x0) - sub_hi 2^32 -> canonical:  (x1:x0) + x2 EPS - (sub_hi:x3); same single signed correction as the multiply
+// (sub_hi < 2^31 here, x3 < 2^32), canonicalised the way gl_mul_canon does.
+__device__ __forceinline__ u64 gl_reduce4_canon(u32 l0, u32 l1, u32 l2, u32 l3, u32 sub_hi) {
+    u32 r0, r1;
+    asm("{\n\t.reg .u32 x0,x1,r2,n,eh,c0,c1,g;\n\t"
+        "mad.lo.cc.u32 x0, %4, %7, %2;\n\t"
+        "madc.hi.cc.u32 x1, %4, %7, %3;\n\t"
+        "madc.lo.u32 r2, %9, %8, 0;\n\t"          // carry
+        "sub.cc.u32 x0, x0, %5;\n\t"
+        "subc.cc.u32 x1, x1, %6;\n\t"
+        "subc.u32 r2, r2, 0;\n\t"
+        "mul.lo.u32 n, r2, %10;\n\t"               // -r2
+        "shr.s32 eh, r2, 31;\n\t"
+        "add.cc.u32 x0, x0, n;\n\t"
+        "madc.lo.u32 x1, eh, %8, x1;\n\t"
+        "add.cc.u32 c0, x0, 0xFFFFFFFF;\n\t"      // carries iff x0 != 0
+        "addc.cc.u32 c1, x1, 0;\n\t"              // carries iff x >= p
+        "madc.lo.u32 g, %9, %8, 0;\n\t"
+        "mad.lo.u32 %0, g, %10, x0;\n\t"
+        "mad.lo.u32 %1, g, %8, x1;\n\t}"
+        : "=r"(r0), "=r"(r1)
+        : "r"(l0), "r"(l1), "r"(l2), "r"(l3), "r"(sub_hi), "r"(GL_EPS32_C), "r"(GL_ONE_C), "r"(GL_ZERO_C), "r"(GL_MINUS1_C));
+    return ((u64)r1 << 32) | r0;
+}
+// x * 2^E (mod p), 0 < E < 96; x canonical -> canonical.  E must be a compile-time constant after unrolling: the limb
+// placement below is then resolved by the compiler and the zero limbs fold away.
+__device__ __forceinline__ u64 gl_mul_pow2_canon(u64 x, int E) {
+    const u32 x0 = (u32)x, x1 = (u32)(x >> 32);
+    const int s = E & 31;
+    const u32 z0 = x0 << s, z1 = __funnelshift_l(x0, x1, s), z2 = s ? (x1 >> (32 - s)) : 0u;  // x << s, three limbs
+    if (E < 32) return gl_reduce4_canon(z0, z1, z2, 0u, 0u);
+    if (E < 64) return gl_reduce4_canon(0u, z0, z1, z2, 0u);
+    return gl_reduce4_canon(0u, 0u, z0, z1, z2);  // 2^128 == -2^32: the top limb is subtracted one word up
+}
+
 // a + b (mod p): a lazy, b CANONICAL (< p) -> lazy.  One wrap fix suffices:
 // a + b - 2^64 + EPS <= (2^64-1) + (p-1) - 2^64 + EPS < 2^64.
 __device__ __forceinline__ u64 gl_add_lazy_canon(u64 a, u64 b) {

@@ -84,6 +84,10 @@ __device__ __forceinline__ int ntt_tw_pos(int e) { return e ^ (e >> 5); }
 #ifndef NTT_HI_VEC
 #define NTT_HI_VEC 1
 #endif
+// 1: the last stage group multiplies by its twiddles (powers of omega_16 = -2^60) with shifts (gl_mul_pow2_canon)
+#ifndef NTT_SHIFT_TW
+#define NTT_SHIFT_TW 1
+#endif
 #ifndef NTT_HI_UNROLL
 #define NTT_HI_UNROLL 4
 #endif
@@ -94,7 +98,7 @@ __device__ __forceinline__ int ntt_tw_pos(int e) { return e ^ (e >> 5); }
 // the 2^RHO points p = ((hi << RHO | m) << lobits) | lo of one column.  Butterfly (m0, m0 + half) of
 // local stage t has twiddle omega_{2^(bits - s0 - t)}^(mlow << lobits | lo)
 //   = omega_{2^bits}^((mlow << (bits - RHO + t)) + (lo << (s0 + t))), read from the table in shared memory.
-template <int RHO, bool LAST>
+template <int RHO, bool LAST, bool INV>
 __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, int bits, int w_log, int s0,
                                           int pitch) {
     constexpr int R = 1 << RHO;
@@ -122,6 +126,20 @@ __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, 
                 const int mlow = bf & (half - 1);
                 const int m0 = ((bf / half) * 2 * half) + mlow;
                 const int m1 = m0 + half;
+#if NTT_SHIFT_TW
+                if (LAST) {
+                    // twiddle omega_{2^RHO}^(mlow << t) = omega_16^j = 2^(156 j) (inverse: 2^(-156 j)); 2^96 == -1, and a
+                    // negative twiddle is the subtraction taken the other way round: (a - b) (-w) = (b - a) w
+                    const int j = (mlow << t) << (4 - RHO);
+                    const int e = INV ? (192 - (156 * j) % 192) % 192 : (156 * j) % 192;
+                    const bool neg = e >= 96;
+                    const u64 a0 = x[m0], b0 = x[m1];
+                    x[m0] = gl_sub_c(a0, gl_neg_p(b0));
+                    const u64 d = neg ? gl_sub_c(b0, a0) : gl_sub_c(a0, b0);
+                    x[m1] = mlow != 0 ? gl_mul_pow2_canon(d, neg ? e - 96 : e) : d;
+                    continue;
+                }
+#endif
                 gl_butterfly_c(x[m0], x[m1]);
                 if (!LAST || mlow != 0) x[m1] = gl_mul_c(x[m1], tws[ntt_tw_pos(e_lo | (mlow << (bits - RHO + t)))]);
             }
@@ -134,6 +152,7 @@ __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, 
     }
 }
 
+template <bool INV>
 __device__ __forceinline__ void dif_tile(u64 *sm, const u64 *__restrict__ tws, int bits, int w_log, int pitch,
                                          const NttGroups &G) {
     int s0 = 0;
@@ -141,17 +160,17 @@ __device__ __forceinline__ void dif_tile(u64 *sm, const u64 *__restrict__ tws, i
         const int rho = G.rho[g];
         if (g == G.n - 1) {
             switch (rho) {
-                case 1: dif_group<1, true>(sm, tws, bits, w_log, s0, pitch); break;
-                case 2: dif_group<2, true>(sm, tws, bits, w_log, s0, pitch); break;
-                case 3: dif_group<3, true>(sm, tws, bits, w_log, s0, pitch); break;
-                default: dif_group<4, true>(sm, tws, bits, w_log, s0, pitch); break;
+                case 1: dif_group<1, true, INV>(sm, tws, bits, w_log, s0, pitch); break;
+                case 2: dif_group<2, true, INV>(sm, tws, bits, w_log, s0, pitch); break;
+                case 3: dif_group<3, true, INV>(sm, tws, bits, w_log, s0, pitch); break;
+                default: dif_group<4, true, INV>(sm, tws, bits, w_log, s0, pitch); break;
             }
         } else {
-            switch (rho) {
-                case 1: dif_group<1, false>(sm, tws, bits, w_log, s0, pitch); break;
-                case 2: dif_group<2, false>(sm, tws, bits, w_log, s0, pitch); break;
-                case 3: dif_group<3, false>(sm, tws, bits, w_log, s0, pitch); break;
-                default: dif_group<4, false>(sm, tws, bits, w_log, s0, pitch); break;
+            switch (rho) {  // the direction only matters where twiddles are compile-time constants (the last group)
+                case 1: dif_group<1, false, false>(sm, tws, bits, w_log, s0, pitch); break;
+                case 2: dif_group<2, false, false>(sm, tws, bits, w_log, s0, pitch); break;
+                case 3: dif_group<3, false, false>(sm, tws, bits, w_log, s0, pitch); break;
+                default: dif_group<4, false, false>(sm, tws, bits, w_log, s0, pitch); break;
             }
         }
         __syncthreads();
@@ -195,7 +214,7 @@ extern "C" void bsx_debug_ntt_profile(unsigned long long *out, int reset) {
 // (with the conditions as run-time branches ptxas kept one load in flight per thread and the pass spent
 // 72 % of its time in these two loops).  POST: 0 = none (single pass; optional scale), 1 = two-level
 // inter-pass twiddle, 2 = full post-factor table.
-template <bool SRC_BITREV, bool HAS_PRE, int POST>
+template <bool SRC_BITREV, bool HAS_PRE, int POST, bool INV>
 __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
     extern __shared__ u64 sm_all[];
     const int a = P.a, b = P.b, w_log = P.w_log, pitch = P.pitch;
@@ -286,7 +305,7 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
         }
         __syncthreads();
         NTT_PROF_MARK(0);
-        dif_tile(sm, tws, a, w_log, pitch, P.groups);
+        dif_tile<INV>(sm, tws, a, w_log, pitch, P.groups);
         NTT_PROF_MARK(1);
         const u64 *__restrict__ post = POST == 2 ? P.post_full + ((size_t)k << P.log_n) + i0_base : nullptr;
 #if NTT_HI_VEC
@@ -353,16 +372,18 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
 }
 
 typedef void (*ntt_hi_fn)(NttKParams);
-static ntt_hi_fn ntt_hi_variant(bool src_bitrev, bool has_pre, int post) {
-    static const ntt_hi_fn tab[2][2][3] = {
-        {{ntt_pass_hi<false, false, 0>, ntt_pass_hi<false, false, 1>, ntt_pass_hi<false, false, 2>},
-         {ntt_pass_hi<false, true, 0>, ntt_pass_hi<false, true, 1>, ntt_pass_hi<false, true, 2>}},
-        {{ntt_pass_hi<true, false, 0>, ntt_pass_hi<true, false, 1>, ntt_pass_hi<true, false, 2>},
-         {ntt_pass_hi<true, true, 0>, ntt_pass_hi<true, true, 1>, ntt_pass_hi<true, true, 2>}}};
-    return tab[src_bitrev ? 1 : 0][has_pre ? 1 : 0][post];
+#define NTT_HI_ROW(B, H, I) {ntt_pass_hi<B, H, 0, I>, ntt_pass_hi<B, H, 1, I>, ntt_pass_hi<B, H, 2, I>}
+static ntt_hi_fn ntt_hi_variant(bool src_bitrev, bool has_pre, int post, bool inverse) {
+    static const ntt_hi_fn tab[2][2][2][3] = {
+        {{NTT_HI_ROW(false, false, false), NTT_HI_ROW(false, true, false)},
+         {NTT_HI_ROW(true, false, false), NTT_HI_ROW(true, true, false)}},
+        {{NTT_HI_ROW(false, false, true), NTT_HI_ROW(false, true, true)},
+         {NTT_HI_ROW(true, false, true), NTT_HI_ROW(true, true, true)}}};
+    return tab[inverse ? 1 : 0][src_bitrev ? 1 : 0][has_pre ? 1 : 0][post];
 }
 
 // Pass LO: in place on rows of 2^b contiguous words; tile = 2^w_log rows.  grid (rows / W, n_cols)
+template <bool INV>
 __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
     extern __shared__ u64 sm_all[];
     const int b = P.b, w_log = P.w_log, pitch = P.pitch;
@@ -411,7 +432,7 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
         }
     }
     __syncthreads();
-    dif_tile(sm, tws, b, w_log, pitch, P.groups);
+    dif_tile<INV>(sm, tws, b, w_log, pitch, P.groups);
     const bool scale = P.scale != 1 && !P.post_full;
 #if NTT_LO_VEC
     if (vec && (P.n_dest == 0 || P.dest_lc >= 1)) {
@@ -464,10 +485,11 @@ int ntt_max_single_pass_log() { return NTT_MAX_A; }
 
 // per-device opt-in to > 48 KB dynamic shared memory; called from bsx_ctx_create
 void ntt_init_device() {
-    for (int i = 0; i < 12; i++)
-        cudaFuncSetAttribute(ntt_hi_variant(i & 1, (i >> 1) & 1, i >> 2), cudaFuncAttributeMaxDynamicSharedMemorySize,
+    for (int i = 0; i < 24; i++)
+        cudaFuncSetAttribute(ntt_hi_variant(i & 1, (i >> 1) & 1, (i >> 2) % 3, i >= 12), cudaFuncAttributeMaxDynamicSharedMemorySize,
                              220 * 1024);
-    cudaFuncSetAttribute(ntt_pass_lo, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
 }
 
 // stage groups for a 2^bits-point tile transform: the last group (compile-time twiddles) takes up to
@@ -534,7 +556,7 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         int threads = NTT_THREADS;
         while (threads > 32 && threads > (int)(n_el >> 1)) threads >>= 1;
         const int post = plan.b == 0 ? 0 : (P.post_full ? 2 : 1);
-        BSX_COUNT_LAUNCH(); ntt_hi_variant(plan.src_bitrev != 0, plan.pre_hi != nullptr, post)<<<grid, threads, smem, st>>>(P);
+        BSX_COUNT_LAUNCH(); ntt_hi_variant(plan.src_bitrev != 0, plan.pre_hi != nullptr, post, plan.inverse != 0)<<<grid, threads, smem, st>>>(P);
     }
     if (plan.b > 0) {
         size_t rows = ((size_t)plan.n_cosets << plan.log_n) >> plan.b;  // per column
@@ -549,7 +571,9 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         size_t smem = sizeof(u64) * (((size_t)P.pitch << w_log) + ((size_t)1 << plan.b) / 2);
         int threads = NTT_THREADS;
         while (threads > 32 && threads > (int)(n_el >> 1)) threads >>= 1;
-        BSX_COUNT_LAUNCH(); ntt_pass_lo<<<grid, threads, smem, st>>>(P);
+        BSX_COUNT_LAUNCH();
+        if (plan.inverse) ntt_pass_lo<true><<<grid, threads, smem, st>>>(P);
+        else ntt_pass_lo<false><<<grid, threads, smem, st>>>(P);
     }
 }
 __global__ void fill_powers_kernel(u64 *out, u64 base, u64 first, size_t n) {
