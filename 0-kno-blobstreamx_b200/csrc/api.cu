@@ -234,14 +234,14 @@ extern "C" int32_t bsx_ctx_create(int32_t device, bsx_ctx **out) {
     }
     ntt_init_device();
     u64 *wf = nullptr, *wi = nullptr;
-    if (bsx_alloc_owned(ctx, &wf, 2048) || bsx_alloc_owned(ctx, &wi, 2048)) {
+    if (bsx_alloc_owned(ctx, &wf, 4096) || bsx_alloc_owned(ctx, &wi, 4096)) {
         cudaStreamDestroy(ctx->stream);
         delete ctx;
         return BSX_ERR_OOM;
     }
     u64 w = gl_host_root(12);
-    launch_fill_powers(wf, w, 1, 2048, ctx->stream);
-    launch_fill_powers(wi, gl_host_inv(w), 1, 2048, ctx->stream);
+    launch_fill_powers(wf, w, 1, 4096, ctx->stream);  // all 4096 powers: the radix stage groups index the full circle
+    launch_fill_powers(wi, gl_host_inv(w), 1, 4096, ctx->stream);
     ctx->tables.w_fwd = wf;
     ctx->tables.w_inv = wi;
     if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) {

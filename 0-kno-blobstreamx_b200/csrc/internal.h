@@ -39,7 +39,7 @@ void launch_gather_siblings(const u64 *digests, int log_leaves, int n_levels, u6
 // ---------------------------------------------------------------- NTT
 #define BSX_MAX_RANKS 16
 struct NttTables {
-    // omega_{4096}^j, j < 2048 (forward / inverse): sub-transform twiddles
+    // omega_{4096}^j, j < 4096 (forward / inverse): sub-transform twiddles
     const u64 *w_fwd, *w_inv;
 };
 // base^e = hi[e >> 12] * lo[e & 4095], e < 2^24

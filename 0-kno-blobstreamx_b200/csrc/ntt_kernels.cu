@@ -88,6 +88,17 @@ __device__ __forceinline__ int ntt_tw_pos(int e) { return e ^ (e >> 5); }
 #ifndef NTT_SHIFT_TW
 #define NTT_SHIFT_TW 1
 #endif
+// 1: the other stage groups run as radix-2^rho steps: shift twiddles inside, and the factors that depend on the thread's
+// position, omega^((lo * bitrev(m)) << s0), collected into ONE multiplication per output after the group (rho * 2^rho / 2
+// table multiplications become 2^rho - 1).  Needs the full table of 2^bits twiddles in shared memory.
+#ifndef NTT_RADIX_GROUPS
+#define NTT_RADIX_GROUPS 1
+#endif
+#define NTT_TW_FULL (NTT_SHIFT_TW && NTT_RADIX_GROUPS)
+// Twiddle table in shared memory: all 2^bits powers and radix groups (FULLTW kernels) for tiles of up to 2^10 points; 2^11-
+// and 2^12-point tiles keep the half table and the per-stage twiddles -- a full table would cost them the third CTA per
+// SM (measured: 2^24-row iNTT 7.28 -> 7.95 ms), and folding omega^(N/2) = -1 into the operand instead was slower too (7.81).
+static inline bool ntt_tw_full(int bits) { return NTT_TW_FULL && bits < 11; }
 #ifndef NTT_HI_UNROLL
 #define NTT_HI_UNROLL 4
 #endif
@@ -98,7 +109,7 @@ __device__ __forceinline__ int ntt_tw_pos(int e) { return e ^ (e >> 5); }
 // the 2^RHO points p = ((hi << RHO | m) << lobits) | lo of one column.  Butterfly (m0, m0 + half) of
 // local stage t has twiddle omega_{2^(bits - s0 - t)}^(mlow << lobits | lo)
 //   = omega_{2^bits}^((mlow << (bits - RHO + t)) + (lo << (s0 + t))), read from the table in shared memory.
-template <int RHO, bool LAST, bool INV>
+template <int RHO, bool LAST, bool INV, bool FULLTW>
 __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, int bits, int w_log, int s0,
                                           int pitch) {
     constexpr int R = 1 << RHO;
@@ -127,7 +138,7 @@ __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, 
                 const int m0 = ((bf / half) * 2 * half) + mlow;
                 const int m1 = m0 + half;
 #if NTT_SHIFT_TW
-                if (LAST) {
+                if (LAST || FULLTW) {
                     // twiddle omega_{2^RHO}^(mlow << t) = omega_16^j = 2^(156 j) (inverse: 2^(-156 j)); 2^96 == -1, and a
                     // negative twiddle is the subtraction taken the other way round: (a - b) (-w) = (b - a) w
                     const int j = (mlow << t) << (4 - RHO);
@@ -144,6 +155,15 @@ __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, 
                 if (!LAST || mlow != 0) x[m1] = gl_mul_c(x[m1], tws[ntt_tw_pos(e_lo | (mlow << (bits - RHO + t)))]);
             }
         }
+        if (!LAST && FULLTW) {
+            // position m holds output k = bitrev_RHO(m) of the radix-R step: its factor is omega_{2^bits}^((lo k) << s0)
+            const int base = lo << s0;
+#pragma unroll
+            for (int m = 1; m < R; m++) {
+                const int k = (int)(__brev((unsigned)m) >> (32 - RHO));
+                x[m] = gl_mul_c(x[m], tws[ntt_tw_pos(base * k)]);
+            }
+        }
 #pragma unroll
         for (int m = 0; m < R; m++) {
             int p = p0 + (m << lobits);
@@ -152,7 +172,7 @@ __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, 
     }
 }
 
-template <bool INV>
+template <bool INV, bool FULLTW>
 __device__ __forceinline__ void dif_tile(u64 *sm, const u64 *__restrict__ tws, int bits, int w_log, int pitch,
                                          const NttGroups &G) {
     int s0 = 0;
@@ -160,17 +180,17 @@ __device__ __forceinline__ void dif_tile(u64 *sm, const u64 *__restrict__ tws, i
         const int rho = G.rho[g];
         if (g == G.n - 1) {
             switch (rho) {
-                case 1: dif_group<1, true, INV>(sm, tws, bits, w_log, s0, pitch); break;
-                case 2: dif_group<2, true, INV>(sm, tws, bits, w_log, s0, pitch); break;
-                case 3: dif_group<3, true, INV>(sm, tws, bits, w_log, s0, pitch); break;
-                default: dif_group<4, true, INV>(sm, tws, bits, w_log, s0, pitch); break;
+                case 1: dif_group<1, true, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 2: dif_group<2, true, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 3: dif_group<3, true, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
+                default: dif_group<4, true, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
             }
         } else {
-            switch (rho) {  // the direction only matters where twiddles are compile-time constants (the last group)
-                case 1: dif_group<1, false, false>(sm, tws, bits, w_log, s0, pitch); break;
-                case 2: dif_group<2, false, false>(sm, tws, bits, w_log, s0, pitch); break;
-                case 3: dif_group<3, false, false>(sm, tws, bits, w_log, s0, pitch); break;
-                default: dif_group<4, false, false>(sm, tws, bits, w_log, s0, pitch); break;
+            switch (rho) {
+                case 1: dif_group<1, false, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 2: dif_group<2, false, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 3: dif_group<3, false, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
+                default: dif_group<4, false, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
             }
         }
         __syncthreads();
@@ -178,9 +198,9 @@ __device__ __forceinline__ void dif_tile(u64 *sm, const u64 *__restrict__ tws, i
     }
 }
 
-// omega_{2^bits}^e, e < 2^(bits-1), from the omega_4096 table into shared memory
-__device__ __forceinline__ void load_twiddles(u64 *tws, const u64 *__restrict__ wtab, int bits) {
-    const int n = bits > 0 ? 1 << (bits - 1) : 0;
+// omega_{2^bits}^e, e < 2^(bits-1) (NTT_TW_FULL: e < 2^bits), from the omega_4096 table into shared memory
+__device__ __forceinline__ void load_twiddles(u64 *tws, const u64 *__restrict__ wtab, int bits, bool full) {
+    const int n = full ? (1 << bits) : (bits > 0 ? 1 << (bits - 1) : 0);
     for (int e = threadIdx.x; e < n; e += blockDim.x)
         tws[ntt_tw_pos(e)] = __ldg(wtab + ((size_t)e << (NTT_MAX_A - bits)));
 }
@@ -214,18 +234,18 @@ extern "C" void bsx_debug_ntt_profile(unsigned long long *out, int reset) {
 // (with the conditions as run-time branches ptxas kept one load in flight per thread and the pass spent
 // 72 % of its time in these two loops).  POST: 0 = none (single pass; optional scale), 1 = two-level
 // inter-pass twiddle, 2 = full post-factor table.
-template <bool SRC_BITREV, bool HAS_PRE, int POST, bool INV>
+template <bool SRC_BITREV, bool HAS_PRE, int POST, bool INV, bool FULLTW>
 __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
     extern __shared__ u64 sm_all[];
     const int a = P.a, b = P.b, w_log = P.w_log, pitch = P.pitch;
     const int R = 1 << a, W = 1 << w_log;
-    u64 *tws = sm_all, *sm = sm_all + (R >> 1);
+    u64 *tws = sm_all, *sm = sm_all + (FULLTW ? R : (R >> 1));
     const int col = blockIdx.x;
     const size_t i0_base = (size_t)blockIdx.y << w_log;
     const u64 *__restrict__ src = P.src + (size_t)col * P.src_stride;
     const int n_el = R << w_log;
     const int n_cosets = 1 << P.r_log;
-    load_twiddles(tws, P.wtab, a);
+    load_twiddles(tws, P.wtab, a, FULLTW);
 #ifdef NTT_PROFILE
     long long t_prev = clock64();
 #endif
@@ -305,7 +325,7 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
         }
         __syncthreads();
         NTT_PROF_MARK(0);
-        dif_tile<INV>(sm, tws, a, w_log, pitch, P.groups);
+        dif_tile<INV, FULLTW>(sm, tws, a, w_log, pitch, P.groups);
         NTT_PROF_MARK(1);
         const u64 *__restrict__ post = POST == 2 ? P.post_full + ((size_t)k << P.log_n) + i0_base : nullptr;
 #if NTT_HI_VEC
@@ -372,27 +392,25 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_hi(NttKParams P) {
 }
 
 typedef void (*ntt_hi_fn)(NttKParams);
-#define NTT_HI_ROW(B, H, I) {ntt_pass_hi<B, H, 0, I>, ntt_pass_hi<B, H, 1, I>, ntt_pass_hi<B, H, 2, I>}
-static ntt_hi_fn ntt_hi_variant(bool src_bitrev, bool has_pre, int post, bool inverse) {
-    static const ntt_hi_fn tab[2][2][2][3] = {
-        {{NTT_HI_ROW(false, false, false), NTT_HI_ROW(false, true, false)},
-         {NTT_HI_ROW(true, false, false), NTT_HI_ROW(true, true, false)}},
-        {{NTT_HI_ROW(false, false, true), NTT_HI_ROW(false, true, true)},
-         {NTT_HI_ROW(true, false, true), NTT_HI_ROW(true, true, true)}}};
-    return tab[inverse ? 1 : 0][src_bitrev ? 1 : 0][has_pre ? 1 : 0][post];
+#define NTT_HI_ROW(B, H, I, F) {ntt_pass_hi<B, H, 0, I, F>, ntt_pass_hi<B, H, 1, I, F>, ntt_pass_hi<B, H, 2, I, F>}
+#define NTT_HI_DIR(I, F) {{NTT_HI_ROW(false, false, I, F), NTT_HI_ROW(false, true, I, F)}, {NTT_HI_ROW(true, false, I, F), NTT_HI_ROW(true, true, I, F)}}
+static ntt_hi_fn ntt_hi_variant(bool src_bitrev, bool has_pre, int post, bool inverse, bool full_tw) {
+    static const ntt_hi_fn tab[2][2][2][2][3] = {{NTT_HI_DIR(false, false), NTT_HI_DIR(true, false)},
+                                                 {NTT_HI_DIR(false, true), NTT_HI_DIR(true, true)}};
+    return tab[full_tw ? 1 : 0][inverse ? 1 : 0][src_bitrev ? 1 : 0][has_pre ? 1 : 0][post];
 }
 
 // Pass LO: in place on rows of 2^b contiguous words; tile = 2^w_log rows.  grid (rows / W, n_cols)
-template <bool INV>
+template <bool INV, bool FULLTW>
 __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
     extern __shared__ u64 sm_all[];
     const int b = P.b, w_log = P.w_log, pitch = P.pitch;
     const int S = 1 << b;
-    u64 *tws = sm_all, *sm = sm_all + (S >> 1);
+    u64 *tws = sm_all, *sm = sm_all + (FULLTW ? S : (S >> 1));
     const int n_el = 1 << (b + w_log);
     const size_t l0 = (size_t)blockIdx.x << (b + w_log);
     u64 *base = P.dst + (size_t)blockIdx.y * P.dst_stride + l0;
-    load_twiddles(tws, P.wtab, b);
+    load_twiddles(tws, P.wtab, b, FULLTW);
 #if NTT_LO_VEC
     // 128-bit global accesses: a thread moves two adjacent points (they stay adjacent in the padded tile: the pad
     // words sit in front of multiples of 32 and the second point of a pair is odd)
@@ -432,7 +450,7 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
         }
     }
     __syncthreads();
-    dif_tile<INV>(sm, tws, b, w_log, pitch, P.groups);
+    dif_tile<INV, FULLTW>(sm, tws, b, w_log, pitch, P.groups);
     const bool scale = P.scale != 1 && !P.post_full;
 #if NTT_LO_VEC
     if (vec && (P.n_dest == 0 || P.dest_lc >= 1)) {
@@ -485,11 +503,13 @@ int ntt_max_single_pass_log() { return NTT_MAX_A; }
 
 // per-device opt-in to > 48 KB dynamic shared memory; called from bsx_ctx_create
 void ntt_init_device() {
-    for (int i = 0; i < 24; i++)
-        cudaFuncSetAttribute(ntt_hi_variant(i & 1, (i >> 1) & 1, (i >> 2) % 3, i >= 12), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             220 * 1024);
-    cudaFuncSetAttribute(ntt_pass_lo<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    cudaFuncSetAttribute(ntt_pass_lo<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    for (int i = 0; i < 48; i++)
+        cudaFuncSetAttribute(ntt_hi_variant(i & 1, (i >> 1) & 1, (i >> 2) % 3, (i / 12) & 1, i >= 24),
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
 }
 
 // stage groups for a 2^bits-point tile transform: the last group (compile-time twiddles) takes up to
@@ -552,11 +572,11 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         dim3 grid((unsigned)n_cols, (unsigned)(((size_t)1 << plan.b) >> w_log));
         size_t n_el = (size_t)1 << (plan.a + w_log);
         P.pitch = ntt_pitch(plan.a);
-        size_t smem = sizeof(u64) * (((size_t)P.pitch << w_log) + ((size_t)1 << plan.a) / 2);
+        size_t smem = sizeof(u64) * (((size_t)P.pitch << w_log) + ((size_t)1 << plan.a) / (ntt_tw_full(plan.a) ? 1 : 2));
         int threads = NTT_THREADS;
         while (threads > 32 && threads > (int)(n_el >> 1)) threads >>= 1;
         const int post = plan.b == 0 ? 0 : (P.post_full ? 2 : 1);
-        BSX_COUNT_LAUNCH(); ntt_hi_variant(plan.src_bitrev != 0, plan.pre_hi != nullptr, post, plan.inverse != 0)<<<grid, threads, smem, st>>>(P);
+        BSX_COUNT_LAUNCH(); ntt_hi_variant(plan.src_bitrev != 0, plan.pre_hi != nullptr, post, plan.inverse != 0, ntt_tw_full(plan.a))<<<grid, threads, smem, st>>>(P);
     }
     if (plan.b > 0) {
         size_t rows = ((size_t)plan.n_cosets << plan.log_n) >> plan.b;  // per column
@@ -568,12 +588,18 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         dim3 grid((unsigned)(rows >> w_log), (unsigned)n_cols);
         size_t n_el = (size_t)1 << (plan.b + w_log);
         P.pitch = ntt_pitch(plan.b);
-        size_t smem = sizeof(u64) * (((size_t)P.pitch << w_log) + ((size_t)1 << plan.b) / 2);
+        size_t smem = sizeof(u64) * (((size_t)P.pitch << w_log) + ((size_t)1 << plan.b) / (ntt_tw_full(plan.b) ? 1 : 2));
         int threads = NTT_THREADS;
         while (threads > 32 && threads > (int)(n_el >> 1)) threads >>= 1;
         BSX_COUNT_LAUNCH();
-        if (plan.inverse) ntt_pass_lo<true><<<grid, threads, smem, st>>>(P);
-        else ntt_pass_lo<false><<<grid, threads, smem, st>>>(P);
+        const bool full = ntt_tw_full(plan.b);
+        if (plan.inverse) {
+            if (full) ntt_pass_lo<true, true><<<grid, threads, smem, st>>>(P);
+            else ntt_pass_lo<true, false><<<grid, threads, smem, st>>>(P);
+        } else {
+            if (full) ntt_pass_lo<false, true><<<grid, threads, smem, st>>>(P);
+            else ntt_pass_lo<false, false><<<grid, threads, smem, st>>>(P);
+        }
     }
 }
 __global__ void fill_powers_kernel(u64 *out, u64 base, u64 first, size_t n) {
