@@ -621,7 +621,18 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, const u64 *const *col_ptr
             std::vector<int> cstart;  // chunk k covers columns [cstart[k], cstart[k + 1])
             {
                 int c = 0;
-                if (n_cols >= 64 && chunk > 12)
+                // BSX_CHUNK_SCHEDULE="4,8,12,..." (measurement aid): explicit chunk sizes; what they leave goes in default chunks
+                if (const char *env = getenv("BSX_CHUNK_SCHEDULE")) {
+                    for (const char *q = env; *q && c < n_cols;) {
+                        int r = atoi(q);
+                        if (r < 1) break;
+                        if (r > n_cols - c) r = n_cols - c;
+                        cstart.push_back(c);
+                        c += r;
+                        while (*q && *q != ',') q++;
+                        if (*q == ',') q++;
+                    }
+                } else if (n_cols >= 64 && chunk > 12)
                     for (int r : {8, 12}) {
                         cstart.push_back(c);
                         c += r;
@@ -630,7 +641,7 @@ static int batch_build(bsx_ctx *ctx, const u64 *input, const u64 *const *col_ptr
                     cstart.push_back(c);
                     c += chunk;
                 }
-                if (cstart.size() > 1 && n_cols - cstart.back() < 8) cstart.pop_back();  // no tile-starved tail
+                if (!getenv("BSX_CHUNK_SCHEDULE") && cstart.size() > 1 && n_cols - cstart.back() < 8) cstart.pop_back();  // no tile-starved tail
                 cstart.push_back(n_cols);
             }
             const int n_chunks = (int)cstart.size() - 1;
