@@ -25,6 +25,8 @@ struct bsx_shard {
     u64 *slab;             // n_cols_total x chunk, column-major: this rank's leaf rows (cudaMalloc: IPC-able)
     u64 *peer[BSX_MAX_RANKS];   // every rank's slab as seen from this device (peer[rank] == slab)
     bool peer_ipc[BSX_MAX_RANKS];
+    bool peer_same_device[BSX_MAX_RANKS];  // an IPC peer that lives on this rank's own GPU (see device_tag)
+    u64 device_tag;
     u64 *staging;          // optional destination-major send buffer: n_ranks x (c1 - c0) x chunk
     u64 *coeffs;           // (c1 - c0) x 2^log_n
     bool coeffs_bitrev;
@@ -80,12 +82,23 @@ extern "C" int32_t bsx_shard_create(bsx_ctx *ctx, int32_t log_n, int32_t n_cols_
     for (int i = 0; i < BSX_MAX_RANKS; i++) {
         s->peer[i] = nullptr;
         s->peer_ipc[i] = false;
+        s->peer_same_device[i] = false;
     }
     s->slab_words = s->chunk * (size_t)n_cols_total;
     s->cap_words = (size_t)4 << (cap_height > log_ranks ? cap_height - log_ranks : 0);
     s->epoch = 0;
     s->timeout_flag = nullptr;
-    const size_t mail_words = (size_t)n_ranks * (2 + s->cap_words);
+    // + one word behind the mailbox: a tag of the physical device (PCI domain : bus : device), so that a peer mapping the
+    // slab through IPC can tell whether it shares this GPU
+    const size_t mail_words = (size_t)n_ranks * (2 + s->cap_words) + 1;
+    {
+        cudaDeviceProp prop;
+        s->device_tag = 0;
+        if (cudaGetDeviceProperties(&prop, ctx->device) == cudaSuccess)
+            s->device_tag = ((u64)1 << 63) | ((u64)(unsigned)prop.pciDomainID << 32) | ((u64)(unsigned)prop.pciBusID << 16) |
+                            (u64)(unsigned)prop.pciDeviceID;
+        cudaGetLastError();
+    }
     size_t bytes = (s->slab_words + mail_words) * sizeof(u64);
     if (bytes) {
         cudaError_t e = cudaMalloc((void **)&s->slab, bytes);  // not the async pool: cudaIpcGetMemHandle needs cudaMalloc
@@ -95,6 +108,7 @@ extern "C" int32_t bsx_shard_create(bsx_ctx *ctx, int32_t log_n, int32_t n_cols_
             return bsx_fail(ctx, BSX_ERR_OOM, "row slab of %zu bytes: %s", bytes, cudaGetErrorString(e));
         }
         cudaMemsetAsync(s->slab + s->slab_words, 0, mail_words * sizeof(u64), ctx->stream);
+        cudaMemcpyAsync(s->slab + s->slab_words + mail_words - 1, &s->device_tag, sizeof(u64), cudaMemcpyHostToDevice, ctx->stream);
         cudaStreamSynchronize(ctx->stream);  // before any peer can learn the address
     }
     s->peer[rank] = s->slab;
@@ -141,6 +155,12 @@ extern "C" int32_t bsx_shard_set_peer_ipc(bsx_shard *s, int32_t peer_rank, const
     CU(s->ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
     s->peer[peer_rank] = (u64 *)p;
     s->peer_ipc[peer_rank] = true;
+    {   // does the peer live on this very GPU?  (two processes on one device: the device-side barrier must not be used)
+        u64 tag = 0;
+        const size_t tag_at = s->slab_words + (size_t)s->n_ranks * (2 + s->cap_words);
+        CU(s->ctx, cudaMemcpy(&tag, (u64 *)p + tag_at, sizeof(u64), cudaMemcpyDeviceToHost));
+        s->peer_same_device[peer_rank] = tag != 0 && tag == s->device_tag;
+    }
     return BSX_OK;
 }
 
@@ -380,10 +400,14 @@ extern "C" int32_t bsx_shard_run_p2p(bsx_shard *s, const uint64_t *input, int32_
     for (int p = 0; p < BSX_MAX_RANKS; p++) M.mail[p] = nullptr;
     for (int p = 0; p < s->n_ranks; p++) {
         if (!s->peer[p]) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "row slab of rank %d is not set", p);
-        if (p != s->rank && !s->peer_ipc[p]) {  // (an IPC mapping always reports the mapping device: one process per GPU is the caller's contract there)
-            cudaPointerAttributes at;
-            CU(ctx, cudaPointerGetAttributes(&at, s->peer[p]));
-            if (at.device == ctx->device)  // two ranks on one GPU: their barrier kernels could wait on each other forever
+        if (p != s->rank) {
+            bool same = s->peer_same_device[p];  // IPC peers: by the device tag behind their mailbox
+            if (!s->peer_ipc[p]) {
+                cudaPointerAttributes at;
+                CU(ctx, cudaPointerGetAttributes(&at, s->peer[p]));
+                same = at.device == ctx->device;
+            }
+            if (same)  // two ranks on one GPU: their barrier kernels could wait on each other forever
                 return bsx_fail(ctx, BSX_ERR_UNSUPPORTED, "rank %d shares device %d with rank %d: the device-side barrier needs "
                                 "one GPU per rank (use bsx_shard_transform / bsx_shard_commit with a host barrier)", p, ctx->device, s->rank);
         }

@@ -205,7 +205,8 @@ int32_t bsx_shard_transform_cols(bsx_shard *s, const uint64_t *input, int32_t me
  * hashing and cap subtrees -> the local caps published to every rank -> rank_caps_host (n_ranks x 2^(local cap height)
  * x 4 words, rank order; equal on every rank).  A pinned host input is uploaded in column chunks under the transforms.
  * Collective: every rank must call it the same number of times.  BSX_ERR_UNSUPPORTED when two ranks share a device
- * (their barrier kernels could wait on each other): use bsx_shard_transform / host barrier / bsx_shard_commit there.
+ * (their barrier kernels could wait on each other; detected for peer pointers and, through a device tag behind the slab,
+ * for IPC peers of other processes): use bsx_shard_transform / host barrier / bsx_shard_commit there.
  * timing->h2d_ms carries the wait for the slowest peer. */
 int32_t bsx_shard_run_p2p(bsx_shard *s, const uint64_t *input, int32_t mem, int32_t input_is_coeffs, bsx_tree **tree_out,
                           uint64_t *rank_caps_host, bsx_timing *timing);

@@ -199,3 +199,16 @@ def test_sharded_prove_openings_equals_single_gpu(pkg, ctx, world, cap_height):
             s.close()
     for b in fresh:
         b.close()
+
+
+def test_device_barrier_refuses_two_processes_on_one_gpu(tmp_path):
+    """bsx_shard_run_p2p spins on flags that the peer's kernel writes: two ranks on ONE GPU (here two processes with
+    IPC-mapped slabs) could wait on each other, so the call must refuse them (device tag behind the mailbox) before it
+    launches anything."""
+    worker = os.path.join(ROOT, "tests", "ipc_same_device_worker.py")
+    ps = [subprocess.Popen([sys.executable, worker, str(r), str(tmp_path)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+          for r in range(2)]
+    outs = [p.communicate(timeout=180) for p in ps]
+    for p, (out, err) in zip(ps, outs):
+        assert p.returncode == 0, err[-2000:]
+        assert "rc=-4" in out and "shares device" in out, out + err[-1000:]
