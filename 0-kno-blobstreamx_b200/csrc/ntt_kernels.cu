@@ -30,6 +30,15 @@
 #endif
 #include "gl.cuh"
 
+// 1: pass LO moves its tile with bulk tensor copies (TMA) instead of LDG/STS + LDS/STG loops: LDE 20.69 -> 19.77 ms,
+// iNTT 2.69 -> 2.56 ms at 2^20 x 135 (profiles/r02_ntt_variants.txt); 0 keeps the loops (A/B builds)
+#ifndef NTT_LO_TMA
+#define NTT_LO_TMA 1
+#endif
+#if NTT_LO_TMA
+#include <cuda.h>
+#endif
+
 #define NTT_THREADS 256
 #define NTT_MAX_A 12
 #ifndef NTT_W_MIN_A12
@@ -77,6 +86,11 @@ __device__ __forceinline__ int ntt_sm(int j, int p, int pitch) { return j * pitc
 // Twiddle table position: stage s reads entries e = off << s, a stride-2^s walk across the lanes; XOR-ing
 // bits 5.. into the low bits spreads every such walk over all banks.
 __device__ __forceinline__ int ntt_tw_pos(int e) { return e ^ (e >> 5); }
+// Unpadded tile as a bulk tensor copy with CU_TENSOR_MAP_SWIZZLE_128B leaves it (NTT_LO_TMA): the 16-byte chunk index
+// inside a 128-byte line is XOR-ed with the line index mod 8, i.e. bits 1..3 of the word index with bits 4..6.
+__device__ __forceinline__ int ntt_xsw(int p) { return p ^ (((p >> 4) & 7) << 1); }
+template <bool XSW>
+__device__ __forceinline__ int ntt_pos(int p) { return XSW ? ntt_xsw(p) : ntt_swz(p); }
 #define NTT_IO_UNROLL 8
 #ifndef NTT_LO_VEC
 #define NTT_LO_VEC 1
@@ -109,7 +123,7 @@ static inline bool ntt_tw_full(int bits) { return NTT_TW_FULL && bits < 11; }
 // the 2^RHO points p = ((hi << RHO | m) << lobits) | lo of one column.  Butterfly (m0, m0 + half) of
 // local stage t has twiddle omega_{2^(bits - s0 - t)}^(mlow << lobits | lo)
 //   = omega_{2^bits}^((mlow << (bits - RHO + t)) + (lo << (s0 + t))), read from the table in shared memory.
-template <int RHO, bool LAST, bool INV, bool FULLTW>
+template <int RHO, bool LAST, bool INV, bool FULLTW, bool XSW = false>
 __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, int bits, int w_log, int s0,
                                           int pitch) {
     constexpr int R = 1 << RHO;
@@ -126,7 +140,7 @@ __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, 
 #pragma unroll
         for (int m = 0; m < R; m++) {
             int p = p0 + (m << lobits);
-            x[m] = col[ntt_swz(p)];
+            x[m] = col[ntt_pos<XSW>(p)];
         }
 #pragma unroll
         for (int t = 0; t < RHO; t++) {
@@ -167,12 +181,12 @@ __device__ __forceinline__ void dif_group(u64 *sm, const u64 *__restrict__ tws, 
 #pragma unroll
         for (int m = 0; m < R; m++) {
             int p = p0 + (m << lobits);
-            col[ntt_swz(p)] = x[m];
+            col[ntt_pos<XSW>(p)] = x[m];
         }
     }
 }
 
-template <bool INV, bool FULLTW>
+template <bool INV, bool FULLTW, bool XSW = false>
 __device__ __forceinline__ void dif_tile(u64 *sm, const u64 *__restrict__ tws, int bits, int w_log, int pitch,
                                          const NttGroups &G) {
     int s0 = 0;
@@ -180,17 +194,17 @@ __device__ __forceinline__ void dif_tile(u64 *sm, const u64 *__restrict__ tws, i
         const int rho = G.rho[g];
         if (g == G.n - 1) {
             switch (rho) {
-                case 1: dif_group<1, true, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
-                case 2: dif_group<2, true, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
-                case 3: dif_group<3, true, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
-                default: dif_group<4, true, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 1: dif_group<1, true, INV, FULLTW, XSW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 2: dif_group<2, true, INV, FULLTW, XSW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 3: dif_group<3, true, INV, FULLTW, XSW>(sm, tws, bits, w_log, s0, pitch); break;
+                default: dif_group<4, true, INV, FULLTW, XSW>(sm, tws, bits, w_log, s0, pitch); break;
             }
         } else {
             switch (rho) {
-                case 1: dif_group<1, false, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
-                case 2: dif_group<2, false, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
-                case 3: dif_group<3, false, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
-                default: dif_group<4, false, INV, FULLTW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 1: dif_group<1, false, INV, FULLTW, XSW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 2: dif_group<2, false, INV, FULLTW, XSW>(sm, tws, bits, w_log, s0, pitch); break;
+                case 3: dif_group<3, false, INV, FULLTW, XSW>(sm, tws, bits, w_log, s0, pitch); break;
+                default: dif_group<4, false, INV, FULLTW, XSW>(sm, tws, bits, w_log, s0, pitch); break;
             }
         }
         __syncthreads();
@@ -476,6 +490,112 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
     }
 }
 
+#if NTT_LO_TMA
+// Pass LO with the tile moved by the copy engine (tiles of 2^7-point rows and up; ntt_pass_lo stays for the small ones and
+// for a driver without cuTensorMapEncodeTiled): the tile is one contiguous run
+// of 2^(b + w_log) words, described to the TMA unit as lines of 16 words; `cp.async.bulk.tensor.2d` brings it in as boxes
+// of 256 lines with the 128-byte hardware swizzle (no pad words; dif_tile<.., XSW>), one thread arms the mbarrier and
+// issues the copies, the others fill the twiddle table meanwhile.  The result goes back the same way unless it has to be
+// scaled or re-routed to another rank's slab.
+__device__ __forceinline__ u32 ntt_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+
+template <bool INV, bool FULLTW>
+__global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo_tma(const __grid_constant__ CUtensorMap tmap, NttKParams P) {
+    extern __shared__ __align__(1024) u64 sm_tma[];
+    const int b = P.b, w_log = P.w_log;
+    const int S = 1 << b;
+    const int n_el = 1 << (b + w_log);
+    u64 *sm = sm_tma, *tws = sm_tma + n_el;
+    u64 *bar = tws + (FULLTW ? S : (S >> 1));
+    const size_t l0 = (size_t)blockIdx.x << (b + w_log);
+    const size_t word0 = (size_t)blockIdx.y * P.dst_stride + l0;
+    const int n_lines = n_el >> 4;
+    const int box = n_lines < 256 ? n_lines : 256;
+    const int line0 = (int)(word0 >> 4);
+    const u32 bar_a = ntt_smem_addr(bar);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_a) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a), "r"(n_el * 8) : "memory");
+        for (int c = 0; c < n_lines; c += box)
+            asm volatile(
+                "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                ::"r"(ntt_smem_addr(sm + ((size_t)c << 4))), "l"(&tmap), "r"(0), "r"(line0 + c), "r"(bar_a)
+                : "memory");
+    }
+    load_twiddles(tws, P.wtab, b, FULLTW);
+    __syncthreads();  // the barrier word is initialised for everybody; the table is complete
+    {
+        u32 done = 0;
+        while (!done)
+            asm volatile(
+                "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                : "=r"(done)
+                : "r"(bar_a), "r"(0)
+                : "memory");
+    }
+    dif_tile<INV, FULLTW, true>(sm, tws, b, w_log, S, P.groups);
+    const bool scale = P.scale != 1 && !P.post_full;
+    if (!scale && P.n_dest == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int c = 0; c < n_lines; c += box)
+                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&tmap),
+                             "r"(0), "r"(line0 + c), "r"(ntt_smem_addr(sm + ((size_t)c << 4)))
+                             : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+        return;
+    }
+    u64 *base = P.dst + word0;
+    for (int q = threadIdx.x; q < n_el / 2; q += blockDim.x) {
+        const int e = 2 * q;
+        const u64 *srcp = sm + ((e >> b) << b) + ntt_xsw(e & (S - 1));
+        u64 v0 = srcp[0], v1 = srcp[1];
+        if (scale) {
+            v0 = gl_mul_c(v0, P.scale);
+            v1 = gl_mul_c(v1, P.scale);
+        }
+        if (P.n_dest && P.dest_lc < 1) {
+            __stcs(ntt_out(P, blockIdx.y, l0 + e), v0);
+            __stcs(ntt_out(P, blockIdx.y, l0 + e + 1), v1);
+        } else {
+            u64 *o = P.n_dest ? ntt_out(P, blockIdx.y, l0 + e) : base + e;
+            __stcs(reinterpret_cast<ulonglong2 *>(o), make_ulonglong2(v0, v1));
+        }
+    }
+}
+
+typedef CUresult (*ntt_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static ntt_encode_fn ntt_tensor_map_encoder() {
+    static ntt_encode_fn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return (ntt_encode_fn)f;
+    }();
+    return fn;
+}
+// the buffer `words` long at `base` as lines of 16 words, boxes of `box` lines, 128-byte swizzle
+static bool ntt_lines_map(CUtensorMap *m, u64 *base, size_t words, int box) {
+    ntt_encode_fn enc = ntt_tensor_map_encoder();
+    if (!enc || ((uintptr_t)base & 127) || (words & 15) || (words >> 4) >= ((size_t)1 << 31)) return false;
+    cuuint64_t dims[2] = {16, (cuuint64_t)(words >> 4)};
+    cuuint64_t strides[1] = {128};
+    cuuint32_t boxd[2] = {16, (cuuint32_t)box};
+    cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, base, dims, strides, boxd, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+#endif
+
 // post_full[k][p][i0] = scale * pre_lo[k][i0] * omega_N^(i0 * bitrev_a(p)): everything pass HI multiplies
 // into an output word besides the data, built once per (size, coset set) and cached in the context
 __global__ void ntt_post_table_kernel(u64 *out, const u64 *pre_lo, const u64 *tw_lo, const u64 *tw_hi, u64 scale,
@@ -510,6 +630,12 @@ void ntt_init_device() {
     cudaFuncSetAttribute(ntt_pass_lo<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
     cudaFuncSetAttribute(ntt_pass_lo<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
     cudaFuncSetAttribute(ntt_pass_lo<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+#if NTT_LO_TMA
+    cudaFuncSetAttribute(ntt_pass_lo_tma<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo_tma<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo_tma<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(ntt_pass_lo_tma<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+#endif
 }
 
 // stage groups for a 2^bits-point tile transform: the last group (compile-time twiddles) takes up to
@@ -593,6 +719,22 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
         while (threads > 32 && threads > (int)(n_el >> 1)) threads >>= 1;
         BSX_COUNT_LAUNCH();
         const bool full = ntt_tw_full(plan.b);
+#if NTT_LO_TMA
+        CUtensorMap tmap;
+        const size_t span = (size_t)(n_cols - 1) * dst_stride + ((size_t)plan.n_cosets << plan.log_n);
+        if (plan.b >= 7 && threads == NTT_THREADS && (dst_stride & 15) == 0 &&
+            ntt_lines_map(&tmap, dst, span, (int)((n_el >> 4) < 256 ? (n_el >> 4) : 256))) {
+            size_t smem_t = sizeof(u64) * (n_el + ((size_t)1 << plan.b) / (full ? 1 : 2) + 2);
+            if (plan.inverse) {
+                if (full) ntt_pass_lo_tma<true, true><<<grid, threads, smem_t, st>>>(tmap, P);
+                else ntt_pass_lo_tma<true, false><<<grid, threads, smem_t, st>>>(tmap, P);
+            } else {
+                if (full) ntt_pass_lo_tma<false, true><<<grid, threads, smem_t, st>>>(tmap, P);
+                else ntt_pass_lo_tma<false, false><<<grid, threads, smem_t, st>>>(tmap, P);
+            }
+            return;
+        }
+#endif
         if (plan.inverse) {
             if (full) ntt_pass_lo<true, true><<<grid, threads, smem, st>>>(P);
             else ntt_pass_lo<true, false><<<grid, threads, smem, st>>>(P);

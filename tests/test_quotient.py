@@ -162,6 +162,51 @@ def test_device_quotient_values_equal_the_oracle(pkg, ctx, oracle, degree_bits, 
 
 
 @pytest.mark.gpu
+def test_device_quotient_over_drawn_circuit_shapes(pkg, ctx, oracle):
+    """`hypothesis` draws the circuit's shape -- rows, wires, routed wires (down to one chunk: no partial products),
+    operations per ArithmeticGate, chunk size, challenges, blowup -- and whether the witness satisfies it; quotient values,
+    chunks and cap must equal the oracle's for every draw."""
+    from hypothesis import HealthCheck, given, settings, strategies as st
+
+    @settings(max_examples=30, deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
+    @given(degree_bits=st.integers(2, 8), factor=st.integers(5, 8), num_ops=st.integers(1, 6), extra_routed=st.integers(0, 11),
+           extra_wires=st.integers(0, 8), num_challenges=st.integers(1, 4), extra_rate=st.integers(0, 1), satisfying=st.booleans(),
+           seed=st.integers(0, 2**20))
+    def run(degree_bits, factor, num_ops, extra_routed, extra_wires, num_challenges, extra_rate, satisfying, seed):
+        routed = max(4, 4 * num_ops) + extra_routed
+        rate_bits = (factor - 1).bit_length() + extra_rate
+        sc = pkg.synthetic_circuit(degree_bits, seed=seed, num_wires=routed + extra_wires, num_routed_wires=routed, num_ops=num_ops,
+                                   quotient_degree_factor=factor, rate_bits=rate_bits, num_challenges=num_challenges)
+        c = sc.circuit
+        if not satisfying:
+            sc.wires = splitmix_field(seed + 1, sc.wires.shape)
+        betas, gammas, alphas = _challenges(seed, num_challenges)
+        ob = _oracle_commitments(oracle, sc, betas, gammas)
+        gb = _device_commitments(pkg, ctx, sc, betas, gammas)
+        try:
+            want = oracle.quotient_values(c.as_dict(), ob[0], ob[1], ob[2], sc.public_inputs_hash, betas, gammas, alphas)
+            got = pkg.quotient_values(ctx, c, gb[0], gb[1], gb[2], sc.public_inputs_hash, betas, gammas, alphas)
+            assert got.shape == want.shape and (got == want).all()
+            if satisfying or factor == 8:
+                qb = pkg.compute_quotient_polys(ctx, c, gb[0], gb[1], gb[2], sc.public_inputs_hash, betas, gammas, alphas, 1)
+                chunks = oracle.quotient_chunks(want, degree_bits, factor)
+                assert (qb.polynomials == chunks).all()
+                assert (qb.cap == oracle.batch_from_values(chunks, rate_bits, 1, from_coeffs=True)["cap"]).all()
+                qb.close()
+            else:
+                with pytest.raises(pkg.BsxError, match="trim_to_len"):
+                    pkg.compute_quotient_polys(ctx, c, gb[0], gb[1], gb[2], sc.public_inputs_hash, betas, gammas, alphas, 1)
+        finally:
+            for b in gb:
+                b.close()
+
+    run()
+    used = ctx.mem_used()  # the context keeps the transform tables of every size it has seen
+    run()                  # the same draws again (derandomize): nothing new to cache, so nothing may stay behind
+    assert ctx.mem_used() == used
+
+
+@pytest.mark.gpu
 def test_quotient_rejects_mismatched_shapes(pkg, ctx):
     sc = pkg.synthetic_circuit(5, seed=2)
     c = sc.circuit
