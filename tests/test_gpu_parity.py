@@ -51,7 +51,8 @@ def test_poseidon_random_and_adversarial(ctx, oracle):
     assert (got == want).all()
 
 
-@pytest.mark.parametrize("log_n", [0, 1, 2, 5, 10, 12, 13, 14, 16])
+# 13: rows of 2^6 words (ntt_pass_lo); 14..19: rows of 2^7..2^9 words, the tile of pass LO moved by TMA (ntt_pass_lo_tma)
+@pytest.mark.parametrize("log_n", [0, 1, 2, 5, 10, 12, 13, 14, 15, 16, 17, 19])
 def test_ntt_kinds(ctx, oracle, log_n):
     n_cols = 3
     v = splitmix_field(100 + log_n, (n_cols, 1 << log_n))
@@ -67,7 +68,7 @@ def test_ntt_kinds(ctx, oracle, log_n):
     assert (got[1] == oracle.coset_fft(v[1], pow(7, 16, P))).all()
 
 
-@pytest.mark.parametrize("log_n,n_cols", [(13, 9), (16, 8), (14, 17)])
+@pytest.mark.parametrize("log_n,n_cols", [(13, 9), (16, 8), (14, 17), (18, 9)])
 def test_ntt_many_columns_full_factor_table(ctx, oracle, log_n, n_cols):
     """>= 8 columns at two-pass sizes take the cached full post-factor table path of pass HI."""
     v = splitmix_field(300 + log_n, (n_cols, 1 << log_n))
