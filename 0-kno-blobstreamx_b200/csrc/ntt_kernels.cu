@@ -17,9 +17,11 @@
 // Inside a tile the stages run in groups of up to four: a thread pulls 2^rho points out of shared
 // memory, runs rho butterfly stages on them in registers (12-instruction canonical add/sub pair,
 // 20-instruction multiply) and puts them back, so a 2^10-point sub-transform makes three trips
-// through shared memory instead of ten.  Shared memory is padded by one word in 32 so that the
-// stride-2^rho accesses of the last group stay conflict-free.  The kernels are bound by integer
-// issue (ALU carry chains + IMAD.WIDE), not by HBM: see DESIGN.md section 3.4 and profiles/.
+// through shared memory instead of ten.  Pass HI's tile is padded by one word in 32 so that the
+// stride-2^rho accesses of the last group and the bit-reversed coefficient scatter stay conflict-free;
+// pass LO's tile is one contiguous run of global memory, so it comes in and goes out as TMA bulk tensor
+// copies with the 128-byte hardware swizzle doing what the pad words do (ntt_pass_lo_tma).  The kernels
+// are bound by integer issue (ALU carry chains + IMAD.WIDE), not by HBM: DESIGN.md section 3.4, profiles/.
 #include "internal.h"
 // pipe-balanced multiply + canonicalisation for the butterflies (gl.cuh gl_mul_canon): the transforms are ALU-pipe bound
 #ifndef GL_FMA_MUL
