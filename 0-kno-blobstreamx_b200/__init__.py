@@ -48,8 +48,12 @@ from .proof import (  # noqa: F401
 )
 from .plonk import (  # noqa: F401
     GATE_ARITHMETIC,
+    GATE_ARITHMETIC_EXTENSION,
+    GATE_BASE_SUM,
     GATE_CONSTANT,
+    GATE_MUL_EXTENSION,
     GATE_NOOP,
+    GATE_POSEIDON,
     GATE_PUBLIC_INPUT,
     CircuitDescription,
     Gate,

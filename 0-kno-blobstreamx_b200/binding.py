@@ -17,7 +17,7 @@ EXPORTED_SYMBOLS = [
     "bsx_batch_tree", "bsx_batch_get_lde_values", "bsx_batch_coeffs", "bsx_batch_export", "bsx_batch_shape",
     "bsx_batch_eval_ext", "bsx_batch_import", "bsx_batch_get_lde_values_packed", "bsx_batch_lde_device", "bsx_batch_digests_device", "bsx_merkle_new", "bsx_merkle_new_colmajor_device",
     "bsx_merkle_free", "bsx_merkle_cap", "bsx_merkle_get", "bsx_merkle_prove", "bsx_merkle_digests",
-    "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_debug_salt_stream", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
+    "bsx_merkle_shape", "bsx_poseidon_permute", "bsx_poseidon_gate_witness", "bsx_debug_salt_stream", "bsx_ntt", "bsx_challenger_init", "bsx_challenger_observe",
     "bsx_challenger_get", "bsx_fri_proof_words", "bsx_fri_prove_openings", "bsx_fri_proof", "bsx_fri_final_poly", "bsx_fri_final_poly_part", "bsx_shard_final_poly_part", "bsx_field_sum",
     "bsx_fri_proof_from_final_poly",
     "bsx_merkle_reduce", "bsx_merkle_reduce_noalloc", "bsx_shard_column_range", "bsx_shard_create", "bsx_shard_free", "bsx_shard_shape",
@@ -100,6 +100,7 @@ def lib():
         "bsx_merkle_digests": (i32, [vp, vp]),
         "bsx_merkle_shape": (i32, [vp] + [C.POINTER(i32)] * 3),
         "bsx_poseidon_permute": (i32, [vp, vp, i32, sz]),
+        "bsx_poseidon_gate_witness": (i32, [vp, vp, i32, sz]),
         "bsx_debug_salt_stream": (i32, [vp, vp, i32, vp, sz]),
         "bsx_ntt": (i32, [vp, vp, i32, i32, i32, i32, u64]),
         "bsx_challenger_init": (None, [vp]),
@@ -237,6 +238,15 @@ class Context:
         flat = s.reshape(-1, 12)
         self.check(lib().bsx_poseidon_permute(self._h, _ptr(flat), BSX_HOST, flat.shape[0]))
         return s
+
+    def poseidon_gate_witness(self, rows):
+        """gates/poseidon.rs PoseidonGenerator on (n, 135) rows: inputs (wires 0..11) and swap (wire 24) are read, the delta
+        wires, the S-box input wires and the outputs are filled in.  Returns the completed copy."""
+        r = np.ascontiguousarray(_np(rows)).copy()
+        if r.ndim != 2 or r.shape[1] != 135:
+            raise BsxError("PoseidonGate rows are (n, 135)")
+        self.check(lib().bsx_poseidon_gate_witness(self._h, _ptr(r), BSX_HOST, r.shape[0]))
+        return r
 
     def salt_stream(self, key, n, raw=False):
         """n words of the ChaCha20 stream blinding salts come from, under `key` (8 x u32); raw: no rejection mod p."""

@@ -2,7 +2,8 @@
 // Replaces plonky2 plonk/prover.rs `compute_quotient_polys` and plonk/vanishing_poly.rs
 // `eval_vanishing_poly_base_batch` / `evaluate_gate_constraints_base_batch` (with plonk/plonk_common.rs
 // `ZeroPolyOnCoset`, `reduce_with_powers_multi`, plonk/vanishing_poly.rs `check_partial_products`, gates/gate.rs
-// `compute_filter`) for circuits made of NoopGate, ConstantGate, PublicInputGate and ArithmeticGate.
+// `compute_filter`) for circuits made of NoopGate, ConstantGate, PublicInputGate, ArithmeticGate, BaseSumGate<2>,
+// ArithmeticExtensionGate<2>, MulExtensionGate<2> (this kernel) and PoseidonGate (a second kernel that adds its share).
 //
 // Upstream walks the quotient domain in batches of 32 points and gathers, per point i, the rows
 // get_lde_values(i, step) of the constants+sigmas, wires and Zs commitments -- on the CPU that means the whole LDE
@@ -15,6 +16,7 @@
 // three-column accumulator per alpha with its precomputed power (reduce_with_powers_multi = sum_j alpha^j term_j),
 // products run in lazy form, and L_0(x) = Z_H(x) / (n (x - 1)) costs one Fermat inversion per point.
 #include "api_internal.h"
+#include "poseidon.cuh"
 
 #define QV_MAX_CHALLENGES 4
 #define QV_MAX_TERMS 4096  // gl_acc3 is exact for sums of up to 2^12 products
@@ -67,6 +69,16 @@ __device__ __forceinline__ void qv_fold(gl_acc3 *res, const QvParams &P, u64 ter
 #pragma unroll
     for (int a = 0; a < QV_MAX_CHALLENGES; a++)
         if (a < P.nc) gl_acc3_mac(res[a], term, __ldg(P.apow + (size_t)a * P.n_terms + idx));
+}
+
+// gates/gate.rs compute_filter(row, group_range, s, many_selector)
+__device__ __forceinline__ u64 qv_filter(const QvParams &P, const bsx_gate &g, const u64 *crow) {
+    const u64 s = __ldg(crow + (size_t)g.selector_index * P.stride);
+    u64 f = 1;
+    for (int r = g.group_start; r < g.group_end; r++)
+        if (r != g.row) f = gl_mul_lazy(f, gl_sub_c((u64)r, s));
+    if (P.many_selector) f = gl_mul_lazy(f, gl_sub_c(0xFFFFFFFFULL, s));  // UNUSED_SELECTOR
+    return f;
 }
 
 __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) {
@@ -142,11 +154,8 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
     for (int gi = 0; gi < P.n_gates; gi++) {
         const bsx_gate g = P.gates[gi];
         if (g.kind == BSX_GATE_NOOP) continue;
-        const u64 s = __ldg(crow + (size_t)g.selector_index * P.stride);
-        u64 f = 1;  // compute_filter
-        for (int r = g.group_start; r < g.group_end; r++)
-            if (r != g.row) f = gl_mul_lazy(f, gl_sub_c((u64)r, s));
-        if (P.many_selector) f = gl_mul_lazy(f, gl_sub_c(0xFFFFFFFFULL, s));  // UNUSED_SELECTOR
+        if (g.kind == BSX_GATE_POSEIDON) continue;  // quotient_poseidon_kernel
+        const u64 f = qv_filter(P, g, crow);
         if (g.kind == BSX_GATE_CONSTANT) {
             for (int t = 0; t < g.param; t++) {
                 const u64 c = gl_sub_c(__ldg(gconst + (size_t)t * P.stride), __ldg(wrow + (size_t)t * P.stride));
@@ -155,7 +164,7 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
         } else if (g.kind == BSX_GATE_PUBLIC_INPUT) {
             for (int t = 0; t < 4; t++)
                 qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(__ldg(wrow + (size_t)t * P.stride), P.pi_hash[t])), P.gate_base + t);
-        } else {  // BSX_GATE_ARITHMETIC: output - (m0 m1 const_0 + addend const_1)
+        } else if (g.kind == BSX_GATE_ARITHMETIC) {  // output - (m0 m1 const_0 + addend const_1)
             const u64 c0 = __ldg(gconst), c1 = __ldg(gconst + P.stride);
             for (int t = 0; t < g.param; t++) {
                 const u64 *wq = wrow + (size_t)(4 * t) * P.stride;
@@ -163,6 +172,34 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
                 const u64 computed = gl_mul_add_lazy(gl_mul_lazy(m0, m1), c0, gl_mul_lazy(ad, c1));
                 qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(o, gl_canon_fast(computed))), P.gate_base + t);
             }
+        } else if (g.kind == BSX_GATE_ARITHMETIC_EXTENSION || g.kind == BSX_GATE_MUL_EXTENSION) {
+            // output - ((m0 m1).scalar_mul(const_0) [+ addend.scalar_mul(const_1)]) in F_p[X] / (X^2 - 7), two constraints
+            // per operation: (a0 + a1 X)(b0 + b1 X) = a0 b0 + 7 a1 b1 + (a0 b1 + a1 b0) X
+            const bool arith = g.kind == BSX_GATE_ARITHMETIC_EXTENSION;
+            const int per = arith ? 8 : 6;
+            const u64 c0 = __ldg(gconst), c1 = arith ? __ldg(gconst + P.stride) : 0;
+            for (int t = 0; t < g.param; t++) {
+                const u64 *wq = wrow + (size_t)(per * t) * P.stride;
+                const u64 a0 = __ldg(wq), a1 = __ldg(wq + P.stride), b0 = __ldg(wq + 2 * P.stride), b1 = __ldg(wq + 3 * P.stride);
+                const u64 pr0 = gl_mul_add_lazy(a0, b0, gl_mul_lazy(gl_mul_lazy(a1, b1), 7));
+                const u64 pr1 = gl_mul_add_lazy(a0, b1, gl_mul_lazy(a1, b0));
+                u64 e0 = gl_mul_lazy(pr0, c0), e1 = gl_mul_lazy(pr1, c0);
+                if (arith) {
+                    e0 = gl_mul_add_lazy(__ldg(wq + 4 * P.stride), c1, e0);
+                    e1 = gl_mul_add_lazy(__ldg(wq + 5 * P.stride), c1, e1);
+                }
+                const u64 o0 = __ldg(wq + (size_t)(per - 2) * P.stride), o1 = __ldg(wq + (size_t)(per - 1) * P.stride);
+                qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(o0, gl_canon_fast(e0))), P.gate_base + 2 * t);
+                qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(o1, gl_canon_fast(e1))), P.gate_base + 2 * t + 1);
+            }
+        } else if (g.kind == BSX_GATE_BASE_SUM) {  // reduce_with_powers(limbs, 2) - sum; limb (limb - 1) per limb
+            u64 acc = 0;
+            for (int t = g.param; t >= 1; t--) {
+                const u64 limb = __ldg(wrow + (size_t)t * P.stride);
+                acc = gl_mul_add_lazy(acc, 2, limb);
+                qv_fold(res, P, gl_mul_lazy(f, gl_mul_lazy(limb, gl_sub_c(limb, 1))), P.gate_base + t);
+            }
+            qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(gl_canon_fast(acc), __ldg(wrow))), P.gate_base);
         }
     }
 
@@ -173,12 +210,164 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
         if (a < nc) P.out[(size_t)a * q_size + i] = gl_canon_fast(gl_mul_lazy(gl_acc3_reduce(res[a]), zh_inv));
 }
 
+// gates/poseidon.rs PoseidonGate wire map
+#define PG_OUT 12
+#define PG_SWAP 24
+#define PG_DELTA 25
+#define PG_FULL0 29
+#define PG_PARTIAL 65
+#define PG_FULL1 87
+#define PG_WIRES 135
+#define PG_CONSTRAINTS 123
+
+// The PoseidonGate's share of the vanishing polynomial: out[a][i] += filter * sum_j alpha_a^(gate_base + j) c_j / Z_H.
+// PoseidonGate::eval_unfiltered_base_one walks the permutation from the (possibly swapped) inputs; wherever the S-box
+// inputs of a round are wires, the running state is compared with them (one constraint each) and continues from the
+// wires.  One thread per point: the state never leaves registers, every round is poseidon.cuh's S-box and
+// multiplication-free MDS layer (s <- M s + RC[r + 1]); the partial rounds are taken in the naive form -- upstream's
+// factored form yields the same lane-0 values for any wires (the same affine maps regrouped).  The filter multiplies
+// the folded sum once instead of each of the 123 constraints.
+__global__ void __launch_bounds__(128) quotient_poseidon_kernel(const QvParams P, const bsx_gate g) {
+    const size_t l = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t q_size = (size_t)1 << P.log_q;
+    if (l >= q_size) return;
+    const u32 i = __brev((u32)l) >> (32 - P.log_q);
+    const u64 *w = P.wires + l;
+#define PG_W(j) __ldg(w + (size_t)(j) * P.stride)
+    gl_acc3 res[QV_MAX_CHALLENGES];
+#pragma unroll
+    for (int a = 0; a < QV_MAX_CHALLENGES; a++) res[a] = gl_acc3_zero();
+    int slot = P.gate_base;
+    u64 s[12];
+    {
+        const u64 swap = PG_W(PG_SWAP);
+        qv_fold(res, P, gl_mul_lazy(swap, gl_sub_c(swap, 1)), slot++);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const u64 lhs = PG_W(k), rhs = PG_W(k + 4), d = PG_W(PG_DELTA + k);
+            qv_fold(res, P, gl_sub_c(gl_canon_fast(gl_mul_lazy(swap, gl_sub_c(rhs, lhs))), d), slot++);
+            s[k] = gl_add_lazy_canon(gl_add_lazy_canon(lhs, d), POSEIDON_RC[k]);
+            s[k + 4] = gl_add_lazy_canon(gl_sub_c(rhs, d), POSEIDON_RC[k + 4]);
+        }
+#pragma unroll
+        for (int k = 8; k < 12; k++) s[k] = gl_add_lazy_canon(PG_W(k), POSEIDON_RC[k]);
+    }
+#pragma unroll 1
+    for (int r = 0; r < 30; r++) {
+        const bool full = r < 4 || r >= 26;
+        if (r >= 1) {  // s = state after this round's constant layer
+            const int w0 = r < 4 ? PG_FULL0 + 12 * (r - 1) : r < 26 ? PG_PARTIAL + (r - 4) : PG_FULL1 + 12 * (r - 26);
+            if (full) {
+#pragma unroll
+                for (int k = 0; k < 12; k++) {
+                    const u64 win = PG_W(w0 + k);
+                    qv_fold(res, P, gl_sub_c(gl_canon_fast(s[k]), win), slot++);
+                    s[k] = win;
+                }
+            } else {
+                const u64 win = PG_W(w0);
+                qv_fold(res, P, gl_sub_c(gl_canon_fast(s[0]), win), slot++);
+                s[0] = win;
+            }
+        }
+        if (full) {
+#pragma unroll
+            for (int k = 0; k < 12; k++) s[k] = poseidon_sbox(s[k]);
+        } else {
+            s[0] = poseidon_sbox(s[0]);
+        }
+        u32 post[36];
+        poseidon_load_post(r, post);
+        poseidon_mds_post_fft(s, post);
+    }
+#pragma unroll
+    for (int k = 0; k < 12; k++) qv_fold(res, P, gl_sub_c(gl_canon_fast(s[k]), PG_W(PG_OUT + k)), slot++);
+#undef PG_W
+    const u64 f = qv_filter(P, g, P.cs + l);
+    const u64 scale = gl_mul_lazy(f, __ldg(P.zh + (1u << P.qdb) + (i & ((1u << P.qdb) - 1))));
+#pragma unroll
+    for (int a = 0; a < QV_MAX_CHALLENGES; a++)
+        if (a < P.nc) {
+            u64 *o = P.out + (size_t)a * q_size + i;
+            *o = gl_canon_fast(gl_mul_add_lazy(gl_acc3_reduce(res[a]), scale, *o));
+        }
+}
+
+// gates/poseidon.rs PoseidonGenerator::run_once on row-major rows of 135 wires: inputs and swap are read, the deltas, the
+// S-box input wires and the outputs are written (canonical).  One thread per row.
+__global__ void __launch_bounds__(128) poseidon_gate_witness_kernel(u64 *rows, size_t n) {
+    const size_t row = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    u64 *w = rows + row * PG_WIRES;
+    u64 s[12];
+    const u64 swap = gl_canon(w[PG_SWAP]);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const u64 lhs = gl_canon(w[k]), rhs = gl_canon(w[k + 4]);
+        const u64 d = gl_canon_fast(gl_mul_lazy(swap, gl_sub_c(rhs, lhs)));
+        w[PG_DELTA + k] = d;
+        s[k] = gl_add_lazy_canon(gl_add_lazy_canon(lhs, d), POSEIDON_RC[k]);
+        s[k + 4] = gl_add_lazy_canon(gl_sub_c(rhs, d), POSEIDON_RC[k + 4]);
+    }
+#pragma unroll
+    for (int k = 8; k < 12; k++) s[k] = gl_add_lazy_canon(gl_canon(w[k]), POSEIDON_RC[k]);
+#pragma unroll 1
+    for (int r = 0; r < 30; r++) {
+        const bool full = r < 4 || r >= 26;
+        if (r >= 1) {
+            const int w0 = r < 4 ? PG_FULL0 + 12 * (r - 1) : r < 26 ? PG_PARTIAL + (r - 4) : PG_FULL1 + 12 * (r - 26);
+            if (full) {
+#pragma unroll
+                for (int k = 0; k < 12; k++) w[w0 + k] = s[k] = gl_canon(s[k]);
+            } else {
+                w[w0] = s[0] = gl_canon(s[0]);
+            }
+        }
+        if (full) {
+#pragma unroll
+            for (int k = 0; k < 12; k++) s[k] = poseidon_sbox(s[k]);
+        } else {
+            s[0] = poseidon_sbox(s[0]);
+        }
+        u32 post[36];
+        poseidon_load_post(r, post);
+        poseidon_mds_post_fft(s, post);
+    }
+#pragma unroll
+    for (int k = 0; k < 12; k++) w[PG_OUT + k] = gl_canon(s[k]);
+}
+
+extern "C" int32_t bsx_poseidon_gate_witness(bsx_ctx *ctx, uint64_t *rows, int32_t mem, size_t n) {
+    if (!ctx || (!rows && n)) return BSX_ERR_INVALID_ARG;
+    BsxScope scope(ctx);
+    if (n == 0) return BSX_OK;
+    CU(ctx, cudaSetDevice(ctx->device));
+    u64 *d = (u64 *)rows;
+    if (mem != BSX_DEVICE) {
+        TRY(bsx_alloc(ctx, &d, n * PG_WIRES));
+        TRY(bsx_copy_in(ctx, d, (const u64 *)rows, n * PG_WIRES, mem));
+    }
+    BSX_COUNT_LAUNCH();
+    poseidon_gate_witness_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(d, n);
+    CU(ctx, cudaGetLastError());
+    if (mem != BSX_DEVICE) {
+        TRY(bsx_copy_out(ctx, (u64 *)rows, d, n * PG_WIRES, mem));
+        bsx_free(ctx, d);
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->stream));
+    return BSX_OK;
+}
+
 static int gate_constraints(const bsx_gate &g) {
     switch (g.kind) {
         case BSX_GATE_NOOP: return 0;
         case BSX_GATE_CONSTANT: return g.param;
         case BSX_GATE_PUBLIC_INPUT: return 4;
         case BSX_GATE_ARITHMETIC: return g.param;
+        case BSX_GATE_POSEIDON: return PG_CONSTRAINTS;
+        case BSX_GATE_ARITHMETIC_EXTENSION: return g.param < 0 ? -1 : 2 * g.param;
+        case BSX_GATE_MUL_EXTENSION: return g.param < 0 ? -1 : 2 * g.param;
+        case BSX_GATE_BASE_SUM: return g.param < 1 ? -1 : 1 + g.param;
         default: return -1;
     }
 }
@@ -225,6 +414,10 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
         if (ok && G.kind == BSX_GATE_CONSTANT) ok = G.param <= n_gate_consts && G.param <= c->num_wires;
         if (ok && G.kind == BSX_GATE_PUBLIC_INPUT) ok = c->num_wires >= 4;
         if (ok && G.kind == BSX_GATE_ARITHMETIC) ok = 4 * G.param <= c->num_wires && n_gate_consts >= 2;
+        if (ok && G.kind == BSX_GATE_POSEIDON) ok = c->num_wires >= PG_WIRES;
+        if (ok && G.kind == BSX_GATE_ARITHMETIC_EXTENSION) ok = 8 * G.param <= c->num_wires && n_gate_consts >= 2;
+        if (ok && G.kind == BSX_GATE_MUL_EXTENSION) ok = 6 * G.param <= c->num_wires && n_gate_consts >= 1;
+        if (ok && G.kind == BSX_GATE_BASE_SUM) ok = G.param <= 63 && 1 + G.param <= c->num_wires;
         if (!ok) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "gate %d (kind %d, param %d) does not fit the circuit", g, G.kind, G.param);
     }
     QvParams P;
@@ -294,6 +487,12 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
     BSX_COUNT_LAUNCH();
     quotient_values_kernel<<<(unsigned)((q_size + 255) / 256), 256, 0, ctx->stream>>>(P);
     CU(ctx, cudaGetLastError());
+    for (int g = 0; g < c->n_gates; g++)
+        if (c->gates[g].kind == BSX_GATE_POSEIDON) {
+            BSX_COUNT_LAUNCH();
+            quotient_poseidon_kernel<<<(unsigned)((q_size + 127) / 128), 128, 0, ctx->stream>>>(P, c->gates[g]);
+            CU(ctx, cudaGetLastError());
+        }
     bsx_free(ctx, tab);
     bsx_free(ctx, (u64 *)gates_dev);
     return BSX_OK;

@@ -1,6 +1,6 @@
 """Host mirror of the prover steps around the commitments (plonky2 plonk/prover.rs): the circuit description that
 `compute_quotient_polys` reads from `CommonCircuitData`, and the device quotient evaluation behind
-bsx_quotient_values / bsx_compute_quotient_polys.  Also a synthetic circuit of the four built-in gates with a
+bsx_quotient_values / bsx_compute_quotient_polys.  Also a synthetic circuit of the built-in gates with a
 satisfying witness (the plonky2x circuits of BlobstreamX are not in the reference mount), used by tests and bench."""
 import ctypes as C
 from dataclasses import dataclass, field
@@ -12,6 +12,10 @@ from .binding import BsxError, PolynomialBatch, Timing, lib, _np, _ptr
 
 P = 0xFFFFFFFF00000001
 GATE_NOOP, GATE_CONSTANT, GATE_PUBLIC_INPUT, GATE_ARITHMETIC = 0, 1, 2, 3
+# gates/poseidon.rs PoseidonGate (135 wires, 123 constraints), gates/arithmetic_extension.rs ArithmeticExtensionGate<2>,
+# gates/multiplication_extension.rs MulExtensionGate<2> (param = num_ops), gates/base_sum.rs BaseSumGate<2> (param = num_limbs)
+GATE_POSEIDON, GATE_ARITHMETIC_EXTENSION, GATE_MUL_EXTENSION, GATE_BASE_SUM = 4, 5, 6, 7
+POSEIDON_GATE_WIRES, POSEIDON_GATE_CONSTRAINTS = 135, 123
 
 
 class _Gate(C.Structure):
@@ -37,7 +41,9 @@ class Gate:
     group_end: int = 1
 
     def num_constraints(self):
-        return {GATE_NOOP: 0, GATE_CONSTANT: self.param, GATE_PUBLIC_INPUT: 4, GATE_ARITHMETIC: self.param}[self.kind]
+        return {GATE_NOOP: 0, GATE_CONSTANT: self.param, GATE_PUBLIC_INPUT: 4, GATE_ARITHMETIC: self.param,
+                GATE_POSEIDON: POSEIDON_GATE_CONSTRAINTS, GATE_ARITHMETIC_EXTENSION: 2 * self.param,
+                GATE_MUL_EXTENSION: 2 * self.param, GATE_BASE_SUM: 1 + self.param}[self.kind]
 
 
 @dataclass
@@ -161,28 +167,74 @@ class SyntheticCircuit:
     public_inputs_hash: np.ndarray
 
 
+UNUSED_SELECTOR = 0xFFFFFFFF  # gates/selectors.rs: what a selector column holds on rows of another group
+
+
+def _ext_mul(a, b):
+    """(a0 + a1 X)(b0 + b1 X) in F_p[X] / (X^2 - 7) on python ints"""
+    return (a[0] * b[0] + 7 * a[1] * b[1]) % P, (a[0] * b[1] + a[1] * b[0]) % P
+
+
 def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_routed_wires=80, num_ops=20,
-                      quotient_degree_factor=8, rate_bits=3, num_challenges=2, public_inputs_hash=None):
-    """A circuit of NoopGate / ConstantGate / PublicInputGate / ArithmeticGate rows (one selector group) with random
-    constants, `n_copies` copy constraints between free arithmetic inputs, and a witness that satisfies all of it."""
+                      quotient_degree_factor=8, rate_bits=3, num_challenges=2, public_inputs_hash=None, gate_set="basic",
+                      poseidon_fill=None, max_poseidon_rows=1 << 12):
+    """A circuit with random constants, `n_copies` copy constraints between free arithmetic inputs, and a witness that
+    satisfies all of it.  gate_set "basic": NoopGate / ConstantGate / PublicInputGate / ArithmeticGate rows in one selector
+    group.  "all" (degree_bits >= 5, quotient_degree_factor 8): two selector groups as gates/selectors.rs would form them
+    for max degree 9 -- [Noop, Constant, PublicInput, BaseSum<2>, Arithmetic, ArithmeticExtension] and [MulExtension,
+    Poseidon] -- with rows of every kind; `poseidon_fill(rows)` completes (k, 135) PoseidonGate rows whose inputs and
+    swap wire are set (Context.poseidon_gate_witness on the device; the Poseidon gate is left out when it is None or
+    the circuit has fewer than 135 wires)."""
     n = 1 << degree_bits
     rng = np.random.default_rng(seed)
-    gates = [Gate(GATE_NOOP, 0, 0, 0, 0, 4), Gate(GATE_CONSTANT, 2, 1, 0, 0, 4), Gate(GATE_PUBLIC_INPUT, 0, 2, 0, 0, 4),
-             Gate(GATE_ARITHMETIC, num_ops, 3, 0, 0, 4)]
-    circ = CircuitDescription(degree_bits, gates, rate_bits=rate_bits, quotient_degree_factor=quotient_degree_factor,
-                              num_challenges=num_challenges, num_wires=num_wires, num_routed_wires=num_routed_wires)
-    sel = np.full(n, 3, dtype=np.uint64)          # arithmetic rows ...
-    sel[0] = 2                                    # ... one public-input row,
-    n_const = max(1, n // 16) if n > 2 else 0
-    sel[1:1 + n_const] = 1                        # some constant rows,
-    if n > 4:
-        sel[n - max(1, n // 32):] = 0             # and padding rows at the end
     rand = lambda shape: rng.integers(0, P, size=shape, dtype=np.uint64)
-    constants = np.stack([sel, rand(n), rand(n)])
+    if gate_set == "all":
+        if degree_bits < 5 or quotient_degree_factor != 8:
+            raise ValueError('gate_set "all" wants degree_bits >= 5 and quotient_degree_factor 8')
+        n_ext, n_mulx, n_limbs = num_routed_wires // 8, num_routed_wires // 6, min(32, num_wires - 1)
+        with_poseidon = poseidon_fill is not None and num_wires >= POSEIDON_GATE_WIRES
+        gates = [Gate(GATE_NOOP, 0, 0, 0, 0, 6), Gate(GATE_CONSTANT, 2, 1, 0, 0, 6), Gate(GATE_PUBLIC_INPUT, 0, 2, 0, 0, 6),
+                 Gate(GATE_BASE_SUM, n_limbs, 3, 0, 0, 6), Gate(GATE_ARITHMETIC, num_ops, 4, 0, 0, 6),
+                 Gate(GATE_ARITHMETIC_EXTENSION, n_ext, 5, 0, 0, 6), Gate(GATE_MUL_EXTENSION, n_mulx, 6, 1, 6, 8)]
+        if with_poseidon:
+            gates.append(Gate(GATE_POSEIDON, 0, 7, 1, 6, 8))
+        else:
+            gates[-1] = Gate(GATE_MUL_EXTENSION, n_mulx, 6, 1, 6, 7)
+        circ = CircuitDescription(degree_bits, gates, rate_bits=rate_bits, quotient_degree_factor=quotient_degree_factor,
+                                  num_challenges=num_challenges, num_wires=num_wires, num_routed_wires=num_routed_wires,
+                                  num_constants=4, num_selectors=2)
+        kind_row = np.full(n, 4, dtype=np.int64)      # arithmetic rows ...
+        kind_row[0] = 2                               # ... one public-input row,
+        cuts = np.cumsum([1, max(1, n // 16), max(1, n // 16), max(1, n // 8), max(1, n // 8),
+                          min(max(1, n // 8), max_poseidon_rows) if with_poseidon else 0])
+        for k, (a, b) in zip((1, 3, 5, 6, 7), zip(cuts[:-1], cuts[1:])):
+            kind_row[a:b] = k                         # constant, base-sum, arithmetic-extension, mul-extension, Poseidon rows
+        kind_row[n - max(1, n // 32):] = 0            # and padding rows at the end
+        group = np.array([g.selector_index for g in gates])[kind_row]
+        sel0 = np.where(group == 0, kind_row, UNUSED_SELECTOR).astype(np.uint64)
+        sel1 = np.where(group == 1, kind_row, UNUSED_SELECTOR).astype(np.uint64)
+        constants = np.stack([sel0, sel1, rand(n), rand(n)])
+        c0, c1 = constants[2], constants[3]
+        arith_kind, const_kind = 4, 1
+    else:
+        gates = [Gate(GATE_NOOP, 0, 0, 0, 0, 4), Gate(GATE_CONSTANT, 2, 1, 0, 0, 4), Gate(GATE_PUBLIC_INPUT, 0, 2, 0, 0, 4),
+                 Gate(GATE_ARITHMETIC, num_ops, 3, 0, 0, 4)]
+        circ = CircuitDescription(degree_bits, gates, rate_bits=rate_bits, quotient_degree_factor=quotient_degree_factor,
+                                  num_challenges=num_challenges, num_wires=num_wires, num_routed_wires=num_routed_wires)
+        kind_row = np.full(n, 3, dtype=np.int64)      # arithmetic rows ...
+        kind_row[0] = 2                               # ... one public-input row,
+        n_const = max(1, n // 16) if n > 2 else 0
+        kind_row[1:1 + n_const] = 1                   # some constant rows,
+        if n > 4:
+            kind_row[n - max(1, n // 32):] = 0        # and padding rows at the end
+        constants = np.stack([kind_row.astype(np.uint64), rand(n), rand(n)])
+        c0, c1 = constants[1], constants[2]
+        arith_kind, const_kind = 3, 1
+    sel = kind_row
     wires = rand((num_wires, n))
     pih = rand(4) if public_inputs_hash is None else np.array(public_inputs_hash, dtype=np.uint64).reshape(4).copy()
     # copy constraints: disjoint pairs of free cells (multiplicands / addends of arithmetic rows)
-    arith_rows = np.nonzero(sel == 3)[0]
+    arith_rows = np.nonzero(sel == arith_kind)[0]
     free = [(4 * i + t, r) for r in arith_rows[: 4096] for i in range(num_ops) for t in range(3)]
     if n_copies is None:
         n_copies = min(len(free) // 2, 4 * n)
@@ -195,13 +247,34 @@ def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_rou
         perm[ja, ra], perm[jb, rb] = ident[jb, rb], ident[ja, ra]
     # satisfy the gates
     w = pow(1753635133440165772, 1 << (32 - degree_bits), P)  # plonky2 primitive_root_of_unity(degree_bits)
-    c_rows = np.nonzero(sel == 1)[0]
-    wires[0, c_rows], wires[1, c_rows] = constants[1, c_rows], constants[2, c_rows]
+    c_rows = np.nonzero(sel == const_kind)[0]
+    wires[0, c_rows], wires[1, c_rows] = c0[c_rows], c1[c_rows]
     wires[0:4, 0] = pih
     for i in range(num_ops):
-        m = _mulmod(_mulmod(wires[4 * i, arith_rows], wires[4 * i + 1, arith_rows]), constants[1, arith_rows])
-        a = _mulmod(wires[4 * i + 2, arith_rows], constants[2, arith_rows])
+        m = _mulmod(_mulmod(wires[4 * i, arith_rows], wires[4 * i + 1, arith_rows]), c0[arith_rows])
+        a = _mulmod(wires[4 * i + 2, arith_rows], c1[arith_rows])
         wires[4 * i + 3, arith_rows] = np.array([(int(x) + int(y)) % P for x, y in zip(m, a)], dtype=np.uint64)
+    if gate_set == "all":
+        for r in np.nonzero(sel == 3)[0]:           # BaseSumGate<2>: wire 0 = sum of 2^i * limb_i, limbs are bits
+            bits = rng.integers(0, 2, size=n_limbs, dtype=np.uint64)
+            wires[1:1 + n_limbs, r] = bits
+            wires[0, r] = sum(int(b) << i for i, b in enumerate(bits)) % P
+        for kind, per, n_ops in ((5, 8, n_ext), (6, 6, n_mulx)):  # output = m0 m1 const_0 (+ addend const_1) in F_p^2
+            for r in np.nonzero(sel == kind)[0]:
+                k0, k1 = int(c0[r]), int(c1[r])
+                for i in range(n_ops):
+                    q = [int(x) for x in wires[per * i:per * i + per, r]]
+                    pr = _ext_mul(q[0:2], q[2:4])
+                    out = [pr[d] * k0 % P for d in range(2)]
+                    if kind == 5:
+                        out = [(out[d] + q[4 + d] * k1) % P for d in range(2)]
+                    wires[per * i + per - 2:per * i + per, r] = out
+        p_rows = np.nonzero(sel == 7)[0]
+        if p_rows.size:
+            rows = np.ascontiguousarray(wires[:POSEIDON_GATE_WIRES, p_rows].T)
+            rows[:, 24] = rng.integers(0, 2, size=p_rows.size, dtype=np.uint64)  # swap
+            rows = _np(poseidon_fill(rows)).reshape(p_rows.size, POSEIDON_GATE_WIRES)
+            wires[:POSEIDON_GATE_WIRES, p_rows] = rows.T
     # sigma polynomials' values: cell (j', r') -> k_j' * omega^r'
     omegas = np.empty(n, dtype=object)
     acc = 1

@@ -423,6 +423,12 @@ int32_t bsx_partial_products_and_zs(bsx_ctx *ctx, const uint64_t *wires, const u
 #define BSX_GATE_CONSTANT 1     /* param = num_consts: constants[i] - wires[i] */
 #define BSX_GATE_PUBLIC_INPUT 2 /* wires[i] - public_inputs_hash[i], i < 4 */
 #define BSX_GATE_ARITHMETIC 3   /* param = num_ops: wires[4i+3] - (wires[4i] wires[4i+1] const_0 + wires[4i+2] const_1) */
+#define BSX_GATE_POSEIDON 4     /* gates/poseidon.rs PoseidonGate: 135 wires, 123 constraints of degree 7 (swap binary, 4 deltas,
+                                   S-box input wires of rounds 1..3 / the 22 partial rounds / the last 4 rounds, 12 outputs) */
+#define BSX_GATE_ARITHMETIC_EXTENSION 5 /* gates/arithmetic_extension.rs, D = 2, param = num_ops: wires 8i .. 8i+7 =
+                                   multiplicand_0, multiplicand_1, addend, output in F_p[X]/(X^2 - 7); 2 constraints each */
+#define BSX_GATE_MUL_EXTENSION 6 /* gates/multiplication_extension.rs, D = 2, param = num_ops: wires 6i .. 6i+5 */
+#define BSX_GATE_BASE_SUM 7     /* gates/base_sum.rs BaseSumGate<2>, param = num_limbs (<= 63): wire 0 = sum, wires 1.. = limbs */
 typedef struct bsx_gate {
     int32_t kind, param, row, selector_index, group_start, group_end;
 } bsx_gate;
@@ -455,6 +461,11 @@ int32_t bsx_compute_quotient_polys(bsx_ctx *ctx, const bsx_circuit *circuit, bsx
 /* ---- test hooks -----------------------------------------------------------------------------
  * Poseidon::poseidon on n states (n x 12 words, in place). */
 int32_t bsx_poseidon_permute(bsx_ctx *ctx, uint64_t *states, int32_t mem, size_t n);
+/* gates/poseidon.rs PoseidonGenerator::run_once on n row-major rows of 135 wires (in place): the inputs (wires 0..11) and
+ * the swap wire (24, 0 or 1) are read; the delta wires, every S-box input wire and the outputs are written.  Witness
+ * generation itself is outside the path this library replaces; this fills the PoseidonGate rows of synthetic circuits
+ * and checks bsx_quotient_values' constraints from the other side. */
+int32_t bsx_poseidon_gate_witness(bsx_ctx *ctx, uint64_t *rows, int32_t mem, size_t n);
 /* n words of the ChaCha20 (RFC 8439 block function, 64-bit block counter) key stream that the blinding salts are
  * drawn from under `key`; raw != 0 returns the stream itself (eight little-endian u64 per block, block t at words
  * 8t .. 8t+7), raw == 0 the salt words (candidates >= p rejected and redrawn).  In a commit the key is 256 bits from

@@ -388,6 +388,15 @@ def _circuit(circuit):
     return c, [gates, k_is]
 
 
+def poseidon_gate_fill(rows):
+    """gates/poseidon.rs PoseidonGenerator on an (n, 135) array: inputs (wires 0..11) and swap (wire 24) are read, the
+    deltas, S-box input wires and outputs are written in place."""
+    assert rows.dtype == np.uint64 and rows.ndim == 2 and rows.shape[1] == 135 and rows.flags.c_contiguous
+    lib().orc_poseidon_gate_fill.restype = None
+    lib().orc_poseidon_gate_fill(_ptr(rows), C.c_size_t(rows.shape[0]))
+    return rows
+
+
 def quotient_values(circuit, constants_sigmas, wires, zs_partial_products, public_inputs_hash, betas, gammas, alphas,
                     cap_height=0):
     """compute_quotient_polys before its `coset_ifft`: (num_challenges, 2^(degree_bits + q)) values on the coset.

@@ -201,6 +201,8 @@ static inline void mds_layer(uint64_t s[12]) {
     ah[0] += MDS_DIAG0 * hi[0];
     for (int r = 0; r < 12; r++) s[r] = reduce128((u128)al[r] + ((u128)ah[r] << 32));
 }
+uint64_t orc_poseidon_sbox(uint64_t x) { return sbox(canon(x)); }
+void orc_poseidon_mds(uint64_t s[12]) { mds_layer(s); }
 void orc_poseidon(uint64_t s[12]) {
     for (int i = 0; i < 12; i++) s[i] = canon(s[i]);
     for (int r = 0; r < 30; r++) {

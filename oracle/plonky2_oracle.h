@@ -54,6 +54,9 @@ void orc_hash_no_pad(const uint64_t *in, size_t len, uint64_t out[4]);
 void orc_hash_or_noop(const uint64_t *in, size_t len, uint64_t out[4]);
 void orc_two_to_one(const uint64_t l[4], const uint64_t r[4], uint64_t out[4]);
 const uint64_t *orc_round_constants(void);
+/* the two layers of one round, for the PoseidonGate constraints (canonical in, canonical out) */
+uint64_t orc_poseidon_sbox(uint64_t x);
+void orc_poseidon_mds(uint64_t state[12]);
 
 /* ---- Merkle tree (hash/merkle_tree.rs, merkle_proofs.rs) ----
  * leaves: row-major n_leaves x leaf_len.  digests (level order, leaf level first):
@@ -148,6 +151,10 @@ int orc_partial_products_and_z(const uint64_t *wires, const uint64_t *sigmas, in
 #define ORC_GATE_CONSTANT 1     /* gates/constant.rs ConstantGate { num_consts = param } */
 #define ORC_GATE_PUBLIC_INPUT 2 /* gates/public_input.rs PublicInputGate */
 #define ORC_GATE_ARITHMETIC 3   /* gates/arithmetic_base.rs ArithmeticGate { num_ops = param } */
+#define ORC_GATE_POSEIDON 4     /* gates/poseidon.rs PoseidonGate: 135 wires, 123 constraints of degree 7 */
+#define ORC_GATE_ARITHMETIC_EXTENSION 5 /* gates/arithmetic_extension.rs ArithmeticExtensionGate<2> { num_ops = param } */
+#define ORC_GATE_MUL_EXTENSION 6        /* gates/multiplication_extension.rs MulExtensionGate<2> { num_ops = param } */
+#define ORC_GATE_BASE_SUM 7             /* gates/base_sum.rs BaseSumGate<2> { num_limbs = param } */
 typedef struct orc_gate { /* one entry of common_data.gates with its share of common_data.selectors_info */
     int32_t kind, param;
     int32_t row;                    /* index in common_data.gates: the selector value that switches it on */
@@ -164,6 +171,8 @@ typedef struct orc_circuit { /* the fields of CommonCircuitData / CircuitConfig 
     const uint64_t *k_is;
 } orc_circuit;
 int orc_gate_num_constraints(const orc_gate *g);
+/* gates/poseidon.rs PoseidonGenerator: fills deltas, S-box input wires and outputs of n row-major rows of 135 wires */
+void orc_poseidon_gate_fill(uint64_t *rows, size_t n);
 /* the quotient values on the coset before `coset_ifft`: out[a][i], a < num_challenges, i < 2^(degree_bits + q) */
 int orc_quotient_values(const orc_circuit *c, const orc_batch_view *constants_sigmas, const orc_batch_view *wires_b,
                         const orc_batch_view *zs_b, const uint64_t public_inputs_hash[4], const uint64_t *betas,

@@ -1,7 +1,9 @@
 /* plonky2_plonk_oracle.c -- CPU restatement of the prover steps either side of the commitments:
  *   plonk/prover.rs `compute_quotient_polys` with plonk/vanishing_poly.rs `eval_vanishing_poly_base_batch`
  *   (the vanishing polynomial on the quotient coset) for circuits built from NoopGate, ConstantGate,
- *   PublicInputGate and ArithmeticGate (gates/{noop,constant,public_input,arithmetic_base}.rs), and
+ *   PublicInputGate, ArithmeticGate, PoseidonGate, ArithmeticExtensionGate, MulExtensionGate and BaseSumGate<2>
+ *   (gates/{noop,constant,public_input,arithmetic_base,poseidon,arithmetic_extension,multiplication_extension,
+ *   base_sum}.rs), and
  *   util/serialization/mod.rs `write_proof_with_public_inputs` (`ProofWithPublicInputs::to_bytes`).
  * TEST INFRASTRUCTURE ONLY; "parity unpinned" against the real prover -- see plonky2_oracle.h. */
 #include "plonky2_oracle.h"
@@ -58,7 +60,80 @@ static uint64_t compute_filter(int row, int g0, int g1, uint64_t s, int many_sel
     return f;
 }
 
-/* eval_unfiltered of the four gates; out[j] for j < num_constraints(gate); returns the constraint count.
+/* gates/poseidon.rs PoseidonGate::eval_unfiltered_base_one.  Wires: input i, output 12 + i, swap 24, delta 25 + i (i < 4),
+ * S-box inputs of the first full rounds 29 + 12 (r - 1) + i (r = 1..3), of the partial rounds 65 + r, of the second full
+ * rounds 87 + 12 r + i.  Constraints in upstream's order: swap binary, the four deltas, then for every round whose
+ * S-box inputs are wires `state - wire` (the state continues from the wire), and the outputs: 1 + 4 + 36 + 22 + 48 + 12.
+ * The partial rounds are written in the naive form (constants, S-box on lane 0, MDS); upstream's factored form
+ * (mds_partial_layer_init / mds_partial_layer_fast) gives the same lane-0 values for ANY wire values, satisfying or not,
+ * because it is the same affine maps regrouped (checked numerically against tools/gen_poseidon_constants.py's
+ * factorisation in tests/test_gates.py). */
+#define PG_SWAP 24
+#define PG_DELTA 25
+#define PG_FULL0 29
+#define PG_PARTIAL 65
+#define PG_FULL1 87
+static int poseidon_gate_eval(const uint64_t *w, uint64_t *out) {
+    const uint64_t *rc = orc_round_constants();
+    int t = 0;
+    const uint64_t swap = w[PG_SWAP];
+    out[t++] = orc_mul(swap, orc_sub(swap, 1));
+    for (int i = 0; i < 4; i++) out[t++] = orc_sub(orc_mul(swap, orc_sub(w[i + 4], w[i])), w[PG_DELTA + i]);
+    uint64_t s[12];
+    for (int i = 0; i < 4; i++) {
+        s[i] = orc_add(w[i], w[PG_DELTA + i]);
+        s[i + 4] = orc_sub(w[i + 4], w[PG_DELTA + i]);
+    }
+    for (int i = 8; i < 12; i++) s[i] = w[i];
+    for (int r = 0; r < 30; r++) {
+        for (int i = 0; i < 12; i++) s[i] = orc_add(s[i], rc[12 * r + i]);
+        const int full = r < 4 || r >= 26;
+        if (r >= 1) {
+            const uint64_t *win = r < 4 ? w + PG_FULL0 + 12 * (r - 1) : r < 26 ? w + PG_PARTIAL + (r - 4) : w + PG_FULL1 + 12 * (r - 26);
+            for (int i = 0; i < (full ? 12 : 1); i++) {
+                out[t++] = orc_sub(s[i], win[i]);
+                s[i] = win[i];
+            }
+        }
+        for (int i = 0; i < (full ? 12 : 1); i++) s[i] = orc_poseidon_sbox(s[i]);
+        orc_poseidon_mds(s);
+    }
+    for (int i = 0; i < 12; i++) out[t++] = orc_sub(s[i], w[12 + i]);
+    return t;
+}
+
+/* gates/poseidon.rs PoseidonGenerator::run_once for n rows of 135 wires (row-major): inputs 0..11 and swap (0 or 1) are
+ * read, the deltas, every S-box input wire and the outputs are written. */
+void orc_poseidon_gate_fill(uint64_t *rows, size_t n) {
+    const uint64_t *rc = orc_round_constants();
+    for (size_t row = 0; row < n; row++) {
+        uint64_t *w = rows + 135 * row, s[12];
+        const uint64_t swap = w[PG_SWAP] % P;
+        for (int i = 0; i < 4; i++) {
+            const uint64_t d = orc_mul(swap, orc_sub(w[i + 4] % P, w[i] % P));
+            w[PG_DELTA + i] = d;
+            s[i] = orc_add(w[i] % P, d);
+            s[i + 4] = orc_sub(w[i + 4] % P, d);
+        }
+        for (int i = 8; i < 12; i++) s[i] = w[i] % P;
+        for (int r = 0; r < 30; r++) {
+            for (int i = 0; i < 12; i++) s[i] = orc_add(s[i], rc[12 * r + i]);
+            const int full = r < 4 || r >= 26;
+            if (r >= 1) {
+                uint64_t *win = r < 4 ? w + PG_FULL0 + 12 * (r - 1) : r < 26 ? w + PG_PARTIAL + (r - 4) : w + PG_FULL1 + 12 * (r - 26);
+                for (int i = 0; i < (full ? 12 : 1); i++) win[i] = s[i];
+            }
+            for (int i = 0; i < (full ? 12 : 1); i++) s[i] = orc_poseidon_sbox(s[i]);
+            orc_poseidon_mds(s);
+        }
+        for (int i = 0; i < 12; i++) w[12 + i] = s[i];
+    }
+}
+
+/* F_p[X] / (X^2 - 7) on base-field pairs: vars.get_local_ext(range) in the base-field evaluation */
+static void x2_mul(const uint64_t a[2], const uint64_t b[2], uint64_t o[2]) { orc_ext_mul(a, b, o); }
+
+/* eval_unfiltered of the gates; out[j] for j < num_constraints(gate); returns the constraint count.
  * consts = local_constants with the selector prefix removed (vars.remove_prefix(num_selectors)). */
 static int gate_eval_unfiltered(const orc_gate *g, const uint64_t *consts, const uint64_t *wires,
                                 const uint64_t pi_hash[4], uint64_t *out) {
@@ -78,6 +153,32 @@ static int gate_eval_unfiltered(const orc_gate *g, const uint64_t *consts, const
                 out[i] = orc_sub(o, computed);
             }
             return g->param;
+        case ORC_GATE_POSEIDON:
+            return poseidon_gate_eval(wires, out);
+        case ORC_GATE_ARITHMETIC_EXTENSION: /* output - ((m0 * m1).scalar_mul(const_0) + addend.scalar_mul(const_1)), D = 2 */
+            for (int i = 0; i < g->param; i++) {
+                const uint64_t *q = wires + 8 * i;
+                uint64_t pr[2];
+                x2_mul(q, q + 2, pr);
+                for (int d = 0; d < 2; d++)
+                    out[2 * i + d] = orc_sub(q[6 + d], orc_add(orc_mul(pr[d], consts[0]), orc_mul(q[4 + d], consts[1])));
+            }
+            return 2 * g->param;
+        case ORC_GATE_MUL_EXTENSION: /* output - (m0 * m1).scalar_mul(const_0) */
+            for (int i = 0; i < g->param; i++) {
+                const uint64_t *q = wires + 6 * i;
+                uint64_t pr[2];
+                x2_mul(q, q + 2, pr);
+                for (int d = 0; d < 2; d++) out[2 * i + d] = orc_sub(q[4 + d], orc_mul(pr[d], consts[0]));
+            }
+            return 2 * g->param;
+        case ORC_GATE_BASE_SUM: { /* reduce_with_powers(limbs, 2) - sum, then limb (limb - 1) per limb; sum = wire 0 */
+            uint64_t acc = 0;
+            for (int i = g->param; i >= 1; i--) acc = orc_add(orc_mul(acc, 2), wires[i]);
+            out[0] = orc_sub(acc, wires[0]);
+            for (int i = 1; i <= g->param; i++) out[i] = orc_mul(wires[i], orc_sub(wires[i], 1));
+            return 1 + g->param;
+        }
         default:
             return -1;
     }
@@ -89,6 +190,10 @@ int orc_gate_num_constraints(const orc_gate *g) {
         case ORC_GATE_CONSTANT: return g->param;
         case ORC_GATE_PUBLIC_INPUT: return 4;
         case ORC_GATE_ARITHMETIC: return g->param;
+        case ORC_GATE_POSEIDON: return 123;
+        case ORC_GATE_ARITHMETIC_EXTENSION: return 2 * g->param;
+        case ORC_GATE_MUL_EXTENSION: return 2 * g->param;
+        case ORC_GATE_BASE_SUM: return 1 + g->param;
         default: return -1;
     }
 }
@@ -130,8 +235,9 @@ static int vanishing_at_point(const orc_circuit *c, uint64_t x, uint64_t l_0_x, 
         const orc_gate *g = &c->gates[gi];
         const uint64_t filter = compute_filter(g->row, g->group_start, g->group_end, local_constants[g->selector_index],
                                                c->num_selectors > 1);
-        int k = gate_eval_unfiltered(g, local_constants + c->num_selectors, local_wires, pi_hash, gate_out);
-        if (k < 0 || k > c->num_gate_constraints) { bad = 1; k = 0; }
+        int k = orc_gate_num_constraints(g); /* checked before the evaluation writes gate_out */
+        if (k < 0 || k > c->num_gate_constraints) { bad = 1; continue; }
+        k = gate_eval_unfiltered(g, local_constants + c->num_selectors, local_wires, pi_hash, gate_out);
         for (int j = 0; j < k; j++) cons[j] = orc_add(cons[j], orc_mul(filter, gate_out[j]));
     }
     t += c->num_gate_constraints;
@@ -220,6 +326,7 @@ int orc_vanishing_at_ext(const orc_circuit *c, const uint64_t zeta[2], const uin
             if (i != g->row) f = e2_mul(f, e2_sub(e2_of((uint64_t)i), s));
         if (c->num_selectors > 1) f = e2_mul(f, e2_sub(e2_of(0xFFFFFFFFULL), s));
         const uint64_t *gc = constants + 2 * (size_t)c->num_selectors; /* constants after the selector prefix */
+        if (orc_gate_num_constraints(g) < 0 || orc_gate_num_constraints(g) > c->num_gate_constraints) { bad = 1; continue; }
         switch (g->kind) {
             case ORC_GATE_NOOP: break;
             case ORC_GATE_CONSTANT:
@@ -235,6 +342,72 @@ int orc_vanishing_at_ext(const orc_circuit *c, const uint64_t zeta[2], const uin
                     terms[t + i] = e2_add(terms[t + i], e2_mul(f, e2_sub(EXT_AT(wires, 4 * i + 3), computed)));
                 }
                 break;
+            case ORC_GATE_POSEIDON: { /* PoseidonGate::eval_unfiltered: the same schedule over F_p^2 (constants and MDS are base-field) */
+                const uint64_t *rc = orc_round_constants();
+                int k = 0;
+#define PG_EMIT(v) do { terms[t + k] = e2_add(terms[t + k], e2_mul(f, (v))); k++; } while (0)
+                const e2 swap = EXT_AT(wires, PG_SWAP);
+                PG_EMIT(e2_mul(swap, e2_sub(swap, one)));
+                for (int i = 0; i < 4; i++)
+                    PG_EMIT(e2_sub(e2_mul(swap, e2_sub(EXT_AT(wires, i + 4), EXT_AT(wires, i))), EXT_AT(wires, PG_DELTA + i)));
+                e2 st[12];
+                for (int i = 0; i < 4; i++) {
+                    st[i] = e2_add(EXT_AT(wires, i), EXT_AT(wires, PG_DELTA + i));
+                    st[i + 4] = e2_sub(EXT_AT(wires, i + 4), EXT_AT(wires, PG_DELTA + i));
+                }
+                for (int i = 8; i < 12; i++) st[i] = EXT_AT(wires, i);
+                for (int r = 0; r < 30; r++) {
+                    for (int i = 0; i < 12; i++) st[i] = e2_add(st[i], e2_of(rc[12 * r + i]));
+                    const int full = r < 4 || r >= 26;
+                    if (r >= 1) {
+                        const int w0 = r < 4 ? PG_FULL0 + 12 * (r - 1) : r < 26 ? PG_PARTIAL + (r - 4) : PG_FULL1 + 12 * (r - 26);
+                        for (int i = 0; i < (full ? 12 : 1); i++) {
+                            PG_EMIT(e2_sub(st[i], EXT_AT(wires, w0 + i)));
+                            st[i] = EXT_AT(wires, w0 + i);
+                        }
+                    }
+                    for (int i = 0; i < (full ? 12 : 1); i++) { /* x^7 */
+                        const e2 x2 = e2_mul(st[i], st[i]), x4 = e2_mul(x2, x2), x3 = e2_mul(x2, st[i]);
+                        st[i] = e2_mul(x3, x4);
+                    }
+                    uint64_t lane[2][12]; /* the MDS matrix is over the base field: component by component */
+                    for (int i = 0; i < 12; i++) lane[0][i] = st[i].c[0], lane[1][i] = st[i].c[1];
+                    orc_poseidon_mds(lane[0]);
+                    orc_poseidon_mds(lane[1]);
+                    for (int i = 0; i < 12; i++) st[i].c[0] = lane[0][i], st[i].c[1] = lane[1][i];
+                }
+                for (int i = 0; i < 12; i++) PG_EMIT(e2_sub(st[i], EXT_AT(wires, 12 + i)));
+#undef PG_EMIT
+                break;
+            }
+            case ORC_GATE_ARITHMETIC_EXTENSION:
+            case ORC_GATE_MUL_EXTENSION: {
+                /* vars.get_local_ext_algebra: pairs of F_p^2 openings as elements of F_p^2[X] / (X^2 - 7)
+                 * (ExtensionAlgebra): (a0 + a1 X)(b0 + b1 X) = a0 b0 + 7 a1 b1 + (a0 b1 + a1 b0) X */
+                const int arith = g->kind == ORC_GATE_ARITHMETIC_EXTENSION, per = arith ? 8 : 6;
+                for (int i = 0; i < g->param; i++) {
+                    const int q = per * i;
+                    const e2 a0 = EXT_AT(wires, q), a1 = EXT_AT(wires, q + 1), b0 = EXT_AT(wires, q + 2), b1 = EXT_AT(wires, q + 3);
+                    e2 pr[2];
+                    pr[0] = e2_add(e2_mul(a0, b0), e2_scale(e2_mul(a1, b1), 7));
+                    pr[1] = e2_add(e2_mul(a0, b1), e2_mul(a1, b0));
+                    for (int d = 0; d < 2; d++) {
+                        e2 computed = e2_mul(pr[d], EXT_AT(gc, 0));
+                        if (arith) computed = e2_add(computed, e2_mul(EXT_AT(wires, q + 4 + d), EXT_AT(gc, 1)));
+                        const e2 o = EXT_AT(wires, q + (arith ? 6 : 4) + d);
+                        terms[t + 2 * i + d] = e2_add(terms[t + 2 * i + d], e2_mul(f, e2_sub(o, computed)));
+                    }
+                }
+                break;
+            }
+            case ORC_GATE_BASE_SUM: {
+                e2 acc = e2_of(0);
+                for (int i = g->param; i >= 1; i--) acc = e2_add(e2_scale(acc, 2), EXT_AT(wires, i));
+                terms[t] = e2_add(terms[t], e2_mul(f, e2_sub(acc, EXT_AT(wires, 0))));
+                for (int i = 1; i <= g->param; i++)
+                    terms[t + i] = e2_add(terms[t + i], e2_mul(f, e2_mul(EXT_AT(wires, i), e2_sub(EXT_AT(wires, i), one))));
+                break;
+            }
             default: bad = 1;
         }
     }

@@ -23,7 +23,8 @@ use crate::oracle::PolynomialBatch;
 use crate::{as_words, with_ctx, words_to_field};
 
 /// `common_data.gates` + `common_data.selectors_info` as the table the library reads; None when a gate is not one of
-/// the four built-in kinds.
+/// the kinds the library evaluates (Noop, Constant, PublicInput, Arithmetic, Poseidon, ArithmeticExtension,
+/// MulExtension, BaseSum<2>).
 pub fn gate_table<F: RichField + Extendable<D>, const D: usize>(common_data: &CommonCircuitData<F, D>) -> Option<Vec<sys::bsx_gate>> {
     let info = &common_data.selectors_info;
     common_data
@@ -40,6 +41,14 @@ pub fn gate_table<F: RichField + Extendable<D>, const D: usize>(common_data: &Co
                 (sys::BSX_GATE_PUBLIC_INPUT, 0)
             } else if id.starts_with("ArithmeticGate") {
                 (sys::BSX_GATE_ARITHMETIC, g.0.num_constraints() as i32) // one constraint per operation
+            } else if id.starts_with("PoseidonGate") && D == 2 {
+                (sys::BSX_GATE_POSEIDON, 0)
+            } else if id.starts_with("ArithmeticExtensionGate") && D == 2 {
+                (sys::BSX_GATE_ARITHMETIC_EXTENSION, (g.0.num_constraints() / D) as i32) // D constraints per operation
+            } else if id.starts_with("MulExtensionGate") && D == 2 {
+                (sys::BSX_GATE_MUL_EXTENSION, (g.0.num_constraints() / D) as i32)
+            } else if id.starts_with("BaseSumGate") && id.contains("Base: 2") {
+                (sys::BSX_GATE_BASE_SUM, (g.0.num_constraints() - 1) as i32) // 1 + num_limbs constraints
             } else {
                 return None;
             };
