@@ -223,29 +223,38 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
 // The PoseidonGate's share of the vanishing polynomial: out[a][i] += filter * sum_j alpha_a^(gate_base + j) c_j / Z_H.
 // PoseidonGate::eval_unfiltered_base_one walks the permutation from the (possibly swapped) inputs; wherever the S-box
 // inputs of a round are wires, the running state is compared with them (one constraint each) and continues from the
-// wires.  One thread per point: the state never leaves registers, every round is poseidon.cuh's S-box and
-// multiplication-free MDS layer (s <- M s + RC[r + 1]); the partial rounds are taken in the naive form -- upstream's
-// factored form yields the same lane-0 values for any wires (the same affine maps regrouped).  The filter multiplies
-// the folded sum once instead of each of the 123 constraints.
-__global__ void __launch_bounds__(128) quotient_poseidon_kernel(const QvParams P, const bsx_gate g) {
+// wires.  One thread per point, the state never leaves registers, and the schedule is poseidon_permute_lazy's
+// (poseidon.cuh): S-box, then the multiplication-free MDS layer with the next round's constants; lanes 1..11 stay in
+// limb planes through the partial rounds.  Those are taken in the naive form -- upstream's factored form
+// (mds_partial_layer_init / _fast) yields the same lane-0 values for any wires, it is the same affine maps regrouped
+// (tests/test_gates.py).  The filter multiplies the folded sum once instead of each of the 123 constraints.
+// Templated on the number of challenges: the accumulators are 9 registers each.
+template <int NC>
+__global__ void __launch_bounds__(128, 4) quotient_poseidon_kernel(const QvParams P, const bsx_gate g) {
     const size_t l = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t q_size = (size_t)1 << P.log_q;
     if (l >= q_size) return;
     const u32 i = __brev((u32)l) >> (32 - P.log_q);
     const u64 *w = P.wires + l;
 #define PG_W(j) __ldg(w + (size_t)(j) * P.stride)
-    gl_acc3 res[QV_MAX_CHALLENGES];
+    gl_acc3 res[NC];
 #pragma unroll
-    for (int a = 0; a < QV_MAX_CHALLENGES; a++) res[a] = gl_acc3_zero();
-    int slot = P.gate_base;
+    for (int a = 0; a < NC; a++) res[a] = gl_acc3_zero();
+    const u64 *apow = P.apow + P.gate_base;
+    int slot = 0;
+    auto fold = [&](u64 c) {
+#pragma unroll
+        for (int a = 0; a < NC; a++) gl_acc3_mac(res[a], c, __ldg(apow + (size_t)a * P.n_terms + slot));
+        slot++;
+    };
     u64 s[12];
     {
         const u64 swap = PG_W(PG_SWAP);
-        qv_fold(res, P, gl_mul_lazy(swap, gl_sub_c(swap, 1)), slot++);
+        fold(gl_mul_lazy(swap, gl_sub_c(swap, 1)));
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const u64 lhs = PG_W(k), rhs = PG_W(k + 4), d = PG_W(PG_DELTA + k);
-            qv_fold(res, P, gl_sub_c(gl_canon_fast(gl_mul_lazy(swap, gl_sub_c(rhs, lhs))), d), slot++);
+            fold(gl_sub_c(gl_canon_fast(gl_mul_lazy(swap, gl_sub_c(rhs, lhs))), d));
             s[k] = gl_add_lazy_canon(gl_add_lazy_canon(lhs, d), POSEIDON_RC[k]);
             s[k + 4] = gl_add_lazy_canon(gl_sub_c(rhs, d), POSEIDON_RC[k + 4]);
         }
@@ -253,44 +262,62 @@ __global__ void __launch_bounds__(128) quotient_poseidon_kernel(const QvParams P
         for (int k = 8; k < 12; k++) s[k] = gl_add_lazy_canon(PG_W(k), POSEIDON_RC[k]);
     }
 #pragma unroll 1
-    for (int r = 0; r < 30; r++) {
-        const bool full = r < 4 || r >= 26;
-        if (r >= 1) {  // s = state after this round's constant layer
-            const int w0 = r < 4 ? PG_FULL0 + 12 * (r - 1) : r < 26 ? PG_PARTIAL + (r - 4) : PG_FULL1 + 12 * (r - 26);
-            if (full) {
+    for (int half = 0; half < 2; half++) {
+#pragma unroll 1
+        for (int r = 0; r < 4; r++) {
+            if (half + r) {  // s = the state after this round's constant layer: the wires say what it has to be
+                const int w0 = half ? PG_FULL1 + 12 * r : PG_FULL0 + 12 * (r - 1);
 #pragma unroll
                 for (int k = 0; k < 12; k++) {
                     const u64 win = PG_W(w0 + k);
-                    qv_fold(res, P, gl_sub_c(gl_canon_fast(s[k]), win), slot++);
+                    fold(gl_sub_c(gl_canon_fast(s[k]), win));
                     s[k] = win;
                 }
-            } else {
-                const u64 win = PG_W(w0);
-                qv_fold(res, P, gl_sub_c(gl_canon_fast(s[0]), win), slot++);
-                s[0] = win;
             }
-        }
-        if (full) {
 #pragma unroll
             for (int k = 0; k < 12; k++) s[k] = poseidon_sbox(s[k]);
-        } else {
-            s[0] = poseidon_sbox(s[0]);
+            u32 post[36];
+            poseidon_load_post(half * 26 + r, post);
+            poseidon_mds_post_fft(s, post);
         }
-        u32 post[36];
-        poseidon_load_post(r, post);
-        poseidon_mds_post_fft(s, post);
+        if (half == 0) {
+            u32 x0[12], x1[12], x2[12], a0, a1, a2;
+#pragma unroll
+            for (int k = 1; k < 12; k++) poseidon_split22(s[k], x0[k], x1[k], x2[k]);
+            poseidon_split22(s[0], a0, a1, a2);
+#pragma unroll 1
+            for (int p = 4; p < 26; p++) {
+                const u64 win = PG_W(PG_PARTIAL + p - 4);
+                fold(gl_sub_c(gl_canon_fast(poseidon_merge22(a0, a1, a2)), win));
+                u32 post[36];
+                poseidon_load_post(p, post);
+                poseidon_split22(poseidon_sbox(win), x0[0], x1[0], x2[0]);
+                u32 y0[12], y1[12], y2[12];
+                poseidon_mds_plane(x0, post, y0);
+                poseidon_mds_plane(x1, post + 12, y1);
+                poseidon_mds_plane(x2, post + 24, y2);
+                a0 = y0[0], a1 = y1[0], a2 = y2[0];
+#pragma unroll
+                for (int k = 1; k < 12; k++) {
+                    poseidon_norm22(y0[k], y1[k], y2[k]);
+                    x0[k] = y0[k], x1[k] = y1[k], x2[k] = y2[k];
+                }
+            }
+            s[0] = poseidon_merge22(a0, a1, a2);
+#pragma unroll
+            for (int k = 1; k < 12; k++) s[k] = poseidon_merge22(x0[k], x1[k], x2[k]);
+        }
     }
 #pragma unroll
-    for (int k = 0; k < 12; k++) qv_fold(res, P, gl_sub_c(gl_canon_fast(s[k]), PG_W(PG_OUT + k)), slot++);
+    for (int k = 0; k < 12; k++) fold(gl_sub_c(gl_canon_fast(s[k]), PG_W(PG_OUT + k)));
 #undef PG_W
     const u64 f = qv_filter(P, g, P.cs + l);
     const u64 scale = gl_mul_lazy(f, __ldg(P.zh + (1u << P.qdb) + (i & ((1u << P.qdb) - 1))));
 #pragma unroll
-    for (int a = 0; a < QV_MAX_CHALLENGES; a++)
-        if (a < P.nc) {
-            u64 *o = P.out + (size_t)a * q_size + i;
-            *o = gl_canon_fast(gl_mul_add_lazy(gl_acc3_reduce(res[a]), scale, *o));
-        }
+    for (int a = 0; a < NC; a++) {
+        u64 *o = P.out + (size_t)a * q_size + i;
+        *o = gl_canon_fast(gl_mul_add_lazy(gl_acc3_reduce(res[a]), scale, *o));
+    }
 }
 
 // gates/poseidon.rs PoseidonGenerator::run_once on row-major rows of 135 wires: inputs and swap are read, the deltas, the
@@ -490,7 +517,13 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
     for (int g = 0; g < c->n_gates; g++)
         if (c->gates[g].kind == BSX_GATE_POSEIDON) {
             BSX_COUNT_LAUNCH();
-            quotient_poseidon_kernel<<<(unsigned)((q_size + 127) / 128), 128, 0, ctx->stream>>>(P, c->gates[g]);
+            const unsigned blocks = (unsigned)((q_size + 127) / 128);
+            switch (nc) {
+                case 1: quotient_poseidon_kernel<1><<<blocks, 128, 0, ctx->stream>>>(P, c->gates[g]); break;
+                case 2: quotient_poseidon_kernel<2><<<blocks, 128, 0, ctx->stream>>>(P, c->gates[g]); break;
+                case 3: quotient_poseidon_kernel<3><<<blocks, 128, 0, ctx->stream>>>(P, c->gates[g]); break;
+                default: quotient_poseidon_kernel<4><<<blocks, 128, 0, ctx->stream>>>(P, c->gates[g]); break;
+            }
             CU(ctx, cudaGetLastError());
         }
     bsx_free(ctx, tab);

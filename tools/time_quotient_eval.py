@@ -21,18 +21,23 @@ def commit(w):
     del t
     return b
 cs, wires, zs = commit(84), commit(135), commit(20)
-circuit = prove_circuit(pkg)
 out = torch.empty((2, n << 3), dtype=torch.int64, device="cuda:0")
-ts = []
-for rep in range(6):
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    pkg.quotient_values(ctx, circuit, cs, wires, zs, [1, 2, 3, 4], [3, 4], [5, 6], [7, 8], out_device_ptr=out.data_ptr())
-    e1.record(stream)
-    torch.cuda.synchronize()
-    ts.append(e0.elapsed_time(e1))
-ms = float(np.median(ts[1:]))
 bytes_ = 8 * (84 + 135 + 20 + 2) * (n << 3) + 16 * (n << 3)
-qb = [pkg.compute_quotient_polys(ctx, circuit, cs, wires, zs, [1, 2, 3, 4], [3, 4], [5, 6], [7, 8], 4) for _ in range(4)]
-print("kernel alone (events inside bsx_compute_quotient_polys): %s ms" % [round(b.eval_ms, 2) for b in qb])
-print("quotient_values %.2f ms  (%.0f GB/s of LDE rows read; checksum %016x)" % (ms, bytes_ / ms / 1e6, int(out.view(-1)[12345].item()) & (2**64 - 1)))
+for gate_set in ("basic", "all"):
+    circuit = prove_circuit(pkg, gate_set)
+    ts = []
+    for rep in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        pkg.quotient_values(ctx, circuit, cs, wires, zs, [1, 2, 3, 4], [3, 4], [5, 6], [7, 8], out_device_ptr=out.data_ptr())
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ms = float(np.median(ts[1:]))
+    qb = [pkg.compute_quotient_polys(ctx, circuit, cs, wires, zs, [1, 2, 3, 4], [3, 4], [5, 6], [7, 8], 4) for _ in range(4)]
+    print("gates %-5s (%d kinds, %d constraints): kernels alone (events inside bsx_compute_quotient_polys) %s ms" %
+          (gate_set, len(circuit.gates), circuit.num_gate_constraints, [round(b.eval_ms, 2) for b in qb]))
+    print("   quotient_values %.2f ms  (%.0f GB/s of LDE rows read; checksum %016x)" %
+          (ms, bytes_ / ms / 1e6, int(out.view(-1)[12345].item()) & (2**64 - 1)))
+    for b in qb:
+        b.close()
