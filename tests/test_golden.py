@@ -133,6 +133,40 @@ def test_oracle_reproduces_golden_proof(oracle):
     assert plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)[0]
 
 
+def _golden_gate_rows():
+    rows = np.zeros((2, 135), dtype=np.uint64)
+    rows[:, :12] = splitmix_field(G["poseidon_gate"]["inputs_seed"], (2, 12))
+    rows[1, 24] = 1
+    return rows
+
+
+def _check_golden_gate_rows(rows):
+    q = G["poseidon_gate"]
+    assert digest(rows) == q["rows_sha256"] and hx(rows[0, 12:24]) == q["row0_outputs"] and hx(rows[1, 25:29]) == q["row1_deltas"]
+    assert hx(rows[1, 65:68]) == q["row1_partial_sbox_inputs_head"] and hx(rows[1, 123:126]) == q["row1_last_full_sbox_inputs_head"]
+
+
+def _golden_gates_circuit(pkg, fill):
+    q = G["gates"]
+    sc = pkg.synthetic_circuit(q["degree_bits"], seed=q["seed"], gate_set="all", poseidon_fill=fill)
+    assert [[g.kind, g.param, g.row, g.selector_index, g.group_start, g.group_end] for g in sc.circuit.gates] == q["gates"]
+    assert digest(sc.wires) == q["wires_sha256"] and digest(sc.constants) == q["constants_sha256"]
+    assert digest(sc.sigmas) == q["sigmas_sha256"] and hx(sc.public_inputs_hash) == q["public_inputs_hash"]
+    return sc
+
+
+def test_oracle_reproduces_golden_gates(oracle):
+    """PoseidonGate rows and the quotient values of the circuit with every gate kind."""
+    import __graft_entry__ as GE
+    import test_quotient as TQ
+    _check_golden_gate_rows(oracle.poseidon_gate_fill(_golden_gate_rows()))
+    sc = _golden_gates_circuit(GE.load_package(), oracle.poseidon_gate_fill)
+    be, ga, al = TQ._challenges(G["gates"]["challenge_seed"], 2)
+    ob = TQ._oracle_commitments(oracle, sc, be, ga)
+    qa = oracle.quotient_values(sc.circuit.as_dict(), ob[0], ob[1], ob[2], sc.public_inputs_hash, be, ga, al)
+    assert digest(qa) == G["gates"]["quotient_values_sha256"] and hx(qa[0, :4]) == G["gates"]["quotient_values_head"]
+
+
 # ------------------------------------------------------------------ GPU: the CUDA path vs the committed vectors
 @pytest.fixture(scope="module")
 def pkg():
@@ -236,3 +270,16 @@ def test_device_reproduces_golden_proof(pkg, ctx):
     sc.public_inputs_hash = pkg.hash_no_pad(ctx, pis)
     pw, aux = pkg.prove(ctx, sc, cfg, pis)
     _check_golden_proof(pw, aux)
+
+
+@pytest.mark.gpu
+def test_device_reproduces_golden_gates(pkg, ctx):
+    import test_quotient as TQ
+    _check_golden_gate_rows(ctx.poseidon_gate_witness(_golden_gate_rows()))
+    sc = _golden_gates_circuit(pkg, ctx.poseidon_gate_witness)
+    be, ga, al = TQ._challenges(G["gates"]["challenge_seed"], 2)
+    gb = TQ._device_commitments(pkg, ctx, sc, be, ga)
+    qa = pkg.quotient_values(ctx, sc.circuit, gb[0], gb[1], gb[2], sc.public_inputs_hash, be, ga, al)
+    assert digest(qa) == G["gates"]["quotient_values_sha256"] and hx(qa[0, :4]) == G["gates"]["quotient_values_head"]
+    for b in gb:
+        b.close()
