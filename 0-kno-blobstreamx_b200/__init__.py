@@ -51,10 +51,15 @@ from .plonk import (  # noqa: F401
     GATE_ARITHMETIC_EXTENSION,
     GATE_BASE_SUM,
     GATE_CONSTANT,
+    GATE_EXPONENTIATION,
     GATE_MUL_EXTENSION,
     GATE_NOOP,
     GATE_POSEIDON,
+    GATE_POSEIDON_MDS,
     GATE_PUBLIC_INPUT,
+    GATE_RANDOM_ACCESS,
+    GATE_REDUCING,
+    GATE_REDUCING_EXTENSION,
     CircuitDescription,
     Gate,
     SyntheticCircuit,

@@ -3,7 +3,8 @@
 // `eval_vanishing_poly_base_batch` / `evaluate_gate_constraints_base_batch` (with plonk/plonk_common.rs
 // `ZeroPolyOnCoset`, `reduce_with_powers_multi`, plonk/vanishing_poly.rs `check_partial_products`, gates/gate.rs
 // `compute_filter`) for circuits made of NoopGate, ConstantGate, PublicInputGate, ArithmeticGate, BaseSumGate<2>,
-// ArithmeticExtensionGate<2>, MulExtensionGate<2> (this kernel) and PoseidonGate (a second kernel that adds its share).
+// ArithmeticExtensionGate<2>, MulExtensionGate<2>, ExponentiationGate, ReducingGate<2>, ReducingExtensionGate<2>,
+// RandomAccessGate<2> (up to 4 bits), PoseidonMdsGate<2> (this kernel) and PoseidonGate (a second kernel that adds its share).
 //
 // Upstream walks the quotient domain in batches of 32 points and gathers, per point i, the rows
 // get_lde_values(i, step) of the constants+sigmas, wires and Zs commitments -- on the CPU that means the whole LDE
@@ -65,10 +66,10 @@ __device__ __forceinline__ u64 qv_inv(u64 a) {  // a^(p - 2), p - 2 = 2^64 - 2^3
 }
 
 // term (lazy) times alpha_a^idx into every accumulator
+template <int NC>
 __device__ __forceinline__ void qv_fold(gl_acc3 *res, const QvParams &P, u64 term, int idx) {
 #pragma unroll
-    for (int a = 0; a < QV_MAX_CHALLENGES; a++)
-        if (a < P.nc) gl_acc3_mac(res[a], term, __ldg(P.apow + (size_t)a * P.n_terms + idx));
+    for (int a = 0; a < NC; a++) gl_acc3_mac(res[a], term, __ldg(P.apow + (size_t)a * P.n_terms + idx));
 }
 
 // gates/gate.rs compute_filter(row, group_range, s, many_selector)
@@ -81,38 +82,40 @@ __device__ __forceinline__ u64 qv_filter(const QvParams &P, const bsx_gate &g, c
     return f;
 }
 
-__global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) {
+// Templated on the number of challenges: accumulators, running products and betas are per challenge.
+template <int NC>
+__global__ void __launch_bounds__(256, 2) quotient_values_kernel(const QvParams P) {
     const size_t l = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // leaf = row of the LDE buffers
     const size_t q_size = (size_t)1 << P.log_q;
     if (l >= q_size) return;
     const u32 i = __brev((u32)l) >> (32 - P.log_q);                   // domain index, x = omega^i
     const u32 i_next = (i + (1u << P.qdb)) & (u32)(q_size - 1);
     const size_t l_next = __brev(i_next) >> (32 - P.log_q);
-    const int nc = P.nc;
+    constexpr int nc = NC;
     u64 x = __ldg(P.tw.lo + (i & 4095));
     if (i >> 12) x = gl_mul_lazy(x, __ldg(P.tw.hi + (i >> 12)));
     const u64 sx = gl_canon_fast(gl_mul_lazy(x, 7));  // F::coset_shift() * x
-    gl_acc3 res[QV_MAX_CHALLENGES];
+    gl_acc3 res[NC];
 #pragma unroll
-    for (int a = 0; a < QV_MAX_CHALLENGES; a++) res[a] = gl_acc3_zero();
+    for (int a = 0; a < NC; a++) res[a] = gl_acc3_zero();
 
     // ---- vanishing_z_1_terms: L_0(x) (Z(x) - 1), L_0(x) = Z_H(x) / (n (x - 1))
     const u64 zh = __ldg(P.zh + (i & ((1u << P.qdb) - 1)));
     const u64 l0 = gl_mul_lazy(zh, qv_inv(gl_mul_lazy(P.n_field, gl_sub_c(sx, 1))));
     const u64 *zrow = P.zs + l;
 #pragma unroll
-    for (int k = 0; k < QV_MAX_CHALLENGES; k++)
-        if (k < nc) qv_fold(res, P, gl_mul_lazy(l0, gl_sub_c(__ldg(zrow + (size_t)k * P.stride), 1)), k);
+    for (int k = 0; k < NC; k++)
+        if (k < nc) qv_fold<NC>(res, P, gl_mul_lazy(l0, gl_sub_c(__ldg(zrow + (size_t)k * P.stride), 1)), k);
 
     // ---- vanishing_partial_products_terms: check_partial_products for every challenge, one pass over the wires
-    u64 bx[QV_MAX_CHALLENGES];
+    u64 bx[NC];
 #pragma unroll
-    for (int k = 0; k < QV_MAX_CHALLENGES; k++) bx[k] = k < nc ? gl_mul_lazy(P.betas[k], sx) : 0;
+    for (int k = 0; k < NC; k++) bx[k] = k < nc ? gl_mul_lazy(P.betas[k], sx) : 0;
     const u64 *wrow = P.wires + l, *srow = P.cs + (size_t)P.num_constants * P.stride + l;
     for (int m = 0; m < P.n_chunks; m++) {
-        u64 num[QV_MAX_CHALLENGES], den[QV_MAX_CHALLENGES];
+        u64 num[NC], den[NC];
 #pragma unroll
-        for (int k = 0; k < QV_MAX_CHALLENGES; k++) num[k] = den[k] = 1;
+        for (int k = 0; k < NC; k++) num[k] = den[k] = 1;
         const int j0 = m * P.max_degree, j1 = min(P.n_routed, j0 + P.max_degree);
         // QV_BATCH wires at a time: their loads are issued before the first multiply needs one of them
         for (int jb = j0; jb < j1; jb += QV_BATCH) {
@@ -128,7 +131,7 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
             for (int t = 0; t < QV_BATCH; t++) {
                 if (jb + t >= j1) break;
 #pragma unroll
-                for (int k = 0; k < QV_MAX_CHALLENGES; k++)
+                for (int k = 0; k < NC; k++)
                     if (k < nc) {
                         const u64 wg = gl_add_lazy_canon(wv[t], P.gammas[k]);                 // w + gamma (w < p: no second wrap)
                         num[k] = gl_mul_lazy(num[k], gl_mul_add_lazy(bx[k], kv[t], wg));       // w + beta k_j x + gamma
@@ -137,14 +140,14 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
             }
         }
 #pragma unroll
-        for (int k = 0; k < QV_MAX_CHALLENGES; k++)
+        for (int k = 0; k < NC; k++)
             if (k < nc) {
                 // product_accs = z_x, partial products of challenge k, z_gx; window (m, m + 1)
                 const u64 *pp = zrow + (size_t)(nc + k * (P.n_chunks - 1)) * P.stride;
                 const u64 prev = m == 0 ? __ldg(zrow + (size_t)k * P.stride) : __ldg(pp + (size_t)(m - 1) * P.stride);
                 const u64 next = m == P.n_chunks - 1 ? __ldg(P.zs + (size_t)k * P.stride + l_next) : __ldg(pp + (size_t)m * P.stride);
                 const u64 t = gl_sub_c(gl_canon_fast(gl_mul_lazy(prev, num[k])), gl_canon_fast(gl_mul_lazy(next, den[k])));
-                qv_fold(res, P, t, nc + k * P.n_chunks + m);
+                qv_fold<NC>(res, P, t, nc + k * P.n_chunks + m);
             }
     }
 
@@ -155,22 +158,30 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
         const bsx_gate g = P.gates[gi];
         if (g.kind == BSX_GATE_NOOP) continue;
         if (g.kind == BSX_GATE_POSEIDON) continue;  // quotient_poseidon_kernel
-        const u64 f = qv_filter(P, g, crow);
+        // sum_j alpha^(gate_base + j) filter c_j = filter * sum_j alpha^(gate_base + j) c_j: the constraints of one gate go
+        // into accumulators of their own and the filter multiplies the folded sum once
+        gl_acc3 ga[NC];
+#pragma unroll
+        for (int a = 0; a < NC; a++) ga[a] = gl_acc3_zero();
+        auto gfold = [&](u64 c, int slot_abs) {
+#pragma unroll
+            for (int a = 0; a < NC; a++) gl_acc3_mac(ga[a], c, __ldg(P.apow + (size_t)a * P.n_terms + slot_abs));
+        };
         if (g.kind == BSX_GATE_CONSTANT) {
             for (int t = 0; t < g.param; t++) {
                 const u64 c = gl_sub_c(__ldg(gconst + (size_t)t * P.stride), __ldg(wrow + (size_t)t * P.stride));
-                qv_fold(res, P, gl_mul_lazy(f, c), P.gate_base + t);
+                gfold(c, P.gate_base + t);
             }
         } else if (g.kind == BSX_GATE_PUBLIC_INPUT) {
             for (int t = 0; t < 4; t++)
-                qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(__ldg(wrow + (size_t)t * P.stride), P.pi_hash[t])), P.gate_base + t);
+                gfold(gl_sub_c(__ldg(wrow + (size_t)t * P.stride), P.pi_hash[t]), P.gate_base + t);
         } else if (g.kind == BSX_GATE_ARITHMETIC) {  // output - (m0 m1 const_0 + addend const_1)
             const u64 c0 = __ldg(gconst), c1 = __ldg(gconst + P.stride);
             for (int t = 0; t < g.param; t++) {
                 const u64 *wq = wrow + (size_t)(4 * t) * P.stride;
                 const u64 m0 = __ldg(wq), m1 = __ldg(wq + P.stride), ad = __ldg(wq + 2 * P.stride), o = __ldg(wq + 3 * P.stride);
                 const u64 computed = gl_mul_add_lazy(gl_mul_lazy(m0, m1), c0, gl_mul_lazy(ad, c1));
-                qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(o, gl_canon_fast(computed))), P.gate_base + t);
+                gfold(gl_sub_c(o, gl_canon_fast(computed)), P.gate_base + t);
             }
         } else if (g.kind == BSX_GATE_ARITHMETIC_EXTENSION || g.kind == BSX_GATE_MUL_EXTENSION) {
             // output - ((m0 m1).scalar_mul(const_0) [+ addend.scalar_mul(const_1)]) in F_p[X] / (X^2 - 7), two constraints
@@ -189,24 +200,109 @@ __global__ void __launch_bounds__(256) quotient_values_kernel(const QvParams P) 
                     e1 = gl_mul_add_lazy(__ldg(wq + 5 * P.stride), c1, e1);
                 }
                 const u64 o0 = __ldg(wq + (size_t)(per - 2) * P.stride), o1 = __ldg(wq + (size_t)(per - 1) * P.stride);
-                qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(o0, gl_canon_fast(e0))), P.gate_base + 2 * t);
-                qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(o1, gl_canon_fast(e1))), P.gate_base + 2 * t + 1);
+                gfold(gl_sub_c(o0, gl_canon_fast(e0)), P.gate_base + 2 * t);
+                gfold(gl_sub_c(o1, gl_canon_fast(e1)), P.gate_base + 2 * t + 1);
+            }
+        } else if (g.kind == BSX_GATE_EXPONENTIATION) {
+            // wires: base 0, power bits 1.. (little-endian), output 1 + n, intermediate values 2 + n..;
+            // prev^2 (bit base + 1 - bit) - intermediate_i with the bits taken from the top, then output - last
+            const int n = g.param;
+            const u64 base = __ldg(wrow);
+            u64 prev = 1;
+            for (int t = 0; t < n; t++) {
+                const u64 bit = __ldg(wrow + (size_t)(n - t) * P.stride), iv = __ldg(wrow + (size_t)(2 + n + t) * P.stride);
+                const u64 sel = gl_canon_fast(gl_mul_add_lazy(bit, gl_sub_c(base, 1), 1));  // bit base + (1 - bit)
+                gfold(gl_sub_c(gl_canon_fast(gl_mul_lazy(prev, sel)), iv), P.gate_base + t);
+                prev = gl_sqr_lazy(iv);
+            }
+            const u64 last = __ldg(wrow + (size_t)(2 + n + n - 1) * P.stride);
+            gfold(gl_sub_c(__ldg(wrow + (size_t)(1 + n) * P.stride), last), P.gate_base + n);
+        } else if (g.kind == BSX_GATE_REDUCING || g.kind == BSX_GATE_REDUCING_EXTENSION) {
+            // wires: output 0..2, alpha 2..4, old_acc 4..6, coeffs from 6 (one or two words each), then the accumulators (the
+            // last one is the output): acc alpha + coeff_i - acc_i in F_p[X] / (X^2 - 7)
+            const int n = g.param, cw = g.kind == BSX_GATE_REDUCING_EXTENSION ? 2 : 1, start_accs = 6 + n * cw;
+            const u64 al0 = __ldg(wrow + 2 * P.stride), al1 = __ldg(wrow + 3 * P.stride);
+            u64 a0 = __ldg(wrow + 4 * P.stride), a1 = __ldg(wrow + 5 * P.stride);
+            for (int t = 0; t < n; t++) {
+                const u64 *acc_t = wrow + (size_t)(t == n - 1 ? 0 : start_accs + 2 * t) * P.stride;
+                const u64 n0 = __ldg(acc_t), n1 = __ldg(acc_t + P.stride);
+                const u64 co0 = __ldg(wrow + (size_t)(6 + cw * t) * P.stride);
+                u64 t0 = gl_mul_add_lazy(a0, al0, gl_mul_lazy(gl_mul_lazy(a1, al1), 7));
+                u64 t1 = gl_mul_add_lazy(a0, al1, gl_mul_lazy(a1, al0));
+                t0 = gl_add_lazy_canon(t0, co0);
+                if (cw == 2) t1 = gl_add_lazy_canon(t1, __ldg(wrow + (size_t)(6 + 2 * t + 1) * P.stride));
+                gfold(gl_sub_c(gl_canon_fast(t0), n0), P.gate_base + 2 * t);
+                gfold(gl_sub_c(gl_canon_fast(t1), n1), P.gate_base + 2 * t + 1);
+                a0 = n0, a1 = n1;
+            }
+        } else if (g.kind == BSX_GATE_RANDOM_ACCESS) {
+            // per copy: access_index, claimed_element, 2^bits list items; the index bits sit after the routed wires.
+            // bit (bit - 1) per bit, bits recomposed - index, the list folded by the bits - claimed element; then the extra
+            // constants.  bits <= 4 here: the list lives in 16 registers.
+            const int bits = g.param & 0xFF, copies = (g.param >> 8) & 0xFF, extra = g.param >> 16, vec = 1 << bits;
+            const int routed = (2 + vec) * copies + extra;
+            int slot = P.gate_base;
+            for (int cp = 0; cp < copies; cp++) {
+                const u64 *q = wrow + (size_t)((2 + vec) * cp) * P.stride, *bw = wrow + (size_t)(routed + cp * bits) * P.stride;
+                u64 b[4], list[16];
+                u64 rec = 0;
+#pragma unroll
+                for (int t = 3; t >= 0; t--) {
+                    b[t] = t < bits ? __ldg(bw + (size_t)t * P.stride) : 0;
+                    if (t < bits) rec = gl_add_lazy_canon(gl_add_lazy_canon(rec, gl_canon_fast(rec)), b[t]);
+                }
+#pragma unroll
+                for (int t = 0; t < 4; t++)
+                    if (t < bits) gfold(gl_mul_lazy(b[t], gl_sub_c(b[t], 1)), slot++);
+                gfold(gl_sub_c(gl_canon_fast(rec), __ldg(q)), slot++);
+#pragma unroll
+                for (int j = 0; j < 16; j++) list[j] = j < vec ? __ldg(q + (size_t)(2 + j) * P.stride) : 0;
+#pragma unroll
+                for (int t = 0; t < 4; t++) {
+                    if (t < bits) {
+#pragma unroll
+                        for (int j = 0; j < (8 >> t); j++)  // x + b (y - x), canonical
+                            list[j] = gl_canon_fast(gl_mul_add_lazy(b[t], gl_sub_c(list[2 * j + 1], list[2 * j]), list[2 * j]));
+                    }
+                }
+                gfold(gl_sub_c(list[0], __ldg(q + P.stride)), slot++);
+            }
+            for (int t = 0; t < extra; t++)
+                gfold(gl_sub_c(__ldg(gconst + (size_t)t * P.stride),
+                                                        __ldg(wrow + (size_t)((2 + vec) * copies + t) * P.stride)), slot++);
+        } else if (g.kind == BSX_GATE_POSEIDON_MDS) {
+            // output_r - (sum_i CIRC[i] input_{(i + r) % 12} + 8 input_0 [r == 0]), the two coordinates of the algebra
+            // elements separately: the multiplication-free layer of the permutation with zero constants
+            u32 zero[36];
+#pragma unroll
+            for (int t = 0; t < 36; t++) zero[t] = 0;
+            for (int d = 0; d < 2; d++) {
+                u64 lane[12];
+#pragma unroll
+                for (int t = 0; t < 12; t++) lane[t] = __ldg(wrow + (size_t)(2 * t + d) * P.stride);
+                poseidon_mds_post_fft(lane, zero);
+#pragma unroll
+                for (int t = 0; t < 12; t++)
+                    gfold(gl_sub_c(__ldg(wrow + (size_t)(24 + 2 * t + d) * P.stride), gl_canon_fast(lane[t])), P.gate_base + 2 * t + d);
             }
         } else if (g.kind == BSX_GATE_BASE_SUM) {  // reduce_with_powers(limbs, 2) - sum; limb (limb - 1) per limb
             u64 acc = 0;
             for (int t = g.param; t >= 1; t--) {
                 const u64 limb = __ldg(wrow + (size_t)t * P.stride);
                 acc = gl_mul_add_lazy(acc, 2, limb);
-                qv_fold(res, P, gl_mul_lazy(f, gl_mul_lazy(limb, gl_sub_c(limb, 1))), P.gate_base + t);
+                gfold(gl_mul_lazy(limb, gl_sub_c(limb, 1)), P.gate_base + t);
             }
-            qv_fold(res, P, gl_mul_lazy(f, gl_sub_c(gl_canon_fast(acc), __ldg(wrow))), P.gate_base);
+            gfold(gl_sub_c(gl_canon_fast(acc), __ldg(wrow)), P.gate_base);
         }
+        const u64 f = qv_filter(P, g, crow);
+#pragma unroll
+        for (int a = 0; a < NC; a++) gl_acc3_mac(res[a], f, gl_acc3_reduce(ga[a]));
     }
 
     // ---- * z_h_on_coset.eval_inverse(i)
     const u64 zh_inv = __ldg(P.zh + (1u << P.qdb) + (i & ((1u << P.qdb) - 1)));
 #pragma unroll
-    for (int a = 0; a < QV_MAX_CHALLENGES; a++)
+    for (int a = 0; a < NC; a++)
         if (a < nc) P.out[(size_t)a * q_size + i] = gl_canon_fast(gl_mul_lazy(gl_acc3_reduce(res[a]), zh_inv));
 }
 
@@ -395,6 +491,14 @@ static int gate_constraints(const bsx_gate &g) {
         case BSX_GATE_ARITHMETIC_EXTENSION: return g.param < 0 ? -1 : 2 * g.param;
         case BSX_GATE_MUL_EXTENSION: return g.param < 0 ? -1 : 2 * g.param;
         case BSX_GATE_BASE_SUM: return g.param < 1 ? -1 : 1 + g.param;
+        case BSX_GATE_EXPONENTIATION: return g.param < 1 ? -1 : g.param + 1;
+        case BSX_GATE_REDUCING: return g.param < 1 ? -1 : 2 * g.param;
+        case BSX_GATE_REDUCING_EXTENSION: return g.param < 1 ? -1 : 2 * g.param;
+        case BSX_GATE_RANDOM_ACCESS: {
+            const int bits = g.param & 0xFF, copies = (g.param >> 8) & 0xFF, extra = g.param >> 16;
+            return bits < 1 || bits > 4 || copies < 1 || extra < 0 ? -1 : copies * (bits + 2) + extra;
+        }
+        case BSX_GATE_POSEIDON_MDS: return 24;
         default: return -1;
     }
 }
@@ -445,6 +549,14 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
         if (ok && G.kind == BSX_GATE_ARITHMETIC_EXTENSION) ok = 8 * G.param <= c->num_wires && n_gate_consts >= 2;
         if (ok && G.kind == BSX_GATE_MUL_EXTENSION) ok = 6 * G.param <= c->num_wires && n_gate_consts >= 1;
         if (ok && G.kind == BSX_GATE_BASE_SUM) ok = G.param <= 63 && 1 + G.param <= c->num_wires;
+        if (ok && G.kind == BSX_GATE_EXPONENTIATION) ok = 2 + 2 * G.param <= c->num_wires;
+        if (ok && G.kind == BSX_GATE_REDUCING) ok = 6 + G.param + 2 * (G.param - 1) <= c->num_wires;
+        if (ok && G.kind == BSX_GATE_REDUCING_EXTENSION) ok = 6 + 2 * G.param + 2 * (G.param - 1) <= c->num_wires;
+        if (ok && G.kind == BSX_GATE_RANDOM_ACCESS) {
+            const int bits = G.param & 0xFF, copies = (G.param >> 8) & 0xFF, extra = G.param >> 16;
+            ok = (2 + (1 << bits)) * copies + extra + copies * bits <= c->num_wires && extra <= n_gate_consts;
+        }
+        if (ok && G.kind == BSX_GATE_POSEIDON_MDS) ok = c->num_wires >= 48;
         if (!ok) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "gate %d (kind %d, param %d) does not fit the circuit", g, G.kind, G.param);
     }
     QvParams P;
@@ -512,7 +624,15 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
     P.out = out_dev;
     const size_t q_size = (size_t)1 << P.log_q;
     BSX_COUNT_LAUNCH();
-    quotient_values_kernel<<<(unsigned)((q_size + 255) / 256), 256, 0, ctx->stream>>>(P);
+    {
+        const unsigned blocks = (unsigned)((q_size + 255) / 256);
+        switch (nc) {
+            case 1: quotient_values_kernel<1><<<blocks, 256, 0, ctx->stream>>>(P); break;
+            case 2: quotient_values_kernel<2><<<blocks, 256, 0, ctx->stream>>>(P); break;
+            case 3: quotient_values_kernel<3><<<blocks, 256, 0, ctx->stream>>>(P); break;
+            default: quotient_values_kernel<4><<<blocks, 256, 0, ctx->stream>>>(P); break;
+        }
+    }
     CU(ctx, cudaGetLastError());
     for (int g = 0; g < c->n_gates; g++)
         if (c->gates[g].kind == BSX_GATE_POSEIDON) {

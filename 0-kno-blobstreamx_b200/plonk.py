@@ -15,6 +15,10 @@ GATE_NOOP, GATE_CONSTANT, GATE_PUBLIC_INPUT, GATE_ARITHMETIC = 0, 1, 2, 3
 # gates/poseidon.rs PoseidonGate (135 wires, 123 constraints), gates/arithmetic_extension.rs ArithmeticExtensionGate<2>,
 # gates/multiplication_extension.rs MulExtensionGate<2> (param = num_ops), gates/base_sum.rs BaseSumGate<2> (param = num_limbs)
 GATE_POSEIDON, GATE_ARITHMETIC_EXTENSION, GATE_MUL_EXTENSION, GATE_BASE_SUM = 4, 5, 6, 7
+# gates/exponentiation.rs ExponentiationGate (param = num_power_bits), gates/reducing.rs ReducingGate<2> and
+# gates/reducing_extension.rs ReducingExtensionGate<2> (param = num_coeffs), gates/random_access.rs RandomAccessGate<2>
+# (param = bits | num_copies << 8 | num_extra_constants << 16), gates/poseidon_mds.rs PoseidonMdsGate<2>
+GATE_EXPONENTIATION, GATE_REDUCING, GATE_REDUCING_EXTENSION, GATE_RANDOM_ACCESS, GATE_POSEIDON_MDS = 8, 9, 10, 11, 12
 POSEIDON_GATE_WIRES, POSEIDON_GATE_CONSTRAINTS = 135, 123
 
 
@@ -43,7 +47,10 @@ class Gate:
     def num_constraints(self):
         return {GATE_NOOP: 0, GATE_CONSTANT: self.param, GATE_PUBLIC_INPUT: 4, GATE_ARITHMETIC: self.param,
                 GATE_POSEIDON: POSEIDON_GATE_CONSTRAINTS, GATE_ARITHMETIC_EXTENSION: 2 * self.param,
-                GATE_MUL_EXTENSION: 2 * self.param, GATE_BASE_SUM: 1 + self.param}[self.kind]
+                GATE_MUL_EXTENSION: 2 * self.param, GATE_BASE_SUM: 1 + self.param,
+                GATE_EXPONENTIATION: self.param + 1, GATE_REDUCING: 2 * self.param, GATE_REDUCING_EXTENSION: 2 * self.param,
+                GATE_RANDOM_ACCESS: ((self.param >> 8) & 0xFF) * ((self.param & 0xFF) + 2) + (self.param >> 16),
+                GATE_POSEIDON_MDS: 24}[self.kind]
 
 
 @dataclass
@@ -175,66 +182,92 @@ def _ext_mul(a, b):
     return (a[0] * b[0] + 7 * a[1] * b[1]) % P, (a[0] * b[1] + a[1] * b[0]) % P
 
 
+def _all_gates(num_wires, num_routed_wires, num_ops, with_poseidon):
+    """The gate table of gate_set "all": every kind that fits the wire counts, in selector groups that keep
+    gate degree + group size <= 9 (gates/selectors.rs for quotient_degree_factor 8)."""
+    ra_bits = 4
+    while ra_bits > 1 and (2 + (1 << ra_bits)) > min(num_routed_wires, num_wires - ra_bits):
+        ra_bits -= 1
+    vec = 1 << ra_bits
+    ra_copies = min(num_routed_wires // (2 + vec), num_wires // (2 + vec + ra_bits))
+    ra_extra = min(num_routed_wires - (2 + vec) * ra_copies, 2)
+    groups = [
+        [(GATE_NOOP, 0), (GATE_CONSTANT, 2), (GATE_PUBLIC_INPUT, 0), (GATE_POSEIDON_MDS, 0),
+         (GATE_BASE_SUM, min(32, num_wires - 1)), (GATE_REDUCING, min(num_routed_wires - 6, (num_wires - 4) // 3))],
+        [(GATE_REDUCING_EXTENSION, min((num_routed_wires - 6) // 2, (num_wires - 4) // 4)), (GATE_ARITHMETIC, num_ops),
+         (GATE_ARITHMETIC_EXTENSION, num_routed_wires // 8), (GATE_MUL_EXTENSION, num_routed_wires // 6),
+         (GATE_EXPONENTIATION, min(num_routed_wires - 3, (num_wires - 2) // 2))],
+        [(GATE_RANDOM_ACCESS, ra_bits | ra_copies << 8 | ra_extra << 16), (GATE_POSEIDON, 0)]]
+    fits = lambda k, p: not ((k == GATE_POSEIDON and not (with_poseidon and num_wires >= POSEIDON_GATE_WIRES)) or
+                             (k == GATE_POSEIDON_MDS and num_wires < 48) or (k == GATE_RANDOM_ACCESS and ra_copies < 1) or
+                             (k in (GATE_REDUCING, GATE_REDUCING_EXTENSION, GATE_EXPONENTIATION) and p < 1))
+    gates, row = [], 0
+    for sel, grp in enumerate(groups):
+        grp = [(k, p) for k, p in grp if fits(k, p)]
+        for k, p in grp:
+            gates.append(Gate(k, p, row + len([1 for g in gates if g.selector_index == sel]), sel, row, row + len(grp)))
+        row += len(grp)
+    return gates
+
+
 def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_routed_wires=80, num_ops=20,
                       quotient_degree_factor=8, rate_bits=3, num_challenges=2, public_inputs_hash=None, gate_set="basic",
                       poseidon_fill=None, max_poseidon_rows=1 << 12):
     """A circuit with random constants, `n_copies` copy constraints between free arithmetic inputs, and a witness that
     satisfies all of it.  gate_set "basic": NoopGate / ConstantGate / PublicInputGate / ArithmeticGate rows in one selector
-    group.  "all" (degree_bits >= 5, quotient_degree_factor 8): two selector groups as gates/selectors.rs would form them
-    for max degree 9 -- [Noop, Constant, PublicInput, BaseSum<2>, Arithmetic, ArithmeticExtension] and [MulExtension,
-    Poseidon] -- with rows of every kind; `poseidon_fill(rows)` completes (k, 135) PoseidonGate rows whose inputs and
-    swap wire are set (Context.poseidon_gate_witness on the device; the Poseidon gate is left out when it is None or
-    the circuit has fewer than 135 wires)."""
+    group.  "all" (degree_bits >= 6, quotient_degree_factor 8): three selector groups as gates/selectors.rs would form them
+    for max degree 9 -- [Noop, Constant, PublicInput, PoseidonMds, BaseSum<2>, Reducing], [ReducingExtension, Arithmetic,
+    ArithmeticExtension, MulExtension, Exponentiation] and [RandomAccess, Poseidon] -- with rows of every kind;
+    `poseidon_fill(rows)` completes (k, 135) PoseidonGate rows whose inputs and swap wire are set
+    (Context.poseidon_gate_witness on the device; the Poseidon gate is left out when it is None or the circuit has fewer
+    than 135 wires)."""
     n = 1 << degree_bits
     rng = np.random.default_rng(seed)
     rand = lambda shape: rng.integers(0, P, size=shape, dtype=np.uint64)
     if gate_set == "all":
-        if degree_bits < 5 or quotient_degree_factor != 8:
-            raise ValueError('gate_set "all" wants degree_bits >= 5 and quotient_degree_factor 8')
-        n_ext, n_mulx, n_limbs = num_routed_wires // 8, num_routed_wires // 6, min(32, num_wires - 1)
-        with_poseidon = poseidon_fill is not None and num_wires >= POSEIDON_GATE_WIRES
-        gates = [Gate(GATE_NOOP, 0, 0, 0, 0, 6), Gate(GATE_CONSTANT, 2, 1, 0, 0, 6), Gate(GATE_PUBLIC_INPUT, 0, 2, 0, 0, 6),
-                 Gate(GATE_BASE_SUM, n_limbs, 3, 0, 0, 6), Gate(GATE_ARITHMETIC, num_ops, 4, 0, 0, 6),
-                 Gate(GATE_ARITHMETIC_EXTENSION, n_ext, 5, 0, 0, 6), Gate(GATE_MUL_EXTENSION, n_mulx, 6, 1, 6, 8)]
-        if with_poseidon:
-            gates.append(Gate(GATE_POSEIDON, 0, 7, 1, 6, 8))
-        else:
-            gates[-1] = Gate(GATE_MUL_EXTENSION, n_mulx, 6, 1, 6, 7)
+        if degree_bits < 6 or quotient_degree_factor != 8:
+            raise ValueError('gate_set "all" wants degree_bits >= 6 and quotient_degree_factor 8')
+        gates = _all_gates(num_wires, num_routed_wires, num_ops, poseidon_fill is not None)
+        n_sel = 3
         circ = CircuitDescription(degree_bits, gates, rate_bits=rate_bits, quotient_degree_factor=quotient_degree_factor,
                                   num_challenges=num_challenges, num_wires=num_wires, num_routed_wires=num_routed_wires,
-                                  num_constants=4, num_selectors=2)
-        kind_row = np.full(n, 4, dtype=np.int64)      # arithmetic rows ...
-        kind_row[0] = 2                               # ... one public-input row,
-        cuts = np.cumsum([1, max(1, n // 16), max(1, n // 16), max(1, n // 8), max(1, n // 8),
-                          min(max(1, n // 8), max_poseidon_rows) if with_poseidon else 0])
-        for k, (a, b) in zip((1, 3, 5, 6, 7), zip(cuts[:-1], cuts[1:])):
-            kind_row[a:b] = k                         # constant, base-sum, arithmetic-extension, mul-extension, Poseidon rows
-        kind_row[n - max(1, n // 32):] = 0            # and padding rows at the end
-        group = np.array([g.selector_index for g in gates])[kind_row]
-        sel0 = np.where(group == 0, kind_row, UNUSED_SELECTOR).astype(np.uint64)
-        sel1 = np.where(group == 1, kind_row, UNUSED_SELECTOR).astype(np.uint64)
-        constants = np.stack([sel0, sel1, rand(n), rand(n)])
-        c0, c1 = constants[2], constants[3]
-        arith_kind, const_kind = 4, 1
+                                  num_constants=n_sel + 2, num_selectors=n_sel)
+        kind_row = np.full(n, GATE_ARITHMETIC, dtype=np.int64)   # arithmetic rows ...
+        kind_row[0] = GATE_PUBLIC_INPUT                           # ... one public-input row,
+        at = 1
+        for g in gates:                                           # a run of rows of every other kind,
+            if g.kind in (GATE_NOOP, GATE_PUBLIC_INPUT, GATE_ARITHMETIC):
+                continue
+            k = max(1, n // 32)
+            if g.kind == GATE_POSEIDON:
+                k = min(max(1, n // 8), max_poseidon_rows)
+            kind_row[at:at + k] = g.kind
+            at += k
+        kind_row[n - max(1, n // 32):] = GATE_NOOP                # and padding rows at the end
     else:
         gates = [Gate(GATE_NOOP, 0, 0, 0, 0, 4), Gate(GATE_CONSTANT, 2, 1, 0, 0, 4), Gate(GATE_PUBLIC_INPUT, 0, 2, 0, 0, 4),
                  Gate(GATE_ARITHMETIC, num_ops, 3, 0, 0, 4)]
+        n_sel = 1
         circ = CircuitDescription(degree_bits, gates, rate_bits=rate_bits, quotient_degree_factor=quotient_degree_factor,
                                   num_challenges=num_challenges, num_wires=num_wires, num_routed_wires=num_routed_wires)
-        kind_row = np.full(n, 3, dtype=np.int64)      # arithmetic rows ...
-        kind_row[0] = 2                               # ... one public-input row,
+        kind_row = np.full(n, GATE_ARITHMETIC, dtype=np.int64)    # arithmetic rows ...
+        kind_row[0] = GATE_PUBLIC_INPUT                           # ... one public-input row,
         n_const = max(1, n // 16) if n > 2 else 0
-        kind_row[1:1 + n_const] = 1                   # some constant rows,
+        kind_row[1:1 + n_const] = GATE_CONSTANT                   # some constant rows,
         if n > 4:
-            kind_row[n - max(1, n // 32):] = 0        # and padding rows at the end
-        constants = np.stack([kind_row.astype(np.uint64), rand(n), rand(n)])
-        c0, c1 = constants[1], constants[2]
-        arith_kind, const_kind = 3, 1
-    sel = kind_row
+            kind_row[n - max(1, n // 32):] = GATE_NOOP            # and padding rows at the end
+    by_kind = {g.kind: g for g in gates}
+    gate_idx = np.array([by_kind[int(k)].row for k in kind_row])
+    gate_sel = np.array([by_kind[int(k)].selector_index for k in kind_row])
+    sel_cols = [np.where(gate_sel == t, gate_idx, UNUSED_SELECTOR).astype(np.uint64) for t in range(n_sel)]
+    constants = np.stack(sel_cols + [rand(n), rand(n)])
+    c0, c1 = constants[n_sel], constants[n_sel + 1]
+    rows_of = lambda kind: np.nonzero(kind_row == kind)[0]
+    param_of = lambda kind: by_kind[kind].param
     wires = rand((num_wires, n))
     pih = rand(4) if public_inputs_hash is None else np.array(public_inputs_hash, dtype=np.uint64).reshape(4).copy()
     # copy constraints: disjoint pairs of free cells (multiplicands / addends of arithmetic rows)
-    arith_rows = np.nonzero(sel == arith_kind)[0]
+    arith_rows = rows_of(GATE_ARITHMETIC)
     free = [(4 * i + t, r) for r in arith_rows[: 4096] for i in range(num_ops) for t in range(3)]
     if n_copies is None:
         n_copies = min(len(free) // 2, 4 * n)
@@ -247,7 +280,7 @@ def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_rou
         perm[ja, ra], perm[jb, rb] = ident[jb, rb], ident[ja, ra]
     # satisfy the gates
     w = pow(1753635133440165772, 1 << (32 - degree_bits), P)  # plonky2 primitive_root_of_unity(degree_bits)
-    c_rows = np.nonzero(sel == const_kind)[0]
+    c_rows = rows_of(GATE_CONSTANT)
     wires[0, c_rows], wires[1, c_rows] = c0[c_rows], c1[c_rows]
     wires[0:4, 0] = pih
     for i in range(num_ops):
@@ -255,26 +288,7 @@ def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_rou
         a = _mulmod(wires[4 * i + 2, arith_rows], c1[arith_rows])
         wires[4 * i + 3, arith_rows] = np.array([(int(x) + int(y)) % P for x, y in zip(m, a)], dtype=np.uint64)
     if gate_set == "all":
-        for r in np.nonzero(sel == 3)[0]:           # BaseSumGate<2>: wire 0 = sum of 2^i * limb_i, limbs are bits
-            bits = rng.integers(0, 2, size=n_limbs, dtype=np.uint64)
-            wires[1:1 + n_limbs, r] = bits
-            wires[0, r] = sum(int(b) << i for i, b in enumerate(bits)) % P
-        for kind, per, n_ops in ((5, 8, n_ext), (6, 6, n_mulx)):  # output = m0 m1 const_0 (+ addend const_1) in F_p^2
-            for r in np.nonzero(sel == kind)[0]:
-                k0, k1 = int(c0[r]), int(c1[r])
-                for i in range(n_ops):
-                    q = [int(x) for x in wires[per * i:per * i + per, r]]
-                    pr = _ext_mul(q[0:2], q[2:4])
-                    out = [pr[d] * k0 % P for d in range(2)]
-                    if kind == 5:
-                        out = [(out[d] + q[4 + d] * k1) % P for d in range(2)]
-                    wires[per * i + per - 2:per * i + per, r] = out
-        p_rows = np.nonzero(sel == 7)[0]
-        if p_rows.size:
-            rows = np.ascontiguousarray(wires[:POSEIDON_GATE_WIRES, p_rows].T)
-            rows[:, 24] = rng.integers(0, 2, size=p_rows.size, dtype=np.uint64)  # swap
-            rows = _np(poseidon_fill(rows)).reshape(p_rows.size, POSEIDON_GATE_WIRES)
-            wires[:POSEIDON_GATE_WIRES, p_rows] = rows.T
+        _fill_gate_rows(wires, rows_of, param_of, by_kind, c0, c1, rng, poseidon_fill)
     # sigma polynomials' values: cell (j', r') -> k_j' * omega^r'
     omegas = np.empty(n, dtype=object)
     acc = 1
@@ -287,6 +301,75 @@ def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_rou
     jj, rr = flat // n, flat % n
     sig.reshape(-1)[:] = np.array([k[j] * omegas[r] % P for j, r in zip(jj, rr)], dtype=np.uint64)
     return SyntheticCircuit(circ, constants, sig, wires, pih)
+
+
+MDS_CIRC = [17, 15, 41, 16, 2, 28, 13, 13, 39, 18, 34, 20]  # hash/poseidon_goldilocks.rs MDS_MATRIX_CIRC; DIAG = [8, 0, ...]
+
+
+def _fill_gate_rows(wires, rows_of, param_of, by_kind, c0, c1, rng, poseidon_fill):
+    """What the gates' generators (SimpleGenerator::run_once of each gate file) compute, on python ints."""
+    W = lambda j, r: int(wires[j, r])
+    if GATE_BASE_SUM in by_kind:                     # wire 0 = sum of 2^i * limb_i, limbs are bits
+        n_limbs = param_of(GATE_BASE_SUM)
+        for r in rows_of(GATE_BASE_SUM):
+            bits = rng.integers(0, 2, size=n_limbs, dtype=np.uint64)
+            wires[1:1 + n_limbs, r] = bits
+            wires[0, r] = sum(int(b) << i for i, b in enumerate(bits)) % P
+    for kind, per in ((GATE_ARITHMETIC_EXTENSION, 8), (GATE_MUL_EXTENSION, 6)):  # output = m0 m1 const_0 (+ addend const_1) in F_p^2
+        for r in rows_of(kind) if kind in by_kind else ():
+            k0, k1 = int(c0[r]), int(c1[r])
+            for i in range(param_of(kind)):
+                q = [W(per * i + t, r) for t in range(per)]
+                pr = _ext_mul(q[0:2], q[2:4])
+                out = [pr[d] * k0 % P for d in range(2)]
+                if kind == GATE_ARITHMETIC_EXTENSION:
+                    out = [(out[d] + q[4 + d] * k1) % P for d in range(2)]
+                wires[per * i + per - 2:per * i + per, r] = out
+    if GATE_EXPONENTIATION in by_kind:               # base 0, power bits 1.. (little-endian), output 1 + n, intermediates 2 + n..
+        nb = param_of(GATE_EXPONENTIATION)
+        for r in rows_of(GATE_EXPONENTIATION):
+            bits = rng.integers(0, 2, size=nb, dtype=np.uint64)
+            wires[1:1 + nb, r] = bits
+            base, acc = W(0, r), 1
+            for i in range(nb):
+                acc = acc * acc % P * (base if bits[nb - 1 - i] else 1) % P
+                wires[2 + nb + i, r] = acc
+            wires[1 + nb, r] = acc
+    for kind, cw in ((GATE_REDUCING, 1), (GATE_REDUCING_EXTENSION, 2)):  # acc_i = acc_{i-1} alpha + coeff_i, last one = output
+        for r in rows_of(kind) if kind in by_kind else ():
+            nco = param_of(kind)
+            alpha, acc = (W(2, r), W(3, r)), (W(4, r), W(5, r))
+            for i in range(nco):
+                t = _ext_mul(acc, alpha)
+                acc = ((t[0] + W(6 + cw * i, r)) % P, (t[1] + (W(6 + 2 * i + 1, r) if cw == 2 else 0)) % P)
+                at = 0 if i == nco - 1 else 6 + nco * cw + 2 * i
+                wires[at:at + 2, r] = acc
+    if GATE_RANDOM_ACCESS in by_kind:                # per copy: access_index, claimed_element, 2^bits items; bits after the routed wires
+        p = param_of(GATE_RANDOM_ACCESS)
+        bits, copies, extra = p & 0xFF, (p >> 8) & 0xFF, p >> 16
+        vec = 1 << bits
+        routed = (2 + vec) * copies + extra
+        for r in rows_of(GATE_RANDOM_ACCESS):
+            for c in range(copies):
+                idx = int(rng.integers(0, vec))
+                q = (2 + vec) * c
+                wires[q, r] = idx
+                wires[q + 1, r] = wires[q + 2 + idx, r]
+                wires[routed + c * bits:routed + (c + 1) * bits, r] = [(idx >> i) & 1 for i in range(bits)]
+            for i in range(extra):
+                wires[(2 + vec) * copies + i, r] = (c0, c1)[i][r]
+    if GATE_POSEIDON_MDS in by_kind:                 # outputs (wires 24..47) = MDS * inputs (wires 0..23), component by component
+        for r in rows_of(GATE_POSEIDON_MDS):
+            for d in range(2):
+                x = [W(2 * i + d, r) for i in range(12)]
+                for o in range(12):
+                    wires[24 + 2 * o + d, r] = (sum(MDS_CIRC[i] * x[(i + o) % 12] for i in range(12)) + (8 * x[0] if o == 0 else 0)) % P
+    p_rows = rows_of(GATE_POSEIDON) if GATE_POSEIDON in by_kind else np.zeros(0, dtype=np.int64)
+    if p_rows.size:
+        rows = np.ascontiguousarray(wires[:POSEIDON_GATE_WIRES, p_rows].T)
+        rows[:, 24] = rng.integers(0, 2, size=p_rows.size, dtype=np.uint64)  # swap
+        rows = _np(poseidon_fill(rows)).reshape(p_rows.size, POSEIDON_GATE_WIRES)
+        wires[:POSEIDON_GATE_WIRES, p_rows] = rows.T
 
 
 # ---------------------------------------------------------------------------------------------

@@ -429,6 +429,12 @@ int32_t bsx_partial_products_and_zs(bsx_ctx *ctx, const uint64_t *wires, const u
                                    multiplicand_0, multiplicand_1, addend, output in F_p[X]/(X^2 - 7); 2 constraints each */
 #define BSX_GATE_MUL_EXTENSION 6 /* gates/multiplication_extension.rs, D = 2, param = num_ops: wires 6i .. 6i+5 */
 #define BSX_GATE_BASE_SUM 7     /* gates/base_sum.rs BaseSumGate<2>, param = num_limbs (<= 63): wire 0 = sum, wires 1.. = limbs */
+#define BSX_GATE_EXPONENTIATION 8 /* gates/exponentiation.rs, param = num_power_bits: base 0, bits 1.., output 1 + n, intermediates 2 + n.. */
+#define BSX_GATE_REDUCING 9     /* gates/reducing.rs ReducingGate<2>, param = num_coeffs: output, alpha, old_acc, coeffs, accumulators */
+#define BSX_GATE_REDUCING_EXTENSION 10 /* gates/reducing_extension.rs ReducingExtensionGate<2>, param = num_coeffs */
+#define BSX_GATE_RANDOM_ACCESS 11 /* gates/random_access.rs RandomAccessGate<2>: param = bits | num_copies << 8 |
+                                   num_extra_constants << 16, bits <= 4 */
+#define BSX_GATE_POSEIDON_MDS 12 /* gates/poseidon_mds.rs PoseidonMdsGate<2>: wires 24 + 2r + d = MDS row r of wires 2i + d */
 typedef struct bsx_gate {
     int32_t kind, param, row, selector_index, group_start, group_end;
 } bsx_gate;

@@ -155,6 +155,12 @@ int orc_partial_products_and_z(const uint64_t *wires, const uint64_t *sigmas, in
 #define ORC_GATE_ARITHMETIC_EXTENSION 5 /* gates/arithmetic_extension.rs ArithmeticExtensionGate<2> { num_ops = param } */
 #define ORC_GATE_MUL_EXTENSION 6        /* gates/multiplication_extension.rs MulExtensionGate<2> { num_ops = param } */
 #define ORC_GATE_BASE_SUM 7             /* gates/base_sum.rs BaseSumGate<2> { num_limbs = param } */
+#define ORC_GATE_EXPONENTIATION 8       /* gates/exponentiation.rs ExponentiationGate { num_power_bits = param } */
+#define ORC_GATE_REDUCING 9             /* gates/reducing.rs ReducingGate<2> { num_coeffs = param } */
+#define ORC_GATE_REDUCING_EXTENSION 10  /* gates/reducing_extension.rs ReducingExtensionGate<2> { num_coeffs = param } */
+#define ORC_GATE_RANDOM_ACCESS 11       /* gates/random_access.rs RandomAccessGate<2>: param = bits | num_copies << 8 |
+                                           num_extra_constants << 16 */
+#define ORC_GATE_POSEIDON_MDS 12        /* gates/poseidon_mds.rs PoseidonMdsGate<2>: 24 inputs -> 24 outputs */
 typedef struct orc_gate { /* one entry of common_data.gates with its share of common_data.selectors_info */
     int32_t kind, param;
     int32_t row;                    /* index in common_data.gates: the selector value that switches it on */

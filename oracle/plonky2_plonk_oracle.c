@@ -1,9 +1,10 @@
 /* plonky2_plonk_oracle.c -- CPU restatement of the prover steps either side of the commitments:
  *   plonk/prover.rs `compute_quotient_polys` with plonk/vanishing_poly.rs `eval_vanishing_poly_base_batch`
  *   (the vanishing polynomial on the quotient coset) for circuits built from NoopGate, ConstantGate,
- *   PublicInputGate, ArithmeticGate, PoseidonGate, ArithmeticExtensionGate, MulExtensionGate and BaseSumGate<2>
+ *   PublicInputGate, ArithmeticGate, PoseidonGate, ArithmeticExtensionGate, MulExtensionGate, BaseSumGate<2>,
+ *   ExponentiationGate, ReducingGate, ReducingExtensionGate, RandomAccessGate and PoseidonMdsGate
  *   (gates/{noop,constant,public_input,arithmetic_base,poseidon,arithmetic_extension,multiplication_extension,
- *   base_sum}.rs), and
+ *   base_sum,exponentiation,reducing,reducing_extension,random_access,poseidon_mds}.rs), and
  *   util/serialization/mod.rs `write_proof_with_public_inputs` (`ProofWithPublicInputs::to_bytes`).
  * TEST INFRASTRUCTURE ONLY; "parity unpinned" against the real prover -- see plonky2_oracle.h. */
 #include "plonky2_oracle.h"
@@ -172,6 +173,63 @@ static int gate_eval_unfiltered(const orc_gate *g, const uint64_t *consts, const
                 for (int d = 0; d < 2; d++) out[2 * i + d] = orc_sub(q[4 + d], orc_mul(pr[d], consts[0]));
             }
             return 2 * g->param;
+        case ORC_GATE_EXPONENTIATION: { /* wires: base 0, power bits 1.. (little-endian), output 1 + n, intermediate values 2 + n.. */
+            const int n = g->param;
+            const uint64_t *iv = wires + 2 + n;
+            for (int i = 0; i < n; i++) {
+                const uint64_t prev = i == 0 ? 1 : orc_mul(iv[i - 1], iv[i - 1]);
+                const uint64_t bit = wires[1 + (n - 1 - i)]; /* accumulated in big-endian order */
+                out[i] = orc_sub(orc_mul(prev, orc_add(orc_mul(bit, wires[0]), orc_sub(1, bit))), iv[i]);
+            }
+            out[n] = orc_sub(wires[1 + n], iv[n - 1]);
+            return n + 1;
+        }
+        case ORC_GATE_REDUCING:
+        case ORC_GATE_REDUCING_EXTENSION: { /* wires: output 0..2, alpha 2..4, old_acc 4..6, coeffs from 6, then the accumulators
+                                             * (the last one is the output): acc alpha + coeff_i - acc_i */
+            const int n = g->param, cw = g->kind == ORC_GATE_REDUCING_EXTENSION ? 2 : 1, start_accs = 6 + n * cw;
+            const uint64_t *acc = wires + 4;
+            for (int i = 0; i < n; i++) {
+                const uint64_t *acc_i = i == n - 1 ? wires : wires + start_accs + 2 * i;
+                uint64_t t[2];
+                x2_mul(acc, wires + 2, t);
+                t[0] = orc_add(t[0], wires[6 + cw * i]);
+                if (cw == 2) t[1] = orc_add(t[1], wires[6 + 2 * i + 1]);
+                out[2 * i] = orc_sub(t[0], acc_i[0]);
+                out[2 * i + 1] = orc_sub(t[1], acc_i[1]);
+                acc = acc_i;
+            }
+            return 2 * n;
+        }
+        case ORC_GATE_RANDOM_ACCESS: { /* per copy: access_index, claimed_element, 2^bits list items; bits after the routed wires */
+            const int bits = g->param & 0xFF, copies = (g->param >> 8) & 0xFF, extra = g->param >> 16, vec = 1 << bits;
+            const int routed = (2 + vec) * copies + extra;
+            int t = 0;
+            uint64_t list[256];
+            for (int c = 0; c < copies; c++) {
+                const uint64_t *q = wires + (2 + vec) * c, *b = wires + routed + c * bits;
+                for (int i = 0; i < bits; i++) out[t++] = orc_mul(b[i], orc_sub(b[i], 1));
+                uint64_t rec = 0;
+                for (int i = bits - 1; i >= 0; i--) rec = orc_add(orc_add(rec, rec), b[i]);
+                out[t++] = orc_sub(rec, q[0]);
+                for (int j = 0; j < vec; j++) list[j] = q[2 + j];
+                for (int i = 0, len = vec; i < bits; i++, len >>= 1)
+                    for (int j = 0; j < len / 2; j++)
+                        list[j] = orc_add(list[2 * j], orc_mul(b[i], orc_sub(list[2 * j + 1], list[2 * j])));
+                out[t++] = orc_sub(list[0], q[1]);
+            }
+            for (int i = 0; i < extra; i++) out[t++] = orc_sub(consts[i], wires[(2 + vec) * copies + i]);
+            return t;
+        }
+        case ORC_GATE_POSEIDON_MDS: { /* output_r - (sum_i CIRC[i] input_{(i + r) % 12} + DIAG[r] input_r), component by component */
+            for (int d = 0; d < 2; d++) {
+                uint64_t lane[12];
+                for (int i = 0; i < 12; i++) lane[i] = wires[2 * i + d];
+                orc_poseidon_mds(lane);
+                for (int r = 0; r < 12; r++) out[2 * r + d] = orc_sub(wires[24 + 2 * r + d], lane[r]);
+            }
+            return 24;
+        }
         case ORC_GATE_BASE_SUM: { /* reduce_with_powers(limbs, 2) - sum, then limb (limb - 1) per limb; sum = wire 0 */
             uint64_t acc = 0;
             for (int i = g->param; i >= 1; i--) acc = orc_add(orc_mul(acc, 2), wires[i]);
@@ -194,6 +252,14 @@ int orc_gate_num_constraints(const orc_gate *g) {
         case ORC_GATE_ARITHMETIC_EXTENSION: return 2 * g->param;
         case ORC_GATE_MUL_EXTENSION: return 2 * g->param;
         case ORC_GATE_BASE_SUM: return 1 + g->param;
+        case ORC_GATE_EXPONENTIATION: return g->param < 1 ? -1 : g->param + 1;
+        case ORC_GATE_REDUCING: return g->param < 1 ? -1 : 2 * g->param;
+        case ORC_GATE_REDUCING_EXTENSION: return g->param < 1 ? -1 : 2 * g->param;
+        case ORC_GATE_RANDOM_ACCESS: {
+            const int bits = g->param & 0xFF, copies = (g->param >> 8) & 0xFF, extra = g->param >> 16;
+            return bits < 1 || bits > 8 || copies < 1 ? -1 : copies * (bits + 2) + extra;
+        }
+        case ORC_GATE_POSEIDON_MDS: return 24;
         default: return -1;
     }
 }
@@ -398,6 +464,73 @@ int orc_vanishing_at_ext(const orc_circuit *c, const uint64_t zeta[2], const uin
                         terms[t + 2 * i + d] = e2_add(terms[t + 2 * i + d], e2_mul(f, e2_sub(o, computed)));
                     }
                 }
+                break;
+            }
+            case ORC_GATE_EXPONENTIATION: {
+                const int n = g->param;
+                for (int i = 0; i < n; i++) {
+                    const e2 prev = i == 0 ? one : e2_mul(EXT_AT(wires, 2 + n + i - 1), EXT_AT(wires, 2 + n + i - 1));
+                    const e2 bit = EXT_AT(wires, 1 + (n - 1 - i));
+                    const e2 computed = e2_mul(prev, e2_add(e2_mul(bit, EXT_AT(wires, 0)), e2_sub(one, bit)));
+                    terms[t + i] = e2_add(terms[t + i], e2_mul(f, e2_sub(computed, EXT_AT(wires, 2 + n + i))));
+                }
+                terms[t + n] = e2_add(terms[t + n], e2_mul(f, e2_sub(EXT_AT(wires, 1 + n), EXT_AT(wires, 2 + n + n - 1))));
+                break;
+            }
+            case ORC_GATE_REDUCING:
+            case ORC_GATE_REDUCING_EXTENSION: { /* ExtensionAlgebra: acc * alpha + coeff - acc_i, two F_p^2 constraints each */
+                const int n = g->param, cw = g->kind == ORC_GATE_REDUCING_EXTENSION ? 2 : 1, start_accs = 6 + n * cw;
+                const e2 al0 = EXT_AT(wires, 2), al1 = EXT_AT(wires, 3);
+                int acc = 4;
+                for (int i = 0; i < n; i++) {
+                    const int acc_i = i == n - 1 ? 0 : start_accs + 2 * i;
+                    const e2 a0 = EXT_AT(wires, acc), a1 = EXT_AT(wires, acc + 1);
+                    e2 t0 = e2_add(e2_mul(a0, al0), e2_scale(e2_mul(a1, al1), 7)), t1 = e2_add(e2_mul(a0, al1), e2_mul(a1, al0));
+                    t0 = e2_add(t0, EXT_AT(wires, 6 + cw * i));
+                    if (cw == 2) t1 = e2_add(t1, EXT_AT(wires, 6 + 2 * i + 1));
+                    terms[t + 2 * i] = e2_add(terms[t + 2 * i], e2_mul(f, e2_sub(t0, EXT_AT(wires, acc_i))));
+                    terms[t + 2 * i + 1] = e2_add(terms[t + 2 * i + 1], e2_mul(f, e2_sub(t1, EXT_AT(wires, acc_i + 1))));
+                    acc = acc_i;
+                }
+                break;
+            }
+            case ORC_GATE_RANDOM_ACCESS: {
+                const int bits = g->param & 0xFF, copies = (g->param >> 8) & 0xFF, extra = g->param >> 16, vec = 1 << bits;
+                const int routed = (2 + vec) * copies + extra;
+                int k = 0;
+                e2 list[256];
+                for (int cp = 0; cp < copies; cp++) {
+                    const int q = (2 + vec) * cp, b = routed + cp * bits;
+                    for (int i = 0; i < bits; i++, k++)
+                        terms[t + k] = e2_add(terms[t + k], e2_mul(f, e2_mul(EXT_AT(wires, b + i), e2_sub(EXT_AT(wires, b + i), one))));
+                    e2 rec = e2_of(0);
+                    for (int i = bits - 1; i >= 0; i--) rec = e2_add(e2_add(rec, rec), EXT_AT(wires, b + i));
+                    terms[t + k] = e2_add(terms[t + k], e2_mul(f, e2_sub(rec, EXT_AT(wires, q))));
+                    k++;
+                    for (int j = 0; j < vec; j++) list[j] = EXT_AT(wires, q + 2 + j);
+                    for (int i = 0, len = vec; i < bits; i++, len >>= 1)
+                        for (int j = 0; j < len / 2; j++)
+                            list[j] = e2_add(list[2 * j], e2_mul(EXT_AT(wires, b + i), e2_sub(list[2 * j + 1], list[2 * j])));
+                    terms[t + k] = e2_add(terms[t + k], e2_mul(f, e2_sub(list[0], EXT_AT(wires, q + 1))));
+                    k++;
+                }
+                for (int i = 0; i < extra; i++, k++)
+                    terms[t + k] = e2_add(terms[t + k], e2_mul(f, e2_sub(EXT_AT(gc, i), EXT_AT(wires, (2 + vec) * copies + i))));
+                break;
+            }
+            case ORC_GATE_POSEIDON_MDS: { /* mds_layer_algebra: the matrix is over the base field, so every one of the four
+                                           * base-field coordinates of the 12 algebra elements goes through it on its own */
+                for (int d = 0; d < 2; d++)
+                    for (int cc = 0; cc < 2; cc++) {
+                        uint64_t lane[12];
+                        for (int i = 0; i < 12; i++) lane[i] = EXT_AT(wires, 2 * i + d).c[cc];
+                        orc_poseidon_mds(lane);
+                        for (int r = 0; r < 12; r++) {
+                            e2 diff = e2_of(0);
+                            diff.c[cc] = orc_sub(EXT_AT(wires, 24 + 2 * r + d).c[cc], lane[r]);
+                            terms[t + 2 * r + d] = e2_add(terms[t + 2 * r + d], e2_mul(f, diff));
+                        }
+                    }
                 break;
             }
             case ORC_GATE_BASE_SUM: {

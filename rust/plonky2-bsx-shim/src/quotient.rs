@@ -23,8 +23,8 @@ use crate::oracle::PolynomialBatch;
 use crate::{as_words, with_ctx, words_to_field};
 
 /// `common_data.gates` + `common_data.selectors_info` as the table the library reads; None when a gate is not one of
-/// the kinds the library evaluates (Noop, Constant, PublicInput, Arithmetic, Poseidon, ArithmeticExtension,
-/// MulExtension, BaseSum<2>).
+/// the kinds the library evaluates (Noop, Constant, PublicInput, Arithmetic, Poseidon, PoseidonMds, ArithmeticExtension,
+/// MulExtension, BaseSum<2>, Exponentiation, Reducing, ReducingExtension, RandomAccess up to 4 bits).
 pub fn gate_table<F: RichField + Extendable<D>, const D: usize>(common_data: &CommonCircuitData<F, D>) -> Option<Vec<sys::bsx_gate>> {
     let info = &common_data.selectors_info;
     common_data
@@ -49,6 +49,25 @@ pub fn gate_table<F: RichField + Extendable<D>, const D: usize>(common_data: &Co
                 (sys::BSX_GATE_MUL_EXTENSION, (g.0.num_constraints() / D) as i32)
             } else if id.starts_with("BaseSumGate") && id.contains("Base: 2") {
                 (sys::BSX_GATE_BASE_SUM, (g.0.num_constraints() - 1) as i32) // 1 + num_limbs constraints
+            } else if id.starts_with("ExponentiationGate") {
+                (sys::BSX_GATE_EXPONENTIATION, (g.0.num_constraints() - 1) as i32) // num_power_bits + 1 constraints
+            } else if id.starts_with("ReducingExtensionGate") && D == 2 {
+                (sys::BSX_GATE_REDUCING_EXTENSION, (g.0.num_constraints() / D) as i32)
+            } else if id.starts_with("ReducingGate") && D == 2 {
+                (sys::BSX_GATE_REDUCING, (g.0.num_constraints() / D) as i32)
+            } else if id.starts_with("RandomAccessGate") && D == 2 {
+                // "RandomAccessGate { bits: b, num_copies: c, num_extra_constants: e, .. }"
+                let field = |name: &str| -> Option<i32> {
+                    let at = id.find(name)? + name.len();
+                    id[at..].trim_start_matches(|ch: char| ch == ':' || ch == ' ').split(|ch: char| !ch.is_ascii_digit()).next()?.parse().ok()
+                };
+                let (bits, copies, extra) = (field("bits")?, field("num_copies")?, field("num_extra_constants")?);
+                if bits > 4 {
+                    return None;
+                }
+                (sys::BSX_GATE_RANDOM_ACCESS, bits | copies << 8 | extra << 16)
+            } else if id.starts_with("PoseidonMdsGate") && D == 2 {
+                (sys::BSX_GATE_POSEIDON_MDS, 0)
             } else {
                 return None;
             };

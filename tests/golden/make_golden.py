@@ -146,7 +146,7 @@ def main():
                   "proof_bytes_sha256": hashlib.sha256(pw.to_bytes(aux["fri_params"], aux["widths"])).hexdigest(),
                   "proof_bytes_len": len(pw.to_bytes(aux["fri_params"], aux["widths"]))}
     # gates beyond the basic four: two PoseidonGate rows (gates/poseidon.rs wire map; row 1 with swap = 1) and the quotient
-    # values of a 32-row circuit with every gate kind in two selector groups (synthetic_circuit(gate_set="all"))
+    # values of a 64-row circuit with every gate kind in three selector groups (synthetic_circuit(gate_set="all"))
     rows = np.zeros((2, 135), dtype=np.uint64)
     rows[:, :12] = splitmix_field(80, (2, 12))
     rows[1, 24] = 1
@@ -154,11 +154,11 @@ def main():
     g["poseidon_gate"] = {"inputs_seed": 80, "rows_sha256": digest(rows), "row0_outputs": hx(rows[0, 12:24]),
                           "row1_deltas": hx(rows[1, 25:29]), "row1_partial_sbox_inputs_head": hx(rows[1, 65:68]),
                           "row1_last_full_sbox_inputs_head": hx(rows[1, 123:126])}
-    sa = pkg.synthetic_circuit(5, seed=81, gate_set="all", poseidon_fill=O.poseidon_gate_fill)
+    sa = pkg.synthetic_circuit(6, seed=81, gate_set="all", poseidon_fill=O.poseidon_gate_fill)
     be, ga, al = TQ._challenges(82, 2)
     ob = TQ._oracle_commitments(O, sa, be, ga)
     qa = O.quotient_values(sa.circuit.as_dict(), ob[0], ob[1], ob[2], sa.public_inputs_hash, be, ga, al)
-    g["gates"] = {"degree_bits": 5, "seed": 81, "challenge_seed": 82,
+    g["gates"] = {"degree_bits": 6, "seed": 81, "challenge_seed": 82,
                   "gates": [[gt.kind, gt.param, gt.row, gt.selector_index, gt.group_start, gt.group_end] for gt in sa.circuit.gates],
                   "wires_sha256": digest(sa.wires), "constants_sha256": digest(sa.constants), "sigmas_sha256": digest(sa.sigmas),
                   "public_inputs_hash": hx(sa.public_inputs_hash), "quotient_values_sha256": digest(qa),

@@ -1,13 +1,15 @@
 """The gates beyond the four basic ones in the quotient evaluation: gates/poseidon.rs PoseidonGate,
-gates/arithmetic_extension.rs ArithmeticExtensionGate<2>, gates/multiplication_extension.rs MulExtensionGate<2> and
-gates/base_sum.rs BaseSumGate<2>, on a synthetic circuit with two selector groups.
+gates/arithmetic_extension.rs ArithmeticExtensionGate<2>, gates/multiplication_extension.rs MulExtensionGate<2>,
+gates/base_sum.rs BaseSumGate<2>, gates/exponentiation.rs ExponentiationGate, gates/reducing.rs ReducingGate<2>,
+gates/reducing_extension.rs ReducingExtensionGate<2>, gates/random_access.rs RandomAccessGate<2> and gates/poseidon_mds.rs
+PoseidonMdsGate<2>, on a synthetic circuit with three selector groups.
 
 CPU tier: the oracle's constraints are checked through what defines them -- a witness produced by the generators makes
 the vanishing polynomial divisible by Z_H (the verifier identity holds at a random point), a single changed wire on a row
 of each gate kind breaks it; PoseidonGate rows reproduce the permutation; and the naive partial rounds the restatement
 uses give the constraint values of upstream's factored form for ARBITRARY wires.
 GPU tier: bsx_poseidon_gate_witness equals the oracle's generator, bsx_quotient_values equals the oracle's quotient values
-word for word with all eight gate kinds (satisfying and random wires), and whole device proofs are accepted by the
+word for word with all thirteen gate kinds (satisfying and random wires), and whole device proofs are accepted by the
 verifier restatement (which evaluates the gates over the extension field)."""
 import os
 import sys
@@ -20,6 +22,7 @@ import __graft_entry__ as G
 from test_quotient import _challenges, _device_commitments, _identity_holds, _oracle_commitments, _pis_and_circuit
 
 POSEIDON, ARITH_EXT, MUL_EXT, BASE_SUM = 4, 5, 6, 7
+EXPONENTIATION, REDUCING, REDUCING_EXT, RANDOM_ACCESS, POSEIDON_MDS = 8, 9, 10, 11, 12
 
 
 @pytest.fixture(scope="module")
@@ -77,19 +80,29 @@ def test_naive_partial_rounds_give_the_factored_forms_constraints_for_any_wires(
     assert naive == fast and s == t
 
 
-@pytest.mark.parametrize("degree_bits,kw", [(5, {}), (7, {}), (6, dict(num_wires=40, num_routed_wires=24, num_ops=5))])
+@pytest.mark.parametrize("degree_bits,kw", [(6, {}), (8, {}), (6, dict(num_wires=40, num_routed_wires=24, num_ops=5))])
 def test_oracle_identity_with_every_gate_kind(pkg, oracle, degree_bits, kw):
     sc = pkg.synthetic_circuit(degree_bits, seed=13, gate_set="all", poseidon_fill=oracle.poseidon_gate_fill, **kw)
     c = sc.circuit
     kinds = sorted(g.kind for g in c.gates)
-    assert kinds == ([0, 1, 2, 3, 4, 5, 6, 7] if c.num_wires >= 135 else [0, 1, 2, 3, 5, 6, 7])
-    assert c.num_selectors == 2 and c.num_gate_constraints == (123 if c.num_wires >= 135 else 33)
+    big = c.num_wires >= 135
+    assert kinds == (list(range(13)) if big else [0, 1, 2, 3, 5, 6, 7, 8, 9, 10, 11])  # 40 wires: no Poseidon / PoseidonMds
+    assert c.num_selectors == 3 and c.num_gate_constraints == (123 if big else 33)
+    for g in c.gates:  # a run of rows of every kind
+        assert (sc.constants[g.selector_index] == g.row).any(), g
     betas, gammas, alphas = _challenges(31, c.num_challenges)
     assert _identity_holds(oracle, sc, betas, gammas, alphas) == (True, True)
     # one wire of one row of each kind: (kind, wire); the Poseidon ones hit a delta, a partial-round and a last-round S-box wire
-    tampers = [(BASE_SUM, 0), (BASE_SUM, 5), (ARITH_EXT, 6), (ARITH_EXT, 1), (MUL_EXT, 5), (MUL_EXT, 2)]
-    if c.num_wires >= 135:
-        tampers += [(POSEIDON, 3), (POSEIDON, 24), (POSEIDON, 26), (POSEIDON, 40), (POSEIDON, 70), (POSEIDON, 100), (POSEIDON, 13)]
+    ra = next(g.param for g in c.gates if g.kind == RANDOM_ACCESS)
+    ra_bit0 = (2 + (1 << (ra & 0xFF))) * ((ra >> 8) & 0xFF) + (ra >> 16)
+    n_exp = next(g.param for g in c.gates if g.kind == EXPONENTIATION)
+    tampers = [(BASE_SUM, 0), (BASE_SUM, 5), (ARITH_EXT, 6), (ARITH_EXT, 1), (MUL_EXT, 5), (MUL_EXT, 2),
+               (EXPONENTIATION, 0), (EXPONENTIATION, 1 + n_exp), (EXPONENTIATION, 2 + n_exp + 3), (REDUCING, 2), (REDUCING, 7),
+               (REDUCING, 0), (REDUCING_EXT, 5), (REDUCING_EXT, 9), (RANDOM_ACCESS, 0), (RANDOM_ACCESS, 1),
+               (RANDOM_ACCESS, ra_bit0 + 1), (RANDOM_ACCESS, ra_bit0 - 1)]
+    if big:
+        tampers += [(POSEIDON, 3), (POSEIDON, 24), (POSEIDON, 26), (POSEIDON, 40), (POSEIDON, 70), (POSEIDON, 100), (POSEIDON, 13),
+                    (POSEIDON_MDS, 5), (POSEIDON_MDS, 30)]
     for kind, wire in tampers:
         row = _row_of(sc, kind)
         keep = sc.wires[wire, row]
@@ -101,13 +114,30 @@ def test_oracle_identity_with_every_gate_kind(pkg, oracle, degree_bits, kw):
 
 def test_base_sum_limbs_must_be_bits(pkg, oracle):
     """a limb of 2 with the sum adjusted passes the sum constraint and fails limb (limb - 1)"""
-    sc = pkg.synthetic_circuit(5, seed=2, gate_set="all", poseidon_fill=oracle.poseidon_gate_fill)
+    sc = pkg.synthetic_circuit(6, seed=2, gate_set="all", poseidon_fill=oracle.poseidon_gate_fill)
     betas, gammas, alphas = _challenges(3, 2)
     row = _row_of(sc, BASE_SUM)
     old = int(sc.wires[3, row])
     sc.wires[3, row] = 2
     sc.wires[0, row] = (int(sc.wires[0, row]) + (2 - old) * 4) % P
     assert not _identity_holds(oracle, sc, betas, gammas, alphas)[0]
+
+
+def test_random_access_bits_must_match_the_index(pkg, oracle):
+    """the claimed element of another index with the bits left alone fails; with index and bits changed together it passes"""
+    sc = pkg.synthetic_circuit(6, seed=4, gate_set="all", poseidon_fill=oracle.poseidon_gate_fill)
+    betas, gammas, alphas = _challenges(4, 2)
+    g = next(g for g in sc.circuit.gates if g.kind == RANDOM_ACCESS)
+    bits, copies, extra = g.param & 0xFF, (g.param >> 8) & 0xFF, g.param >> 16
+    row, vec = _row_of(sc, RANDOM_ACCESS), 1 << bits
+    idx = int(sc.wires[0, row])
+    other = (idx + 1) % vec
+    sc.wires[1, row] = sc.wires[2 + other, row]
+    assert not _identity_holds(oracle, sc, betas, gammas, alphas)[0]
+    sc.wires[0, row] = other
+    b0 = (2 + vec) * copies + extra
+    sc.wires[b0:b0 + bits, row] = [(other >> i) & 1 for i in range(bits)]
+    assert _identity_holds(oracle, sc, betas, gammas, alphas)[0]
 
 
 # ------------------------------------------------------------------------------------------ GPU tier
@@ -132,7 +162,7 @@ def test_device_poseidon_gate_witness_equals_the_oracle(ctx, oracle):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("degree_bits,kw,satisfying", [
-    (5, {}, True), (8, {}, True), (8, {}, False), (11, {}, True),
+    (6, {}, True), (8, {}, True), (8, {}, False), (11, {}, True),
     (6, dict(num_wires=40, num_routed_wires=24, num_ops=5), True), (7, dict(num_challenges=3, rate_bits=4), False)])
 def test_device_quotient_values_with_every_gate_kind(pkg, ctx, oracle, degree_bits, kw, satisfying):
     sc = pkg.synthetic_circuit(degree_bits, seed=50 + degree_bits, gate_set="all", poseidon_fill=ctx.poseidon_gate_witness, **kw)
@@ -177,7 +207,8 @@ def test_device_proof_with_every_gate_kind_is_accepted(pkg, ctx, oracle, degree_
     pw, aux = pkg.prove(ctx, sc, cfg, public_inputs)
     ok, why = plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)
     assert ok, why
-    for kind, wire in ((POSEIDON, 77), (ARITH_EXT, 7), (BASE_SUM, 2)):
+    for kind, wire in ((POSEIDON, 77), (ARITH_EXT, 7), (BASE_SUM, 2), (EXPONENTIATION, 0), (REDUCING_EXT, 3), (RANDOM_ACCESS, 1),
+                       (POSEIDON_MDS, 47)):
         row = _row_of(sc, kind)
         keep = sc.wires[wire, row]
         sc.wires[wire, row] = (int(keep) + 1) % P
