@@ -1,5 +1,5 @@
 """Quotient evaluation: plonk/prover.rs compute_quotient_polys + plonk/vanishing_poly.rs
-eval_vanishing_poly_base_batch on a synthetic circuit of the four built-in gates.
+eval_vanishing_poly_base_batch on a synthetic circuit of the four base-field gates (the other nine kinds: tests/test_gates.py).
 
 CPU tier: the oracle's restatement is checked through the property that defines it -- for a witness that satisfies
 every gate and copy constraint the vanishing polynomial is divisible by Z_H, i.e. the quotient's coefficients beyond
