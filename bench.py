@@ -476,6 +476,32 @@ def prove_arm(args, pkg, ctx, stream, rank, world, local_rank, wires_np):
                         (LOG_N, PROVE_WIDTHS[1], PROVE_WIDTHS[2], PROVE_WIDTHS[3], PROVE_WIDTHS[0])}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """What `numactl --cpunodebind` does in a deployment with one rank per GPU: run this process (and the library's copy
+    threads, which inherit the mask) on the CPUs NVML lists as local to its GPU, so that first-touch places the pinned and
+    pageable host buffers on that socket's memory.  Returns what was done for the JSON line; any failure leaves the
+    process unbound."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(local_rank)
+        bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        try:
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(bus)
+        except TypeError:
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * w + b for w, v in enumerate(words) for b in range(64) if (int(v) >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return {"bound": False, "why": "no local CPU in the allowed set"}
+        os.sched_setaffinity(0, allowed)
+        return {"bound": True, "gpu": bus, "cpus": len(allowed), "first_cpu": allowed[0]}
+    except Exception as e:  # no NVML, no permission, an old torch: measured unbound
+        return {"bound": False, "why": "%s: %s" % (type(e).__name__, str(e)[:80])}
+
+
 def gpu_arm(args, rank, world, local_rank):
     # stdout carries exactly one JSON line: whatever libraries print there (NCCL's version banner) goes to stderr
     real_stdout = os.fdopen(os.dup(1), "w")
@@ -487,6 +513,9 @@ def gpu_arm(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
+    # N > 1 only: at N = 1 the CPU baseline leg of this process wants every host core
+    numa = (bind_to_gpu_numa_node(local_rank) if world > 1 and os.environ.get("BSX_BENCH_NO_NUMA_BIND") != "1"
+            else {"bound": False, "why": "single rank" if world == 1 else "disabled"})
     ctx = pkg.Context(local_rank)  # raises without the built CUDA library or a GPU: no fallback
     stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
     n = 1 << LOG_N
@@ -619,7 +648,7 @@ def gpu_arm(args, rank, world, local_rank):
         "e2e_pageable": {"value": world * elems / (ms_pageable * 1e-3) / 1e6, "unit": "Melem/s", "ms_per_step": ms_pageable,
                          "source": "%d separately allocated pageable host vectors per commit (Vec<PolynomialValues<F>>), "
                                    "staged by host threads through a pinned ring" % N_COLS},
-        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+        "gpu_launches": int(launches), "clocks": clocks, "host_binding": numa, "roofline": roofline,
         "phases_ms": avg,
         "roofline_ntt": {
             "ifft": dict(roof(16 * elems, avg["ifft_ms"], traffic.get("ifft")), algorithmic_bytes=16 * elems),
