@@ -12,6 +12,8 @@
  *   comm <G> <same_cap> <same_rows_paths> <same_proof>   the same commit and proof through bsx_comm_create with G ranks
  *                                      emulated on device 0 (bsx_sharded_from_values / bsx_sharded_prove_openings)
  *   fribytes <len> <fnv64>             bsx_fri_proof_bytes of that proof; layout <total_words> from bsx_fri_proof_layout
+ *   qv <log_n> <fnv64> <first> <last>  bsx_quotient_values of a thirteen-kind gate table over three commitments of SplitMix columns
+ *   pgw <2 x 135 words>                bsx_poseidon_gate_witness on two rows (swap 0 and 1)
  * tests/test_gpu_c_abi.py recomputes every record with the oracle. */
 #include <inttypes.h>
 #include <stdio.h>
@@ -221,6 +223,46 @@ int main(int argc, char **argv) {
         for (size_t i = 0; i < len; i++) fnv = (fnv ^ bytes[i]) * 0x100000001B3ULL;
         printf("fribytes %zu %016" PRIx64 " %" PRIu64 " %" PRIu64 "\n", len, fnv, lay.total_words, proof[lay.pow_witness_offset]);
         free(bytes);
+    }
+
+    /* quotient evaluation with a thirteen-kind gate table (three selector groups) over random committed columns, and two
+     * PoseidonGate rows from the device generator */
+    {
+        const int qn = log_n < 7 ? log_n : 7, nc = 2, routed = 80, wires_w = 135, consts = 5, chunks = 10;
+        const size_t rows = (size_t)1 << qn;
+        bsx_gate gates[13] = {{BSX_GATE_NOOP, 0, 0, 0, 0, 6}, {BSX_GATE_CONSTANT, 2, 1, 0, 0, 6}, {BSX_GATE_PUBLIC_INPUT, 0, 2, 0, 0, 6},
+                              {BSX_GATE_POSEIDON_MDS, 0, 3, 0, 0, 6}, {BSX_GATE_BASE_SUM, 32, 4, 0, 0, 6}, {BSX_GATE_REDUCING, 43, 5, 0, 0, 6},
+                              {BSX_GATE_REDUCING_EXTENSION, 32, 6, 1, 6, 11}, {BSX_GATE_ARITHMETIC, 20, 7, 1, 6, 11},
+                              {BSX_GATE_ARITHMETIC_EXTENSION, 10, 8, 1, 6, 11}, {BSX_GATE_MUL_EXTENSION, 13, 9, 1, 6, 11},
+                              {BSX_GATE_EXPONENTIATION, 66, 10, 1, 6, 11}, {BSX_GATE_RANDOM_ACCESS, 4 | 4 << 8 | 2 << 16, 11, 2, 11, 13},
+                              {BSX_GATE_POSEIDON, 0, 12, 2, 11, 13}};
+        uint64_t k_is[80];
+        for (int j = 0; j < routed; j++) k_is[j] = splitmix(seed + 400, (uint64_t)j);
+        bsx_circuit circ = {qn, 3, 8, nc, wires_w, routed, consts, 3, chunks - 1, 123, 13, gates, k_is};
+        const int widths[3] = {consts + routed, wires_w, nc * chunks};
+        bsx_batch *b3[3] = {NULL, NULL, NULL};
+        for (int k = 0; k < 3; k++) {
+            uint64_t *col = malloc(sizeof(uint64_t) * rows * (size_t)widths[k]);
+            for (size_t i = 0; i < rows * (size_t)widths[k]; i++) col[i] = splitmix(seed + 500 + (uint64_t)k, i);
+            CHECK(ctx, bsx_batch_from_values(ctx, col, BSX_HOST, qn, widths[k], 3, 0, 0, NULL, &b3[k], NULL));
+            free(col);
+        }
+        const uint64_t pih[4] = {seed % P, 1, 2, 3}, betas[2] = {seed % P + 6, seed % P + 7}, gammas[2] = {seed % P + 8, seed % P + 9},
+                       alphas[2] = {seed % P + 10, seed % P + 11};
+        const size_t qwords = (size_t)nc << (qn + 3);
+        uint64_t *qv = malloc(sizeof(uint64_t) * qwords);
+        CHECK(ctx, bsx_quotient_values(ctx, &circ, b3[0], b3[1], b3[2], pih, betas, gammas, alphas, qv, BSX_HOST));
+        uint64_t fnv = 0;
+        for (size_t i = 0; i < qwords; i++) fnv = (fnv * 0x100000001B3ULL) ^ qv[i];
+        printf("qv %d %016" PRIx64 " %016" PRIx64 " %016" PRIx64 "\n", qn, fnv, qv[0], qv[qwords - 1]);
+        free(qv);
+        for (int k = 0; k < 3; k++) bsx_batch_free(b3[k]);
+        uint64_t pg[2 * 135];
+        for (int i = 0; i < 2 * 135; i++) pg[i] = splitmix(seed + 600, (uint64_t)i);
+        pg[24] = 0;
+        pg[135 + 24] = 1;
+        CHECK(ctx, bsx_poseidon_gate_witness(ctx, pg, BSX_HOST, 2));
+        print_words("pgw", -1, pg, 2 * 135);
     }
 
     /* misuse is reported, not fatal: upstream panics with this message */
