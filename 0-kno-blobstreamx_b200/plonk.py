@@ -190,7 +190,7 @@ def _all_gates(num_wires, num_routed_wires, num_ops, with_poseidon):
         ra_bits -= 1
     vec = 1 << ra_bits
     ra_copies = min(num_routed_wires // (2 + vec), num_wires // (2 + vec + ra_bits))
-    ra_extra = min(num_routed_wires - (2 + vec) * ra_copies, 2)
+    ra_extra = max(0, min(num_routed_wires - (2 + vec) * ra_copies, 2, num_wires - (2 + vec + ra_bits) * ra_copies))
     groups = [
         [(GATE_NOOP, 0), (GATE_CONSTANT, 2), (GATE_PUBLIC_INPUT, 0), (GATE_POSEIDON_MDS, 0),
          (GATE_BASE_SUM, min(32, num_wires - 1)), (GATE_REDUCING, min(num_routed_wires - 6, (num_wires - 4) // 3))],

@@ -184,6 +184,36 @@ def test_device_quotient_values_with_every_gate_kind(pkg, ctx, oracle, degree_bi
 
 
 @pytest.mark.gpu
+def test_device_quotient_over_drawn_gate_parameters(pkg, ctx, oracle):
+    """`hypothesis` draws the wire counts, from which the gates take their parameters (operations per extension gate,
+    power bits, coefficients, limbs, the RandomAccess bits / copies / extra constants; PoseidonMds and Poseidon drop out
+    below 48 / 135 wires), the challenge count and whether the witness satisfies the circuit."""
+    from hypothesis import HealthCheck, given, settings, strategies as st
+
+    @settings(max_examples=25, deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
+    @given(routed=st.integers(8, 80), extra_wires=st.integers(0, 60), ops=st.integers(1, 20), num_challenges=st.integers(1, 4),
+           satisfying=st.booleans(), seed=st.integers(0, 2**20))
+    def run(routed, extra_wires, ops, num_challenges, satisfying, seed):
+        sc = pkg.synthetic_circuit(6, seed=seed, gate_set="all", poseidon_fill=ctx.poseidon_gate_witness, num_wires=routed + extra_wires,
+                                   num_routed_wires=routed, num_ops=max(1, min(routed // 4, ops)), num_challenges=num_challenges)
+        c = sc.circuit
+        if not satisfying:
+            sc.wires = splitmix_field(seed + 1, sc.wires.shape)
+        betas, gammas, alphas = _challenges(seed, num_challenges)
+        ob = _oracle_commitments(oracle, sc, betas, gammas)
+        gb = _device_commitments(pkg, ctx, sc, betas, gammas)
+        try:
+            want = oracle.quotient_values(c.as_dict(), ob[0], ob[1], ob[2], sc.public_inputs_hash, betas, gammas, alphas)
+            got = pkg.quotient_values(ctx, c, gb[0], gb[1], gb[2], sc.public_inputs_hash, betas, gammas, alphas)
+            assert got.shape == want.shape and (got == want).all(), [(g.kind, g.param) for g in c.gates]
+        finally:
+            for b in gb:
+                b.close()
+
+    run()
+
+
+@pytest.mark.gpu
 def test_poseidon_gate_needs_135_wires(pkg, ctx):
     sc = pkg.synthetic_circuit(5, seed=2, num_wires=40, num_routed_wires=24, num_ops=5)
     c = sc.circuit
