@@ -68,6 +68,7 @@ struct NttKParams {
     int pitch;               // words between tile columns in shared memory
     NttGroups groups;
     int n_dest, dest_lc;     // row-sharded output (see NttPlan)
+    int dest_tma;            // the destination slabs have tensor maps (ntt_pass_lo_tma)
     u64 *dest[BSX_MAX_RANKS];
 };
 
@@ -501,8 +502,18 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
 // scaled or re-routed to another rank's slab.
 __device__ __forceinline__ u32 ntt_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
 
+// one tensor map per destination slab of a row-sharded output (NTT_LO_TMA_DEST): a tile of pass LO is 2^(b + w_log)
+// consecutive leaves of one column, which lie inside ONE rank's slab, contiguously
+struct NttDestMaps {
+    CUtensorMap m[BSX_MAX_RANKS];
+};
+#ifndef NTT_LO_TMA_DEST
+#define NTT_LO_TMA_DEST 1
+#endif
+
 template <bool INV, bool FULLTW>
-__global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo_tma(const __grid_constant__ CUtensorMap tmap, NttKParams P) {
+__global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo_tma(const __grid_constant__ CUtensorMap tmap,
+                                                                  const __grid_constant__ NttDestMaps dmaps, NttKParams P) {
     extern __shared__ __align__(1024) u64 sm_tma[];
     const int b = P.b, w_log = P.w_log;
     const int S = 1 << b;
@@ -539,16 +550,27 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo_tma(const __grid_c
     }
     dif_tile<INV, FULLTW, true>(sm, tws, b, w_log, S, P.groups);
     const bool scale = P.scale != 1 && !P.post_full;
-    if (!scale && P.n_dest == 0) {
+    // row-sharded output: the tile goes to the slab of rank l0 >> dest_lc (peer memory over NVLink, or a local send
+    // buffer), at column blockIdx.y of that slab; bulk store only when the tile lies inside one slab
+    const bool dest_tma = NTT_LO_TMA_DEST && P.n_dest != 0 && P.dest_tma && P.dest_lc >= b + w_log;
+    if (!scale && (P.n_dest == 0 || dest_tma)) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
         if (threadIdx.x == 0) {
+            const CUtensorMap *mp = &tmap;
+            int line_out = line0;
+            if (P.n_dest != 0) {
+                mp = &dmaps.m[l0 >> P.dest_lc];
+                line_out = (int)((((size_t)blockIdx.y << P.dest_lc) + (l0 & (((size_t)1 << P.dest_lc) - 1))) >> 4);
+            }
             for (int c = 0; c < n_lines; c += box)
-                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&tmap),
-                             "r"(0), "r"(line0 + c), "r"(ntt_smem_addr(sm + ((size_t)c << 4)))
+                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(mp),
+                             "r"(0), "r"(line_out + c), "r"(ntt_smem_addr(sm + ((size_t)c << 4)))
                              : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            // local output: the tile only has to stay until it has been read; another rank's slab: until the writes are done
+            if (P.n_dest != 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+            else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         }
         return;
     }
@@ -685,6 +707,7 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
     P.r_log = r_log;
     P.post_full = plan.b > 0 ? plan.post_full : nullptr;
     P.n_dest = plan.n_dest;
+    P.dest_tma = 0;
     P.dest_lc = plan.dest_lc;
     for (int i = 0; i < BSX_MAX_RANKS; i++) P.dest[i] = i < plan.n_dest ? plan.dest[i] : nullptr;
     // pass HI: tile of 2^a points x W adjacent i0
@@ -724,15 +747,25 @@ void launch_ntt(const NttTables &T, const NttPlan &plan, const u64 *src, size_t 
 #if NTT_LO_TMA
         CUtensorMap tmap;
         const size_t span = (size_t)(n_cols - 1) * dst_stride + ((size_t)plan.n_cosets << plan.log_n);
-        if (plan.b >= 7 && threads == NTT_THREADS && (dst_stride & 15) == 0 &&
-            ntt_lines_map(&tmap, dst, span, (int)((n_el >> 4) < 256 ? (n_el >> 4) : 256))) {
+        const int box = (int)((n_el >> 4) < 256 ? (n_el >> 4) : 256);
+        if (plan.b >= 7 && threads == NTT_THREADS && (dst_stride & 15) == 0 && ntt_lines_map(&tmap, dst, span, box)) {
             size_t smem_t = sizeof(u64) * (n_el + ((size_t)1 << plan.b) / (full ? 1 : 2) + 2);
+            static NttDestMaps dmaps;  // only read by the kernel when P.dest_tma is set; copied into the launch
+            NttDestMaps dm = dmaps;
+            P.dest_tma = 0;
+#if NTT_LO_TMA_DEST
+            if (plan.n_dest > 0 && plan.dest_lc >= plan.b + w_log) {
+                bool ok = true;  // slab of rank d: n_cols columns of 2^dest_lc leaves
+                for (int d = 0; d < plan.n_dest && ok; d++) ok = ntt_lines_map(&dm.m[d], plan.dest[d], (size_t)n_cols << plan.dest_lc, box);
+                P.dest_tma = ok ? 1 : 0;
+            }
+#endif
             if (plan.inverse) {
-                if (full) ntt_pass_lo_tma<true, true><<<grid, threads, smem_t, st>>>(tmap, P);
-                else ntt_pass_lo_tma<true, false><<<grid, threads, smem_t, st>>>(tmap, P);
+                if (full) ntt_pass_lo_tma<true, true><<<grid, threads, smem_t, st>>>(tmap, dm, P);
+                else ntt_pass_lo_tma<true, false><<<grid, threads, smem_t, st>>>(tmap, dm, P);
             } else {
-                if (full) ntt_pass_lo_tma<false, true><<<grid, threads, smem_t, st>>>(tmap, P);
-                else ntt_pass_lo_tma<false, false><<<grid, threads, smem_t, st>>>(tmap, P);
+                if (full) ntt_pass_lo_tma<false, true><<<grid, threads, smem_t, st>>>(tmap, dm, P);
+                else ntt_pass_lo_tma<false, false><<<grid, threads, smem_t, st>>>(tmap, dm, P);
             }
             return;
         }
