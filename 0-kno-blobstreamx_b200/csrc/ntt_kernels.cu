@@ -498,8 +498,8 @@ __global__ void __launch_bounds__(NTT_THREADS, 3) ntt_pass_lo(NttKParams P) {
 // for a driver without cuTensorMapEncodeTiled): the tile is one contiguous run
 // of 2^(b + w_log) words, described to the TMA unit as lines of 16 words; `cp.async.bulk.tensor.2d` brings it in as boxes
 // of 256 lines with the 128-byte hardware swizzle (no pad words; dif_tile<.., XSW>), one thread arms the mbarrier and
-// issues the copies, the others fill the twiddle table meanwhile.  The result goes back the same way unless it has to be
-// scaled or re-routed to another rank's slab.
+// issues the copies, the others fill the twiddle table meanwhile.  The result goes back the same way -- into the local
+// buffer, or into the slab of the rank that owns these leaves (NttDestMaps) -- unless it has to be scaled on the way.
 __device__ __forceinline__ u32 ntt_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
 
 // one tensor map per destination slab of a row-sharded output (NTT_LO_TMA_DEST): a tile of pass LO is 2^(b + w_log)
