@@ -51,6 +51,7 @@ from .plonk import (  # noqa: F401
     GATE_ARITHMETIC_EXTENSION,
     GATE_BASE_SUM,
     GATE_CONSTANT,
+    GATE_COSET_INTERPOLATION,
     GATE_EXPONENTIATION,
     GATE_MUL_EXTENSION,
     GATE_NOOP,

@@ -4,7 +4,8 @@
 // `ZeroPolyOnCoset`, `reduce_with_powers_multi`, plonk/vanishing_poly.rs `check_partial_products`, gates/gate.rs
 // `compute_filter`) for circuits made of NoopGate, ConstantGate, PublicInputGate, ArithmeticGate, BaseSumGate<2>,
 // ArithmeticExtensionGate<2>, MulExtensionGate<2>, ExponentiationGate, ReducingGate<2>, ReducingExtensionGate<2>,
-// RandomAccessGate<2> (up to 4 bits), PoseidonMdsGate<2> (this kernel) and PoseidonGate (a second kernel that adds its share).
+// RandomAccessGate<2> (up to 4 bits), PoseidonMdsGate<2>, CosetInterpolationGate<2> (this kernel) and PoseidonGate (a second
+// kernel that adds its share).
 //
 // Upstream walks the quotient domain in batches of 32 points and gathers, per point i, the rows
 // get_lde_values(i, step) of the constants+sigmas, wires and Zs commitments -- on the CPU that means the whole LDE
@@ -35,6 +36,7 @@ struct QvParams {
     const u64 *k_is;
     const u64 *apow;  // [nc][n_terms]: alpha_a^j
     const u64 *zh;    // [2^qdb] Z_H on the coset, then [2^qdb] its inverses
+    const u64 *ci_tab;  // CosetInterpolationGate: the subgroup of order 2^bits, then its barycentric weights
     u64 betas[QV_MAX_CHALLENGES], gammas[QV_MAX_CHALLENGES], pi_hash[4];
     u64 n_field;      // F::from_canonical_usize(n)
     PowTable tw;      // powers of omega_{2^log_q}
@@ -270,6 +272,46 @@ __global__ void __launch_bounds__(256, 2) quotient_values_kernel(const QvParams 
             for (int t = 0; t < extra; t++)
                 gfold(gl_sub_c(__ldg(gconst + (size_t)t * P.stride),
                                                         __ldg(wrow + (size_t)((2 + vec) * copies + t) * P.stride)), slot++);
+        } else if (g.kind == BSX_GATE_COSET_INTERPOLATION) {
+            // wires: shift 0, values 1 + 2 q, evaluation point, evaluation value, intermediate evals, intermediate prods,
+            // shifted evaluation point.  evaluation_point - shifted_point * shift; the barycentric sum over the subgroup in
+            // chunks (first `degree` points, then degree - 1 each), (eval, prod) <- (eval (x - x_q) + v_q w_q prod,
+            // prod (x - x_q)) in F_p[X]/(X^2 - 7), pinned to wires after every chunk; evaluation_value - the last eval
+            const int bits = g.param & 0xFF, degree = g.param >> 8, np = 1 << bits, ni = (np - 2) / (degree - 1);
+            const int ep = 1 + 2 * np, ev = ep + 2, im = ev + 2, sp = im + 4 * ni;
+            const u64 *dom = P.ci_tab, *wts = P.ci_tab + np;
+            const u64 shift = __ldg(wrow), x0 = __ldg(wrow + (size_t)sp * P.stride), x1 = __ldg(wrow + (size_t)(sp + 1) * P.stride);
+            int slot = P.gate_base;
+            gfold(gl_sub_c(__ldg(wrow + (size_t)ep * P.stride), gl_canon_fast(gl_mul_lazy(x0, shift))), slot++);
+            gfold(gl_sub_c(__ldg(wrow + (size_t)(ep + 1) * P.stride), gl_canon_fast(gl_mul_lazy(x1, shift))), slot++);
+            u64 e0 = 0, e1 = 0, p0 = 1, p1 = 0;  // canonical between the steps
+            int first = 0, last = degree;
+            for (int i = 0; i <= ni; i++) {
+                for (int q = first; q < last; q++) {
+                    const u64 w = __ldg(wts + q);
+                    const u64 v0 = gl_mul_lazy(__ldg(wrow + (size_t)(1 + 2 * q) * P.stride), w);
+                    const u64 v1 = gl_mul_lazy(__ldg(wrow + (size_t)(2 + 2 * q) * P.stride), w);
+                    const u64 t0 = gl_sub_c(x0, __ldg(dom + q)), t1 = x1;
+                    // (a0 + a1 X)(b0 + b1 X) = a0 b0 + 7 a1 b1 + (a0 b1 + a1 b0) X, for eval * term + val * prod and prod * term
+                    const u64 n0 = gl_mul_add_lazy(e0, t0, gl_mul_add_lazy(v0, p0, gl_mul_lazy(gl_add_lazy_canon(gl_mul_lazy(e1, t1), gl_canon_fast(gl_mul_lazy(v1, p1))), 7)));
+                    const u64 n1 = gl_mul_add_lazy(e0, t1, gl_mul_add_lazy(e1, t0, gl_mul_add_lazy(v0, p1, gl_mul_lazy(v1, p0))));
+                    const u64 q0 = gl_mul_add_lazy(p0, t0, gl_mul_lazy(gl_mul_lazy(p1, t1), 7));
+                    const u64 q1 = gl_mul_add_lazy(p0, t1, gl_mul_lazy(p1, t0));
+                    e0 = gl_canon_fast(n0), e1 = gl_canon_fast(n1), p0 = gl_canon_fast(q0), p1 = gl_canon_fast(q1);
+                }
+                if (i == ni) break;
+                const u64 *ie = wrow + (size_t)(im + 2 * i) * P.stride, *ip = wrow + (size_t)(im + 2 * (ni + i)) * P.stride;
+                const u64 ie0 = __ldg(ie), ie1 = __ldg(ie + P.stride), ip0 = __ldg(ip), ip1 = __ldg(ip + P.stride);
+                gfold(gl_sub_c(ie0, e0), slot++);
+                gfold(gl_sub_c(ie1, e1), slot++);
+                gfold(gl_sub_c(ip0, p0), slot++);
+                gfold(gl_sub_c(ip1, p1), slot++);
+                e0 = ie0, e1 = ie1, p0 = ip0, p1 = ip1;
+                first = 1 + (degree - 1) * (i + 1);
+                last = min(first + degree - 1, np);
+            }
+            gfold(gl_sub_c(__ldg(wrow + (size_t)ev * P.stride), e0), slot++);
+            gfold(gl_sub_c(__ldg(wrow + (size_t)(ev + 1) * P.stride), e1), slot++);
         } else if (g.kind == BSX_GATE_POSEIDON_MDS) {
             // output_r - (sum_i CIRC[i] input_{(i + r) % 12} + 8 input_0 [r == 0]), the two coordinates of the algebra
             // elements separately: the multiplication-free layer of the permutation with zero constants
@@ -499,6 +541,10 @@ static int gate_constraints(const bsx_gate &g) {
             return bits < 1 || bits > 4 || copies < 1 || extra < 0 ? -1 : copies * (bits + 2) + extra;
         }
         case BSX_GATE_POSEIDON_MDS: return 24;
+        case BSX_GATE_COSET_INTERPOLATION: {
+            const int bits = g.param & 0xFF, degree = g.param >> 8;
+            return bits < 1 || bits > 8 || degree < 2 || degree > (1 << bits) ? -1 : 2 * (2 + 2 * (((1 << bits) - 2) / (degree - 1)));
+        }
         default: return -1;
     }
 }
@@ -537,6 +583,7 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
     }
     if (c->num_selectors < 0 || c->num_selectors > c->num_constants) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "bad selector count");
     const int n_gate_consts = c->num_constants - c->num_selectors;
+    int ci_gate = -1;
     for (int g = 0; g < c->n_gates; g++) {
         const bsx_gate &G = c->gates[g];
         const int k = gate_constraints(G);
@@ -557,6 +604,11 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
             ok = (2 + (1 << bits)) * copies + extra + copies * bits <= c->num_wires && extra <= n_gate_consts;
         }
         if (ok && G.kind == BSX_GATE_POSEIDON_MDS) ok = c->num_wires >= 48;
+        if (ok && G.kind == BSX_GATE_COSET_INTERPOLATION) {
+            const int bits = G.param & 0xFF, degree = G.param >> 8, np = 1 << bits;
+            ok = 1 + 2 * np + 6 + 4 * ((np - 2) / (degree - 1)) <= c->num_wires && ci_gate < 0;  // one such gate per circuit
+            ci_gate = g;
+        }
         if (!ok) return bsx_fail(ctx, BSX_ERR_INVALID_ARG, "gate %d (kind %d, param %d) does not fit the circuit", g, G.kind, G.param);
     }
     QvParams P;
@@ -567,7 +619,8 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
     CU(ctx, cudaSetDevice(ctx->device));
     // host-side tables: alpha powers, Z_H on the coset and its inverses (ZeroPolyOnCoset::new), k_is, gates
     const int rate = 1 << qdb;
-    std::vector<u64> h((size_t)nc * P.n_terms + 2 * rate + c->num_routed_wires);
+    const int ci_np = ci_gate >= 0 ? 1 << (c->gates[ci_gate].param & 0xFF) : 0;
+    std::vector<u64> h((size_t)nc * P.n_terms + 2 * rate + c->num_routed_wires + 2 * (size_t)ci_np);
     for (int a = 0; a < nc; a++) {
         u64 pw = 1, al = alphas[a] % GL_P;
         for (int j = 0; j < P.n_terms; j++) {
@@ -588,6 +641,18 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
         xv = gl_host_mul(xv, v);
     }
     for (int j = 0; j < c->num_routed_wires; j++) zh[2 * rate + j] = c->k_is[j] % GL_P;
+    if (ci_np) {  // F::two_adic_subgroup(bits) and field/interpolation.rs barycentric_weights on it
+        u64 *dom = zh + 2 * rate + c->num_routed_wires, *wts = dom + ci_np;
+        const u64 gen = gl_host_root(c->gates[ci_gate].param & 0xFF);
+        u64 xg = 1;
+        for (int k = 0; k < ci_np; k++, xg = gl_host_mul(xg, gen)) dom[k] = xg;
+        for (int k = 0; k < ci_np; k++) {
+            u64 pr = 1;
+            for (int j = 0; j < ci_np; j++)
+                if (j != k) pr = gl_host_mul(pr, dom[k] >= dom[j] ? dom[k] - dom[j] : dom[k] + (GL_P - dom[j]));
+            wts[k] = gl_host_inv(pr);
+        }
+    }
     u64 *tab;
     bsx_gate *gates_dev = nullptr;
     TRY(bsx_alloc(ctx, &tab, h.size()));
@@ -614,6 +679,7 @@ static int quotient_values_device(bsx_ctx *ctx, const bsx_circuit *c, bsx_batch 
     P.apow = tab;
     P.zh = tab + (size_t)nc * P.n_terms;
     P.k_is = P.zh + 2 * rate;
+    P.ci_tab = P.k_is + c->num_routed_wires;
     for (int k = 0; k < QV_MAX_CHALLENGES; k++) {
         P.betas[k] = k < nc ? betas[k] % GL_P : 0;
         P.gammas[k] = k < nc ? gammas[k] % GL_P : 0;

@@ -19,6 +19,7 @@ GATE_POSEIDON, GATE_ARITHMETIC_EXTENSION, GATE_MUL_EXTENSION, GATE_BASE_SUM = 4,
 # gates/reducing_extension.rs ReducingExtensionGate<2> (param = num_coeffs), gates/random_access.rs RandomAccessGate<2>
 # (param = bits | num_copies << 8 | num_extra_constants << 16), gates/poseidon_mds.rs PoseidonMdsGate<2>
 GATE_EXPONENTIATION, GATE_REDUCING, GATE_REDUCING_EXTENSION, GATE_RANDOM_ACCESS, GATE_POSEIDON_MDS = 8, 9, 10, 11, 12
+GATE_COSET_INTERPOLATION = 13  # gates/coset_interpolation.rs CosetInterpolationGate<2>: param = subgroup_bits | degree << 8
 POSEIDON_GATE_WIRES, POSEIDON_GATE_CONSTRAINTS = 135, 123
 
 
@@ -50,7 +51,8 @@ class Gate:
                 GATE_MUL_EXTENSION: 2 * self.param, GATE_BASE_SUM: 1 + self.param,
                 GATE_EXPONENTIATION: self.param + 1, GATE_REDUCING: 2 * self.param, GATE_REDUCING_EXTENSION: 2 * self.param,
                 GATE_RANDOM_ACCESS: ((self.param >> 8) & 0xFF) * ((self.param & 0xFF) + 2) + (self.param >> 16),
-                GATE_POSEIDON_MDS: 24}[self.kind]
+                GATE_POSEIDON_MDS: 24,
+                GATE_COSET_INTERPOLATION: 2 * (2 + 2 * (((1 << (self.param & 0xFF)) - 2) // max(1, (self.param >> 8) - 1)))}[self.kind]
 
 
 @dataclass
@@ -191,16 +193,22 @@ def _all_gates(num_wires, num_routed_wires, num_ops, with_poseidon):
     vec = 1 << ra_bits
     ra_copies = min(num_routed_wires // (2 + vec), num_wires // (2 + vec + ra_bits))
     ra_extra = max(0, min(num_routed_wires - (2 + vec) * ra_copies, 2, num_wires - (2 + vec + ra_bits) * ra_copies))
+    # CosetInterpolationGate::with_max_degree(subgroup_bits, 8): the smallest degree with as few intermediates as degree 8
+    ci_bits = 4 if (num_wires >= 47 and num_routed_wires >= 37) else 2 if (num_wires >= 15 and num_routed_wires >= 13) else 0
+    n_int = lambda d: ((1 << ci_bits) - 2) // (d - 1)
+    ci_degree = min((d for d in range(2, min(8, 1 << ci_bits) + 1) if n_int(d) == n_int(min(8, 1 << ci_bits))), default=0) if ci_bits else 0
     groups = [
         [(GATE_NOOP, 0), (GATE_CONSTANT, 2), (GATE_PUBLIC_INPUT, 0), (GATE_POSEIDON_MDS, 0),
          (GATE_BASE_SUM, min(32, num_wires - 1)), (GATE_REDUCING, min(num_routed_wires - 6, (num_wires - 4) // 3))],
         [(GATE_REDUCING_EXTENSION, min((num_routed_wires - 6) // 2, (num_wires - 4) // 4)), (GATE_ARITHMETIC, num_ops),
          (GATE_ARITHMETIC_EXTENSION, num_routed_wires // 8), (GATE_MUL_EXTENSION, num_routed_wires // 6),
          (GATE_EXPONENTIATION, min(num_routed_wires - 3, (num_wires - 2) // 2))],
-        [(GATE_RANDOM_ACCESS, ra_bits | ra_copies << 8 | ra_extra << 16), (GATE_POSEIDON, 0)]]
+        [(GATE_RANDOM_ACCESS, ra_bits | ra_copies << 8 | ra_extra << 16), (GATE_COSET_INTERPOLATION, ci_bits | ci_degree << 8)],
+        [(GATE_POSEIDON, 0)]]
     fits = lambda k, p: not ((k == GATE_POSEIDON and not (with_poseidon and num_wires >= POSEIDON_GATE_WIRES)) or
                              (k == GATE_POSEIDON_MDS and num_wires < 48) or (k == GATE_RANDOM_ACCESS and ra_copies < 1) or
-                             (k in (GATE_REDUCING, GATE_REDUCING_EXTENSION, GATE_EXPONENTIATION) and p < 1))
+                             (k in (GATE_REDUCING, GATE_REDUCING_EXTENSION, GATE_EXPONENTIATION) and p < 1) or
+                             (k == GATE_COSET_INTERPOLATION and ci_bits == 0))
     gates, row = [], 0
     for sel, grp in enumerate(groups):
         grp = [(k, p) for k, p in grp if fits(k, p)]
@@ -215,9 +223,10 @@ def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_rou
                       poseidon_fill=None, max_poseidon_rows=1 << 12):
     """A circuit with random constants, `n_copies` copy constraints between free arithmetic inputs, and a witness that
     satisfies all of it.  gate_set "basic": NoopGate / ConstantGate / PublicInputGate / ArithmeticGate rows in one selector
-    group.  "all" (degree_bits >= 6, quotient_degree_factor 8): three selector groups as gates/selectors.rs would form them
+    group.  "all" (degree_bits >= 6, quotient_degree_factor 8): four selector groups as gates/selectors.rs would form them
     for max degree 9 -- [Noop, Constant, PublicInput, PoseidonMds, BaseSum<2>, Reducing], [ReducingExtension, Arithmetic,
-    ArithmeticExtension, MulExtension, Exponentiation] and [RandomAccess, Poseidon] -- with rows of every kind;
+    ArithmeticExtension, MulExtension, Exponentiation], [RandomAccess, CosetInterpolation] and [Poseidon] -- with rows of
+    every kind;
     `poseidon_fill(rows)` completes (k, 135) PoseidonGate rows whose inputs and swap wire are set
     (Context.poseidon_gate_witness on the device; the Poseidon gate is left out when it is None or the circuit has fewer
     than 135 wires)."""
@@ -228,7 +237,7 @@ def synthetic_circuit(degree_bits, seed=1, n_copies=None, num_wires=135, num_rou
         if degree_bits < 6 or quotient_degree_factor != 8:
             raise ValueError('gate_set "all" wants degree_bits >= 6 and quotient_degree_factor 8')
         gates = _all_gates(num_wires, num_routed_wires, num_ops, poseidon_fill is not None)
-        n_sel = 3
+        n_sel = 4
         circ = CircuitDescription(degree_bits, gates, rate_bits=rate_bits, quotient_degree_factor=quotient_degree_factor,
                                   num_challenges=num_challenges, num_wires=num_wires, num_routed_wires=num_routed_wires,
                                   num_constants=n_sel + 2, num_selectors=n_sel)
@@ -358,6 +367,42 @@ def _fill_gate_rows(wires, rows_of, param_of, by_kind, c0, c1, rng, poseidon_fil
                 wires[routed + c * bits:routed + (c + 1) * bits, r] = [(idx >> i) & 1 for i in range(bits)]
             for i in range(extra):
                 wires[(2 + vec) * copies + i, r] = (c0, c1)[i][r]
+    if GATE_COSET_INTERPOLATION in by_kind:          # shift 0, values 1 + 2 i, evaluation point, value, intermediates, shifted point
+        p = param_of(GATE_COSET_INTERPOLATION)
+        bits, degree = p & 0xFF, p >> 8
+        npts = 1 << bits
+        ni = (npts - 2) // (degree - 1)
+        ep, ev, im = 1 + 2 * npts, 3 + 2 * npts, 5 + 2 * npts
+        sp = im + 4 * ni
+        gen = pow(1753635133440165772, 1 << (32 - bits), P)
+        dom = [pow(gen, i, P) for i in range(npts)]
+        wts = []
+        for i in range(npts):
+            pr = 1
+            for j in range(npts):
+                if j != i:
+                    pr = pr * (dom[i] - dom[j]) % P
+            wts.append(pow(pr, P - 2, P))
+        for r in rows_of(GATE_COSET_INTERPOLATION):
+            shift = W(0, r) or 1
+            wires[0, r] = shift
+            x = (W(sp, r), W(sp + 1, r))
+            wires[ep, r], wires[ep + 1, r] = x[0] * shift % P, x[1] * shift % P
+            ev_, pr_ = (0, 0), (1, 0)
+            first, last = 0, degree
+            for i in range(ni + 1):
+                for q in range(first, last):   # partial_interpolate
+                    val = (W(1 + 2 * q, r) * wts[q] % P, W(2 + 2 * q, r) * wts[q] % P)
+                    term = ((x[0] - dom[q]) % P, x[1])
+                    a, b = _ext_mul(ev_, term), _ext_mul(val, pr_)
+                    ev_, pr_ = ((a[0] + b[0]) % P, (a[1] + b[1]) % P), _ext_mul(pr_, term)
+                if i == ni:
+                    break
+                wires[im + 2 * i:im + 2 * i + 2, r] = ev_
+                wires[im + 2 * (ni + i):im + 2 * (ni + i) + 2, r] = pr_
+                first = 1 + (degree - 1) * (i + 1)
+                last = min(first + degree - 1, npts)
+            wires[ev:ev + 2, r] = ev_
     if GATE_POSEIDON_MDS in by_kind:                 # outputs (wires 24..47) = MDS * inputs (wires 0..23), component by component
         for r in rows_of(GATE_POSEIDON_MDS):
             for d in range(2):

@@ -301,14 +301,14 @@ def sharded_arm(args, pkg, ctx, stream, rank, world, local_rank, cap_rank0):
     return out
 
 
-PROVE_WIDTHS = (85, 135, 20, 16)  # constants (3 selectors + 2) + sigmas | wires | Zs+partial products | quotient chunks (8 x 2 challenges)
+PROVE_WIDTHS = (86, 135, 20, 16)  # constants (4 selectors + 2) + sigmas | wires | Zs+partial products | quotient chunks (8 x 2 challenges)
 
 
 def prove_circuit(pkg, gate_set="all"):
     """standard_recursion_config shape for the synthetic prove: 135 wires, 80 routed, and the gate table of a
-    recursion-style circuit in three selector groups (what gates/selectors.rs forms for max degree 9): [Noop, Constant,
+    recursion-style circuit in four selector groups (what gates/selectors.rs forms for max degree 9): [Noop, Constant,
     PublicInput, PoseidonMds, BaseSum<2>, Reducing], [ReducingExtension, Arithmetic, ArithmeticExtension, MulExtension,
-    Exponentiation], [RandomAccess(4 bits), Poseidon]; "basic": the four base-field gates only.  The committed columns
+    Exponentiation], [RandomAccess(4 bits), CosetInterpolation(4 bits, degree 6)], [Poseidon]; "basic": the four base-field gates only.  The committed columns
     are random, so the gate and permutation constraints do not vanish on H; with quotient_degree_factor = 8 = 2^3
     `trim_to_len` checks nothing (upstream's prover would not notice either), and the work per proof is exactly that of a
     satisfied circuit."""
@@ -322,8 +322,8 @@ def prove_circuit(pkg, gate_set="all"):
              g(pkg.GATE_REDUCING_EXTENSION, 32, 6, 1, 6, 11), g(pkg.GATE_ARITHMETIC, 20, 7, 1, 6, 11),
              g(pkg.GATE_ARITHMETIC_EXTENSION, 10, 8, 1, 6, 11), g(pkg.GATE_MUL_EXTENSION, 13, 9, 1, 6, 11),
              g(pkg.GATE_EXPONENTIATION, 66, 10, 1, 6, 11), g(pkg.GATE_RANDOM_ACCESS, 4 | 4 << 8 | 2 << 16, 11, 2, 11, 13),
-             g(pkg.GATE_POSEIDON, 0, 12, 2, 11, 13)]
-    return pkg.CircuitDescription(LOG_N, gates, num_constants=5, num_selectors=3)
+             g(pkg.GATE_COSET_INTERPOLATION, 4 | 6 << 8, 12, 2, 11, 13), g(pkg.GATE_POSEIDON, 0, 13, 3, 13, 14)]
+    return pkg.CircuitDescription(LOG_N, gates, num_constants=6, num_selectors=4)
 
 
 def prove_arm(args, pkg, ctx, stream, rank, world, local_rank, wires_np):
@@ -469,7 +469,7 @@ def prove_arm(args, pkg, ctx, stream, rank, world, local_rank, wires_np):
             "quotient_eval_ms": float(np.median(eval_ms[2:])) if len(eval_ms) > 2 else None,
             "fri_arity_bits": list(fp.reduction_arity_bits),
             "workload": "shape-equivalent synthetic prove, 2^%d rows: commits of %d/%d columns from host memory, the "
-                        "quotient evaluated on the device from the resident LDEs (13 gate kinds incl. PoseidonGate's 123 constraints, 3 selector groups) and "
+                        "quotient evaluated on the device from the resident LDEs (14 gate kinds incl. PoseidonGate's 123 constraints, 4 selector groups) and "
                         "committed as %d chunks (+%d columns precommitted), opening set at zeta and g*zeta, "
                         "prove_openings, ProofWithPublicInputs bytes; standard_recursion_config; random columns, "
                         "NOT a real header_range proof; one proof per GPU, replicas" %

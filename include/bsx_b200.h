@@ -435,6 +435,8 @@ int32_t bsx_partial_products_and_zs(bsx_ctx *ctx, const uint64_t *wires, const u
 #define BSX_GATE_RANDOM_ACCESS 11 /* gates/random_access.rs RandomAccessGate<2>: param = bits | num_copies << 8 |
                                    num_extra_constants << 16, bits <= 4 */
 #define BSX_GATE_POSEIDON_MDS 12 /* gates/poseidon_mds.rs PoseidonMdsGate<2>: wires 24 + 2r + d = MDS row r of wires 2i + d */
+#define BSX_GATE_COSET_INTERPOLATION 13 /* gates/coset_interpolation.rs CosetInterpolationGate<2>: param = subgroup_bits |
+                                   degree << 8; at most one per circuit */
 typedef struct bsx_gate {
     int32_t kind, param, row, selector_index, group_start, group_end;
 } bsx_gate;

@@ -161,6 +161,8 @@ int orc_partial_products_and_z(const uint64_t *wires, const uint64_t *sigmas, in
 #define ORC_GATE_RANDOM_ACCESS 11       /* gates/random_access.rs RandomAccessGate<2>: param = bits | num_copies << 8 |
                                            num_extra_constants << 16 */
 #define ORC_GATE_POSEIDON_MDS 12        /* gates/poseidon_mds.rs PoseidonMdsGate<2>: 24 inputs -> 24 outputs */
+#define ORC_GATE_COSET_INTERPOLATION 13 /* gates/coset_interpolation.rs CosetInterpolationGate<2>: param = subgroup_bits |
+                                           degree << 8 */
 typedef struct orc_gate { /* one entry of common_data.gates with its share of common_data.selectors_info */
     int32_t kind, param;
     int32_t row;                    /* index in common_data.gates: the selector value that switches it on */

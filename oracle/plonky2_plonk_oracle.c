@@ -2,9 +2,10 @@
  *   plonk/prover.rs `compute_quotient_polys` with plonk/vanishing_poly.rs `eval_vanishing_poly_base_batch`
  *   (the vanishing polynomial on the quotient coset) for circuits built from NoopGate, ConstantGate,
  *   PublicInputGate, ArithmeticGate, PoseidonGate, ArithmeticExtensionGate, MulExtensionGate, BaseSumGate<2>,
- *   ExponentiationGate, ReducingGate, ReducingExtensionGate, RandomAccessGate and PoseidonMdsGate
+ *   ExponentiationGate, ReducingGate, ReducingExtensionGate, RandomAccessGate, PoseidonMdsGate and
+ *   CosetInterpolationGate
  *   (gates/{noop,constant,public_input,arithmetic_base,poseidon,arithmetic_extension,multiplication_extension,
- *   base_sum,exponentiation,reducing,reducing_extension,random_access,poseidon_mds}.rs), and
+ *   base_sum,exponentiation,reducing,reducing_extension,random_access,poseidon_mds,coset_interpolation}.rs), and
  *   util/serialization/mod.rs `write_proof_with_public_inputs` (`ProofWithPublicInputs::to_bytes`).
  * TEST INFRASTRUCTURE ONLY; "parity unpinned" against the real prover -- see plonky2_oracle.h. */
 #include "plonky2_oracle.h"
@@ -134,6 +135,38 @@ void orc_poseidon_gate_fill(uint64_t *rows, size_t n) {
 /* F_p[X] / (X^2 - 7) on base-field pairs: vars.get_local_ext(range) in the base-field evaluation */
 static void x2_mul(const uint64_t a[2], const uint64_t b[2], uint64_t o[2]) { orc_ext_mul(a, b, o); }
 
+/* gates/coset_interpolation.rs: the subgroup of order 2^bits and field/interpolation.rs barycentric_weights on it,
+ * w_i = 1 / prod_{j != i} (x_i - x_j) */
+static void ci_tables(int bits, uint64_t *domain, uint64_t *weights) {
+    const int n = 1 << bits;
+    const uint64_t g = orc_root_of_unity(bits);
+    uint64_t x = 1;
+    for (int i = 0; i < n; i++, x = orc_mul(x, g)) domain[i] = x;
+    for (int i = 0; i < n; i++) {
+        uint64_t pr = 1;
+        for (int j = 0; j < n; j++)
+            if (j != i) pr = orc_mul(pr, orc_sub(domain[i], domain[j]));
+        weights[i] = orc_inv(pr);
+    }
+}
+/* gates/coset_interpolation.rs partial_interpolate over F_p[X]/(X^2 - 7): for the points [first, last) fold
+ * (eval, prod) <- (eval (x - x_i) + value_i w_i prod, prod (x - x_i)); value i sits at wires 1 + 2 i */
+static void ci_partial(const uint64_t *domain, const uint64_t *weights, const uint64_t *wires, int first, int last,
+                       const uint64_t x[2], uint64_t eval[2], uint64_t prod[2]) {
+    for (int i = first; i < last; i++) {
+        const uint64_t val[2] = {orc_mul(wires[1 + 2 * i], weights[i]), orc_mul(wires[2 + 2 * i], weights[i])};
+        const uint64_t term[2] = {orc_sub(x[0], domain[i]), x[1]};
+        uint64_t a[2], b[2];
+        x2_mul(eval, term, a);
+        x2_mul(val, prod, b);
+        eval[0] = orc_add(a[0], b[0]);
+        eval[1] = orc_add(a[1], b[1]);
+        x2_mul(prod, term, a);
+        prod[0] = a[0];
+        prod[1] = a[1];
+    }
+}
+
 /* eval_unfiltered of the gates; out[j] for j < num_constraints(gate); returns the constraint count.
  * consts = local_constants with the selector prefix removed (vars.remove_prefix(num_selectors)). */
 static int gate_eval_unfiltered(const orc_gate *g, const uint64_t *consts, const uint64_t *wires,
@@ -221,6 +254,34 @@ static int gate_eval_unfiltered(const orc_gate *g, const uint64_t *consts, const
             for (int i = 0; i < extra; i++) out[t++] = orc_sub(consts[i], wires[(2 + vec) * copies + i]);
             return t;
         }
+        case ORC_GATE_COSET_INTERPOLATION: {
+            /* wires: shift 0, values 1 + 2 i, evaluation point, evaluation value, then intermediate evals, intermediate
+             * prods and the shifted evaluation point.  evaluation_point - shifted_point * shift; the barycentric sum in
+             * chunks (the first of `degree` points, then degree - 1 each) with the running (eval, prod) pinned to wires
+             * after every chunk; evaluation_value - the last eval */
+            const int bits = g->param & 0xFF, degree = g->param >> 8, np = 1 << bits, ni = (np - 2) / (degree - 1);
+            const int ep = 1 + 2 * np, ev = ep + 2, im = ev + 2, sp = im + 4 * ni;
+            uint64_t domain[256], weights[256];
+            ci_tables(bits, domain, weights);
+            int t = 0;
+            out[t++] = orc_sub(wires[ep], orc_mul(wires[sp], wires[0]));
+            out[t++] = orc_sub(wires[ep + 1], orc_mul(wires[sp + 1], wires[0]));
+            uint64_t eval[2] = {0, 0}, prod[2] = {1, 0};
+            ci_partial(domain, weights, wires, 0, degree, wires + sp, eval, prod);
+            for (int i = 0; i < ni; i++) {
+                const uint64_t *ie = wires + im + 2 * i, *ip = wires + im + 2 * (ni + i);
+                out[t++] = orc_sub(ie[0], eval[0]);
+                out[t++] = orc_sub(ie[1], eval[1]);
+                out[t++] = orc_sub(ip[0], prod[0]);
+                out[t++] = orc_sub(ip[1], prod[1]);
+                const int start = 1 + (degree - 1) * (i + 1), end = start + degree - 1 < np ? start + degree - 1 : np;
+                eval[0] = ie[0], eval[1] = ie[1], prod[0] = ip[0], prod[1] = ip[1];
+                ci_partial(domain, weights, wires, start, end, wires + sp, eval, prod);
+            }
+            out[t++] = orc_sub(wires[ev], eval[0]);
+            out[t++] = orc_sub(wires[ev + 1], eval[1]);
+            return t;
+        }
         case ORC_GATE_POSEIDON_MDS: { /* output_r - (sum_i CIRC[i] input_{(i + r) % 12} + DIAG[r] input_r), component by component */
             for (int d = 0; d < 2; d++) {
                 uint64_t lane[12];
@@ -260,6 +321,10 @@ int orc_gate_num_constraints(const orc_gate *g) {
             return bits < 1 || bits > 8 || copies < 1 ? -1 : copies * (bits + 2) + extra;
         }
         case ORC_GATE_POSEIDON_MDS: return 24;
+        case ORC_GATE_COSET_INTERPOLATION: {
+            const int bits = g->param & 0xFF, degree = g->param >> 8;
+            return bits < 1 || bits > 8 || degree < 2 || degree > (1 << bits) ? -1 : 2 * (2 + 2 * (((1 << bits) - 2) / (degree - 1)));
+        }
         default: return -1;
     }
 }
@@ -516,6 +581,43 @@ int orc_vanishing_at_ext(const orc_circuit *c, const uint64_t zeta[2], const uin
                 }
                 for (int i = 0; i < extra; i++, k++)
                     terms[t + k] = e2_add(terms[t + k], e2_mul(f, e2_sub(EXT_AT(gc, i), EXT_AT(wires, (2 + vec) * copies + i))));
+                break;
+            }
+            case ORC_GATE_COSET_INTERPOLATION: { /* the same over the ExtensionAlgebra: elements (A0, A1) of F_p^2 pairs */
+                const int bits = g->param & 0xFF, degree = g->param >> 8, np = 1 << bits, ni = (np - 2) / (degree - 1);
+                const int ep = 1 + 2 * np, ev = ep + 2, im = ev + 2, sp = im + 4 * ni;
+                uint64_t domain[256], weights[256];
+                ci_tables(bits, domain, weights);
+                int k = 0;
+#define CI_EMIT(v) do { terms[t + k] = e2_add(terms[t + k], e2_mul(f, (v))); k++; } while (0)
+                const e2 shift = EXT_AT(wires, 0), x0 = EXT_AT(wires, sp), x1 = EXT_AT(wires, sp + 1);
+                CI_EMIT(e2_sub(EXT_AT(wires, ep), e2_mul(x0, shift)));
+                CI_EMIT(e2_sub(EXT_AT(wires, ep + 1), e2_mul(x1, shift)));
+                e2 ev0 = e2_of(0), ev1 = e2_of(0), pr0 = one, pr1 = e2_of(0);
+                int first = 0, last = degree;
+                for (int i = 0; i <= ni; i++) {
+                    for (int q = first; q < last; q++) { /* partial_interpolate */
+                        const e2 v0 = e2_scale(EXT_AT(wires, 1 + 2 * q), weights[q]), v1 = e2_scale(EXT_AT(wires, 2 + 2 * q), weights[q]);
+                        const e2 t0 = e2_sub(x0, e2_of(domain[q])), t1 = x1;
+                        /* (a0 + a1 X)(b0 + b1 X) = a0 b0 + 7 a1 b1 + (a0 b1 + a1 b0) X */
+                        const e2 n0 = e2_add(e2_add(e2_mul(ev0, t0), e2_scale(e2_mul(ev1, t1), 7)), e2_add(e2_mul(v0, pr0), e2_scale(e2_mul(v1, pr1), 7)));
+                        const e2 n1 = e2_add(e2_add(e2_mul(ev0, t1), e2_mul(ev1, t0)), e2_add(e2_mul(v0, pr1), e2_mul(v1, pr0)));
+                        const e2 p0 = e2_add(e2_mul(pr0, t0), e2_scale(e2_mul(pr1, t1), 7)), p1 = e2_add(e2_mul(pr0, t1), e2_mul(pr1, t0));
+                        ev0 = n0, ev1 = n1, pr0 = p0, pr1 = p1;
+                    }
+                    if (i == ni) break;
+                    const int ie = im + 2 * i, ip = im + 2 * (ni + i);
+                    CI_EMIT(e2_sub(EXT_AT(wires, ie), ev0));
+                    CI_EMIT(e2_sub(EXT_AT(wires, ie + 1), ev1));
+                    CI_EMIT(e2_sub(EXT_AT(wires, ip), pr0));
+                    CI_EMIT(e2_sub(EXT_AT(wires, ip + 1), pr1));
+                    ev0 = EXT_AT(wires, ie), ev1 = EXT_AT(wires, ie + 1), pr0 = EXT_AT(wires, ip), pr1 = EXT_AT(wires, ip + 1);
+                    first = 1 + (degree - 1) * (i + 1);
+                    last = first + degree - 1 < np ? first + degree - 1 : np;
+                }
+                CI_EMIT(e2_sub(EXT_AT(wires, ev), ev0));
+                CI_EMIT(e2_sub(EXT_AT(wires, ev + 1), ev1));
+#undef CI_EMIT
                 break;
             }
             case ORC_GATE_POSEIDON_MDS: { /* mds_layer_algebra: the matrix is over the base field, so every one of the four

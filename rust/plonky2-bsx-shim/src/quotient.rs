@@ -24,7 +24,7 @@ use crate::{as_words, with_ctx, words_to_field};
 
 /// `common_data.gates` + `common_data.selectors_info` as the table the library reads; None when a gate is not one of
 /// the kinds the library evaluates (Noop, Constant, PublicInput, Arithmetic, Poseidon, PoseidonMds, ArithmeticExtension,
-/// MulExtension, BaseSum<2>, Exponentiation, Reducing, ReducingExtension, RandomAccess up to 4 bits).
+/// MulExtension, BaseSum<2>, Exponentiation, Reducing, ReducingExtension, RandomAccess up to 4 bits, CosetInterpolation).
 pub fn gate_table<F: RichField + Extendable<D>, const D: usize>(common_data: &CommonCircuitData<F, D>) -> Option<Vec<sys::bsx_gate>> {
     let info = &common_data.selectors_info;
     common_data
@@ -68,6 +68,11 @@ pub fn gate_table<F: RichField + Extendable<D>, const D: usize>(common_data: &Co
                 (sys::BSX_GATE_RANDOM_ACCESS, bits | copies << 8 | extra << 16)
             } else if id.starts_with("PoseidonMdsGate") && D == 2 {
                 (sys::BSX_GATE_POSEIDON_MDS, 0)
+            } else if id.starts_with("CosetInterpolationGate") && D == 2 {
+                // "CosetInterpolationGate { subgroup_bits: b, degree: d, barycentric_weights: [..] }"; Gate::degree() is d
+                let at = id.find("subgroup_bits")? + "subgroup_bits".len();
+                let bits: i32 = id[at..].trim_start_matches(|ch: char| ch == ':' || ch == ' ').split(|ch: char| !ch.is_ascii_digit()).next()?.parse().ok()?;
+                (sys::BSX_GATE_COSET_INTERPOLATION, bits | (g.0.degree() as i32) << 8)
             } else {
                 return None;
             };

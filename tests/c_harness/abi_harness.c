@@ -12,7 +12,7 @@
  *   comm <G> <same_cap> <same_rows_paths> <same_proof>   the same commit and proof through bsx_comm_create with G ranks
  *                                      emulated on device 0 (bsx_sharded_from_values / bsx_sharded_prove_openings)
  *   fribytes <len> <fnv64>             bsx_fri_proof_bytes of that proof; layout <total_words> from bsx_fri_proof_layout
- *   qv <log_n> <fnv64> <first> <last>  bsx_quotient_values of a thirteen-kind gate table over three commitments of SplitMix columns
+ *   qv <log_n> <fnv64> <first> <last>  bsx_quotient_values of a fourteen-kind gate table over three commitments of SplitMix columns
  *   pgw <2 x 135 words>                bsx_poseidon_gate_witness on two rows (swap 0 and 1)
  * tests/test_gpu_c_abi.py recomputes every record with the oracle. */
 #include <inttypes.h>
@@ -225,20 +225,20 @@ int main(int argc, char **argv) {
         free(bytes);
     }
 
-    /* quotient evaluation with a thirteen-kind gate table (three selector groups) over random committed columns, and two
+    /* quotient evaluation with a fourteen-kind gate table (four selector groups) over random committed columns, and two
      * PoseidonGate rows from the device generator */
     {
-        const int qn = log_n < 7 ? log_n : 7, nc = 2, routed = 80, wires_w = 135, consts = 5, chunks = 10;
+        const int qn = log_n < 7 ? log_n : 7, nc = 2, routed = 80, wires_w = 135, consts = 6, chunks = 10;
         const size_t rows = (size_t)1 << qn;
-        bsx_gate gates[13] = {{BSX_GATE_NOOP, 0, 0, 0, 0, 6}, {BSX_GATE_CONSTANT, 2, 1, 0, 0, 6}, {BSX_GATE_PUBLIC_INPUT, 0, 2, 0, 0, 6},
+        bsx_gate gates[14] = {{BSX_GATE_NOOP, 0, 0, 0, 0, 6}, {BSX_GATE_CONSTANT, 2, 1, 0, 0, 6}, {BSX_GATE_PUBLIC_INPUT, 0, 2, 0, 0, 6},
                               {BSX_GATE_POSEIDON_MDS, 0, 3, 0, 0, 6}, {BSX_GATE_BASE_SUM, 32, 4, 0, 0, 6}, {BSX_GATE_REDUCING, 43, 5, 0, 0, 6},
                               {BSX_GATE_REDUCING_EXTENSION, 32, 6, 1, 6, 11}, {BSX_GATE_ARITHMETIC, 20, 7, 1, 6, 11},
                               {BSX_GATE_ARITHMETIC_EXTENSION, 10, 8, 1, 6, 11}, {BSX_GATE_MUL_EXTENSION, 13, 9, 1, 6, 11},
                               {BSX_GATE_EXPONENTIATION, 66, 10, 1, 6, 11}, {BSX_GATE_RANDOM_ACCESS, 4 | 4 << 8 | 2 << 16, 11, 2, 11, 13},
-                              {BSX_GATE_POSEIDON, 0, 12, 2, 11, 13}};
+                              {BSX_GATE_COSET_INTERPOLATION, 4 | 6 << 8, 12, 2, 11, 13}, {BSX_GATE_POSEIDON, 0, 13, 3, 13, 14}};
         uint64_t k_is[80];
         for (int j = 0; j < routed; j++) k_is[j] = splitmix(seed + 400, (uint64_t)j);
-        bsx_circuit circ = {qn, 3, 8, nc, wires_w, routed, consts, 3, chunks - 1, 123, 13, gates, k_is};
+        bsx_circuit circ = {qn, 3, 8, nc, wires_w, routed, consts, 4, chunks - 1, 123, 14, gates, k_is};
         const int widths[3] = {consts + routed, wires_w, nc * chunks};
         bsx_batch *b3[3] = {NULL, NULL, NULL};
         for (int k = 0; k < 3; k++) {

@@ -146,7 +146,7 @@ def main():
                   "proof_bytes_sha256": hashlib.sha256(pw.to_bytes(aux["fri_params"], aux["widths"])).hexdigest(),
                   "proof_bytes_len": len(pw.to_bytes(aux["fri_params"], aux["widths"]))}
     # gates beyond the basic four: two PoseidonGate rows (gates/poseidon.rs wire map; row 1 with swap = 1) and the quotient
-    # values of a 64-row circuit with every gate kind in three selector groups (synthetic_circuit(gate_set="all"))
+    # values of a 64-row circuit with every gate kind in four selector groups (synthetic_circuit(gate_set="all"))
     rows = np.zeros((2, 135), dtype=np.uint64)
     rows[:, :12] = splitmix_field(80, (2, 12))
     rows[1, 24] = 1

@@ -1,15 +1,15 @@
 """The gates beyond the four basic ones in the quotient evaluation: gates/poseidon.rs PoseidonGate,
 gates/arithmetic_extension.rs ArithmeticExtensionGate<2>, gates/multiplication_extension.rs MulExtensionGate<2>,
 gates/base_sum.rs BaseSumGate<2>, gates/exponentiation.rs ExponentiationGate, gates/reducing.rs ReducingGate<2>,
-gates/reducing_extension.rs ReducingExtensionGate<2>, gates/random_access.rs RandomAccessGate<2> and gates/poseidon_mds.rs
-PoseidonMdsGate<2>, on a synthetic circuit with three selector groups.
+gates/reducing_extension.rs ReducingExtensionGate<2>, gates/random_access.rs RandomAccessGate<2>, gates/poseidon_mds.rs
+PoseidonMdsGate<2> and gates/coset_interpolation.rs CosetInterpolationGate<2>, on a synthetic circuit with four selector groups.
 
 CPU tier: the oracle's constraints are checked through what defines them -- a witness produced by the generators makes
 the vanishing polynomial divisible by Z_H (the verifier identity holds at a random point), a single changed wire on a row
 of each gate kind breaks it; PoseidonGate rows reproduce the permutation; and the naive partial rounds the restatement
 uses give the constraint values of upstream's factored form for ARBITRARY wires.
 GPU tier: bsx_poseidon_gate_witness equals the oracle's generator, bsx_quotient_values equals the oracle's quotient values
-word for word with all thirteen gate kinds (satisfying and random wires), and whole device proofs are accepted by the
+word for word with all fourteen gate kinds (satisfying and random wires), and whole device proofs are accepted by the
 verifier restatement (which evaluates the gates over the extension field)."""
 import os
 import sys
@@ -22,7 +22,7 @@ import __graft_entry__ as G
 from test_quotient import _challenges, _device_commitments, _identity_holds, _oracle_commitments, _pis_and_circuit
 
 POSEIDON, ARITH_EXT, MUL_EXT, BASE_SUM = 4, 5, 6, 7
-EXPONENTIATION, REDUCING, REDUCING_EXT, RANDOM_ACCESS, POSEIDON_MDS = 8, 9, 10, 11, 12
+EXPONENTIATION, REDUCING, REDUCING_EXT, RANDOM_ACCESS, POSEIDON_MDS, COSET_INTERPOLATION = 8, 9, 10, 11, 12, 13
 
 
 @pytest.fixture(scope="module")
@@ -86,8 +86,8 @@ def test_oracle_identity_with_every_gate_kind(pkg, oracle, degree_bits, kw):
     c = sc.circuit
     kinds = sorted(g.kind for g in c.gates)
     big = c.num_wires >= 135
-    assert kinds == (list(range(13)) if big else [0, 1, 2, 3, 5, 6, 7, 8, 9, 10, 11])  # 40 wires: no Poseidon / PoseidonMds
-    assert c.num_selectors == 3 and c.num_gate_constraints == (123 if big else 33)
+    assert kinds == (list(range(14)) if big else [0, 1, 2, 3, 5, 6, 7, 8, 9, 10, 11, 13])  # 40 wires: no Poseidon / PoseidonMds
+    assert c.num_selectors == 4 and c.num_gate_constraints == (123 if big else 33)
     for g in c.gates:  # a run of rows of every kind
         assert (sc.constants[g.selector_index] == g.row).any(), g
     betas, gammas, alphas = _challenges(31, c.num_challenges)
@@ -100,6 +100,14 @@ def test_oracle_identity_with_every_gate_kind(pkg, oracle, degree_bits, kw):
                (EXPONENTIATION, 0), (EXPONENTIATION, 1 + n_exp), (EXPONENTIATION, 2 + n_exp + 3), (REDUCING, 2), (REDUCING, 7),
                (REDUCING, 0), (REDUCING_EXT, 5), (REDUCING_EXT, 9), (RANDOM_ACCESS, 0), (RANDOM_ACCESS, 1),
                (RANDOM_ACCESS, ra_bit0 + 1), (RANDOM_ACCESS, ra_bit0 - 1)]
+    ci = next(g.param for g in c.gates if g.kind == COSET_INTERPOLATION)
+    ci_np = 1 << (ci & 0xFF)
+    # shift, a value, the evaluation point, the evaluation value, the shifted point (last two wires of the gate)
+    ci_end = 1 + 2 * ci_np + 4 + 4 * ((ci_np - 2) // ((ci >> 8) - 1)) + 2
+    tampers += [(COSET_INTERPOLATION, 0), (COSET_INTERPOLATION, 4), (COSET_INTERPOLATION, 1 + 2 * ci_np),
+                (COSET_INTERPOLATION, 3 + 2 * ci_np), (COSET_INTERPOLATION, ci_end - 1)]
+    if (ci_np - 2) // ((ci >> 8) - 1):
+        tampers += [(COSET_INTERPOLATION, 5 + 2 * ci_np), (COSET_INTERPOLATION, ci_end - 3)]  # an intermediate eval / prod
     if big:
         tampers += [(POSEIDON, 3), (POSEIDON, 24), (POSEIDON, 26), (POSEIDON, 40), (POSEIDON, 70), (POSEIDON, 100), (POSEIDON, 13),
                     (POSEIDON_MDS, 5), (POSEIDON_MDS, 30)]
@@ -110,6 +118,29 @@ def test_oracle_identity_with_every_gate_kind(pkg, oracle, degree_bits, kw):
         assert not _identity_holds(oracle, sc, betas, gammas, alphas)[0], (kind, wire)
         sc.wires[wire, row] = keep
     assert _identity_holds(oracle, sc, betas, gammas, alphas)[0]
+
+
+def test_coset_interpolation_rows_hold_the_interpolant(pkg, oracle):
+    """what the gate is for: evaluation_value = the polynomial through (shift * g^i, value_i), i < 2^bits, at evaluation_point,
+    in F_p[X] / (X^2 - 7) -- plain Lagrange interpolation on python ints against the generated row"""
+    sc = pkg.synthetic_circuit(6, seed=6, gate_set="all", poseidon_fill=oracle.poseidon_gate_fill)
+    g = next(g for g in sc.circuit.gates if g.kind == COSET_INTERPOLATION)
+    bits, npts = g.param & 0xFF, 1 << (g.param & 0xFF)
+    row = _row_of(sc, COSET_INTERPOLATION)
+    w = [int(x) for x in sc.wires[:, row]]
+    mul = lambda a, b: ((a[0] * b[0] + 7 * a[1] * b[1]) % P, (a[0] * b[1] + a[1] * b[0]) % P)
+    gen = pow(1753635133440165772, 1 << (32 - bits), P)
+    xs = [w[0] * pow(gen, i, P) % P for i in range(npts)]
+    z = (w[1 + 2 * npts], w[2 + 2 * npts])
+    acc = (0, 0)
+    for i in range(npts):
+        term = (w[1 + 2 * i], w[2 + 2 * i])
+        for j in range(npts):
+            if j != i:
+                inv = pow((xs[i] - xs[j]) % P, P - 2, P)
+                term = mul(term, ((z[0] - xs[j]) * inv % P, z[1] * inv % P))
+        acc = ((acc[0] + term[0]) % P, (acc[1] + term[1]) % P)
+    assert acc == (w[3 + 2 * npts], w[4 + 2 * npts])
 
 
 def test_base_sum_limbs_must_be_bits(pkg, oracle):
@@ -238,7 +269,7 @@ def test_device_proof_with_every_gate_kind_is_accepted(pkg, ctx, oracle, degree_
     ok, why = plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)
     assert ok, why
     for kind, wire in ((POSEIDON, 77), (ARITH_EXT, 7), (BASE_SUM, 2), (EXPONENTIATION, 0), (REDUCING_EXT, 3), (RANDOM_ACCESS, 1),
-                       (POSEIDON_MDS, 47)):
+                       (POSEIDON_MDS, 47), (COSET_INTERPOLATION, 9)):
         row = _row_of(sc, kind)
         keep = sc.wires[wire, row]
         sc.wires[wire, row] = (int(keep) + 1) % P

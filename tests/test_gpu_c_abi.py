@@ -82,15 +82,15 @@ def test_c_program_matches_oracle(oracle, log_n, n_cols, rate_bits, cap_height, 
         fnv = ((fnv ^ b) * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
     fb = by["fribytes"][0]
     assert int(fb[0]) == len(data) and int(fb[1], 16) == fnv and int(fb[2]) == proof.size and int(fb[3]) == int(proof[-1])
-    # quotient evaluation over the thirteen-kind gate table and the PoseidonGate generator: same streams as the C program
+    # quotient evaluation over the fourteen-kind gate table and the PoseidonGate generator: same streams as the C program
     qn = min(log_n, 7)
     kinds = [(0, 0, 0, 0, 0, 6), (1, 2, 1, 0, 0, 6), (2, 0, 2, 0, 0, 6), (12, 0, 3, 0, 0, 6), (7, 32, 4, 0, 0, 6), (9, 43, 5, 0, 0, 6),
              (10, 32, 6, 1, 6, 11), (3, 20, 7, 1, 6, 11), (5, 10, 8, 1, 6, 11), (6, 13, 9, 1, 6, 11), (8, 66, 10, 1, 6, 11),
-             (11, 4 | 4 << 8 | 2 << 16, 11, 2, 11, 13), (4, 0, 12, 2, 11, 13)]
+             (11, 4 | 4 << 8 | 2 << 16, 11, 2, 11, 13), (13, 4 | 6 << 8, 12, 2, 11, 13), (4, 0, 13, 3, 13, 14)]
     circ = {"degree_bits": qn, "rate_bits": 3, "quotient_degree_factor": 8, "num_challenges": 2, "num_wires": 135,
-            "num_routed_wires": 80, "num_constants": 5, "num_selectors": 3, "num_partial_products": 9, "num_gate_constraints": 123,
+            "num_routed_wires": 80, "num_constants": 6, "num_selectors": 4, "num_partial_products": 9, "num_gate_constraints": 123,
             "gates": kinds, "k_is": splitmix_field(seed + 400, (80,))}
-    bs = [oracle.batch_from_values(splitmix_field(seed + 500 + k, (w, 1 << qn)), 3, 0) for k, w in enumerate((85, 135, 20))]
+    bs = [oracle.batch_from_values(splitmix_field(seed + 500 + k, (w, 1 << qn)), 3, 0) for k, w in enumerate((86, 135, 20))]
     s0 = seed % P
     qv = oracle.quotient_values(circ, bs[0], bs[1], bs[2], [s0, 1, 2, 3], [s0 + 6, s0 + 7], [s0 + 8, s0 + 9], [s0 + 10, s0 + 11])
     fnv = 0

@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""Device time of the quotient evaluation (bsx_quotient_values) at the headline shape: constants+sigmas (84 / 85 columns),
+"""Device time of the quotient evaluation (bsx_quotient_values) at the headline shape: constants+sigmas (84 / 86 columns),
 wires (135) and Zs + partial products (20) committed from random columns at 2^20 rows, rate_bits 3; the kernel reads
 the three resident LDEs (15.3 GB) and writes 2 x 2^23 quotient values."""
 import os, sys
