@@ -415,8 +415,9 @@ int32_t bsx_partial_products_and_zs(bsx_ctx *ctx, const uint64_t *wires, const u
 
 /* ---- quotient evaluation on the device (plonk/prover.rs compute_quotient_polys) ------------------------------
  * The circuit as compute_quotient_polys and plonk/vanishing_poly.rs eval_vanishing_poly_base_batch read it from
- * CommonCircuitData / CircuitConfig.  Gates are data, not code: a table of (kind, parameter, selector info); the four
- * kinds below are built in (gates/noop.rs, constant.rs, public_input.rs, arithmetic_base.rs).  `row` is the gate's index
+ * CommonCircuitData / CircuitConfig.  Gates are data, not code: a table of (kind, parameter, selector info); the fourteen
+ * kinds below are built in (the gates of plonky2's own recursion circuits; extension gates for D = 2); any other kind makes
+ * the calls below fail with BSX_ERR_INVALID_ARG.  `row` is the gate's index
  * in common_data.gates (the value its selector polynomial takes on rows that use it), selector_index / group_* are
  * selectors_info.selector_indices[row] and selectors_info.groups[selector_index]. */
 #define BSX_GATE_NOOP 0
