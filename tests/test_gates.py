@@ -171,6 +171,28 @@ def test_random_access_bits_must_match_the_index(pkg, oracle):
     assert _identity_holds(oracle, sc, betas, gammas, alphas)[0]
 
 
+def test_oracle_proof_with_every_gate_kind_verifies(pkg, oracle):
+    """The whole prove() flow on the CPU oracle for a circuit with all fourteen kinds, checked by the verifier restatement:
+    this is the CPU-tier test of the F_p^2 gate evaluators (ExtensionAlgebra for the extension gates), which otherwise only
+    the GPU tier's whole-proof tests reach.  One changed wire on a row of each kind and the vanishing identity fails."""
+    import plonk_verifier
+    from test_quotient import _oracle_prove
+    public_inputs, sc = _pis_and_circuit(pkg, oracle, 6, 9, gate_set="all", poseidon_fill=oracle.poseidon_gate_fill)
+    cfg = pkg.FriConfig(rate_bits=sc.circuit.rate_bits, cap_height=1, proof_of_work_bits=4, num_query_rounds=3)
+    pw, aux = _oracle_prove(pkg, oracle, sc, cfg, public_inputs)
+    ok, why = plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw, aux)
+    assert ok, why
+    for kind, wire in ((POSEIDON, 66), (POSEIDON_MDS, 40), (ARITH_EXT, 3), (MUL_EXT, 4), (BASE_SUM, 1), (EXPONENTIATION, 2),
+                       (REDUCING, 4), (REDUCING_EXT, 6), (RANDOM_ACCESS, 1), (COSET_INTERPOLATION, 2)):
+        row = _row_of(sc, kind)
+        keep = sc.wires[wire, row]
+        sc.wires[wire, row] = (int(keep) + 1) % P
+        pw_bad, aux_bad = _oracle_prove(pkg, oracle, sc, cfg, public_inputs)
+        ok, why = plonk_verifier.verify(oracle, sc.circuit.as_dict(), pw_bad, aux_bad)
+        assert not ok and "vanishing" in why, (kind, wire)
+        sc.wires[wire, row] = keep
+
+
 # ------------------------------------------------------------------------------------------ GPU tier
 @pytest.fixture(scope="module")
 def ctx(pkg):
